@@ -1,0 +1,152 @@
+/*
+ * phasm_ovl.h -- C ABI of the B200 (sm_100a) exact overlapper: the drop-in boundary for
+ * PHASM's `phasm overlap` hot path.
+ *
+ * Every entry point names the reference interface it replaces (paths relative to the
+ * AbeelLab/phasm checkout).  Plain pointers and sizes only; no C++/torch/pybind11 types.
+ * The library is built by `__graft_entry__.build()` into phasm_b200/_lib/libphasm_ovl.so.
+ *
+ * Conventions
+ *   - every call returns 0 on success, a negative OVL_E_* code on failure;
+ *     ovl_last_error() gives the message (a NULL ctx returns the last ovl_create error).
+ *   - an ovl_ctx is bound to one CUDA device and is NOT thread-safe (the reference object is
+ *     not either: src/phasm.cpp:12-15 holds the GIL for the whole call).
+ *   - there is NO CPU fallback: without a usable CUDA device ovl_create fails.
+ */
+#ifndef PHASM_OVL_H
+#define PHASM_OVL_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define OVL_OK            0
+#define OVL_E_CUDA       -1  /* CUDA runtime / driver error (-> RuntimeError)            */
+#define OVL_E_NOMEM      -2  /* host or device allocation failed (-> MemoryError)        */
+#define OVL_E_ALPHABET   -3  /* a base outside upper-case ACGT (-> ValueError); the       */
+                             /* reference compares raw bytes (src/overlapper.h:26), the  */
+                             /* 2-bit device layout cannot: documented deviation         */
+#define OVL_E_ARG        -4  /* bad argument / bad call order                            */
+#define OVL_E_LIMIT      -5  /* a size limit of the device layout was exceeded           */
+#define OVL_E_NCCL       -6  /* NCCL error in the multi-GPU path                         */
+
+typedef struct ovl_ctx ovl_ctx;
+
+/* One overlap row.  Replaces OverlapT = tuple<string,string,int,int,int,int>
+ * (src/overlapper.h:17): a and b index the entry table (ovl_entry_id gives the strings);
+ * bstart is always 0 in the reference (src/overlapper.cpp:81,109) and is not stored. */
+typedef struct {
+    uint32_t a;      /* entry whose suffix / substring matches        */
+    uint32_t b;      /* entry whose prefix / whole sequence matches   */
+    uint32_t astart;
+    uint32_t aend;
+    uint32_t bend;
+} ovl_row;
+
+/* Counters and device-side stage times of the last ovl_overlaps* call. */
+typedef struct {
+    uint64_t entries;          /* M                                                       */
+    uint64_t bases;            /* sum of entry lengths (both strands when added as reads) */
+    uint64_t ascii_bytes;      /* host->device bytes of sequence data                     */
+    uint64_t granules;         /* 64-base packed granules (16 B each)                     */
+    uint64_t anchors;          /* entries with |b| >= min_length                          */
+    uint64_t anchor_keys;      /* distinct prefix k-mers                                  */
+    uint64_t candidates;       /* (a,p,b) emitted by the scan                             */
+    uint64_t hits;             /* candidates that verified                                */
+    uint64_t rows;
+    uint64_t compared_bases;   /* sum m_c (only when stats collection is on, else 0)      */
+    uint64_t operand_bytes;    /* sum 2*ceil(m_c/4), idem                                 */
+    uint64_t scan_positions;   /* A positions with |a|-p >= min_length                    */
+    uint32_t kmer;             /* anchor length k = min(max(l,1),32)                      */
+    uint32_t launches;         /* kernels of this library launched by the call            */
+    uint32_t lib_launches;     /* CUB device-wide primitive calls (sort / scan)           */
+    uint32_t retries;          /* scan re-runs after a candidate-buffer overflow          */
+    float ms_h2d, ms_pack, ms_anchor, ms_scan, ms_verify, ms_emit, ms_d2h;
+    float ms_device;           /* pack..emit: ASCII resident in HBM -> rows resident      */
+    float ms_total;            /* h2d..d2h                                                */
+} ovl_stats;
+
+/* ---- lifetime -------------------------------------------------------------------------
+ * Replaces ExactOverlapper::ExactOverlapper() (src/overlapper.cpp:19, src/phasm.cpp:13). */
+int ovl_create(int device, ovl_ctx **out);
+void ovl_destroy(ovl_ctx *ctx);
+const char *ovl_last_error(const ovl_ctx *ctx);
+
+/* ---- entry store ----------------------------------------------------------------------
+ * ovl_add_sequence replaces ExactOverlapper::addSequence(id, seq) (src/overlapper.cpp:22-26,
+ * bound as add_sequence in src/phasm.cpp:14): id and seq are COPIED, the caller keeps
+ * ownership; ids are opaque bytes (duplicates allowed). */
+int ovl_add_sequence(ovl_ctx *ctx, const char *id, size_t id_len, const char *seq, size_t seq_len);
+
+/* ovl_add_read replaces the pair of calls phasm/cli/assembler.py:39-40 makes per FASTA
+ * record: entry 2i = (name+"+", seq), entry 2i+1 = (name+"-", reverse_complement(seq)).
+ * The sequence is staged once; the reverse complement is produced on the device. */
+int ovl_add_read(ovl_ctx *ctx, const char *name, size_t name_len, const char *seq, size_t seq_len);
+
+/* Bulk form of ovl_add_read / ovl_add_sequence: n records, record i is
+ * buf[offsets[i] .. offsets[i+1]); names may be NULL (ids are then empty) or a blob with
+ * name_offsets[n+1].  both_strands != 0 adds "+" and "-" entries per record. */
+int ovl_add_bulk(ovl_ctx *ctx, const uint8_t *buf, const uint64_t *offsets, uint32_t n,
+                 const char *names, const uint64_t *name_offsets, int both_strands);
+
+/* Pre-size the pinned host staging area (optional; avoids regrowth while adding). */
+int ovl_reserve(ovl_ctx *ctx, uint64_t seq_bytes, uint32_t n_entries);
+
+/* Multi-GPU only: declare n records whose BASES live on another rank (only their lengths are
+ * known here).  Together with the local records they must form the same entry table, in the
+ * same order, on every rank; ids of remote entries are "" (+ strand suffix). */
+int ovl_add_remote(ovl_ctx *ctx, const uint32_t *lengths, uint32_t n, int both_strands);
+
+int ovl_clear(ovl_ctx *ctx); /* drop all entries, keep device buffers */
+
+int ovl_entry_count(const ovl_ctx *ctx, uint32_t *m);
+int ovl_entry_id(const ovl_ctx *ctx, uint32_t idx, const char **id, size_t *id_len);
+int ovl_entry_length(const ovl_ctx *ctx, uint32_t idx, uint32_t *len);
+
+/* ---- the hot path ----------------------------------------------------------------------
+ * ovl_overlaps replaces ExactOverlapper::overlaps(min_length) (src/overlapper.cpp:28-150,
+ * bound in src/phasm.cpp:15): host buffers in, host rows out.  min_length 0 behaves as 1
+ * like the reference.  *rows points into memory owned by ctx, valid until the next
+ * ovl_overlaps* / ovl_clear / ovl_destroy call.  Rows are sorted by (a,b,astart,aend,bend);
+ * the reference's order is unspecified so any comparison sorts.
+ * An empty entry table returns 0 rows (the reference segfaults there). */
+int ovl_overlaps(ovl_ctx *ctx, uint32_t min_length, const ovl_row **rows, uint64_t *n_rows);
+
+/* The same call split at the PCIe boundary, for device-resident timing:
+ *   ovl_upload          host ASCII -> HBM (no-op if nothing was added since the last upload)
+ *   ovl_overlaps_device pack .. emit, rows stay in HBM
+ *   ovl_fetch_rows      HBM -> host rows                                                  */
+int ovl_upload(ovl_ctx *ctx);
+int ovl_overlaps_device(ovl_ctx *ctx, uint32_t min_length, uint64_t *n_rows);
+int ovl_fetch_rows(ovl_ctx *ctx, const ovl_row **rows, uint64_t *n_rows);
+
+/* Collect sum m_c / operand bytes in the verifier (adds a little work; off by default). */
+int ovl_set_collect_stats(ovl_ctx *ctx, int on);
+int ovl_get_stats(const ovl_ctx *ctx, ovl_stats *out);
+
+/* ---- multi-GPU (one process per GPU) ---------------------------------------------------
+ * All ranks add the SAME entry table in the same order; rank r scans only the A entries of
+ * its contiguous, base-balanced range and returns only those rows.  The rank's packed reads
+ * and prefix anchors are exchanged with ncclAllGather over NVLink (libnccl is dlopen'ed on
+ * first use).  ovl_comm_unique_id fills a 128-byte NCCL id on rank 0, the caller ships it to
+ * the other ranks (torch.distributed, a file, ...) and every rank calls ovl_comm_init. */
+int ovl_comm_unique_id(uint8_t id_out[128]);
+int ovl_comm_init(ovl_ctx *ctx, const uint8_t id[128], int rank, int nranks);
+/* After ovl_upload on every rank: exchange the local entry ranges and check that they tile the
+ * entry table in rank order. */
+int ovl_comm_sync_ranges(ovl_ctx *ctx);
+/* Gather every rank's rows to rank 0 (rank order == canonical order); other ranks get 0. */
+int ovl_comm_gather_rows(ovl_ctx *ctx, const ovl_row **rows, uint64_t *n_rows);
+
+/* ---- debug / test hooks (device layout introspection) -----------------------------------
+ * Copy the 2-bit packed granules of entry idx (ceil(len/64)*16 bytes) to out; used by the
+ * pack / reverse-complement parity tests. */
+int ovl_debug_packed(ovl_ctx *ctx, uint32_t idx, uint8_t *out, size_t out_cap, size_t *out_len);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* PHASM_OVL_H */

@@ -1,0 +1,956 @@
+// ovl.cu -- host side of libphasm_ovl.so: the C ABI of include/phasm_ovl.h over the sm_100a
+// kernels K0..K5.  No torch, no pybind11, no CPU compute path: every ovl_overlaps* call runs
+// the CUDA pipeline or fails.
+//
+// Pipeline of one ovl_overlaps_device() call (reference: ExactOverlapper::overlaps,
+// /root/reference/src/overlapper.cpp:28-150):
+//
+//   K0 k0_gran_entry   granule -> entry map
+//   K1 k1_pack         ASCII -> 2-bit granules, "-" entries reverse-complemented on the fly
+//   K2 select/keys/sort/build   prefix anchors of all entries with |b| >= l, hash table + bloom
+//   K3 k3_scan         every A position with |a|-p >= l probes the anchors -> candidates
+//   K4 k4_verify       warp per candidate compares a[p:] with b[0:] -> 64-bit hit keys
+//   K5 sort/count/scan/emit     longest suffix-prefix per pair + all containments -> rows
+//
+// Device-wide sort / select / prefix-sum come from CUB (ships with CUDA 12.9); everything else
+// is in the k*.cuh files next to this one.
+#include <cstdarg>
+#include <cstdio>
+#include <cstdlib>
+#include <cstring>
+#include <new>
+#include <string>
+#include <vector>
+
+#include <cub/cub.cuh>
+#include <cuda_runtime.h>
+
+#include "../../include/phasm_ovl.h"
+#include "k1_pack.cuh"
+#include "k2_anchor.cuh"
+#include "k3_scan.cuh"
+#include "k4_verify.cuh"
+#include "k5_emit.cuh"
+#include "nccl_dyn.h"
+
+static_assert(sizeof(ovl_row) == sizeof(ovl::Row), "row layouts must agree");
+static_assert(sizeof(ovl_row) == 20, "ovl_row is 5 x u32");
+
+namespace {
+
+constexpr uint64_t NO_SRC = ~0ull;  // entry whose bases live on another rank
+constexpr size_t SLACK = 16;        // bytes of slack at both ends of the ASCII staging area
+
+thread_local std::string g_create_err;
+
+struct DevBuf {
+    void* p = nullptr;
+    size_t cap = 0;
+    template <class T> T* as() const { return static_cast<T*>(p); }
+};
+
+struct PinBuf {
+    uint8_t* p = nullptr;
+    size_t cap = 0;
+};
+
+enum Ev { E_H2D0, E_PACK0, E_ANCHOR0, E_SCAN0, E_VERIFY0, E_EMIT0, E_END, E_D2H0, E_D2H1, E_COUNT };
+
+// device counter block (one 64-bit word each)
+enum Ctr { C_ERR, C_NANC, C_NKEYS, C_NCAND, C_NHITS, C_SELF, C_SUMM, C_SUMB, C_COUNT };
+
+}  // namespace
+
+struct ovl_ctx {
+    int device = 0;
+    int n_sm = 148;
+    cudaStream_t st = nullptr, st_comm = nullptr;
+    cudaEvent_t ev[E_COUNT] = {};
+    cudaEvent_t ev_comm = nullptr, ev_pack = nullptr;
+    std::string err;
+
+    // ---- host entry store ----
+    PinBuf ascii;            // [SLACK][record, 16-byte aligned]...[SLACK]
+    size_t ascii_used = SLACK;
+    std::vector<uint64_t> src;   // byte offset of the entry's record, NO_SRC if remote
+    std::vector<uint32_t> len;
+    std::vector<uint8_t> flags;  // bit0: reverse complement of the record
+    std::vector<char> id_blob;
+    std::vector<uint64_t> id_off{0};
+    std::vector<uint32_t> gran0;
+    uint64_t bases = 0, max_len = 0;
+    bool uploaded = false;
+    uint32_t e_lo = 0, e_hi = 0;  // entries whose bases are local (contiguous)
+
+    // ---- device ----
+    DevBuf d_ascii, d_src, d_len, d_flags, d_gran0, d_gran_ent, d_packed;
+    DevBuf d_anc_ent, d_anc_ent2, d_keys, d_keys2, d_table, d_filter, d_ctr, d_tmp;
+    DevBuf d_cand, d_hits, d_hits2, d_cnt, d_offs, d_rows;
+    uint64_t* h_ctr = nullptr;  // pinned mirror of d_ctr
+    uint64_t cand_cap = 0;
+    uint64_t n_rows = 0;
+    PinBuf h_rows;
+    bool rows_fetched = false;
+    int collect = 0;
+    ovl_stats stats{};
+
+    // ---- multi-GPU ----
+    ncclComm_t comm = nullptr;
+    int rank = 0, nranks = 1;
+    std::vector<uint32_t> rank_e;  // [nranks+1] entry range of every rank
+    PinBuf h_gather;
+};
+
+namespace {
+
+int fail(ovl_ctx* c, int code, const char* fmt, ...) {
+    char buf[512];
+    va_list ap;
+    va_start(ap, fmt);
+    vsnprintf(buf, sizeof buf, fmt, ap);
+    va_end(ap);
+    if (c) c->err = buf; else g_create_err = buf;
+    return code;
+}
+
+#define CK(call)                                                                              \
+    do {                                                                                      \
+        cudaError_t e_ = (call);                                                              \
+        if (e_ != cudaSuccess)                                                                \
+            return fail(c, e_ == cudaErrorMemoryAllocation ? OVL_E_NOMEM : OVL_E_CUDA,        \
+                        "CUDA error %s at %s:%d: %s", cudaGetErrorName(e_), __FILE__, __LINE__, \
+                        cudaGetErrorString(e_));                                              \
+    } while (0)
+
+#define CKN(call)                                                                             \
+    do {                                                                                      \
+        ncclResult_t r_ = (call);                                                             \
+        if (r_ != ncclSuccess)                                                                \
+            return fail(c, OVL_E_NCCL, "NCCL error %d at %s:%d: %s", (int)r_, __FILE__,       \
+                        __LINE__, nccl_dyn::api().GetErrorString(r_));                        \
+    } while (0)
+
+#define OVL_TRY(expr)                  \
+    do {                               \
+        int rc_ = (expr);              \
+        if (rc_ != OVL_OK) return rc_; \
+    } while (0)
+
+int dev_ensure(ovl_ctx* c, DevBuf& b, size_t bytes, bool slack = true) {
+    if (bytes <= b.cap) return OVL_OK;
+    if (b.p) CK(cudaFree(b.p));
+    b.p = nullptr;
+    b.cap = 0;
+    size_t want = slack ? bytes + bytes / 8 + 256 : bytes;
+    cudaError_t e = cudaMalloc(&b.p, want);
+    if (e != cudaSuccess && want != bytes) {
+        (void)cudaGetLastError();
+        want = bytes;
+        e = cudaMalloc(&b.p, want);
+    }
+    if (e != cudaSuccess) {
+        (void)cudaGetLastError();
+        b.p = nullptr;
+        return fail(c, OVL_E_NOMEM, "cudaMalloc of %zu bytes failed: %s", want, cudaGetErrorString(e));
+    }
+    b.cap = want;
+    return OVL_OK;
+}
+
+int pin_ensure(ovl_ctx* c, PinBuf& b, size_t bytes, size_t keep) {
+    if (bytes <= b.cap) return OVL_OK;
+    size_t want = b.cap ? b.cap : 4096;
+    while (want < bytes) want += want / 2 + 4096;
+    uint8_t* np = nullptr;
+    cudaError_t e = cudaHostAlloc(reinterpret_cast<void**>(&np), want, cudaHostAllocDefault);
+    if (e != cudaSuccess) {
+        (void)cudaGetLastError();
+        return fail(c, OVL_E_NOMEM, "cudaHostAlloc of %zu bytes failed: %s", want, cudaGetErrorString(e));
+    }
+    if (b.p) {
+        if (keep) memcpy(np, b.p, keep);
+        cudaFreeHost(b.p);
+    }
+    b.p = np;
+    b.cap = want;
+    return OVL_OK;
+}
+
+inline int ceil_log2(uint64_t x) {
+    int b = 0;
+    while ((1ull << b) < x) ++b;
+    return b;
+}
+
+inline size_t align16(size_t x) { return (x + 15) & ~size_t(15); }
+
+struct LenGE {
+    const uint32_t* len;
+    uint32_t l;
+    __device__ __forceinline__ bool operator()(uint32_t e) const { return len[e] >= l; }
+};
+
+int push_entry(ovl_ctx* c, const char* id, size_t id_len, const char* sfx, uint64_t src, uint64_t n,
+               uint8_t fl) {
+    if (n > 0xfffffff0ull) return fail(c, OVL_E_LIMIT, "sequence of %llu bases exceeds the 32-bit position limit", (unsigned long long)n);
+    if (c->len.size() >= 0xfffffff0ull) return fail(c, OVL_E_LIMIT, "too many entries");
+    c->src.push_back(src);
+    c->len.push_back((uint32_t)n);
+    c->flags.push_back(fl);
+    if (id_len) c->id_blob.insert(c->id_blob.end(), id, id + id_len);
+    if (sfx) c->id_blob.push_back(*sfx);
+    c->id_off.push_back(c->id_blob.size());
+    c->bases += n;
+    if (n > c->max_len) c->max_len = n;
+    c->uploaded = false;
+    return OVL_OK;
+}
+
+// copy one record into the pinned staging area; returns its byte offset
+int stage_record(ovl_ctx* c, const char* seq, size_t n, uint64_t* off) {
+    const size_t need = c->ascii_used + align16(n) + SLACK;
+    OVL_TRY(pin_ensure(c, c->ascii, need, c->ascii_used));
+    *off = c->ascii_used;
+    if (n) memcpy(c->ascii.p + c->ascii_used, seq, n);
+    c->ascii_used += align16(n);
+    return OVL_OK;
+}
+
+int set_dev(ovl_ctx* c) {
+    CK(cudaSetDevice(c->device));
+    return OVL_OK;
+}
+
+float ev_ms(ovl_ctx* c, int a, int b) {
+    float ms = 0.f;
+    if (cudaEventElapsedTime(&ms, c->ev[a], c->ev[b]) != cudaSuccess) {
+        (void)cudaGetLastError();
+        return 0.f;
+    }
+    return ms;
+}
+
+// read the device counter block (synchronises the compute stream)
+int read_ctr(ovl_ctx* c) {
+    CK(cudaMemcpyAsync(c->h_ctr, c->d_ctr.p, C_COUNT * sizeof(uint64_t), cudaMemcpyDeviceToHost, c->st));
+    CK(cudaStreamSynchronize(c->st));
+    return OVL_OK;
+}
+
+}  // namespace
+
+// =========================================================================================
+extern "C" {
+
+int ovl_create(int device, ovl_ctx** out) {
+    ovl_ctx* c = nullptr;
+    if (!out) return fail(c, OVL_E_ARG, "ovl_create: out is NULL");
+    *out = nullptr;
+    int n = 0;
+    cudaError_t e = cudaGetDeviceCount(&n);
+    if (e != cudaSuccess || n <= 0) {
+        (void)cudaGetLastError();
+        return fail(c, OVL_E_CUDA, "no usable CUDA device (%s); this library has no CPU fallback",
+                    e != cudaSuccess ? cudaGetErrorString(e) : "device count is 0");
+    }
+    if (device < 0 || device >= n) return fail(c, OVL_E_ARG, "device %d out of range (0..%d)", device, n - 1);
+    ovl_ctx* x = new (std::nothrow) ovl_ctx();
+    if (!x) return fail(c, OVL_E_NOMEM, "out of host memory");
+    x->device = device;
+    c = x;
+    auto bail = [&](int code) {
+        g_create_err = x->err;
+        ovl_destroy(x);
+        return code;
+    };
+    cudaDeviceProp prop;
+    if (cudaSetDevice(device) != cudaSuccess || cudaGetDeviceProperties(&prop, device) != cudaSuccess) {
+        fail(c, OVL_E_CUDA, "cannot select CUDA device %d: %s", device, cudaGetErrorString(cudaGetLastError()));
+        return bail(OVL_E_CUDA);
+    }
+    if (prop.major < 10) {
+        fail(c, OVL_E_CUDA, "device %d is sm_%d%d; this library is built for sm_100a (B200) only", device, prop.major, prop.minor);
+        return bail(OVL_E_CUDA);
+    }
+    x->n_sm = prop.multiProcessorCount;
+    auto init = [&]() -> int {
+        CK(cudaStreamCreateWithFlags(&x->st, cudaStreamNonBlocking));
+        CK(cudaStreamCreateWithFlags(&x->st_comm, cudaStreamNonBlocking));
+        for (int i = 0; i < E_COUNT; ++i) CK(cudaEventCreate(&x->ev[i]));
+        CK(cudaEventCreateWithFlags(&x->ev_comm, cudaEventDisableTiming));
+        CK(cudaEventCreateWithFlags(&x->ev_pack, cudaEventDisableTiming));
+        CK(cudaHostAlloc(reinterpret_cast<void**>(&x->h_ctr), C_COUNT * sizeof(uint64_t), cudaHostAllocDefault));
+        OVL_TRY(dev_ensure(c, x->d_ctr, C_COUNT * sizeof(uint64_t), false));
+        CK(cudaFuncSetAttribute(ovl::k3_scan<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, 128 * 1024));
+        return OVL_OK;
+    };
+    int rc = init();
+    if (rc != OVL_OK) return bail(rc);
+    *out = x;
+    return OVL_OK;
+}
+
+void ovl_destroy(ovl_ctx* c) {
+    if (!c) return;
+    cudaSetDevice(c->device);
+    if (c->comm) nccl_dyn::api().CommDestroy(c->comm);
+    DevBuf* bufs[] = {&c->d_ascii, &c->d_src, &c->d_len, &c->d_flags, &c->d_gran0, &c->d_gran_ent,
+                      &c->d_packed, &c->d_anc_ent, &c->d_anc_ent2, &c->d_keys, &c->d_keys2,
+                      &c->d_table, &c->d_filter, &c->d_ctr, &c->d_tmp, &c->d_cand, &c->d_hits,
+                      &c->d_hits2, &c->d_cnt, &c->d_offs, &c->d_rows};
+    for (DevBuf* b : bufs)
+        if (b->p) cudaFree(b->p);
+    if (c->ascii.p) cudaFreeHost(c->ascii.p);
+    if (c->h_rows.p) cudaFreeHost(c->h_rows.p);
+    if (c->h_gather.p) cudaFreeHost(c->h_gather.p);
+    if (c->h_ctr) cudaFreeHost(c->h_ctr);
+    for (int i = 0; i < E_COUNT; ++i)
+        if (c->ev[i]) cudaEventDestroy(c->ev[i]);
+    if (c->ev_comm) cudaEventDestroy(c->ev_comm);
+    if (c->ev_pack) cudaEventDestroy(c->ev_pack);
+    if (c->st) cudaStreamDestroy(c->st);
+    if (c->st_comm) cudaStreamDestroy(c->st_comm);
+    (void)cudaGetLastError();
+    delete c;
+}
+
+const char* ovl_last_error(const ovl_ctx* c) { return c ? c->err.c_str() : g_create_err.c_str(); }
+
+int ovl_reserve(ovl_ctx* c, uint64_t seq_bytes, uint32_t n_entries) {
+    if (!c) return OVL_E_ARG;
+    OVL_TRY(set_dev(c));
+    try {
+        c->src.reserve(n_entries);
+        c->len.reserve(n_entries);
+        c->flags.reserve(n_entries);
+        c->id_off.reserve((size_t)n_entries + 1);
+    } catch (const std::bad_alloc&) {
+        return fail(c, OVL_E_NOMEM, "out of host memory");
+    }
+    return pin_ensure(c, c->ascii, c->ascii_used + seq_bytes + 16ull * n_entries + SLACK, c->ascii_used);
+}
+
+int ovl_add_sequence(ovl_ctx* c, const char* id, size_t id_len, const char* seq, size_t seq_len) {
+    if (!c || (!id && id_len) || (!seq && seq_len)) return fail(c, OVL_E_ARG, "ovl_add_sequence: NULL argument");
+    OVL_TRY(set_dev(c));
+    try {
+        uint64_t off = 0;
+        OVL_TRY(stage_record(c, seq, seq_len, &off));
+        return push_entry(c, id, id_len, nullptr, off, seq_len, 0);
+    } catch (const std::bad_alloc&) {
+        return fail(c, OVL_E_NOMEM, "out of host memory");
+    }
+}
+
+int ovl_add_read(ovl_ctx* c, const char* name, size_t name_len, const char* seq, size_t seq_len) {
+    if (!c || (!name && name_len) || (!seq && seq_len)) return fail(c, OVL_E_ARG, "ovl_add_read: NULL argument");
+    OVL_TRY(set_dev(c));
+    try {
+        uint64_t off = 0;
+        OVL_TRY(stage_record(c, seq, seq_len, &off));
+        OVL_TRY(push_entry(c, name, name_len, "+", off, seq_len, 0));
+        return push_entry(c, name, name_len, "-", off, seq_len, 1);
+    } catch (const std::bad_alloc&) {
+        return fail(c, OVL_E_NOMEM, "out of host memory");
+    }
+}
+
+int ovl_add_bulk(ovl_ctx* c, const uint8_t* buf, const uint64_t* offsets, uint32_t n, const char* names,
+                 const uint64_t* name_offsets, int both_strands) {
+    if (!c || (n && (!buf || !offsets)) || (names && !name_offsets))
+        return fail(c, OVL_E_ARG, "ovl_add_bulk: NULL argument");
+    if (!n) return OVL_OK;
+    OVL_TRY(set_dev(c));
+    try {
+        OVL_TRY(ovl_reserve(c, offsets[n] - offsets[0], (uint32_t)(c->len.size() + (both_strands ? 2ull * n : n))));
+        for (uint32_t i = 0; i < n; ++i) {
+            if (offsets[i + 1] < offsets[i]) return fail(c, OVL_E_ARG, "ovl_add_bulk: offsets not monotone at %u", i);
+            const size_t sl = (size_t)(offsets[i + 1] - offsets[i]);
+            const char* nm = names ? names + name_offsets[i] : nullptr;
+            const size_t nl = names ? (size_t)(name_offsets[i + 1] - name_offsets[i]) : 0;
+            uint64_t off = 0;
+            OVL_TRY(stage_record(c, reinterpret_cast<const char*>(buf + offsets[i]), sl, &off));
+            if (both_strands) {
+                OVL_TRY(push_entry(c, nm, nl, "+", off, sl, 0));
+                OVL_TRY(push_entry(c, nm, nl, "-", off, sl, 1));
+            } else {
+                OVL_TRY(push_entry(c, nm, nl, nullptr, off, sl, 0));
+            }
+        }
+    } catch (const std::bad_alloc&) {
+        return fail(c, OVL_E_NOMEM, "out of host memory");
+    }
+    return OVL_OK;
+}
+
+int ovl_add_remote(ovl_ctx* c, const uint32_t* lengths, uint32_t n, int both_strands) {
+    if (!c || (n && !lengths)) return fail(c, OVL_E_ARG, "ovl_add_remote: NULL argument");
+    try {
+        for (uint32_t i = 0; i < n; ++i) {
+            OVL_TRY(push_entry(c, nullptr, 0, both_strands ? "+" : nullptr, NO_SRC, lengths[i], 0));
+            if (both_strands) OVL_TRY(push_entry(c, nullptr, 0, "-", NO_SRC, lengths[i], 1));
+        }
+    } catch (const std::bad_alloc&) {
+        return fail(c, OVL_E_NOMEM, "out of host memory");
+    }
+    return OVL_OK;
+}
+
+int ovl_clear(ovl_ctx* c) {
+    if (!c) return OVL_E_ARG;
+    c->ascii_used = SLACK;
+    c->src.clear();
+    c->len.clear();
+    c->flags.clear();
+    c->id_blob.clear();
+    c->id_off.assign(1, 0);
+    c->gran0.clear();
+    c->bases = c->max_len = 0;
+    c->uploaded = false;
+    c->n_rows = 0;
+    c->rows_fetched = false;
+    c->e_lo = c->e_hi = 0;
+    return OVL_OK;
+}
+
+int ovl_entry_count(const ovl_ctx* c, uint32_t* m) {
+    if (!c || !m) return OVL_E_ARG;
+    *m = (uint32_t)c->len.size();
+    return OVL_OK;
+}
+
+int ovl_entry_id(const ovl_ctx* c, uint32_t idx, const char** id, size_t* id_len) {
+    if (!c || !id || !id_len || idx >= c->len.size()) return OVL_E_ARG;
+    *id = c->id_blob.data() + c->id_off[idx];
+    *id_len = (size_t)(c->id_off[idx + 1] - c->id_off[idx]);
+    return OVL_OK;
+}
+
+int ovl_entry_length(const ovl_ctx* c, uint32_t idx, uint32_t* len) {
+    if (!c || !len || idx >= c->len.size()) return OVL_E_ARG;
+    *len = c->len[idx];
+    return OVL_OK;
+}
+
+int ovl_set_collect_stats(ovl_ctx* c, int on) {
+    if (!c) return OVL_E_ARG;
+    c->collect = on ? 1 : 0;
+    return OVL_OK;
+}
+
+int ovl_get_stats(const ovl_ctx* c, ovl_stats* out) {
+    if (!c || !out) return OVL_E_ARG;
+    *out = c->stats;
+    return OVL_OK;
+}
+
+// -----------------------------------------------------------------------------------------
+// host -> HBM: ASCII records of the local entries + the entry table
+int ovl_upload(ovl_ctx* c) {
+    if (!c) return OVL_E_ARG;
+    OVL_TRY(set_dev(c));
+    const size_t M = c->len.size();
+    // local entry range (contiguous) and granule prefix sum
+    uint32_t lo = (uint32_t)M, hi = 0;
+    try {
+        c->gran0.resize(M + 1);
+    } catch (const std::bad_alloc&) {
+        return fail(c, OVL_E_NOMEM, "out of host memory");
+    }
+    uint64_t g = 0;
+    for (size_t e = 0; e < M; ++e) {
+        c->gran0[e] = (uint32_t)g;
+        g += (c->len[e] + 63u) / 64u;
+        if (c->src[e] != NO_SRC) {
+            if (e < lo) lo = (uint32_t)e;
+            hi = (uint32_t)e + 1;
+        }
+    }
+    if (g >= 0xffffffffull) return fail(c, OVL_E_LIMIT, "more than 2^32 granules (%llu)", (unsigned long long)g);
+    if (M) c->gran0[M] = (uint32_t)g;
+    if (lo > hi) lo = hi = 0;
+    for (uint32_t e = lo; e < hi; ++e)
+        if (c->src[e] == NO_SRC) return fail(c, OVL_E_ARG, "local entries must be one contiguous range (entry %u is remote)", e);
+    c->e_lo = lo;
+    c->e_hi = hi;
+    if (c->nranks == 1 && (lo != 0 || hi != M)) return fail(c, OVL_E_ARG, "remote entries need ovl_comm_init");
+
+    CK(cudaEventRecord(c->ev[E_H2D0], c->st));
+    if (M) {
+        const size_t ab = c->ascii_used + SLACK;
+        OVL_TRY(dev_ensure(c, c->d_ascii, ab));
+        OVL_TRY(dev_ensure(c, c->d_src, M * 8));
+        OVL_TRY(dev_ensure(c, c->d_len, M * 4));
+        OVL_TRY(dev_ensure(c, c->d_flags, M));
+        OVL_TRY(dev_ensure(c, c->d_gran0, (M + 1) * 4));
+        OVL_TRY(dev_ensure(c, c->d_gran_ent, (g + 1) * 4));
+        OVL_TRY(dev_ensure(c, c->d_packed, (g + 1) * 16));
+        if (c->ascii.p) CK(cudaMemcpyAsync(c->d_ascii.p, c->ascii.p, ab, cudaMemcpyHostToDevice, c->st));
+        CK(cudaMemcpyAsync(c->d_src.p, c->src.data(), M * 8, cudaMemcpyHostToDevice, c->st));
+        CK(cudaMemcpyAsync(c->d_len.p, c->len.data(), M * 4, cudaMemcpyHostToDevice, c->st));
+        CK(cudaMemcpyAsync(c->d_flags.p, c->flags.data(), M, cudaMemcpyHostToDevice, c->st));
+        CK(cudaMemcpyAsync(c->d_gran0.p, c->gran0.data(), (M + 1) * 4, cudaMemcpyHostToDevice, c->st));
+        c->stats.ascii_bytes = ab;
+    }
+    CK(cudaEventRecord(c->ev[E_PACK0], c->st));
+    CK(cudaStreamSynchronize(c->st));  // the pageable vectors above must not change under the copy
+    c->stats.ms_h2d = ev_ms(c, E_H2D0, E_PACK0);
+    c->uploaded = true;
+    return OVL_OK;
+}
+
+// -----------------------------------------------------------------------------------------
+int ovl_overlaps_device(ovl_ctx* c, uint32_t min_length, uint64_t* n_rows_out) {
+    using namespace ovl;
+    if (!c) return OVL_E_ARG;
+    OVL_TRY(set_dev(c));
+    if (!c->uploaded) return fail(c, OVL_E_ARG, "ovl_overlaps_device: call ovl_upload first");
+    const uint32_t l = min_length < 1 ? 1u : min_length;  // min_length 0 behaves as 1
+    const int k = l < 32 ? (int)l : 32;
+    const uint32_t M = (uint32_t)c->len.size();
+    ovl_stats& S = c->stats;
+    const float keep_h2d = S.ms_h2d;
+    const uint64_t keep_ab = S.ascii_bytes;
+    memset(&S, 0, sizeof S);
+    S.ms_h2d = keep_h2d;
+    S.ascii_bytes = keep_ab;
+    S.entries = M;
+    S.bases = c->bases;
+    S.kmer = (uint32_t)k;
+    c->n_rows = 0;
+    c->rows_fetched = false;
+    if (n_rows_out) *n_rows_out = 0;
+    if (M == 0) return OVL_OK;  // the reference segfaults here; we return no rows
+
+    const uint32_t G = c->gran0[M];
+    S.granules = G;
+    KeyFmt fmt;
+    fmt.bits_e = ceil_log2((uint64_t)M < 2 ? 2 : M);
+    fmt.bits_p = ceil_log2(c->max_len + 1 < 2 ? 2 : c->max_len + 1);
+    if (fmt.total() > 64)
+        return fail(c, OVL_E_LIMIT, "hit key needs %d bits (entries %u, longest %llu): over the 64-bit key layout",
+                    fmt.total(), M, (unsigned long long)c->max_len);
+    cudaStream_t st = c->st;
+    uint64_t* ctr = c->d_ctr.as<uint64_t>();
+    uint32_t launches = 0, lib = 0;
+    const int nsm = c->n_sm;
+
+    CK(cudaEventRecord(c->ev[E_PACK0], st));
+    CK(cudaMemsetAsync(ctr, 0, C_COUNT * sizeof(uint64_t), st));
+    // ---- K0 + K1: pack the local entries ------------------------------------------------
+    const uint32_t g_lo = c->gran0[c->e_lo], g_hi = c->gran0[c->e_hi];
+    if (c->e_hi > c->e_lo) {
+        k0_gran_entry<<<nsm * 4, 256, 0, st>>>(c->d_gran0.as<uint32_t>(), c->d_gran_ent.as<uint32_t>(), c->e_lo, c->e_hi);
+        ++launches;
+        if (g_hi > g_lo) {
+            k1_pack<<<nsm * 8, 256, 0, st>>>(c->d_ascii.as<uint8_t>(), c->d_src.as<uint64_t>(), c->d_len.as<uint32_t>(),
+                                            c->d_flags.as<uint8_t>(), c->d_gran0.as<uint32_t>(),
+                                            c->d_gran_ent.as<uint32_t>(), c->d_packed.as<uint32_t>(),
+                                            4ull * g_lo, 4ull * g_hi, reinterpret_cast<uint32_t*>(ctr + C_ERR));
+            ++launches;
+        }
+    }
+    CK(cudaMemsetAsync(c->d_packed.as<uint4>() + G, 0, 16, st));  // terminator granule
+    CK(cudaGetLastError());
+    // ---- multi-GPU: replicate the packed granules (needed by K2 keys and by K4) ---------
+    if (c->nranks > 1) {
+        auto& N = nccl_dyn::api();
+        CK(cudaEventRecord(c->ev_pack, st));
+        CK(cudaStreamWaitEvent(c->st_comm, c->ev_pack, 0));
+        CKN(N.GroupStart());
+        for (int r = 0; r < c->nranks; ++r) {
+            const uint32_t a = c->gran0[c->rank_e[r]], b = c->gran0[c->rank_e[r + 1]];
+            if (b > a) {
+                uint4* p = c->d_packed.as<uint4>() + a;
+                CKN(N.Broadcast(p, p, (size_t)(b - a) * 16, ncclUint8, r, c->comm, c->st_comm));
+            }
+        }
+        CKN(N.GroupEnd());
+        CK(cudaEventRecord(c->ev_comm, c->st_comm));
+    }
+    CK(cudaEventRecord(c->ev[E_ANCHOR0], st));
+
+    // ---- K2: anchors ----------------------------------------------------------------------
+    OVL_TRY(dev_ensure(c, c->d_anc_ent, (size_t)M * 4));
+    OVL_TRY(dev_ensure(c, c->d_anc_ent2, (size_t)M * 4));
+    OVL_TRY(dev_ensure(c, c->d_keys, (size_t)M * 8));
+    OVL_TRY(dev_ensure(c, c->d_keys2, (size_t)M * 8));
+    {
+        size_t tb = 0;
+        cub::CountingInputIterator<uint32_t> it(0);
+        LenGE pred{c->d_len.as<uint32_t>(), l};
+        CK(cub::DeviceSelect::If(nullptr, tb, it, c->d_anc_ent.as<uint32_t>(), ctr + C_NANC, (int)M, pred, st));
+        OVL_TRY(dev_ensure(c, c->d_tmp, tb));
+        tb = c->d_tmp.cap;
+        CK(cub::DeviceSelect::If(c->d_tmp.p, tb, it, c->d_anc_ent.as<uint32_t>(), ctr + C_NANC, (int)M, pred, st));
+        ++lib;
+    }
+    OVL_TRY(read_ctr(c));
+    if (c->h_ctr[C_ERR]) {
+        const uint32_t e = (uint32_t)c->h_ctr[C_ERR] - 1;
+        return fail(c, OVL_E_ALPHABET, "entry %u ('%.*s') holds a byte outside upper-case ACGT", e,
+                    (int)(c->id_off[e + 1] - c->id_off[e]), c->id_blob.data() + c->id_off[e]);
+    }
+    const uint32_t n_anc = (uint32_t)c->h_ctr[C_NANC];
+    S.anchors = n_anc;
+    uint64_t npos = 0;  // local A positions with |a|-p >= l (statistics)
+    for (uint32_t e = c->e_lo; e < c->e_hi; ++e)
+        if (c->len[e] >= l) npos += c->len[e] - l + 1;
+    S.scan_positions = npos;
+    auto finish_empty = [&]() -> int {
+        CK(cudaEventRecord(c->ev[E_SCAN0], st));
+        CK(cudaEventRecord(c->ev[E_VERIFY0], st));
+        CK(cudaEventRecord(c->ev[E_EMIT0], st));
+        CK(cudaEventRecord(c->ev[E_END], st));
+        if (c->nranks > 1) CK(cudaStreamWaitEvent(st, c->ev_comm, 0));
+        CK(cudaStreamSynchronize(st));
+        S.launches = launches;
+        S.lib_launches = lib;
+        S.ms_pack = ev_ms(c, E_PACK0, E_ANCHOR0);
+        S.ms_anchor = ev_ms(c, E_ANCHOR0, E_SCAN0);
+        S.ms_device = ev_ms(c, E_PACK0, E_END);
+        return OVL_OK;
+    };
+    if (n_anc == 0 || g_hi == g_lo) return finish_empty();
+
+    if (c->nranks > 1) CK(cudaStreamWaitEvent(st, c->ev_comm, 0));  // keys read remote granules
+    k2_keys<<<(n_anc + 255) / 256, 256, 0, st>>>(reinterpret_cast<const uint64_t*>(c->d_packed.p), c->d_gran0.as<uint32_t>(),
+                                                 c->d_anc_ent.as<uint32_t>(), c->d_keys.as<uint64_t>(), n_anc, kmer_mask(k));
+    ++launches;
+    {
+        size_t tb = 0;
+        CK(cub::DeviceRadixSort::SortPairs(nullptr, tb, c->d_keys.as<uint64_t>(), c->d_keys2.as<uint64_t>(),
+                                           c->d_anc_ent.as<uint32_t>(), c->d_anc_ent2.as<uint32_t>(), (int)n_anc, 0, 2 * k, st));
+        OVL_TRY(dev_ensure(c, c->d_tmp, tb));
+        tb = c->d_tmp.cap;
+        CK(cub::DeviceRadixSort::SortPairs(c->d_tmp.p, tb, c->d_keys.as<uint64_t>(), c->d_keys2.as<uint64_t>(),
+                                           c->d_anc_ent.as<uint32_t>(), c->d_anc_ent2.as<uint32_t>(), (int)n_anc, 0, 2 * k, st));
+        ++lib;
+    }
+    const int tbits = ceil_log2(2ull * n_anc) < 4 ? 4 : ceil_log2(2ull * n_anc);
+    const bool smem_filter = n_anc <= (1u << 17);
+    int fw_bits = smem_filter ? ceil_log2(n_anc) : ceil_log2(2ull * n_anc);
+    if (fw_bits < 5) fw_bits = 5;
+    if (smem_filter && fw_bits > 15) fw_bits = 15;
+    if (fw_bits > 27) fw_bits = 27;
+    OVL_TRY(dev_ensure(c, c->d_table, sizeof(Slot) << tbits));
+    OVL_TRY(dev_ensure(c, c->d_filter, 4ull << fw_bits));
+    CK(cudaMemsetAsync(c->d_table.p, 0, sizeof(Slot) << tbits, st));
+    CK(cudaMemsetAsync(c->d_filter.p, 0, 4ull << fw_bits, st));
+    k2_build<<<(n_anc + 255) / 256, 256, 0, st>>>(c->d_keys2.as<uint64_t>(), n_anc, c->d_table.as<Slot>(), tbits,
+                                                  c->d_filter.as<uint32_t>(), fw_bits,
+                                                  reinterpret_cast<unsigned long long*>(ctr + C_NKEYS));
+    ++launches;
+    CK(cudaGetLastError());
+    CK(cudaEventRecord(c->ev[E_SCAN0], st));
+
+    // ---- K3: scan (re-run once with the exact size if the candidate buffer was too small) --
+    if (c->cand_cap == 0) {
+        uint64_t cap = 96ull * (c->e_hi - c->e_lo);
+        if (cap < (1ull << 20)) cap = 1ull << 20;
+        OVL_TRY(dev_ensure(c, c->d_cand, cap * sizeof(Cand), false));
+        c->cand_cap = c->d_cand.cap / sizeof(Cand);
+    }
+    uint64_t n_cand = 0;
+    for (int attempt = 0;; ++attempt) {
+        ScanParams P;
+        P.packed = c->d_packed.as<uint4>();
+        P.gran_ent = c->d_gran_ent.as<uint32_t>();
+        P.gran0 = c->d_gran0.as<uint32_t>();
+        P.len = c->d_len.as<uint32_t>();
+        P.g_begin = g_lo;
+        P.g_end = g_hi;
+        P.l = l;
+        P.k = k;
+        P.filter = c->d_filter.as<uint32_t>();
+        P.fw_bits = fw_bits;
+        P.table = c->d_table.as<Slot>();
+        P.tbits = tbits;
+        P.anc_ent = c->d_anc_ent2.as<uint32_t>();
+        P.cand = c->d_cand.as<Cand>();
+        P.n_cand = reinterpret_cast<unsigned long long*>(ctr + C_NCAND);
+        P.cap = c->cand_cap;
+        if (smem_filter)
+            k3_scan<true><<<nsm, 1024, 4u << fw_bits, st>>>(P);
+        else
+            k3_scan<false><<<nsm, 1024, 0, st>>>(P);
+        ++launches;
+        CK(cudaGetLastError());
+        OVL_TRY(read_ctr(c));
+        n_cand = c->h_ctr[C_NCAND];
+        if (n_cand <= c->cand_cap) break;
+        if (attempt >= 2) return fail(c, OVL_E_LIMIT, "candidate buffer overflow persists (%llu)", (unsigned long long)n_cand);
+        ++S.retries;
+        OVL_TRY(dev_ensure(c, c->d_cand, (n_cand + n_cand / 16) * sizeof(Cand), false));
+        c->cand_cap = c->d_cand.cap / sizeof(Cand);
+        CK(cudaMemsetAsync(ctr + C_NCAND, 0, 8, st));
+    }
+    S.candidates = n_cand;
+    S.anchor_keys = c->h_ctr[C_NKEYS];
+    CK(cudaEventRecord(c->ev[E_VERIFY0], st));
+    if (n_cand == 0) {
+        CK(cudaEventRecord(c->ev[E_EMIT0], st));
+        CK(cudaEventRecord(c->ev[E_END], st));
+        if (c->nranks > 1) CK(cudaStreamWaitEvent(st, c->ev_comm, 0));
+        CK(cudaStreamSynchronize(st));
+        S.launches = launches;
+        S.lib_launches = lib;
+        S.ms_pack = ev_ms(c, E_PACK0, E_ANCHOR0);
+        S.ms_anchor = ev_ms(c, E_ANCHOR0, E_SCAN0);
+        S.ms_scan = ev_ms(c, E_SCAN0, E_VERIFY0);
+        S.ms_device = ev_ms(c, E_PACK0, E_END);
+        return OVL_OK;
+    }
+
+    // ---- K4: verify -----------------------------------------------------------------------
+    OVL_TRY(dev_ensure(c, c->d_hits, n_cand * 8));
+    OVL_TRY(dev_ensure(c, c->d_hits2, n_cand * 8));
+    {
+        VerifyParams V;
+        V.cand = c->d_cand.as<Cand>();
+        V.n_cand = reinterpret_cast<unsigned long long*>(ctr + C_NCAND);
+        V.cap = c->cand_cap;
+        V.packed64 = reinterpret_cast<const uint64_t*>(c->d_packed.p);
+        V.gran0 = c->d_gran0.as<uint32_t>();
+        V.len = c->d_len.as<uint32_t>();
+        V.fmt = fmt;
+        V.hits = c->d_hits.as<uint64_t>();
+        V.n_hits = reinterpret_cast<unsigned long long*>(ctr + C_NHITS);
+        V.counters = reinterpret_cast<unsigned long long*>(ctr + C_SELF);
+        V.collect = c->collect;
+        uint64_t blocks = (n_cand + 7) / 8;
+        if (blocks > (uint64_t)nsm * 8) blocks = (uint64_t)nsm * 8;
+        k4_verify<<<(unsigned)blocks, 256, 0, st>>>(V);
+        ++launches;
+        CK(cudaGetLastError());
+    }
+    OVL_TRY(read_ctr(c));
+    const uint64_t n_hits = c->h_ctr[C_NHITS];
+    S.hits = n_hits;
+    S.candidates = n_cand - c->h_ctr[C_SELF];  // canonical C of SURVEY 8(d): a != b
+    S.compared_bases = c->h_ctr[C_SUMM];
+    S.operand_bytes = c->h_ctr[C_SUMB];
+    CK(cudaEventRecord(c->ev[E_EMIT0], st));
+
+    // ---- K5: sort hits, select longest, compact ----------------------------------------------
+    uint64_t n_rows = 0;
+    if (n_hits) {
+        if (n_hits > 0x7fffffffull) return fail(c, OVL_E_LIMIT, "more than 2^31 verified hits on one GPU (%llu)", (unsigned long long)n_hits);
+        size_t tb = 0;
+        CK(cub::DeviceRadixSort::SortKeys(nullptr, tb, c->d_hits.as<uint64_t>(), c->d_hits2.as<uint64_t>(), (int)n_hits, 0, fmt.total(), st));
+        OVL_TRY(dev_ensure(c, c->d_tmp, tb));
+        tb = c->d_tmp.cap;
+        CK(cub::DeviceRadixSort::SortKeys(c->d_tmp.p, tb, c->d_hits.as<uint64_t>(), c->d_hits2.as<uint64_t>(), (int)n_hits, 0, fmt.total(), st));
+        ++lib;
+        OVL_TRY(dev_ensure(c, c->d_cnt, n_hits * 4));
+        OVL_TRY(dev_ensure(c, c->d_offs, (n_hits + 1) * 8));
+        const unsigned nb = (unsigned)((n_hits + 255) / 256);
+        k5_count<<<nb, 256, 0, st>>>(c->d_hits2.as<uint64_t>(), n_hits, fmt, c->d_cnt.as<uint32_t>());
+        ++launches;
+        tb = 0;
+        CK(cub::DeviceScan::ExclusiveSum(nullptr, tb, c->d_cnt.as<uint32_t>(), c->d_offs.as<uint64_t>(), (int)n_hits, st));
+        OVL_TRY(dev_ensure(c, c->d_tmp, tb));
+        tb = c->d_tmp.cap;
+        CK(cub::DeviceScan::ExclusiveSum(c->d_tmp.p, tb, c->d_cnt.as<uint32_t>(), c->d_offs.as<uint64_t>(), (int)n_hits, st));
+        ++lib;
+        // total = offs[n-1] + cnt[n-1]
+        uint64_t last_off = 0;
+        uint32_t last_cnt = 0;
+        CK(cudaMemcpyAsync(&c->h_ctr[C_SELF], c->d_offs.as<uint64_t>() + (n_hits - 1), 8, cudaMemcpyDeviceToHost, st));
+        CK(cudaMemcpyAsync(&c->h_ctr[C_SUMM], c->d_cnt.as<uint32_t>() + (n_hits - 1), 4, cudaMemcpyDeviceToHost, st));
+        CK(cudaStreamSynchronize(st));
+        last_off = c->h_ctr[C_SELF];
+        last_cnt = (uint32_t)(c->h_ctr[C_SUMM] & 0xffffffffull);
+        n_rows = last_off + last_cnt;
+        if (n_rows) {
+            OVL_TRY(dev_ensure(c, c->d_rows, n_rows * sizeof(Row)));
+            k5_emit<<<nb, 256, 0, st>>>(c->d_hits2.as<uint64_t>(), n_hits, fmt, c->d_offs.as<uint64_t>(),
+                                        c->d_len.as<uint32_t>(), c->d_rows.as<Row>());
+            ++launches;
+            CK(cudaGetLastError());
+        }
+    }
+    CK(cudaEventRecord(c->ev[E_END], st));
+    CK(cudaStreamSynchronize(st));
+    c->n_rows = n_rows;
+    S.rows = n_rows;
+    S.launches = launches;
+    S.lib_launches = lib;
+    S.ms_pack = ev_ms(c, E_PACK0, E_ANCHOR0);
+    S.ms_anchor = ev_ms(c, E_ANCHOR0, E_SCAN0);
+    S.ms_scan = ev_ms(c, E_SCAN0, E_VERIFY0);
+    S.ms_verify = ev_ms(c, E_VERIFY0, E_EMIT0);
+    S.ms_emit = ev_ms(c, E_EMIT0, E_END);
+    S.ms_device = ev_ms(c, E_PACK0, E_END);
+    if (n_rows_out) *n_rows_out = n_rows;
+    return OVL_OK;
+}
+
+int ovl_fetch_rows(ovl_ctx* c, const ovl_row** rows, uint64_t* n_rows) {
+    if (!c || !rows || !n_rows) return OVL_E_ARG;
+    OVL_TRY(set_dev(c));
+    *rows = nullptr;
+    *n_rows = c->n_rows;
+    if (!c->n_rows) return OVL_OK;
+    if (!c->rows_fetched) {
+        const size_t bytes = c->n_rows * sizeof(ovl_row);
+        OVL_TRY(pin_ensure(c, c->h_rows, bytes, 0));
+        CK(cudaEventRecord(c->ev[E_D2H0], c->st));
+        CK(cudaMemcpyAsync(c->h_rows.p, c->d_rows.p, bytes, cudaMemcpyDeviceToHost, c->st));
+        CK(cudaEventRecord(c->ev[E_D2H1], c->st));
+        CK(cudaStreamSynchronize(c->st));
+        c->stats.ms_d2h = ev_ms(c, E_D2H0, E_D2H1);
+        c->rows_fetched = true;
+    }
+    *rows = reinterpret_cast<const ovl_row*>(c->h_rows.p);
+    return OVL_OK;
+}
+
+int ovl_overlaps(ovl_ctx* c, uint32_t min_length, const ovl_row** rows, uint64_t* n_rows) {
+    if (!c || !rows || !n_rows) return OVL_E_ARG;
+    *rows = nullptr;
+    *n_rows = 0;
+    // host buffers in: the entry store is re-sent on every call, like the reference rebuilds
+    // its index on every call (src/overlapper.cpp:33-36)
+    OVL_TRY(ovl_upload(c));
+    uint64_t n = 0;
+    OVL_TRY(ovl_overlaps_device(c, min_length, &n));
+    OVL_TRY(ovl_fetch_rows(c, rows, n_rows));
+    c->stats.ms_total = c->stats.ms_h2d + c->stats.ms_device + c->stats.ms_d2h;
+    return OVL_OK;
+}
+
+// -----------------------------------------------------------------------------------------
+int ovl_comm_unique_id(uint8_t id_out[128]) {
+    ovl_ctx* c = nullptr;
+    if (!id_out) return OVL_E_ARG;
+    if (!nccl_dyn::load()) return fail(c, OVL_E_NCCL, "cannot load libnccl: %s", nccl_dyn::load_error());
+    ncclUniqueId id;
+    static_assert(sizeof(ncclUniqueId) == 128, "NCCL unique id is 128 bytes");
+    CKN(nccl_dyn::api().GetUniqueId(&id));
+    memcpy(id_out, &id, 128);
+    return OVL_OK;
+}
+
+int ovl_comm_init(ovl_ctx* c, const uint8_t id[128], int rank, int nranks) {
+    if (!c || !id || nranks < 1 || rank < 0 || rank >= nranks) return fail(c, OVL_E_ARG, "ovl_comm_init: bad argument");
+    OVL_TRY(set_dev(c));
+    if (!nccl_dyn::load()) return fail(c, OVL_E_NCCL, "cannot load libnccl: %s", nccl_dyn::load_error());
+    if (c->comm) {
+        nccl_dyn::api().CommDestroy(c->comm);
+        c->comm = nullptr;
+    }
+    ncclUniqueId uid;
+    memcpy(&uid, id, 128);
+    CKN(nccl_dyn::api().CommInitRank(&c->comm, nranks, uid, rank));
+    c->rank = rank;
+    c->nranks = nranks;
+    c->uploaded = false;
+    return OVL_OK;
+}
+
+// Exchange every rank's local entry range; must tile [0, M) in rank order.
+int ovl_comm_sync_ranges(ovl_ctx* c) {
+    if (!c) return OVL_E_ARG;
+    OVL_TRY(set_dev(c));
+    c->rank_e.assign((size_t)c->nranks + 1, 0);
+    const uint32_t M = (uint32_t)c->len.size();
+    if (c->nranks == 1) {
+        c->rank_e[1] = M;
+        return OVL_OK;
+    }
+    if (!c->uploaded) return fail(c, OVL_E_ARG, "ovl_comm_sync_ranges: call ovl_upload first");
+    auto& N = nccl_dyn::api();
+    OVL_TRY(dev_ensure(c, c->d_tmp, 8ull * (c->nranks + 1)));
+    uint32_t mine[2] = {c->e_lo, c->e_hi};
+    uint32_t* d = c->d_tmp.as<uint32_t>();
+    CK(cudaMemcpyAsync(d + 2 * c->rank, mine, 8, cudaMemcpyHostToDevice, c->st));
+    CKN(N.AllGather(d + 2 * c->rank, d, 2, ncclUint32, c->comm, c->st));
+    std::vector<uint32_t> all(2 * (size_t)c->nranks);
+    CK(cudaMemcpyAsync(all.data(), d, 8ull * c->nranks, cudaMemcpyDeviceToHost, c->st));
+    CK(cudaStreamSynchronize(c->st));
+    uint32_t pos = 0;
+    for (int r = 0; r < c->nranks; ++r) {
+        uint32_t lo = all[2 * r], hi = all[2 * r + 1];
+        if (hi == lo) lo = hi = pos;  // a rank may own nothing
+        if (lo != pos) return fail(c, OVL_E_ARG, "rank %d owns entries [%u,%u) but [%u,..) was expected: ranges must tile the entry table in rank order", r, lo, hi, pos);
+        c->rank_e[r] = lo;
+        pos = hi;
+    }
+    if (pos != M) return fail(c, OVL_E_ARG, "ranks cover %u of %u entries", pos, M);
+    c->rank_e[c->nranks] = M;
+    return OVL_OK;
+}
+
+int ovl_comm_gather_rows(ovl_ctx* c, const ovl_row** rows, uint64_t* n_rows) {
+    if (!c || !rows || !n_rows) return OVL_E_ARG;
+    OVL_TRY(set_dev(c));
+    *rows = nullptr;
+    *n_rows = 0;
+    if (c->nranks == 1) return ovl_fetch_rows(c, rows, n_rows);
+    auto& N = nccl_dyn::api();
+    const int R = c->nranks;
+    // counts
+    OVL_TRY(dev_ensure(c, c->d_tmp, 8ull * R));
+    uint64_t* d = c->d_tmp.as<uint64_t>();
+    CK(cudaMemcpyAsync(d + c->rank, &c->n_rows, 8, cudaMemcpyHostToDevice, c->st));
+    CKN(N.AllGather(d + c->rank, d, 1, ncclUint64, c->comm, c->st));
+    std::vector<uint64_t> cnt(R);
+    CK(cudaMemcpyAsync(cnt.data(), d, 8ull * R, cudaMemcpyDeviceToHost, c->st));
+    CK(cudaStreamSynchronize(c->st));
+    uint64_t total = 0, before = 0;
+    for (int r = 0; r < R; ++r) {
+        if (r < c->rank) before += cnt[r];
+        total += cnt[r];
+    }
+    CK(cudaEventRecord(c->ev[E_D2H0], c->st));
+    if (c->rank == 0) {
+        // grow d_rows to hold everything, keeping the local rows at the front
+        if (total * sizeof(ovl_row) > c->d_rows.cap) {
+            DevBuf nb;
+            OVL_TRY(dev_ensure(c, nb, total * sizeof(ovl_row)));
+            if (c->n_rows) CK(cudaMemcpyAsync(nb.p, c->d_rows.p, c->n_rows * sizeof(ovl_row), cudaMemcpyDeviceToDevice, c->st));
+            CK(cudaStreamSynchronize(c->st));
+            if (c->d_rows.p) CK(cudaFree(c->d_rows.p));
+            c->d_rows = nb;
+        }
+        CKN(N.GroupStart());
+        uint64_t off = cnt[0];
+        for (int r = 1; r < R; ++r) {
+            if (cnt[r]) CKN(N.Recv(c->d_rows.as<ovl_row>() + off, cnt[r] * sizeof(ovl_row), ncclUint8, r, c->comm, c->st));
+            off += cnt[r];
+        }
+        CKN(N.GroupEnd());
+        c->n_rows = total;
+        c->rows_fetched = false;
+        c->stats.rows = total;
+        OVL_TRY(ovl_fetch_rows(c, rows, n_rows));
+        c->stats.ms_d2h = ev_ms(c, E_D2H0, E_D2H1);
+    } else {
+        if (c->n_rows) {
+            CKN(N.GroupStart());
+            CKN(N.Send(c->d_rows.p, c->n_rows * sizeof(ovl_row), ncclUint8, 0, c->comm, c->st));
+            CKN(N.GroupEnd());
+        }
+        CK(cudaEventRecord(c->ev[E_D2H1], c->st));
+        CK(cudaStreamSynchronize(c->st));
+        c->stats.ms_d2h = ev_ms(c, E_D2H0, E_D2H1);
+    }
+    (void)before;
+    return OVL_OK;
+}
+
+// -----------------------------------------------------------------------------------------
+int ovl_debug_packed(ovl_ctx* c, uint32_t idx, uint8_t* out, size_t out_cap, size_t* out_len) {
+    if (!c || !out_len || idx >= c->len.size()) return fail(c, OVL_E_ARG, "ovl_debug_packed: bad argument");
+    OVL_TRY(set_dev(c));
+    if (!c->uploaded || c->gran0.size() != c->len.size() + 1) return fail(c, OVL_E_ARG, "ovl_debug_packed: nothing packed yet");
+    const size_t bytes = (size_t)(c->gran0[idx + 1] - c->gran0[idx]) * 16;
+    *out_len = bytes;
+    if (!bytes) return OVL_OK;
+    if (!out || out_cap < bytes) return fail(c, OVL_E_ARG, "ovl_debug_packed: buffer too small (%zu needed)", bytes);
+    CK(cudaMemcpy(out, c->d_packed.as<uint8_t>() + (size_t)c->gran0[idx] * 16, bytes, cudaMemcpyDeviceToHost));
+    return OVL_OK;
+}
+
+}  // extern "C"

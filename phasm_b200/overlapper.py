@@ -1,0 +1,231 @@
+"""Host-side mirror of the reference's pybind11 module ``phasm.overlapper``.
+
+Reference interface (/root/reference/src/phasm.cpp:8-18):
+
+    ExactOverlapper()                       no-arg constructor         (phasm.cpp:13)
+    .add_sequence(id, seq) -> None          positional, copies both    (phasm.cpp:14)
+    .overlaps(min_length) -> list[tuple[str, str, int, int, int, int]] (phasm.cpp:15)
+
+Same names, argument meaning and error behaviour; the work happens in hand-written sm_100a
+CUDA behind the C ABI of ``include/phasm_ovl.h`` (``libphasm_ovl.so``).  There is no CPU
+path: constructing an ``ExactOverlapper`` without a usable B200 raises.
+
+Additive extras (not in the reference; defaults keep reference behaviour):
+``add_read`` (both strands, reverse complement made on the device), ``add_reads_bulk``,
+``overlaps_arrays`` (index rows as a numpy array instead of 10^7 Python tuples), ``stats``.
+"""
+from __future__ import annotations
+
+import ctypes
+import numbers
+from ctypes import byref, c_size_t, c_uint32, c_uint64, c_void_p
+from typing import List, Optional, Sequence, Tuple
+
+import numpy as np
+
+from . import _capi
+from ._capi import OvlRow, OvlStats
+
+__doc__module__ = "Optimised C++ all-vs-all exact overlap finder for PHASM"  # phasm.cpp:9-10
+
+Row = Tuple[str, str, int, int, int, int]
+
+
+def _as_bytes(x, what: str) -> bytes:
+    if isinstance(x, str):
+        return x.encode("utf-8")
+    if isinstance(x, (bytes, bytearray, memoryview)):
+        return bytes(x)
+    raise TypeError("%s must be str or bytes, not %s" % (what, type(x).__name__))
+
+
+def _as_unsigned(x, what: str) -> int:
+    # pybind11 converts to `unsigned int`: bool/int accepted, float and negatives rejected
+    if isinstance(x, bool) or not isinstance(x, numbers.Integral):
+        if isinstance(x, bool):
+            return int(x)
+        raise TypeError("%s: incompatible function arguments (expected unsigned int, got %s)"
+                        % (what, type(x).__name__))
+    x = int(x)
+    if x < 0 or x > 0xFFFFFFFF:
+        raise TypeError("%s: incompatible function arguments (value %d does not fit unsigned int)"
+                        % (what, x))
+    return x
+
+
+class ExactOverlapper:
+    """All-vs-all exact suffix-prefix overlap finder (drop-in for phasm.overlapper.ExactOverlapper)."""
+
+    def __init__(self, device: int = 0):
+        self._lib = _capi.load_library()
+        self._ctx = c_void_p()
+        rc = self._lib.ovl_create(int(device), byref(self._ctx))
+        if rc != _capi.OVL_OK:
+            msg = (self._lib.ovl_last_error(None) or b"").decode("utf-8", "replace")
+            self._ctx = c_void_p()
+            _capi.raise_for(rc, "ExactOverlapper: " + msg)
+
+    # ---- plumbing -----------------------------------------------------------------------
+    def _check(self, rc: int):
+        if rc != _capi.OVL_OK:
+            msg = (self._lib.ovl_last_error(self._ctx) or b"").decode("utf-8", "replace")
+            _capi.raise_for(rc, msg)
+
+    def close(self):
+        if getattr(self, "_ctx", None) is not None and self._ctx.value:
+            self._lib.ovl_destroy(self._ctx)
+            self._ctx = c_void_p()
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    # ---- reference API ------------------------------------------------------------------
+    def add_sequence(self, id, seq, /) -> None:
+        """ExactOverlapper::addSequence (src/overlapper.cpp:22-26): append a copy of (id, seq)."""
+        bid, bseq = _as_bytes(id, "id"), _as_bytes(seq, "seq")
+        self._check(self._lib.ovl_add_sequence(self._ctx, bid, len(bid), bseq, len(bseq)))
+
+    def overlaps(self, min_length, /) -> List[Row]:
+        """ExactOverlapper::overlaps (src/overlapper.cpp:28-150).
+
+        Returns ``[(a_id, b_id, astart, aend, bstart, bend)]`` with bstart always 0.  The
+        reference's row order is unspecified; here rows are sorted by entry index, position.
+        """
+        rows = self.overlaps_arrays(min_length)
+        ids = self.ids()
+        a = rows[:, 0].tolist()
+        b = rows[:, 1].tolist()
+        s = rows[:, 2].tolist()
+        e = rows[:, 3].tolist()
+        be = rows[:, 4].tolist()
+        return [(ids[a[i]], ids[b[i]], s[i], e[i], 0, be[i]) for i in range(len(a))]
+
+    # ---- additive extras ------------------------------------------------------------------
+    def add_read(self, name, seq) -> None:
+        """What phasm/cli/assembler.py:39-40 does per FASTA record: entries name+"+" (seq) and
+        name+"-" (reverse complement, computed on the device)."""
+        bn, bs = _as_bytes(name, "name"), _as_bytes(seq, "seq")
+        self._check(self._lib.ovl_add_read(self._ctx, bn, len(bn), bs, len(bs)))
+
+    def add_reads_bulk(self, buf, offsets, names: Optional[Sequence[str]] = None,
+                       both_strands: bool = True) -> None:
+        """Add ``len(offsets)-1`` records at once: record i is ``buf[offsets[i]:offsets[i+1]]``."""
+        buf = np.ascontiguousarray(buf, dtype=np.uint8)
+        offsets = np.ascontiguousarray(offsets, dtype=np.uint64)
+        n = len(offsets) - 1
+        if n <= 0:
+            return
+        if names is not None:
+            enc = [_as_bytes(x, "name") for x in names]
+            if len(enc) != n:
+                raise ValueError("names must have one entry per record")
+            noff = np.zeros(n + 1, dtype=np.uint64)
+            noff[1:] = np.cumsum([len(x) for x in enc], dtype=np.uint64)
+            blob = b"".join(enc)
+            nptr = ctypes.cast(ctypes.c_char_p(blob), c_void_p)
+            self._check(self._lib.ovl_add_bulk(self._ctx, buf.ctypes.data, offsets.ctypes.data, n,
+                                               nptr, noff.ctypes.data, int(both_strands)))
+        else:
+            self._check(self._lib.ovl_add_bulk(self._ctx, buf.ctypes.data, offsets.ctypes.data, n,
+                                               None, None, int(both_strands)))
+
+    def add_remote(self, lengths, both_strands: bool = True) -> None:
+        """Multi-GPU: declare records held by another rank (lengths only)."""
+        lengths = np.ascontiguousarray(lengths, dtype=np.uint32)
+        if len(lengths):
+            self._check(self._lib.ovl_add_remote(self._ctx, lengths.ctypes.data, len(lengths),
+                                                 int(both_strands)))
+
+    def clear(self) -> None:
+        self._check(self._lib.ovl_clear(self._ctx))
+
+    def __len__(self) -> int:
+        m = c_uint32()
+        self._check(self._lib.ovl_entry_count(self._ctx, byref(m)))
+        return m.value
+
+    def ids(self) -> List[str]:
+        out = []
+        p, n = c_void_p(), c_size_t()
+        for i in range(len(self)):
+            self._check(self._lib.ovl_entry_id(self._ctx, i, byref(p), byref(n)))
+            out.append(ctypes.string_at(p.value, n.value).decode("utf-8") if n.value else "")
+        return out
+
+    def lengths(self) -> np.ndarray:
+        m = len(self)
+        out = np.empty(m, dtype=np.uint32)
+        v = c_uint32()
+        for i in range(m):
+            self._check(self._lib.ovl_entry_length(self._ctx, i, byref(v)))
+            out[i] = v.value
+        return out
+
+    @staticmethod
+    def _rows_array(p: c_void_p, n: int) -> np.ndarray:
+        if not n:
+            return np.zeros((0, 5), dtype=np.uint32)
+        arr = np.ctypeslib.as_array(ctypes.cast(p, ctypes.POINTER(c_uint32)), shape=(n, 5))
+        return arr.copy()
+
+    def overlaps_arrays(self, min_length) -> np.ndarray:
+        """Rows as a ``(n, 5)`` uint32 array ``(a, b, astart, aend, bend)`` on entry indices."""
+        l = _as_unsigned(min_length, "overlaps")
+        p, n = c_void_p(), c_uint64()
+        self._check(self._lib.ovl_overlaps(self._ctx, l, byref(p), byref(n)))
+        return self._rows_array(p, n.value)
+
+    # split form (device-resident timing)
+    def upload(self) -> None:
+        self._check(self._lib.ovl_upload(self._ctx))
+
+    def overlaps_device(self, min_length) -> int:
+        n = c_uint64()
+        self._check(self._lib.ovl_overlaps_device(self._ctx, _as_unsigned(min_length, "overlaps"),
+                                                  byref(n)))
+        return n.value
+
+    def fetch_rows(self) -> np.ndarray:
+        p, n = c_void_p(), c_uint64()
+        self._check(self._lib.ovl_fetch_rows(self._ctx, byref(p), byref(n)))
+        return self._rows_array(p, n.value)
+
+    def set_collect_stats(self, on: bool) -> None:
+        self._check(self._lib.ovl_set_collect_stats(self._ctx, int(bool(on))))
+
+    def stats(self) -> dict:
+        st = OvlStats()
+        self._check(self._lib.ovl_get_stats(self._ctx, byref(st)))
+        return st.as_dict()
+
+    def debug_packed(self, idx: int) -> np.ndarray:
+        n = c_size_t()
+        cap = (int(self.lengths()[idx]) + 63) // 64 * 16
+        out = np.zeros(max(cap, 1), dtype=np.uint8)
+        self._check(self._lib.ovl_debug_packed(self._ctx, idx, out.ctypes.data, cap, byref(n)))
+        return out[:n.value]
+
+    # ---- multi-GPU (one process per GPU) ---------------------------------------------------
+    @staticmethod
+    def comm_unique_id() -> bytes:
+        lib = _capi.load_library()
+        buf = (ctypes.c_uint8 * 128)()
+        rc = lib.ovl_comm_unique_id(buf)
+        if rc != _capi.OVL_OK:
+            _capi.raise_for(rc, (lib.ovl_last_error(None) or b"").decode("utf-8", "replace"))
+        return bytes(buf)
+
+    def comm_init(self, uid: bytes, rank: int, nranks: int) -> None:
+        buf = (ctypes.c_uint8 * 128).from_buffer_copy(uid)
+        self._check(self._lib.ovl_comm_init(self._ctx, buf, int(rank), int(nranks)))
+
+    def comm_sync_ranges(self) -> None:
+        self._check(self._lib.ovl_comm_sync_ranges(self._ctx))
+
+    def comm_gather_rows(self) -> np.ndarray:
+        p, n = c_void_p(), c_uint64()
+        self._check(self._lib.ovl_comm_gather_rows(self._ctx, byref(p), byref(n)))
+        return self._rows_array(p, n.value)

@@ -1,0 +1,74 @@
+"""Shared test helpers (TEST code: may import oracle/)."""
+import json
+import os
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+GOLDEN = os.path.join(ROOT, "tests", "golden")
+
+_RC = bytes.maketrans(b"ACGT", b"TGCA")
+
+
+def revcomp(s: str) -> str:
+    return s.encode("ascii").translate(_RC)[::-1].decode("ascii")
+
+
+def load_tiny():
+    with open(os.path.join(GOLDEN, "tiny.json")) as f:
+        d = json.load(f)
+    for c in d["tiny"]:
+        c["entries"] = [tuple(e) for e in c["entries"]]
+        c["rows"] = [tuple(r) for r in c["rows"]]
+    d["toy"]["reads"] = [tuple(r) for r in d["toy"]["reads"]]
+    d["toy"]["rows"] = [tuple(r) for r in d["toy"]["rows"]]
+    return d
+
+
+def load_mid():
+    return np.load(os.path.join(GOLDEN, "mid.npz"))
+
+
+def sort_rows(arr: np.ndarray) -> np.ndarray:
+    arr = np.asarray(arr, dtype=np.uint32).reshape(-1, 5)
+    if len(arr) == 0:
+        return arr
+    order = np.lexsort((arr[:, 4], arr[:, 3], arr[:, 2], arr[:, 1], arr[:, 0]))
+    return arr[order]
+
+
+def reads_of(buf, off, names):
+    return [(n, buf[int(off[i]):int(off[i + 1])].tobytes().decode()) for i, n in enumerate(names)]
+
+
+def reads_to_buffer(reads):
+    bs = [s.encode() for _, s in reads]
+    off = np.zeros(len(bs) + 1, dtype=np.uint64)
+    if bs:
+        off[1:] = np.cumsum([len(b) for b in bs], dtype=np.uint64)
+    buf = np.frombuffer(b"".join(bs), dtype=np.uint8) if bs else np.zeros(0, np.uint8)
+    return buf, off, [n for n, _ in reads]
+
+
+MID_SPECS = {
+    # key in mid.npz -> how to regenerate the input
+    "edge_s3_l200": ("edge", 3, 200),
+    "edge_s4_l33": ("edge", 4, 33),
+    "edge_s5_l20": ("edge", 5, 20),
+    "cfg1_x0.02": ("cfg", 1, 0.02),
+    "cfg2_x0.015": ("cfg", 2, 0.015),
+    "cfg3_x0.002": ("cfg", 3, 0.002),
+    "cfg4_x0.004": ("cfg", 4, 0.004),
+    "cfg5_x0.001": ("cfg", 5, 0.001),
+}
+
+
+def mid_input(key):
+    """-> (reads [(name, seq)], min_length) of a mid.npz golden vector."""
+    from phasm_b200 import synth
+    kind, x, y = MID_SPECS[key]
+    if kind == "edge":
+        return synth.edge_mix(x, y), y
+    sh = synth.CONFIGS[x].scaled(y)
+    buf, off, names = synth.generate(sh)
+    return reads_of(buf, off, names), sh.min_length

@@ -1,0 +1,251 @@
+"""GPU parity tests: the CUDA path, called through the C ABI (ctypes -> libphasm_ovl.so), against
+
+* the golden vectors generated from the COMPILED REFERENCE (tests/golden, make_golden.py),
+* the C restatement oracle (oracle/overlap_oracle.c) on fresh seeded inputs,
+* the brute-force restatement (oracle/bruteforce.py) on tiny random sets,
+* size-independent properties (mirror invariant, restriction property, idempotence).
+
+Bit-exact: the row multiset (a, b, astart, aend, bstart=0, bend) must be identical after a
+canonical sort, duplicates included.
+"""
+import random
+
+import numpy as np
+import pytest
+
+import helpers
+from helpers import revcomp, sort_rows
+
+pytestmark = pytest.mark.gpu
+
+
+@pytest.fixture(scope="module")
+def ov():
+    from phasm_b200.overlapper import ExactOverlapper
+    o = ExactOverlapper()
+    yield o
+    o.close()
+
+
+def run_entries(ov, entries, l):
+    ov.clear()
+    for eid, seq in entries:
+        ov.add_sequence(eid, seq)
+    return sorted(ov.overlaps(l))
+
+
+def run_reads_idx(ov, reads, l):
+    ov.clear()
+    for name, seq in reads:
+        ov.add_read(name, seq)
+    return sort_rows(ov.overlaps_arrays(l))
+
+
+# ---- K1: pack + reverse complement ---------------------------------------------------------
+def unpack(packed: np.ndarray, n: int) -> str:
+    codes = np.zeros(len(packed) * 4, dtype=np.uint8)
+    for j in range(4):
+        codes[j::4] = (packed >> (2 * j)) & 3
+    return np.frombuffer(b"ACTG", dtype=np.uint8)[codes[:n]].tobytes().decode()
+
+
+def test_pack_and_revcomp_roundtrip(ov):
+    rnd = random.Random(7)
+    reads = []
+    for n in [0, 1, 2, 15, 16, 17, 31, 32, 33, 63, 64, 65, 127, 128, 129, 1000, 4097]:
+        reads.append(("p%d" % n, "".join(rnd.choice("ACGT") for _ in range(n))))
+    ov.clear()
+    for name, seq in reads:
+        ov.add_read(name, seq)
+    ov.overlaps_arrays(1 << 30)  # nothing is long enough: pack only
+    for i, (name, seq) in enumerate(reads):
+        fw = ov.debug_packed(2 * i)
+        rc = ov.debug_packed(2 * i + 1)
+        assert len(fw) == (len(seq) + 63) // 64 * 16
+        assert unpack(fw, len(seq)) == seq
+        assert unpack(rc, len(seq)) == revcomp(seq)
+        # zero padding up to the granule boundary (the scan relies on it)
+        assert unpack(fw, len(fw) * 4)[len(seq):] == "A" * (len(fw) * 4 - len(seq))
+        assert unpack(rc, len(rc) * 4)[len(seq):] == "A" * (len(rc) * 4 - len(seq))
+
+
+def test_non_acgt_is_rejected(ov):
+    for bad in ("ACGTNACGT", "acgtacgtac", "ACGT ACGT", "ACGU", "ACG\x00"):
+        ov.clear()
+        ov.add_sequence("x", "ACGTACGTACGT")
+        ov.add_sequence("bad", bad)
+        with pytest.raises(ValueError):
+            ov.overlaps(3)
+    ov.clear()
+    ov.add_read("y", "ACGTTTGN")
+    with pytest.raises(ValueError):
+        ov.overlaps(3)
+
+
+# ---- golden vectors from the compiled reference ---------------------------------------------
+def test_golden_toy_fasta(ov):
+    g = helpers.load_tiny()["toy"]
+    ov.clear()
+    for name, seq in g["reads"]:
+        ov.add_read(name, seq)
+    got = sorted(ov.overlaps(g["min_length"]))
+    assert got == sorted(g["rows"])
+    assert len(got) == 11
+    assert ("read1+", "read2+", 3, 7, 0, 4) in got
+
+
+def test_golden_tiny_cases(ov):
+    cases = helpers.load_tiny()["tiny"]
+    assert len(cases) >= 300
+    for i, c in enumerate(cases):
+        got = run_entries(ov, c["entries"], c["min_length"])
+        assert got == sorted(c["rows"]), "tiny case %d (l=%d): %r" % (i, c["min_length"], c["entries"])
+
+
+@pytest.mark.parametrize("key", sorted(helpers.MID_SPECS))
+def test_golden_mid(ov, key):
+    want = sort_rows(helpers.load_mid()[key])
+    reads, l = helpers.mid_input(key)
+    got = run_reads_idx(ov, reads, l)
+    assert got.shape == want.shape
+    assert np.array_equal(got, want)
+
+
+# ---- oracle on fresh inputs -----------------------------------------------------------------
+def test_bruteforce_random_tiny(ov):
+    from oracle.bruteforce import both_strand_entries, overlaps_bruteforce
+    rnd = random.Random(99)
+    for it in range(150):
+        alpha = rnd.choice(["A", "AC", "ACG", "ACGT"])
+        ents = []
+        for i in range(rnd.randint(1, 8)):
+            s = "".join(rnd.choice(alpha) for _ in range(rnd.randint(0, 40)))
+            if ents and rnd.random() < 0.4:
+                t = rnd.choice(ents)[1]
+                if t:
+                    i0 = rnd.randrange(len(t))
+                    i1 = rnd.randint(i0, len(t))
+                    s = rnd.choice([t[i0:i1] + s, s + t[i0:i1], t[i0:i1], t])
+            ents.append(("e%d" % i, s))
+        if rnd.random() < 0.5:
+            ents = both_strand_entries(ents)
+        l = rnd.choice([0, 1, 2, 3, 5, 8, 13, 31, 32, 33, 34])
+        assert run_entries(ov, ents, l) == overlaps_bruteforce(ents, l), (it, l, ents)
+
+
+@pytest.mark.parametrize("cid,factor", [(1, 0.05), (2, 0.04), (4, 0.02)])
+def test_oracle_port_config_shapes(ov, cid, factor):
+    from oracle import port
+    from phasm_b200 import synth
+    sh = synth.CONFIGS[cid].scaled(factor)
+    sh = synth.Shape(sh.name, sh.genome, sh.ploidy, sh.cov, sh.read_len, sh.min_length,
+                     sh.seed + 77, sh.snp_rate, sh.n_dups, sh.dup_len, sh.dup_div)
+    buf, off, names = synth.generate(sh)
+    reads = helpers.reads_of(buf, off, names)
+    from oracle.bruteforce import both_strand_entries
+    ebuf, eoff = port.entries_to_buffer(both_strand_entries(reads))
+    want, ost = port.oracle_overlaps(ebuf, eoff, sh.min_length)
+    ov.clear()
+    ov.set_collect_stats(True)
+    ov.add_reads_bulk(buf, off, names)
+    got = sort_rows(ov.overlaps_arrays(sh.min_length))
+    st = ov.stats()
+    ov.set_collect_stats(False)
+    assert np.array_equal(got, sort_rows(want))
+    assert st["rows"] == ost["rows"] and st["hits"] == ost["hits"]
+    assert st["anchors"] == ost["anchors"]
+    assert st["scan_positions"] == ost["positions"]
+    if sh.min_length >= 32:
+        # same canonical candidate definition; self candidates are dropped
+        # before the comparison on the device and never counted by the oracle
+        assert st["candidates"] >= ost["candidates"]
+        assert st["compared_bases"] == ost["compared_bases"]
+        assert st["operand_bytes"] == ost["operand_bytes"]
+
+
+def test_variable_lengths_and_short_l(ov):
+    from oracle import port
+    from oracle.bruteforce import both_strand_entries
+    from phasm_b200 import synth
+    for seed, l in ((11, 64), (12, 17), (13, 5)):
+        reads = synth.edge_mix(seed, l, n_reads=120, genome=20000, max_len=1500)
+        ebuf, eoff = port.entries_to_buffer(both_strand_entries(reads))
+        want, _ = port.oracle_overlaps(ebuf, eoff, l)
+        got = run_reads_idx(ov, reads, l)
+        assert np.array_equal(got, sort_rows(want)), (seed, l)
+
+
+# ---- properties -----------------------------------------------------------------------------
+def test_mirror_invariant_and_idempotence(ov):
+    from phasm_b200 import synth
+    sh = synth.CONFIGS[1].scaled(0.03)
+    buf, off, names = synth.generate(sh)
+    ov.clear()
+    ov.add_reads_bulk(buf, off, names)
+    r1 = sort_rows(ov.overlaps_arrays(sh.min_length))
+    r2 = sort_rows(ov.overlaps_arrays(sh.min_length))
+    assert np.array_equal(r1, r2)                      # repeatable, index rebuilt per call
+    lens = ov.lengths()
+    rows = set(map(tuple, r1.tolist()))
+    # (a,b,|a|-L,|a|,L) in R1  <=>  (b^,a^,|b|-L,|b|,L) in R1   
+    for a, b, s, e, be in r1.tolist():
+        if e == lens[a] and be == e - s:               # a suffix-prefix row
+            L = be
+            assert (b ^ 1, a ^ 1, int(lens[b]) - L, int(lens[b]), L) in rows
+    assert len(r1) > 0
+
+
+def test_restriction_property(ov):
+    """overlaps(S') == overlaps(S) filtered to pairs inside S' (SURVEY.md 3.3)."""
+    from phasm_b200 import synth
+    sh = synth.CONFIGS[2].scaled(0.02)
+    buf, off, names = synth.generate(sh)
+    reads = helpers.reads_of(buf, off, names)
+    full = run_reads_idx(ov, reads, sh.min_length)
+    keep = np.arange(0, len(reads), 2)
+    sub = run_reads_idx(ov, [reads[i] for i in keep], sh.min_length)
+    remap = -np.ones(2 * len(reads), dtype=np.int64)
+    for j, i in enumerate(keep):
+        remap[2 * i] = 2 * j
+        remap[2 * i + 1] = 2 * j + 1
+    f = full[(remap[full[:, 0]] >= 0) & (remap[full[:, 1]] >= 0)].copy()
+    f[:, 0] = remap[f[:, 0]]
+    f[:, 1] = remap[f[:, 1]]
+    assert np.array_equal(sort_rows(f), sub)
+
+
+# ---- API behaviour of the reference binding ----------------------------------
+def test_api_behaviour(ov):
+    ov.clear()
+    assert ov.overlaps(5) == []                         # the reference segfaults; we return []
+    ov.add_sequence("only", "")
+    assert ov.overlaps(0) == []
+    ov.clear()
+    ov.add_sequence("dup", "ACGTACGTAA")
+    ov.add_sequence("dup", "ACGTAAGGGG")                 # ids are opaque: duplicates allowed
+    ov.add_sequence(b"bytes-id", b"GGGGCC")              # bytes accepted
+    rows = ov.overlaps(4)
+    assert ("dup", "dup", 4, 10, 0, 6) in rows
+    assert ("dup", "bytes-id", 6, 10, 0, 4) in rows
+    with pytest.raises(TypeError):
+        ov.overlaps(-1)
+    with pytest.raises(TypeError):
+        ov.overlaps(2.5)
+    with pytest.raises(TypeError):
+        ov.add_sequence("x", 5)
+    # min_length 0 behaves as 1; can be called again after more add_sequence calls
+    r0, r1 = ov.overlaps(0), ov.overlaps(1)
+    assert r0 == r1
+    ov.add_sequence("late", "CCAAAA")
+    assert ("bytes-id", "late", 4, 6, 0, 2) in ov.overlaps(2)
+
+
+def test_self_reverse_complement_pairs_are_reported(ov):
+    # identity is by entry index: x+ vs x- ARE compared (overlapper.cpp:72-74)
+    ov.clear()
+    pal = "ACGTTGCATGCAACGT"                             # equals its own reverse complement
+    assert revcomp(pal) == pal
+    ov.add_read("pal", pal)
+    rows = ov.overlaps(4)
+    assert ("pal+", "pal-", 0, 16, 0, 16) in rows and ("pal-", "pal+", 0, 16, 0, 16) in rows
+    assert rows.count(("pal+", "pal-", 0, 16, 0, 16)) == 2   # R1 + R2 duplicate row

@@ -1,0 +1,110 @@
+"""CPU tests: pin the oracles (oracle/bruteforce.py, oracle/overlap_oracle.c) against the golden
+vectors the COMPILED REFERENCE produced (tests/golden/make_golden.py) and, where oracle/_ref
+is present, against the compiled reference itself on fresh inputs."""
+import random
+
+import numpy as np
+import pytest
+
+import helpers
+from helpers import sort_rows
+from oracle import port, ref
+from oracle.bruteforce import both_strand_entries, overlaps_bruteforce, revcomp
+
+
+def port_rows(entries, l):
+    buf, off = port.entries_to_buffer(entries)
+    rows, st = port.oracle_overlaps(buf, off, l)
+    return port.rows_to_tuples(rows, [i for i, _ in entries]), st
+
+
+def test_bruteforce_matches_golden_toy_and_tiny():
+    g = helpers.load_tiny()
+    toy = g["toy"]
+    ents = both_strand_entries(toy["reads"])
+    assert overlaps_bruteforce(ents, toy["min_length"]) == sorted(toy["rows"])
+    assert len(toy["rows"]) == 11
+    for c in g["tiny"]:
+        assert overlaps_bruteforce(c["entries"], c["min_length"]) == sorted(c["rows"])
+
+
+def test_port_matches_golden_toy_and_tiny():
+    g = helpers.load_tiny()
+    toy = g["toy"]
+    got, _ = port_rows(both_strand_entries(toy["reads"]), toy["min_length"])
+    assert got == sorted(toy["rows"])
+    for c in g["tiny"]:
+        got, _ = port_rows(c["entries"], c["min_length"])
+        assert got == sorted(c["rows"])
+
+
+@pytest.mark.parametrize("key", sorted(helpers.MID_SPECS))
+def test_port_matches_golden_mid(key):
+    want = sort_rows(helpers.load_mid()[key])
+    reads, l = helpers.mid_input(key)
+    buf, off = port.entries_to_buffer(both_strand_entries(reads))
+    got, st = port.oracle_overlaps(buf, off, l)
+    assert np.array_equal(sort_rows(got), want)
+    assert st["rows"] == len(want)
+
+
+def test_port_thread_count_does_not_change_result():
+    reads, l = helpers.mid_input("edge_s4_l33")
+    buf, off = port.entries_to_buffer(both_strand_entries(reads))
+    r1, s1 = port.oracle_overlaps(buf, off, l, nthreads=1)
+    r4, s4 = port.oracle_overlaps(buf, off, l, nthreads=4)
+    assert np.array_equal(r1, r4) and s1 == s4
+
+
+def test_port_matches_bruteforce_random():
+    rnd = random.Random(5)
+    for _ in range(200):
+        ents = []
+        for i in range(rnd.randint(1, 6)):
+            s = "".join(rnd.choice("ACGT"[:rnd.randint(1, 4)]) for _ in range(rnd.randint(0, 30)))
+            if ents and rnd.random() < 0.4 and ents[-1][1]:
+                t = ents[-1][1]
+                s = rnd.choice([t[len(t) // 2:] + s, t, t[1:], s + t[:len(t) // 2]])
+            ents.append(("e%d" % i, s))
+        if rnd.random() < 0.5:
+            ents = both_strand_entries(ents)
+        l = rnd.choice([0, 1, 2, 3, 7, 31, 32, 33])
+        got, _ = port_rows(ents, l)
+        assert got == overlaps_bruteforce(ents, l)
+
+
+def test_revcomp():
+    assert revcomp("AACGT") == "ACGTT"
+    assert revcomp("") == ""
+
+
+@pytest.mark.skipif(not ref.available(), reason="oracle/_ref (compiled reference) not built here")
+def test_oracles_match_compiled_reference_on_fresh_inputs():
+    rnd = random.Random(31337)
+    for _ in range(60):
+        ents = []
+        for i in range(rnd.randint(1, 7)):
+            s = "".join(rnd.choice("ACGT"[:rnd.randint(1, 4)]) for _ in range(rnd.randint(0, 20)))
+            if ents and rnd.random() < 0.4 and ents[-1][1]:
+                t = ents[-1][1]
+                s = rnd.choice([t[len(t) // 2:] + s, t, t[1:]])
+            ents.append(("e%d" % i, s))
+        if all(not s for _, s in ents):
+            continue  # the reference segfaults when every entry is empty
+        ents = both_strand_entries(ents) if rnd.random() < 0.5 else ents
+        l = rnd.randint(0, 6)
+        want = ref.ref_overlaps(ents, l)
+        assert overlaps_bruteforce(ents, l) == want
+        assert port_rows(ents, l)[0] == want
+
+
+@pytest.mark.skipif(not ref.available(), reason="oracle/_ref (compiled reference) not built here")
+def test_port_matches_compiled_reference_mid():
+    from phasm_b200 import synth
+    sh = synth.CONFIGS[1].scaled(0.01)
+    sh = synth.Shape(sh.name, sh.genome, sh.ploidy, sh.cov, sh.read_len, sh.min_length, 4242)
+    buf, off, names = synth.generate(sh)
+    ents = both_strand_entries(helpers.reads_of(buf, off, names))
+    want = ref.ref_overlaps(ents, sh.min_length)
+    assert port_rows(ents, sh.min_length)[0] == want
+    assert len(want) > 100
