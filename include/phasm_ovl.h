@@ -127,6 +127,12 @@ int ovl_fetch_rows(ovl_ctx *ctx, const ovl_row **rows, uint64_t *n_rows);
 int ovl_set_collect_stats(ovl_ctx *ctx, int on);
 int ovl_get_stats(const ovl_ctx *ctx, ovl_stats *out);
 
+/* Device-side stopwatch on the stream every kernel of this ctx is launched on (the CUDA-event
+ * bracket bench.py times K steps with): start records an event, stop records a second one,
+ * waits for it and returns the elapsed milliseconds between the two. */
+int ovl_timer_start(ovl_ctx *ctx);
+int ovl_timer_stop(ovl_ctx *ctx, float *ms);
+
 /* ---- multi-GPU (one process per GPU) ---------------------------------------------------
  * All ranks add the SAME entry table in the same order; rank r scans only the A entries of
  * its contiguous, base-balanced range and returns only those rows.  The rank's packed reads
@@ -138,7 +144,9 @@ int ovl_comm_init(ovl_ctx *ctx, const uint8_t id[128], int rank, int nranks);
 /* After ovl_upload on every rank: exchange the local entry ranges and check that they tile the
  * entry table in rank order. */
 int ovl_comm_sync_ranges(ovl_ctx *ctx);
-/* Gather every rank's rows to rank 0 (rank order == canonical order); other ranks get 0. */
+/* Gather every rank's rows to rank 0 (rank order == canonical order); other ranks get 0.
+ * The _device form leaves the gathered rows in rank 0's HBM (ovl_fetch_rows reads them). */
+int ovl_comm_gather_rows_device(ovl_ctx *ctx, uint64_t *n_rows);
 int ovl_comm_gather_rows(ovl_ctx *ctx, const ovl_row **rows, uint64_t *n_rows);
 
 /* ---- debug / test hooks (device layout introspection) -----------------------------------

@@ -56,9 +56,12 @@ SIGNATURES = {
     "ovl_fetch_rows": (c_int, [_P, POINTER(c_void_p), POINTER(c_uint64)]),
     "ovl_set_collect_stats": (c_int, [_P, c_int]),
     "ovl_get_stats": (c_int, [_P, POINTER(OvlStats)]),
+    "ovl_timer_start": (c_int, [_P]),
+    "ovl_timer_stop": (c_int, [_P, POINTER(c_float)]),
     "ovl_comm_unique_id": (c_int, [c_void_p]),
     "ovl_comm_init": (c_int, [_P, c_void_p, c_int, c_int]),
     "ovl_comm_sync_ranges": (c_int, [_P]),
+    "ovl_comm_gather_rows_device": (c_int, [_P, POINTER(c_uint64)]),
     "ovl_comm_gather_rows": (c_int, [_P, POINTER(c_void_p), POINTER(c_uint64)]),
     "ovl_debug_packed": (c_int, [_P, c_uint32, c_void_p, c_size_t, POINTER(c_size_t)]),
 }

@@ -67,6 +67,7 @@ struct ovl_ctx {
     cudaStream_t st = nullptr, st_comm = nullptr;
     cudaEvent_t ev[E_COUNT] = {};
     cudaEvent_t ev_comm = nullptr, ev_pack = nullptr;
+    cudaEvent_t ev_t0 = nullptr, ev_t1 = nullptr;  // ovl_timer_*
     std::string err;
 
     // ---- host entry store ----
@@ -85,12 +86,13 @@ struct ovl_ctx {
     // ---- device ----
     DevBuf d_ascii, d_src, d_len, d_flags, d_gran0, d_gran_ent, d_packed;
     DevBuf d_anc_ent, d_anc_ent2, d_keys, d_keys2, d_table, d_filter, d_ctr, d_tmp;
-    DevBuf d_cand, d_hits, d_hits2, d_cnt, d_offs, d_rows;
+    DevBuf d_cand, d_hits, d_hits2, d_cnt, d_offs, d_rows, d_cnts;
     uint64_t* h_ctr = nullptr;  // pinned mirror of d_ctr
     uint64_t cand_cap = 0;
     uint64_t n_rows = 0;
     PinBuf h_rows;
     bool rows_fetched = false;
+    bool gathered = false;  // ovl_comm_gather_rows_device already ran for the current rows
     int collect = 0;
     ovl_stats stats{};
 
@@ -279,6 +281,8 @@ int ovl_create(int device, ovl_ctx** out) {
         for (int i = 0; i < E_COUNT; ++i) CK(cudaEventCreate(&x->ev[i]));
         CK(cudaEventCreateWithFlags(&x->ev_comm, cudaEventDisableTiming));
         CK(cudaEventCreateWithFlags(&x->ev_pack, cudaEventDisableTiming));
+        CK(cudaEventCreate(&x->ev_t0));
+        CK(cudaEventCreate(&x->ev_t1));
         CK(cudaHostAlloc(reinterpret_cast<void**>(&x->h_ctr), C_COUNT * sizeof(uint64_t), cudaHostAllocDefault));
         OVL_TRY(dev_ensure(c, x->d_ctr, C_COUNT * sizeof(uint64_t), false));
         CK(cudaFuncSetAttribute(ovl::k3_scan<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, 128 * 1024));
@@ -297,7 +301,7 @@ void ovl_destroy(ovl_ctx* c) {
     DevBuf* bufs[] = {&c->d_ascii, &c->d_src, &c->d_len, &c->d_flags, &c->d_gran0, &c->d_gran_ent,
                       &c->d_packed, &c->d_anc_ent, &c->d_anc_ent2, &c->d_keys, &c->d_keys2,
                       &c->d_table, &c->d_filter, &c->d_ctr, &c->d_tmp, &c->d_cand, &c->d_hits,
-                      &c->d_hits2, &c->d_cnt, &c->d_offs, &c->d_rows};
+                      &c->d_hits2, &c->d_cnt, &c->d_offs, &c->d_rows, &c->d_cnts};
     for (DevBuf* b : bufs)
         if (b->p) cudaFree(b->p);
     if (c->ascii.p) cudaFreeHost(c->ascii.p);
@@ -308,6 +312,8 @@ void ovl_destroy(ovl_ctx* c) {
         if (c->ev[i]) cudaEventDestroy(c->ev[i]);
     if (c->ev_comm) cudaEventDestroy(c->ev_comm);
     if (c->ev_pack) cudaEventDestroy(c->ev_pack);
+    if (c->ev_t0) cudaEventDestroy(c->ev_t0);
+    if (c->ev_t1) cudaEventDestroy(c->ev_t1);
     if (c->st) cudaStreamDestroy(c->st);
     if (c->st_comm) cudaStreamDestroy(c->st_comm);
     (void)cudaGetLastError();
@@ -409,6 +415,7 @@ int ovl_clear(ovl_ctx* c) {
     c->uploaded = false;
     c->n_rows = 0;
     c->rows_fetched = false;
+    c->gathered = false;
     c->e_lo = c->e_hi = 0;
     return OVL_OK;
 }
@@ -441,6 +448,22 @@ int ovl_set_collect_stats(ovl_ctx* c, int on) {
 int ovl_get_stats(const ovl_ctx* c, ovl_stats* out) {
     if (!c || !out) return OVL_E_ARG;
     *out = c->stats;
+    return OVL_OK;
+}
+
+int ovl_timer_start(ovl_ctx* c) {
+    if (!c) return OVL_E_ARG;
+    OVL_TRY(set_dev(c));
+    CK(cudaEventRecord(c->ev_t0, c->st));
+    return OVL_OK;
+}
+
+int ovl_timer_stop(ovl_ctx* c, float* ms) {
+    if (!c || !ms) return OVL_E_ARG;
+    OVL_TRY(set_dev(c));
+    CK(cudaEventRecord(c->ev_t1, c->st));
+    CK(cudaEventSynchronize(c->ev_t1));
+    CK(cudaEventElapsedTime(ms, c->ev_t0, c->ev_t1));
     return OVL_OK;
 }
 
@@ -519,6 +542,7 @@ int ovl_overlaps_device(ovl_ctx* c, uint32_t min_length, uint64_t* n_rows_out) {
     S.kmer = (uint32_t)k;
     c->n_rows = 0;
     c->rows_fetched = false;
+    c->gathered = false;
     if (n_rows_out) *n_rows_out = 0;
     if (M == 0) return OVL_OK;  // the reference segfaults here; we return no rows
 
@@ -882,28 +906,29 @@ int ovl_comm_sync_ranges(ovl_ctx* c) {
     return OVL_OK;
 }
 
-int ovl_comm_gather_rows(ovl_ctx* c, const ovl_row** rows, uint64_t* n_rows) {
-    if (!c || !rows || !n_rows) return OVL_E_ARG;
+// Gather every rank's rows into rank 0's HBM (rank order == canonical order); rows stay on the
+// device.  Idempotent per ovl_overlaps_device call.
+int ovl_comm_gather_rows_device(ovl_ctx* c, uint64_t* n_rows) {
+    if (!c) return OVL_E_ARG;
     OVL_TRY(set_dev(c));
-    *rows = nullptr;
-    *n_rows = 0;
-    if (c->nranks == 1) return ovl_fetch_rows(c, rows, n_rows);
+    if (n_rows) *n_rows = 0;
+    if (c->nranks == 1 || c->gathered) {
+        if (n_rows) *n_rows = c->n_rows;
+        return OVL_OK;
+    }
     auto& N = nccl_dyn::api();
     const int R = c->nranks;
     // counts
-    OVL_TRY(dev_ensure(c, c->d_tmp, 8ull * R));
-    uint64_t* d = c->d_tmp.as<uint64_t>();
-    CK(cudaMemcpyAsync(d + c->rank, &c->n_rows, 8, cudaMemcpyHostToDevice, c->st));
+    OVL_TRY(dev_ensure(c, c->d_cnts, 8ull * R));
+    uint64_t* d = c->d_cnts.as<uint64_t>();
+    c->h_ctr[C_SELF] = c->n_rows;
+    CK(cudaMemcpyAsync(d + c->rank, &c->h_ctr[C_SELF], 8, cudaMemcpyHostToDevice, c->st));
     CKN(N.AllGather(d + c->rank, d, 1, ncclUint64, c->comm, c->st));
     std::vector<uint64_t> cnt(R);
     CK(cudaMemcpyAsync(cnt.data(), d, 8ull * R, cudaMemcpyDeviceToHost, c->st));
     CK(cudaStreamSynchronize(c->st));
-    uint64_t total = 0, before = 0;
-    for (int r = 0; r < R; ++r) {
-        if (r < c->rank) before += cnt[r];
-        total += cnt[r];
-    }
-    CK(cudaEventRecord(c->ev[E_D2H0], c->st));
+    uint64_t total = 0;
+    for (int r = 0; r < R; ++r) total += cnt[r];
     if (c->rank == 0) {
         // grow d_rows to hold everything, keeping the local rows at the front
         if (total * sizeof(ovl_row) > c->d_rows.cap) {
@@ -922,22 +947,28 @@ int ovl_comm_gather_rows(ovl_ctx* c, const ovl_row** rows, uint64_t* n_rows) {
         }
         CKN(N.GroupEnd());
         c->n_rows = total;
-        c->rows_fetched = false;
         c->stats.rows = total;
-        OVL_TRY(ovl_fetch_rows(c, rows, n_rows));
-        c->stats.ms_d2h = ev_ms(c, E_D2H0, E_D2H1);
     } else {
         if (c->n_rows) {
             CKN(N.GroupStart());
             CKN(N.Send(c->d_rows.p, c->n_rows * sizeof(ovl_row), ncclUint8, 0, c->comm, c->st));
             CKN(N.GroupEnd());
         }
-        CK(cudaEventRecord(c->ev[E_D2H1], c->st));
-        CK(cudaStreamSynchronize(c->st));
-        c->stats.ms_d2h = ev_ms(c, E_D2H0, E_D2H1);
+        c->n_rows = 0;
     }
-    (void)before;
+    CK(cudaStreamSynchronize(c->st));
+    c->rows_fetched = false;
+    c->gathered = true;
+    if (n_rows) *n_rows = c->n_rows;
     return OVL_OK;
+}
+
+int ovl_comm_gather_rows(ovl_ctx* c, const ovl_row** rows, uint64_t* n_rows) {
+    if (!c || !rows || !n_rows) return OVL_E_ARG;
+    *rows = nullptr;
+    *n_rows = 0;
+    OVL_TRY(ovl_comm_gather_rows_device(c, nullptr));
+    return ovl_fetch_rows(c, rows, n_rows);
 }
 
 // -----------------------------------------------------------------------------------------

@@ -201,6 +201,16 @@ class ExactOverlapper:
         self._check(self._lib.ovl_get_stats(self._ctx, byref(st)))
         return st.as_dict()
 
+    def timer_start(self) -> None:
+        """Record a CUDA event on the stream this object's kernels are launched on."""
+        self._check(self._lib.ovl_timer_start(self._ctx))
+
+    def timer_stop(self) -> float:
+        """Record a second event, wait for it; milliseconds since ``timer_start``."""
+        ms = ctypes.c_float()
+        self._check(self._lib.ovl_timer_stop(self._ctx, byref(ms)))
+        return ms.value
+
     def debug_packed(self, idx: int) -> np.ndarray:
         n = c_size_t()
         cap = (int(self.lengths()[idx]) + 63) // 64 * 16
@@ -224,6 +234,11 @@ class ExactOverlapper:
 
     def comm_sync_ranges(self) -> None:
         self._check(self._lib.ovl_comm_sync_ranges(self._ctx))
+
+    def comm_gather_rows_device(self) -> int:
+        n = c_uint64()
+        self._check(self._lib.ovl_comm_gather_rows_device(self._ctx, byref(n)))
+        return n.value
 
     def comm_gather_rows(self) -> np.ndarray:
         p, n = c_void_p(), c_uint64()
