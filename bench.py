@@ -277,7 +277,7 @@ def run_b200(args):
     barrier()
     if rank == 0:
         sampler.start()
-    stage = {k: 0.0 for k in ("ms_pack", "ms_anchor", "ms_scan", "ms_verify", "ms_emit", "ms_device")}
+    stage = {k: 0.0 for k in ("ms_pack", "ms_anchor", "ms_scan", "ms_sort", "ms_verify", "ms_emit", "ms_device")}
     launches = lib_launches = 0
     ov.timer_start()
     for _ in range(args.steps):

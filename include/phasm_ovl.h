@@ -53,18 +53,19 @@ typedef struct {
     uint64_t ascii_bytes;      /* host->device bytes of sequence data                     */
     uint64_t granules;         /* 64-base packed granules (16 B each)                     */
     uint64_t anchors;          /* entries with |b| >= min_length                          */
-    uint64_t anchor_keys;      /* distinct prefix k-mers                                  */
-    uint64_t candidates;       /* (a,p,b) emitted by the scan                             */
+    uint64_t candidates;       /* (a,p,b), a != b, emitted by the scan                    */
     uint64_t hits;             /* candidates that verified                                */
     uint64_t rows;
     uint64_t compared_bases;   /* sum m_c (only when stats collection is on, else 0)      */
     uint64_t operand_bytes;    /* sum 2*ceil(m_c/4), idem                                 */
     uint64_t scan_positions;   /* A positions with |a|-p >= min_length                    */
     uint32_t kmer;             /* anchor length k = min(max(l,1),32)                      */
+    uint32_t anchor_stride;    /* every stride-th A position is probed (1 = dense scan)   */
     uint32_t launches;         /* kernels of this library launched by the call            */
     uint32_t lib_launches;     /* CUB device-wide primitive calls (sort / scan)           */
     uint32_t retries;          /* scan re-runs after a candidate-buffer overflow          */
-    float ms_h2d, ms_pack, ms_anchor, ms_scan, ms_verify, ms_emit, ms_d2h;
+    uint32_t pad_;
+    float ms_h2d, ms_pack, ms_anchor, ms_scan, ms_sort, ms_verify, ms_emit, ms_d2h;
     float ms_device;           /* pack..emit: ASCII resident in HBM -> rows resident      */
     float ms_total;            /* h2d..d2h                                                */
 } ovl_stats;
@@ -123,8 +124,13 @@ int ovl_upload(ovl_ctx *ctx);
 int ovl_overlaps_device(ovl_ctx *ctx, uint32_t min_length, uint64_t *n_rows);
 int ovl_fetch_rows(ovl_ctx *ctx, const ovl_row **rows, uint64_t *n_rows);
 
-/* Collect sum m_c / operand bytes in the verifier (adds a little work; off by default). */
+/* Collect sum m_c / operand bytes in the verifier (off by default).  The byte accounting of
+ * SURVEY.md 8(d) is defined on the canonical candidates (first k-mer of B at every A position),
+ * so this also forces the dense stride-1 scan. */
 int ovl_set_collect_stats(ovl_ctx *ctx, int on);
+/* Tuning knobs.  "anchor_stride": 0 = auto (largest power of two <= min(64, l-k+1)), else an
+ * upper bound (1 forces the dense scan). */
+int ovl_set_option(ovl_ctx *ctx, const char *name, int64_t value);
 int ovl_get_stats(const ovl_ctx *ctx, ovl_stats *out);
 
 /* Device-side stopwatch on the stream every kernel of this ctx is launched on (the CUDA-event

@@ -24,12 +24,13 @@ class OvlRow(Structure):
 
 class OvlStats(Structure):
     _fields_ = ([(n, c_uint64) for n in
-                 ("entries", "bases", "ascii_bytes", "granules", "anchors", "anchor_keys",
+                 ("entries", "bases", "ascii_bytes", "granules", "anchors",
                   "candidates", "hits", "rows", "compared_bases", "operand_bytes",
                   "scan_positions")] +
-                [(n, c_uint32) for n in ("kmer", "launches", "lib_launches", "retries")] +
-                [(n, c_float) for n in ("ms_h2d", "ms_pack", "ms_anchor", "ms_scan", "ms_verify",
-                                        "ms_emit", "ms_d2h", "ms_device", "ms_total")])
+                [(n, c_uint32) for n in ("kmer", "anchor_stride", "launches", "lib_launches",
+                                         "retries", "pad_")] +
+                [(n, c_float) for n in ("ms_h2d", "ms_pack", "ms_anchor", "ms_scan", "ms_sort",
+                                        "ms_verify", "ms_emit", "ms_d2h", "ms_device", "ms_total")])
 
     def as_dict(self):
         return {n: getattr(self, n) for n, _ in self._fields_}
@@ -55,6 +56,7 @@ SIGNATURES = {
     "ovl_overlaps_device": (c_int, [_P, c_uint32, POINTER(c_uint64)]),
     "ovl_fetch_rows": (c_int, [_P, POINTER(c_void_p), POINTER(c_uint64)]),
     "ovl_set_collect_stats": (c_int, [_P, c_int]),
+    "ovl_set_option": (c_int, [_P, c_char_p, ctypes.c_int64]),
     "ovl_get_stats": (c_int, [_P, POINTER(OvlStats)]),
     "ovl_timer_start": (c_int, [_P]),
     "ovl_timer_stop": (c_int, [_P, POINTER(c_float)]),

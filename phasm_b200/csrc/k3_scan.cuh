@@ -1,55 +1,121 @@
-// k3_scan.cuh -- K3: streaming k-mer scan of every A position against the anchor table.
+// k3_scan.cuh -- K3: streaming k-mer scan of the A entries against the anchor table.
 //
 // Replaces the suffix-tree DFS push phase (/root/reference/src/overlapper.cpp:38-62): instead
 // of walking a suffix tree to learn which suffixes of A end at a node on the path to B's leaf,
-// every position p of every entry A with |A|-p >= l looks its k-mer up among the B prefixes.
+// A positions look their k-mer up among the indexed B k-mers (k2_anchor.cuh).
 //
-// Mapping: a warp owns a tile of 32 consecutive granules (2048 bases); each lane loads its
-// granule with ONE coalesced 128-bit load (512 B per warp), takes the following word from the
-// next lane by shuffle (the hash carry across granules), and tests its 64 positions against a
-// blocked bloom filter (shared memory when it fits, else L2-resident global).  Filter hits are
-// collected in a 64-bit mask and resolved afterwards, warp-converged, against the hash table;
-// candidates are appended with one warp-aggregated atomic per round.
+// Mapping (both kernels): a warp owns a tile of 32 consecutive granules (2048 bases); each lane
+// loads its granule with ONE coalesced 128-bit load (512 B per warp) and takes the following
+// word from the next lane by shuffle (the k-mer carry across granules).
 //
-// Roofline: nominally HBM (0.25 B per scanned base + 4 B per granule for gran_ent), in practice
-// integer-issue bound (~14 instructions per position); see DESIGN.md.
+//   k3_probe  (stride >= 2; stride 64 whenever l >= 95): only the positions q = 0 mod stride are
+//             probed -- 64/stride k-mers per granule, word-aligned for stride 32/64 -- against
+//             an L2-resident one-bit-per-key bitmap, then the hash table.  The kernel streams
+//             the packed reads at 0.25 B/base and is HBM/L2-latency bound, not issue bound.
+//   k3_scan   (stride 1: l < 33, or the canonical-candidate accounting pass): every position
+//             rolls its k-mer and tests a blocked bloom filter held in shared memory; filter
+//             hits are resolved afterwards, warp-converged, against the table.  ~14 integer
+//             instructions per position: issue bound.
+//
+// Candidates are 64-bit keys [a|b|p|00]; they are staged per warp in shared memory and
+// flushed with one global atomic per ~224 keys.
 #pragma once
+#include "k2_anchor.cuh"
 #include "ovl_common.cuh"
 
 namespace ovl {
 
 struct ScanParams {
-    const uint4* packed;        // granules (G + 1, last one zero)
+    const uint4* packed;        // granules (G + 2, last two zero)
     const uint32_t* gran_ent;   // [G]
-    const uint32_t* gran0;      // [M+1]
-    const uint32_t* len;        // [M]
+    const uint2* ent;           // [M] {gran0, len}
     uint32_t g_begin, g_end;    // granule range of the A entries this launch scans
     uint32_t l;                 // min overlap length (>= 1)
     int k;                      // anchor length
-    const uint32_t* filter;     // 2^fw_bits words
-    int fw_bits;
+    int stride_log2;
+    const uint32_t* filter;     // sparse: bitmap words; dense: bloom words
+    int bm_bits;                // sparse: log2 bits; dense: log2 words
     const Slot* table;
     int tbits;
-    const uint32_t* anc_ent;    // key-sorted B list
-    Cand* cand;
-    unsigned long long* n_cand; // total candidates found (may exceed cap)
-    uint64_t cap;
+    const uint32_t* next;
+    KeyFmt fmt;
+    CandSink sink;
 };
 
-__device__ __forceinline__ uint4 ldg_stream(const uint4* p) {
-    uint4 r;
-    asm volatile("ld.global.nc.L1::no_allocate.v4.u32 {%0,%1,%2,%3}, [%4];"
-                 : "=r"(r.x), "=r"(r.y), "=r"(r.z), "=r"(r.w)
-                 : "l"(p));
-    return r;
+// ---- sparse path ------------------------------------------------------------------------
+__global__ void __launch_bounds__(256) k3_probe(const ScanParams P) {
+    __shared__ uint64_t s_buf[8][WBUF];
+    const uint32_t lane = threadIdx.x & 31;
+    const uint32_t wib = threadIdx.x >> 5;
+    const uint32_t warp = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+    const uint32_t nwarps = (gridDim.x * blockDim.x) >> 5;
+    const uint32_t n_gran = P.g_end - P.g_begin;
+    const uint32_t n_tiles = (n_gran + 31) / 32;
+    const uint64_t kmask = kmer_mask(P.k);
+    const uint64_t* packed64 = reinterpret_cast<const uint64_t*>(P.packed);
+    const uint32_t stride = 1u << P.stride_log2;
+    const uint32_t n_probe = GRAN_BASES >> P.stride_log2;
+    uint64_t* buf = s_buf[wib];
+    uint32_t nbuf = 0;
+
+    for (uint32_t tile = warp; tile < n_tiles; tile += nwarps) {
+        const uint32_t g = P.g_begin + tile * 32 + lane;
+        const bool inr = g < P.g_end;
+        uint64_t w0 = 0, w1 = 0;
+        uint32_t a = 0, pos0 = 0, L = 0;
+        if (inr) {
+            const uint4 v = ldg_stream(P.packed + g);
+            w0 = (uint64_t)v.x | ((uint64_t)v.y << 32);
+            w1 = (uint64_t)v.z | ((uint64_t)v.w << 32);
+            a = __ldg(P.gran_ent + g);
+            const uint2 m = __ldg(P.ent + a);
+            L = m.y;
+            pos0 = (g - m.x) * GRAN_BASES;
+        }
+        uint64_t w2 = __shfl_down_sync(FULL, w0, 1);
+        if (lane == 31 && P.stride_log2 < 5) w2 = inr ? packed64[2ull * (g + 1)] : 0;
+        const bool a_ok = inr && L >= P.l;
+
+        for (uint32_t j = 0; j < n_probe; ++j) {
+            const uint32_t off = j << P.stride_log2;
+            const uint32_t q = pos0 + off;
+            uint32_t node = NIL;
+            if (a_ok && q + (uint32_t)P.k <= L) {
+                const uint64_t x = (off < 32 ? kmer_at(w0, w1, off) : kmer_at(w1, w2, off - 32)) & kmask;
+                const uint64_t h = mix64(x);
+                const uint32_t bit = bitmap_bit(h, P.bm_bits);
+                if ((__ldg(P.filter + (bit >> 5)) >> (bit & 31)) & 1u) node = table_find(P.table, P.tbits, x, h);
+            }
+            while (__any_sync(FULL, node != NIL)) {
+                bool have = false;
+                uint64_t key = 0;
+                if (node != NIL) {
+                    const uint32_t b = node >> P.stride_log2;
+                    const uint32_t delta = node & (stride - 1u);
+                    // candidate p = q - delta: needs p >= 0, |a| - p >= l, and b != a
+                    // (identity by index: overlapper.cpp:72-74,101-104)
+                    if (q >= delta && b != a && L - (q - delta) >= P.l) {
+                        have = true;
+                        key = P.fmt.make(a, b, q - delta);
+                    }
+                    node = __ldg(P.next + node);
+                }
+                wbuf_push(buf, nbuf, P.sink, lane, have, key);
+            }
+        }
+    }
+    if (nbuf) wbuf_flush(buf, nbuf, P.sink, lane);
 }
 
+// ---- dense path (stride 1) -----------------------------------------------------------------
 template <bool SMEM_FILTER>
 __global__ void __launch_bounds__(1024, 1) k3_scan(const ScanParams P) {
-    extern __shared__ uint32_t s_filter[];
+    extern __shared__ __align__(16) unsigned char s_raw[];
+    uint64_t* s_bufs = reinterpret_cast<uint64_t*>(s_raw);               // [32][WBUF]
+    uint32_t* s_filter = reinterpret_cast<uint32_t*>(s_raw + 32 * WBUF * 8);
     const uint32_t* filt;
     if (SMEM_FILTER) {
-        const uint32_t nw = 1u << P.fw_bits;
+        const uint32_t nw = 1u << P.bm_bits;
         for (uint32_t i = threadIdx.x; i < nw; i += blockDim.x) s_filter[i] = P.filter[i];
         __syncthreads();
         filt = s_filter;
@@ -63,7 +129,9 @@ __global__ void __launch_bounds__(1024, 1) k3_scan(const ScanParams P) {
     const uint32_t n_tiles = (n_gran + 31) / 32;
     const uint64_t kmask = kmer_mask(P.k);
     const uint64_t* packed64 = reinterpret_cast<const uint64_t*>(P.packed);
-    const int fwb = P.fw_bits;
+    const int fwb = P.bm_bits;
+    uint64_t* buf = s_bufs + (threadIdx.x >> 5) * WBUF;
+    uint32_t nbuf = 0;
 
     for (uint32_t tile = warp; tile < n_tiles; tile += nwarps) {
         const uint32_t g = P.g_begin + tile * 32 + lane;
@@ -76,10 +144,10 @@ __global__ void __launch_bounds__(1024, 1) k3_scan(const ScanParams P) {
             w0 = (uint64_t)v.x | ((uint64_t)v.y << 32);
             w1 = (uint64_t)v.z | ((uint64_t)v.w << 32);
             a = __ldg(P.gran_ent + g);
-            const uint32_t L = __ldg(P.len + a);
-            pos0 = (g - __ldg(P.gran0 + a)) * GRAN_BASES;
+            const uint2 m = __ldg(P.ent + a);
+            pos0 = (g - m.x) * GRAN_BASES;
             // positions p in [pos0, pos0+64) with L - p >= l
-            const int64_t nv = (int64_t)L - (int64_t)P.l + 1 - (int64_t)pos0;
+            const int64_t nv = (int64_t)m.y - (int64_t)P.l + 1 - (int64_t)pos0;
             nvalid = nv <= 0 ? 0 : (nv >= GRAN_BASES ? GRAN_BASES : (int)nv);
         }
         if (!__any_sync(FULL, nvalid > 0)) continue;
@@ -103,47 +171,32 @@ __global__ void __launch_bounds__(1024, 1) k3_scan(const ScanParams P) {
 
         // ---- resolve filter hits against the table, one position per lane per round ----
         while (__any_sync(FULL, hits != 0)) {
-            uint32_t start = 0, n_emit = 0, p = 0;
+            uint32_t node = NIL, p = 0;
             if (hits) {
                 const int j = __ffsll((long long)hits) - 1;
                 hits &= hits - 1;
                 p = pos0 + j;
                 const uint64_t x = (j < 32 ? kmer_at(w0, w1, j) : kmer_at(w1, w2, j - 32)) & kmask;
-                const uint32_t tmask = (1u << P.tbits) - 1u;
-                uint32_t s = slot_hash(kmer_hash(x)) >> (32 - P.tbits);
-                for (;;) {
-                    const Slot sl = P.table[s];
-                    if (sl.count == 0) break;
-                    if (sl.key == x) {
-                        start = sl.start;
-                        // the list may hold a itself (always at p == 0, and at p != 0 for
-                        // periodic reads); those records are written too and dropped by the
-                        // verifier (identity by index: overlapper.cpp:72-74,101-104)
-                        n_emit = sl.count;
-                        break;
+                node = table_find(P.table, P.tbits, x, mix64(x));
+            }
+            while (__any_sync(FULL, node != NIL)) {
+                bool have = false;
+                uint64_t key = 0;
+                if (node != NIL) {
+                    // stride 1: the anchor id IS b.  The list may hold a itself (always at
+                    // p == 0, and at p != 0 for periodic reads): identity by index,
+                    // overlapper.cpp:72-74,101-104
+                    if (node != a) {
+                        have = true;
+                        key = P.fmt.make(a, node, p);
                     }
-                    s = (s + 1) & tmask;
+                    node = __ldg(P.next + node);
                 }
-            }
-            // warp-aggregated slot allocation
-            uint32_t incl = n_emit;
-#pragma unroll
-            for (int d = 1; d < 32; d <<= 1) {
-                const uint32_t t = __shfl_up_sync(FULL, incl, d);
-                if (lane >= d) incl += t;
-            }
-            const uint32_t total = __shfl_sync(FULL, incl, 31);
-            if (total == 0) continue;
-            unsigned long long base = 0;
-            if (lane == 0) base = atomicAdd(P.n_cand, (unsigned long long)total);
-            base = __shfl_sync(FULL, base, 0);
-            if (n_emit) {
-                uint64_t o = base + (incl - n_emit);
-                for (uint32_t i = 0; i < n_emit; ++i, ++o)
-                    if (o < P.cap) P.cand[o] = Cand{a, p, __ldg(P.anc_ent + start + i), 0u};
+                wbuf_push(buf, nbuf, P.sink, lane, have, key);
             }
         }
     }
+    if (nbuf) wbuf_flush(buf, nbuf, P.sink, lane);
 }
 
 }  // namespace ovl

@@ -1,33 +1,40 @@
-// k5_emit.cuh -- K5: select-longest + deterministic compaction of verified hits into rows.
+// k5_emit.cuh -- K5: select-longest + deterministic compaction of verified candidates into rows.
 //
 // Replaces the two emission sites of the reference DFS:
 //   R1  /root/reference/src/overlapper.cpp:64-91   only the TOP of A's stack (= the longest
 //       suffix of A that is a prefix of B) is emitted per ordered pair (A,B);
 //   R2  /root/reference/src/overlapper.cpp:93-115  every occurrence of the whole B inside A.
 //
-// Input: 64-bit hit keys [a | b | p | cont | sp] radix-sorted ascending, so hits of one (a,b)
-// pair are adjacent and ordered by p.  rem = |a|-p falls as p grows, hence inside a pair the
-// flags go  CONT-only ... (CONT|SP at rem == |b|) ... SP-only: the first hit carrying SP is
-// the smallest p, i.e. the longest suffix-prefix overlap.  A hit with both flags yields the
-// same row twice -- that is the reference's duplicate row.
+// Input: the candidate keys [a | b | p | cont | sp], radix-sorted ascending BEFORE verification
+// (flag bits were zero then), with the flag bits of verified candidates set by K4.  Candidates
+// of one (a,b) pair are adjacent and ordered by p; failed candidates (flags 00) sit between
+// the hits.  rem = |a|-p falls as p grows, so the first key of a pair carrying SP is the
+// smallest p, i.e. the longest suffix-prefix overlap: a key with SP emits its R1 row iff no
+// EARLIER key of the same pair carries SP (look-back over the pair's keys, usually 0-2).  A
+// key with both flags yields the same row twice -- that is the reference's duplicate row
+// (SURVEY.md 3.3).
 //
-// Because rows of one hit share astart = p and hits are sorted by (a,b,p), the emitted rows are
+// Because rows of one key share astart = p and keys are sorted by (a,b,p), the emitted rows are
 // already in (a,b,astart,aend,bend) order: the output is deterministic and canonical.
 //
-// Roofline: HBM, 8 B read per hit (x2: count pass + emit pass) + 20 B written per row.
+// Roofline: HBM, 8 B read per candidate (x2: count pass + emit pass) + 20 B written per row.
 #pragma once
 #include "ovl_common.cuh"
 
 namespace ovl {
 
-__device__ __forceinline__ uint32_t hit_rows(const uint64_t* __restrict__ keys, uint64_t i,
+__device__ __forceinline__ uint32_t key_rows(const uint64_t* __restrict__ keys, uint64_t i,
                                              uint64_t key, int pair_shift) {
     uint32_t c = (key & HIT_CONT) ? 1u : 0u;
     if (key & HIT_SP) {
         bool first = true;
-        if (i) {
-            const uint64_t prev = keys[i - 1];
-            first = ((prev >> pair_shift) != (key >> pair_shift)) || !(prev & HIT_SP);
+        for (uint64_t j = i; j > 0;) {
+            const uint64_t prev = keys[--j];
+            if ((prev >> pair_shift) != (key >> pair_shift)) break;
+            if (prev & HIT_SP) {
+                first = false;
+                break;
+            }
         }
         c += first;
     }
@@ -37,25 +44,27 @@ __device__ __forceinline__ uint32_t hit_rows(const uint64_t* __restrict__ keys, 
 __global__ void __launch_bounds__(256)
 k5_count(const uint64_t* __restrict__ keys, uint64_t n, KeyFmt fmt, uint32_t* __restrict__ cnt) {
     const uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
-    if (i < n) cnt[i] = hit_rows(keys, i, keys[i], fmt.bits_p + 2);
+    if (i < n) {
+        const uint64_t key = keys[i];
+        cnt[i] = (key & 3) ? key_rows(keys, i, key, fmt.bits_p + 2) : 0u;
+    }
 }
 
 __global__ void __launch_bounds__(256)
 k5_emit(const uint64_t* __restrict__ keys, uint64_t n, KeyFmt fmt,
-        const uint64_t* __restrict__ offs, const uint32_t* __restrict__ len,
-        Row* __restrict__ rows) {
+        const uint64_t* __restrict__ offs, const uint32_t* __restrict__ cnt,
+        const uint2* __restrict__ ent, Row* __restrict__ rows) {
     const uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= n) return;
-    const uint64_t key = keys[i];
-    const uint32_t c = hit_rows(keys, i, key, fmt.bits_p + 2);
+    const uint32_t c = cnt[i];
     if (!c) return;
-    const uint32_t p = (uint32_t)((key >> 2) & ((1ull << fmt.bits_p) - 1ull));
-    const uint32_t b = (uint32_t)((key >> (2 + fmt.bits_p)) & ((1ull << fmt.bits_e) - 1ull));
-    const uint32_t a = (uint32_t)(key >> (2 + fmt.bits_p + fmt.bits_e));
-    const uint32_t la = __ldg(len + a), lb = __ldg(len + b);
+    const uint64_t key = keys[i];
+    const uint32_t p = fmt.p(key), b = fmt.b(key), a = fmt.a(key);
+    const uint32_t la = __ldg(ent + a).y, lb = __ldg(ent + b).y;
     uint64_t o = offs[i];
-    if (key & HIT_CONT) rows[o++] = Row{a, b, p, p + lb, lb};           // R2
-    if (o < offs[i] + c) rows[o] = Row{a, b, p, la, la - p};             // R1 (longest)
+    const uint64_t end = o + c;
+    if (key & HIT_CONT) rows[o++] = Row{a, b, p, p + lb, lb};  // R2
+    if (o < end) rows[o] = Row{a, b, p, la, la - p};           // R1 (longest)
 }
 
 }  // namespace ovl

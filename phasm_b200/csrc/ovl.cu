@@ -54,10 +54,10 @@ struct PinBuf {
     size_t cap = 0;
 };
 
-enum Ev { E_H2D0, E_PACK0, E_ANCHOR0, E_SCAN0, E_VERIFY0, E_EMIT0, E_END, E_D2H0, E_D2H1, E_COUNT };
+enum Ev { E_H2D0, E_PACK0, E_ANCHOR0, E_SCAN0, E_SORT0, E_VERIFY0, E_EMIT0, E_END, E_D2H0, E_D2H1, E_COUNT };
 
 // device counter block (one 64-bit word each)
-enum Ctr { C_ERR, C_NANC, C_NKEYS, C_NCAND, C_NHITS, C_SELF, C_SUMM, C_SUMB, C_COUNT };
+enum Ctr { C_ERR, C_NANC, C_NCAND, C_NHITS, C_SUMM, C_SUMB, C_COUNT };  // h_ctr has 2 spare words behind
 
 }  // namespace
 
@@ -84,9 +84,9 @@ struct ovl_ctx {
     uint32_t e_lo = 0, e_hi = 0;  // entries whose bases are local (contiguous)
 
     // ---- device ----
-    DevBuf d_ascii, d_src, d_len, d_flags, d_gran0, d_gran_ent, d_packed;
-    DevBuf d_anc_ent, d_anc_ent2, d_keys, d_keys2, d_table, d_filter, d_ctr, d_tmp;
-    DevBuf d_cand, d_hits, d_hits2, d_cnt, d_offs, d_rows, d_cnts;
+    DevBuf d_ascii, d_src, d_len, d_flags, d_gran0, d_gran_ent, d_ent, d_packed;
+    DevBuf d_table, d_filter, d_next, d_ctr, d_tmp;
+    DevBuf d_cand, d_cand2, d_cnt, d_offs, d_rows, d_cnts;
     uint64_t* h_ctr = nullptr;  // pinned mirror of d_ctr
     uint64_t cand_cap = 0;
     uint64_t n_rows = 0;
@@ -94,6 +94,7 @@ struct ovl_ctx {
     bool rows_fetched = false;
     bool gathered = false;  // ovl_comm_gather_rows_device already ran for the current rows
     int collect = 0;
+    int opt_stride = 0;  // 0 = auto; else upper bound on the anchor stride (1 = dense scan)
     ovl_stats stats{};
 
     // ---- multi-GPU ----
@@ -186,12 +187,6 @@ inline int ceil_log2(uint64_t x) {
 
 inline size_t align16(size_t x) { return (x + 15) & ~size_t(15); }
 
-struct LenGE {
-    const uint32_t* len;
-    uint32_t l;
-    __device__ __forceinline__ bool operator()(uint32_t e) const { return len[e] >= l; }
-};
-
 int push_entry(ovl_ctx* c, const char* id, size_t id_len, const char* sfx, uint64_t src, uint64_t n,
                uint8_t fl) {
     if (n > 0xfffffff0ull) return fail(c, OVL_E_LIMIT, "sequence of %llu bases exceeds the 32-bit position limit", (unsigned long long)n);
@@ -283,9 +278,10 @@ int ovl_create(int device, ovl_ctx** out) {
         CK(cudaEventCreateWithFlags(&x->ev_pack, cudaEventDisableTiming));
         CK(cudaEventCreate(&x->ev_t0));
         CK(cudaEventCreate(&x->ev_t1));
-        CK(cudaHostAlloc(reinterpret_cast<void**>(&x->h_ctr), C_COUNT * sizeof(uint64_t), cudaHostAllocDefault));
+        CK(cudaHostAlloc(reinterpret_cast<void**>(&x->h_ctr), (C_COUNT + 2) * sizeof(uint64_t), cudaHostAllocDefault));
         OVL_TRY(dev_ensure(c, x->d_ctr, C_COUNT * sizeof(uint64_t), false));
-        CK(cudaFuncSetAttribute(ovl::k3_scan<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, 128 * 1024));
+        CK(cudaFuncSetAttribute(ovl::k3_scan<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, 32 * ovl::WBUF * 8 + 128 * 1024));
+        CK(cudaFuncSetAttribute(ovl::k3_scan<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, 32 * ovl::WBUF * 8));
         return OVL_OK;
     };
     int rc = init();
@@ -299,9 +295,8 @@ void ovl_destroy(ovl_ctx* c) {
     cudaSetDevice(c->device);
     if (c->comm) nccl_dyn::api().CommDestroy(c->comm);
     DevBuf* bufs[] = {&c->d_ascii, &c->d_src, &c->d_len, &c->d_flags, &c->d_gran0, &c->d_gran_ent,
-                      &c->d_packed, &c->d_anc_ent, &c->d_anc_ent2, &c->d_keys, &c->d_keys2,
-                      &c->d_table, &c->d_filter, &c->d_ctr, &c->d_tmp, &c->d_cand, &c->d_hits,
-                      &c->d_hits2, &c->d_cnt, &c->d_offs, &c->d_rows, &c->d_cnts};
+                      &c->d_ent, &c->d_packed, &c->d_table, &c->d_filter, &c->d_next, &c->d_ctr,
+                      &c->d_tmp, &c->d_cand, &c->d_cand2, &c->d_cnt, &c->d_offs, &c->d_rows, &c->d_cnts};
     for (DevBuf* b : bufs)
         if (b->p) cudaFree(b->p);
     if (c->ascii.p) cudaFreeHost(c->ascii.p);
@@ -445,6 +440,16 @@ int ovl_set_collect_stats(ovl_ctx* c, int on) {
     return OVL_OK;
 }
 
+int ovl_set_option(ovl_ctx* c, const char* name, int64_t value) {
+    if (!c || !name) return OVL_E_ARG;
+    if (!strcmp(name, "anchor_stride")) {
+        if (value < 0 || value > 64 || (value & (value - 1))) return fail(c, OVL_E_ARG, "anchor_stride must be 0 (auto) or a power of two <= 64");
+        c->opt_stride = (int)value;
+        return OVL_OK;
+    }
+    return fail(c, OVL_E_ARG, "unknown option '%s'", name);
+}
+
 int ovl_get_stats(const ovl_ctx* c, ovl_stats* out) {
     if (!c || !out) return OVL_E_ARG;
     *out = c->stats;
@@ -507,7 +512,8 @@ int ovl_upload(ovl_ctx* c) {
         OVL_TRY(dev_ensure(c, c->d_flags, M));
         OVL_TRY(dev_ensure(c, c->d_gran0, (M + 1) * 4));
         OVL_TRY(dev_ensure(c, c->d_gran_ent, (g + 1) * 4));
-        OVL_TRY(dev_ensure(c, c->d_packed, (g + 1) * 16));
+        OVL_TRY(dev_ensure(c, c->d_ent, M * 8));
+        OVL_TRY(dev_ensure(c, c->d_packed, (g + 2) * 16));
         if (c->ascii.p) CK(cudaMemcpyAsync(c->d_ascii.p, c->ascii.p, ab, cudaMemcpyHostToDevice, c->st));
         CK(cudaMemcpyAsync(c->d_src.p, c->src.data(), M * 8, cudaMemcpyHostToDevice, c->st));
         CK(cudaMemcpyAsync(c->d_len.p, c->len.data(), M * 4, cudaMemcpyHostToDevice, c->st));
@@ -552,29 +558,55 @@ int ovl_overlaps_device(ovl_ctx* c, uint32_t min_length, uint64_t* n_rows_out) {
     fmt.bits_e = ceil_log2((uint64_t)M < 2 ? 2 : M);
     fmt.bits_p = ceil_log2(c->max_len + 1 < 2 ? 2 : c->max_len + 1);
     if (fmt.total() > 64)
-        return fail(c, OVL_E_LIMIT, "hit key needs %d bits (entries %u, longest %llu): over the 64-bit key layout",
+        return fail(c, OVL_E_LIMIT, "candidate key needs %d bits (entries %u, longest %llu): over the 64-bit key layout",
                     fmt.total(), M, (unsigned long long)c->max_len);
+    // anchor stride: largest power of two <= min(64, l-k+1); 1 = canonical dense scan
+    int slog = 0;
+    {
+        uint32_t smax = l - (uint32_t)k + 1;  // >= 1
+        if (smax > 64) smax = 64;
+        if (c->opt_stride > 0 && (uint32_t)c->opt_stride < smax) smax = (uint32_t)c->opt_stride;
+        if (c->collect) smax = 1;  // byte accounting is defined on the canonical candidates
+        while ((2u << slog) <= smax) ++slog;
+        while (slog > 0 && (((uint64_t)M << slog) > 0xfffffff0ull)) --slog;
+    }
+    const bool dense = slog == 0;
+    S.anchor_stride = 1u << slog;
     cudaStream_t st = c->st;
     uint64_t* ctr = c->d_ctr.as<uint64_t>();
     uint32_t launches = 0, lib = 0;
     const int nsm = c->n_sm;
 
+    // host-known sizes (no device round trip): anchors, scan positions
+    uint64_t n_anc = 0, npos = 0;
+    for (uint32_t e = 0; e < M; ++e) n_anc += c->len[e] >= l;
+    for (uint32_t e = c->e_lo; e < c->e_hi; ++e)
+        if (c->len[e] >= l) npos += c->len[e] - l + 1;
+    S.anchors = n_anc;
+    S.scan_positions = npos;
+
     CK(cudaEventRecord(c->ev[E_PACK0], st));
     CK(cudaMemsetAsync(ctr, 0, C_COUNT * sizeof(uint64_t), st));
     // ---- K0 + K1: pack the local entries ------------------------------------------------
     const uint32_t g_lo = c->gran0[c->e_lo], g_hi = c->gran0[c->e_hi];
+    k0_ent_table<<<(M + 255) / 256, 256, 0, st>>>(c->d_gran0.as<uint32_t>(), c->d_len.as<uint32_t>(), c->d_ent.as<uint2>(), M);
+    ++launches;
     if (c->e_hi > c->e_lo) {
         k0_gran_entry<<<nsm * 4, 256, 0, st>>>(c->d_gran0.as<uint32_t>(), c->d_gran_ent.as<uint32_t>(), c->e_lo, c->e_hi);
         ++launches;
         if (g_hi > g_lo) {
-            k1_pack<<<nsm * 8, 256, 0, st>>>(c->d_ascii.as<uint8_t>(), c->d_src.as<uint64_t>(), c->d_len.as<uint32_t>(),
-                                            c->d_flags.as<uint8_t>(), c->d_gran0.as<uint32_t>(),
-                                            c->d_gran_ent.as<uint32_t>(), c->d_packed.as<uint32_t>(),
-                                            4ull * g_lo, 4ull * g_hi, reinterpret_cast<uint32_t*>(ctr + C_ERR));
+            const uint64_t u0 = 4ull * g_lo, u1 = 4ull * g_hi;
+            const uint64_t tiles = (u1 - u0 + 30) / 31;
+            uint64_t blocks = (tiles + 7) / 8;
+            if (blocks > (uint64_t)nsm * 32) blocks = (uint64_t)nsm * 32;
+            k1_pack<<<(unsigned)blocks, 256, 0, st>>>(c->d_ascii.as<uint8_t>(), c->d_src.as<uint64_t>(), c->d_ent.as<uint2>(),
+                                                      c->d_flags.as<uint8_t>(), c->d_gran_ent.as<uint32_t>(),
+                                                      c->d_packed.as<uint32_t>(), M, u0, u1,
+                                                      reinterpret_cast<uint32_t*>(ctr + C_ERR));
             ++launches;
         }
     }
-    CK(cudaMemsetAsync(c->d_packed.as<uint4>() + G, 0, 16, st));  // terminator granule
+    CK(cudaMemsetAsync(c->d_packed.as<uint4>() + G, 0, 32, st));  // terminator granules
     CK(cudaGetLastError());
     // ---- multi-GPU: replicate the packed granules (needed by K2 keys and by K4) ---------
     if (c->nranks > 1) {
@@ -591,205 +623,193 @@ int ovl_overlaps_device(ovl_ctx* c, uint32_t min_length, uint64_t* n_rows_out) {
         }
         CKN(N.GroupEnd());
         CK(cudaEventRecord(c->ev_comm, c->st_comm));
+        CK(cudaStreamWaitEvent(st, c->ev_comm, 0));  // K2 reads every rank's granules
     }
     CK(cudaEventRecord(c->ev[E_ANCHOR0], st));
 
-    // ---- K2: anchors ----------------------------------------------------------------------
-    OVL_TRY(dev_ensure(c, c->d_anc_ent, (size_t)M * 4));
-    OVL_TRY(dev_ensure(c, c->d_anc_ent2, (size_t)M * 4));
-    OVL_TRY(dev_ensure(c, c->d_keys, (size_t)M * 8));
-    OVL_TRY(dev_ensure(c, c->d_keys2, (size_t)M * 8));
-    {
-        size_t tb = 0;
-        cub::CountingInputIterator<uint32_t> it(0);
-        LenGE pred{c->d_len.as<uint32_t>(), l};
-        CK(cub::DeviceSelect::If(nullptr, tb, it, c->d_anc_ent.as<uint32_t>(), ctr + C_NANC, (int)M, pred, st));
-        OVL_TRY(dev_ensure(c, c->d_tmp, tb));
-        tb = c->d_tmp.cap;
-        CK(cub::DeviceSelect::If(c->d_tmp.p, tb, it, c->d_anc_ent.as<uint32_t>(), ctr + C_NANC, (int)M, pred, st));
-        ++lib;
-    }
-    OVL_TRY(read_ctr(c));
-    if (c->h_ctr[C_ERR]) {
-        const uint32_t e = (uint32_t)c->h_ctr[C_ERR] - 1;
-        return fail(c, OVL_E_ALPHABET, "entry %u ('%.*s') holds a byte outside upper-case ACGT", e,
-                    (int)(c->id_off[e + 1] - c->id_off[e]), c->id_blob.data() + c->id_off[e]);
-    }
-    const uint32_t n_anc = (uint32_t)c->h_ctr[C_NANC];
-    S.anchors = n_anc;
-    uint64_t npos = 0;  // local A positions with |a|-p >= l (statistics)
-    for (uint32_t e = c->e_lo; e < c->e_hi; ++e)
-        if (c->len[e] >= l) npos += c->len[e] - l + 1;
-    S.scan_positions = npos;
-    auto finish_empty = [&]() -> int {
-        CK(cudaEventRecord(c->ev[E_SCAN0], st));
-        CK(cudaEventRecord(c->ev[E_VERIFY0], st));
-        CK(cudaEventRecord(c->ev[E_EMIT0], st));
-        CK(cudaEventRecord(c->ev[E_END], st));
-        if (c->nranks > 1) CK(cudaStreamWaitEvent(st, c->ev_comm, 0));
-        CK(cudaStreamSynchronize(st));
+    auto stage_times = [&]() {
         S.launches = launches;
         S.lib_launches = lib;
         S.ms_pack = ev_ms(c, E_PACK0, E_ANCHOR0);
         S.ms_anchor = ev_ms(c, E_ANCHOR0, E_SCAN0);
+        S.ms_scan = ev_ms(c, E_SCAN0, E_SORT0);
+        S.ms_sort = ev_ms(c, E_SORT0, E_VERIFY0);
+        S.ms_verify = ev_ms(c, E_VERIFY0, E_EMIT0);
+        S.ms_emit = ev_ms(c, E_EMIT0, E_END);
         S.ms_device = ev_ms(c, E_PACK0, E_END);
+    };
+    auto check_alphabet = [&]() -> int {
+        if (c->h_ctr[C_ERR]) {
+            const uint32_t e = (uint32_t)c->h_ctr[C_ERR] - 1;
+            return fail(c, OVL_E_ALPHABET, "entry %u ('%.*s') holds a byte outside upper-case ACGT", e,
+                        (int)(c->id_off[e + 1] - c->id_off[e]), c->id_blob.data() + c->id_off[e]);
+        }
         return OVL_OK;
     };
-    if (n_anc == 0 || g_hi == g_lo) return finish_empty();
+    // record the remaining stage events from `from` on, wait, fill the stage times
+    auto finish_from = [&](int from) -> int {
+        for (int e = from; e <= E_END; ++e) CK(cudaEventRecord(c->ev[e], st));
+        OVL_TRY(read_ctr(c));
+        OVL_TRY(check_alphabet());
+        stage_times();
+        return OVL_OK;
+    };
+    if (n_anc == 0 || g_hi == g_lo) return finish_from(E_SCAN0);
 
-    if (c->nranks > 1) CK(cudaStreamWaitEvent(st, c->ev_comm, 0));  // keys read remote granules
-    k2_keys<<<(n_anc + 255) / 256, 256, 0, st>>>(reinterpret_cast<const uint64_t*>(c->d_packed.p), c->d_gran0.as<uint32_t>(),
-                                                 c->d_anc_ent.as<uint32_t>(), c->d_keys.as<uint64_t>(), n_anc, kmer_mask(k));
-    ++launches;
-    {
-        size_t tb = 0;
-        CK(cub::DeviceRadixSort::SortPairs(nullptr, tb, c->d_keys.as<uint64_t>(), c->d_keys2.as<uint64_t>(),
-                                           c->d_anc_ent.as<uint32_t>(), c->d_anc_ent2.as<uint32_t>(), (int)n_anc, 0, 2 * k, st));
-        OVL_TRY(dev_ensure(c, c->d_tmp, tb));
-        tb = c->d_tmp.cap;
-        CK(cub::DeviceRadixSort::SortPairs(c->d_tmp.p, tb, c->d_keys.as<uint64_t>(), c->d_keys2.as<uint64_t>(),
-                                           c->d_anc_ent.as<uint32_t>(), c->d_anc_ent2.as<uint32_t>(), (int)n_anc, 0, 2 * k, st));
-        ++lib;
+    // ---- K2: anchor table ---------------------------------------------------------------------
+    const uint64_t n_keys = n_anc << slog;
+    const int tbits = ceil_log2(2 * n_keys) < 6 ? 6 : ceil_log2(2 * n_keys);
+    if (tbits > 31) return fail(c, OVL_E_LIMIT, "anchor table of 2^%d slots is over the layout limit", tbits);
+    const bool smem_filter = dense && n_anc <= (1u << 17);
+    int bm_bits;  // dense: log2 words of the blocked bloom filter; sparse: log2 bits of the bitmap
+    if (dense) {
+        bm_bits = smem_filter ? ceil_log2(n_anc) : ceil_log2(2 * n_anc);
+        if (bm_bits < 5) bm_bits = 5;
+        if (smem_filter && bm_bits > 15) bm_bits = 15;
+        if (bm_bits > 27) bm_bits = 27;
+    } else {
+        bm_bits = ceil_log2(32 * n_keys);
+        if (bm_bits < 15) bm_bits = 15;
+        if (bm_bits > 31) bm_bits = 31;
     }
-    const int tbits = ceil_log2(2ull * n_anc) < 4 ? 4 : ceil_log2(2ull * n_anc);
-    const bool smem_filter = n_anc <= (1u << 17);
-    int fw_bits = smem_filter ? ceil_log2(n_anc) : ceil_log2(2ull * n_anc);
-    if (fw_bits < 5) fw_bits = 5;
-    if (smem_filter && fw_bits > 15) fw_bits = 15;
-    if (fw_bits > 27) fw_bits = 27;
-    OVL_TRY(dev_ensure(c, c->d_table, sizeof(Slot) << tbits));
-    OVL_TRY(dev_ensure(c, c->d_filter, 4ull << fw_bits));
-    CK(cudaMemsetAsync(c->d_table.p, 0, sizeof(Slot) << tbits, st));
-    CK(cudaMemsetAsync(c->d_filter.p, 0, 4ull << fw_bits, st));
-    k2_build<<<(n_anc + 255) / 256, 256, 0, st>>>(c->d_keys2.as<uint64_t>(), n_anc, c->d_table.as<Slot>(), tbits,
-                                                  c->d_filter.as<uint32_t>(), fw_bits,
-                                                  reinterpret_cast<unsigned long long*>(ctr + C_NKEYS));
-    ++launches;
-    CK(cudaGetLastError());
+    const size_t filter_bytes = dense ? (4ull << bm_bits) : ((1ull << bm_bits) / 8);
+    const size_t table_bytes = sizeof(Slot) * ((1ull << tbits) + 1);
+    OVL_TRY(dev_ensure(c, c->d_table, table_bytes));
+    OVL_TRY(dev_ensure(c, c->d_filter, filter_bytes));
+    OVL_TRY(dev_ensure(c, c->d_next, ((uint64_t)M << slog) * 4));
+    CK(cudaMemsetAsync(c->d_table.p, 0xff, table_bytes, st));  // {EMPTY_KEY, NIL, ~0}
+    CK(cudaMemsetAsync(c->d_filter.p, 0, filter_bytes, st));
+    {
+        AnchorParams A;
+        A.packed64 = reinterpret_cast<const uint64_t*>(c->d_packed.p);
+        A.ent = c->d_ent.as<uint2>();
+        A.M = M;
+        A.l = l;
+        A.k = k;
+        A.stride_log2 = slog;
+        A.table = c->d_table.as<Slot>();
+        A.tbits = tbits;
+        A.next = c->d_next.as<uint32_t>();
+        A.bitmap = c->d_filter.as<uint32_t>();
+        A.bm_bits = bm_bits;
+        A.dense = dense ? 1 : 0;
+        A.n_anchors = reinterpret_cast<unsigned long long*>(ctr + C_NANC);
+        const uint64_t nthreads = (uint64_t)M << slog;
+        k2_insert<<<(unsigned)((nthreads + 255) / 256), 256, 0, st>>>(A);
+        ++launches;
+        CK(cudaGetLastError());
+    }
     CK(cudaEventRecord(c->ev[E_SCAN0], st));
 
     // ---- K3: scan (re-run once with the exact size if the candidate buffer was too small) --
     if (c->cand_cap == 0) {
         uint64_t cap = 96ull * (c->e_hi - c->e_lo);
         if (cap < (1ull << 20)) cap = 1ull << 20;
-        OVL_TRY(dev_ensure(c, c->d_cand, cap * sizeof(Cand), false));
-        c->cand_cap = c->d_cand.cap / sizeof(Cand);
+        OVL_TRY(dev_ensure(c, c->d_cand, cap * 8, false));
+        c->cand_cap = c->d_cand.cap / 8;
     }
     uint64_t n_cand = 0;
     for (int attempt = 0;; ++attempt) {
         ScanParams P;
         P.packed = c->d_packed.as<uint4>();
         P.gran_ent = c->d_gran_ent.as<uint32_t>();
-        P.gran0 = c->d_gran0.as<uint32_t>();
-        P.len = c->d_len.as<uint32_t>();
+        P.ent = c->d_ent.as<uint2>();
         P.g_begin = g_lo;
         P.g_end = g_hi;
         P.l = l;
         P.k = k;
+        P.stride_log2 = slog;
         P.filter = c->d_filter.as<uint32_t>();
-        P.fw_bits = fw_bits;
+        P.bm_bits = bm_bits;
         P.table = c->d_table.as<Slot>();
         P.tbits = tbits;
-        P.anc_ent = c->d_anc_ent2.as<uint32_t>();
-        P.cand = c->d_cand.as<Cand>();
-        P.n_cand = reinterpret_cast<unsigned long long*>(ctr + C_NCAND);
-        P.cap = c->cand_cap;
-        if (smem_filter)
-            k3_scan<true><<<nsm, 1024, 4u << fw_bits, st>>>(P);
-        else
-            k3_scan<false><<<nsm, 1024, 0, st>>>(P);
+        P.next = c->d_next.as<uint32_t>();
+        P.fmt = fmt;
+        P.sink.out = c->d_cand.as<uint64_t>();
+        P.sink.n_out = reinterpret_cast<unsigned long long*>(ctr + C_NCAND);
+        P.sink.cap = c->cand_cap;
+        if (!dense) {
+            const uint32_t tiles = (g_hi - g_lo + 31) / 32;
+            uint32_t blocks = (tiles + 7) / 8;
+            if (blocks > (uint32_t)nsm * 8) blocks = (uint32_t)nsm * 8;
+            k3_probe<<<blocks, 256, 0, st>>>(P);
+        } else if (smem_filter) {
+            k3_scan<true><<<nsm, 1024, 32 * WBUF * 8 + (4u << bm_bits), st>>>(P);
+        } else {
+            k3_scan<false><<<nsm, 1024, 32 * WBUF * 8, st>>>(P);
+        }
         ++launches;
         CK(cudaGetLastError());
         OVL_TRY(read_ctr(c));
+        OVL_TRY(check_alphabet());
         n_cand = c->h_ctr[C_NCAND];
         if (n_cand <= c->cand_cap) break;
         if (attempt >= 2) return fail(c, OVL_E_LIMIT, "candidate buffer overflow persists (%llu)", (unsigned long long)n_cand);
         ++S.retries;
-        OVL_TRY(dev_ensure(c, c->d_cand, (n_cand + n_cand / 16) * sizeof(Cand), false));
-        c->cand_cap = c->d_cand.cap / sizeof(Cand);
+        OVL_TRY(dev_ensure(c, c->d_cand, (n_cand + n_cand / 16) * 8, false));
+        c->cand_cap = c->d_cand.cap / 8;
         CK(cudaMemsetAsync(ctr + C_NCAND, 0, 8, st));
     }
     S.candidates = n_cand;
-    S.anchor_keys = c->h_ctr[C_NKEYS];
-    CK(cudaEventRecord(c->ev[E_VERIFY0], st));
-    if (n_cand == 0) {
-        CK(cudaEventRecord(c->ev[E_EMIT0], st));
-        CK(cudaEventRecord(c->ev[E_END], st));
-        if (c->nranks > 1) CK(cudaStreamWaitEvent(st, c->ev_comm, 0));
-        CK(cudaStreamSynchronize(st));
-        S.launches = launches;
-        S.lib_launches = lib;
-        S.ms_pack = ev_ms(c, E_PACK0, E_ANCHOR0);
-        S.ms_anchor = ev_ms(c, E_ANCHOR0, E_SCAN0);
-        S.ms_scan = ev_ms(c, E_SCAN0, E_VERIFY0);
-        S.ms_device = ev_ms(c, E_PACK0, E_END);
-        return OVL_OK;
+    if (n_cand == 0) return finish_from(E_SORT0);
+    if (n_cand > 0x7fffffffull) return fail(c, OVL_E_LIMIT, "more than 2^31 candidates on one GPU (%llu)", (unsigned long long)n_cand);
+
+    // ---- sort the candidate keys by (a, b, p) ------------------------------------------------
+    CK(cudaEventRecord(c->ev[E_SORT0], st));
+    OVL_TRY(dev_ensure(c, c->d_cand2, n_cand * 8));
+    {
+        size_t tb = 0;
+        CK(cub::DeviceRadixSort::SortKeys(nullptr, tb, c->d_cand.as<uint64_t>(), c->d_cand2.as<uint64_t>(), (int)n_cand, 2, fmt.total(), st));
+        OVL_TRY(dev_ensure(c, c->d_tmp, tb));
+        tb = c->d_tmp.cap;
+        CK(cub::DeviceRadixSort::SortKeys(c->d_tmp.p, tb, c->d_cand.as<uint64_t>(), c->d_cand2.as<uint64_t>(), (int)n_cand, 2, fmt.total(), st));
+        ++lib;
     }
+    uint64_t* keys = c->d_cand2.as<uint64_t>();
+    CK(cudaEventRecord(c->ev[E_VERIFY0], st));
 
     // ---- K4: verify -----------------------------------------------------------------------
-    OVL_TRY(dev_ensure(c, c->d_hits, n_cand * 8));
-    OVL_TRY(dev_ensure(c, c->d_hits2, n_cand * 8));
     {
         VerifyParams V;
-        V.cand = c->d_cand.as<Cand>();
-        V.n_cand = reinterpret_cast<unsigned long long*>(ctr + C_NCAND);
-        V.cap = c->cand_cap;
-        V.packed64 = reinterpret_cast<const uint64_t*>(c->d_packed.p);
-        V.gran0 = c->d_gran0.as<uint32_t>();
-        V.len = c->d_len.as<uint32_t>();
+        V.keys = keys;
+        V.n = n_cand;
+        V.packed = c->d_packed.as<uint4>();
+        V.ent = c->d_ent.as<uint2>();
         V.fmt = fmt;
-        V.hits = c->d_hits.as<uint64_t>();
         V.n_hits = reinterpret_cast<unsigned long long*>(ctr + C_NHITS);
-        V.counters = reinterpret_cast<unsigned long long*>(ctr + C_SELF);
+        V.counters = reinterpret_cast<unsigned long long*>(ctr + C_SUMM);
         V.collect = c->collect;
-        uint64_t blocks = (n_cand + 7) / 8;
+        uint64_t blocks = (n_cand + 255) / 256;
         if (blocks > (uint64_t)nsm * 8) blocks = (uint64_t)nsm * 8;
         k4_verify<<<(unsigned)blocks, 256, 0, st>>>(V);
         ++launches;
         CK(cudaGetLastError());
     }
-    OVL_TRY(read_ctr(c));
-    const uint64_t n_hits = c->h_ctr[C_NHITS];
-    S.hits = n_hits;
-    S.candidates = n_cand - c->h_ctr[C_SELF];  // canonical C of SURVEY 8(d): a != b
-    S.compared_bases = c->h_ctr[C_SUMM];
-    S.operand_bytes = c->h_ctr[C_SUMB];
     CK(cudaEventRecord(c->ev[E_EMIT0], st));
 
-    // ---- K5: sort hits, select longest, compact ----------------------------------------------
+    // ---- K5: select longest, compact ---------------------------------------------------------
     uint64_t n_rows = 0;
-    if (n_hits) {
-        if (n_hits > 0x7fffffffull) return fail(c, OVL_E_LIMIT, "more than 2^31 verified hits on one GPU (%llu)", (unsigned long long)n_hits);
-        size_t tb = 0;
-        CK(cub::DeviceRadixSort::SortKeys(nullptr, tb, c->d_hits.as<uint64_t>(), c->d_hits2.as<uint64_t>(), (int)n_hits, 0, fmt.total(), st));
-        OVL_TRY(dev_ensure(c, c->d_tmp, tb));
-        tb = c->d_tmp.cap;
-        CK(cub::DeviceRadixSort::SortKeys(c->d_tmp.p, tb, c->d_hits.as<uint64_t>(), c->d_hits2.as<uint64_t>(), (int)n_hits, 0, fmt.total(), st));
-        ++lib;
-        OVL_TRY(dev_ensure(c, c->d_cnt, n_hits * 4));
-        OVL_TRY(dev_ensure(c, c->d_offs, (n_hits + 1) * 8));
-        const unsigned nb = (unsigned)((n_hits + 255) / 256);
-        k5_count<<<nb, 256, 0, st>>>(c->d_hits2.as<uint64_t>(), n_hits, fmt, c->d_cnt.as<uint32_t>());
+    {
+        OVL_TRY(dev_ensure(c, c->d_cnt, n_cand * 4));
+        OVL_TRY(dev_ensure(c, c->d_offs, (n_cand + 1) * 8));
+        const unsigned nb = (unsigned)((n_cand + 255) / 256);
+        k5_count<<<nb, 256, 0, st>>>(keys, n_cand, fmt, c->d_cnt.as<uint32_t>());
         ++launches;
-        tb = 0;
-        CK(cub::DeviceScan::ExclusiveSum(nullptr, tb, c->d_cnt.as<uint32_t>(), c->d_offs.as<uint64_t>(), (int)n_hits, st));
+        size_t tb = 0;
+        CK(cub::DeviceScan::ExclusiveSum(nullptr, tb, c->d_cnt.as<uint32_t>(), c->d_offs.as<uint64_t>(), (int)n_cand, st));
         OVL_TRY(dev_ensure(c, c->d_tmp, tb));
         tb = c->d_tmp.cap;
-        CK(cub::DeviceScan::ExclusiveSum(c->d_tmp.p, tb, c->d_cnt.as<uint32_t>(), c->d_offs.as<uint64_t>(), (int)n_hits, st));
+        CK(cub::DeviceScan::ExclusiveSum(c->d_tmp.p, tb, c->d_cnt.as<uint32_t>(), c->d_offs.as<uint64_t>(), (int)n_cand, st));
         ++lib;
-        // total = offs[n-1] + cnt[n-1]
-        uint64_t last_off = 0;
-        uint32_t last_cnt = 0;
-        CK(cudaMemcpyAsync(&c->h_ctr[C_SELF], c->d_offs.as<uint64_t>() + (n_hits - 1), 8, cudaMemcpyDeviceToHost, st));
-        CK(cudaMemcpyAsync(&c->h_ctr[C_SUMM], c->d_cnt.as<uint32_t>() + (n_hits - 1), 4, cudaMemcpyDeviceToHost, st));
-        CK(cudaStreamSynchronize(st));
-        last_off = c->h_ctr[C_SELF];
-        last_cnt = (uint32_t)(c->h_ctr[C_SUMM] & 0xffffffffull);
-        n_rows = last_off + last_cnt;
+        // total = offs[n-1] + cnt[n-1]; the counter block rides along
+        CK(cudaMemcpyAsync(&c->h_ctr[C_COUNT], c->d_offs.as<uint64_t>() + (n_cand - 1), 8, cudaMemcpyDeviceToHost, st));
+        CK(cudaMemcpyAsync(&c->h_ctr[C_COUNT + 1], c->d_cnt.as<uint32_t>() + (n_cand - 1), 4, cudaMemcpyDeviceToHost, st));
+        OVL_TRY(read_ctr(c));
+        n_rows = c->h_ctr[C_COUNT] + (c->h_ctr[C_COUNT + 1] & 0xffffffffull);
         if (n_rows) {
             OVL_TRY(dev_ensure(c, c->d_rows, n_rows * sizeof(Row)));
-            k5_emit<<<nb, 256, 0, st>>>(c->d_hits2.as<uint64_t>(), n_hits, fmt, c->d_offs.as<uint64_t>(),
-                                        c->d_len.as<uint32_t>(), c->d_rows.as<Row>());
+            k5_emit<<<nb, 256, 0, st>>>(keys, n_cand, fmt, c->d_offs.as<uint64_t>(), c->d_cnt.as<uint32_t>(),
+                                        c->d_ent.as<uint2>(), c->d_rows.as<Row>());
             ++launches;
             CK(cudaGetLastError());
         }
@@ -798,14 +818,10 @@ int ovl_overlaps_device(ovl_ctx* c, uint32_t min_length, uint64_t* n_rows_out) {
     CK(cudaStreamSynchronize(st));
     c->n_rows = n_rows;
     S.rows = n_rows;
-    S.launches = launches;
-    S.lib_launches = lib;
-    S.ms_pack = ev_ms(c, E_PACK0, E_ANCHOR0);
-    S.ms_anchor = ev_ms(c, E_ANCHOR0, E_SCAN0);
-    S.ms_scan = ev_ms(c, E_SCAN0, E_VERIFY0);
-    S.ms_verify = ev_ms(c, E_VERIFY0, E_EMIT0);
-    S.ms_emit = ev_ms(c, E_EMIT0, E_END);
-    S.ms_device = ev_ms(c, E_PACK0, E_END);
+    S.hits = c->h_ctr[C_NHITS];
+    S.compared_bases = c->h_ctr[C_SUMM];
+    S.operand_bytes = c->h_ctr[C_SUMB];
+    stage_times();
     if (n_rows_out) *n_rows_out = n_rows;
     return OVL_OK;
 }
@@ -921,8 +937,8 @@ int ovl_comm_gather_rows_device(ovl_ctx* c, uint64_t* n_rows) {
     // counts
     OVL_TRY(dev_ensure(c, c->d_cnts, 8ull * R));
     uint64_t* d = c->d_cnts.as<uint64_t>();
-    c->h_ctr[C_SELF] = c->n_rows;
-    CK(cudaMemcpyAsync(d + c->rank, &c->h_ctr[C_SELF], 8, cudaMemcpyHostToDevice, c->st));
+    c->h_ctr[C_COUNT] = c->n_rows;
+    CK(cudaMemcpyAsync(d + c->rank, &c->h_ctr[C_COUNT], 8, cudaMemcpyHostToDevice, c->st));
     CKN(N.AllGather(d + c->rank, d, 1, ncclUint64, c->comm, c->st));
     std::vector<uint64_t> cnt(R);
     CK(cudaMemcpyAsync(cnt.data(), d, 8ull * R, cudaMemcpyDeviceToHost, c->st));

@@ -3,18 +3,24 @@
 // HBM layout (all arrays live for the duration of one ovl_overlaps* call, cached in the ctx):
 //
 //   ascii     u8     staged sequence bytes, every record 16-byte aligned, 16 B slack at both
-//                    ends (the reverse-complement reader touches up to 15 bytes before a
-//                    record and 4 after it)
+//                    ends
 //   packed    uint4  one 16-byte GRANULE = 64 bases, 2 bits/base, base j of a granule in bits
 //                    [2j, 2j+2) of the granule's 128-bit little-endian value; every entry
-//                    starts on a granule boundary and is zero padded to it; one extra zero
-//                    granule terminates the array.  code = (ascii >> 1) & 3  (A0 C1 T2 G3), so
+//                    starts on a granule boundary and is zero padded to it; TWO extra zero
+//                    granules terminate the array (the verifier reads one granule past an
+//                    entry's end).  code = (ascii >> 1) & 3  (A0 C1 T2 G3), so
 //                    complement = code ^ 2.
 //   gran_ent  u32    entry index of every granule
+//   ent       uint2  [M]   {first granule, length in bases} of every entry
 //   gran0     u32    [M+1] first granule of every entry (prefix sum of ceil(len/64))
 //   len       u32    [M]   entry lengths in bases
 //   src       u64    [M]   byte offset of the entry's source record in `ascii`
-//   flags     u8     [M]   bit0: entry is the reverse complement of its source record
+//   flags     u8     [M]   bit0: entry is the reverse complement of its source record (it then
+//                          directly follows the forward entry of the same record)
+//
+// Candidate / hit key (64 bit): [a | b | p | cont | sp], most significant first.  K3 emits keys
+// with both flag bits clear, a radix sort orders them by (a, b, p), K4 sets the flag bits of the
+// candidates that verify, K5 turns flagged keys into rows.
 //
 // Reference semantics restated by these kernels: /root/reference/src/overlapper.cpp:28-150
 // (see SURVEY.md 3.3 for the normative R1/R2 statement).
@@ -27,27 +33,37 @@ namespace ovl {
 constexpr int GRAN_BASES = 64;
 constexpr unsigned FULL = 0xffffffffu;
 
-// Candidate: suffix a[p:] against prefix of b.
-struct __align__(16) Cand {
-    uint32_t a, p, b, pad;
-};
-
-// Anchor hash-table slot: key = first k bases of the B entries [start, start+count) of the
-// key-sorted anchor list.  count == 0 marks an empty slot.
+// Anchor hash-table slot.  key == EMPTY_KEY marks a free slot; the k-mer whose packed value IS
+// EMPTY_KEY (32 x 'G') lives in the reserved slot behind the table.  head starts a linked list
+// (through `next`) of anchor ids  b * stride + delta.
 struct __align__(16) Slot {
-    uint64_t key;
-    uint32_t start, count;
+    unsigned long long key;
+    uint32_t head, pad;
 };
+constexpr unsigned long long EMPTY_KEY = ~0ull;
+constexpr uint32_t NIL = 0xffffffffu;
 
 struct Row {
     uint32_t a, b, astart, aend, bend;
 };
 
-// Bit layout of a 64-bit hit key: [a | b | p | cont | sp], most significant first.
+// Bit layout of a 64-bit candidate key: [a | b | p | cont | sp], most significant first.
 struct KeyFmt {
     int bits_e;  // bits of an entry index
     int bits_p;  // bits of a position
     __host__ __device__ int total() const { return 2 * bits_e + bits_p + 2; }
+    __host__ __device__ uint64_t make(uint32_t a, uint32_t b, uint32_t p) const {
+        return ((((uint64_t)a << bits_e) | b) << bits_p | p) << 2;
+    }
+    __host__ __device__ uint32_t p(uint64_t key) const {
+        return (uint32_t)((key >> 2) & ((1ull << bits_p) - 1ull));
+    }
+    __host__ __device__ uint32_t b(uint64_t key) const {
+        return (uint32_t)((key >> (2 + bits_p)) & ((1ull << bits_e) - 1ull));
+    }
+    __host__ __device__ uint32_t a(uint64_t key) const {
+        return (uint32_t)(key >> (2 + bits_p + bits_e));
+    }
 };
 constexpr uint64_t HIT_SP = 1;    // rem <= |b|: suffix-prefix (R1 candidate)
 constexpr uint64_t HIT_CONT = 2;  // rem >= |b|: b wholly inside a (R2 row)
@@ -56,16 +72,10 @@ __host__ __device__ __forceinline__ uint64_t kmer_mask(int k) {
     return k >= 32 ? ~0ull : ((1ull << (2 * k)) - 1ull);
 }
 
+// ---- dense path (stride 1): shared-memory blocked bloom filter ---------------------------
 // 32-bit hash of a packed k-mer: high half of a 64-bit multiplicative hash.
 __host__ __device__ __forceinline__ uint32_t kmer_hash(uint64_t x) {
     return (uint32_t)((x * 0x9E3779B97F4A7C15ull) >> 32);
-}
-// second-level mix for the table slot (slow path only)
-__host__ __device__ __forceinline__ uint32_t slot_hash(uint32_t h) {
-    h ^= h >> 15;
-    h *= 0x2C1B3C6Du;
-    h ^= h >> 12;
-    return h;
 }
 // Blocked bloom filter: one 32-bit word per key, two bits in it.
 __host__ __device__ __forceinline__ uint32_t filter_word(uint32_t h, int fw_bits) {
@@ -75,10 +85,66 @@ __host__ __device__ __forceinline__ uint32_t filter_bits(uint32_t h) {
     return (1u << (h & 31)) | (1u << ((h >> 5) & 31));
 }
 
+// ---- table hash (both paths) ----------------------------------------------------------------
+__host__ __device__ __forceinline__ uint64_t mix64(uint64_t x) {
+    x *= 0x9E3779B97F4A7C15ull;
+    x ^= x >> 32;
+    x *= 0xD6E8FEB86659FD93ull;
+    x ^= x >> 29;
+    return x;
+}
+__host__ __device__ __forceinline__ uint32_t slot_of(uint64_t h, int tbits) {
+    return (uint32_t)(h >> (64 - tbits));
+}
+// single-bit L2-resident bitmap (sparse path): bit index from the LOW hash bits
+__host__ __device__ __forceinline__ uint32_t bitmap_bit(uint64_t h, int bm_bits) {
+    return (uint32_t)h & ((1u << bm_bits) - 1u);
+}
+
 // k-mer starting at base j (0..31) of word w0, continuing into w1.
 __device__ __forceinline__ uint64_t kmer_at(uint64_t w0, uint64_t w1, int j) {
     const int s = 2 * j;
     return s ? ((w0 >> s) | (w1 << (64 - s))) : w0;
+}
+
+__device__ __forceinline__ uint4 ldg_stream(const uint4* p) {
+    uint4 r;
+    asm volatile("ld.global.nc.L1::no_allocate.v4.u32 {%0,%1,%2,%3}, [%4];"
+                 : "=r"(r.x), "=r"(r.y), "=r"(r.z), "=r"(r.w)
+                 : "l"(p));
+    return r;
+}
+
+// Per-warp candidate staging buffer in shared memory: keys are appended warp-synchronously and
+// flushed to the global candidate array with ONE global atomic per flush (instead of one per
+// probe round), in coalesced 256-byte stores.
+constexpr int WBUF = 256;  // keys per warp
+
+struct CandSink {
+    uint64_t* out;
+    unsigned long long* n_out;  // total candidates found (may exceed cap)
+    uint64_t cap;
+};
+
+__device__ __forceinline__ void wbuf_flush(uint64_t* buf, uint32_t& n, const CandSink& S, uint32_t lane) {
+    unsigned long long base = 0;
+    if (lane == 0) base = atomicAdd(S.n_out, (unsigned long long)n);
+    base = __shfl_sync(FULL, base, 0);
+    for (uint32_t i = lane; i < n; i += 32)
+        if (base + i < S.cap) S.out[base + i] = buf[i];
+    n = 0;
+    __syncwarp();
+}
+
+// Append `key` from every lane with have != 0.  All 32 lanes must call.
+__device__ __forceinline__ void wbuf_push(uint64_t* buf, uint32_t& n, const CandSink& S, uint32_t lane,
+                                          bool have, uint64_t key) {
+    const unsigned m = __ballot_sync(FULL, have);
+    if (!m) return;
+    if (n + 32 > WBUF) wbuf_flush(buf, n, S, lane);
+    if (have) buf[n + __popc(m & ((1u << lane) - 1u))] = key;
+    n += __popc(m);
+    __syncwarp();
 }
 
 }  // namespace ovl

@@ -196,6 +196,10 @@ class ExactOverlapper:
     def set_collect_stats(self, on: bool) -> None:
         self._check(self._lib.ovl_set_collect_stats(self._ctx, int(bool(on))))
 
+    def set_option(self, name: str, value: int) -> None:
+        """Tuning knob of the C ABI (``ovl_set_option``), e.g. ``anchor_stride``."""
+        self._check(self._lib.ovl_set_option(self._ctx, name.encode(), int(value)))
+
     def stats(self) -> dict:
         st = OvlStats()
         self._check(self._lib.ovl_get_stats(self._ctx, byref(st)))

@@ -111,6 +111,29 @@ def test_golden_mid(ov, key):
     assert np.array_equal(got, want)
 
 
+@pytest.mark.parametrize("stride", [1, 2, 8, 32, 64])
+def test_anchor_stride_does_not_change_rows(ov, stride):
+    """Every anchor stride (dense canonical scan .. every 64th position) gives the same rows."""
+    try:
+        ov.set_option("anchor_stride", stride)
+        for key in ("edge_s3_l200", "cfg4_x0.004", "cfg2_x0.015"):
+            want = sort_rows(helpers.load_mid()[key])
+            reads, l = helpers.mid_input(key)
+            got = run_reads_idx(ov, reads, l)
+            assert np.array_equal(got, want), (key, stride)
+            assert ov.stats()["anchor_stride"] == min(stride, 64)
+    finally:
+        ov.set_option("anchor_stride", 0)
+
+
+def test_auto_stride_follows_min_length(ov):
+    reads = helpers.mid_input("edge_s5_l20")[0]
+    for l, want in ((1, 1), (20, 1), (32, 1), (33, 2), (35, 4), (47, 16), (63, 32), (94, 32),
+                    (95, 64), (1000, 64)):
+        run_reads_idx(ov, reads, l)
+        assert ov.stats()["anchor_stride"] == want, l
+
+
 # ---- oracle on fresh inputs -----------------------------------------------------------------
 def test_bruteforce_random_tiny(ov):
     from oracle.bruteforce import both_strand_entries, overlaps_bruteforce
