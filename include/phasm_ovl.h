@@ -129,7 +129,8 @@ int ovl_fetch_rows(ovl_ctx *ctx, const ovl_row **rows, uint64_t *n_rows);
  * so this also forces the dense stride-1 scan. */
 int ovl_set_collect_stats(ovl_ctx *ctx, int on);
 /* Tuning knobs.  "anchor_stride": 0 = auto (largest power of two <= min(64, l-k+1)), else an
- * upper bound (1 forces the dense scan). */
+ * upper bound (1 forces the dense scan).  "serial_verify": 1 = chunk-by-chunk early-exit
+ * verifier instead of the head/tail two-pass form. */
 int ovl_set_option(ovl_ctx *ctx, const char *name, int64_t value);
 int ovl_get_stats(const ovl_ctx *ctx, ovl_stats *out);
 

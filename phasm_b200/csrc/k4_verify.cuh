@@ -6,15 +6,15 @@
 // overlapper.cpp:93-115); rem == |b| is both, which is where the reference's duplicate rows
 // come from.
 //
-// Input: candidate keys radix-sorted by (a, b, p).  A warp takes 32 consecutive keys: every
-// lane decodes one key and fetches the two entry records in parallel (one dependent-load chain
-// per 32 candidates instead of one per candidate), then the warp walks the 32 candidates; per
-// step a lane compares one 64-base granule: B comes as one aligned streaming 128-bit load,
-// A as two aligned 128-bit loads (granules i, i+1) funnel-shifted by (p mod 64) bases.
-// Because the keys are sorted by a, the 8 warps of a block work on the same few A entries and
-// the A operand is served by L1; B streams from L2/HBM.  The first step covers 2048 bases,
-// later steps 4096 (two independent load groups in flight).  Verified candidates get their
-// flag bits set in place.
+// Input: the candidate keys as the scan flushed them (per-warp runs of one A entry).  Output:
+// the keys of the candidates that verified, flag bits set, appended to the hit list.
+//
+// k4_verify_serial (the accounting form: exact m_c per candidate): a warp takes 32 consecutive
+// keys, every lane decodes one key and fetches the two entry records in parallel, then the warp
+// walks the 32 candidates; per step a lane compares one 64-base granule: B comes as one aligned
+// streaming 128-bit load, A as two aligned 128-bit loads (granules i, i+1) funnel-shifted by
+// (p mod 64) bases.  The first step covers 2048 bases, later steps 4096; the warp leaves a
+// candidate at the first step holding a mismatch.
 //
 // Roofline: HBM/L2.  Algorithmic bytes: 2*ceil(m_c/4) per candidate (both operands, m_c bases
 // up to and including the first mismatch), SURVEY.md 8(d).
@@ -24,12 +24,12 @@
 namespace ovl {
 
 struct VerifyParams {
-    uint64_t* keys;                    // sorted candidate keys, flags set in place
+    const uint64_t* keys;              // candidate keys (flags clear), any order
     uint64_t n;
     const uint4* packed;
     const uint2* ent;                  // {gran0, len}
     KeyFmt fmt;
-    unsigned long long* n_hits;
+    CandSink hits;                     // verified keys with their flag bits set
     unsigned long long* counters;      // [0] sum m_c, [1] sum 2*ceil(m_c/4)   (collect only)
     int collect;
 };
@@ -73,12 +73,15 @@ __device__ __forceinline__ uint32_t first_diff_base(const uint4 d) {  // d != 0
     return 48 + ((__ffs(d.w) - 1) >> 1);
 }
 
-__global__ void __launch_bounds__(256) k4_verify(const VerifyParams P) {
+__global__ void __launch_bounds__(256) k4_verify_serial(const VerifyParams P) {
+    __shared__ uint64_t s_buf[8][WBUF];
+    uint64_t* buf = s_buf[threadIdx.x >> 5];
+    uint32_t nbuf = 0;
     const uint32_t lane = threadIdx.x & 31;
     const uint64_t warp = ((uint64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
     const uint64_t nwarps = ((uint64_t)gridDim.x * blockDim.x) >> 5;
     const uint64_t n_tiles = (P.n + 31) / 32;
-    unsigned long long hit_cnt = 0, sum_m = 0, sum_b = 0;
+    unsigned long long sum_m = 0, sum_b = 0;
 
     for (uint64_t tile = warp; tile < n_tiles; tile += nwarps) {
         const uint64_t c = tile * 32 + lane;
@@ -139,20 +142,211 @@ __global__ void __launch_bounds__(256) k4_verify(const VerifyParams P) {
             }
             if (ok && lane == j) my_ok = 1;
         }
-        if (my_ok) {
-            P.keys[c] = key | my_fl;
-            ++hit_cnt;
-        }
+        wbuf_push(buf, nbuf, P.hits, lane, my_ok != 0, key | my_fl);
     }
-    // per-warp totals -> one atomic each
-    for (int d = 16; d; d >>= 1) hit_cnt += __shfl_down_sync(FULL, hit_cnt, d);
+    if (nbuf) wbuf_flush(buf, nbuf, P.hits, lane);
     if (lane == 0) {
-        if (hit_cnt) atomicAdd(P.n_hits, hit_cnt);
         if (P.collect && sum_m) {
             atomicAdd(P.counters + 0, sum_m);
             atomicAdd(P.counters + 1, sum_b);
         }
     }
+}
+
+// ---------------------------------------------------------------------------------------------
+// Two-pass throughput form (the default).  The serial kernel above walks a candidate chunk by
+// chunk and leaves at the first mismatch: one dependent HBM round trip per chunk per warp, which
+// is latency bound (ncu r01b: 55 % of the stall samples wait on the B load).  Error-free reads
+// make the outcome predictable instead: a false candidate (another haplotype, a repeat copy)
+// almost always differs within its first 2048 bases, and a candidate that survives them is
+// almost always a true overlap that must be compared to its end anyway.  So:
+//
+//   k4a_head  every candidate's first FIRST_GRAN granules (2048 bases), 4 candidates per warp
+//             step with all loads of a lane issued before the first compare.  Candidates that
+//             end inside the head are appended to the hit list; the others that match so far go
+//             to the survivor list.
+//   k4b_tail  one warp per survivor compares the remaining granules, 4 granules per lane in
+//             flight, no exit test inside the loop, one vote at the end.
+//
+// Both read A as three 64-bit words per granule (8-byte aligned at p/32) so that the re-alignment
+// is one 32-bit word select + four funnel shifts; the tail kernel hoists the select out of its
+// loop (two loop bodies, warp-uniform branch).  Candidates need not be sorted: the scan flushes
+// them in per-warp runs of one A entry, which is what keeps the A operand in L1.
+// Bytes touched beyond the first mismatch are the price: <= 2048 bases per false candidate.
+constexpr uint32_t FIRST_GRAN = 32;
+constexpr int HEAD_UNROLL = 4;
+
+struct Verify2Params {
+    const uint64_t* keys;              // candidate keys (flags clear), any order
+    uint64_t n;
+    const uint64_t* packed64;
+    const uint2* ent;                  // {gran0, len}
+    KeyFmt fmt;
+    uint32_t* surv;                    // k4a -> k4b: indices of candidates alive after the head
+    unsigned long long* n_surv;
+    CandSink hits;                     // verified keys with their flag bits set
+};
+
+struct CandMeta {
+    uint32_t wa_lo, wa_hi;  // 64-bit word index of a[p]
+    uint32_t gb;            // first granule of b
+    uint32_t n, sh, fl;     // bases to compare, bit shift (0..62, even), HIT_* flags
+};
+
+__device__ __forceinline__ CandMeta cand_meta(const Verify2Params& P, uint64_t key) {
+    CandMeta m;
+    const uint32_t a = P.fmt.a(key), b = P.fmt.b(key), p = P.fmt.p(key);
+    const uint2 ma = __ldg(P.ent + a), mb = __ldg(P.ent + b);
+    const uint32_t rem = ma.y - p;
+    m.n = rem < mb.y ? rem : mb.y;
+    m.fl = (rem <= mb.y ? (uint32_t)HIT_SP : 0u) | (rem >= mb.y ? (uint32_t)HIT_CONT : 0u);
+    const uint64_t wa = 2ull * ma.x + (p >> 5);
+    m.wa_lo = (uint32_t)wa;
+    m.wa_hi = (uint32_t)(wa >> 32);
+    m.gb = mb.x;
+    m.sh = 2u * (p & 31u);
+    return m;
+}
+
+// granule = bits [sh, sh+128) of the 192-bit value (w2:w1:w0); HI32 = (sh >= 32), t = sh & 31
+template <bool HI32>
+__device__ __forceinline__ uint4 shr192(uint64_t w0, uint64_t w1, uint64_t w2, uint32_t t) {
+    const uint32_t x0 = (uint32_t)w0, x1 = (uint32_t)(w0 >> 32), x2 = (uint32_t)w1, x3 = (uint32_t)(w1 >> 32),
+                   x4 = (uint32_t)w2, x5 = (uint32_t)(w2 >> 32);
+    if (HI32)
+        return make_uint4(__funnelshift_r(x1, x2, t), __funnelshift_r(x2, x3, t), __funnelshift_r(x3, x4, t),
+                          __funnelshift_r(x4, x5, t));
+    return make_uint4(__funnelshift_r(x0, x1, t), __funnelshift_r(x1, x2, t), __funnelshift_r(x2, x3, t),
+                      __funnelshift_r(x3, x4, t));
+}
+
+__global__ void __launch_bounds__(256) k4a_head(const Verify2Params P) {
+    __shared__ uint64_t s_buf[8][WBUF];
+    const uint32_t lane = threadIdx.x & 31;
+    const uint64_t warp = ((uint64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+    const uint64_t nwarps = ((uint64_t)gridDim.x * blockDim.x) >> 5;
+    const uint64_t n_tiles = (P.n + 31) / 32;
+    uint64_t* buf = s_buf[threadIdx.x >> 5];
+    uint32_t nbuf = 0;
+    const uint4* packed128 = reinterpret_cast<const uint4*>(P.packed64);
+
+    for (uint64_t tile = warp; tile < n_tiles; tile += nwarps) {
+        const uint64_t c = tile * 32 + lane;
+        uint64_t key = 0;
+        CandMeta my = {0, 0, 0, 0, 0, 0};  // n == 0 marks "no candidate" (a real one has n >= l >= 1)
+        if (c < P.n) {
+            key = P.keys[c];
+            my = cand_meta(P, key);
+        }
+        uint32_t ok_mask = 0;  // bit j: candidate j matched over its head
+        for (uint32_t j0 = 0; j0 < 32; j0 += HEAD_UNROLL) {
+            if (__shfl_sync(FULL, my.n, j0) == 0) break;  // tile tail (warp-uniform)
+            uint4 bv[HEAD_UNROLL];
+            uint64_t w0[HEAD_UNROLL], w1[HEAD_UNROLL], w2[HEAD_UNROLL];
+            uint32_t sh[HEAD_UNROLL], nn[HEAD_UNROLL];
+#pragma unroll
+            for (int u = 0; u < HEAD_UNROLL; ++u) {
+                const uint32_t lo = __shfl_sync(FULL, my.wa_lo, j0 + u);
+                const uint32_t hi = __shfl_sync(FULL, my.wa_hi, j0 + u);
+                const uint32_t gb = __shfl_sync(FULL, my.gb, j0 + u);
+                sh[u] = __shfl_sync(FULL, my.sh, j0 + u);
+                nn[u] = __shfl_sync(FULL, my.n, j0 + u);
+                bv[u] = make_uint4(0, 0, 0, 0);
+                w0[u] = w1[u] = w2[u] = 0;
+                if (64u * lane < nn[u]) {
+                    const uint64_t* pa = P.packed64 + (((uint64_t)hi << 32) | lo) + 2u * lane;
+                    bv[u] = ldg_stream(packed128 + gb + lane);
+                    w0[u] = __ldg(pa);
+                    w1[u] = __ldg(pa + 1);
+                    w2[u] = __ldg(pa + 2);
+                }
+            }
+#pragma unroll
+            for (int u = 0; u < HEAD_UNROLL; ++u) {
+                const uint32_t t = sh[u] & 31u;
+                const uint4 x = (sh[u] & 32u) ? shr192<true>(w0[u], w1[u], w2[u], t)
+                                              : shr192<false>(w0[u], w1[u], w2[u], t);
+                uint4 d = make_uint4(x.x ^ bv[u].x, x.y ^ bv[u].y, x.z ^ bv[u].z, x.w ^ bv[u].w);
+                const int nb = (int)nn[u] - 64 * (int)lane;
+                if (nb < 64) {
+                    const uint4 m = low_bases_mask128(nb);  // all zero for nb <= 0
+                    d.x &= m.x; d.y &= m.y; d.z &= m.z; d.w &= m.w;
+                }
+                const unsigned bad = __ballot_sync(FULL, (d.x | d.y | d.z | d.w) != 0);
+                if (!bad && nn[u]) ok_mask |= 1u << (j0 + u);
+            }
+        }
+        const bool ok = (ok_mask >> lane) & 1u;
+        const bool done = ok && my.n <= 64u * FIRST_GRAN;
+        const bool alive = ok && !done;
+        wbuf_push(buf, nbuf, P.hits, lane, done, key | my.fl);
+        const unsigned am = __ballot_sync(FULL, alive);
+        if (am) {
+            unsigned long long base = 0;
+            if (lane == 0) base = atomicAdd(P.n_surv, (unsigned long long)__popc(am));
+            base = __shfl_sync(FULL, base, 0);
+            if (alive) P.surv[base + __popc(am & ((1u << lane) - 1u))] = (uint32_t)c;
+        }
+    }
+    if (nbuf) wbuf_flush(buf, nbuf, P.hits, lane);
+}
+
+// OR of the differences of granules [FIRST_GRAN, ng) for one lane (stride 32, 4 in flight)
+template <bool HI32>
+__device__ __forceinline__ uint4 tail_diff(const uint64_t* __restrict__ pa, const uint4* __restrict__ pb,
+                                           uint32_t n, uint32_t t, uint32_t lane) {
+    const uint32_t ng = (n + 63) >> 6;
+    uint4 acc = make_uint4(0, 0, 0, 0);
+    for (uint32_t i = FIRST_GRAN + lane; i < ng; i += 128) {
+        uint4 bv[4];
+        uint64_t w0[4], w1[4], w2[4];
+#pragma unroll
+        for (int u = 0; u < 4; ++u) {
+            const uint32_t g = i + 32u * u;
+            bv[u] = make_uint4(0, 0, 0, 0);
+            w0[u] = w1[u] = w2[u] = 0;
+            if (g < ng) {
+                bv[u] = ldg_stream(pb + g);
+                w0[u] = __ldg(pa + 2u * g);
+                w1[u] = __ldg(pa + 2u * g + 1);
+                w2[u] = __ldg(pa + 2u * g + 2);
+            }
+        }
+#pragma unroll
+        for (int u = 0; u < 4; ++u) {
+            const uint4 x = shr192<HI32>(w0[u], w1[u], w2[u], t);
+            uint4 d = make_uint4(x.x ^ bv[u].x, x.y ^ bv[u].y, x.z ^ bv[u].z, x.w ^ bv[u].w);
+            const int nb = (int)n - 64 * (int)(i + 32u * u);
+            if (nb < 64) {  // the last granule of the comparison, or past it
+                const uint4 m = low_bases_mask128(nb);
+                d.x &= m.x; d.y &= m.y; d.z &= m.z; d.w &= m.w;
+            }
+            acc.x |= d.x; acc.y |= d.y; acc.z |= d.z; acc.w |= d.w;
+        }
+    }
+    return acc;
+}
+
+__global__ void __launch_bounds__(256) k4b_tail(const Verify2Params P) {
+    __shared__ uint64_t s_buf[8][WBUF];
+    const uint32_t lane = threadIdx.x & 31;
+    const uint64_t warp = ((uint64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+    const uint64_t nwarps = ((uint64_t)gridDim.x * blockDim.x) >> 5;
+    const uint64_t ns = *P.n_surv;
+    uint64_t* buf = s_buf[threadIdx.x >> 5];
+    uint32_t nbuf = 0;
+    const uint4* packed128 = reinterpret_cast<const uint4*>(P.packed64);
+    for (uint64_t s = warp; s < ns; s += nwarps) {
+        const uint64_t key = P.keys[P.surv[s]];
+        const CandMeta m = cand_meta(P, key);
+        const uint64_t* pa = P.packed64 + (((uint64_t)m.wa_hi << 32) | m.wa_lo);
+        const uint4* pb = packed128 + m.gb;
+        const uint32_t t = m.sh & 31u;
+        const uint4 acc = (m.sh & 32u) ? tail_diff<true>(pa, pb, m.n, t, lane) : tail_diff<false>(pa, pb, m.n, t, lane);
+        const unsigned bad = __ballot_sync(FULL, (acc.x | acc.y | acc.z | acc.w) != 0);
+        wbuf_push(buf, nbuf, P.hits, lane, !bad && lane == 0, key | m.fl);
+    }
+    if (nbuf) wbuf_flush(buf, nbuf, P.hits, lane);
 }
 
 }  // namespace ovl

@@ -5,19 +5,16 @@
 //       suffix of A that is a prefix of B) is emitted per ordered pair (A,B);
 //   R2  /root/reference/src/overlapper.cpp:93-115  every occurrence of the whole B inside A.
 //
-// Input: the candidate keys [a | b | p | cont | sp], radix-sorted ascending BEFORE verification
-// (flag bits were zero then), with the flag bits of verified candidates set by K4.  Candidates
-// of one (a,b) pair are adjacent and ordered by p; failed candidates (flags 00) sit between
-// the hits.  rem = |a|-p falls as p grows, so the first key of a pair carrying SP is the
-// smallest p, i.e. the longest suffix-prefix overlap: a key with SP emits its R1 row iff no
-// EARLIER key of the same pair carries SP (look-back over the pair's keys, usually 0-2).  A
-// key with both flags yields the same row twice -- that is the reference's duplicate row
-// (SURVEY.md 3.3).
+// Input: the keys [a | b | p | cont | sp] of the verified candidates, radix-sorted ascending, so
+// hits of one (a,b) pair are adjacent and ordered by p.  rem = |a|-p falls as p grows, hence
+// inside a pair the flags go  CONT-only ... (CONT|SP at rem == |b|) ... SP-only: the first hit
+// carrying SP is the smallest p, i.e. the longest suffix-prefix overlap.  A hit with both flags
+// yields the same row twice -- that is the reference's duplicate row.
 //
 // Because rows of one key share astart = p and keys are sorted by (a,b,p), the emitted rows are
 // already in (a,b,astart,aend,bend) order: the output is deterministic and canonical.
 //
-// Roofline: HBM, 8 B read per candidate (x2: count pass + emit pass) + 20 B written per row.
+// Roofline: HBM, 8 B read per hit (x2: count pass + emit pass) + 20 B written per row.
 #pragma once
 #include "ovl_common.cuh"
 
@@ -28,13 +25,9 @@ __device__ __forceinline__ uint32_t key_rows(const uint64_t* __restrict__ keys, 
     uint32_t c = (key & HIT_CONT) ? 1u : 0u;
     if (key & HIT_SP) {
         bool first = true;
-        for (uint64_t j = i; j > 0;) {
-            const uint64_t prev = keys[--j];
-            if ((prev >> pair_shift) != (key >> pair_shift)) break;
-            if (prev & HIT_SP) {
-                first = false;
-                break;
-            }
+        if (i) {
+            const uint64_t prev = keys[i - 1];
+            first = ((prev >> pair_shift) != (key >> pair_shift)) || !(prev & HIT_SP);
         }
         c += first;
     }
@@ -46,7 +39,7 @@ k5_count(const uint64_t* __restrict__ keys, uint64_t n, KeyFmt fmt, uint32_t* __
     const uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
     if (i < n) {
         const uint64_t key = keys[i];
-        cnt[i] = (key & 3) ? key_rows(keys, i, key, fmt.bits_p + 2) : 0u;
+        cnt[i] = key_rows(keys, i, key, fmt.bits_p + 2);
     }
 }
 

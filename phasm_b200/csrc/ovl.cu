@@ -54,10 +54,10 @@ struct PinBuf {
     size_t cap = 0;
 };
 
-enum Ev { E_H2D0, E_PACK0, E_ANCHOR0, E_SCAN0, E_SORT0, E_VERIFY0, E_EMIT0, E_END, E_D2H0, E_D2H1, E_COUNT };
+enum Ev { E_H2D0, E_PACK0, E_ANCHOR0, E_SCAN0, E_VERIFY0, E_SORT0, E_EMIT0, E_END, E_D2H0, E_D2H1, E_COUNT };
 
 // device counter block (one 64-bit word each)
-enum Ctr { C_ERR, C_NANC, C_NCAND, C_NHITS, C_SUMM, C_SUMB, C_COUNT };  // h_ctr has 2 spare words behind
+enum Ctr { C_ERR, C_NANC, C_NCAND, C_NHITS, C_SUMM, C_SUMB, C_NSURV, C_COUNT };  // h_ctr has 2 spare words behind
 
 }  // namespace
 
@@ -95,6 +95,7 @@ struct ovl_ctx {
     bool gathered = false;  // ovl_comm_gather_rows_device already ran for the current rows
     int collect = 0;
     int opt_stride = 0;  // 0 = auto; else upper bound on the anchor stride (1 = dense scan)
+    int opt_serial_verify = 0;  // 1: chunk-by-chunk early-exit verifier instead of head/tail
     ovl_stats stats{};
 
     // ---- multi-GPU ----
@@ -447,6 +448,10 @@ int ovl_set_option(ovl_ctx* c, const char* name, int64_t value) {
         c->opt_stride = (int)value;
         return OVL_OK;
     }
+    if (!strcmp(name, "serial_verify")) {
+        c->opt_serial_verify = value != 0;
+        return OVL_OK;
+    }
     return fail(c, OVL_E_ARG, "unknown option '%s'", name);
 }
 
@@ -632,9 +637,9 @@ int ovl_overlaps_device(ovl_ctx* c, uint32_t min_length, uint64_t* n_rows_out) {
         S.lib_launches = lib;
         S.ms_pack = ev_ms(c, E_PACK0, E_ANCHOR0);
         S.ms_anchor = ev_ms(c, E_ANCHOR0, E_SCAN0);
-        S.ms_scan = ev_ms(c, E_SCAN0, E_SORT0);
-        S.ms_sort = ev_ms(c, E_SORT0, E_VERIFY0);
-        S.ms_verify = ev_ms(c, E_VERIFY0, E_EMIT0);
+        S.ms_scan = ev_ms(c, E_SCAN0, E_VERIFY0);
+        S.ms_verify = ev_ms(c, E_VERIFY0, E_SORT0);
+        S.ms_sort = ev_ms(c, E_SORT0, E_EMIT0);
         S.ms_emit = ev_ms(c, E_EMIT0, E_END);
         S.ms_device = ev_ms(c, E_PACK0, E_END);
     };
@@ -751,64 +756,89 @@ int ovl_overlaps_device(ovl_ctx* c, uint32_t min_length, uint64_t* n_rows_out) {
         CK(cudaMemsetAsync(ctr + C_NCAND, 0, 8, st));
     }
     S.candidates = n_cand;
-    if (n_cand == 0) return finish_from(E_SORT0);
+    if (n_cand == 0) return finish_from(E_VERIFY0);
     if (n_cand > 0x7fffffffull) return fail(c, OVL_E_LIMIT, "more than 2^31 candidates on one GPU (%llu)", (unsigned long long)n_cand);
 
-    // ---- sort the candidate keys by (a, b, p) ------------------------------------------------
-    CK(cudaEventRecord(c->ev[E_SORT0], st));
-    OVL_TRY(dev_ensure(c, c->d_cand2, n_cand * 8));
-    {
-        size_t tb = 0;
-        CK(cub::DeviceRadixSort::SortKeys(nullptr, tb, c->d_cand.as<uint64_t>(), c->d_cand2.as<uint64_t>(), (int)n_cand, 2, fmt.total(), st));
-        OVL_TRY(dev_ensure(c, c->d_tmp, tb));
-        tb = c->d_tmp.cap;
-        CK(cub::DeviceRadixSort::SortKeys(c->d_tmp.p, tb, c->d_cand.as<uint64_t>(), c->d_cand2.as<uint64_t>(), (int)n_cand, 2, fmt.total(), st));
-        ++lib;
-    }
-    uint64_t* keys = c->d_cand2.as<uint64_t>();
-    CK(cudaEventRecord(c->ev[E_VERIFY0], st));
-
     // ---- K4: verify -----------------------------------------------------------------------
+    CK(cudaEventRecord(c->ev[E_VERIFY0], st));
+    OVL_TRY(dev_ensure(c, c->d_cand2, n_cand * 8));  // hit keys
+    OVL_TRY(dev_ensure(c, c->d_cnt, n_cand * 4));    // survivor list now, row counts in K5
     {
-        VerifyParams V;
-        V.keys = keys;
-        V.n = n_cand;
-        V.packed = c->d_packed.as<uint4>();
-        V.ent = c->d_ent.as<uint2>();
-        V.fmt = fmt;
-        V.n_hits = reinterpret_cast<unsigned long long*>(ctr + C_NHITS);
-        V.counters = reinterpret_cast<unsigned long long*>(ctr + C_SUMM);
-        V.collect = c->collect;
+        CandSink hits;
+        hits.out = c->d_cand2.as<uint64_t>();
+        hits.n_out = reinterpret_cast<unsigned long long*>(ctr + C_NHITS);
+        hits.cap = n_cand;
         uint64_t blocks = (n_cand + 255) / 256;
         if (blocks > (uint64_t)nsm * 8) blocks = (uint64_t)nsm * 8;
-        k4_verify<<<(unsigned)blocks, 256, 0, st>>>(V);
-        ++launches;
+        if (c->collect || c->opt_serial_verify) {
+            VerifyParams V;
+            V.keys = c->d_cand.as<uint64_t>();
+            V.n = n_cand;
+            V.packed = c->d_packed.as<uint4>();
+            V.ent = c->d_ent.as<uint2>();
+            V.fmt = fmt;
+            V.hits = hits;
+            V.counters = reinterpret_cast<unsigned long long*>(ctr + C_SUMM);
+            V.collect = c->collect;
+            k4_verify_serial<<<(unsigned)blocks, 256, 0, st>>>(V);
+            ++launches;
+        } else {
+            Verify2Params V;
+            V.keys = c->d_cand.as<uint64_t>();
+            V.n = n_cand;
+            V.packed64 = reinterpret_cast<const uint64_t*>(c->d_packed.p);
+            V.ent = c->d_ent.as<uint2>();
+            V.fmt = fmt;
+            V.surv = c->d_cnt.as<uint32_t>();
+            V.n_surv = reinterpret_cast<unsigned long long*>(ctr + C_NSURV);
+            V.hits = hits;
+            k4a_head<<<(unsigned)blocks, 256, 0, st>>>(V);
+            k4b_tail<<<nsm * 8, 256, 0, st>>>(V);
+            launches += 2;
+        }
         CK(cudaGetLastError());
+    }
+    OVL_TRY(read_ctr(c));
+    const uint64_t n_hits = c->h_ctr[C_NHITS];
+    S.hits = n_hits;
+    S.compared_bases = c->h_ctr[C_SUMM];
+    S.operand_bytes = c->h_ctr[C_SUMB];
+    if (n_hits == 0) return finish_from(E_SORT0);
+
+    // ---- sort the hit keys by (a, b, p) --------------------------------------------------------
+    CK(cudaEventRecord(c->ev[E_SORT0], st));
+    uint64_t* keys = c->d_cand.as<uint64_t>();  // the candidate buffer is free again
+    {
+        size_t tb = 0;
+        CK(cub::DeviceRadixSort::SortKeys(nullptr, tb, c->d_cand2.as<uint64_t>(), keys, (int)n_hits, 0, fmt.total(), st));
+        OVL_TRY(dev_ensure(c, c->d_tmp, tb));
+        tb = c->d_tmp.cap;
+        CK(cub::DeviceRadixSort::SortKeys(c->d_tmp.p, tb, c->d_cand2.as<uint64_t>(), keys, (int)n_hits, 0, fmt.total(), st));
+        ++lib;
     }
     CK(cudaEventRecord(c->ev[E_EMIT0], st));
 
     // ---- K5: select longest, compact ---------------------------------------------------------
     uint64_t n_rows = 0;
     {
-        OVL_TRY(dev_ensure(c, c->d_cnt, n_cand * 4));
-        OVL_TRY(dev_ensure(c, c->d_offs, (n_cand + 1) * 8));
-        const unsigned nb = (unsigned)((n_cand + 255) / 256);
-        k5_count<<<nb, 256, 0, st>>>(keys, n_cand, fmt, c->d_cnt.as<uint32_t>());
+        OVL_TRY(dev_ensure(c, c->d_offs, (n_hits + 1) * 8));
+        const unsigned nb = (unsigned)((n_hits + 255) / 256);
+        k5_count<<<nb, 256, 0, st>>>(keys, n_hits, fmt, c->d_cnt.as<uint32_t>());
         ++launches;
         size_t tb = 0;
-        CK(cub::DeviceScan::ExclusiveSum(nullptr, tb, c->d_cnt.as<uint32_t>(), c->d_offs.as<uint64_t>(), (int)n_cand, st));
+        CK(cub::DeviceScan::ExclusiveSum(nullptr, tb, c->d_cnt.as<uint32_t>(), c->d_offs.as<uint64_t>(), (int)n_hits, st));
         OVL_TRY(dev_ensure(c, c->d_tmp, tb));
         tb = c->d_tmp.cap;
-        CK(cub::DeviceScan::ExclusiveSum(c->d_tmp.p, tb, c->d_cnt.as<uint32_t>(), c->d_offs.as<uint64_t>(), (int)n_cand, st));
+        CK(cub::DeviceScan::ExclusiveSum(c->d_tmp.p, tb, c->d_cnt.as<uint32_t>(), c->d_offs.as<uint64_t>(), (int)n_hits, st));
         ++lib;
-        // total = offs[n-1] + cnt[n-1]; the counter block rides along
-        CK(cudaMemcpyAsync(&c->h_ctr[C_COUNT], c->d_offs.as<uint64_t>() + (n_cand - 1), 8, cudaMemcpyDeviceToHost, st));
-        CK(cudaMemcpyAsync(&c->h_ctr[C_COUNT + 1], c->d_cnt.as<uint32_t>() + (n_cand - 1), 4, cudaMemcpyDeviceToHost, st));
-        OVL_TRY(read_ctr(c));
+        // total = offs[n-1] + cnt[n-1]
+        CK(cudaMemcpyAsync(&c->h_ctr[C_COUNT], c->d_offs.as<uint64_t>() + (n_hits - 1), 8, cudaMemcpyDeviceToHost, st));
+        CK(cudaMemcpyAsync(&c->h_ctr[C_COUNT + 1], c->d_cnt.as<uint32_t>() + (n_hits - 1), 4, cudaMemcpyDeviceToHost, st));
+        CK(cudaStreamSynchronize(st));
         n_rows = c->h_ctr[C_COUNT] + (c->h_ctr[C_COUNT + 1] & 0xffffffffull);
         if (n_rows) {
             OVL_TRY(dev_ensure(c, c->d_rows, n_rows * sizeof(Row)));
-            k5_emit<<<nb, 256, 0, st>>>(keys, n_cand, fmt, c->d_offs.as<uint64_t>(), c->d_cnt.as<uint32_t>(),
+            k5_emit<<<nb, 256, 0, st>>>(keys, n_hits, fmt, c->d_offs.as<uint64_t>(), c->d_cnt.as<uint32_t>(),
                                         c->d_ent.as<uint2>(), c->d_rows.as<Row>());
             ++launches;
             CK(cudaGetLastError());
@@ -818,9 +848,6 @@ int ovl_overlaps_device(ovl_ctx* c, uint32_t min_length, uint64_t* n_rows_out) {
     CK(cudaStreamSynchronize(st));
     c->n_rows = n_rows;
     S.rows = n_rows;
-    S.hits = c->h_ctr[C_NHITS];
-    S.compared_bases = c->h_ctr[C_SUMM];
-    S.operand_bytes = c->h_ctr[C_SUMB];
     stage_times();
     if (n_rows_out) *n_rows_out = n_rows;
     return OVL_OK;

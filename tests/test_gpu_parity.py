@@ -126,6 +126,17 @@ def test_anchor_stride_does_not_change_rows(ov, stride):
         ov.set_option("anchor_stride", 0)
 
 
+def test_serial_verifier_gives_the_same_rows(ov):
+    try:
+        ov.set_option("serial_verify", 1)
+        for key in ("edge_s4_l33", "cfg3_x0.002", "cfg5_x0.001"):
+            want = sort_rows(helpers.load_mid()[key])
+            reads, l = helpers.mid_input(key)
+            assert np.array_equal(run_reads_idx(ov, reads, l), want), key
+    finally:
+        ov.set_option("serial_verify", 0)
+
+
 def test_auto_stride_follows_min_length(ov):
     reads = helpers.mid_input("edge_s5_l20")[0]
     for l, want in ((1, 1), (20, 1), (32, 1), (33, 2), (35, 4), (47, 16), (63, 32), (94, 32),
