@@ -140,6 +140,20 @@ int ovl_get_stats(const ovl_ctx *ctx, ovl_stats *out);
 int ovl_timer_start(ovl_ctx *ctx);
 int ovl_timer_stop(ovl_ctx *ctx, float *ms);
 
+/* ---- text I/O on the host -------------------------------------
+ * ovl_add_fasta replaces the dinopy FastaReader loop of phasm/cli/assembler.py:32-40: every
+ * record of the FASTA file becomes one read (both_strands != 0: entries name+"+" and name+"-",
+ * reverse complement made on the device) or one entry.  Record name = header line after '>',
+ * right-stripped; multi-line records and blank lines are accepted (tests/data/test.fasta). */
+int ovl_add_fasta(ovl_ctx *ctx, const char *path, int both_strands, uint32_t *n_records);
+
+/* ovl_write_gfa replaces the GFA2 writing loop of phasm/cli/assembler.py:30,38,46-48 over
+ * gfa_header/gfa_line (phasm/io/gfa.py:230-240), byte for byte: `what` bit0 = header line
+ * "H\tVN:z:2.0", bit1 = one "S\t<name>\t<len>\t*" line per record in input order, bit2 = one
+ * "E\t*\t<a>\t<b>\t<astart>\t<aend>\t0\t<bend>\t*" line per row of the last ovl_overlaps* call.
+ * Writes to the file descriptor fd (the caller flushes its own buffered writer first). */
+int ovl_write_gfa(ovl_ctx *ctx, int fd, int what, uint64_t *bytes_written);
+
 /* ---- multi-GPU (one process per GPU) ---------------------------------------------------
  * All ranks add the SAME entry table in the same order; rank r scans only the A entries of
  * its contiguous, base-balanced range and returns only those rows.  The rank's packed reads

@@ -60,6 +60,8 @@ SIGNATURES = {
     "ovl_get_stats": (c_int, [_P, POINTER(OvlStats)]),
     "ovl_timer_start": (c_int, [_P]),
     "ovl_timer_stop": (c_int, [_P, POINTER(c_float)]),
+    "ovl_add_fasta": (c_int, [_P, c_char_p, c_int, POINTER(c_uint32)]),
+    "ovl_write_gfa": (c_int, [_P, c_int, c_int, POINTER(c_uint64)]),
     "ovl_comm_unique_id": (c_int, [c_void_p]),
     "ovl_comm_init": (c_int, [_P, c_void_p, c_int, c_int]),
     "ovl_comm_sync_ranges": (c_int, [_P]),

@@ -14,6 +14,7 @@
 //
 // Device-wide sort / select / prefix-sum come from CUB (ships with CUDA 12.9); everything else
 // is in the k*.cuh files next to this one.
+#include <cerrno>
 #include <cstdarg>
 #include <cstdio>
 #include <cstdlib>
@@ -1028,3 +1029,5 @@ int ovl_debug_packed(ovl_ctx* c, uint32_t idx, uint8_t* out, size_t out_cap, siz
 }
 
 }  // extern "C"
+
+#include "ovl_io.inl"

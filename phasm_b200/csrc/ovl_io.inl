@@ -1,0 +1,230 @@
+// ovl_io.inl -- host-side text I/O of the C ABI (included at the end of ovl.cu):
+//   ovl_add_fasta   FASTA -> entry store.  Replaces the dinopy FastaReader loop of
+//                   /root/reference/phasm/cli/assembler.py:32-40 (dinopy is not vendored).
+//   ovl_write_gfa   entry store + rows of the last ovl_overlaps* call -> GFA2 text.  Replaces
+//                   the per-row Python loop /root/reference/phasm/cli/assembler.py:30,38,46-48
+//                   over gfa_header/gfa_line (/root/reference/phasm/io/gfa.py:230-240).
+// Pure byte shuffling on the host; no overlap computation happens here.
+#include <algorithm>
+#include <fcntl.h>
+#include <sys/mman.h>
+#include <sys/stat.h>
+#include <thread>
+#include <unistd.h>
+
+namespace {
+
+// append bytes to the record being staged at the end of the pinned ASCII area
+int stage_append(ovl_ctx* c, size_t rec_off, size_t& rec_len, const char* p, size_t n) {
+    if (!n) return OVL_OK;
+    const size_t need = rec_off + align16(rec_len + n) + SLACK;
+    OVL_TRY(pin_ensure(c, c->ascii, need, rec_off + rec_len));
+    memcpy(c->ascii.p + rec_off + rec_len, p, n);
+    rec_len += n;
+    return OVL_OK;
+}
+
+inline size_t rstrip(const char* p, size_t n) {
+    while (n && (p[n - 1] == '\r' || p[n - 1] == ' ' || p[n - 1] == '\t')) --n;
+    return n;
+}
+
+inline char* put_u32(char* p, uint32_t v) {
+    char tmp[10];
+    int n = 0;
+    do {
+        tmp[n++] = (char)('0' + v % 10);
+        v /= 10;
+    } while (v);
+    while (n) *p++ = tmp[--n];
+    return p;
+}
+
+int write_all(ovl_ctx* c, int fd, const char* p, size_t n) {
+    while (n) {
+        const ssize_t w = write(fd, p, n);
+        if (w < 0) {
+            if (errno == EINTR) continue;
+            return fail(c, OVL_E_ARG, "ovl_write_gfa: write failed: %s", strerror(errno));
+        }
+        p += w;
+        n -= (size_t)w;
+    }
+    return OVL_OK;
+}
+
+}  // namespace
+
+extern "C" {
+
+// FASTA rules (documented; dinopy's own are unverifiable here): a record starts
+// at a line beginning with '>'; its name is the rest of that line, right-stripped; its sequence
+// is the concatenation of the following lines (right-stripped, blank lines skipped) up to the
+// next '>' line or EOF.  Bytes are taken as they are: anything outside upper-case ACGT is
+// rejected later by the pack kernel (OVL_E_ALPHABET).
+int ovl_add_fasta(ovl_ctx* c, const char* path, int both_strands, uint32_t* n_records) {
+    if (!c || !path) return fail(c, OVL_E_ARG, "ovl_add_fasta: NULL argument");
+    if (n_records) *n_records = 0;
+    OVL_TRY(set_dev(c));
+    const int fd = open(path, O_RDONLY);
+    if (fd < 0) return fail(c, OVL_E_ARG, "ovl_add_fasta: cannot open '%s': %s", path, strerror(errno));
+    struct stat sb;
+    if (fstat(fd, &sb) != 0) {
+        close(fd);
+        return fail(c, OVL_E_ARG, "ovl_add_fasta: cannot stat '%s'", path);
+    }
+    const size_t fsz = (size_t)sb.st_size;
+    if (!fsz) {
+        close(fd);
+        return OVL_OK;
+    }
+    void* mp = mmap(nullptr, fsz, PROT_READ, MAP_PRIVATE, fd, 0);
+    close(fd);
+    if (mp == MAP_FAILED) return fail(c, OVL_E_NOMEM, "ovl_add_fasta: mmap of '%s' failed", path);
+    madvise(mp, fsz, MADV_SEQUENTIAL);
+    const char* const base = static_cast<const char*>(mp);
+    const char* const end = base + fsz;
+    int rc = OVL_OK;
+    uint32_t nrec = 0;
+    try {
+        rc = pin_ensure(c, c->ascii, c->ascii_used + fsz + SLACK, c->ascii_used);
+        const char* p = base;
+        bool open_rec = false;
+        const char* name = nullptr;
+        size_t name_len = 0, rec_off = 0, rec_len = 0;
+        auto close_rec = [&]() -> int {
+            if (!open_rec) return OVL_OK;
+            open_rec = false;
+            c->ascii_used = rec_off + align16(rec_len);
+            ++nrec;
+            if (both_strands) {
+                OVL_TRY(push_entry(c, name, name_len, "+", rec_off, rec_len, 0));
+                return push_entry(c, name, name_len, "-", rec_off, rec_len, 1);
+            }
+            return push_entry(c, name, name_len, nullptr, rec_off, rec_len, 0);
+        };
+        while (rc == OVL_OK && p < end) {
+            const char* nl = static_cast<const char*>(memchr(p, '\n', (size_t)(end - p)));
+            const char* le = nl ? nl : end;
+            size_t n = rstrip(p, (size_t)(le - p));
+            if (n && p[0] == '>') {
+                rc = close_rec();
+                name = p + 1;
+                name_len = n - 1;
+                rec_off = c->ascii_used;
+                rec_len = 0;
+                open_rec = true;
+            } else if (n) {
+                if (!open_rec) {
+                    rc = fail(c, OVL_E_ARG, "ovl_add_fasta: '%s' has sequence data before the first '>' line", path);
+                    break;
+                }
+                rc = stage_append(c, rec_off, rec_len, p, n);
+            }
+            p = nl ? nl + 1 : end;
+        }
+        if (rc == OVL_OK) rc = close_rec();
+    } catch (const std::bad_alloc&) {
+        rc = fail(c, OVL_E_NOMEM, "out of host memory");
+    }
+    munmap(mp, fsz);
+    if (n_records) *n_records = nrec;
+    return rc;
+}
+
+// what: bit0 header line, bit1 segment lines, bit2 edge lines (of the last ovl_overlaps* call).
+//   H\tVN:z:2.0                                  assembler.py:30 / gfa.py:234-240
+//   S\t<name>\t<len>\t*                          assembler.py:38   one per RECORD, input order
+//   E\t*\t<a>\t<b>\t<as>\t<ae>\t0\t<be>\t*       assembler.py:46-48
+// A record is an entry that is not a reverse-complement twin (ovl_add_read / _bulk / _fasta
+// with both strands: its name is the entry id without the trailing '+'; ovl_add_sequence
+// entries are written with their id as it is).
+int ovl_write_gfa(ovl_ctx* c, int fd, int what, uint64_t* bytes_written) {
+    if (!c || fd < 0) return fail(c, OVL_E_ARG, "ovl_write_gfa: bad argument");
+    uint64_t total = 0;
+    const size_t M = c->len.size();
+    try {
+        std::string out;
+        if (what & 1) out += "H\tVN:z:2.0\n";
+        if (what & 2) {
+            out.reserve(out.size() + 24 * M + c->id_blob.size());
+            char num[16];
+            for (size_t e = 0; e < M; ++e) {
+                if (c->flags[e] & 1) continue;
+                const bool twin = e + 1 < M && (c->flags[e + 1] & 1);
+                const char* id = c->id_blob.data() + c->id_off[e];
+                size_t il = (size_t)(c->id_off[e + 1] - c->id_off[e]);
+                if (twin && il) --il;  // drop the '+'
+                out += "S\t";
+                out.append(id, il);
+                out += '\t';
+                out.append(num, (size_t)(put_u32(num, c->len[e]) - num));
+                out += "\t*\n";
+            }
+        }
+        if (!out.empty()) {
+            OVL_TRY(write_all(c, fd, out.data(), out.size()));
+            total += out.size();
+        }
+        if (what & 4) {
+            const ovl_row* rows = nullptr;
+            uint64_t n = 0;
+            OVL_TRY(ovl_fetch_rows(c, &rows, &n));
+            size_t max_id = 0;
+            for (size_t e = 0; e < M; ++e) max_id = std::max(max_id, (size_t)(c->id_off[e + 1] - c->id_off[e]));
+            const size_t max_line = 2 * max_id + 64;
+            unsigned nt = std::thread::hardware_concurrency();
+            if (nt == 0) nt = 1;
+            if (nt > 32) nt = 32;
+            const uint64_t CHUNK = 1u << 16;  // rows per formatting task
+            for (uint64_t r0 = 0; r0 < n; r0 += (uint64_t)nt * CHUNK) {
+                const unsigned tasks = (unsigned)std::min<uint64_t>(nt, (n - r0 + CHUNK - 1) / CHUNK);
+                std::vector<std::string> bufs(tasks);
+                auto work = [&](unsigned t) {
+                    const uint64_t lo = r0 + (uint64_t)t * CHUNK, hi = std::min<uint64_t>(lo + CHUNK, n);
+                    std::string& b = bufs[t];
+                    b.resize((size_t)(hi - lo) * max_line);
+                    char* p = &b[0];
+                    for (uint64_t i = lo; i < hi; ++i) {
+                        const ovl_row& r = rows[i];
+                        memcpy(p, "E\t*\t", 4);
+                        p += 4;
+                        size_t il = (size_t)(c->id_off[r.a + 1] - c->id_off[r.a]);
+                        memcpy(p, c->id_blob.data() + c->id_off[r.a], il);
+                        p += il;
+                        *p++ = '\t';
+                        il = (size_t)(c->id_off[r.b + 1] - c->id_off[r.b]);
+                        memcpy(p, c->id_blob.data() + c->id_off[r.b], il);
+                        p += il;
+                        *p++ = '\t';
+                        p = put_u32(p, r.astart);
+                        *p++ = '\t';
+                        p = put_u32(p, r.aend);
+                        memcpy(p, "\t0\t", 3);
+                        p += 3;
+                        p = put_u32(p, r.bend);
+                        memcpy(p, "\t*\n", 3);
+                        p += 3;
+                    }
+                    b.resize((size_t)(p - b.data()));
+                };
+                std::vector<std::thread> th;
+                for (unsigned t = 1; t < tasks; ++t) th.emplace_back(work, t);
+                work(0);
+                for (auto& x : th) x.join();
+                for (unsigned t = 0; t < tasks; ++t) {
+                    OVL_TRY(write_all(c, fd, bufs[t].data(), bufs[t].size()));
+                    total += bufs[t].size();
+                }
+            }
+        }
+    } catch (const std::bad_alloc&) {
+        return fail(c, OVL_E_NOMEM, "out of host memory");
+    } catch (const std::system_error& e) {
+        return fail(c, OVL_E_ARG, "ovl_write_gfa: %s", e.what());
+    }
+    if (bytes_written) *bytes_written = total;
+    return OVL_OK;
+}
+
+}  // extern "C"

@@ -132,6 +132,29 @@ class ExactOverlapper:
             self._check(self._lib.ovl_add_bulk(self._ctx, buf.ctypes.data, offsets.ctypes.data, n,
                                                None, None, int(both_strands)))
 
+    def add_fasta(self, path, both_strands: bool = True) -> int:
+        """Native FASTA ingest (``ovl_add_fasta``): what the dinopy loop of
+        phasm/cli/assembler.py:32-40 does, without Python objects per read.  Returns the number
+        of records."""
+        import os
+        n = c_uint32()
+        self._check(self._lib.ovl_add_fasta(self._ctx, os.fsencode(path), int(both_strands), byref(n)))
+        return n.value
+
+    def write_gfa(self, out, header: bool = True, segments: bool = True, edges: bool = True) -> int:
+        """Native GFA2 writer (``ovl_write_gfa``): header / S-lines / E-lines of the last
+        ``overlaps*`` call, byte-identical to phasm/cli/assembler.py:30,38,46-48.  ``out`` is a
+        file descriptor or a file object with ``fileno()`` (flushed first).  Returns bytes written."""
+        if hasattr(out, "fileno"):
+            out.flush()
+            fd = out.fileno()
+        else:
+            fd = int(out)
+        nb = c_uint64()
+        what = (1 if header else 0) | (2 if segments else 0) | (4 if edges else 0)
+        self._check(self._lib.ovl_write_gfa(self._ctx, fd, what, byref(nb)))
+        return nb.value
+
     def add_remote(self, lengths, both_strands: bool = True) -> None:
         """Multi-GPU: declare records held by another rank (lengths only)."""
         lengths = np.ascontiguousarray(lengths, dtype=np.uint32)

@@ -72,3 +72,13 @@ def mid_input(key):
     sh = synth.CONFIGS[x].scaled(y)
     buf, off, names = synth.generate(sh)
     return reads_of(buf, off, names), sh.min_length
+
+
+def has_gpu() -> bool:
+    import ctypes
+    try:
+        lib = ctypes.CDLL("libcudart.so.12")
+    except OSError:
+        return False
+    n = ctypes.c_int(0)
+    return lib.cudaGetDeviceCount(ctypes.byref(n)) == 0 and n.value > 0
