@@ -242,6 +242,9 @@ def run_b200(args):
     n_bases_total = shape.n_bases
 
     ov = ExactOverlapper(local)
+    for kv in args.opt:
+        name, _, val = kv.partition("=")
+        ov.set_option(name, int(val))
     rl = shape.read_len
     if lo:
         ov.add_remote(np.full(lo, rl, dtype=np.uint32))
@@ -353,10 +356,12 @@ def run_b200(args):
             "scaling": "weak", "vs_baseline": None, "dtype": "u8", "data": "synthetic",
             "config": workload_config(shape, world),
             "overlaps_per_s": n_rows / (ms_step * 1e-3), "rows": n_rows,
-            "candidates": candidates, "stage_ms": stage,
+            "candidates": candidates, "verified": st["verified"], "hits": st["hits"],
+            "mirror": st["mirror"], "anchor_stride": st["anchor_stride"], "stage_ms": stage,
             "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": h2d,
                     "d2h_bytes_per_step": d2h, "ms_per_step": 1e3 * t_e2e,
                     "overlaps_per_s": n_rows / t_e2e,
+                    "ms_h2d": st_e["ms_h2d"], "ms_device": st_e["ms_device"], "ms_d2h": st_e["ms_d2h"],
                     "call": "ExactOverlapper.overlaps_arrays (ovl_overlaps: host ASCII in, host rows out)"},
             "gpu_launches": launches, "lib_launches": lib_launches,
             "roofline": roofline, "clocks": clocks,
@@ -383,6 +388,8 @@ def main():
     ap.add_argument("--cpu-sample", type=int, default=4_000_000,
                     help="forward bases of the cpu_baseline sample (~15-20 s of reference CPU work)")
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
+    ap.add_argument("--opt", action="append", default=[], metavar="NAME=VALUE",
+                    help="debug: ovl_set_option tuning knob (e.g. anchor_stride=16, mirror=0)")
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3) if args.impl == "b200" else args.warmup
     args.steps = max(args.steps, 1)

@@ -53,7 +53,8 @@ typedef struct {
     uint64_t ascii_bytes;      /* host->device bytes of sequence data                     */
     uint64_t granules;         /* 64-base packed granules (16 B each)                     */
     uint64_t anchors;          /* entries with |b| >= min_length                          */
-    uint64_t candidates;       /* (a,p,b), a != b, emitted by the scan                    */
+    uint64_t candidates;       /* (a,p,b), a != b, emitted by the scan (mirror mode: only  */
+                               /* the self-verifying half)                                */
     uint64_t hits;             /* candidates that verified                                */
     uint64_t rows;
     uint64_t compared_bases;   /* sum m_c (only when stats collection is on, else 0)      */
@@ -64,7 +65,8 @@ typedef struct {
     uint32_t launches;         /* kernels of this library launched by the call            */
     uint32_t lib_launches;     /* CUB device-wide primitive calls (sort / scan)           */
     uint32_t retries;          /* scan re-runs after a candidate-buffer overflow          */
-    uint32_t pad_;
+    uint32_t mirror;           /* 1: strand-mirror halving was on (every entry has its twin) */
+    uint64_t verified;         /* candidates actually compared by the verifier            */
     float ms_h2d, ms_pack, ms_anchor, ms_scan, ms_sort, ms_verify, ms_emit, ms_d2h;
     float ms_device;           /* pack..emit: ASCII resident in HBM -> rows resident      */
     float ms_total;            /* h2d..d2h                                                */
@@ -130,7 +132,9 @@ int ovl_fetch_rows(ovl_ctx *ctx, const ovl_row **rows, uint64_t *n_rows);
 int ovl_set_collect_stats(ovl_ctx *ctx, int on);
 /* Tuning knobs.  "anchor_stride": 0 = auto (largest power of two <= min(64, l-k+1)), else an
  * upper bound (1 forces the dense scan).  "serial_verify": 1 = chunk-by-chunk early-exit
- * verifier instead of the head/tail two-pass form. */
+ * verifier instead of the head/tail two-pass form.  "mirror": 0 = compare every candidate even
+ * when every read is present on both strands (default 1: compare one of each strand-mirror
+ * pair and emit both rows). */
 int ovl_set_option(ovl_ctx *ctx, const char *name, int64_t value);
 int ovl_get_stats(const ovl_ctx *ctx, ovl_stats *out);
 

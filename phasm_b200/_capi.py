@@ -28,7 +28,8 @@ class OvlStats(Structure):
                   "candidates", "hits", "rows", "compared_bases", "operand_bytes",
                   "scan_positions")] +
                 [(n, c_uint32) for n in ("kmer", "anchor_stride", "launches", "lib_launches",
-                                         "retries", "pad_")] +
+                                         "retries", "mirror")] +
+                [("verified", c_uint64)] +
                 [(n, c_float) for n in ("ms_h2d", "ms_pack", "ms_anchor", "ms_scan", "ms_sort",
                                         "ms_verify", "ms_emit", "ms_d2h", "ms_device", "ms_total")])
 

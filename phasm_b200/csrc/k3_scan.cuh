@@ -40,6 +40,7 @@ struct ScanParams {
     const uint32_t* next;
     KeyFmt fmt;
     CandSink sink;
+    MirrorRule mirror;          // on: emit only the candidates that verify for themselves
 };
 
 // ---- sparse path ------------------------------------------------------------------------
@@ -95,7 +96,7 @@ __global__ void __launch_bounds__(256) k3_probe(const ScanParams P) {
                     // candidate p = q - delta: needs p >= 0, |a| - p >= l, and b != a
                     // (identity by index: overlapper.cpp:72-74,101-104)
                     if (q >= delta && b != a && L - (q - delta) >= P.l) {
-                        have = true;
+                        have = !P.mirror.on || mirror_items(P.mirror, a, L, b, __ldg(P.ent + b).y, q - delta) != 0;
                         key = P.fmt.make(a, b, q - delta);
                     }
                     node = __ldg(P.next + node);
@@ -187,7 +188,8 @@ __global__ void __launch_bounds__(1024, 1) k3_scan(const ScanParams P) {
                     // p == 0, and at p != 0 for periodic reads): identity by index,
                     // overlapper.cpp:72-74,101-104
                     if (node != a) {
-                        have = true;
+                        have = !P.mirror.on ||
+                               mirror_items(P.mirror, a, __ldg(P.ent + a).y, node, __ldg(P.ent + node).y, p) != 0;
                         key = P.fmt.make(a, node, p);
                     }
                     node = __ldg(P.next + node);

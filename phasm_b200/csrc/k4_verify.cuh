@@ -176,6 +176,20 @@ __global__ void __launch_bounds__(256) k4_verify_serial(const VerifyParams P) {
 constexpr uint32_t FIRST_GRAN = 32;
 constexpr int HEAD_UNROLL = 4;
 
+// Strand-mirror halving.  When every read was added on both strands (entry 2i = read i, entry
+// 2i+1 = its reverse complement: assembler.py:39-40) a match statement has an equivalent twin
+// on the opposite strands (x' = x ^ 1 is the other strand of x):
+//
+//   SP   a[p:] == b[:rem]            <=>  b'[|b|-rem:] == a'[:rem]       key (b', a', |b|-rem)
+//   CONT a[p:p+|b|] == b             <=>  a'[|a|-p-|b| : |a|-p] == b'    key (a', b', |a|-p-|b|)
+//
+// Both maps are involutions on (key, type) items, so exactly one item of every twin pair is
+// compared (SP: the one with a <= b'; CONT: the one with a forward) and, if it matches, BOTH
+// keys are appended to the hit list.  The scan finds every true hit on its own, so a true hit
+// whose item is not the canonical one is always produced by its canonical twin; a false
+// candidate's twin is false too.  Half of the operand bytes are never read.
+// Multi-GPU: a rank only emits rows of its own A range; the SP twin is used only when b' is
+// local as well (otherwise both ranks compare their own candidate), the CONT twin always is.
 struct Verify2Params {
     const uint64_t* keys;              // candidate keys (flags clear), any order
     uint64_t n;
@@ -185,12 +199,13 @@ struct Verify2Params {
     uint32_t* surv;                    // k4a -> k4b: indices of candidates alive after the head
     unsigned long long* n_surv;
     CandSink hits;                     // verified keys with their flag bits set
+    MirrorRule mirror;                 // on: the scan kept only the self-verifying candidates
 };
 
 struct CandMeta {
     uint32_t wa_lo, wa_hi;  // 64-bit word index of a[p]
     uint32_t gb;            // first granule of b
-    uint32_t n, sh, fl;     // bases to compare, bit shift (0..62, even), HIT_* flags
+    uint32_t n, sh, fl;     // bases to compare (0: skip), bit shift (0..62, even), HIT_* items to emit
 };
 
 __device__ __forceinline__ CandMeta cand_meta(const Verify2Params& P, uint64_t key) {
@@ -199,13 +214,27 @@ __device__ __forceinline__ CandMeta cand_meta(const Verify2Params& P, uint64_t k
     const uint2 ma = __ldg(P.ent + a), mb = __ldg(P.ent + b);
     const uint32_t rem = ma.y - p;
     m.n = rem < mb.y ? rem : mb.y;
-    m.fl = (rem <= mb.y ? (uint32_t)HIT_SP : 0u) | (rem >= mb.y ? (uint32_t)HIT_CONT : 0u);
+    m.fl = mirror_items(P.mirror, a, ma.y, b, mb.y, p);  // never 0: the scan dropped those
     const uint64_t wa = 2ull * ma.x + (p >> 5);
     m.wa_lo = (uint32_t)wa;
     m.wa_hi = (uint32_t)(wa >> 32);
     m.gb = mb.x;
     m.sh = 2u * (p & 31u);
     return m;
+}
+
+// keys a matching candidate contributes: [0] its own, [1] the SP twin, [2] the CONT twin (0 = none;
+// a real key is never 0 because its flag bits are set)
+__device__ __forceinline__ void hit_keys(const Verify2Params& P, uint64_t key, uint32_t fl, uint64_t out[3]) {
+    out[0] = key | fl;
+    out[1] = out[2] = 0;
+    if (!P.mirror.on) return;
+    const uint32_t a = P.fmt.a(key), b = P.fmt.b(key), p = P.fmt.p(key);
+    const uint32_t la = __ldg(P.ent + a).y, lb = __ldg(P.ent + b).y;
+    const uint32_t bt = b ^ 1u, at = a ^ 1u;
+    if ((fl & HIT_SP) && bt >= P.mirror.own_lo && bt < P.mirror.own_hi && a < bt)
+        out[1] = P.fmt.make(bt, at, lb - (la - p)) | HIT_SP;
+    if (fl & HIT_CONT) out[2] = P.fmt.make(at, bt, la - p - lb) | HIT_CONT;
 }
 
 // granule = bits [sh, sh+128) of the 192-bit value (w2:w1:w0); HI32 = (sh >= 32), t = sh & 31
@@ -279,7 +308,10 @@ __global__ void __launch_bounds__(256) k4a_head(const Verify2Params P) {
         const bool ok = (ok_mask >> lane) & 1u;
         const bool done = ok && my.n <= 64u * FIRST_GRAN;
         const bool alive = ok && !done;
-        wbuf_push(buf, nbuf, P.hits, lane, done, key | my.fl);
+        uint64_t hk[3] = {0, 0, 0};
+        if (done) hit_keys(P, key, my.fl, hk);
+#pragma unroll
+        for (int i = 0; i < 3; ++i) wbuf_push(buf, nbuf, P.hits, lane, hk[i] != 0, hk[i]);
         const unsigned am = __ballot_sync(FULL, alive);
         if (am) {
             unsigned long long base = 0;
@@ -344,7 +376,10 @@ __global__ void __launch_bounds__(256) k4b_tail(const Verify2Params P) {
         const uint32_t t = m.sh & 31u;
         const uint4 acc = (m.sh & 32u) ? tail_diff<true>(pa, pb, m.n, t, lane) : tail_diff<false>(pa, pb, m.n, t, lane);
         const unsigned bad = __ballot_sync(FULL, (acc.x | acc.y | acc.z | acc.w) != 0);
-        wbuf_push(buf, nbuf, P.hits, lane, !bad && lane == 0, key | m.fl);
+        uint64_t hk[3] = {0, 0, 0};
+        if (!bad) hit_keys(P, key, m.fl, hk);
+        const uint64_t mine = lane == 0 ? hk[0] : (lane == 1 ? hk[1] : (lane == 2 ? hk[2] : 0));
+        wbuf_push(buf, nbuf, P.hits, lane, mine != 0, mine);
     }
     if (nbuf) wbuf_flush(buf, nbuf, P.hits, lane);
 }

@@ -97,6 +97,7 @@ struct ovl_ctx {
     int collect = 0;
     int opt_stride = 0;  // 0 = auto; else upper bound on the anchor stride (1 = dense scan)
     int opt_serial_verify = 0;  // 1: chunk-by-chunk early-exit verifier instead of head/tail
+    int opt_mirror = 1;         // 1: strand-mirror halving when every entry has its twin
     ovl_stats stats{};
 
     // ---- multi-GPU ----
@@ -453,6 +454,10 @@ int ovl_set_option(ovl_ctx* c, const char* name, int64_t value) {
         c->opt_serial_verify = value != 0;
         return OVL_OK;
     }
+    if (!strcmp(name, "mirror")) {
+        c->opt_mirror = value != 0;
+        return OVL_OK;
+    }
     return fail(c, OVL_E_ARG, "unknown option '%s'", name);
 }
 
@@ -557,6 +562,14 @@ int ovl_overlaps_device(ovl_ctx* c, uint32_t min_length, uint64_t* n_rows_out) {
     c->gathered = false;
     if (n_rows_out) *n_rows_out = 0;
     if (M == 0) return OVL_OK;  // the reference segfaults here; we return no rows
+    // strand-mirror halving needs entry e ^ 1 to be the other strand of entry e, for every e
+    bool mirror = c->opt_mirror && !c->collect && !c->opt_serial_verify && (M % 2 == 0);
+    for (uint32_t e = 0; mirror && e < M; e += 2) mirror = !(c->flags[e] & 1) && (c->flags[e + 1] & 1);
+    S.mirror = mirror ? 1u : 0u;
+    ovl::MirrorRule mrule;
+    mrule.on = mirror ? 1 : 0;
+    mrule.own_lo = c->e_lo;
+    mrule.own_hi = c->e_hi;
 
     const uint32_t G = c->gran0[M];
     S.granules = G;
@@ -734,6 +747,7 @@ int ovl_overlaps_device(ovl_ctx* c, uint32_t min_length, uint64_t* n_rows_out) {
         P.sink.out = c->d_cand.as<uint64_t>();
         P.sink.n_out = reinterpret_cast<unsigned long long*>(ctr + C_NCAND);
         P.sink.cap = c->cand_cap;
+        P.mirror = mrule;
         if (!dense) {
             const uint32_t tiles = (g_hi - g_lo + 31) / 32;
             uint32_t blocks = (tiles + 7) / 8;
@@ -762,13 +776,14 @@ int ovl_overlaps_device(ovl_ctx* c, uint32_t min_length, uint64_t* n_rows_out) {
 
     // ---- K4: verify -----------------------------------------------------------------------
     CK(cudaEventRecord(c->ev[E_VERIFY0], st));
-    OVL_TRY(dev_ensure(c, c->d_cand2, n_cand * 8));  // hit keys
-    OVL_TRY(dev_ensure(c, c->d_cnt, n_cand * 4));    // survivor list now, row counts in K5
+    const uint64_t hit_cap = mirror ? 3 * n_cand : n_cand;  // own key + SP twin + CONT twin
+    OVL_TRY(dev_ensure(c, c->d_cand2, hit_cap * 8));  // hit keys
+    OVL_TRY(dev_ensure(c, c->d_cnt, hit_cap * 4));    // survivor list now, row counts in K5
     {
         CandSink hits;
         hits.out = c->d_cand2.as<uint64_t>();
         hits.n_out = reinterpret_cast<unsigned long long*>(ctr + C_NHITS);
-        hits.cap = n_cand;
+        hits.cap = hit_cap;
         uint64_t blocks = (n_cand + 255) / 256;
         if (blocks > (uint64_t)nsm * 8) blocks = (uint64_t)nsm * 8;
         if (c->collect || c->opt_serial_verify) {
@@ -793,6 +808,7 @@ int ovl_overlaps_device(ovl_ctx* c, uint32_t min_length, uint64_t* n_rows_out) {
             V.surv = c->d_cnt.as<uint32_t>();
             V.n_surv = reinterpret_cast<unsigned long long*>(ctr + C_NSURV);
             V.hits = hits;
+            V.mirror = mrule;
             k4a_head<<<(unsigned)blocks, 256, 0, st>>>(V);
             k4b_tail<<<nsm * 8, 256, 0, st>>>(V);
             launches += 2;
@@ -802,12 +818,18 @@ int ovl_overlaps_device(ovl_ctx* c, uint32_t min_length, uint64_t* n_rows_out) {
     OVL_TRY(read_ctr(c));
     const uint64_t n_hits = c->h_ctr[C_NHITS];
     S.hits = n_hits;
+    if (n_hits > hit_cap) return fail(c, OVL_E_LIMIT, "hit list overflow (%llu > %llu): internal error", (unsigned long long)n_hits, (unsigned long long)hit_cap);
+    S.verified = n_cand;
     S.compared_bases = c->h_ctr[C_SUMM];
     S.operand_bytes = c->h_ctr[C_SUMB];
     if (n_hits == 0) return finish_from(E_SORT0);
 
     // ---- sort the hit keys by (a, b, p) --------------------------------------------------------
     CK(cudaEventRecord(c->ev[E_SORT0], st));
+    if (n_hits > c->cand_cap) {  // mirror mode can (in theory) return more entries than candidates
+        OVL_TRY(dev_ensure(c, c->d_cand, n_hits * 8, false));
+        c->cand_cap = c->d_cand.cap / 8;
+    }
     uint64_t* keys = c->d_cand.as<uint64_t>();  // the candidate buffer is free again
     {
         size_t tb = 0;

@@ -18,7 +18,7 @@
 //   flags     u8     [M]   bit0: entry is the reverse complement of its source record (it then
 //                          directly follows the forward entry of the same record)
 //
-// Candidate / hit key (64 bit): [a | b | p | cont | sp], most significant first.  K3 emits keys
+// Candidate / hit key (64 bit): [a | b | p | sp | cont], most significant first.  K3 emits keys
 // with both flag bits clear, a radix sort orders them by (a, b, p), K4 sets the flag bits of the
 // candidates that verify, K5 turns flagged keys into rows.
 //
@@ -47,7 +47,7 @@ struct Row {
     uint32_t a, b, astart, aend, bend;
 };
 
-// Bit layout of a 64-bit candidate key: [a | b | p | cont | sp], most significant first.
+// Bit layout of a 64-bit candidate key: [a | b | p | sp | cont], most significant first.
 struct KeyFmt {
     int bits_e;  // bits of an entry index
     int bits_p;  // bits of a position
@@ -65,8 +65,31 @@ struct KeyFmt {
         return (uint32_t)(key >> (2 + bits_p + bits_e));
     }
 };
-constexpr uint64_t HIT_SP = 1;    // rem <= |b|: suffix-prefix (R1 candidate)
-constexpr uint64_t HIT_CONT = 2;  // rem >= |b|: b wholly inside a (R2 row)
+// CONT sorts before SP so that, when the two items of one key arrive as separate entries (mirror
+// mode, k4_verify.cuh), the SP entries of a pair stay contiguous at the end of the pair's run.
+constexpr uint64_t HIT_CONT = 1;  // rem >= |b|: b wholly inside a (R2 row)
+constexpr uint64_t HIT_SP = 2;    // rem <= |b|: suffix-prefix (R1 candidate)
+
+// Strand-mirror halving (k4_verify.cuh explains why it is exact).  When every read is present
+// on both strands (entry e ^ 1 is the other strand of entry e) only one candidate of each
+// strand-mirror pair is compared.  mirror_items() returns the HIT_* items candidate (a,p,b)
+// has to verify and emit itself; 0 means its twins cover it.
+struct MirrorRule {
+    int on;
+    uint32_t own_lo, own_hi;  // entries whose rows this rank emits (multi-GPU: the SP twin is
+                              // used only when b ^ 1 is local as well)
+};
+__device__ __forceinline__ uint32_t mirror_items(const MirrorRule& R, uint32_t a, uint32_t la, uint32_t b,
+                                                 uint32_t lb, uint32_t p) {
+    const uint32_t rem = la - p;
+    uint32_t fl = (rem <= lb ? (uint32_t)HIT_SP : 0u) | (rem >= lb ? (uint32_t)HIT_CONT : 0u);
+    if (R.on) {
+        const uint32_t bt = b ^ 1u;
+        if ((fl & HIT_SP) && bt >= R.own_lo && bt < R.own_hi && a > bt) fl &= ~(uint32_t)HIT_SP;
+        if (a & 1u) fl &= ~(uint32_t)HIT_CONT;
+    }
+    return fl;
+}
 
 __host__ __device__ __forceinline__ uint64_t kmer_mask(int k) {
     return k >= 32 ? ~0ull : ((1ull << (2 * k)) - 1ull);

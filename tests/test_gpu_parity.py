@@ -137,6 +137,64 @@ def test_serial_verifier_gives_the_same_rows(ov):
         ov.set_option("serial_verify", 0)
 
 
+def test_strand_mirror_halving_gives_the_same_rows(ov):
+    """Mirror mode (compare one candidate of each strand-mirror pair, emit both rows) vs comparing
+    every candidate: identical rows; it is on only when every entry has its twin."""
+    for key in sorted(helpers.MID_SPECS):
+        want = sort_rows(helpers.load_mid()[key])
+        reads, l = helpers.mid_input(key)
+        got = run_reads_idx(ov, reads, l)
+        st = ov.stats()
+        assert st["mirror"] == 1 and np.array_equal(got, want), key
+        assert st["verified"] <= st["candidates"]
+        try:
+            ov.set_option("mirror", 0)
+            got0 = run_reads_idx(ov, reads, l)
+            st0 = ov.stats()
+        finally:
+            ov.set_option("mirror", 1)
+        assert st0["mirror"] == 0 and st0["verified"] == st0["candidates"]
+        assert np.array_equal(got0, want), key
+    # add_sequence entries carry no twin information: mirror mode must stay off
+    toy = helpers.load_tiny()["toy"]
+    from oracle.bruteforce import both_strand_entries
+    assert run_entries(ov, both_strand_entries(toy["reads"]), toy["min_length"]) == sorted(toy["rows"])
+    assert ov.stats()["mirror"] == 0
+    # mixed: reads + a lone sequence
+    ov.clear()
+    for name, seq in toy["reads"]:
+        ov.add_read(name, seq)
+    ov.add_sequence("lone", "GGGGGGGACTG")
+    ov.overlaps_arrays(3)
+    assert ov.stats()["mirror"] == 0
+
+
+def test_mirror_tiny_random_both_strands(ov):
+    """Tiny random read sets on both strands (palindromes, duplicates, containments, periodic
+    reads) through add_read -> mirror mode, against the brute-force restatement."""
+    from oracle.bruteforce import both_strand_entries, overlaps_bruteforce
+    rnd = random.Random(77)
+    for case in range(150):
+        alpha = rnd.choice(["A", "AT", "ACGT", "ACGT"])
+        reads = []
+        for i in range(rnd.randint(1, 6)):
+            s = "".join(rnd.choice(alpha) for _ in range(rnd.randint(1, 16)))
+            if reads and rnd.random() < 0.4:
+                t = rnd.choice(reads)[1]
+                i0 = rnd.randrange(len(t)); i1 = rnd.randint(i0, len(t))
+                s = rnd.choice([t[i0:i1] + s, s + t[i0:i1], t, revcomp(t), s + revcomp(s)])
+            reads.append(("r%d" % i, s))
+        l = rnd.randint(0, 5)
+        ents = both_strand_entries(reads)
+        want = sorted(overlaps_bruteforce(ents, l))
+        ov.clear()
+        for name, seq in reads:
+            ov.add_read(name, seq)
+        got = sorted(ov.overlaps(l))
+        assert ov.stats()["mirror"] == 1
+        assert got == want, (case, reads, l)
+
+
 def test_auto_stride_follows_min_length(ov):
     reads = helpers.mid_input("edge_s5_l20")[0]
     for l, want in ((1, 1), (20, 1), (32, 1), (33, 2), (35, 4), (47, 16), (63, 32), (94, 32),
