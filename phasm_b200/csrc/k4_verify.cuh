@@ -32,6 +32,7 @@ struct VerifyParams {
     CandSink hits;                     // verified keys with their flag bits set
     unsigned long long* counters;      // [0] sum m_c, [1] sum 2*ceil(m_c/4)   (collect only)
     int collect;
+    MirrorRule mirror;
 };
 
 // (hi:lo) >> sh for sh in [0, 128), sh even; lo/hi are 128-bit little-endian granules.
@@ -73,6 +74,21 @@ __device__ __forceinline__ uint32_t first_diff_base(const uint4 d) {  // d != 0
     return 48 + ((__ffs(d.w) - 1) >> 1);
 }
 
+// keys a matching candidate contributes: [0] its own, [1] the SP twin, [2] the CONT twin (0 = none;
+// a real key is never 0 because its flag bits are set).  See "Strand-mirror halving" below.
+__device__ __forceinline__ void hit_keys(const KeyFmt& fmt, const uint2* __restrict__ ent, const MirrorRule& R,
+                                         uint64_t key, uint32_t fl, uint64_t out[3]) {
+    out[0] = key | fl;
+    out[1] = out[2] = 0;
+    if (!R.on) return;
+    const uint32_t a = fmt.a(key), b = fmt.b(key), p = fmt.p(key);
+    const uint32_t la = __ldg(ent + a).y, lb = __ldg(ent + b).y;
+    const uint32_t bt = b ^ 1u, at = a ^ 1u;
+    if ((fl & HIT_SP) && bt >= R.own_lo && bt < R.own_hi && a < bt)
+        out[1] = fmt.make(bt, at, lb - (la - p)) | HIT_SP;
+    if (fl & HIT_CONT) out[2] = fmt.make(at, bt, la - p - lb) | HIT_CONT;
+}
+
 __global__ void __launch_bounds__(256) k4_verify_serial(const VerifyParams P) {
     __shared__ uint64_t s_buf[8][WBUF];
     uint64_t* buf = s_buf[threadIdx.x >> 5];
@@ -93,7 +109,7 @@ __global__ void __launch_bounds__(256) k4_verify_serial(const VerifyParams P) {
             const uint2 ma = __ldg(P.ent + a), mb = __ldg(P.ent + b);
             const uint32_t rem = ma.y - p;
             my_n = rem < mb.y ? rem : mb.y;
-            my_fl = (rem <= mb.y ? (uint32_t)HIT_SP : 0u) | (rem >= mb.y ? (uint32_t)HIT_CONT : 0u);
+            my_fl = mirror_items(P.mirror, a, ma.y, b, mb.y, p);
             my_ga = ma.x + (p >> 6);
             my_gb = mb.x;
             my_sh = 2u * (p & 63u);
@@ -142,7 +158,10 @@ __global__ void __launch_bounds__(256) k4_verify_serial(const VerifyParams P) {
             }
             if (ok && lane == j) my_ok = 1;
         }
-        wbuf_push(buf, nbuf, P.hits, lane, my_ok != 0, key | my_fl);
+        uint64_t hk[3] = {0, 0, 0};
+        if (my_ok) hit_keys(P.fmt, P.ent, P.mirror, key, my_fl, hk);
+#pragma unroll
+        for (int i = 0; i < 3; ++i) wbuf_push(buf, nbuf, P.hits, lane, hk[i] != 0, hk[i]);
     }
     if (nbuf) wbuf_flush(buf, nbuf, P.hits, lane);
     if (lane == 0) {
@@ -200,7 +219,16 @@ struct Verify2Params {
     unsigned long long* n_surv;
     CandSink hits;                     // verified keys with their flag bits set
     MirrorRule mirror;                 // on: the scan kept only the self-verifying candidates
+    unsigned long long* tile_ctr;      // [0] k4a, [1] k4b: next tile to hand out (zeroed per call)
 };
+
+// dynamic tile hand-out: comparisons differ a lot in length, a static grid-stride split leaves
+// the last wave unbalanced
+__device__ __forceinline__ uint64_t next_tile(unsigned long long* ctr, uint32_t lane) {
+    unsigned long long t = 0;
+    if (lane == 0) t = atomicAdd(ctr, 1ull);
+    return __shfl_sync(FULL, t, 0);
+}
 
 struct CandMeta {
     uint32_t wa_lo, wa_hi;  // 64-bit word index of a[p]
@@ -223,20 +251,6 @@ __device__ __forceinline__ CandMeta cand_meta(const Verify2Params& P, uint64_t k
     return m;
 }
 
-// keys a matching candidate contributes: [0] its own, [1] the SP twin, [2] the CONT twin (0 = none;
-// a real key is never 0 because its flag bits are set)
-__device__ __forceinline__ void hit_keys(const Verify2Params& P, uint64_t key, uint32_t fl, uint64_t out[3]) {
-    out[0] = key | fl;
-    out[1] = out[2] = 0;
-    if (!P.mirror.on) return;
-    const uint32_t a = P.fmt.a(key), b = P.fmt.b(key), p = P.fmt.p(key);
-    const uint32_t la = __ldg(P.ent + a).y, lb = __ldg(P.ent + b).y;
-    const uint32_t bt = b ^ 1u, at = a ^ 1u;
-    if ((fl & HIT_SP) && bt >= P.mirror.own_lo && bt < P.mirror.own_hi && a < bt)
-        out[1] = P.fmt.make(bt, at, lb - (la - p)) | HIT_SP;
-    if (fl & HIT_CONT) out[2] = P.fmt.make(at, bt, la - p - lb) | HIT_CONT;
-}
-
 // granule = bits [sh, sh+128) of the 192-bit value (w2:w1:w0); HI32 = (sh >= 32), t = sh & 31
 template <bool HI32>
 __device__ __forceinline__ uint4 shr192(uint64_t w0, uint64_t w1, uint64_t w2, uint32_t t) {
@@ -252,14 +266,12 @@ __device__ __forceinline__ uint4 shr192(uint64_t w0, uint64_t w1, uint64_t w2, u
 __global__ void __launch_bounds__(256) k4a_head(const Verify2Params P) {
     __shared__ uint64_t s_buf[8][WBUF];
     const uint32_t lane = threadIdx.x & 31;
-    const uint64_t warp = ((uint64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
-    const uint64_t nwarps = ((uint64_t)gridDim.x * blockDim.x) >> 5;
     const uint64_t n_tiles = (P.n + 31) / 32;
     uint64_t* buf = s_buf[threadIdx.x >> 5];
     uint32_t nbuf = 0;
     const uint4* packed128 = reinterpret_cast<const uint4*>(P.packed64);
 
-    for (uint64_t tile = warp; tile < n_tiles; tile += nwarps) {
+    for (uint64_t tile = next_tile(P.tile_ctr, lane); tile < n_tiles; tile = next_tile(P.tile_ctr, lane)) {
         const uint64_t c = tile * 32 + lane;
         uint64_t key = 0;
         CandMeta my = {0, 0, 0, 0, 0, 0};  // n == 0 marks "no candidate" (a real one has n >= l >= 1)
@@ -309,7 +321,7 @@ __global__ void __launch_bounds__(256) k4a_head(const Verify2Params P) {
         const bool done = ok && my.n <= 64u * FIRST_GRAN;
         const bool alive = ok && !done;
         uint64_t hk[3] = {0, 0, 0};
-        if (done) hit_keys(P, key, my.fl, hk);
+        if (done) hit_keys(P.fmt, P.ent, P.mirror, key, my.fl, hk);
 #pragma unroll
         for (int i = 0; i < 3; ++i) wbuf_push(buf, nbuf, P.hits, lane, hk[i] != 0, hk[i]);
         const unsigned am = __ballot_sync(FULL, alive);
@@ -362,24 +374,41 @@ __device__ __forceinline__ uint4 tail_diff(const uint64_t* __restrict__ pa, cons
 __global__ void __launch_bounds__(256) k4b_tail(const Verify2Params P) {
     __shared__ uint64_t s_buf[8][WBUF];
     const uint32_t lane = threadIdx.x & 31;
-    const uint64_t warp = ((uint64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
-    const uint64_t nwarps = ((uint64_t)gridDim.x * blockDim.x) >> 5;
     const uint64_t ns = *P.n_surv;
+    const uint64_t n_tiles = (ns + 31) / 32;
     uint64_t* buf = s_buf[threadIdx.x >> 5];
     uint32_t nbuf = 0;
     const uint4* packed128 = reinterpret_cast<const uint4*>(P.packed64);
-    for (uint64_t s = warp; s < ns; s += nwarps) {
-        const uint64_t key = P.keys[P.surv[s]];
-        const CandMeta m = cand_meta(P, key);
-        const uint64_t* pa = P.packed64 + (((uint64_t)m.wa_hi << 32) | m.wa_lo);
-        const uint4* pb = packed128 + m.gb;
-        const uint32_t t = m.sh & 31u;
-        const uint4 acc = (m.sh & 32u) ? tail_diff<true>(pa, pb, m.n, t, lane) : tail_diff<false>(pa, pb, m.n, t, lane);
-        const unsigned bad = __ballot_sync(FULL, (acc.x | acc.y | acc.z | acc.w) != 0);
+    // A warp takes 32 survivors at a time: every lane fetches and decodes ONE of them (one
+    // dependent surv -> key -> entry chain per 32 survivors instead of per survivor), then the
+    // warp walks the 32 comparisons, one operand round trip each.
+    for (uint64_t tile = next_tile(P.tile_ctr + 1, lane); tile < n_tiles; tile = next_tile(P.tile_ctr + 1, lane)) {
+        const uint64_t s = tile * 32 + lane;
+        uint64_t key = 0;
+        CandMeta my = {0, 0, 0, 0, 0, 0};
+        if (s < ns) {
+            key = P.keys[P.surv[s]];
+            my = cand_meta(P, key);
+        }
+        const uint32_t cnt = (uint32_t)((ns - tile * 32) < 32 ? (ns - tile * 32) : 32);
+        uint32_t ok_mask = 0;
+        for (uint32_t j = 0; j < cnt; ++j) {
+            const uint32_t lo = __shfl_sync(FULL, my.wa_lo, j);
+            const uint32_t hi = __shfl_sync(FULL, my.wa_hi, j);
+            const uint32_t gb = __shfl_sync(FULL, my.gb, j);
+            const uint32_t sh = __shfl_sync(FULL, my.sh, j);
+            const uint32_t n = __shfl_sync(FULL, my.n, j);
+            const uint64_t* pa = P.packed64 + (((uint64_t)hi << 32) | lo);
+            const uint4* pb = packed128 + gb;
+            const uint32_t t = sh & 31u;
+            const uint4 acc = (sh & 32u) ? tail_diff<true>(pa, pb, n, t, lane) : tail_diff<false>(pa, pb, n, t, lane);
+            const unsigned bad = __ballot_sync(FULL, (acc.x | acc.y | acc.z | acc.w) != 0);
+            if (!bad) ok_mask |= 1u << j;
+        }
         uint64_t hk[3] = {0, 0, 0};
-        if (!bad) hit_keys(P, key, m.fl, hk);
-        const uint64_t mine = lane == 0 ? hk[0] : (lane == 1 ? hk[1] : (lane == 2 ? hk[2] : 0));
-        wbuf_push(buf, nbuf, P.hits, lane, mine != 0, mine);
+        if ((ok_mask >> lane) & 1u) hit_keys(P.fmt, P.ent, P.mirror, key, my.fl, hk);
+#pragma unroll
+        for (int i = 0; i < 3; ++i) wbuf_push(buf, nbuf, P.hits, lane, hk[i] != 0, hk[i]);
     }
     if (nbuf) wbuf_flush(buf, nbuf, P.hits, lane);
 }

@@ -58,7 +58,7 @@ struct PinBuf {
 enum Ev { E_H2D0, E_PACK0, E_ANCHOR0, E_SCAN0, E_VERIFY0, E_SORT0, E_EMIT0, E_END, E_D2H0, E_D2H1, E_COUNT };
 
 // device counter block (one 64-bit word each)
-enum Ctr { C_ERR, C_NANC, C_NCAND, C_NHITS, C_SUMM, C_SUMB, C_NSURV, C_COUNT };  // h_ctr has 2 spare words behind
+enum Ctr { C_ERR, C_NANC, C_NCAND, C_NHITS, C_SUMM, C_SUMB, C_NSURV, C_TILE_A, C_TILE_B, C_COUNT };  // h_ctr has 2 spare words behind
 
 }  // namespace
 
@@ -563,7 +563,7 @@ int ovl_overlaps_device(ovl_ctx* c, uint32_t min_length, uint64_t* n_rows_out) {
     if (n_rows_out) *n_rows_out = 0;
     if (M == 0) return OVL_OK;  // the reference segfaults here; we return no rows
     // strand-mirror halving needs entry e ^ 1 to be the other strand of entry e, for every e
-    bool mirror = c->opt_mirror && !c->collect && !c->opt_serial_verify && (M % 2 == 0);
+    bool mirror = c->opt_mirror && (M % 2 == 0);
     for (uint32_t e = 0; mirror && e < M; e += 2) mirror = !(c->flags[e] & 1) && (c->flags[e + 1] & 1);
     S.mirror = mirror ? 1u : 0u;
     ovl::MirrorRule mrule;
@@ -796,6 +796,7 @@ int ovl_overlaps_device(ovl_ctx* c, uint32_t min_length, uint64_t* n_rows_out) {
             V.hits = hits;
             V.counters = reinterpret_cast<unsigned long long*>(ctr + C_SUMM);
             V.collect = c->collect;
+            V.mirror = mrule;
             k4_verify_serial<<<(unsigned)blocks, 256, 0, st>>>(V);
             ++launches;
         } else {
@@ -809,6 +810,7 @@ int ovl_overlaps_device(ovl_ctx* c, uint32_t min_length, uint64_t* n_rows_out) {
             V.n_surv = reinterpret_cast<unsigned long long*>(ctr + C_NSURV);
             V.hits = hits;
             V.mirror = mrule;
+            V.tile_ctr = reinterpret_cast<unsigned long long*>(ctr + C_TILE_A);
             k4a_head<<<(unsigned)blocks, 256, 0, st>>>(V);
             k4b_tail<<<nsm * 8, 256, 0, st>>>(V);
             launches += 2;

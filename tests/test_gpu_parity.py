@@ -239,11 +239,22 @@ def test_oracle_port_config_shapes(ov, cid, factor):
     want, ost = port.oracle_overlaps(ebuf, eoff, sh.min_length)
     ov.clear()
     ov.set_collect_stats(True)
+    ov.set_option("mirror", 0)  # the SURVEY 8(d) accounting is defined on ALL canonical candidates
     ov.add_reads_bulk(buf, off, names)
-    got = sort_rows(ov.overlaps_arrays(sh.min_length))
-    st = ov.stats()
-    ov.set_collect_stats(False)
+    try:
+        got = sort_rows(ov.overlaps_arrays(sh.min_length))
+        st = ov.stats()
+        ov.set_option("mirror", 1)
+        got_m = sort_rows(ov.overlaps_arrays(sh.min_length))
+        st_m = ov.stats()
+    finally:
+        ov.set_option("mirror", 1)
+        ov.set_collect_stats(False)
     assert np.array_equal(got, sort_rows(want))
+    assert np.array_equal(got_m, sort_rows(want))
+    # mirror mode compares about half of the candidates / operand bytes
+    assert st_m["mirror"] == 1 and st_m["candidates"] < 0.6 * st["candidates"]
+    assert st_m["operand_bytes"] < 0.6 * st["operand_bytes"]
     assert st["rows"] == ost["rows"] and st["hits"] == ost["hits"]
     assert st["anchors"] == ost["anchors"]
     assert st["scan_positions"] == ost["positions"]
