@@ -6,13 +6,15 @@
 // (/root/reference/phasm/cli/assembler.py:39-40) followed by the byte copy into the
 // StringSet (/root/reference/src/overlapper.cpp:22-26).
 //
-// One thread packs one 16-base UNIT (one aligned 128-bit ASCII load -> one 32-bit word) of a
-// forward entry.  If the entry has a reverse-complement twin (flags bit0 of the next entry),
-// the same thread also writes one word of the twin: rc word j of a read of L = 16m + r bases
-// is the bit-reversed, complemented 32-bit window that starts 2r bits into forward word
-// m-j-1, so a thread needs its own word and its right neighbour's, which comes by warp
-// shuffle.  Warps are tiled with a one-unit overlap (lane 31 only supplies the neighbour
-// word), so the ASCII is read once (+3 %) and never re-read for the second strand.
+// A warp packs one TILE = 128 consecutive 16-base units (2048 bases) of ONE forward entry, so
+// all entry metadata is warp-uniform: four coalesced 128-bit ASCII loads per lane are in flight
+// before the first is packed (unit 32*i + lane), and every unit becomes one 32-bit word,
+// stored coalesced.  If the entry has a reverse-complement twin (flags bit0 of the next
+// entry) the same thread also writes one word of the twin: rc word j of a read of
+// L = 16m + r bases is the bit-reversed, complemented 32-bit window that starts 2r bits into
+// forward word m-j-1, so a thread needs its own word and its right neighbour's, which comes
+// by warp shuffle (the tile's last unit re-packs one halo unit).  The ASCII is read once and
+// never re-read for the second strand.  The tile -> entry map is written by K0.
 //
 // Roofline: HBM.  Algorithmic bytes per FORWARD base when both strands are added:
 // 1.0 (ASCII read once) + 0.5 (2 x 2 bit written).
@@ -25,6 +27,8 @@ namespace ovl {
 // {first granule, length} pair the scan / verify kernels read.
 __global__ void __launch_bounds__(256) k0_gran_entry(const uint32_t* __restrict__ gran0,
                                                      uint32_t* __restrict__ gran_ent,
+                                                     const uint32_t* __restrict__ tile0,
+                                                     uint32_t* __restrict__ tile_ent,
                                                      uint32_t e_begin, uint32_t e_end) {
     const uint32_t lane = threadIdx.x & 31;
     const uint32_t warp = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
@@ -32,6 +36,8 @@ __global__ void __launch_bounds__(256) k0_gran_entry(const uint32_t* __restrict_
     for (uint32_t e = e_begin + warp; e < e_end; e += nwarps) {
         const uint32_t g0 = gran0[e], g1 = gran0[e + 1];
         for (uint32_t g = g0 + lane; g < g1; g += 32) gran_ent[g] = e;
+        const uint32_t t0 = tile0[e], t1 = tile0[e + 1];
+        for (uint32_t t = t0 + lane; t < t1; t += 32) tile_ent[t] = e;
     }
 }
 
@@ -46,15 +52,35 @@ __device__ __forceinline__ uint32_t low_bytes_mask(int n) {  // n low bytes set,
     return n >= 4 ? 0xffffffffu : (n <= 0 ? 0u : ((1u << (8 * n)) - 1u));
 }
 
-// Four ASCII bytes (upper-case ACGT expected) -> 8 bits, byte i in bits [2i,2i+2).
-// `bad` accumulates a non-zero value if any byte is outside {A,C,G,T}.
-__device__ __forceinline__ uint32_t pack4(uint32_t w, uint32_t& bad) {
-    const uint32_t x = w ^ 0x41414141u;  // A->00 C->02 G->06 T->15
-    bad |= (x & 0xE8E8E8E8u) | ((x ^ (x >> 4)) & 0x01010101u) |
-           ((((x >> 2) & ~(x >> 1)) ^ (x >> 4)) & 0x01010101u);
-    uint32_t c = (w >> 1) & 0x03030303u;
-    c = c | (c >> 6) | (c >> 12) | (c >> 18);
-    return c & 0xffu;
+// Four ASCII bytes -> their 2-bit codes in the TOP byte of the result (base i in bits
+// [24+2i, 24+2i+2)); `bad` becomes non-zero if a byte is not one of upper-case A, C, G, T.
+// code = (byte >> 1) & 3 (A0 C1 T2 G3).  The multiply gathers the four 2-bit fields (disjoint
+// bit ranges, so no carries); the check rebuilds the expected letters from the codes with a
+// byte permute of "ACTG" and compares them with the input.
+__device__ __forceinline__ uint32_t pack4_top(uint32_t w, uint32_t& bad) {
+    const uint32_t c = (w >> 1) & 0x03030303u;
+    const uint32_t s = c | (c >> 4);                                  // byte0 = c0|c1<<4, byte2 = c2|c3<<4
+    const uint32_t sel = __byte_perm(s, 0, 0x4420);                   // c0 | c1<<4 | c2<<8 | c3<<12
+    bad |= __byte_perm(0x47544341u /* "ACTG" */, 0, sel) ^ w;
+    return c * 0x01041040u;
+}
+
+// 16 ASCII bytes (one uint4) -> one 32-bit packed word
+__device__ __forceinline__ uint32_t pack16(const uint4 v, uint32_t& bad) {
+    const uint32_t t0 = pack4_top(v.x, bad), t1 = pack4_top(v.y, bad);
+    const uint32_t t2 = pack4_top(v.z, bad), t3 = pack4_top(v.w, bad);
+    return __byte_perm(__byte_perm(t0, t1, 0x0073), __byte_perm(t2, t3, 0x0073), 0x5410);
+}
+
+// the same for a unit with only nvalid (1..15) bases inside its entry: the rest reads as 'A'
+__device__ __forceinline__ uint32_t pack16_partial(uint4 v, int nvalid, uint32_t& bad) {
+    uint32_t w[4] = {v.x, v.y, v.z, v.w};
+#pragma unroll
+    for (int i = 0; i < 4; ++i) {
+        const uint32_t m4 = low_bytes_mask(nvalid - 4 * i);
+        w[i] = (w[i] & m4) | (0x41414141u & ~m4);
+    }
+    return pack16(make_uint4(w[0], w[1], w[2], w[3]), bad);
 }
 
 __device__ __forceinline__ uint32_t reverse_groups2(uint32_t x) {
@@ -62,58 +88,81 @@ __device__ __forceinline__ uint32_t reverse_groups2(uint32_t x) {
     return ((r >> 1) & 0x55555555u) | ((r & 0x55555555u) << 1);
 }
 
-// K1.  Units [u_begin, u_end) are the 16-base units of the granules of the local entries
-// (4 per granule); warp w of the grid owns units u_begin + 31*w + [0, 31) and lane 31 only
-// computes the neighbour word.  err[0] is set to (entry index + 1) of some entry holding a
-// non-ACGT byte.
-__global__ void __launch_bounds__(256)
-k1_pack(const uint8_t* __restrict__ ascii, const uint64_t* __restrict__ src,
-        const uint2* __restrict__ ent, const uint8_t* __restrict__ flags,
-        const uint32_t* __restrict__ gran_ent, uint32_t* __restrict__ packed32, uint32_t M,
-        uint64_t u_begin, uint64_t u_end, uint32_t* __restrict__ err) {
+constexpr uint32_t PACK_TILE_UNITS = 128;  // 16-base units per warp tile
+
+struct PackParams {
+    const uint8_t* ascii;
+    const uint64_t* src;       // [M] byte offset of the entry's record
+    const uint2* ent;          // [M] {gran0, len}
+    const uint8_t* flags;      // [M]
+    const uint32_t* tile0;     // [M+1] first tile of every entry (0 tiles for twins / remote entries)
+    const uint32_t* tile_ent;  // [n_tiles]
+    uint32_t* packed32;
+    uint32_t M;
+    uint32_t t_begin, t_end;   // tiles of the local entries
+    uint32_t* err;             // set to (entry index + 1) of some entry holding a non-ACGT byte
+};
+
+// K1: one warp per tile (grid-stride).
+__global__ void __launch_bounds__(256) k1_pack(const PackParams P) {
     const uint32_t lane = threadIdx.x & 31;
-    const uint64_t warp = ((uint64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
-    const uint64_t nwarps = ((uint64_t)gridDim.x * blockDim.x) >> 5;
-    const uint64_t n_tiles = (u_end - u_begin + 30) / 31;
-    for (uint64_t tile = warp; tile < n_tiles; tile += nwarps) {
-        const uint64_t t = u_begin + tile * 31 + lane;
-        uint32_t W = 0, e = 0, u = 0, L = 0, g0 = 0;
-        bool fwd = false;
-        if (t < u_end) {
-            const uint32_t g = (uint32_t)(t >> 2);
-            e = __ldg(gran_ent + g);
-            fwd = !(__ldg(flags + e) & 1);
-            if (fwd) {
-                const uint2 m = __ldg(ent + e);
-                g0 = m.x;
-                L = m.y;
-                u = (uint32_t)(t - 4ull * g0);
-                const int nvalid = (int)L - 16 * (int)u;  // may be <= 0 (padding unit)
-                if (nvalid > 0) {
-                    const uint4 v = ldg_stream(reinterpret_cast<const uint4*>(ascii + __ldg(src + e) + 16ull * u));
-                    const uint32_t w[4] = {v.x, v.y, v.z, v.w};
-                    uint32_t bad = 0;
-#pragma unroll
-                    for (int i = 0; i < 4; ++i) {
-                        // bytes outside the entry are replaced by 'A' (packs to 0, validates clean)
-                        const uint32_t m4 = low_bytes_mask(nvalid - 4 * i);
-                        W |= pack4((w[i] & m4) | (0x41414141u & ~m4), bad) << (8 * i);
-                    }
-                    if (bad) atomicMax(err, e + 1);
-                }
-            }
-        }
-        const uint32_t Wn_s = __shfl_down_sync(FULL, W, 1);
-        if (!fwd || lane == 31) continue;
-        packed32[t] = W;
-        if (e + 1 >= M || !(__ldg(flags + e + 1) & 1)) continue;  // no reverse-complement twin
+    const uint32_t warp = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+    const uint32_t nwarps = (gridDim.x * blockDim.x) >> 5;
+    for (uint32_t tile = P.t_begin + warp; tile < P.t_end; tile += nwarps) {
+        const uint32_t e = __ldg(P.tile_ent + tile);
+        const uint2 m_e = __ldg(P.ent + e);
+        const uint32_t L = m_e.y;
         const uint32_t units = 4u * ((L + 63u) >> 6);
-        const uint32_t Wn = (u + 1 < units) ? Wn_s : 0u;        // next unit of the SAME entry
+        const uint32_t u0 = (tile - __ldg(P.tile0 + e)) * PACK_TILE_UNITS;
+        const uint4* in = reinterpret_cast<const uint4*>(P.ascii + __ldg(P.src + e));
+        uint32_t* out = P.packed32 + 4ull * m_e.x;
+        const bool twin = e + 1 < P.M && (__ldg(P.flags + e + 1) & 1);
+
+        // ---- load: 4 (+1 halo) independent 128-bit loads per lane ----
+        uint4 v[4];
+#pragma unroll
+        for (int i = 0; i < 4; ++i) {
+            const uint32_t u = u0 + 32u * i + lane;
+            v[i] = make_uint4(0x41414141u, 0x41414141u, 0x41414141u, 0x41414141u);
+            if (16u * u < L) v[i] = ldg_stream(in + u);
+        }
+        const uint32_t uh = u0 + PACK_TILE_UNITS;  // halo: first unit of the next tile
+        uint4 vh = make_uint4(0x41414141u, 0x41414141u, 0x41414141u, 0x41414141u);
+        const bool need_halo = twin && lane == 31 && 16u * uh < L;
+        if (need_halo) vh = ldg_stream(in + uh);
+
+        // ---- pack ----
+        uint32_t W[4], bad = 0;
+#pragma unroll
+        for (int i = 0; i < 4; ++i) {
+            const uint32_t u = u0 + 32u * i + lane;
+            const int nvalid = (int)L - 16 * (int)u;
+            W[i] = nvalid >= 16 ? pack16(v[i], bad) : (nvalid > 0 ? pack16_partial(v[i], nvalid, bad) : 0u);
+            if (u < units) out[u] = W[i];
+        }
+        uint32_t Wh = 0;
+        if (need_halo) {
+            const int nvalid = (int)L - 16 * (int)uh;
+            Wh = nvalid >= 16 ? pack16(vh, bad) : pack16_partial(vh, nvalid, bad);
+        }
+        if (bad) atomicMax(P.err, e + 1);
+        if (!twin) continue;  // warp-uniform
+
+        // ---- reverse-complement twin ----
         const uint32_t m = L >> 4, r = L & 15u;
-        uint32_t* rc = packed32 + 4ull * __ldg(ent + e + 1).x;
-        if (u < m) rc[m - u - 1] = reverse_groups2(__funnelshift_r(W, Wn, 2 * r)) ^ 0xAAAAAAAAu;
-        if (u == 0 && r) rc[m] = (reverse_groups2(W << (32 - 2 * r)) ^ 0xAAAAAAAAu) & ((1u << (2 * r)) - 1u);
-        if (u >= m + (r ? 1u : 0u)) rc[u] = 0u;
+        uint32_t* rc = P.packed32 + 4ull * __ldg(P.ent + e + 1).x;
+#pragma unroll
+        for (int i = 0; i < 4; ++i) {
+            const uint32_t u = u0 + 32u * i + lane;
+            // right neighbour: next lane of this round, lane 0 of the next round, or the halo
+            uint32_t Wn = __shfl_down_sync(FULL, W[i], 1);
+            const uint32_t first_next = __shfl_sync(FULL, i < 3 ? W[i < 3 ? i + 1 : 3] : 0u, 0);
+            if (lane == 31) Wn = i < 3 ? first_next : Wh;
+            if (u >= units) continue;
+            if (u < m) rc[m - u - 1] = reverse_groups2(__funnelshift_r(W[i], Wn, 2 * r)) ^ 0xAAAAAAAAu;
+            if (u == 0 && r) rc[m] = (reverse_groups2(W[i] << (32 - 2 * r)) ^ 0xAAAAAAAAu) & ((1u << (2 * r)) - 1u);
+            if (u >= m + (r ? 1u : 0u)) rc[u] = 0u;
+        }
     }
 }
 

@@ -11,7 +11,7 @@
 //   k      = min(max(l,1), 32)
 //   stride = largest power of two <= min(64, l - k + 1)
 //
-// The table is open addressing on the packed k-mer with a linked list of anchor ids
+// The table is open addressing on a 32-bit fingerprint of the k-mer with a linked list of anchor ids
 // (b * stride + delta) per key: one kernel, no sort.  Which anchor ends up where in a list
 // depends on thread timing, but the candidates are radix-sorted before they are verified, so
 // the output is deterministic.
@@ -29,7 +29,7 @@ struct AnchorParams {
     uint32_t l;
     int k;
     int stride_log2;
-    Slot* table;            // (1 << tbits) + 1 slots, all {EMPTY_KEY, NIL, 0}
+    Slot* table;            // 1 << tbits slots, all EMPTY_SLOT
     int tbits;
     uint32_t* next;         // [M << stride_log2]
     uint32_t* bitmap;       // sparse path: 1 << bm_bits bits   (dense path: bloom words)
@@ -51,20 +51,26 @@ __global__ void __launch_bounds__(256) k2_insert(const AnchorParams P) {
             const uint64_t* w = P.packed64 + 2ull * m.x + (delta >> 5);
             const uint64_t x = kmer_at(w[0], w[1], delta & 31) & kmer_mask(P.k);
             const uint64_t h = mix64(x);
-            uint32_t s;
-            if (x == EMPTY_KEY) {
-                s = 1u << P.tbits;  // reserved slot
-                P.table[s].key = x;
-            } else {
-                const uint32_t tmask = (1u << P.tbits) - 1u;
-                s = slot_of(h, P.tbits);
-                for (;;) {
-                    const unsigned long long old = atomicCAS(&P.table[s].key, EMPTY_KEY, x);
-                    if (old == EMPTY_KEY || old == x) break;
-                    s = (s + 1) & tmask;
+            const uint32_t fp = (uint32_t)h;
+            const uint32_t tmask = (1u << P.tbits) - 1u;
+            uint32_t s = slot_of(h, P.tbits);
+            uint32_t prev_head;
+            for (;;) {
+                unsigned long long v = *reinterpret_cast<volatile unsigned long long*>(P.table + s);
+                if (v == EMPTY_SLOT) {
+                    v = atomicCAS(P.table + s, EMPTY_SLOT, ((unsigned long long)fp << 32) | (uint32_t)idx);
+                    if (v == EMPTY_SLOT) {  // claimed the slot: this anchor is the list's tail
+                        prev_head = NIL;
+                        break;
+                    }
                 }
+                if ((uint32_t)(v >> 32) == fp) {  // the key's slot: push on its list
+                    prev_head = atomicExch(reinterpret_cast<uint32_t*>(P.table + s), (uint32_t)idx);
+                    break;
+                }
+                s = (s + 1) & tmask;
             }
-            P.next[idx] = atomicExch(&P.table[s].head, (uint32_t)idx);
+            P.next[idx] = prev_head;
             if (P.dense) {
                 const uint32_t h32 = kmer_hash(x);
                 atomicOr(&P.bitmap[filter_word(h32, P.bm_bits)], filter_bits(h32));
@@ -79,16 +85,14 @@ __global__ void __launch_bounds__(256) k2_insert(const AnchorParams P) {
 }
 
 // Table lookup shared by the scan kernels: head of the anchor list of k-mer x, NIL if absent.
-__device__ __forceinline__ uint32_t table_find(const Slot* __restrict__ table, int tbits, uint64_t x,
-                                               uint64_t h) {
-    if (x == EMPTY_KEY) return table[1u << tbits].head;
+__device__ __forceinline__ uint32_t table_find(const Slot* __restrict__ table, int tbits, uint64_t h) {
     const uint32_t tmask = (1u << tbits) - 1u;
+    const uint32_t fp = (uint32_t)h;
     uint32_t s = slot_of(h, tbits);
     for (;;) {
-        const uint4 v = *reinterpret_cast<const uint4*>(table + s);
-        const uint64_t key = (uint64_t)v.x | ((uint64_t)v.y << 32);
-        if (key == x) return v.z;
-        if (key == EMPTY_KEY) return NIL;
+        const unsigned long long v = __ldg(table + s);
+        if (v == EMPTY_SLOT) return NIL;
+        if ((uint32_t)(v >> 32) == fp) return (uint32_t)v;
         s = (s + 1) & tmask;
     }
 }

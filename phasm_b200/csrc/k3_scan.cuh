@@ -85,7 +85,7 @@ __global__ void __launch_bounds__(256) k3_probe(const ScanParams P) {
                 const uint64_t x = (off < 32 ? kmer_at(w0, w1, off) : kmer_at(w1, w2, off - 32)) & kmask;
                 const uint64_t h = mix64(x);
                 const uint32_t bit = bitmap_bit(h, P.bm_bits);
-                if ((__ldg(P.filter + (bit >> 5)) >> (bit & 31)) & 1u) node = table_find(P.table, P.tbits, x, h);
+                if ((__ldg(P.filter + (bit >> 5)) >> (bit & 31)) & 1u) node = table_find(P.table, P.tbits, h);
             }
             while (__any_sync(FULL, node != NIL)) {
                 bool have = false;
@@ -178,7 +178,7 @@ __global__ void __launch_bounds__(1024, 1) k3_scan(const ScanParams P) {
                 hits &= hits - 1;
                 p = pos0 + j;
                 const uint64_t x = (j < 32 ? kmer_at(w0, w1, j) : kmer_at(w1, w2, j - 32)) & kmask;
-                node = table_find(P.table, P.tbits, x, mix64(x));
+                node = table_find(P.table, P.tbits, mix64(x));
             }
             while (__any_sync(FULL, node != NIL)) {
                 bool have = false;

@@ -80,12 +80,13 @@ struct ovl_ctx {
     std::vector<char> id_blob;
     std::vector<uint64_t> id_off{0};
     std::vector<uint32_t> gran0;
+    std::vector<uint32_t> tile0;  // [M+1] first K1 tile of every entry
     uint64_t bases = 0, max_len = 0;
     bool uploaded = false;
     uint32_t e_lo = 0, e_hi = 0;  // entries whose bases are local (contiguous)
 
     // ---- device ----
-    DevBuf d_ascii, d_src, d_len, d_flags, d_gran0, d_gran_ent, d_ent, d_packed;
+    DevBuf d_ascii, d_src, d_len, d_flags, d_gran0, d_gran_ent, d_ent, d_packed, d_tile0, d_tile_ent;
     DevBuf d_table, d_filter, d_next, d_ctr, d_tmp;
     DevBuf d_cand, d_cand2, d_cnt, d_offs, d_rows, d_cnts;
     uint64_t* h_ctr = nullptr;  // pinned mirror of d_ctr
@@ -299,7 +300,8 @@ void ovl_destroy(ovl_ctx* c) {
     if (c->comm) nccl_dyn::api().CommDestroy(c->comm);
     DevBuf* bufs[] = {&c->d_ascii, &c->d_src, &c->d_len, &c->d_flags, &c->d_gran0, &c->d_gran_ent,
                       &c->d_ent, &c->d_packed, &c->d_table, &c->d_filter, &c->d_next, &c->d_ctr,
-                      &c->d_tmp, &c->d_cand, &c->d_cand2, &c->d_cnt, &c->d_offs, &c->d_rows, &c->d_cnts};
+                      &c->d_tmp, &c->d_cand, &c->d_cand2, &c->d_cnt, &c->d_offs, &c->d_rows, &c->d_cnts,
+                      &c->d_tile0, &c->d_tile_ent};
     for (DevBuf* b : bufs)
         if (b->p) cudaFree(b->p);
     if (c->ascii.p) cudaFreeHost(c->ascii.p);
@@ -409,6 +411,7 @@ int ovl_clear(ovl_ctx* c) {
     c->id_blob.clear();
     c->id_off.assign(1, 0);
     c->gran0.clear();
+    c->tile0.clear();
     c->bases = c->max_len = 0;
     c->uploaded = false;
     c->n_rows = 0;
@@ -493,20 +496,28 @@ int ovl_upload(ovl_ctx* c) {
     uint32_t lo = (uint32_t)M, hi = 0;
     try {
         c->gran0.resize(M + 1);
+        c->tile0.resize(M + 1);
     } catch (const std::bad_alloc&) {
         return fail(c, OVL_E_NOMEM, "out of host memory");
     }
-    uint64_t g = 0;
+    uint64_t g = 0, nt = 0;
     for (size_t e = 0; e < M; ++e) {
         c->gran0[e] = (uint32_t)g;
-        g += (c->len[e] + 63u) / 64u;
+        c->tile0[e] = (uint32_t)nt;
+        const uint64_t ge = (c->len[e] + 63u) / 64u;
+        g += ge;
+        // K1 tiles: forward local entries only (a twin is written by its forward entry's tiles)
+        if (c->src[e] != NO_SRC && !(c->flags[e] & 1)) nt += (4 * ge + ovl::PACK_TILE_UNITS - 1) / ovl::PACK_TILE_UNITS;
         if (c->src[e] != NO_SRC) {
             if (e < lo) lo = (uint32_t)e;
             hi = (uint32_t)e + 1;
         }
     }
     if (g >= 0xffffffffull) return fail(c, OVL_E_LIMIT, "more than 2^32 granules (%llu)", (unsigned long long)g);
-    if (M) c->gran0[M] = (uint32_t)g;
+    if (M) {
+        c->gran0[M] = (uint32_t)g;
+        c->tile0[M] = (uint32_t)nt;
+    }
     if (lo > hi) lo = hi = 0;
     for (uint32_t e = lo; e < hi; ++e)
         if (c->src[e] == NO_SRC) return fail(c, OVL_E_ARG, "local entries must be one contiguous range (entry %u is remote)", e);
@@ -525,6 +536,9 @@ int ovl_upload(ovl_ctx* c) {
         OVL_TRY(dev_ensure(c, c->d_gran_ent, (g + 1) * 4));
         OVL_TRY(dev_ensure(c, c->d_ent, M * 8));
         OVL_TRY(dev_ensure(c, c->d_packed, (g + 2) * 16));
+        OVL_TRY(dev_ensure(c, c->d_tile0, (M + 1) * 4));
+        OVL_TRY(dev_ensure(c, c->d_tile_ent, (nt + 1) * 4));
+        CK(cudaMemcpyAsync(c->d_tile0.p, c->tile0.data(), (M + 1) * 4, cudaMemcpyHostToDevice, c->st));
         if (c->ascii.p) CK(cudaMemcpyAsync(c->d_ascii.p, c->ascii.p, ab, cudaMemcpyHostToDevice, c->st));
         CK(cudaMemcpyAsync(c->d_src.p, c->src.data(), M * 8, cudaMemcpyHostToDevice, c->st));
         CK(cudaMemcpyAsync(c->d_len.p, c->len.data(), M * 4, cudaMemcpyHostToDevice, c->st));
@@ -611,17 +625,26 @@ int ovl_overlaps_device(ovl_ctx* c, uint32_t min_length, uint64_t* n_rows_out) {
     k0_ent_table<<<(M + 255) / 256, 256, 0, st>>>(c->d_gran0.as<uint32_t>(), c->d_len.as<uint32_t>(), c->d_ent.as<uint2>(), M);
     ++launches;
     if (c->e_hi > c->e_lo) {
-        k0_gran_entry<<<nsm * 4, 256, 0, st>>>(c->d_gran0.as<uint32_t>(), c->d_gran_ent.as<uint32_t>(), c->e_lo, c->e_hi);
+        k0_gran_entry<<<nsm * 4, 256, 0, st>>>(c->d_gran0.as<uint32_t>(), c->d_gran_ent.as<uint32_t>(),
+                                               c->d_tile0.as<uint32_t>(), c->d_tile_ent.as<uint32_t>(), c->e_lo, c->e_hi);
         ++launches;
-        if (g_hi > g_lo) {
-            const uint64_t u0 = 4ull * g_lo, u1 = 4ull * g_hi;
-            const uint64_t tiles = (u1 - u0 + 30) / 31;
-            uint64_t blocks = (tiles + 7) / 8;
-            if (blocks > (uint64_t)nsm * 32) blocks = (uint64_t)nsm * 32;
-            k1_pack<<<(unsigned)blocks, 256, 0, st>>>(c->d_ascii.as<uint8_t>(), c->d_src.as<uint64_t>(), c->d_ent.as<uint2>(),
-                                                      c->d_flags.as<uint8_t>(), c->d_gran_ent.as<uint32_t>(),
-                                                      c->d_packed.as<uint32_t>(), M, u0, u1,
-                                                      reinterpret_cast<uint32_t*>(ctr + C_ERR));
+        const uint32_t t_lo = c->tile0[c->e_lo], t_hi = c->tile0[c->e_hi];
+        if (t_hi > t_lo) {
+            PackParams K;
+            K.ascii = c->d_ascii.as<uint8_t>();
+            K.src = c->d_src.as<uint64_t>();
+            K.ent = c->d_ent.as<uint2>();
+            K.flags = c->d_flags.as<uint8_t>();
+            K.tile0 = c->d_tile0.as<uint32_t>();
+            K.tile_ent = c->d_tile_ent.as<uint32_t>();
+            K.packed32 = c->d_packed.as<uint32_t>();
+            K.M = M;
+            K.t_begin = t_lo;
+            K.t_end = t_hi;
+            K.err = reinterpret_cast<uint32_t*>(ctr + C_ERR);
+            uint32_t blocks = (t_hi - t_lo + 7) / 8;
+            if (blocks > (uint32_t)nsm * 16) blocks = (uint32_t)nsm * 16;
+            k1_pack<<<blocks, 256, 0, st>>>(K);
             ++launches;
         }
     }
@@ -692,11 +715,11 @@ int ovl_overlaps_device(ovl_ctx* c, uint32_t min_length, uint64_t* n_rows_out) {
         if (bm_bits > 31) bm_bits = 31;
     }
     const size_t filter_bytes = dense ? (4ull << bm_bits) : ((1ull << bm_bits) / 8);
-    const size_t table_bytes = sizeof(Slot) * ((1ull << tbits) + 1);
+    const size_t table_bytes = sizeof(Slot) * (1ull << tbits);
     OVL_TRY(dev_ensure(c, c->d_table, table_bytes));
     OVL_TRY(dev_ensure(c, c->d_filter, filter_bytes));
     OVL_TRY(dev_ensure(c, c->d_next, ((uint64_t)M << slog) * 4));
-    CK(cudaMemsetAsync(c->d_table.p, 0xff, table_bytes, st));  // {EMPTY_KEY, NIL, ~0}
+    CK(cudaMemsetAsync(c->d_table.p, 0xff, table_bytes, st));  // EMPTY_SLOT
     CK(cudaMemsetAsync(c->d_filter.p, 0, filter_bytes, st));
     {
         AnchorParams A;

@@ -33,14 +33,14 @@ namespace ovl {
 constexpr int GRAN_BASES = 64;
 constexpr unsigned FULL = 0xffffffffu;
 
-// Anchor hash-table slot.  key == EMPTY_KEY marks a free slot; the k-mer whose packed value IS
-// EMPTY_KEY (32 x 'G') lives in the reserved slot behind the table.  head starts a linked list
-// (through `next`) of anchor ids  b * stride + delta.
-struct __align__(16) Slot {
-    unsigned long long key;
-    uint32_t head, pad;
-};
-constexpr unsigned long long EMPTY_KEY = ~0ull;
+// Anchor hash-table slot: one 64-bit word {fingerprint (high 32) | head (low 32)}.  The
+// fingerprint is the low half of the k-mer's 64-bit hash (the slot index comes from the high
+// bits), head starts a linked list (through `next`) of anchor ids  b * stride + delta.  Two
+// different k-mers that collide on slot AND fingerprint (~2^-32 per probe) share a list: the scan
+// then emits a few false candidates, which the verifier rejects -- the table only has to return
+// a superset.  8-byte slots keep the whole table L2-resident.
+typedef unsigned long long Slot;
+constexpr unsigned long long EMPTY_SLOT = ~0ull;
 constexpr uint32_t NIL = 0xffffffffu;
 
 struct Row {
