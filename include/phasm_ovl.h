@@ -67,6 +67,8 @@ typedef struct {
     uint32_t retries;          /* scan re-runs after a candidate-buffer overflow          */
     uint32_t mirror;           /* 1: strand-mirror halving was on (every entry has its twin) */
     uint64_t verified;         /* candidates actually compared by the verifier            */
+    uint64_t hits_sent;        /* multi-GPU mirror mode: hit keys shipped to other ranks  */
+    uint64_t hits_received;    /* ... and received from them                              */
     float ms_h2d, ms_pack, ms_anchor, ms_scan, ms_sort, ms_verify, ms_emit, ms_d2h;
     float ms_device;           /* pack..emit: ASCII resident in HBM -> rows resident      */
     float ms_total;            /* h2d..d2h                                                */

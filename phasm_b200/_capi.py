@@ -29,7 +29,7 @@ class OvlStats(Structure):
                   "scan_positions")] +
                 [(n, c_uint32) for n in ("kmer", "anchor_stride", "launches", "lib_launches",
                                          "retries", "mirror")] +
-                [("verified", c_uint64)] +
+                [("verified", c_uint64), ("hits_sent", c_uint64), ("hits_received", c_uint64)] +
                 [(n, c_float) for n in ("ms_h2d", "ms_pack", "ms_anchor", "ms_scan", "ms_sort",
                                         "ms_verify", "ms_emit", "ms_d2h", "ms_device", "ms_total")])
 

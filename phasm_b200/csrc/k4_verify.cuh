@@ -84,7 +84,7 @@ __device__ __forceinline__ void hit_keys(const KeyFmt& fmt, const uint2* __restr
     const uint32_t a = fmt.a(key), b = fmt.b(key), p = fmt.p(key);
     const uint32_t la = __ldg(ent + a).y, lb = __ldg(ent + b).y;
     const uint32_t bt = b ^ 1u, at = a ^ 1u;
-    if ((fl & HIT_SP) && bt >= R.own_lo && bt < R.own_hi && a < bt)
+    if ((fl & HIT_SP) && a != bt)  // (fl has SP only if this candidate is the one that compares)
         out[1] = fmt.make(bt, at, lb - (la - p)) | HIT_SP;
     if (fl & HIT_CONT) out[2] = fmt.make(at, bt, la - p - lb) | HIT_CONT;
 }
@@ -203,12 +203,12 @@ constexpr int HEAD_UNROLL = 4;
 //   CONT a[p:p+|b|] == b             <=>  a'[|a|-p-|b| : |a|-p] == b'    key (a', b', |a|-p-|b|)
 //
 // Both maps are involutions on (key, type) items, so exactly one item of every twin pair is
-// compared (SP: the one with a <= b'; CONT: the one with a forward) and, if it matches, BOTH
+// compared (SP: picked by the swap-symmetric rule sp_self(); CONT: the one with a forward) and, if it matches, BOTH
 // keys are appended to the hit list.  The scan finds every true hit on its own, so a true hit
 // whose item is not the canonical one is always produced by its canonical twin; a false
 // candidate's twin is false too.  Half of the operand bytes are never read.
-// Multi-GPU: a rank only emits rows of its own A range; the SP twin is used only when b' is
-// local as well (otherwise both ranks compare their own candidate), the CONT twin always is.
+// Multi-GPU: the twin's key may belong to another rank's A range; k6_exchange.cuh ships every
+// hit key to the rank that owns its A entry before the sort.
 struct Verify2Params {
     const uint64_t* keys;              // candidate keys (flags clear), any order
     uint64_t n;

@@ -32,6 +32,7 @@
 #include "k3_scan.cuh"
 #include "k4_verify.cuh"
 #include "k5_emit.cuh"
+#include "k6_exchange.cuh"
 #include "nccl_dyn.h"
 
 static_assert(sizeof(ovl_row) == sizeof(ovl::Row), "row layouts must agree");
@@ -86,7 +87,7 @@ struct ovl_ctx {
     uint32_t e_lo = 0, e_hi = 0;  // entries whose bases are local (contiguous)
 
     // ---- device ----
-    DevBuf d_ascii, d_src, d_len, d_flags, d_gran0, d_gran_ent, d_ent, d_packed, d_tile0, d_tile_ent;
+    DevBuf d_ascii, d_src, d_len, d_flags, d_gran0, d_gran_ent, d_ent, d_packed, d_tile0, d_tile_ent, d_xchg;
     DevBuf d_table, d_filter, d_next, d_ctr, d_tmp;
     DevBuf d_cand, d_cand2, d_cnt, d_offs, d_rows, d_cnts;
     uint64_t* h_ctr = nullptr;  // pinned mirror of d_ctr
@@ -238,6 +239,71 @@ int read_ctr(ovl_ctx* c) {
     return OVL_OK;
 }
 
+// Multi-GPU mirror mode: partition the n_hits keys in d_cand2 by owner rank, ship every run to
+// its owner (grouped ncclSend/ncclRecv), leave this rank's keys (own + received, unsorted) in
+// d_cand2 and their number in *n_hits.  Collective: every rank must call it.
+int exchange_hits(ovl_ctx* c, const ovl::KeyFmt& fmt, uint64_t* n_hits, uint32_t* launches, uint32_t* lib) {
+    using namespace ovl;
+    (void)lib;
+    auto& N = nccl_dyn::api();
+    const int R = c->nranks, me = c->rank;
+    if (R > MAX_RANKS) return fail(c, OVL_E_LIMIT, "more than %d ranks", MAX_RANKS);
+    if ((int)c->rank_e.size() != R + 1) return fail(c, OVL_E_ARG, "call ovl_comm_sync_ranges before ovl_overlaps_device");
+    cudaStream_t st = c->st;
+    RankMap map;
+    map.n = R;
+    for (int r = 0; r <= R; ++r) map.e[r] = c->rank_e[r];
+    const uint64_t n = *n_hits;
+    // device scratch: counts[R] | cursor[R] | matrix[R*R]
+    OVL_TRY(dev_ensure(c, c->d_xchg, 8ull * (2 * R + (size_t)R * R), false));
+    unsigned long long* d_counts = c->d_xchg.as<unsigned long long>();
+    unsigned long long* d_cursor = d_counts + R;
+    unsigned long long* d_matrix = d_cursor + R;
+    CK(cudaMemsetAsync(d_counts, 0, 16ull * R, st));
+    if (n > c->cand_cap) {  // partition output (the candidate buffer is free after the verifier)
+        OVL_TRY(dev_ensure(c, c->d_cand, n * 8, false));
+        c->cand_cap = c->d_cand.cap / 8;
+    }
+    if (n) {
+        unsigned blocks = (unsigned)((n + 255) / 256);
+        if (blocks > (unsigned)c->n_sm * 8) blocks = (unsigned)c->n_sm * 8;
+        k6_count<<<blocks, 256, 0, st>>>(c->d_cand2.as<uint64_t>(), n, fmt, map, d_counts);
+        k6_scatter<<<blocks, 256, 0, st>>>(c->d_cand2.as<uint64_t>(), n, fmt, map, d_counts, d_cursor, c->d_cand.as<uint64_t>());
+        *launches += 2;
+        CK(cudaGetLastError());
+    }
+    CKN(N.AllGather(d_counts, d_matrix, (size_t)R, ncclUint64, c->comm, st));
+    std::vector<unsigned long long> mat((size_t)R * R);
+    CK(cudaMemcpyAsync(mat.data(), d_matrix, 8ull * R * R, cudaMemcpyDeviceToHost, st));
+    CK(cudaStreamSynchronize(st));
+    // mat[s*R + d] = keys rank s holds for rank d
+    uint64_t total = 0;
+    std::vector<uint64_t> soff(R + 1, 0), roff(R + 1, 0);
+    for (int r = 0; r < R; ++r) {
+        soff[r + 1] = soff[r] + mat[(size_t)me * R + r];
+        roff[r + 1] = roff[r] + mat[(size_t)r * R + me];
+    }
+    total = roff[R];
+    if (soff[R] != n) return fail(c, OVL_E_NCCL, "hit exchange: partition counted %llu of %llu keys", (unsigned long long)soff[R], (unsigned long long)n);
+    OVL_TRY(dev_ensure(c, c->d_cand2, (total ? total : 1) * 8));  // old contents live in d_cand now
+    uint64_t* src = c->d_cand.as<uint64_t>();
+    uint64_t* dst = c->d_cand2.as<uint64_t>();
+    const uint64_t own = mat[(size_t)me * R + me];
+    if (own) CK(cudaMemcpyAsync(dst + roff[me], src + soff[me], own * 8, cudaMemcpyDeviceToDevice, st));
+    CKN(N.GroupStart());
+    for (int r = 0; r < R; ++r) {
+        if (r == me) continue;
+        const uint64_t ns = mat[(size_t)me * R + r], nr = mat[(size_t)r * R + me];
+        if (ns) CKN(N.Send(src + soff[r], ns, ncclUint64, r, c->comm, st));
+        if (nr) CKN(N.Recv(dst + roff[r], nr, ncclUint64, r, c->comm, st));
+    }
+    CKN(N.GroupEnd());
+    c->stats.hits_sent = n - own;
+    c->stats.hits_received = total - own;
+    *n_hits = total;
+    return OVL_OK;
+}
+
 }  // namespace
 
 // =========================================================================================
@@ -301,7 +367,7 @@ void ovl_destroy(ovl_ctx* c) {
     DevBuf* bufs[] = {&c->d_ascii, &c->d_src, &c->d_len, &c->d_flags, &c->d_gran0, &c->d_gran_ent,
                       &c->d_ent, &c->d_packed, &c->d_table, &c->d_filter, &c->d_next, &c->d_ctr,
                       &c->d_tmp, &c->d_cand, &c->d_cand2, &c->d_cnt, &c->d_offs, &c->d_rows, &c->d_cnts,
-                      &c->d_tile0, &c->d_tile_ent};
+                      &c->d_tile0, &c->d_tile_ent, &c->d_xchg};
     for (DevBuf* b : bufs)
         if (b->p) cudaFree(b->p);
     if (c->ascii.p) cudaFreeHost(c->ascii.p);
@@ -582,8 +648,6 @@ int ovl_overlaps_device(ovl_ctx* c, uint32_t min_length, uint64_t* n_rows_out) {
     S.mirror = mirror ? 1u : 0u;
     ovl::MirrorRule mrule;
     mrule.on = mirror ? 1 : 0;
-    mrule.own_lo = c->e_lo;
-    mrule.own_hi = c->e_hi;
 
     const uint32_t G = c->gran0[M];
     S.granules = G;
@@ -696,7 +760,12 @@ int ovl_overlaps_device(ovl_ctx* c, uint32_t min_length, uint64_t* n_rows_out) {
         stage_times();
         return OVL_OK;
     };
-    if (n_anc == 0 || g_hi == g_lo) return finish_from(E_SCAN0);
+    if (n_anc == 0) return finish_from(E_SCAN0);  // same decision on every rank
+    // multi-GPU + mirror: hits are exchanged between ranks, so a rank without own work must
+    // still walk through the collective
+    const bool xchg = mirror && c->nranks > 1;
+    const bool have_a = g_hi > g_lo;
+    if (!have_a && !xchg) return finish_from(E_SCAN0);
 
     // ---- K2: anchor table ---------------------------------------------------------------------
     const uint64_t n_keys = n_anc << slog;
@@ -714,95 +783,101 @@ int ovl_overlaps_device(ovl_ctx* c, uint32_t min_length, uint64_t* n_rows_out) {
         if (bm_bits < 15) bm_bits = 15;
         if (bm_bits > 31) bm_bits = 31;
     }
-    const size_t filter_bytes = dense ? (4ull << bm_bits) : ((1ull << bm_bits) / 8);
-    const size_t table_bytes = sizeof(Slot) * (1ull << tbits);
-    OVL_TRY(dev_ensure(c, c->d_table, table_bytes));
-    OVL_TRY(dev_ensure(c, c->d_filter, filter_bytes));
-    OVL_TRY(dev_ensure(c, c->d_next, ((uint64_t)M << slog) * 4));
-    CK(cudaMemsetAsync(c->d_table.p, 0xff, table_bytes, st));  // EMPTY_SLOT
-    CK(cudaMemsetAsync(c->d_filter.p, 0, filter_bytes, st));
-    {
-        AnchorParams A;
-        A.packed64 = reinterpret_cast<const uint64_t*>(c->d_packed.p);
-        A.ent = c->d_ent.as<uint2>();
-        A.M = M;
-        A.l = l;
-        A.k = k;
-        A.stride_log2 = slog;
-        A.table = c->d_table.as<Slot>();
-        A.tbits = tbits;
-        A.next = c->d_next.as<uint32_t>();
-        A.bitmap = c->d_filter.as<uint32_t>();
-        A.bm_bits = bm_bits;
-        A.dense = dense ? 1 : 0;
-        A.n_anchors = reinterpret_cast<unsigned long long*>(ctr + C_NANC);
-        const uint64_t nthreads = (uint64_t)M << slog;
-        k2_insert<<<(unsigned)((nthreads + 255) / 256), 256, 0, st>>>(A);
-        ++launches;
-        CK(cudaGetLastError());
-    }
-    CK(cudaEventRecord(c->ev[E_SCAN0], st));
-
-    // ---- K3: scan (re-run once with the exact size if the candidate buffer was too small) --
-    if (c->cand_cap == 0) {
-        uint64_t cap = 96ull * (c->e_hi - c->e_lo);
-        if (cap < (1ull << 20)) cap = 1ull << 20;
-        OVL_TRY(dev_ensure(c, c->d_cand, cap * 8, false));
-        c->cand_cap = c->d_cand.cap / 8;
-    }
     uint64_t n_cand = 0;
-    for (int attempt = 0;; ++attempt) {
-        ScanParams P;
-        P.packed = c->d_packed.as<uint4>();
-        P.gran_ent = c->d_gran_ent.as<uint32_t>();
-        P.ent = c->d_ent.as<uint2>();
-        P.g_begin = g_lo;
-        P.g_end = g_hi;
-        P.l = l;
-        P.k = k;
-        P.stride_log2 = slog;
-        P.filter = c->d_filter.as<uint32_t>();
-        P.bm_bits = bm_bits;
-        P.table = c->d_table.as<Slot>();
-        P.tbits = tbits;
-        P.next = c->d_next.as<uint32_t>();
-        P.fmt = fmt;
-        P.sink.out = c->d_cand.as<uint64_t>();
-        P.sink.n_out = reinterpret_cast<unsigned long long*>(ctr + C_NCAND);
-        P.sink.cap = c->cand_cap;
-        P.mirror = mrule;
-        if (!dense) {
-            const uint32_t tiles = (g_hi - g_lo + 31) / 32;
-            uint32_t blocks = (tiles + 7) / 8;
-            if (blocks > (uint32_t)nsm * 8) blocks = (uint32_t)nsm * 8;
-            k3_probe<<<blocks, 256, 0, st>>>(P);
-        } else if (smem_filter) {
-            k3_scan<true><<<nsm, 1024, 32 * WBUF * 8 + (4u << bm_bits), st>>>(P);
-        } else {
-            k3_scan<false><<<nsm, 1024, 32 * WBUF * 8, st>>>(P);
+    if (have_a) {
+        const size_t filter_bytes = dense ? (4ull << bm_bits) : ((1ull << bm_bits) / 8);
+        const size_t table_bytes = sizeof(Slot) * (1ull << tbits);
+        OVL_TRY(dev_ensure(c, c->d_table, table_bytes));
+        OVL_TRY(dev_ensure(c, c->d_filter, filter_bytes));
+        OVL_TRY(dev_ensure(c, c->d_next, ((uint64_t)M << slog) * 4));
+        CK(cudaMemsetAsync(c->d_table.p, 0xff, table_bytes, st));  // EMPTY_SLOT
+        CK(cudaMemsetAsync(c->d_filter.p, 0, filter_bytes, st));
+        {
+            AnchorParams A;
+            A.packed64 = reinterpret_cast<const uint64_t*>(c->d_packed.p);
+            A.ent = c->d_ent.as<uint2>();
+            A.M = M;
+            A.l = l;
+            A.k = k;
+            A.stride_log2 = slog;
+            A.table = c->d_table.as<Slot>();
+            A.tbits = tbits;
+            A.next = c->d_next.as<uint32_t>();
+            A.bitmap = c->d_filter.as<uint32_t>();
+            A.bm_bits = bm_bits;
+            A.dense = dense ? 1 : 0;
+            A.n_anchors = reinterpret_cast<unsigned long long*>(ctr + C_NANC);
+            const uint64_t nthreads = (uint64_t)M << slog;
+            k2_insert<<<(unsigned)((nthreads + 255) / 256), 256, 0, st>>>(A);
+            ++launches;
+            CK(cudaGetLastError());
         }
-        ++launches;
-        CK(cudaGetLastError());
-        OVL_TRY(read_ctr(c));
-        OVL_TRY(check_alphabet());
-        n_cand = c->h_ctr[C_NCAND];
-        if (n_cand <= c->cand_cap) break;
-        if (attempt >= 2) return fail(c, OVL_E_LIMIT, "candidate buffer overflow persists (%llu)", (unsigned long long)n_cand);
-        ++S.retries;
-        OVL_TRY(dev_ensure(c, c->d_cand, (n_cand + n_cand / 16) * 8, false));
-        c->cand_cap = c->d_cand.cap / 8;
-        CK(cudaMemsetAsync(ctr + C_NCAND, 0, 8, st));
+        CK(cudaEventRecord(c->ev[E_SCAN0], st));
+
+        // ---- K3: scan (re-run with the exact size if the candidate buffer was too small) ------
+        if (c->cand_cap == 0) {
+            uint64_t cap = 96ull * (c->e_hi - c->e_lo);
+            if (cap < (1ull << 20)) cap = 1ull << 20;
+            OVL_TRY(dev_ensure(c, c->d_cand, cap * 8, false));
+            c->cand_cap = c->d_cand.cap / 8;
+        }
+        for (int attempt = 0;; ++attempt) {
+            ScanParams P;
+            P.packed = c->d_packed.as<uint4>();
+            P.gran_ent = c->d_gran_ent.as<uint32_t>();
+            P.ent = c->d_ent.as<uint2>();
+            P.g_begin = g_lo;
+            P.g_end = g_hi;
+            P.l = l;
+            P.k = k;
+            P.stride_log2 = slog;
+            P.filter = c->d_filter.as<uint32_t>();
+            P.bm_bits = bm_bits;
+            P.table = c->d_table.as<Slot>();
+            P.tbits = tbits;
+            P.next = c->d_next.as<uint32_t>();
+            P.fmt = fmt;
+            P.sink.out = c->d_cand.as<uint64_t>();
+            P.sink.n_out = reinterpret_cast<unsigned long long*>(ctr + C_NCAND);
+            P.sink.cap = c->cand_cap;
+            P.mirror = mrule;
+            if (!dense) {
+                const uint32_t tiles = (g_hi - g_lo + 31) / 32;
+                uint32_t blocks = (tiles + 7) / 8;
+                if (blocks > (uint32_t)nsm * 8) blocks = (uint32_t)nsm * 8;
+                k3_probe<<<blocks, 256, 0, st>>>(P);
+            } else if (smem_filter) {
+                k3_scan<true><<<nsm, 1024, 32 * WBUF * 8 + (4u << bm_bits), st>>>(P);
+            } else {
+                k3_scan<false><<<nsm, 1024, 32 * WBUF * 8, st>>>(P);
+            }
+            ++launches;
+            CK(cudaGetLastError());
+            OVL_TRY(read_ctr(c));
+            OVL_TRY(check_alphabet());
+            n_cand = c->h_ctr[C_NCAND];
+            if (n_cand <= c->cand_cap) break;
+            if (attempt >= 2) return fail(c, OVL_E_LIMIT, "candidate buffer overflow persists (%llu)", (unsigned long long)n_cand);
+            ++S.retries;
+            OVL_TRY(dev_ensure(c, c->d_cand, (n_cand + n_cand / 16) * 8, false));
+            c->cand_cap = c->d_cand.cap / 8;
+            CK(cudaMemsetAsync(ctr + C_NCAND, 0, 8, st));
+        }
+    } else {
+        CK(cudaEventRecord(c->ev[E_SCAN0], st));
     }
     S.candidates = n_cand;
-    if (n_cand == 0) return finish_from(E_VERIFY0);
+    S.verified = n_cand;
+    if (n_cand == 0 && !xchg) return finish_from(E_VERIFY0);
     if (n_cand > 0x7fffffffull) return fail(c, OVL_E_LIMIT, "more than 2^31 candidates on one GPU (%llu)", (unsigned long long)n_cand);
 
     // ---- K4: verify -----------------------------------------------------------------------
     CK(cudaEventRecord(c->ev[E_VERIFY0], st));
     const uint64_t hit_cap = mirror ? 3 * n_cand : n_cand;  // own key + SP twin + CONT twin
-    OVL_TRY(dev_ensure(c, c->d_cand2, hit_cap * 8));  // hit keys
-    OVL_TRY(dev_ensure(c, c->d_cnt, hit_cap * 4));    // survivor list now, row counts in K5
-    {
+    uint64_t n_hits = 0;
+    if (n_cand) {
+        OVL_TRY(dev_ensure(c, c->d_cand2, hit_cap * 8));  // hit keys
+        OVL_TRY(dev_ensure(c, c->d_cnt, hit_cap * 4));    // survivor list now, row counts in K5
         CandSink hits;
         hits.out = c->d_cand2.as<uint64_t>();
         hits.n_out = reinterpret_cast<unsigned long long*>(ctr + C_NHITS);
@@ -839,19 +914,20 @@ int ovl_overlaps_device(ovl_ctx* c, uint32_t min_length, uint64_t* n_rows_out) {
             launches += 2;
         }
         CK(cudaGetLastError());
+        OVL_TRY(read_ctr(c));
+        n_hits = c->h_ctr[C_NHITS];
+        S.compared_bases = c->h_ctr[C_SUMM];
+        S.operand_bytes = c->h_ctr[C_SUMB];
+        if (n_hits > hit_cap) return fail(c, OVL_E_LIMIT, "hit list overflow (%llu > %llu): internal error", (unsigned long long)n_hits, (unsigned long long)hit_cap);
     }
-    OVL_TRY(read_ctr(c));
-    const uint64_t n_hits = c->h_ctr[C_NHITS];
     S.hits = n_hits;
-    if (n_hits > hit_cap) return fail(c, OVL_E_LIMIT, "hit list overflow (%llu > %llu): internal error", (unsigned long long)n_hits, (unsigned long long)hit_cap);
-    S.verified = n_cand;
-    S.compared_bases = c->h_ctr[C_SUMM];
-    S.operand_bytes = c->h_ctr[C_SUMB];
-    if (n_hits == 0) return finish_from(E_SORT0);
+    // ---- multi-GPU mirror mode: every hit key goes to the rank that owns its A entry ---------
+    CK(cudaEventRecord(c->ev[E_SORT0], st));
+    if (xchg) OVL_TRY(exchange_hits(c, fmt, &n_hits, &launches, &lib));
+    if (n_hits == 0) return finish_from(E_EMIT0);
 
     // ---- sort the hit keys by (a, b, p) --------------------------------------------------------
-    CK(cudaEventRecord(c->ev[E_SORT0], st));
-    if (n_hits > c->cand_cap) {  // mirror mode can (in theory) return more entries than candidates
+    if (n_hits > c->cand_cap) {  // mirror mode can return more entries than candidates
         OVL_TRY(dev_ensure(c, c->d_cand, n_hits * 8, false));
         c->cand_cap = c->d_cand.cap / 8;
     }
@@ -869,6 +945,7 @@ int ovl_overlaps_device(ovl_ctx* c, uint32_t min_length, uint64_t* n_rows_out) {
     // ---- K5: select longest, compact ---------------------------------------------------------
     uint64_t n_rows = 0;
     {
+        OVL_TRY(dev_ensure(c, c->d_cnt, n_hits * 4));
         OVL_TRY(dev_ensure(c, c->d_offs, (n_hits + 1) * 8));
         const unsigned nb = (unsigned)((n_hits + 255) / 256);
         k5_count<<<nb, 256, 0, st>>>(keys, n_hits, fmt, c->d_cnt.as<uint32_t>());

@@ -76,16 +76,21 @@ constexpr uint64_t HIT_SP = 2;    // rem <= |b|: suffix-prefix (R1 candidate)
 // has to verify and emit itself; 0 means its twins cover it.
 struct MirrorRule {
     int on;
-    uint32_t own_lo, own_hi;  // entries whose rows this rank emits (multi-GPU: the SP twin is
-                              // used only when b ^ 1 is local as well)
 };
+// SP twins (a,.,b) <-> (b^1,.,a^1): which of the two compares is decided by a rule that is
+// symmetric under the swap and splits every rank's candidates about evenly (a plain "smaller a
+// wins" would leave the last rank of a multi-GPU run with nothing to compare).
+__host__ __device__ __forceinline__ bool sp_self(uint32_t a, uint32_t bt) {
+    if (a == bt) return true;  // fixed point: the candidate is its own twin
+    const bool lt = a < bt;
+    return (((a ^ bt) >> 1) & 1u) ? !lt : lt;
+}
 __device__ __forceinline__ uint32_t mirror_items(const MirrorRule& R, uint32_t a, uint32_t la, uint32_t b,
                                                  uint32_t lb, uint32_t p) {
     const uint32_t rem = la - p;
     uint32_t fl = (rem <= lb ? (uint32_t)HIT_SP : 0u) | (rem >= lb ? (uint32_t)HIT_CONT : 0u);
     if (R.on) {
-        const uint32_t bt = b ^ 1u;
-        if ((fl & HIT_SP) && bt >= R.own_lo && bt < R.own_hi && a > bt) fl &= ~(uint32_t)HIT_SP;
+        if ((fl & HIT_SP) && !sp_self(a, b ^ 1u)) fl &= ~(uint32_t)HIT_SP;
         if (a & 1u) fl &= ~(uint32_t)HIT_CONT;
     }
     return fl;
