@@ -23,7 +23,7 @@
 namespace ovl {
 
 struct AnchorParams {
-    const uint64_t* packed64;
+    const uint64_t* pre64;  // [M][4]: the first two granules (128 bases) of every entry
     const uint2* ent;       // {gran0, len}
     uint32_t M;
     uint32_t l;
@@ -38,6 +38,21 @@ struct AnchorParams {
     unsigned long long* n_anchors;  // entries with |b| >= l
 };
 
+// Prefix table: the first two granules of every entry of [e_begin, e_end) in one compact array.
+// K2 only ever needs bases [0, stride + k - 1) <= [0, 95) of an entry; on N > 1 GPUs this small
+// array (32 B per entry) is what the ranks exchange BEFORE the anchor build, so that the big
+// replication of the packed reads can overlap K2 and K3 (ovl.cu).
+__global__ void __launch_bounds__(256) k2_prefix(const uint4* __restrict__ packed, const uint2* __restrict__ ent,
+                                                 uint4* __restrict__ pre, uint32_t e_begin, uint32_t e_end) {
+    const uint32_t e = e_begin + blockIdx.x * blockDim.x + threadIdx.x;
+    if (e >= e_end) return;
+    const uint2 m = __ldg(ent + e);
+    const uint32_t ng = (m.y + 63u) >> 6;
+    const uint4 z = make_uint4(0, 0, 0, 0);
+    pre[2ull * e] = ng > 0 ? packed[m.x] : z;
+    pre[2ull * e + 1] = ng > 1 ? packed[m.x + 1] : z;
+}
+
 // One thread per (entry, delta).
 __global__ void __launch_bounds__(256) k2_insert(const AnchorParams P) {
     const uint64_t idx = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
@@ -48,7 +63,7 @@ __global__ void __launch_bounds__(256) k2_insert(const AnchorParams P) {
         if (m.y >= P.l) {
             const uint32_t delta = (uint32_t)idx & ((1u << P.stride_log2) - 1u);
             is_anchor0 = delta == 0;
-            const uint64_t* w = P.packed64 + 2ull * m.x + (delta >> 5);
+            const uint64_t* w = P.pre64 + 4ull * b + (delta >> 5);  // delta + k <= 95: words 0..2
             const uint64_t x = kmer_at(w[0], w[1], delta & 31) & kmer_mask(P.k);
             const uint64_t h = mix64(x);
             const uint32_t fp = (uint32_t)h;

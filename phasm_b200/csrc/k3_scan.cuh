@@ -77,15 +77,29 @@ __global__ void __launch_bounds__(256) k3_probe(const ScanParams P) {
         if (lane == 31 && P.stride_log2 < 5) w2 = inr ? packed64[2ull * (g + 1)] : 0;
         const bool a_ok = inr && L >= P.l;
 
-        for (uint32_t j = 0; j < n_probe; ++j) {
-            const uint32_t off = j << P.stride_log2;
-            const uint32_t q = pos0 + off;
-            uint32_t node = NIL;
-            if (a_ok && q + (uint32_t)P.k <= L) {
+        // phase 1: filter bit of every probed position of this granule (independent loads)
+        uint32_t hitmask = 0;
+        if (a_ok) {
+#pragma unroll 4
+            for (uint32_t j = 0; j < n_probe; ++j) {
+                const uint32_t off = j << P.stride_log2;
+                if (pos0 + off + (uint32_t)P.k <= L) {
+                    const uint64_t x = (off < 32 ? kmer_at(w0, w1, off) : kmer_at(w1, w2, off - 32)) & kmask;
+                    const uint32_t bit = bitmap_bit(mix64(x), P.bm_bits);
+                    hitmask |= ((__ldg(P.filter + (bit >> 5)) >> (bit & 31)) & 1u) << j;
+                }
+            }
+        }
+        // phase 2: resolve the (few) filter hits against the table, one position per lane per round
+        while (__any_sync(FULL, hitmask != 0)) {
+            uint32_t node = NIL, q = 0;
+            if (hitmask) {
+                const uint32_t j = __ffs(hitmask) - 1;
+                hitmask &= hitmask - 1;
+                const uint32_t off = j << P.stride_log2;
+                q = pos0 + off;
                 const uint64_t x = (off < 32 ? kmer_at(w0, w1, off) : kmer_at(w1, w2, off - 32)) & kmask;
-                const uint64_t h = mix64(x);
-                const uint32_t bit = bitmap_bit(h, P.bm_bits);
-                if ((__ldg(P.filter + (bit >> 5)) >> (bit & 31)) & 1u) node = table_find(P.table, P.tbits, h);
+                node = table_find(P.table, P.tbits, mix64(x));
             }
             while (__any_sync(FULL, node != NIL)) {
                 bool have = false;

@@ -68,7 +68,7 @@ struct ovl_ctx {
     int n_sm = 148;
     cudaStream_t st = nullptr, st_comm = nullptr;
     cudaEvent_t ev[E_COUNT] = {};
-    cudaEvent_t ev_comm = nullptr, ev_pack = nullptr;
+    cudaEvent_t ev_comm = nullptr, ev_pack = nullptr, ev_pre = nullptr;
     cudaEvent_t ev_t0 = nullptr, ev_t1 = nullptr;  // ovl_timer_*
     std::string err;
 
@@ -87,7 +87,7 @@ struct ovl_ctx {
     uint32_t e_lo = 0, e_hi = 0;  // entries whose bases are local (contiguous)
 
     // ---- device ----
-    DevBuf d_ascii, d_src, d_len, d_flags, d_gran0, d_gran_ent, d_ent, d_packed, d_tile0, d_tile_ent, d_xchg;
+    DevBuf d_ascii, d_src, d_len, d_flags, d_gran0, d_gran_ent, d_ent, d_packed, d_tile0, d_tile_ent, d_xchg, d_pre;
     DevBuf d_table, d_filter, d_next, d_ctr, d_tmp;
     DevBuf d_cand, d_cand2, d_cnt, d_offs, d_rows, d_cnts;
     uint64_t* h_ctr = nullptr;  // pinned mirror of d_ctr
@@ -346,6 +346,7 @@ int ovl_create(int device, ovl_ctx** out) {
         for (int i = 0; i < E_COUNT; ++i) CK(cudaEventCreate(&x->ev[i]));
         CK(cudaEventCreateWithFlags(&x->ev_comm, cudaEventDisableTiming));
         CK(cudaEventCreateWithFlags(&x->ev_pack, cudaEventDisableTiming));
+        CK(cudaEventCreateWithFlags(&x->ev_pre, cudaEventDisableTiming));
         CK(cudaEventCreate(&x->ev_t0));
         CK(cudaEventCreate(&x->ev_t1));
         CK(cudaHostAlloc(reinterpret_cast<void**>(&x->h_ctr), (C_COUNT + 2) * sizeof(uint64_t), cudaHostAllocDefault));
@@ -367,7 +368,7 @@ void ovl_destroy(ovl_ctx* c) {
     DevBuf* bufs[] = {&c->d_ascii, &c->d_src, &c->d_len, &c->d_flags, &c->d_gran0, &c->d_gran_ent,
                       &c->d_ent, &c->d_packed, &c->d_table, &c->d_filter, &c->d_next, &c->d_ctr,
                       &c->d_tmp, &c->d_cand, &c->d_cand2, &c->d_cnt, &c->d_offs, &c->d_rows, &c->d_cnts,
-                      &c->d_tile0, &c->d_tile_ent, &c->d_xchg};
+                      &c->d_tile0, &c->d_tile_ent, &c->d_xchg, &c->d_pre};
     for (DevBuf* b : bufs)
         if (b->p) cudaFree(b->p);
     if (c->ascii.p) cudaFreeHost(c->ascii.p);
@@ -378,6 +379,7 @@ void ovl_destroy(ovl_ctx* c) {
         if (c->ev[i]) cudaEventDestroy(c->ev[i]);
     if (c->ev_comm) cudaEventDestroy(c->ev_comm);
     if (c->ev_pack) cudaEventDestroy(c->ev_pack);
+    if (c->ev_pre) cudaEventDestroy(c->ev_pre);
     if (c->ev_t0) cudaEventDestroy(c->ev_t0);
     if (c->ev_t1) cudaEventDestroy(c->ev_t1);
     if (c->st) cudaStreamDestroy(c->st);
@@ -666,6 +668,31 @@ int ovl_overlaps_device(ovl_ctx* c, uint32_t min_length, uint64_t* n_rows_out) {
         if (c->collect) smax = 1;  // byte accounting is defined on the canonical candidates
         while ((2u << slog) <= smax) ++slog;
         while (slog > 0 && (((uint64_t)M << slog) > 0xfffffff0ull)) --slog;
+        // Auto mode: the table build costs ~ (anchor entries x stride) inserts on EVERY rank (and
+        // much more per insert once the table outgrows L2), the scan ~ (own granules x 64/stride)
+        // filter probes.  Pick the stride with the smallest modelled sum (constants measured on
+        // B200, profiles/r01d_stride_sweep.txt); a dense scan (stride 1) is only taken when
+        // l < 33 forces it.
+        if (c->opt_stride == 0 && slog > 1) {
+            uint64_t n_b = 0;
+            for (uint32_t e = 0; e < M; ++e) n_b += c->len[e] >= l;
+            const double gl = (double)(c->gran0[c->e_hi] - c->gran0[c->e_lo]) / 12.9e6;
+            static const double scan_ms[7] = {0, 1.7, 1.0, 0.68, 0.50, 0.41, 0.35};  // stride 2^i per 12.9 M granules
+            int best = slog;
+            double best_cost = 1e30;
+            for (int sl = slog; sl >= 1; --sl) {
+                const double keys = (double)n_b * (double)(1u << sl);
+                const double table_bytes = 8.0 * (double)(1ull << ceil_log2((uint64_t)(2 * keys) + 1));
+                double per_key_us = table_bytes <= 64.0 * 1048576.0 ? 0.045 : 0.125;
+                if (c->nranks > 1) per_key_us *= 2.0;  // the concurrent replication of the reads thrashes L2
+                const double cost = 0.03 + keys * per_key_us * 1e-3 + gl * scan_ms[sl];
+                if (cost < best_cost) {
+                    best_cost = cost;
+                    best = sl;
+                }
+            }
+            slog = best;
+        }
     }
     const bool dense = slog == 0;
     S.anchor_stride = 1u << slog;
@@ -714,11 +741,33 @@ int ovl_overlaps_device(ovl_ctx* c, uint32_t min_length, uint64_t* n_rows_out) {
     }
     CK(cudaMemsetAsync(c->d_packed.as<uint4>() + G, 0, 32, st));  // terminator granules
     CK(cudaGetLastError());
-    // ---- multi-GPU: replicate the packed granules (needed by K2 keys and by K4) ---------
+    // ---- prefix table (K2's only input) of the local entries ----------------------------------
+    OVL_TRY(dev_ensure(c, c->d_pre, (size_t)M * 32));
+    if (c->e_hi > c->e_lo) {
+        k2_prefix<<<(c->e_hi - c->e_lo + 255) / 256, 256, 0, st>>>(c->d_packed.as<uint4>(), c->d_ent.as<uint2>(),
+                                                                 c->d_pre.as<uint4>(), c->e_lo, c->e_hi);
+        ++launches;
+        CK(cudaGetLastError());
+    }
+    // ---- multi-GPU: replicate on the comm stream (1) the prefix table, which K2 waits for, then
+    //      (2) the packed granules of every rank, which only K4 needs: that transfer runs under
+    //      K2 and K3 -------------------------------------------------------------------------
+    bool wait_packed = false;
     if (c->nranks > 1) {
         auto& N = nccl_dyn::api();
+        if ((int)c->rank_e.size() != c->nranks + 1) return fail(c, OVL_E_ARG, "call ovl_comm_sync_ranges before ovl_overlaps_device");
         CK(cudaEventRecord(c->ev_pack, st));
         CK(cudaStreamWaitEvent(c->st_comm, c->ev_pack, 0));
+        CKN(N.GroupStart());
+        for (int r = 0; r < c->nranks; ++r) {
+            const uint32_t a = c->rank_e[r], b = c->rank_e[r + 1];
+            if (b > a) {
+                uint4* p = c->d_pre.as<uint4>() + 2ull * a;
+                CKN(N.Broadcast(p, p, (size_t)(b - a) * 32, ncclUint8, r, c->comm, c->st_comm));
+            }
+        }
+        CKN(N.GroupEnd());
+        CK(cudaEventRecord(c->ev_pre, c->st_comm));
         CKN(N.GroupStart());
         for (int r = 0; r < c->nranks; ++r) {
             const uint32_t a = c->gran0[c->rank_e[r]], b = c->gran0[c->rank_e[r + 1]];
@@ -729,7 +778,8 @@ int ovl_overlaps_device(ovl_ctx* c, uint32_t min_length, uint64_t* n_rows_out) {
         }
         CKN(N.GroupEnd());
         CK(cudaEventRecord(c->ev_comm, c->st_comm));
-        CK(cudaStreamWaitEvent(st, c->ev_comm, 0));  // K2 reads every rank's granules
+        CK(cudaStreamWaitEvent(st, c->ev_pre, 0));  // K2 reads every rank's prefixes
+        wait_packed = true;
     }
     CK(cudaEventRecord(c->ev[E_ANCHOR0], st));
 
@@ -754,6 +804,7 @@ int ovl_overlaps_device(ovl_ctx* c, uint32_t min_length, uint64_t* n_rows_out) {
     };
     // record the remaining stage events from `from` on, wait, fill the stage times
     auto finish_from = [&](int from) -> int {
+        if (wait_packed) CK(cudaStreamWaitEvent(st, c->ev_comm, 0));  // never leave the replication in flight
         for (int e = from; e <= E_END; ++e) CK(cudaEventRecord(c->ev[e], st));
         OVL_TRY(read_ctr(c));
         OVL_TRY(check_alphabet());
@@ -794,7 +845,7 @@ int ovl_overlaps_device(ovl_ctx* c, uint32_t min_length, uint64_t* n_rows_out) {
         CK(cudaMemsetAsync(c->d_filter.p, 0, filter_bytes, st));
         {
             AnchorParams A;
-            A.packed64 = reinterpret_cast<const uint64_t*>(c->d_packed.p);
+            A.pre64 = reinterpret_cast<const uint64_t*>(c->d_pre.p);
             A.ent = c->d_ent.as<uint2>();
             A.M = M;
             A.l = l;
@@ -873,6 +924,7 @@ int ovl_overlaps_device(ovl_ctx* c, uint32_t min_length, uint64_t* n_rows_out) {
 
     // ---- K4: verify -----------------------------------------------------------------------
     CK(cudaEventRecord(c->ev[E_VERIFY0], st));
+    if (wait_packed) CK(cudaStreamWaitEvent(st, c->ev_comm, 0));  // the operands of other ranks' entries
     const uint64_t hit_cap = mirror ? 3 * n_cand : n_cand;  // own key + SP twin + CONT twin
     uint64_t n_hits = 0;
     if (n_cand) {

@@ -196,11 +196,21 @@ def test_mirror_tiny_random_both_strands(ov):
 
 
 def test_auto_stride_follows_min_length(ov):
+    """Auto stride: a power of two <= min(64, l-k+1) (the bound that keeps the scan complete);
+    below l = 33 only the dense scan is possible.  Inside the bound a cost model picks it."""
     reads = helpers.mid_input("edge_s5_l20")[0]
-    for l, want in ((1, 1), (20, 1), (32, 1), (33, 2), (35, 4), (47, 16), (63, 32), (94, 32),
-                    (95, 64), (1000, 64)):
+    for l, bound in ((1, 1), (20, 1), (32, 1), (33, 2), (35, 4), (47, 16), (63, 32), (94, 32),
+                     (95, 64), (1000, 64)):
         run_reads_idx(ov, reads, l)
-        assert ov.stats()["anchor_stride"] == want, l
+        s = ov.stats()["anchor_stride"]
+        assert 1 <= s <= bound and s & (s - 1) == 0, (l, s)
+        assert (s == 1) == (bound == 1), (l, s)
+        try:
+            ov.set_option("anchor_stride", bound)   # an explicit value is an upper bound that is taken
+            run_reads_idx(ov, reads, l)
+            assert ov.stats()["anchor_stride"] == bound, l
+        finally:
+            ov.set_option("anchor_stride", 0)
 
 
 # ---- oracle on fresh inputs -----------------------------------------------------------------
