@@ -187,10 +187,9 @@ __global__ void __launch_bounds__(256) k4_verify_serial(const VerifyParams P) {
 //   k4b_tail  one warp per survivor compares the remaining granules, 4 granules per lane in
 //             flight, no exit test inside the loop, one vote at the end.
 //
-// Both read A as three 64-bit words per granule (8-byte aligned at p/32) so that the re-alignment
-// is one 32-bit word select + four funnel shifts; the tail kernel hoists the select out of its
-// loop (two loop bodies, warp-uniform branch).  Candidates need not be sorted: the scan flushes
-// them in per-warp runs of one A entry, which is what keeps the A operand in L1.
+// Both read A as one 128-bit + one 64-bit load per granule (load_a below).  Candidates need not be
+// sorted: the scan flushes them in per-warp runs of one A entry, which is what keeps the A
+// operand in L1.
 // Bytes touched beyond the first mismatch are the price: <= 2048 bases per false candidate.
 constexpr uint32_t FIRST_GRAN = 32;
 constexpr int HEAD_UNROLL = 4;
@@ -231,9 +230,9 @@ __device__ __forceinline__ uint64_t next_tile(unsigned long long* ctr, uint32_t 
 }
 
 struct CandMeta {
-    uint32_t wa_lo, wa_hi;  // 64-bit word index of a[p]
+    uint32_t ga;            // granule holding a[p]
     uint32_t gb;            // first granule of b
-    uint32_t n, sh, fl;     // bases to compare (0: skip), bit shift (0..62, even), HIT_* items to emit
+    uint32_t n, sh, fl;     // bases to compare (0: skip), bit offset of a[p] in its granule (0..126, even), HIT_* items
 };
 
 __device__ __forceinline__ CandMeta cand_meta(const Verify2Params& P, uint64_t key) {
@@ -243,27 +242,55 @@ __device__ __forceinline__ CandMeta cand_meta(const Verify2Params& P, uint64_t k
     const uint32_t rem = ma.y - p;
     m.n = rem < mb.y ? rem : mb.y;
     m.fl = mirror_items(P.mirror, a, ma.y, b, mb.y, p);  // never 0: the scan dropped those
-    const uint64_t wa = 2ull * ma.x + (p >> 5);
-    m.wa_lo = (uint32_t)wa;
-    m.wa_hi = (uint32_t)(wa >> 32);
+    m.ga = ma.x + (p >> 6);
     m.gb = mb.x;
-    m.sh = 2u * (p & 31u);
+    m.sh = 2u * (p & 63u);
     return m;
 }
 
-// granule = bits [sh, sh+128) of the 192-bit value (w2:w1:w0); HI32 = (sh >= 32), t = sh & 31
-template <bool HI32>
-__device__ __forceinline__ uint4 shr192(uint64_t w0, uint64_t w1, uint64_t w2, uint32_t t) {
-    const uint32_t x0 = (uint32_t)w0, x1 = (uint32_t)(w0 >> 32), x2 = (uint32_t)w1, x3 = (uint32_t)(w1 >> 32),
-                   x4 = (uint32_t)w2, x5 = (uint32_t)(w2 >> 32);
-    if (HI32)
-        return make_uint4(__funnelshift_r(x1, x2, t), __funnelshift_r(x2, x3, t), __funnelshift_r(x3, x4, t),
-                          __funnelshift_r(x4, x5, t));
-    return make_uint4(__funnelshift_r(x0, x1, t), __funnelshift_r(x1, x2, t), __funnelshift_r(x2, x3, t),
-                      __funnelshift_r(x3, x4, t));
+// The A operand of compare-granule i is bits [sh, sh+128) of the 256-bit value (G1:G0), G0 =
+// granule ga+i, G1 = granule ga+i+1 (32-bit words x0..x7).  Only words x[v .. v+4], v = sh/32, are
+// needed, and they always lie in ONE whole granule plus ONE aligned half of the other:
+//
+//   v = 0,1 (sh < 64):  big = G0 (x0..x3), small = low half of G1  (x4, x5)
+//   v = 2,3 (sh >= 64): big = G1 (x4..x7), small = high half of G0 (x2, x3)
+//
+// so a lane issues one 128-bit and one 64-bit load for A (both addresses are plain arithmetic on
+// sh: no branch in front of the loads) and one streaming 128-bit load for B: 12 L1 wavefronts per
+// 32 granules instead of the 16 of three 64-bit A loads (ncu r01f: k4a_head sat at 88 % of the
+// LSU wavefront rate).  The re-alignment is a warp-uniform 4-way switch on v and four funnel
+// shifts by t = sh mod 32.
+__device__ __forceinline__ void load_a(const uint4* __restrict__ g0, uint32_t hv, uint4& big, uint2& small) {
+    big = __ldg(g0 + hv);
+    small = __ldg(reinterpret_cast<const uint2*>(g0 + 1 - hv) + hv);
 }
 
-__global__ void __launch_bounds__(256) k4a_head(const Verify2Params P) {
+template <int V>
+__device__ __forceinline__ uint4 align_a(const uint4 b, const uint2 s, uint32_t t) {
+    if (V == 0)
+        return make_uint4(__funnelshift_r(b.x, b.y, t), __funnelshift_r(b.y, b.z, t), __funnelshift_r(b.z, b.w, t),
+                          __funnelshift_r(b.w, s.x, t));
+    if (V == 1)
+        return make_uint4(__funnelshift_r(b.y, b.z, t), __funnelshift_r(b.z, b.w, t), __funnelshift_r(b.w, s.x, t),
+                          __funnelshift_r(s.x, s.y, t));
+    if (V == 2)
+        return make_uint4(__funnelshift_r(s.x, s.y, t), __funnelshift_r(s.y, b.x, t), __funnelshift_r(b.x, b.y, t),
+                          __funnelshift_r(b.y, b.z, t));
+    return make_uint4(__funnelshift_r(s.y, b.x, t), __funnelshift_r(b.x, b.y, t), __funnelshift_r(b.y, b.z, t),
+                      __funnelshift_r(b.z, b.w, t));
+}
+
+__device__ __forceinline__ uint4 align_a_dyn(const uint4 b, const uint2 s, uint32_t sh) {
+    const uint32_t t = sh & 31u;
+    switch (sh >> 5) {  // warp-uniform
+        case 0: return align_a<0>(b, s, t);
+        case 1: return align_a<1>(b, s, t);
+        case 2: return align_a<2>(b, s, t);
+        default: return align_a<3>(b, s, t);
+    }
+}
+
+__global__ void __launch_bounds__(256, 4) k4a_head(const Verify2Params P) {
     __shared__ uint64_t s_buf[8][WBUF];
     const uint32_t lane = threadIdx.x & 31;
     const uint64_t n_tiles = (P.n + 31) / 32;
@@ -274,7 +301,7 @@ __global__ void __launch_bounds__(256) k4a_head(const Verify2Params P) {
     for (uint64_t tile = next_tile(P.tile_ctr, lane); tile < n_tiles; tile = next_tile(P.tile_ctr, lane)) {
         const uint64_t c = tile * 32 + lane;
         uint64_t key = 0;
-        CandMeta my = {0, 0, 0, 0, 0, 0};  // n == 0 marks "no candidate" (a real one has n >= l >= 1)
+        CandMeta my = {0, 0, 0, 0, 0};  // n == 0 marks "no candidate" (a real one has n >= l >= 1)
         if (c < P.n) {
             key = P.keys[c];
             my = cand_meta(P, key);
@@ -282,35 +309,28 @@ __global__ void __launch_bounds__(256) k4a_head(const Verify2Params P) {
         uint32_t ok_mask = 0;  // bit j: candidate j matched over its head
         for (uint32_t j0 = 0; j0 < 32; j0 += HEAD_UNROLL) {
             if (__shfl_sync(FULL, my.n, j0) == 0) break;  // tile tail (warp-uniform)
-            uint4 bv[HEAD_UNROLL];
-            uint64_t w0[HEAD_UNROLL], w1[HEAD_UNROLL], w2[HEAD_UNROLL];
-            uint32_t sh[HEAD_UNROLL], nn[HEAD_UNROLL];
+            uint4 bv[HEAD_UNROLL], big[HEAD_UNROLL];
+            uint2 sm[HEAD_UNROLL];
+            uint32_t sh[HEAD_UNROLL], nn[HEAD_UNROLL], gl[HEAD_UNROLL];
 #pragma unroll
             for (int u = 0; u < HEAD_UNROLL; ++u) {
-                const uint32_t lo = __shfl_sync(FULL, my.wa_lo, j0 + u);
-                const uint32_t hi = __shfl_sync(FULL, my.wa_hi, j0 + u);
+                const uint32_t ga = __shfl_sync(FULL, my.ga, j0 + u);
                 const uint32_t gb = __shfl_sync(FULL, my.gb, j0 + u);
                 sh[u] = __shfl_sync(FULL, my.sh, j0 + u);
                 nn[u] = __shfl_sync(FULL, my.n, j0 + u);
-                bv[u] = make_uint4(0, 0, 0, 0);
-                w0[u] = w1[u] = w2[u] = 0;
-                if (64u * lane < nn[u]) {
-                    const uint64_t* pa = P.packed64 + (((uint64_t)hi << 32) | lo) + 2u * lane;
-                    bv[u] = ldg_stream(packed128 + gb + lane);
-                    w0[u] = __ldg(pa);
-                    w1[u] = __ldg(pa + 1);
-                    w2[u] = __ldg(pa + 2);
-                }
+                // lanes past the end re-read the last granule (same address as the last live lane: no
+                // extra wavefront, no zero-initialised registers, no predicates on the loads)
+                gl[u] = min(lane, (nn[u] - 1u) >> 6);
+                load_a(packed128 + ga + gl[u], sh[u] >> 6, big[u], sm[u]);
+                bv[u] = ldg_stream(packed128 + gb + gl[u]);
             }
 #pragma unroll
             for (int u = 0; u < HEAD_UNROLL; ++u) {
-                const uint32_t t = sh[u] & 31u;
-                const uint4 x = (sh[u] & 32u) ? shr192<true>(w0[u], w1[u], w2[u], t)
-                                              : shr192<false>(w0[u], w1[u], w2[u], t);
+                const uint4 x = align_a_dyn(big[u], sm[u], sh[u]);
                 uint4 d = make_uint4(x.x ^ bv[u].x, x.y ^ bv[u].y, x.z ^ bv[u].z, x.w ^ bv[u].w);
-                const int nb = (int)nn[u] - 64 * (int)lane;
+                const int nb = (int)nn[u] - 64 * (int)gl[u];
                 if (nb < 64) {
-                    const uint4 m = low_bases_mask128(nb);  // all zero for nb <= 0
+                    const uint4 m = low_bases_mask128(nb);
                     d.x &= m.x; d.y &= m.y; d.z &= m.z; d.w &= m.w;
                 }
                 const unsigned bad = __ballot_sync(FULL, (d.x | d.y | d.z | d.w) != 0);
@@ -335,43 +355,64 @@ __global__ void __launch_bounds__(256) k4a_head(const Verify2Params P) {
     if (nbuf) wbuf_flush(buf, nbuf, P.hits, lane);
 }
 
-// OR of the differences of granules [FIRST_GRAN, ng) for one lane (stride 32, 4 in flight)
-template <bool HI32>
-__device__ __forceinline__ uint4 tail_diff(const uint64_t* __restrict__ pa, const uint4* __restrict__ pb,
+// OR of the differences of compare-granules [FIRST_GRAN, ceil(n/64)) for one lane (stride 32,
+// TAIL_ROWS rows in flight).  Whole granules need no mask and cost 4 funnel shifts + 4 LOP3
+// (acc |= x ^ b) each; the partial last granule (n mod 64 bases) is one extra masked compare by a
+// single lane.  (ncu r01f: the previous form, which masked inside the loop, ran at 80 % of the
+// ALU pipe -- the verifier was instruction bound, not HBM bound.)  A survivor has
+// n > 64*FIRST_GRAN.
+constexpr int TAIL_ROWS = 4;  // tail_diff's dispatch below is written for 4
+
+// R rows (32 granules each) of one comparison, all loads issued before the first compare; in the
+// last row the lanes past granule `glast` re-read it (same address as a live lane).
+template <int V, int R>
+__device__ __forceinline__ void tail_rows(const uint4* __restrict__ pa, const uint4* __restrict__ pb, uint32_t g0,
+                                          uint32_t glast, uint32_t t, uint4& acc) {
+    uint4 bv[R], big[R];
+    uint2 sm[R];
+#pragma unroll
+    for (int u = 0; u < R; ++u) {
+        uint32_t g = g0 + 32u * u;
+        if (u == R - 1) g = min(g, glast);
+        load_a(pa + g, V >> 1, big[u], sm[u]);
+        bv[u] = ldg_stream(pb + g);
+    }
+#pragma unroll
+    for (int u = 0; u < R; ++u) {
+        const uint4 x = align_a<V>(big[u], sm[u], t);
+        acc.x |= x.x ^ bv[u].x; acc.y |= x.y ^ bv[u].y; acc.z |= x.z ^ bv[u].z; acc.w |= x.w ^ bv[u].w;
+    }
+}
+
+template <int V>
+__device__ __forceinline__ uint4 tail_diff(const uint4* __restrict__ pa, const uint4* __restrict__ pb,
                                            uint32_t n, uint32_t t, uint32_t lane) {
-    const uint32_t ng = (n + 63) >> 6;
+    constexpr uint32_t HV = V >> 1;
+    const uint32_t nf = n >> 6;  // whole granules (>= FIRST_GRAN for a survivor)
     uint4 acc = make_uint4(0, 0, 0, 0);
-    for (uint32_t i = FIRST_GRAN + lane; i < ng; i += 128) {
-        uint4 bv[4];
-        uint64_t w0[4], w1[4], w2[4];
-#pragma unroll
-        for (int u = 0; u < 4; ++u) {
-            const uint32_t g = i + 32u * u;
-            bv[u] = make_uint4(0, 0, 0, 0);
-            w0[u] = w1[u] = w2[u] = 0;
-            if (g < ng) {
-                bv[u] = ldg_stream(pb + g);
-                w0[u] = __ldg(pa + 2u * g);
-                w1[u] = __ldg(pa + 2u * g + 1);
-                w2[u] = __ldg(pa + 2u * g + 2);
-            }
-        }
-#pragma unroll
-        for (int u = 0; u < 4; ++u) {
-            const uint4 x = shr192<HI32>(w0[u], w1[u], w2[u], t);
-            uint4 d = make_uint4(x.x ^ bv[u].x, x.y ^ bv[u].y, x.z ^ bv[u].z, x.w ^ bv[u].w);
-            const int nb = (int)n - 64 * (int)(i + 32u * u);
-            if (nb < 64) {  // the last granule of the comparison, or past it
-                const uint4 m = low_bases_mask128(nb);
-                d.x &= m.x; d.y &= m.y; d.z &= m.z; d.w &= m.w;
-            }
-            acc.x |= d.x; acc.y |= d.y; acc.z |= d.z; acc.w |= d.w;
-        }
+#pragma unroll 1
+    for (uint32_t base = FIRST_GRAN; base < nf; base += 32u * TAIL_ROWS) {
+        const uint32_t rows = (nf - base + 31u) >> 5;  // warp-uniform
+        const uint32_t g0 = base + lane, gl = nf - 1u;
+        if (rows >= 4) tail_rows<V, 4>(pa, pb, g0, gl, t, acc);
+        else if (rows == 3) tail_rows<V, 3>(pa, pb, g0, gl, t, acc);
+        else if (rows == 2) tail_rows<V, 2>(pa, pb, g0, gl, t, acc);
+        else tail_rows<V, 1>(pa, pb, g0, gl, t, acc);
+    }
+    const int nb = (int)(n & 63u);
+    if (nb && lane == (nf & 31u)) {
+        uint4 big;
+        uint2 sm;
+        load_a(pa + nf, HV, big, sm);
+        const uint4 bv = ldg_stream(pb + nf);
+        const uint4 x = align_a<V>(big, sm, t);
+        const uint4 m = low_bases_mask128(nb);
+        acc.x |= (x.x ^ bv.x) & m.x; acc.y |= (x.y ^ bv.y) & m.y; acc.z |= (x.z ^ bv.z) & m.z; acc.w |= (x.w ^ bv.w) & m.w;
     }
     return acc;
 }
 
-__global__ void __launch_bounds__(256) k4b_tail(const Verify2Params P) {
+__global__ void __launch_bounds__(256, 4) k4b_tail(const Verify2Params P) {
     __shared__ uint64_t s_buf[8][WBUF];
     const uint32_t lane = threadIdx.x & 31;
     const uint64_t ns = *P.n_surv;
@@ -385,23 +426,29 @@ __global__ void __launch_bounds__(256) k4b_tail(const Verify2Params P) {
     for (uint64_t tile = next_tile(P.tile_ctr + 1, lane); tile < n_tiles; tile = next_tile(P.tile_ctr + 1, lane)) {
         const uint64_t s = tile * 32 + lane;
         uint64_t key = 0;
-        CandMeta my = {0, 0, 0, 0, 0, 0};
+        CandMeta my = {0, 0, 0, 0, 0};
         if (s < ns) {
             key = P.keys[P.surv[s]];
             my = cand_meta(P, key);
         }
         const uint32_t cnt = (uint32_t)((ns - tile * 32) < 32 ? (ns - tile * 32) : 32);
         uint32_t ok_mask = 0;
+#pragma unroll 1
         for (uint32_t j = 0; j < cnt; ++j) {
-            const uint32_t lo = __shfl_sync(FULL, my.wa_lo, j);
-            const uint32_t hi = __shfl_sync(FULL, my.wa_hi, j);
+            const uint32_t ga = __shfl_sync(FULL, my.ga, j);
             const uint32_t gb = __shfl_sync(FULL, my.gb, j);
             const uint32_t sh = __shfl_sync(FULL, my.sh, j);
             const uint32_t n = __shfl_sync(FULL, my.n, j);
-            const uint64_t* pa = P.packed64 + (((uint64_t)hi << 32) | lo);
+            const uint4* pa = packed128 + ga;
             const uint4* pb = packed128 + gb;
             const uint32_t t = sh & 31u;
-            const uint4 acc = (sh & 32u) ? tail_diff<true>(pa, pb, n, t, lane) : tail_diff<false>(pa, pb, n, t, lane);
+            uint4 acc;
+            switch (sh >> 5) {  // warp-uniform
+                case 0: acc = tail_diff<0>(pa, pb, n, t, lane); break;
+                case 1: acc = tail_diff<1>(pa, pb, n, t, lane); break;
+                case 2: acc = tail_diff<2>(pa, pb, n, t, lane); break;
+                default: acc = tail_diff<3>(pa, pb, n, t, lane); break;
+            }
             const unsigned bad = __ballot_sync(FULL, (acc.x | acc.y | acc.z | acc.w) != 0);
             if (!bad) ok_mask |= 1u << j;
         }

@@ -670,22 +670,26 @@ int ovl_overlaps_device(ovl_ctx* c, uint32_t min_length, uint64_t* n_rows_out) {
         while (slog > 0 && (((uint64_t)M << slog) > 0xfffffff0ull)) --slog;
         // Auto mode: the table build costs ~ (anchor entries x stride) inserts on EVERY rank (and
         // much more per insert once the table outgrows L2), the scan ~ (own granules x 64/stride)
-        // filter probes.  Pick the stride with the smallest modelled sum (constants measured on
-        // B200, profiles/r01d_stride_sweep.txt); a dense scan (stride 1) is only taken when
-        // l < 33 forces it.
+        // filter probes.  Pick the stride with the smallest modelled sum; both tables are B200
+        // measurements on config 2 (55 200 anchor entries, 12.9 M granules; N=1 and N=2 columns of
+        // profiles/r01d_stride_sweep.txt).  A dense scan (stride 1) is only taken when l < 33
+        // forces it.
         if (c->opt_stride == 0 && slog > 1) {
             uint64_t n_b = 0;
             for (uint32_t e = 0; e < M; ++e) n_b += c->len[e] >= l;
             const double gl = (double)(c->gran0[c->e_hi] - c->gran0[c->e_lo]) / 12.9e6;
-            static const double scan_ms[7] = {0, 1.7, 1.0, 0.68, 0.50, 0.41, 0.35};  // stride 2^i per 12.9 M granules
+            const double al = (double)n_b / 55200.0;
+            static const double scan_ms[7] = {0, 1.7, 1.0, 0.68, 0.50, 0.41, 0.35};       // stride 2^i
+            static const double anchor_ms[7] = {0, 0.02, 0.03, 0.05, 0.087, 0.158, 0.199};  // stride 2^i
             int best = slog;
             double best_cost = 1e30;
             for (int sl = slog; sl >= 1; --sl) {
                 const double keys = (double)n_b * (double)(1u << sl);
                 const double table_bytes = 8.0 * (double)(1ull << ceil_log2((uint64_t)(2 * keys) + 1));
-                double per_key_us = table_bytes <= 64.0 * 1048576.0 ? 0.045 : 0.125;
-                if (c->nranks > 1) per_key_us *= 2.0;  // the concurrent replication of the reads thrashes L2
-                const double cost = 0.03 + keys * per_key_us * 1e-3 + gl * scan_ms[sl];
+                double a_ms = al * anchor_ms[sl];
+                if (table_bytes > 64.0 * 1048576.0) a_ms *= 2.5;  // table no longer L2-resident
+                if (c->nranks > 1) a_ms *= 1.4;  // the concurrent replication of the reads competes for L2
+                const double cost = a_ms + gl * scan_ms[sl];
                 if (cost < best_cost) {
                     best_cost = cost;
                     best = sl;
