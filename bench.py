@@ -57,6 +57,21 @@ def measured_peak_gbs():
         return 6650.0, "fallback (B200_PROFILING.md 6.65 TB/s)"
 
 
+def ncu_traffic():
+    """Per-kernel DRAM bytes per launch from the newest committed `ncu --set full` capture
+    (profiles/<tag>_traffic.json, written by tools/profsum.py; same workload as this bench)."""
+    import glob
+    files = sorted(glob.glob(os.path.join(ROOT, "profiles", "*_traffic.json")))
+    if not files:
+        return None, None
+    try:
+        with open(files[-1]) as f:
+            k = json.load(f)["kernels"]
+        return {n: v["dram_bytes_per_launch"] for n, v in k.items()}, os.path.basename(files[-1])
+    except Exception:
+        return None, None
+
+
 class ClockSampler:
     """nvidia-smi clocks / throttle reasons sampled DURING the timed region."""
     Q = ("clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,"
@@ -351,9 +366,17 @@ def run_b200(args):
         per_kernel[k] = {"alg_bytes": b, "ms": ms, "GBps": gbs, "frac": gbs / peak}
     b_alg = (2.0 * n_local + 32.0 * st["anchors"] / world + operand_bytes
              + 32.0 * candidates + 20.0 * st_c["rows"])
+    traffic, traffic_src = ncu_traffic()
+    tmap = {"k1_pack": ("k1_pack",), "k3_scan": ("k3_probe",), "k4_verify": ("k4a_head", "k4b_tail")}
+    for k in per_kernel:
+        t = None
+        if traffic and all(n in traffic for n in tmap[k]):
+            t = sum(traffic[n] for n in tmap[k])
+        per_kernel[k]["traffic"] = t
     roofline = {
         "bound": "hbm", "kernel": dom, "achieved": per_kernel[dom]["GBps"], "peak": peak,
-        "unit": "GB/s", "frac": per_kernel[dom]["frac"], "traffic": None,
+        "unit": "GB/s", "frac": per_kernel[dom]["frac"], "traffic": per_kernel[dom]["traffic"],
+        "traffic_source": traffic_src,
         "peak_source": peak_src, "alg_bytes_per_launch": kern[dom][0],
         "ms_per_launch": kern[dom][1], "per_kernel": per_kernel,
         "k4_verify_canonical": {
