@@ -1,0 +1,171 @@
+// k7_bucket.cuh -- ordering of the verified hit keys and row emission without a host round trip.
+//
+// The hit keys [a | b | p | flags] have to be ordered by (a, b, p, flags) before the
+// select-longest rule of k5_emit.cuh can run (R1/R2, /root/reference/src/overlapper.cpp:64-115).
+// A device-wide radix sort does that in 6 passes of a library kernel and needs the hit count on
+// the host first.  The keys are far from random, though: an entry `a` owns a few dozen hits, so
+//
+//   k7_hist      count the hits of every A entry                      (one L2 atomic per hit)
+//   (exclusive sum over the M+1 counts: CUB DeviceScan, size known on the host)
+//   k7_scatter   move every key into its entry's bucket              (one L2 atomic per hit)
+//   k7_sort      one warp per entry: bitonic sort of the bucket in shared memory (<= BUCKET_MAX
+//                keys), sorted keys written back, rows of the entry counted (key_rows rule)
+//   (exclusive sum over the M+1 row counts)
+//   k7_emit      one warp per entry: rows written at the entry's row offset
+//
+// leaves the keys globally sorted and the rows in canonical (a,b,astart,aend,bend) order --
+// bit-identical to the radix-sort path -- with every size read from device counters: the whole
+// overlap pass then needs ONE host synchronisation, at its end.  An entry with more than
+// BUCKET_MAX hits raises a flag and the host falls back to the radix-sort path for that call.
+//
+// Roofline: HBM/L2, 8 B read + 8 B written per hit in scatter and sort, 20 B written per row.
+#pragma once
+#include "k5_emit.cuh"
+#include "ovl_common.cuh"
+
+namespace ovl {
+
+constexpr uint32_t BUCKET_MAX = 256;  // keys one warp sorts in shared memory
+
+struct BucketParams {
+    const uint64_t* hits;             // unsorted hit keys
+    const unsigned long long* n_ptr;  // their number (device counter)
+    uint64_t cap;                     // capacity of `hits` (the counter may exceed it on overflow)
+    KeyFmt fmt;
+    uint32_t M;
+    uint32_t* cnt;                    // [M+1] hits per entry (zeroed by the host), cnt[M] stays 0
+    const uint64_t* off;              // [M+1] exclusive sum of cnt
+    uint32_t* cur;                    // [M] scatter cursors (zeroed by the host)
+    uint64_t* sorted;                 // bucketed, then sorted keys
+    uint32_t* rowcnt;                 // [M+1] rows per entry, rowcnt[M] = 0
+    const uint64_t* rowoff;           // [M+1] exclusive sum of rowcnt
+    unsigned long long* big;          // set to 1 if a bucket exceeds BUCKET_MAX
+    const uint2* ent;
+    Row* rows;
+    uint64_t rows_cap;
+};
+
+__device__ __forceinline__ uint64_t hit_count(const BucketParams& P) {
+    const unsigned long long n = *P.n_ptr;
+    return n < P.cap ? n : P.cap;
+}
+
+__global__ void __launch_bounds__(256) k7_hist(const BucketParams P) {
+    const uint64_t n = hit_count(P);
+    const int sa = 2 + P.fmt.bits_p + P.fmt.bits_e;
+    for (uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (uint64_t)gridDim.x * blockDim.x)
+        atomicAdd(P.cnt + (uint32_t)(P.hits[i] >> sa), 1u);
+}
+
+__global__ void __launch_bounds__(256) k7_scatter(const BucketParams P) {
+    const uint64_t n = hit_count(P);
+    const int sa = 2 + P.fmt.bits_p + P.fmt.bits_e;
+    for (uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (uint64_t)gridDim.x * blockDim.x) {
+        const uint64_t key = P.hits[i];
+        const uint32_t a = (uint32_t)(key >> sa);
+        P.sorted[P.off[a] + atomicAdd(P.cur + a, 1u)] = key;
+    }
+}
+
+// rows of key i of a sorted run whose predecessor is `prev` (have_prev = false at a run start)
+__device__ __forceinline__ uint32_t key_rows_prev(uint64_t key, uint64_t prev, bool have_prev, int pair_shift) {
+    uint32_t c = (key & HIT_CONT) ? 1u : 0u;
+    if (key & HIT_SP) c += !have_prev || ((prev >> pair_shift) != (key >> pair_shift)) || !(prev & HIT_SP);
+    return c;
+}
+
+__global__ void __launch_bounds__(256) k7_sort(const BucketParams P) {
+    __shared__ uint64_t s_keys[8][BUCKET_MAX];
+    uint64_t* s = s_keys[threadIdx.x >> 5];
+    const uint32_t lane = threadIdx.x & 31;
+    const uint32_t warp = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+    const uint32_t nwarps = (gridDim.x * blockDim.x) >> 5;
+    const int pair_shift = P.fmt.bits_p + 2;
+    for (uint32_t a = warp; a < P.M; a += nwarps) {
+        const uint64_t lo = P.off[a], hi = P.off[a + 1];
+        const uint32_t n = (uint32_t)(hi - lo);
+        if (n == 0) {
+            if (lane == 0) P.rowcnt[a] = 0;
+            continue;
+        }
+        if (hi - lo > BUCKET_MAX) {
+            if (lane == 0) {
+                P.rowcnt[a] = 0;
+                *P.big = 1ull;
+            }
+            continue;
+        }
+        uint32_t np2 = 32;
+        while (np2 < n) np2 <<= 1;
+        for (uint32_t i = lane; i < np2; i += 32) s[i] = i < n ? P.sorted[lo + i] : ~0ull;
+        __syncwarp();
+        if (n > 1) {
+            for (uint32_t k = 2; k <= np2; k <<= 1) {
+                for (uint32_t j = k >> 1; j > 0; j >>= 1) {
+                    for (uint32_t t = lane; t < (np2 >> 1); t += 32) {
+                        const uint32_t i = ((t & ~(j - 1)) << 1) | (t & (j - 1));
+                        const uint32_t x = i | j;
+                        const uint64_t u = s[i], v = s[x];
+                        if ((u > v) == ((i & k) == 0)) {
+                            s[i] = v;
+                            s[x] = u;
+                        }
+                    }
+                    __syncwarp();
+                }
+            }
+        }
+        uint32_t c = 0;
+        for (uint32_t i = lane; i < n; i += 32) {
+            const uint64_t key = s[i];
+            P.sorted[lo + i] = key;
+            c += key_rows_prev(key, i ? s[i - 1] : 0ull, i != 0, pair_shift);
+        }
+#pragma unroll
+        for (int d = 16; d > 0; d >>= 1) c += __shfl_xor_sync(FULL, c, d);
+        if (lane == 0) P.rowcnt[a] = c;
+        __syncwarp();
+    }
+}
+
+__global__ void __launch_bounds__(256) k7_emit(const BucketParams P) {
+    const uint32_t lane = threadIdx.x & 31;
+    const uint32_t warp = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+    const uint32_t nwarps = (gridDim.x * blockDim.x) >> 5;
+    const int pair_shift = P.fmt.bits_p + 2;
+    for (uint32_t a = warp; a < P.M; a += nwarps) {
+        const uint64_t lo = P.off[a], hi = P.off[a + 1];
+        if (hi == lo || hi - lo > BUCKET_MAX) continue;
+        const uint32_t n = (uint32_t)(hi - lo);
+        const uint32_t la = __ldg(P.ent + a).y;
+        uint64_t o = P.rowoff[a];
+        for (uint32_t i0 = 0; i0 < n; i0 += 32) {
+            const uint32_t i = i0 + lane;
+            uint64_t key = 0;
+            uint32_t c = 0;
+            if (i < n) {
+                key = P.sorted[lo + i];
+                c = key_rows_prev(key, i ? P.sorted[lo + i - 1] : 0ull, i != 0, pair_shift);
+            }
+            uint32_t inc = c;  // inclusive warp scan
+#pragma unroll
+            for (int d = 1; d < 32; d <<= 1) {
+                const uint32_t v = __shfl_up_sync(FULL, inc, d);
+                if (lane >= (uint32_t)d) inc += v;
+            }
+            if (c) {
+                uint64_t w = o + inc - c;
+                const uint32_t p = P.fmt.p(key), b = P.fmt.b(key);
+                if ((key & HIT_CONT) && w < P.rows_cap) {
+                    const uint32_t lb = __ldg(P.ent + b).y;
+                    P.rows[w] = Row{a, b, p, p + lb, lb};  // R2
+                    ++w;
+                }
+                if (w < o + inc && w < P.rows_cap) P.rows[w] = Row{a, b, p, la, la - p};  // R1 (longest)
+            }
+            o += __shfl_sync(FULL, inc, 31);
+        }
+    }
+}
+
+}  // namespace ovl

@@ -188,18 +188,25 @@ class ExactOverlapper:
         return out
 
     @staticmethod
-    def _rows_array(p: c_void_p, n: int) -> np.ndarray:
+    def _rows_array(p: c_void_p, n: int, copy: bool = True) -> np.ndarray:
         if not n:
             return np.zeros((0, 5), dtype=np.uint32)
         arr = np.ctypeslib.as_array(ctypes.cast(p, ctypes.POINTER(c_uint32)), shape=(n, 5))
-        return arr.copy()
+        if copy:
+            return arr.copy()
+        arr.flags.writeable = False
+        return arr
 
-    def overlaps_arrays(self, min_length) -> np.ndarray:
-        """Rows as a ``(n, 5)`` uint32 array ``(a, b, astart, aend, bend)`` on entry indices."""
+    def overlaps_arrays(self, min_length, copy: bool = True) -> np.ndarray:
+        """Rows as a ``(n, 5)`` uint32 array ``(a, b, astart, aend, bend)`` on entry indices.
+
+        ``copy=False`` returns a read-only view of the library's pinned result buffer (what the C
+        ABI hands out: ``ovl_overlaps`` returns a pointer it owns); it is valid until the next
+        call on this object."""
         l = _as_unsigned(min_length, "overlaps")
         p, n = c_void_p(), c_uint64()
         self._check(self._lib.ovl_overlaps(self._ctx, l, byref(p), byref(n)))
-        return self._rows_array(p, n.value)
+        return self._rows_array(p, n.value, copy)
 
     # split form (device-resident timing)
     def upload(self) -> None:
@@ -211,10 +218,10 @@ class ExactOverlapper:
                                                   byref(n)))
         return n.value
 
-    def fetch_rows(self) -> np.ndarray:
+    def fetch_rows(self, copy: bool = True) -> np.ndarray:
         p, n = c_void_p(), c_uint64()
         self._check(self._lib.ovl_fetch_rows(self._ctx, byref(p), byref(n)))
-        return self._rows_array(p, n.value)
+        return self._rows_array(p, n.value, copy)
 
     def set_collect_stats(self, on: bool) -> None:
         self._check(self._lib.ovl_set_collect_stats(self._ctx, int(bool(on))))
@@ -267,7 +274,7 @@ class ExactOverlapper:
         self._check(self._lib.ovl_comm_gather_rows_device(self._ctx, byref(n)))
         return n.value
 
-    def comm_gather_rows(self) -> np.ndarray:
+    def comm_gather_rows(self, copy: bool = True) -> np.ndarray:
         p, n = c_void_p(), c_uint64()
         self._check(self._lib.ovl_comm_gather_rows(self._ctx, byref(p), byref(n)))
-        return self._rows_array(p, n.value)
+        return self._rows_array(p, n.value, copy)
