@@ -72,6 +72,9 @@ typedef struct {
     float ms_h2d, ms_pack, ms_anchor, ms_scan, ms_sort, ms_verify, ms_emit, ms_d2h;
     float ms_device;           /* pack..emit: ASCII resident in HBM -> rows resident      */
     float ms_total;            /* h2d..d2h                                                */
+    uint32_t radix_fallback;   /* 1: an entry had too many hits for the bucket sort; the    */
+                               /* device-wide radix sort ordered the hit keys instead      */
+    uint32_t reserved0;
 } ovl_stats;
 
 /* ---- lifetime -------------------------------------------------------------------------

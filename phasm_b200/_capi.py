@@ -31,7 +31,8 @@ class OvlStats(Structure):
                                          "retries", "mirror")] +
                 [("verified", c_uint64), ("hits_sent", c_uint64), ("hits_received", c_uint64)] +
                 [(n, c_float) for n in ("ms_h2d", "ms_pack", "ms_anchor", "ms_scan", "ms_sort",
-                                        "ms_verify", "ms_emit", "ms_d2h", "ms_device", "ms_total")])
+                                        "ms_verify", "ms_emit", "ms_d2h", "ms_device", "ms_total")] +
+                [("radix_fallback", c_uint32), ("reserved0", c_uint32)])
 
     def as_dict(self):
         return {n: getattr(self, n) for n, _ in self._fields_}

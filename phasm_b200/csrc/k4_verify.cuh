@@ -210,7 +210,8 @@ constexpr int HEAD_UNROLL = 4;
 // hit key to the rank that owns its A entry before the sort.
 struct Verify2Params {
     const uint64_t* keys;              // candidate keys (flags clear), any order
-    uint64_t n;
+    const unsigned long long* n_ptr;   // their number: a device counter (no host round trip after the scan)
+    uint64_t cap;                      // capacity of `keys` (the counter may exceed it on overflow)
     const uint64_t* packed64;
     const uint2* ent;                  // {gran0, len}
     KeyFmt fmt;
@@ -293,7 +294,8 @@ __device__ __forceinline__ uint4 align_a_dyn(const uint4 b, const uint2 s, uint3
 __global__ void __launch_bounds__(256, 4) k4a_head(const Verify2Params P) {
     __shared__ uint64_t s_buf[8][WBUF];
     const uint32_t lane = threadIdx.x & 31;
-    const uint64_t n_tiles = (P.n + 31) / 32;
+    const uint64_t n_all = *P.n_ptr < P.cap ? *P.n_ptr : P.cap;
+    const uint64_t n_tiles = (n_all + 31) / 32;
     uint64_t* buf = s_buf[threadIdx.x >> 5];
     uint32_t nbuf = 0;
     const uint4* packed128 = reinterpret_cast<const uint4*>(P.packed64);
@@ -302,7 +304,7 @@ __global__ void __launch_bounds__(256, 4) k4a_head(const Verify2Params P) {
         const uint64_t c = tile * 32 + lane;
         uint64_t key = 0;
         CandMeta my = {0, 0, 0, 0, 0};  // n == 0 marks "no candidate" (a real one has n >= l >= 1)
-        if (c < P.n) {
+        if (c < n_all) {
             key = P.keys[c];
             my = cand_meta(P, key);
         }

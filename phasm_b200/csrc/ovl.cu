@@ -33,6 +33,7 @@
 #include "k4_verify.cuh"
 #include "k5_emit.cuh"
 #include "k6_exchange.cuh"
+#include "k7_bucket.cuh"
 #include "nccl_dyn.h"
 
 static_assert(sizeof(ovl_row) == sizeof(ovl::Row), "row layouts must agree");
@@ -59,7 +60,7 @@ struct PinBuf {
 enum Ev { E_H2D0, E_PACK0, E_ANCHOR0, E_SCAN0, E_VERIFY0, E_SORT0, E_EMIT0, E_END, E_D2H0, E_D2H1, E_COUNT };
 
 // device counter block (one 64-bit word each)
-enum Ctr { C_ERR, C_NANC, C_NCAND, C_NHITS, C_SUMM, C_SUMB, C_NSURV, C_TILE_A, C_TILE_B, C_COUNT };  // h_ctr has 2 spare words behind
+enum Ctr { C_ERR, C_NANC, C_NCAND, C_NHITS, C_SUMM, C_SUMB, C_NSURV, C_TILE_A, C_TILE_B, C_BIG, C_COUNT };  // h_ctr has 2 spare words behind
 
 }  // namespace
 
@@ -89,14 +90,19 @@ struct ovl_ctx {
     // ---- device ----
     DevBuf d_ascii, d_src, d_len, d_flags, d_gran0, d_gran_ent, d_ent, d_packed, d_tile0, d_tile_ent, d_xchg, d_pre;
     DevBuf d_table, d_filter, d_next, d_ctr, d_tmp;
-    DevBuf d_cand, d_cand2, d_cnt, d_offs, d_rows, d_cnts;
+    DevBuf d_cand, d_cand2, d_cnt, d_offs, d_rows, d_cnts, d_bkt;
     uint64_t* h_ctr = nullptr;  // pinned mirror of d_ctr
-    uint64_t cand_cap = 0;
+    uint64_t cand_cap = 0;  // candidate keys one pass may emit (d_cand/d_cand2 hold the derived hit capacity)
     uint64_t n_rows = 0;
     PinBuf h_rows;
     bool rows_fetched = false;
     bool gathered = false;  // ovl_comm_gather_rows_device already ran for the current rows
     int collect = 0;
+    // host-side per-call scans of the entry table, cached between calls (reset by ovl_upload)
+    int cache_pairs = -1;            // 1: entry e^1 is the other strand of entry e, for every e
+    uint32_t cache_l = 0;
+    bool cache_l_valid = false;
+    uint64_t cache_nanc = 0, cache_npos = 0;
     int opt_stride = 0;  // 0 = auto; else upper bound on the anchor stride (1 = dense scan)
     int opt_serial_verify = 0;  // 1: chunk-by-chunk early-exit verifier instead of head/tail
     int opt_mirror = 1;         // 1: strand-mirror halving when every entry has its twin
@@ -260,10 +266,7 @@ int exchange_hits(ovl_ctx* c, const ovl::KeyFmt& fmt, uint64_t* n_hits, uint32_t
     unsigned long long* d_cursor = d_counts + R;
     unsigned long long* d_matrix = d_cursor + R;
     CK(cudaMemsetAsync(d_counts, 0, 16ull * R, st));
-    if (n > c->cand_cap) {  // partition output (the candidate buffer is free after the verifier)
-        OVL_TRY(dev_ensure(c, c->d_cand, n * 8, false));
-        c->cand_cap = c->d_cand.cap / 8;
-    }
+    OVL_TRY(dev_ensure(c, c->d_cand, (n ? n : 1) * 8, false));  // partition output (the candidate buffer is free after the verifier)
     if (n) {
         unsigned blocks = (unsigned)((n + 255) / 256);
         if (blocks > (unsigned)c->n_sm * 8) blocks = (unsigned)c->n_sm * 8;
@@ -368,7 +371,7 @@ void ovl_destroy(ovl_ctx* c) {
     DevBuf* bufs[] = {&c->d_ascii, &c->d_src, &c->d_len, &c->d_flags, &c->d_gran0, &c->d_gran_ent,
                       &c->d_ent, &c->d_packed, &c->d_table, &c->d_filter, &c->d_next, &c->d_ctr,
                       &c->d_tmp, &c->d_cand, &c->d_cand2, &c->d_cnt, &c->d_offs, &c->d_rows, &c->d_cnts,
-                      &c->d_tile0, &c->d_tile_ent, &c->d_xchg, &c->d_pre};
+                      &c->d_tile0, &c->d_tile_ent, &c->d_xchg, &c->d_pre, &c->d_bkt};
     for (DevBuf* b : bufs)
         if (b->p) cudaFree(b->p);
     if (c->ascii.p) cudaFreeHost(c->ascii.p);
@@ -618,6 +621,8 @@ int ovl_upload(ovl_ctx* c) {
     CK(cudaStreamSynchronize(c->st));  // the pageable vectors above must not change under the copy
     c->stats.ms_h2d = ev_ms(c, E_H2D0, E_PACK0);
     c->uploaded = true;
+    c->cache_pairs = -1;
+    c->cache_l_valid = false;
     return OVL_OK;
 }
 
@@ -645,8 +650,12 @@ int ovl_overlaps_device(ovl_ctx* c, uint32_t min_length, uint64_t* n_rows_out) {
     if (n_rows_out) *n_rows_out = 0;
     if (M == 0) return OVL_OK;  // the reference segfaults here; we return no rows
     // strand-mirror halving needs entry e ^ 1 to be the other strand of entry e, for every e
-    bool mirror = c->opt_mirror && (M % 2 == 0);
-    for (uint32_t e = 0; mirror && e < M; e += 2) mirror = !(c->flags[e] & 1) && (c->flags[e + 1] & 1);
+    if (c->cache_pairs < 0) {
+        bool pairs = M % 2 == 0;
+        for (uint32_t e = 0; pairs && e < M; e += 2) pairs = !(c->flags[e] & 1) && (c->flags[e + 1] & 1);
+        c->cache_pairs = pairs ? 1 : 0;
+    }
+    const bool mirror = c->opt_mirror && c->cache_pairs == 1;
     S.mirror = mirror ? 1u : 0u;
     ovl::MirrorRule mrule;
     mrule.on = mirror ? 1 : 0;
@@ -659,6 +668,20 @@ int ovl_overlaps_device(ovl_ctx* c, uint32_t min_length, uint64_t* n_rows_out) {
     if (fmt.total() > 64)
         return fail(c, OVL_E_LIMIT, "candidate key needs %d bits (entries %u, longest %llu): over the 64-bit key layout",
                     fmt.total(), M, (unsigned long long)c->max_len);
+    // host-known sizes (no device round trip): anchors, scan positions
+    if (!c->cache_l_valid || c->cache_l != l) {
+        uint64_t na = 0, np = 0;
+        for (uint32_t e = 0; e < M; ++e) na += c->len[e] >= l;
+        for (uint32_t e = c->e_lo; e < c->e_hi; ++e)
+            if (c->len[e] >= l) np += c->len[e] - l + 1;
+        c->cache_nanc = na;
+        c->cache_npos = np;
+        c->cache_l = l;
+        c->cache_l_valid = true;
+    }
+    const uint64_t n_anc = c->cache_nanc, npos = c->cache_npos;
+    S.anchors = n_anc;
+    S.scan_positions = npos;
     // anchor stride: largest power of two <= min(64, l-k+1); 1 = canonical dense scan
     int slog = 0;
     {
@@ -675,8 +698,7 @@ int ovl_overlaps_device(ovl_ctx* c, uint32_t min_length, uint64_t* n_rows_out) {
         // profiles/r01d_stride_sweep.txt).  A dense scan (stride 1) is only taken when l < 33
         // forces it.
         if (c->opt_stride == 0 && slog > 1) {
-            uint64_t n_b = 0;
-            for (uint32_t e = 0; e < M; ++e) n_b += c->len[e] >= l;
+            const uint64_t n_b = n_anc;
             const double gl = (double)(c->gran0[c->e_hi] - c->gran0[c->e_lo]) / 12.9e6;
             const double al = (double)n_b / 55200.0;
             static const double scan_ms[7] = {0, 1.7, 1.0, 0.68, 0.50, 0.41, 0.35};       // stride 2^i
@@ -704,14 +726,6 @@ int ovl_overlaps_device(ovl_ctx* c, uint32_t min_length, uint64_t* n_rows_out) {
     uint64_t* ctr = c->d_ctr.as<uint64_t>();
     uint32_t launches = 0, lib = 0;
     const int nsm = c->n_sm;
-
-    // host-known sizes (no device round trip): anchors, scan positions
-    uint64_t n_anc = 0, npos = 0;
-    for (uint32_t e = 0; e < M; ++e) n_anc += c->len[e] >= l;
-    for (uint32_t e = c->e_lo; e < c->e_hi; ++e)
-        if (c->len[e] >= l) npos += c->len[e] - l + 1;
-    S.anchors = n_anc;
-    S.scan_positions = npos;
 
     CK(cudaEventRecord(c->ev[E_PACK0], st));
     CK(cudaMemsetAsync(ctr, 0, C_COUNT * sizeof(uint64_t), st));
@@ -838,7 +852,6 @@ int ovl_overlaps_device(ovl_ctx* c, uint32_t min_length, uint64_t* n_rows_out) {
         if (bm_bits < 15) bm_bits = 15;
         if (bm_bits > 31) bm_bits = 31;
     }
-    uint64_t n_cand = 0;
     if (have_a) {
         const size_t filter_bytes = dense ? (4ull << bm_bits) : ((1ull << bm_bits) / 8);
         const size_t table_bytes = sizeof(Slot) * (1ull << tbits);
@@ -869,14 +882,33 @@ int ovl_overlaps_device(ovl_ctx* c, uint32_t min_length, uint64_t* n_rows_out) {
         }
         CK(cudaEventRecord(c->ev[E_SCAN0], st));
 
-        // ---- K3: scan (re-run with the exact size if the candidate buffer was too small) ------
-        if (c->cand_cap == 0) {
-            uint64_t cap = 96ull * (c->e_hi - c->e_lo);
-            if (cap < (1ull << 20)) cap = 1ull << 20;
-            OVL_TRY(dev_ensure(c, c->d_cand, cap * 8, false));
-            c->cand_cap = c->d_cand.cap / 8;
-        }
-        for (int attempt = 0;; ++attempt) {
+    } else {
+        CK(cudaEventRecord(c->ev[E_SCAN0], st));
+    }
+
+    // ---- K3 .. K5 without host round trips ---------------------------------------------------
+    // Every buffer is sized by CAPACITY and every kernel reads its input size from the device
+    // counter block, so a single-GPU pass synchronises with the host once, at its end.  Only the
+    // accounting / serial-verifier modes and the multi-GPU hit exchange (NCCL needs the counts)
+    // read counters in between.  A candidate overflow is detected at the end: the buffers grow and
+    // the pass from K3 on is repeated.
+    const bool host_n = c->collect || c->opt_serial_verify || xchg;
+    if (c->cand_cap == 0) {
+        uint64_t cap = 96ull * (c->e_hi - c->e_lo);
+        if (cap < (1ull << 20)) cap = 1ull << 20;
+        c->cand_cap = cap;
+    }
+    uint64_t n_cand = 0, n_hits = 0, n_rows = 0, hit_cap = 0;
+    const uint32_t kblocks = (uint32_t)nsm * 8;
+    for (int attempt = 0;; ++attempt) {
+        if (c->cand_cap > 0x7fffffffull) return fail(c, OVL_E_LIMIT, "more than 2^31 candidates on one GPU");
+        hit_cap = mirror ? 3 * c->cand_cap : c->cand_cap;  // own key + SP twin + CONT twin
+        OVL_TRY(dev_ensure(c, c->d_cand, hit_cap * 8, false));   // candidates, later the sorted hit keys
+        OVL_TRY(dev_ensure(c, c->d_cand2, hit_cap * 8, false));  // hit keys
+        OVL_TRY(dev_ensure(c, c->d_cnt, c->cand_cap * 4, false));  // survivor list
+        OVL_TRY(dev_ensure(c, c->d_rows, hit_cap * sizeof(Row), false));
+        if (attempt) CK(cudaMemsetAsync(ctr + C_NCAND, 0, (C_COUNT - C_NCAND) * sizeof(uint64_t), st));
+        if (have_a) {
             ScanParams P;
             P.packed = c->d_packed.as<uint4>();
             P.gran_ent = c->d_gran_ent.as<uint32_t>();
@@ -908,55 +940,48 @@ int ovl_overlaps_device(ovl_ctx* c, uint32_t min_length, uint64_t* n_rows_out) {
             }
             ++launches;
             CK(cudaGetLastError());
+        }
+        if (host_n) {
             OVL_TRY(read_ctr(c));
             OVL_TRY(check_alphabet());
             n_cand = c->h_ctr[C_NCAND];
-            if (n_cand <= c->cand_cap) break;
-            if (attempt >= 2) return fail(c, OVL_E_LIMIT, "candidate buffer overflow persists (%llu)", (unsigned long long)n_cand);
-            ++S.retries;
-            OVL_TRY(dev_ensure(c, c->d_cand, (n_cand + n_cand / 16) * 8, false));
-            c->cand_cap = c->d_cand.cap / 8;
-            CK(cudaMemsetAsync(ctr + C_NCAND, 0, 8, st));
+            if (n_cand > c->cand_cap) {
+                if (attempt >= 2) return fail(c, OVL_E_LIMIT, "candidate buffer overflow persists (%llu)", (unsigned long long)n_cand);
+                ++S.retries;
+                c->cand_cap = n_cand + n_cand / 16;
+                continue;
+            }
         }
-    } else {
-        CK(cudaEventRecord(c->ev[E_SCAN0], st));
-    }
-    S.candidates = n_cand;
-    S.verified = n_cand;
-    if (n_cand == 0 && !xchg) return finish_from(E_VERIFY0);
-    if (n_cand > 0x7fffffffull) return fail(c, OVL_E_LIMIT, "more than 2^31 candidates on one GPU (%llu)", (unsigned long long)n_cand);
 
-    // ---- K4: verify -----------------------------------------------------------------------
-    CK(cudaEventRecord(c->ev[E_VERIFY0], st));
-    if (wait_packed) CK(cudaStreamWaitEvent(st, c->ev_comm, 0));  // the operands of other ranks' entries
-    const uint64_t hit_cap = mirror ? 3 * n_cand : n_cand;  // own key + SP twin + CONT twin
-    uint64_t n_hits = 0;
-    if (n_cand) {
-        OVL_TRY(dev_ensure(c, c->d_cand2, hit_cap * 8));  // hit keys
-        OVL_TRY(dev_ensure(c, c->d_cnt, hit_cap * 4));    // survivor list now, row counts in K5
+        // ---- K4: verify -------------------------------------------------------------------
+        CK(cudaEventRecord(c->ev[E_VERIFY0], st));
+        if (wait_packed) CK(cudaStreamWaitEvent(st, c->ev_comm, 0));  // the operands of other ranks' entries
         CandSink hits;
         hits.out = c->d_cand2.as<uint64_t>();
         hits.n_out = reinterpret_cast<unsigned long long*>(ctr + C_NHITS);
         hits.cap = hit_cap;
-        uint64_t blocks = (n_cand + 255) / 256;
-        if (blocks > (uint64_t)nsm * 8) blocks = (uint64_t)nsm * 8;
         if (c->collect || c->opt_serial_verify) {
-            VerifyParams V;
-            V.keys = c->d_cand.as<uint64_t>();
-            V.n = n_cand;
-            V.packed = c->d_packed.as<uint4>();
-            V.ent = c->d_ent.as<uint2>();
-            V.fmt = fmt;
-            V.hits = hits;
-            V.counters = reinterpret_cast<unsigned long long*>(ctr + C_SUMM);
-            V.collect = c->collect;
-            V.mirror = mrule;
-            k4_verify_serial<<<(unsigned)blocks, 256, 0, st>>>(V);
-            ++launches;
+            if (n_cand) {
+                VerifyParams V;
+                V.keys = c->d_cand.as<uint64_t>();
+                V.n = n_cand;
+                V.packed = c->d_packed.as<uint4>();
+                V.ent = c->d_ent.as<uint2>();
+                V.fmt = fmt;
+                V.hits = hits;
+                V.counters = reinterpret_cast<unsigned long long*>(ctr + C_SUMM);
+                V.collect = c->collect;
+                V.mirror = mrule;
+                uint64_t blocks = (n_cand + 255) / 256;
+                if (blocks > kblocks) blocks = kblocks;
+                k4_verify_serial<<<(unsigned)blocks, 256, 0, st>>>(V);
+                ++launches;
+            }
         } else {
             Verify2Params V;
             V.keys = c->d_cand.as<uint64_t>();
-            V.n = n_cand;
+            V.n_ptr = reinterpret_cast<const unsigned long long*>(ctr + C_NCAND);
+            V.cap = c->cand_cap;
             V.packed64 = reinterpret_cast<const uint64_t*>(c->d_packed.p);
             V.ent = c->d_ent.as<uint2>();
             V.fmt = fmt;
@@ -965,54 +990,117 @@ int ovl_overlaps_device(ovl_ctx* c, uint32_t min_length, uint64_t* n_rows_out) {
             V.hits = hits;
             V.mirror = mrule;
             V.tile_ctr = reinterpret_cast<unsigned long long*>(ctr + C_TILE_A);
-            k4a_head<<<(unsigned)blocks, 256, 0, st>>>(V);
-            k4b_tail<<<nsm * 8, 256, 0, st>>>(V);
+            k4a_head<<<kblocks, 256, 0, st>>>(V);
+            k4b_tail<<<kblocks, 256, 0, st>>>(V);
             launches += 2;
         }
         CK(cudaGetLastError());
-        OVL_TRY(read_ctr(c));
-        n_hits = c->h_ctr[C_NHITS];
-        S.compared_bases = c->h_ctr[C_SUMM];
-        S.operand_bytes = c->h_ctr[C_SUMB];
-        if (n_hits > hit_cap) return fail(c, OVL_E_LIMIT, "hit list overflow (%llu > %llu): internal error", (unsigned long long)n_hits, (unsigned long long)hit_cap);
-    }
-    S.hits = n_hits;
-    // ---- multi-GPU mirror mode: every hit key goes to the rank that owns its A entry ---------
-    CK(cudaEventRecord(c->ev[E_SORT0], st));
-    if (xchg) OVL_TRY(exchange_hits(c, fmt, &n_hits, &launches, &lib));
-    if (n_hits == 0) return finish_from(E_EMIT0);
+        CK(cudaEventRecord(c->ev[E_SORT0], st));
+        uint64_t keys_cap = hit_cap;  // capacity of d_cand2 in keys, as the bucket kernels see it
+        if (host_n) {
+            OVL_TRY(read_ctr(c));
+            n_hits = c->h_ctr[C_NHITS];
+            S.compared_bases = c->h_ctr[C_SUMM];
+            S.operand_bytes = c->h_ctr[C_SUMB];
+            if (n_hits > hit_cap) return fail(c, OVL_E_LIMIT, "hit list overflow (%llu > %llu): internal error", (unsigned long long)n_hits, (unsigned long long)hit_cap);
+            // multi-GPU mirror mode: every hit key goes to the rank that owns its A entry
+            if (xchg) {
+                OVL_TRY(exchange_hits(c, fmt, &n_hits, &launches, &lib));
+                if (n_hits > 0xfffffff0ull) return fail(c, OVL_E_LIMIT, "more than 2^32 hit keys on one GPU");
+                c->h_ctr[C_NHITS] = n_hits;
+                CK(cudaMemcpyAsync(ctr + C_NHITS, &c->h_ctr[C_NHITS], 8, cudaMemcpyHostToDevice, st));
+                keys_cap = c->d_cand2.cap / 8;
+                OVL_TRY(dev_ensure(c, c->d_cand, n_hits * 8, false));
+                OVL_TRY(dev_ensure(c, c->d_rows, n_hits * sizeof(Row), false));
+            }
+        }
 
-    // ---- sort the hit keys by (a, b, p) --------------------------------------------------------
-    if (n_hits > c->cand_cap) {  // mirror mode can return more entries than candidates
-        OVL_TRY(dev_ensure(c, c->d_cand, n_hits * 8, false));
-        c->cand_cap = c->d_cand.cap / 8;
+        // ---- order the hit keys by (a, b, p, flags) and emit rows: k7_bucket.cuh ------------------
+        const size_t M1 = (size_t)M + 1;
+        OVL_TRY(dev_ensure(c, c->d_bkt, M1 * (8 + 8 + 4 + 4 + 4)));
+        uint64_t* b_off = c->d_bkt.as<uint64_t>();
+        uint64_t* b_rowoff = b_off + M1;
+        uint32_t* b_cnt = reinterpret_cast<uint32_t*>(b_rowoff + M1);
+        uint32_t* b_cur = b_cnt + M1;
+        uint32_t* b_rowcnt = b_cur + M1;
+        size_t tb = 0;
+        CK(cub::DeviceScan::ExclusiveSum(nullptr, tb, b_cnt, b_off, (int)M1, st));
+        OVL_TRY(dev_ensure(c, c->d_tmp, tb));
+        BucketParams B;
+        B.hits = c->d_cand2.as<uint64_t>();
+        B.n_ptr = reinterpret_cast<const unsigned long long*>(ctr + C_NHITS);
+        B.cap = keys_cap;
+        B.fmt = fmt;
+        B.M = M;
+        B.cnt = b_cnt;
+        B.off = b_off;
+        B.cur = b_cur;
+        B.sorted = c->d_cand.as<uint64_t>();
+        B.rowcnt = b_rowcnt;
+        B.rowoff = b_rowoff;
+        B.big = reinterpret_cast<unsigned long long*>(ctr + C_BIG);
+        B.ent = c->d_ent.as<uint2>();
+        B.rows = c->d_rows.as<Row>();
+        B.rows_cap = c->d_rows.cap / sizeof(Row);
+        uint32_t wblocks = (M + 7) / 8;
+        if (wblocks > (uint32_t)nsm * 16) wblocks = (uint32_t)nsm * 16;
+        CK(cudaMemsetAsync(b_cnt, 0, M1 * 12, st));  // cnt, cur, rowcnt
+        k7_hist<<<kblocks, 256, 0, st>>>(B);
+        tb = c->d_tmp.cap;
+        CK(cub::DeviceScan::ExclusiveSum(c->d_tmp.p, tb, b_cnt, b_off, (int)M1, st));
+        k7_scatter<<<kblocks, 256, 0, st>>>(B);
+        k7_sort<<<wblocks, 256, 0, st>>>(B);
+        CK(cudaEventRecord(c->ev[E_EMIT0], st));
+        tb = c->d_tmp.cap;
+        CK(cub::DeviceScan::ExclusiveSum(c->d_tmp.p, tb, b_rowcnt, b_rowoff, (int)M1, st));
+        k7_emit<<<wblocks, 256, 0, st>>>(B);
+        launches += 4;
+        lib += 2;
+        CK(cudaGetLastError());
+        CK(cudaMemcpyAsync(&c->h_ctr[C_COUNT], b_rowoff + M, 8, cudaMemcpyDeviceToHost, st));
+        CK(cudaEventRecord(c->ev[E_END], st));
+        OVL_TRY(read_ctr(c));  // the one synchronisation of a single-GPU pass
+        OVL_TRY(check_alphabet());
+        if (!host_n) {
+            n_cand = c->h_ctr[C_NCAND];
+            if (n_cand > c->cand_cap) {
+                if (attempt >= 2) return fail(c, OVL_E_LIMIT, "candidate buffer overflow persists (%llu)", (unsigned long long)n_cand);
+                ++S.retries;
+                c->cand_cap = n_cand + n_cand / 16;
+                continue;
+            }
+            n_hits = c->h_ctr[C_NHITS];
+            if (n_hits > hit_cap) return fail(c, OVL_E_LIMIT, "hit list overflow (%llu > %llu): internal error", (unsigned long long)n_hits, (unsigned long long)hit_cap);
+        }
+        n_rows = c->h_ctr[C_COUNT];
+        break;
     }
-    uint64_t* keys = c->d_cand.as<uint64_t>();  // the candidate buffer is free again
-    {
+    S.candidates = n_cand;
+    S.verified = n_cand;
+    S.hits = n_hits;
+
+    // ---- an A entry with more than BUCKET_MAX hits: redo the ordering with the device-wide radix
+    //      sort (library call) and the per-key K5 kernels ------------------------------------------
+    if (c->h_ctr[C_BIG] && n_hits) {
+        S.radix_fallback = 1;
+        uint64_t* keys = c->d_cand.as<uint64_t>();
         size_t tb = 0;
         CK(cub::DeviceRadixSort::SortKeys(nullptr, tb, c->d_cand2.as<uint64_t>(), keys, (int)n_hits, 0, fmt.total(), st));
         OVL_TRY(dev_ensure(c, c->d_tmp, tb));
         tb = c->d_tmp.cap;
         CK(cub::DeviceRadixSort::SortKeys(c->d_tmp.p, tb, c->d_cand2.as<uint64_t>(), keys, (int)n_hits, 0, fmt.total(), st));
         ++lib;
-    }
-    CK(cudaEventRecord(c->ev[E_EMIT0], st));
-
-    // ---- K5: select longest, compact ---------------------------------------------------------
-    uint64_t n_rows = 0;
-    {
         OVL_TRY(dev_ensure(c, c->d_cnt, n_hits * 4));
         OVL_TRY(dev_ensure(c, c->d_offs, (n_hits + 1) * 8));
         const unsigned nb = (unsigned)((n_hits + 255) / 256);
         k5_count<<<nb, 256, 0, st>>>(keys, n_hits, fmt, c->d_cnt.as<uint32_t>());
         ++launches;
-        size_t tb = 0;
+        tb = 0;
         CK(cub::DeviceScan::ExclusiveSum(nullptr, tb, c->d_cnt.as<uint32_t>(), c->d_offs.as<uint64_t>(), (int)n_hits, st));
         OVL_TRY(dev_ensure(c, c->d_tmp, tb));
         tb = c->d_tmp.cap;
         CK(cub::DeviceScan::ExclusiveSum(c->d_tmp.p, tb, c->d_cnt.as<uint32_t>(), c->d_offs.as<uint64_t>(), (int)n_hits, st));
         ++lib;
-        // total = offs[n-1] + cnt[n-1]
         CK(cudaMemcpyAsync(&c->h_ctr[C_COUNT], c->d_offs.as<uint64_t>() + (n_hits - 1), 8, cudaMemcpyDeviceToHost, st));
         CK(cudaMemcpyAsync(&c->h_ctr[C_COUNT + 1], c->d_cnt.as<uint32_t>() + (n_hits - 1), 4, cudaMemcpyDeviceToHost, st));
         CK(cudaStreamSynchronize(st));
@@ -1024,9 +1112,9 @@ int ovl_overlaps_device(ovl_ctx* c, uint32_t min_length, uint64_t* n_rows_out) {
             ++launches;
             CK(cudaGetLastError());
         }
+        CK(cudaEventRecord(c->ev[E_END], st));
+        CK(cudaStreamSynchronize(st));
     }
-    CK(cudaEventRecord(c->ev[E_END], st));
-    CK(cudaStreamSynchronize(st));
     c->n_rows = n_rows;
     S.rows = n_rows;
     stage_times();

@@ -362,3 +362,49 @@ def test_self_reverse_complement_pairs_are_reported(ov):
     rows = ov.overlaps(4)
     assert ("pal+", "pal-", 0, 16, 0, 16) in rows and ("pal-", "pal+", 0, 16, 0, 16) in rows
     assert rows.count(("pal+", "pal-", 0, 16, 0, 16)) == 2   # R1 + R2 duplicate row
+
+
+# ---- hit ordering: bucket sort (default) and its radix-sort fallback ---------------------------
+def test_heavy_entries_take_the_radix_fallback(ov):
+    """An entry with more hits than one warp's bucket (k7_bucket.cuh BUCKET_MAX) makes the call
+    fall back to the device-wide radix sort; rows must not change.  300 copies of one read give
+    every entry ~600 hits; a second, ordinary set afterwards must be back on the bucket path."""
+    from oracle import port
+    from oracle.bruteforce import both_strand_entries
+    rng = random.Random(77)
+    base = "".join(rng.choice("ACGT") for _ in range(300))
+    other = "".join(rng.choice("ACGT") for _ in range(500))
+    reads = [("d%03d" % i, base) for i in range(300)] + [("x0", other), ("x1", other[100:] + base[:150])]
+    ebuf, eoff = port.entries_to_buffer(both_strand_entries(reads))
+    for l in (100, 300):
+        want, _ = port.oracle_overlaps(ebuf, eoff, l)
+        got = run_reads_idx(ov, reads, l)
+        st = ov.stats()
+        assert st["radix_fallback"] == 1, st
+        assert np.array_equal(got, want), l
+    key = sorted(helpers.MID_SPECS)[0]
+    reads2, l2 = helpers.mid_input(key)
+    assert np.array_equal(run_reads_idx(ov, reads2, l2), sort_rows(helpers.load_mid()[key]))
+    assert ov.stats()["radix_fallback"] == 0
+
+
+def test_bucket_path_matches_serial_and_nonmirror_variants(ov):
+    """The single-synchronisation pipeline (device-side counts) against the modes that still read
+    counters on the host (serial verifier, accounting pass), mirror on and off."""
+    from phasm_b200 import synth
+    sh = synth.CONFIGS[4].scaled(0.01)
+    buf, off, names = synth.generate(sh)
+    reads = helpers.reads_of(buf, off, names)
+    base = run_reads_idx(ov, reads, sh.min_length)
+    assert len(base) > 0
+    try:
+        for opt, val in (("serial_verify", 1), ("mirror", 0)):
+            ov.set_option(opt, val)
+            assert np.array_equal(run_reads_idx(ov, reads, sh.min_length), base), opt
+            ov.set_option(opt, 1 - val)
+        ov.set_collect_stats(True)
+        assert np.array_equal(run_reads_idx(ov, reads, sh.min_length), base)
+    finally:
+        ov.set_collect_stats(False)
+        ov.set_option("serial_verify", 0)
+        ov.set_option("mirror", 1)
