@@ -44,6 +44,13 @@ struct ScanParams {
 };
 
 // ---- sparse path ------------------------------------------------------------------------
+// SL >= 0: the stride is the compile-time constant 2^SL (6 and 5 are instantiated: one or two
+// word-aligned k-mers per granule, no shifts); SL < 0: read it from the parameters.
+// The warp's NEXT tile (packed granule + entry index) is loaded before the current one is
+// processed, and the filter words are requested before the entry record is needed, so the
+// dependent chain per tile is filter -> table slot -> anchor list, all L2 hits (ncu r01f: 60 % of
+// the stall samples of the previous form waited on exactly these loads one after the other).
+template <int SL>
 __global__ void __launch_bounds__(256) k3_probe(const ScanParams P) {
     __shared__ uint64_t s_buf[8][WBUF];
     const uint32_t lane = threadIdx.x & 31;
@@ -54,41 +61,60 @@ __global__ void __launch_bounds__(256) k3_probe(const ScanParams P) {
     const uint32_t n_tiles = (n_gran + 31) / 32;
     const uint64_t kmask = kmer_mask(P.k);
     const uint64_t* packed64 = reinterpret_cast<const uint64_t*>(P.packed);
-    const uint32_t stride = 1u << P.stride_log2;
-    const uint32_t n_probe = GRAN_BASES >> P.stride_log2;
+    const int sl = SL >= 0 ? SL : P.stride_log2;
+    const uint32_t stride = 1u << sl;
+    const uint32_t n_probe = GRAN_BASES >> sl;
     uint64_t* buf = s_buf[wib];
     uint32_t nbuf = 0;
 
+    uint4 v_nx = make_uint4(0, 0, 0, 0);
+    uint32_t a_nx = 0;
+    if (warp < n_tiles) {
+        const uint32_t g = P.g_begin + warp * 32 + lane;
+        if (g < P.g_end) {
+            v_nx = ldg_stream(P.packed + g);
+            a_nx = __ldg(P.gran_ent + g);
+        }
+    }
     for (uint32_t tile = warp; tile < n_tiles; tile += nwarps) {
         const uint32_t g = P.g_begin + tile * 32 + lane;
         const bool inr = g < P.g_end;
-        uint64_t w0 = 0, w1 = 0;
-        uint32_t a = 0, pos0 = 0, L = 0;
-        if (inr) {
-            const uint4 v = ldg_stream(P.packed + g);
-            w0 = (uint64_t)v.x | ((uint64_t)v.y << 32);
-            w1 = (uint64_t)v.z | ((uint64_t)v.w << 32);
-            a = __ldg(P.gran_ent + g);
-            const uint2 m = __ldg(P.ent + a);
-            L = m.y;
-            pos0 = (g - m.x) * GRAN_BASES;
+        const uint4 v = v_nx;
+        const uint32_t a = a_nx;
+        {  // prefetch the next tile of this warp
+            const uint32_t gn = g + nwarps * 32;
+            if (tile + nwarps < n_tiles && gn < P.g_end) {
+                v_nx = ldg_stream(P.packed + gn);
+                a_nx = __ldg(P.gran_ent + gn);
+            }
         }
-        uint64_t w2 = __shfl_down_sync(FULL, w0, 1);
-        if (lane == 31 && P.stride_log2 < 5) w2 = inr ? packed64[2ull * (g + 1)] : 0;
-        const bool a_ok = inr && L >= P.l;
-
-        // phase 1: filter bit of every probed position of this granule (independent loads)
-        uint32_t hitmask = 0;
-        if (a_ok) {
+        const uint64_t w0 = (uint64_t)v.x | ((uint64_t)v.y << 32);
+        const uint64_t w1 = (uint64_t)v.z | ((uint64_t)v.w << 32);
+        uint2 m = make_uint2(0, 0);
+        if (inr) m = __ldg(P.ent + a);
+        uint64_t w2 = 0;
+        if (sl < 5) {  // k-mers that start in the second word run into the next granule
+            w2 = __shfl_down_sync(FULL, w0, 1);
+            if (lane == 31) w2 = inr ? packed64[2ull * (g + 1)] : 0;
+        }
+        // phase 1: filter bit of every probed position of this granule (independent loads, issued
+        // before the entry record is looked at)
+        uint32_t fbits = 0;
+        if (inr) {
 #pragma unroll 4
             for (uint32_t j = 0; j < n_probe; ++j) {
-                const uint32_t off = j << P.stride_log2;
-                if (pos0 + off + (uint32_t)P.k <= L) {
-                    const uint64_t x = (off < 32 ? kmer_at(w0, w1, off) : kmer_at(w1, w2, off - 32)) & kmask;
-                    const uint32_t bit = bitmap_bit(mix64(x), P.bm_bits);
-                    hitmask |= ((__ldg(P.filter + (bit >> 5)) >> (bit & 31)) & 1u) << j;
-                }
+                const uint32_t off = j << sl;
+                const uint64_t x = (off < 32 ? kmer_at(w0, w1, off) : kmer_at(w1, w2, off - 32)) & kmask;
+                const uint32_t bit = bitmap_bit(mix64(x), P.bm_bits);
+                fbits |= ((__ldg(P.filter + (bit >> 5)) >> (bit & 31)) & 1u) << j;
             }
+        }
+        const uint32_t L = m.y;
+        const uint32_t pos0 = (g - m.x) * GRAN_BASES;
+        uint32_t hitmask = 0;
+        if (inr && L >= P.l && pos0 + (uint32_t)P.k <= L) {
+            const uint32_t nv = ((L - (uint32_t)P.k - pos0) >> sl) + 1u;  // probes with pos0 + off + k <= L
+            hitmask = nv >= 32 ? fbits : (fbits & ((1u << nv) - 1u));
         }
         // phase 2: resolve the (few) filter hits against the table, one position per lane per round
         while (__any_sync(FULL, hitmask != 0)) {
@@ -96,7 +122,7 @@ __global__ void __launch_bounds__(256) k3_probe(const ScanParams P) {
             if (hitmask) {
                 const uint32_t j = __ffs(hitmask) - 1;
                 hitmask &= hitmask - 1;
-                const uint32_t off = j << P.stride_log2;
+                const uint32_t off = j << sl;
                 q = pos0 + off;
                 const uint64_t x = (off < 32 ? kmer_at(w0, w1, off) : kmer_at(w1, w2, off - 32)) & kmask;
                 node = table_find(P.table, P.tbits, mix64(x));
@@ -105,15 +131,16 @@ __global__ void __launch_bounds__(256) k3_probe(const ScanParams P) {
                 bool have = false;
                 uint64_t key = 0;
                 if (node != NIL) {
-                    const uint32_t b = node >> P.stride_log2;
+                    const uint32_t b = node >> sl;
                     const uint32_t delta = node & (stride - 1u);
+                    const uint32_t nxt = __ldg(P.next + node);
                     // candidate p = q - delta: needs p >= 0, |a| - p >= l, and b != a
                     // (identity by index: overlapper.cpp:72-74,101-104)
                     if (q >= delta && b != a && L - (q - delta) >= P.l) {
                         have = !P.mirror.on || mirror_items(P.mirror, a, L, b, __ldg(P.ent + b).y, q - delta) != 0;
                         key = P.fmt.make(a, b, q - delta);
                     }
-                    node = __ldg(P.next + node);
+                    node = nxt;
                 }
                 wbuf_push(buf, nbuf, P.sink, lane, have, key);
             }

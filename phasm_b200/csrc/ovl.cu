@@ -932,7 +932,9 @@ int ovl_overlaps_device(ovl_ctx* c, uint32_t min_length, uint64_t* n_rows_out) {
                 const uint32_t tiles = (g_hi - g_lo + 31) / 32;
                 uint32_t blocks = (tiles + 7) / 8;
                 if (blocks > (uint32_t)nsm * 8) blocks = (uint32_t)nsm * 8;
-                k3_probe<<<blocks, 256, 0, st>>>(P);
+                if (slog == 6) k3_probe<6><<<blocks, 256, 0, st>>>(P);
+                else if (slog == 5) k3_probe<5><<<blocks, 256, 0, st>>>(P);
+                else k3_probe<-1><<<blocks, 256, 0, st>>>(P);
             } else if (smem_filter) {
                 k3_scan<true><<<nsm, 1024, 32 * WBUF * 8 + (4u << bm_bits), st>>>(P);
             } else {
