@@ -67,9 +67,10 @@ enum Ctr { C_ERR, C_NANC, C_NCAND, C_NHITS, C_SUMM, C_SUMB, C_NSURV, C_TILE_A, C
 struct ovl_ctx {
     int device = 0;
     int n_sm = 148;
-    cudaStream_t st = nullptr, st_comm = nullptr;
+    cudaStream_t st = nullptr, st_comm = nullptr, st_k2 = nullptr;
     cudaEvent_t ev[E_COUNT] = {};
     cudaEvent_t ev_comm = nullptr, ev_pack = nullptr, ev_pre = nullptr;
+    cudaEvent_t ev_k0 = nullptr, ev_prel = nullptr, ev_k2 = nullptr;  // fork/join of the anchor-build stream
     cudaEvent_t ev_t0 = nullptr, ev_t1 = nullptr;  // ovl_timer_*
     std::string err;
 
@@ -106,6 +107,7 @@ struct ovl_ctx {
     int opt_stride = 0;  // 0 = auto; else upper bound on the anchor stride (1 = dense scan)
     int opt_serial_verify = 0;  // 1: chunk-by-chunk early-exit verifier instead of head/tail
     int opt_mirror = 1;         // 1: strand-mirror halving when every entry has its twin
+    int opt_pack_bpsm = 16;     // K1 blocks per SM (fewer leave room for the concurrent anchor build)
     ovl_stats stats{};
 
     // ---- multi-GPU ----
@@ -346,6 +348,10 @@ int ovl_create(int device, ovl_ctx** out) {
     auto init = [&]() -> int {
         CK(cudaStreamCreateWithFlags(&x->st, cudaStreamNonBlocking));
         CK(cudaStreamCreateWithFlags(&x->st_comm, cudaStreamNonBlocking));
+        CK(cudaStreamCreateWithFlags(&x->st_k2, cudaStreamNonBlocking));
+        CK(cudaEventCreateWithFlags(&x->ev_k0, cudaEventDisableTiming));
+        CK(cudaEventCreateWithFlags(&x->ev_prel, cudaEventDisableTiming));
+        CK(cudaEventCreateWithFlags(&x->ev_k2, cudaEventDisableTiming));
         for (int i = 0; i < E_COUNT; ++i) CK(cudaEventCreate(&x->ev[i]));
         CK(cudaEventCreateWithFlags(&x->ev_comm, cudaEventDisableTiming));
         CK(cudaEventCreateWithFlags(&x->ev_pack, cudaEventDisableTiming));
@@ -383,6 +389,10 @@ void ovl_destroy(ovl_ctx* c) {
     if (c->ev_comm) cudaEventDestroy(c->ev_comm);
     if (c->ev_pack) cudaEventDestroy(c->ev_pack);
     if (c->ev_pre) cudaEventDestroy(c->ev_pre);
+    if (c->ev_k0) cudaEventDestroy(c->ev_k0);
+    if (c->ev_prel) cudaEventDestroy(c->ev_prel);
+    if (c->ev_k2) cudaEventDestroy(c->ev_k2);
+    if (c->st_k2) cudaStreamDestroy(c->st_k2);
     if (c->ev_t0) cudaEventDestroy(c->ev_t0);
     if (c->ev_t1) cudaEventDestroy(c->ev_t1);
     if (c->st) cudaStreamDestroy(c->st);
@@ -526,6 +536,11 @@ int ovl_set_option(ovl_ctx* c, const char* name, int64_t value) {
     }
     if (!strcmp(name, "serial_verify")) {
         c->opt_serial_verify = value != 0;
+        return OVL_OK;
+    }
+    if (!strcmp(name, "pack_blocks_per_sm")) {
+        if (value < 1 || value > 32) return fail(c, OVL_E_ARG, "pack_blocks_per_sm must be in 1..32");
+        c->opt_pack_bpsm = (int)value;
         return OVL_OK;
     }
     if (!strcmp(name, "mirror")) {
@@ -695,14 +710,14 @@ int ovl_overlaps_device(ovl_ctx* c, uint32_t min_length, uint64_t* n_rows_out) {
         // much more per insert once the table outgrows L2), the scan ~ (own granules x 64/stride)
         // filter probes.  Pick the stride with the smallest modelled sum; both tables are B200
         // measurements on config 2 (55 200 anchor entries, 12.9 M granules; N=1 and N=2 columns of
-        // profiles/r01d_stride_sweep.txt).  A dense scan (stride 1) is only taken when l < 33
+        // profiles/r01i_stride_sweep.txt).  A dense scan (stride 1) is only taken when l < 33
         // forces it.
         if (c->opt_stride == 0 && slog > 1) {
             const uint64_t n_b = n_anc;
             const double gl = (double)(c->gran0[c->e_hi] - c->gran0[c->e_lo]) / 12.9e6;
             const double al = (double)n_b / 55200.0;
-            static const double scan_ms[7] = {0, 1.7, 1.0, 0.68, 0.50, 0.41, 0.35};       // stride 2^i
-            static const double anchor_ms[7] = {0, 0.02, 0.03, 0.05, 0.087, 0.158, 0.199};  // stride 2^i
+            static const double scan_ms[7] = {0, 1.45, 0.85, 0.61, 0.44, 0.34, 0.27};      // stride 2^i
+            static const double anchor_ms[7] = {0, 0.01, 0.02, 0.03, 0.06, 0.13, 0.17};    // stride 2^i: what K2 adds beyond the concurrent K1
             int best = slog;
             double best_cost = 1e30;
             for (int sl = slog; sl >= 1; --sl) {
@@ -733,6 +748,21 @@ int ovl_overlaps_device(ovl_ctx* c, uint32_t min_length, uint64_t* n_rows_out) {
     const uint32_t g_lo = c->gran0[c->e_lo], g_hi = c->gran0[c->e_hi];
     k0_ent_table<<<(M + 255) / 256, 256, 0, st>>>(c->d_gran0.as<uint32_t>(), c->d_len.as<uint32_t>(), c->d_ent.as<uint2>(), M);
     ++launches;
+    // ---- fork: the anchor-build stream.  The prefix table (K2's only input) is packed straight
+    //      from the ASCII records, so K2 does not wait for K1 -------------------------------------
+    cudaStream_t sk = c->st_k2;
+    CK(cudaEventRecord(c->ev_k0, st));
+    CK(cudaStreamWaitEvent(sk, c->ev_k0, 0));
+    OVL_TRY(dev_ensure(c, c->d_pre, (size_t)M * 32));
+    if (c->e_hi > c->e_lo) {
+        k2_prefix_ascii<<<(c->e_hi - c->e_lo + 127) / 128, 128, 0, sk>>>(
+            c->d_ascii.as<uint8_t>(), c->d_src.as<uint64_t>(), c->d_len.as<uint32_t>(), c->d_flags.as<uint8_t>(),
+            c->d_pre.as<uint4>(), c->e_lo, c->e_hi);
+        ++launches;
+        CK(cudaGetLastError());
+    }
+    CK(cudaEventRecord(c->ev_prel, sk));
+    cudaEvent_t k2_last = c->ev_prel;  // last event on the anchor-build stream: every exit path joins it
     if (c->e_hi > c->e_lo) {
         k0_gran_entry<<<nsm * 4, 256, 0, st>>>(c->d_gran0.as<uint32_t>(), c->d_gran_ent.as<uint32_t>(),
                                                c->d_tile0.as<uint32_t>(), c->d_tile_ent.as<uint32_t>(), c->e_lo, c->e_hi);
@@ -752,21 +782,13 @@ int ovl_overlaps_device(ovl_ctx* c, uint32_t min_length, uint64_t* n_rows_out) {
             K.t_end = t_hi;
             K.err = reinterpret_cast<uint32_t*>(ctr + C_ERR);
             uint32_t blocks = (t_hi - t_lo + 7) / 8;
-            if (blocks > (uint32_t)nsm * 16) blocks = (uint32_t)nsm * 16;
+            if (blocks > (uint32_t)(nsm * c->opt_pack_bpsm)) blocks = (uint32_t)(nsm * c->opt_pack_bpsm);
             k1_pack<<<blocks, 256, 0, st>>>(K);
             ++launches;
         }
     }
     CK(cudaMemsetAsync(c->d_packed.as<uint4>() + G, 0, 32, st));  // terminator granules
     CK(cudaGetLastError());
-    // ---- prefix table (K2's only input) of the local entries ----------------------------------
-    OVL_TRY(dev_ensure(c, c->d_pre, (size_t)M * 32));
-    if (c->e_hi > c->e_lo) {
-        k2_prefix<<<(c->e_hi - c->e_lo + 255) / 256, 256, 0, st>>>(c->d_packed.as<uint4>(), c->d_ent.as<uint2>(),
-                                                                 c->d_pre.as<uint4>(), c->e_lo, c->e_hi);
-        ++launches;
-        CK(cudaGetLastError());
-    }
     // ---- multi-GPU: replicate on the comm stream (1) the prefix table, which K2 waits for, then
     //      (2) the packed granules of every rank, which only K4 needs: that transfer runs under
     //      K2 and K3 -------------------------------------------------------------------------
@@ -774,8 +796,7 @@ int ovl_overlaps_device(ovl_ctx* c, uint32_t min_length, uint64_t* n_rows_out) {
     if (c->nranks > 1) {
         auto& N = nccl_dyn::api();
         if ((int)c->rank_e.size() != c->nranks + 1) return fail(c, OVL_E_ARG, "call ovl_comm_sync_ranges before ovl_overlaps_device");
-        CK(cudaEventRecord(c->ev_pack, st));
-        CK(cudaStreamWaitEvent(c->st_comm, c->ev_pack, 0));
+        CK(cudaStreamWaitEvent(c->st_comm, c->ev_prel, 0));
         CKN(N.GroupStart());
         for (int r = 0; r < c->nranks; ++r) {
             const uint32_t a = c->rank_e[r], b = c->rank_e[r + 1];
@@ -786,6 +807,9 @@ int ovl_overlaps_device(ovl_ctx* c, uint32_t min_length, uint64_t* n_rows_out) {
         }
         CKN(N.GroupEnd());
         CK(cudaEventRecord(c->ev_pre, c->st_comm));
+        CK(cudaStreamWaitEvent(sk, c->ev_pre, 0));  // K2 reads every rank's prefixes
+        CK(cudaEventRecord(c->ev_pack, st));        // K1 done: the packed granules may travel
+        CK(cudaStreamWaitEvent(c->st_comm, c->ev_pack, 0));
         CKN(N.GroupStart());
         for (int r = 0; r < c->nranks; ++r) {
             const uint32_t a = c->gran0[c->rank_e[r]], b = c->gran0[c->rank_e[r + 1]];
@@ -796,7 +820,6 @@ int ovl_overlaps_device(ovl_ctx* c, uint32_t min_length, uint64_t* n_rows_out) {
         }
         CKN(N.GroupEnd());
         CK(cudaEventRecord(c->ev_comm, c->st_comm));
-        CK(cudaStreamWaitEvent(st, c->ev_pre, 0));  // K2 reads every rank's prefixes
         wait_packed = true;
     }
     CK(cudaEventRecord(c->ev[E_ANCHOR0], st));
@@ -823,6 +846,7 @@ int ovl_overlaps_device(ovl_ctx* c, uint32_t min_length, uint64_t* n_rows_out) {
     // record the remaining stage events from `from` on, wait, fill the stage times
     auto finish_from = [&](int from) -> int {
         if (wait_packed) CK(cudaStreamWaitEvent(st, c->ev_comm, 0));  // never leave the replication in flight
+        CK(cudaStreamWaitEvent(st, k2_last, 0));                      // ... nor the anchor-build stream
         for (int e = from; e <= E_END; ++e) CK(cudaEventRecord(c->ev[e], st));
         OVL_TRY(read_ctr(c));
         OVL_TRY(check_alphabet());
@@ -858,8 +882,8 @@ int ovl_overlaps_device(ovl_ctx* c, uint32_t min_length, uint64_t* n_rows_out) {
         OVL_TRY(dev_ensure(c, c->d_table, table_bytes));
         OVL_TRY(dev_ensure(c, c->d_filter, filter_bytes));
         OVL_TRY(dev_ensure(c, c->d_next, ((uint64_t)M << slog) * 4));
-        CK(cudaMemsetAsync(c->d_table.p, 0xff, table_bytes, st));  // EMPTY_SLOT
-        CK(cudaMemsetAsync(c->d_filter.p, 0, filter_bytes, st));
+        CK(cudaMemsetAsync(c->d_table.p, 0xff, table_bytes, sk));  // EMPTY_SLOT
+        CK(cudaMemsetAsync(c->d_filter.p, 0, filter_bytes, sk));
         {
             AnchorParams A;
             A.pre64 = reinterpret_cast<const uint64_t*>(c->d_pre.p);
@@ -876,13 +900,18 @@ int ovl_overlaps_device(ovl_ctx* c, uint32_t min_length, uint64_t* n_rows_out) {
             A.dense = dense ? 1 : 0;
             A.n_anchors = reinterpret_cast<unsigned long long*>(ctr + C_NANC);
             const uint64_t nthreads = (uint64_t)M << slog;
-            k2_insert<<<(unsigned)((nthreads + 255) / 256), 256, 0, st>>>(A);
+            k2_insert<<<(unsigned)((nthreads + 255) / 256), 256, 0, sk>>>(A);
             ++launches;
             CK(cudaGetLastError());
         }
+        // ---- join: the scan needs the table ------------------------------------------------------
+        CK(cudaEventRecord(c->ev_k2, sk));
+        k2_last = c->ev_k2;
+        CK(cudaStreamWaitEvent(st, c->ev_k2, 0));
         CK(cudaEventRecord(c->ev[E_SCAN0], st));
 
     } else {
+        CK(cudaStreamWaitEvent(st, k2_last, 0));
         CK(cudaEventRecord(c->ev[E_SCAN0], st));
     }
 
