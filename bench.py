@@ -323,6 +323,11 @@ def run_b200(args):
     ms_step = ms_total / args.steps
     for k in stage:
         stage[k] /= args.steps
+    stage_rank0 = dict(stage)
+    if world > 1:   # slowest rank per stage (the step time is the max over ranks too)
+        t = torch.tensor([stage[k] for k in sorted(stage)], dtype=torch.float64, device="cuda")
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        stage = {k: float(v) for k, v in zip(sorted(stage), t.tolist())}
     st = ov.stats()
     n_rows = st["rows"] if rank == 0 else 0
     n_rows = int(sum_over_ranks(float(n_rows)))  # after the gather rank 0 holds all rows
@@ -397,7 +402,7 @@ def run_b200(args):
             "config": workload_config(shape, world),
             "overlaps_per_s": n_rows / (ms_step * 1e-3), "rows": n_rows,
             "candidates": candidates, "verified": st["verified"], "hits": st["hits"],
-            "mirror": st["mirror"], "anchor_stride": st["anchor_stride"], "stage_ms": stage,
+            "mirror": st["mirror"], "anchor_stride": st["anchor_stride"], "stage_ms": stage, "stage_ms_rank0": stage_rank0,
             "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": h2d,
                     "d2h_bytes_per_step": d2h, "ms_per_step": 1e3 * t_e2e,
                     "overlaps_per_s": n_rows / t_e2e,
