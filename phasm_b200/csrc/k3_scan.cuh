@@ -44,8 +44,8 @@ struct ScanParams {
 };
 
 // ---- sparse path ------------------------------------------------------------------------
-// SL >= 0: the stride is the compile-time constant 2^SL (6 and 5 are instantiated: one or two
-// word-aligned k-mers per granule, no shifts); SL < 0: read it from the parameters.
+// SL >= 0: the stride is the compile-time constant 2^SL (6, 5, 4 and 3 are instantiated: 1, 2, 4 or
+// 8 k-mers per granule at fixed offsets, loops fully unrolled); SL < 0: read it from the parameters.
 // The warp's NEXT tile (packed granule + entry index) is loaded before the current one is
 // processed, and the filter words are requested before the entry record is needed, so the
 // dependent chain per tile is filter -> table slot -> anchor list, all L2 hits (ncu r01f: 60 % of
@@ -101,7 +101,7 @@ __global__ void __launch_bounds__(256) k3_probe(const ScanParams P) {
         // before the entry record is looked at)
         uint32_t fbits = 0;
         if (inr) {
-#pragma unroll 4
+#pragma unroll 8
             for (uint32_t j = 0; j < n_probe; ++j) {
                 const uint32_t off = j << sl;
                 const uint64_t x = (off < 32 ? kmer_at(w0, w1, off) : kmer_at(w1, w2, off - 32)) & kmask;

@@ -716,7 +716,7 @@ int ovl_overlaps_device(ovl_ctx* c, uint32_t min_length, uint64_t* n_rows_out) {
             const uint64_t n_b = n_anc;
             const double gl = (double)(c->gran0[c->e_hi] - c->gran0[c->e_lo]) / 12.9e6;
             const double al = (double)n_b / 55200.0;
-            static const double scan_ms[7] = {0, 1.45, 0.85, 0.61, 0.44, 0.34, 0.27};      // stride 2^i
+            static const double scan_ms[7] = {0, 1.45, 0.98, 0.56, 0.40, 0.34, 0.27};      // stride 2^i
             static const double anchor_ms[7] = {0, 0.01, 0.02, 0.03, 0.06, 0.13, 0.17};    // stride 2^i: what K2 adds beyond the concurrent K1
             int best = slog;
             double best_cost = 1e30;
@@ -961,9 +961,13 @@ int ovl_overlaps_device(ovl_ctx* c, uint32_t min_length, uint64_t* n_rows_out) {
                 const uint32_t tiles = (g_hi - g_lo + 31) / 32;
                 uint32_t blocks = (tiles + 7) / 8;
                 if (blocks > (uint32_t)nsm * 8) blocks = (uint32_t)nsm * 8;
-                if (slog == 6) k3_probe<6><<<blocks, 256, 0, st>>>(P);
-                else if (slog == 5) k3_probe<5><<<blocks, 256, 0, st>>>(P);
-                else k3_probe<-1><<<blocks, 256, 0, st>>>(P);
+                switch (slog) {
+                    case 6: k3_probe<6><<<blocks, 256, 0, st>>>(P); break;
+                    case 5: k3_probe<5><<<blocks, 256, 0, st>>>(P); break;
+                    case 4: k3_probe<4><<<blocks, 256, 0, st>>>(P); break;
+                    case 3: k3_probe<3><<<blocks, 256, 0, st>>>(P); break;
+                    default: k3_probe<-1><<<blocks, 256, 0, st>>>(P); break;
+                }
             } else if (smem_filter) {
                 k3_scan<true><<<nsm, 1024, 32 * WBUF * 8 + (4u << bm_bits), st>>>(P);
             } else {
