@@ -378,10 +378,14 @@ def run_b200(args):
         if traffic and all(n in traffic for n in tmap[k]):
             t = sum(traffic[n] for n in tmap[k])
         per_kernel[k]["traffic"] = t
+        # measured DRAM bytes of the ncu capture / live kernel time: the fraction of the HBM peak
+        # the kernel really draws (the algorithmic figure above counts operand bytes served by L1/L2)
+        ms_k = per_kernel[k]["ms"]
+        per_kernel[k]["dram_frac"] = (t / (ms_k * 1e-3) / 1e9 / peak) if (t and ms_k > 0) else None
     roofline = {
         "bound": "hbm", "kernel": dom, "achieved": per_kernel[dom]["GBps"], "peak": peak,
         "unit": "GB/s", "frac": per_kernel[dom]["frac"], "traffic": per_kernel[dom]["traffic"],
-        "traffic_source": traffic_src,
+        "traffic_source": traffic_src, "dram_frac": per_kernel[dom]["dram_frac"],
         "peak_source": peak_src, "alg_bytes_per_launch": kern[dom][0],
         "ms_per_launch": kern[dom][1], "per_kernel": per_kernel,
         "k4_verify_canonical": {

@@ -98,6 +98,8 @@ struct PackParams {
     const uint32_t* tile0;     // [M+1] first tile of every entry (0 tiles for twins / remote entries)
     const uint32_t* tile_ent;  // [n_tiles]
     uint32_t* packed32;
+    uint32_t* fwd32;           // multi-GPU, paired entries: compact copy of the FORWARD granules (entry e at
+                               // granule gran0[e]/2) -- what the ranks exchange; nullptr otherwise
     uint32_t M;
     uint32_t t_begin, t_end;   // tiles of the local entries
     uint32_t* err;             // set to (entry index + 1) of some entry holding a non-ACGT byte
@@ -138,7 +140,10 @@ __global__ void __launch_bounds__(256) k1_pack(const PackParams P) {
             const uint32_t u = u0 + 32u * i + lane;
             const int nvalid = (int)L - 16 * (int)u;
             W[i] = nvalid >= 16 ? pack16(v[i], bad) : (nvalid > 0 ? pack16_partial(v[i], nvalid, bad) : 0u);
-            if (u < units) out[u] = W[i];
+            if (u < units) {
+                out[u] = W[i];
+                if (P.fwd32) P.fwd32[4ull * (m_e.x >> 1) + u] = W[i];
+            }
         }
         uint32_t Wh = 0;
         if (need_halo) {
@@ -161,6 +166,39 @@ __global__ void __launch_bounds__(256) k1_pack(const PackParams P) {
             if (u >= units) continue;
             if (u < m) rc[m - u - 1] = reverse_groups2(__funnelshift_r(W[i], Wn, 2 * r)) ^ 0xAAAAAAAAu;
             if (u == 0 && r) rc[m] = (reverse_groups2(W[i] << (32 - 2 * r)) ^ 0xAAAAAAAAu) & ((1u << (2 * r)) - 1u);
+            if (u >= m + (r ? 1u : 0u)) rc[u] = 0u;
+        }
+    }
+}
+
+// Multi-GPU: rebuild both strands of the REMOTE reads from the compact forward granules the ranks
+// exchanged (half the NVLink volume of replicating the packed array itself).  Paired layout only:
+// entry 2i is read i forward at granule gran0[2i], entry 2i+1 its reverse complement right behind
+// it, so the compact array holds read i at granule gran0[2i]/2.  One block per read of
+// [pair_begin, pair_end), one thread per granule: copies it into place and writes the four
+// reverse-complement words it determines (same word arithmetic as the twin part of k1_pack).
+__global__ void __launch_bounds__(128) k1_expand(const uint4* __restrict__ fwd, const uint32_t* __restrict__ gran0,
+                                                 const uint32_t* __restrict__ len, uint32_t* __restrict__ packed32,
+                                                 uint32_t pair_begin, uint32_t pair_end) {
+    const uint32_t e = 2u * (pair_begin + blockIdx.x);
+    if (e >= 2u * pair_end) return;
+    const uint32_t g0 = __ldg(gran0 + e), g1 = __ldg(gran0 + e + 1), L = __ldg(len + e);
+    const uint32_t ng = (L + 63u) >> 6, units = 4u * ng;
+    const uint4* src = fwd + (g0 >> 1);
+    uint4* dst = reinterpret_cast<uint4*>(packed32) + g0;
+    uint32_t* rc = packed32 + 4ull * g1;
+    const uint32_t m = L >> 4, r = L & 15u;
+    for (uint32_t ig = threadIdx.x; ig < ng; ig += blockDim.x) {
+        const uint4 v = src[ig];
+        const uint32_t wn = ig + 1 < ng ? reinterpret_cast<const uint32_t*>(src + ig + 1)[0] : 0u;
+        dst[ig] = v;
+        const uint32_t W[5] = {v.x, v.y, v.z, v.w, wn};
+#pragma unroll
+        for (int k = 0; k < 4; ++k) {
+            const uint32_t u = 4u * ig + k;
+            if (u >= units) continue;
+            if (u < m) rc[m - u - 1] = reverse_groups2(__funnelshift_r(W[k], W[k + 1], 2 * r)) ^ 0xAAAAAAAAu;
+            if (u == 0 && r) rc[m] = (reverse_groups2(W[k] << (32 - 2 * r)) ^ 0xAAAAAAAAu) & ((1u << (2 * r)) - 1u);
             if (u >= m + (r ? 1u : 0u)) rc[u] = 0u;
         }
     }

@@ -70,7 +70,8 @@ struct ovl_ctx {
     cudaStream_t st = nullptr, st_comm = nullptr, st_k2 = nullptr;
     cudaEvent_t ev[E_COUNT] = {};
     cudaEvent_t ev_comm = nullptr, ev_pack = nullptr, ev_pre = nullptr;
-    cudaEvent_t ev_k0 = nullptr, ev_prel = nullptr, ev_k2 = nullptr;  // fork/join of the anchor-build stream
+    cudaEvent_t ev_k0 = nullptr, ev_prel = nullptr, ev_k2 = nullptr;
+    cudaEvent_t ev_dbg[4] = {};  // OVL_DEBUG=1: timing of the replication on the comm stream  // fork/join of the anchor-build stream
     cudaEvent_t ev_t0 = nullptr, ev_t1 = nullptr;  // ovl_timer_*
     std::string err;
 
@@ -91,7 +92,7 @@ struct ovl_ctx {
     // ---- device ----
     DevBuf d_ascii, d_src, d_len, d_flags, d_gran0, d_gran_ent, d_ent, d_packed, d_tile0, d_tile_ent, d_xchg, d_pre;
     DevBuf d_table, d_filter, d_next, d_ctr, d_tmp;
-    DevBuf d_cand, d_cand2, d_cnt, d_offs, d_rows, d_cnts, d_bkt;
+    DevBuf d_cand, d_cand2, d_cnt, d_offs, d_rows, d_cnts, d_bkt, d_fwd;
     uint64_t* h_ctr = nullptr;  // pinned mirror of d_ctr
     uint64_t cand_cap = 0;  // candidate keys one pass may emit (d_cand/d_cand2 hold the derived hit capacity)
     uint64_t n_rows = 0;
@@ -352,6 +353,7 @@ int ovl_create(int device, ovl_ctx** out) {
         CK(cudaEventCreateWithFlags(&x->ev_k0, cudaEventDisableTiming));
         CK(cudaEventCreateWithFlags(&x->ev_prel, cudaEventDisableTiming));
         CK(cudaEventCreateWithFlags(&x->ev_k2, cudaEventDisableTiming));
+        for (int i = 0; i < 4; ++i) CK(cudaEventCreate(&x->ev_dbg[i]));
         for (int i = 0; i < E_COUNT; ++i) CK(cudaEventCreate(&x->ev[i]));
         CK(cudaEventCreateWithFlags(&x->ev_comm, cudaEventDisableTiming));
         CK(cudaEventCreateWithFlags(&x->ev_pack, cudaEventDisableTiming));
@@ -377,7 +379,7 @@ void ovl_destroy(ovl_ctx* c) {
     DevBuf* bufs[] = {&c->d_ascii, &c->d_src, &c->d_len, &c->d_flags, &c->d_gran0, &c->d_gran_ent,
                       &c->d_ent, &c->d_packed, &c->d_table, &c->d_filter, &c->d_next, &c->d_ctr,
                       &c->d_tmp, &c->d_cand, &c->d_cand2, &c->d_cnt, &c->d_offs, &c->d_rows, &c->d_cnts,
-                      &c->d_tile0, &c->d_tile_ent, &c->d_xchg, &c->d_pre, &c->d_bkt};
+                      &c->d_tile0, &c->d_tile_ent, &c->d_xchg, &c->d_pre, &c->d_bkt, &c->d_fwd};
     for (DevBuf* b : bufs)
         if (b->p) cudaFree(b->p);
     if (c->ascii.p) cudaFreeHost(c->ascii.p);
@@ -392,6 +394,8 @@ void ovl_destroy(ovl_ctx* c) {
     if (c->ev_k0) cudaEventDestroy(c->ev_k0);
     if (c->ev_prel) cudaEventDestroy(c->ev_prel);
     if (c->ev_k2) cudaEventDestroy(c->ev_k2);
+    for (int i = 0; i < 4; ++i)
+        if (c->ev_dbg[i]) cudaEventDestroy(c->ev_dbg[i]);
     if (c->st_k2) cudaStreamDestroy(c->st_k2);
     if (c->ev_t0) cudaEventDestroy(c->ev_t0);
     if (c->ev_t1) cudaEventDestroy(c->ev_t1);
@@ -746,6 +750,9 @@ int ovl_overlaps_device(ovl_ctx* c, uint32_t min_length, uint64_t* n_rows_out) {
     CK(cudaMemsetAsync(ctr, 0, C_COUNT * sizeof(uint64_t), st));
     // ---- K0 + K1: pack the local entries ------------------------------------------------
     const uint32_t g_lo = c->gran0[c->e_lo], g_hi = c->gran0[c->e_hi];
+    // multi-GPU with paired entries: the ranks exchange compact FORWARD granules only (k1_expand)
+    const bool fwd_x = c->nranks > 1 && c->cache_pairs == 1;
+    if (fwd_x) OVL_TRY(dev_ensure(c, c->d_fwd, ((size_t)G / 2 + 2) * 16));
     k0_ent_table<<<(M + 255) / 256, 256, 0, st>>>(c->d_gran0.as<uint32_t>(), c->d_len.as<uint32_t>(), c->d_ent.as<uint2>(), M);
     ++launches;
     // ---- fork: the anchor-build stream.  The prefix table (K2's only input) is packed straight
@@ -777,6 +784,7 @@ int ovl_overlaps_device(ovl_ctx* c, uint32_t min_length, uint64_t* n_rows_out) {
             K.tile0 = c->d_tile0.as<uint32_t>();
             K.tile_ent = c->d_tile_ent.as<uint32_t>();
             K.packed32 = c->d_packed.as<uint32_t>();
+            K.fwd32 = fwd_x ? c->d_fwd.as<uint32_t>() : nullptr;
             K.M = M;
             K.t_begin = t_lo;
             K.t_end = t_hi;
@@ -810,15 +818,50 @@ int ovl_overlaps_device(ovl_ctx* c, uint32_t min_length, uint64_t* n_rows_out) {
         CK(cudaStreamWaitEvent(sk, c->ev_pre, 0));  // K2 reads every rank's prefixes
         CK(cudaEventRecord(c->ev_pack, st));        // K1 done: the packed granules may travel
         CK(cudaStreamWaitEvent(c->st_comm, c->ev_pack, 0));
-        CKN(N.GroupStart());
-        for (int r = 0; r < c->nranks; ++r) {
-            const uint32_t a = c->gran0[c->rank_e[r]], b = c->gran0[c->rank_e[r + 1]];
-            if (b > a) {
-                uint4* p = c->d_packed.as<uint4>() + a;
-                CKN(N.Broadcast(p, p, (size_t)(b - a) * 16, ncclUint8, r, c->comm, c->st_comm));
+        CK(cudaEventRecord(c->ev_dbg[0], c->st_comm));
+        if (fwd_x) {
+            // equal shares (the usual case): one in-place all-gather; else one broadcast per rank
+            bool equal = true;
+            const uint32_t cnt0 = (c->gran0[c->rank_e[1]] - c->gran0[c->rank_e[0]]) / 2;
+            for (int r = 0; r < c->nranks; ++r)
+                equal = equal && (c->gran0[c->rank_e[r + 1]] - c->gran0[c->rank_e[r]]) / 2 == cnt0;
+            if (equal && cnt0) {
+                uint4* all = c->d_fwd.as<uint4>();
+                CKN(N.AllGather(all + (size_t)c->rank * cnt0, all, (size_t)cnt0 * 16, ncclUint8, c->comm, c->st_comm));
+            } else {
+                CKN(N.GroupStart());
+                for (int r = 0; r < c->nranks; ++r) {
+                    const uint32_t a = c->gran0[c->rank_e[r]] / 2, b = c->gran0[c->rank_e[r + 1]] / 2;
+                    if (b > a) {
+                        uint4* p = c->d_fwd.as<uint4>() + a;
+                        CKN(N.Broadcast(p, p, (size_t)(b - a) * 16, ncclUint8, r, c->comm, c->st_comm));
+                    }
+                }
+                CKN(N.GroupEnd());
             }
+            CK(cudaEventRecord(c->ev_dbg[1], c->st_comm));
+            // both strands of the remote reads, rebuilt locally: below and above the own range
+            const uint32_t pr[2][2] = {{0u, c->e_lo / 2}, {c->e_hi / 2, M / 2}};
+            for (int i = 0; i < 2; ++i)
+                if (pr[i][1] > pr[i][0]) {
+                    k1_expand<<<pr[i][1] - pr[i][0], 128, 0, c->st_comm>>>(
+                        c->d_fwd.as<uint4>(), c->d_gran0.as<uint32_t>(), c->d_len.as<uint32_t>(),
+                        c->d_packed.as<uint32_t>(), pr[i][0], pr[i][1]);
+                    ++launches;
+                }
+            CK(cudaGetLastError());
+        } else {
+            CKN(N.GroupStart());
+            for (int r = 0; r < c->nranks; ++r) {
+                const uint32_t a = c->gran0[c->rank_e[r]], b = c->gran0[c->rank_e[r + 1]];
+                if (b > a) {
+                    uint4* p = c->d_packed.as<uint4>() + a;
+                    CKN(N.Broadcast(p, p, (size_t)(b - a) * 16, ncclUint8, r, c->comm, c->st_comm));
+                }
+            }
+            CKN(N.GroupEnd());
         }
-        CKN(N.GroupEnd());
+        CK(cudaEventRecord(c->ev_dbg[2], c->st_comm));
         CK(cudaEventRecord(c->ev_comm, c->st_comm));
         wait_packed = true;
     }
@@ -1153,6 +1196,16 @@ int ovl_overlaps_device(ovl_ctx* c, uint32_t min_length, uint64_t* n_rows_out) {
     c->n_rows = n_rows;
     S.rows = n_rows;
     stage_times();
+    if (wait_packed && getenv("OVL_DEBUG")) {
+        float t_pk = 0, t_bc = 0, t_ex = 0, t_v = 0;
+        cudaEventElapsedTime(&t_pk, c->ev[E_PACK0], c->ev_dbg[0]);
+        if (fwd_x) cudaEventElapsedTime(&t_bc, c->ev_dbg[0], c->ev_dbg[1]);
+        cudaEventElapsedTime(&t_ex, fwd_x ? c->ev_dbg[1] : c->ev_dbg[0], c->ev_dbg[2]);
+        cudaEventElapsedTime(&t_v, c->ev[E_PACK0], c->ev[E_VERIFY0]);
+        (void)cudaGetLastError();
+        fprintf(stderr, "[ovl rank %d] comm stream: starts +%.3f ms, broadcast %.3f ms, %s %.3f ms; verify stage starts +%.3f ms\n",
+                c->rank, t_pk, t_bc, fwd_x ? "expand" : "replicate", t_ex, t_v);
+    }
     if (n_rows_out) *n_rows_out = n_rows;
     return OVL_OK;
 }
