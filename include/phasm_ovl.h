@@ -135,8 +135,9 @@ int ovl_fetch_rows(ovl_ctx *ctx, const ovl_row **rows, uint64_t *n_rows);
  * SURVEY.md 8(d) is defined on the canonical candidates (first k-mer of B at every A position),
  * so this also forces the dense stride-1 scan. */
 int ovl_set_collect_stats(ovl_ctx *ctx, int on);
-/* Tuning knobs.  "anchor_stride": 0 = auto (largest power of two <= min(64, l-k+1)), else an
- * upper bound (1 forces the dense scan).  "serial_verify": 1 = chunk-by-chunk early-exit
+/* Tuning knobs.  "anchor_stride": 0 = auto (a power of two <= min(64, l-k+1) picked by a measured
+ * cost model of table build vs scan), else an upper bound (1 forces the dense scan).
+ * "pack_blocks_per_sm": K1 grid size per SM (1..32, default 16).  "serial_verify": 1 = chunk-by-chunk early-exit
  * verifier instead of the head/tail two-pass form.  "mirror": 0 = compare every candidate even
  * when every read is present on both strands (default 1: compare one of each strand-mirror
  * pair and emit both rows). */
