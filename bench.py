@@ -85,7 +85,7 @@ class ClockSampler:
         try:
             self.proc = subprocess.Popen(
                 ["nvidia-smi", "-i", str(self.gpu), "--query-gpu=" + self.Q,
-                 "--format=csv,noheader,nounits", "-lms", "100"],
+                 "--format=csv,noheader,nounits", "-lms", "20"],
                 stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
         except OSError:
             self.proc = None
@@ -300,12 +300,12 @@ def run_b200(args):
     executed_bytes = st_x["operand_bytes"]
 
     # ---- device-resident: W warm-up + K timed steps ---------------------------------------
+    sampler = ClockSampler(local)
+    if rank == 0:
+        sampler.start()     # sampled from the warm-up on, so that a short timed region still sees samples
     for _ in range(args.warmup):
         step_device()
-    sampler = ClockSampler(local)
     barrier()
-    if rank == 0:
-        sampler.start()
     stage = {k: 0.0 for k in ("ms_pack", "ms_anchor", "ms_scan", "ms_sort", "ms_verify", "ms_emit", "ms_device")}
     launches = lib_launches = 0
     ov.timer_start()
@@ -318,7 +318,6 @@ def run_b200(args):
         lib_launches += st["lib_launches"]
     ms_total = ov.timer_stop()
     barrier()
-    clocks = sampler.stop() if rank == 0 else None
     ms_total = max_over_ranks(ms_total)
     ms_step = ms_total / args.steps
     for k in stage:
@@ -351,6 +350,7 @@ def run_b200(args):
     torch.cuda.synchronize()
     t_e2e = max_over_ranks(time.perf_counter() - t0) / e2e_steps
     barrier()
+    clocks = sampler.stop() if rank == 0 else None   # warm-up + timed region + e2e steps
     st_e = ov.stats()
     h2d = int(sum_over_ranks(float(st_e["ascii_bytes"] + 17 * st_e["entries"] + 4)))
     d2h = n_rows * 20
@@ -375,8 +375,10 @@ def run_b200(args):
     tmap = {"k1_pack": ("k1_pack",), "k3_scan": ("k3_probe",), "k4_verify": ("k4a_head", "k4b_tail")}
     for k in per_kernel:
         t = None
-        if traffic and all(n in traffic for n in tmap[k]):
-            t = sum(traffic[n] for n in tmap[k])
+        if traffic:   # ncu names carry template arguments (k3_probe<6>): match on the prefix
+            got = [sum(v for n, v in traffic.items() if n.startswith(p)) for p in tmap[k]]
+            if all(x > 0 for x in got):
+                t = sum(got)
         per_kernel[k]["traffic"] = t
         # measured DRAM bytes of the ncu capture / live kernel time: the fraction of the HBM peak
         # the kernel really draws (the algorithmic figure above counts operand bytes served by L1/L2)
