@@ -164,6 +164,46 @@ int ovl_add_fasta(ovl_ctx *ctx, const char *path, int both_strands, uint32_t *n_
  * Writes to the file descriptor fd (the caller flushes its own buffered writer first). */
 int ovl_write_gfa(ovl_ctx *ctx, int fd, int what, uint64_t *bytes_written);
 
+/* ---- overlap-consumer filters on the device (OPTIONAL, never applied by
+ * ovl_overlaps*) -------------------------------------------------------------------------
+ * ovl_filter_rows runs the alignment filters of the reference's `layout` stage over the rows of
+ * the last ovl_overlaps* call, in the reference's order and with its streaming semantics
+ * (phasm/cli/assembler.py:76-86,96-98; phasm/filter.py:36-122; LocalAlignment.classify,
+ * get_overlap_length, get_overhang: phasm/alignments.py:237-258), rows taken in the order this
+ * library returns them (= the E-line order ovl_write_gfa writes):
+ *   contained_reads     ContainedReads(): a row whose A (B) is contained marks that entry and is
+ *                       dropped; a later row touching a marked entry is dropped too;
+ *   min_read_length     MinReadLength(n), 0 = off;   min_overlap_length  MinOverlapLength(n), 0 = off;
+ *   max_overhang        MaxOverhang(max_overhang_abs, max_overhang_rel): keep iff
+ *                       overhang <= min(abs, rel * overlap_length);
+ *   collapse_pairs      of the surviving rows keep the LAST one per ordered pair (a, b) -- the row
+ *                       that ends up on the edge a->b when the reference adds edges in order
+ *                       (assembler.py:72-74, build_assembly_graph).
+ * The kept rows come back in the same canonical order in a buffer owned by the ctx (valid until
+ * the next ovl_filter_rows / ovl_overlaps* call); the unfiltered rows stay available. */
+typedef struct {
+    uint32_t contained_reads;
+    uint32_t min_read_length;
+    uint32_t min_overlap_length;
+    uint32_t max_overhang;
+    int64_t max_overhang_abs;
+    double max_overhang_rel;
+    uint32_t collapse_pairs;
+    uint32_t reserved0;
+} ovl_filter_opts;
+
+typedef struct {
+    uint64_t rows_in;
+    uint64_t rows_kept;
+    uint64_t rows_contained;   /* rows classified A_CONTAINED or B_CONTAINED                  */
+    uint64_t entries_removed;  /* entries marked by ContainedReads (its nodes_to_remove)      */
+    float ms_device;
+    uint32_t reserved0;
+} ovl_filter_stats;
+
+int ovl_filter_rows(ovl_ctx *ctx, const ovl_filter_opts *opts, const ovl_row **rows, uint64_t *n_rows,
+                    ovl_filter_stats *stats);
+
 /* ---- multi-GPU (one process per GPU) ---------------------------------------------------
  * All ranks add the SAME entry table in the same order; rank r scans only the A entries of
  * its contiguous, base-balanced range and returns only those rows.  The rank's packed reads

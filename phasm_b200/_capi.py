@@ -38,6 +38,21 @@ class OvlStats(Structure):
         return {n: getattr(self, n) for n, _ in self._fields_}
 
 
+class OvlFilterOpts(Structure):
+    _fields_ = [("contained_reads", c_uint32), ("min_read_length", c_uint32),
+                ("min_overlap_length", c_uint32), ("max_overhang", c_uint32),
+                ("max_overhang_abs", ctypes.c_int64), ("max_overhang_rel", ctypes.c_double),
+                ("collapse_pairs", c_uint32), ("reserved0", c_uint32)]
+
+
+class OvlFilterStats(Structure):
+    _fields_ = [("rows_in", c_uint64), ("rows_kept", c_uint64), ("rows_contained", c_uint64),
+                ("entries_removed", c_uint64), ("ms_device", c_float), ("reserved0", c_uint32)]
+
+    def as_dict(self):
+        return {n: getattr(self, n) for n, _ in self._fields_ if n != "reserved0"}
+
+
 # every symbol include/phasm_ovl.h declares: name -> (restype, argtypes)
 _P = c_void_p
 SIGNATURES = {
@@ -64,6 +79,8 @@ SIGNATURES = {
     "ovl_timer_stop": (c_int, [_P, POINTER(c_float)]),
     "ovl_add_fasta": (c_int, [_P, c_char_p, c_int, POINTER(c_uint32)]),
     "ovl_write_gfa": (c_int, [_P, c_int, c_int, POINTER(c_uint64)]),
+    "ovl_filter_rows": (c_int, [_P, POINTER(OvlFilterOpts), POINTER(c_void_p), POINTER(c_uint64),
+                                POINTER(OvlFilterStats)]),
     "ovl_comm_unique_id": (c_int, [c_void_p]),
     "ovl_comm_init": (c_int, [_P, c_void_p, c_int, c_int]),
     "ovl_comm_sync_ranges": (c_int, [_P]),

@@ -34,6 +34,7 @@
 #include "k5_emit.cuh"
 #include "k6_exchange.cuh"
 #include "k7_bucket.cuh"
+#include "k8_filter.cuh"
 #include "nccl_dyn.h"
 
 static_assert(sizeof(ovl_row) == sizeof(ovl::Row), "row layouts must agree");
@@ -93,6 +94,8 @@ struct ovl_ctx {
     DevBuf d_ascii, d_src, d_len, d_flags, d_gran0, d_gran_ent, d_ent, d_packed, d_tile0, d_tile_ent, d_xchg, d_pre;
     DevBuf d_table, d_filter, d_next, d_ctr, d_tmp;
     DevBuf d_cand, d_cand2, d_cnt, d_offs, d_rows, d_cnts, d_bkt, d_fwd;
+    DevBuf d_fmark, d_fkeep, d_foff, d_frows;  // ovl_filter_rows
+    PinBuf h_frows;
     uint64_t* h_ctr = nullptr;  // pinned mirror of d_ctr
     uint64_t cand_cap = 0;  // candidate keys one pass may emit (d_cand/d_cand2 hold the derived hit capacity)
     uint64_t n_rows = 0;
@@ -379,12 +382,13 @@ void ovl_destroy(ovl_ctx* c) {
     DevBuf* bufs[] = {&c->d_ascii, &c->d_src, &c->d_len, &c->d_flags, &c->d_gran0, &c->d_gran_ent,
                       &c->d_ent, &c->d_packed, &c->d_table, &c->d_filter, &c->d_next, &c->d_ctr,
                       &c->d_tmp, &c->d_cand, &c->d_cand2, &c->d_cnt, &c->d_offs, &c->d_rows, &c->d_cnts,
-                      &c->d_tile0, &c->d_tile_ent, &c->d_xchg, &c->d_pre, &c->d_bkt, &c->d_fwd};
+                      &c->d_tile0, &c->d_tile_ent, &c->d_xchg, &c->d_pre, &c->d_bkt, &c->d_fwd, &c->d_fmark, &c->d_fkeep, &c->d_foff, &c->d_frows};
     for (DevBuf* b : bufs)
         if (b->p) cudaFree(b->p);
     if (c->ascii.p) cudaFreeHost(c->ascii.p);
     if (c->h_rows.p) cudaFreeHost(c->h_rows.p);
     if (c->h_gather.p) cudaFreeHost(c->h_gather.p);
+    if (c->h_frows.p) cudaFreeHost(c->h_frows.p);
     if (c->h_ctr) cudaFreeHost(c->h_ctr);
     for (int i = 0; i < E_COUNT; ++i)
         if (c->ev[i]) cudaEventDestroy(c->ev[i]);

@@ -228,3 +228,89 @@ int ovl_write_gfa(ovl_ctx* c, int fd, int what, uint64_t* bytes_written) {
 }
 
 }  // extern "C"
+
+// =========================================================================================
+// Optional device post-pass over the rows of the last call: the `layout` stage's alignment
+// filters (include/phasm_ovl.h, k8_filter.cuh).
+extern "C" int ovl_filter_rows(ovl_ctx* c, const ovl_filter_opts* o, const ovl_row** rows, uint64_t* n_rows,
+                               ovl_filter_stats* fs) {
+    using namespace ovl;
+    if (!c || !o || !rows || !n_rows) return fail(c, OVL_E_ARG, "ovl_filter_rows: NULL argument");
+    OVL_TRY(set_dev(c));
+    *rows = nullptr;
+    *n_rows = 0;
+    if (fs) memset(fs, 0, sizeof *fs);
+    const uint64_t n = c->n_rows;
+    const uint32_t M = (uint32_t)c->len.size();
+    if (fs) fs->rows_in = n;
+    if (n == 0) return OVL_OK;
+    if (n >= 0xffffffffull) return fail(c, OVL_E_LIMIT, "ovl_filter_rows: more than 2^32 rows");
+    cudaStream_t st = c->st;
+    const size_t fm_bytes = ((size_t)M * 4 + 7) & ~(size_t)7;
+    OVL_TRY(dev_ensure(c, c->d_fmark, fm_bytes + 16));  // firstmark[M] | counters[2]
+    OVL_TRY(dev_ensure(c, c->d_fkeep, n * 8));          // keep[n] | keep2[n]
+    OVL_TRY(dev_ensure(c, c->d_foff, (n + 1) * 8));
+    OVL_TRY(dev_ensure(c, c->d_frows, n * sizeof(Row)));
+    uint32_t* fmark = c->d_fmark.as<uint32_t>();
+    unsigned long long* fctr = reinterpret_cast<unsigned long long*>(c->d_fmark.as<uint8_t>() + fm_bytes);
+    uint32_t* keep = c->d_fkeep.as<uint32_t>();
+    uint32_t* keep2 = keep + n;
+    CK(cudaEventRecord(c->ev[E_D2H0], st));
+    CK(cudaMemsetAsync(fmark, 0xff, (size_t)M * 4, st));
+    CK(cudaMemsetAsync(fctr, 0, 16, st));
+    FilterParams P;
+    P.rows = c->d_rows.as<Row>();
+    P.n = n;
+    P.ent = c->d_ent.as<uint2>();
+    P.firstmark = fmark;
+    P.keep = keep;
+    P.contained_reads = o->contained_reads;
+    P.min_read_length = o->min_read_length;
+    P.min_overlap_length = o->min_overlap_length;
+    P.max_overhang = o->max_overhang;
+    P.collapse_pairs = o->collapse_pairs;
+    P.max_overhang_abs = (long long)o->max_overhang_abs;
+    P.max_overhang_rel = o->max_overhang_rel;
+    P.counters = fctr;
+    unsigned blocks = (unsigned)((n + 255) / 256);
+    if (blocks > (unsigned)c->n_sm * 16) blocks = (unsigned)c->n_sm * 16;
+    if (o->contained_reads) {
+        k8_mark<<<blocks, 256, 0, st>>>(P);
+        k8_count_marked<<<(M + 255) / 256 < 1024 ? (M + 255) / 256 : 1024, 256, 0, st>>>(fmark, M, fctr + 1);
+    }
+    k8_keep<<<blocks, 256, 0, st>>>(P);
+    const uint32_t* kfinal = keep;
+    if (o->collapse_pairs) {
+        k8_collapse<<<blocks, 256, 0, st>>>(P, keep2);
+        kfinal = keep2;
+    }
+    CK(cudaGetLastError());
+    size_t tb = 0;
+    CK(cub::DeviceScan::ExclusiveSum(nullptr, tb, kfinal, c->d_foff.as<uint64_t>(), (int)n, st));
+    OVL_TRY(dev_ensure(c, c->d_tmp, tb));
+    tb = c->d_tmp.cap;
+    CK(cub::DeviceScan::ExclusiveSum(c->d_tmp.p, tb, kfinal, c->d_foff.as<uint64_t>(), (int)n, st));
+    k8_compact<<<blocks, 256, 0, st>>>(P.rows, n, kfinal, c->d_foff.as<uint64_t>(), c->d_frows.as<Row>());
+    CK(cudaGetLastError());
+    uint64_t h[4] = {0, 0, 0, 0};  // last offset, last flag, contained rows, marked entries
+    CK(cudaMemcpyAsync(&h[0], c->d_foff.as<uint64_t>() + (n - 1), 8, cudaMemcpyDeviceToHost, st));
+    CK(cudaMemcpyAsync(&h[1], kfinal + (n - 1), 4, cudaMemcpyDeviceToHost, st));
+    CK(cudaMemcpyAsync(&h[2], fctr, 16, cudaMemcpyDeviceToHost, st));
+    CK(cudaEventRecord(c->ev[E_D2H1], st));
+    CK(cudaStreamSynchronize(st));
+    const uint64_t kept = h[0] + (h[1] & 0xffffffffull);
+    if (kept) {
+        OVL_TRY(pin_ensure(c, c->h_frows, kept * sizeof(ovl_row), 0));
+        CK(cudaMemcpyAsync(c->h_frows.p, c->d_frows.p, kept * sizeof(ovl_row), cudaMemcpyDeviceToHost, st));
+        CK(cudaStreamSynchronize(st));
+        *rows = reinterpret_cast<const ovl_row*>(c->h_frows.p);
+    }
+    *n_rows = kept;
+    if (fs) {
+        fs->rows_kept = kept;
+        fs->rows_contained = h[2];
+        fs->entries_removed = h[3];
+        fs->ms_device = ev_ms(c, E_D2H0, E_D2H1);
+    }
+    return OVL_OK;
+}

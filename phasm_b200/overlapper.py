@@ -223,6 +223,29 @@ class ExactOverlapper:
         self._check(self._lib.ovl_fetch_rows(self._ctx, byref(p), byref(n)))
         return self._rows_array(p, n.value, copy)
 
+    def filter_rows(self, contained_reads: bool = True, min_read_length: int = 0,
+                    min_overlap_length: int = 0, max_overhang_abs=1000, max_overhang_rel=0.8,
+                    collapse_pairs: bool = False, copy: bool = True):
+        """Optional device post-pass over the rows of the last ``overlaps*`` call: the alignment
+        filters of the reference's ``layout`` stage, in its order and with its streaming semantics
+        (``phasm/cli/assembler.py:76-86``: ``ContainedReads()``, ``MinReadLength``,
+        ``MinOverlapLength``, ``MaxOverhang(abs, rel)``; defaults as the reference CLI,
+        ``assembler.py:469-490``).  ``max_overhang_abs=None`` switches MaxOverhang off.
+        Returns ``(rows, stats)``: the kept rows in canonical order and a dict of counters."""
+        from ._capi import OvlFilterOpts, OvlFilterStats
+        o = OvlFilterOpts()
+        o.contained_reads = int(bool(contained_reads))
+        o.min_read_length = int(min_read_length)
+        o.min_overlap_length = int(min_overlap_length)
+        o.max_overhang = 0 if max_overhang_abs is None else 1
+        o.max_overhang_abs = 0 if max_overhang_abs is None else int(max_overhang_abs)
+        o.max_overhang_rel = float(max_overhang_rel)
+        o.collapse_pairs = int(bool(collapse_pairs))
+        st = OvlFilterStats()
+        p, n = c_void_p(), c_uint64()
+        self._check(self._lib.ovl_filter_rows(self._ctx, byref(o), byref(p), byref(n), byref(st)))
+        return self._rows_array(p, n.value, copy), st.as_dict()
+
     def set_collect_stats(self, on: bool) -> None:
         self._check(self._lib.ovl_set_collect_stats(self._ctx, int(bool(on))))
 
