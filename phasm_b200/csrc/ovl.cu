@@ -95,6 +95,7 @@ struct ovl_ctx {
     DevBuf d_table, d_filter, d_next, d_ctr, d_tmp;
     DevBuf d_cand, d_cand2, d_cnt, d_offs, d_rows, d_cnts, d_bkt, d_fwd;
     DevBuf d_fmark, d_fkeep, d_foff, d_frows;  // ovl_filter_rows
+    DevBuf d_gath;                             // row gather slots (multi-GPU)
     PinBuf h_frows;
     uint64_t* h_ctr = nullptr;  // pinned mirror of d_ctr
     uint64_t cand_cap = 0;  // candidate keys one pass may emit (d_cand/d_cand2 hold the derived hit capacity)
@@ -382,7 +383,7 @@ void ovl_destroy(ovl_ctx* c) {
     DevBuf* bufs[] = {&c->d_ascii, &c->d_src, &c->d_len, &c->d_flags, &c->d_gran0, &c->d_gran_ent,
                       &c->d_ent, &c->d_packed, &c->d_table, &c->d_filter, &c->d_next, &c->d_ctr,
                       &c->d_tmp, &c->d_cand, &c->d_cand2, &c->d_cnt, &c->d_offs, &c->d_rows, &c->d_cnts,
-                      &c->d_tile0, &c->d_tile_ent, &c->d_xchg, &c->d_pre, &c->d_bkt, &c->d_fwd, &c->d_fmark, &c->d_fkeep, &c->d_foff, &c->d_frows};
+                      &c->d_tile0, &c->d_tile_ent, &c->d_xchg, &c->d_pre, &c->d_bkt, &c->d_fwd, &c->d_fmark, &c->d_fkeep, &c->d_foff, &c->d_frows, &c->d_gath};
     for (DevBuf* b : bufs)
         if (b->p) cudaFree(b->p);
     if (c->ascii.p) cudaFreeHost(c->ascii.p);
@@ -1333,6 +1334,18 @@ int ovl_comm_gather_rows_device(ovl_ctx* c, uint64_t* n_rows) {
     CK(cudaStreamSynchronize(c->st));
     uint64_t total = 0;
     for (int r = 0; r < R; ++r) total += cnt[r];
+    uint64_t maxc = 0;
+    for (int r = 0; r < R; ++r) maxc = cnt[r] > maxc ? cnt[r] : maxc;
+    // Rows travel by ONE in-place all-gather of equal, padded slots (a collective uses every NCCL
+    // channel; the grouped point-to-point receives it replaces reached ~40 GB/s per peer, 1.1 ms for
+    // the 32 MB of a 2-rank run).  Above 8 GB of slots fall back to point-to-point.
+    const bool by_allgather = maxc > 0 && (uint64_t)R * maxc * sizeof(ovl_row) <= (8ull << 30);
+    if (by_allgather) {
+        OVL_TRY(dev_ensure(c, c->d_gath, (size_t)R * maxc * sizeof(ovl_row)));
+        ovl_row* G = c->d_gath.as<ovl_row>();
+        if (c->n_rows) CK(cudaMemcpyAsync(G + (size_t)c->rank * maxc, c->d_rows.p, c->n_rows * sizeof(ovl_row), cudaMemcpyDeviceToDevice, c->st));
+        CKN(N.AllGather(G + (size_t)c->rank * maxc, G, (size_t)maxc * sizeof(ovl_row), ncclUint8, c->comm, c->st));
+    }
     if (c->rank == 0) {
         // grow d_rows to hold everything, keeping the local rows at the front
         if (total * sizeof(ovl_row) > c->d_rows.cap) {
@@ -1343,17 +1356,25 @@ int ovl_comm_gather_rows_device(ovl_ctx* c, uint64_t* n_rows) {
             if (c->d_rows.p) CK(cudaFree(c->d_rows.p));
             c->d_rows = nb;
         }
-        CKN(N.GroupStart());
         uint64_t off = cnt[0];
-        for (int r = 1; r < R; ++r) {
-            if (cnt[r]) CKN(N.Recv(c->d_rows.as<ovl_row>() + off, cnt[r] * sizeof(ovl_row), ncclUint8, r, c->comm, c->st));
-            off += cnt[r];
+        if (by_allgather) {
+            const ovl_row* G = c->d_gath.as<ovl_row>();
+            for (int r = 1; r < R; ++r) {
+                if (cnt[r]) CK(cudaMemcpyAsync(c->d_rows.as<ovl_row>() + off, G + (size_t)r * maxc, cnt[r] * sizeof(ovl_row), cudaMemcpyDeviceToDevice, c->st));
+                off += cnt[r];
+            }
+        } else {
+            CKN(N.GroupStart());
+            for (int r = 1; r < R; ++r) {
+                if (cnt[r]) CKN(N.Recv(c->d_rows.as<ovl_row>() + off, cnt[r] * sizeof(ovl_row), ncclUint8, r, c->comm, c->st));
+                off += cnt[r];
+            }
+            CKN(N.GroupEnd());
         }
-        CKN(N.GroupEnd());
         c->n_rows = total;
         c->stats.rows = total;
     } else {
-        if (c->n_rows) {
+        if (c->n_rows && !by_allgather) {
             CKN(N.GroupStart());
             CKN(N.Send(c->d_rows.p, c->n_rows * sizeof(ovl_row), ncclUint8, 0, c->comm, c->st));
             CKN(N.GroupEnd());
