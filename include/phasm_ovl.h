@@ -204,6 +204,29 @@ typedef struct {
 int ovl_filter_rows(ovl_ctx *ctx, const ovl_filter_opts *opts, const ovl_row **rows, uint64_t *n_rows,
                     ovl_filter_stats *stats);
 
+/* ---- GFA2 ingest for the consumer of the overlaps (parsing part; host only,
+ * needs no GPU and no ctx) ----------------------------------------------------------------
+ * ovl_gfa_read replaces the two Python passes of the reference's `layout` stage over the GFA2 file
+ * (phasm/cli/assembler.py:55-60,93-95): gfa2_parse_segments / gfa2_segment_to_read
+ * (phasm/io/gfa.py:34-47,105-107) for the S lines -- a later S line with the same name replaces
+ * the earlier one, as the dict does -- and gfa2_parse_edge / gfa2_line_to_la (gfa.py:72-103) for
+ * the E lines: fields 2 and 3 are segment names with a trailing orientation character, fields 4..7
+ * positions with an optional trailing '$'.  An edge naming an unknown segment is an error
+ * (the reference raises KeyError).  Edges come back in file order, on segment indices. */
+typedef struct ovl_gfa ovl_gfa;
+typedef struct {
+    uint32_t a, b;             /* segment indices (first appearance order of the names)      */
+    uint32_t astart, aend, bstart, bend;
+    uint8_t a_strand, b_strand; /* '+' or '-' (the raw orientation character)               */
+    uint8_t reserved[2];
+} ovl_gfa_edge;
+
+int ovl_gfa_read(const char *path, ovl_gfa **out);
+void ovl_gfa_free(ovl_gfa *g);
+int ovl_gfa_counts(const ovl_gfa *g, uint32_t *n_segments, uint64_t *n_edges);
+int ovl_gfa_segment(const ovl_gfa *g, uint32_t idx, const char **name, size_t *name_len, uint32_t *length);
+int ovl_gfa_edges(const ovl_gfa *g, const ovl_gfa_edge **edges, uint64_t *n_edges);
+
 /* ---- multi-GPU (one process per GPU) ---------------------------------------------------
  * All ranks add the SAME entry table in the same order; rank r scans only the A entries of
  * its contiguous, base-balanced range and returns only those rows.  The rank's packed reads

@@ -38,6 +38,11 @@ class OvlStats(Structure):
         return {n: getattr(self, n) for n, _ in self._fields_}
 
 
+class OvlGfaEdge(Structure):
+    _fields_ = [(n, c_uint32) for n in ("a", "b", "astart", "aend", "bstart", "bend")] + \
+               [("a_strand", ctypes.c_uint8), ("b_strand", ctypes.c_uint8), ("reserved", ctypes.c_uint8 * 2)]
+
+
 class OvlFilterOpts(Structure):
     _fields_ = [("contained_reads", c_uint32), ("min_read_length", c_uint32),
                 ("min_overlap_length", c_uint32), ("max_overhang", c_uint32),
@@ -81,6 +86,11 @@ SIGNATURES = {
     "ovl_write_gfa": (c_int, [_P, c_int, c_int, POINTER(c_uint64)]),
     "ovl_filter_rows": (c_int, [_P, POINTER(OvlFilterOpts), POINTER(c_void_p), POINTER(c_uint64),
                                 POINTER(OvlFilterStats)]),
+    "ovl_gfa_read": (c_int, [c_char_p, POINTER(_P)]),
+    "ovl_gfa_free": (None, [_P]),
+    "ovl_gfa_counts": (c_int, [_P, POINTER(c_uint32), POINTER(c_uint64)]),
+    "ovl_gfa_segment": (c_int, [_P, c_uint32, POINTER(c_void_p), POINTER(c_size_t), POINTER(c_uint32)]),
+    "ovl_gfa_edges": (c_int, [_P, POINTER(c_void_p), POINTER(c_uint64)]),
     "ovl_comm_unique_id": (c_int, [c_void_p]),
     "ovl_comm_init": (c_int, [_P, c_void_p, c_int, c_int]),
     "ovl_comm_sync_ranges": (c_int, [_P]),

@@ -314,3 +314,203 @@ extern "C" int ovl_filter_rows(ovl_ctx* c, const ovl_filter_opts* o, const ovl_r
     }
     return OVL_OK;
 }
+
+// =========================================================================================
+// GFA2 ingest (host only): S and E lines -> segment table + index edges.  Restates
+// gfa2_segment_to_read / gfa2_parse_segments / gfa2_parse_edge / gfa2_line_to_la of
+// /root/reference/phasm/io/gfa.py:34-47,65-107 (see include/phasm_ovl.h).
+#include <unordered_map>
+
+struct ovl_gfa {
+    std::vector<std::string> names;
+    std::vector<uint32_t> lengths;
+    std::vector<ovl_gfa_edge> edges;
+};
+
+namespace {
+
+inline bool py_space(char ch) { return ch == ' ' || ch == '\t' || ch == '\n' || ch == '\r' || ch == '\v' || ch == '\f'; }
+
+inline void py_strip(const char*& p, size_t& n) {
+    while (n && py_space(p[0])) { ++p; --n; }
+    while (n && py_space(p[n - 1])) --n;
+}
+
+// split [p, p+n) on '\t' into at most `cap` fields; returns the number of fields found (may exceed cap)
+inline size_t split_tabs(const char* p, size_t n, const char** f, size_t* fl, size_t cap) {
+    size_t k = 0, start = 0;
+    for (size_t i = 0; i <= n; ++i) {
+        if (i == n || p[i] == '\t') {
+            if (k < cap) { f[k] = p + start; fl[k] = i - start; }
+            ++k;
+            start = i + 1;
+        }
+    }
+    return k;
+}
+
+// Python int() of a field (surrounding whitespace allowed, optional sign); `dollar`: drop one trailing '$' first
+inline bool parse_pos(const char* p, size_t n, bool dollar, uint32_t* out) {
+    if (dollar && n && p[n - 1] == '$') --n;
+    py_strip(p, n);
+    if (n && p[0] == '+') { ++p; --n; }
+    if (!n) return false;
+    uint64_t v = 0;
+    for (size_t i = 0; i < n; ++i) {
+        if (p[i] < '0' || p[i] > '9') return false;
+        v = v * 10 + (uint64_t)(p[i] - '0');
+        if (v > 0xffffffffull) return false;
+    }
+    *out = (uint32_t)v;
+    return true;
+}
+
+int gfa_fail(int code, const char* fmt, ...) {
+    char buf[512];
+    va_list ap;
+    va_start(ap, fmt);
+    vsnprintf(buf, sizeof buf, fmt, ap);
+    va_end(ap);
+    g_create_err = buf;
+    return code;
+}
+
+}  // namespace
+
+extern "C" {
+
+int ovl_gfa_read(const char* path, ovl_gfa** out) {
+    if (!path || !out) return gfa_fail(OVL_E_ARG, "ovl_gfa_read: NULL argument");
+    *out = nullptr;
+    const int fd = open(path, O_RDONLY);
+    if (fd < 0) return gfa_fail(OVL_E_ARG, "cannot open '%s': %s", path, strerror(errno));
+    struct stat sb;
+    if (fstat(fd, &sb) != 0) {
+        close(fd);
+        return gfa_fail(OVL_E_ARG, "cannot stat '%s': %s", path, strerror(errno));
+    }
+    const size_t size = (size_t)sb.st_size;
+    const char* data = nullptr;
+    if (size) {
+        void* m = mmap(nullptr, size, PROT_READ, MAP_PRIVATE, fd, 0);
+        if (m == MAP_FAILED) {
+            close(fd);
+            return gfa_fail(OVL_E_NOMEM, "cannot map '%s': %s", path, strerror(errno));
+        }
+        data = static_cast<const char*>(m);
+    }
+    close(fd);
+    ovl_gfa* g = new (std::nothrow) ovl_gfa();
+    int rc = g ? OVL_OK : gfa_fail(OVL_E_NOMEM, "out of host memory");
+    try {
+        std::unordered_map<std::string, uint32_t> index;
+        // pass 1: segments (gfa2_parse_segments: a dict, so a repeated name keeps its first slot
+        // and takes the later line's length)
+        for (size_t pos = 0, ln = 1; rc == OVL_OK && pos < size; ++ln) {
+            const char* nl = static_cast<const char*>(memchr(data + pos, '\n', size - pos));
+            const size_t len = nl ? (size_t)(nl - (data + pos)) : size - pos;
+            const char* p = data + pos;
+            pos += len + 1;
+            if (!len || p[0] != 'S') continue;
+            size_t n = len;
+            py_strip(p, n);
+            const char* f[4];
+            size_t fl[4];
+            const size_t k = split_tabs(p, n, f, fl, 4);
+            uint32_t L = 0;
+            if (k < 4) rc = gfa_fail(OVL_E_ARG, "%s:%zu: S line with %zu fields (4 needed)", path, ln, k);
+            else if (!parse_pos(f[2], fl[2], false, &L)) rc = gfa_fail(OVL_E_ARG, "%s:%zu: bad segment length", path, ln);
+            if (rc != OVL_OK) break;
+            const char* np = f[1];
+            size_t nn = fl[1];
+            py_strip(np, nn);
+            std::string name(np, nn);
+            auto it = index.find(name);
+            if (it == index.end()) {
+                index.emplace(std::move(name), (uint32_t)g->names.size());
+                g->names.emplace_back(np, nn);
+                g->lengths.push_back(L);
+            } else {
+                g->lengths[it->second] = L;
+            }
+        }
+        // pass 2: edges
+        for (size_t pos = 0, ln = 1; rc == OVL_OK && pos < size; ++ln) {
+            const char* nl = static_cast<const char*>(memchr(data + pos, '\n', size - pos));
+            const size_t len = nl ? (size_t)(nl - (data + pos)) : size - pos;
+            const char* p = data + pos;
+            pos += len + 1;
+            if (!len || p[0] != 'E') continue;
+            size_t n = len;
+            py_strip(p, n);
+            const char* f[9];
+            size_t fl[9];
+            const size_t k = split_tabs(p, n, f, fl, 9);
+            if (k < 9) {
+                rc = gfa_fail(OVL_E_ARG, "%s:%zu: E line with %zu fields (9 needed)", path, ln, k);
+                break;
+            }
+            ovl_gfa_edge e;
+            memset(&e, 0, sizeof e);
+            uint32_t* seg[2] = {&e.a, &e.b};
+            uint8_t* strand[2] = {&e.a_strand, &e.b_strand};
+            for (int s = 0; s < 2 && rc == OVL_OK; ++s) {
+                const char* sp = f[2 + s];
+                size_t sn = fl[2 + s];
+                py_strip(sp, sn);
+                if (!sn) {
+                    rc = gfa_fail(OVL_E_ARG, "%s:%zu: empty segment reference", path, ln);
+                    break;
+                }
+                *strand[s] = (uint8_t)sp[sn - 1];
+                auto it = index.find(std::string(sp, sn - 1));
+                if (it == index.end()) rc = gfa_fail(OVL_E_ARG, "%s:%zu: edge names unknown segment '%.*s'", path, ln, (int)(sn - 1), sp);
+                else *seg[s] = it->second;
+            }
+            if (rc != OVL_OK) break;
+            uint32_t* posf[4] = {&e.astart, &e.aend, &e.bstart, &e.bend};
+            for (int q = 0; q < 4; ++q)
+                if (!parse_pos(f[4 + q], fl[4 + q], true, posf[q])) {
+                    rc = gfa_fail(OVL_E_ARG, "%s:%zu: bad position in field %d", path, ln, 5 + q);
+                    break;
+                }
+            if (rc != OVL_OK) break;
+            g->edges.push_back(e);
+        }
+    } catch (const std::bad_alloc&) {
+        rc = gfa_fail(OVL_E_NOMEM, "out of host memory");
+    }
+    if (data) munmap(const_cast<char*>(data), size);
+    if (rc != OVL_OK) {
+        delete g;
+        return rc;
+    }
+    *out = g;
+    return OVL_OK;
+}
+
+void ovl_gfa_free(ovl_gfa* g) { delete g; }
+
+int ovl_gfa_counts(const ovl_gfa* g, uint32_t* n_segments, uint64_t* n_edges) {
+    if (!g) return OVL_E_ARG;
+    if (n_segments) *n_segments = (uint32_t)g->names.size();
+    if (n_edges) *n_edges = g->edges.size();
+    return OVL_OK;
+}
+
+int ovl_gfa_segment(const ovl_gfa* g, uint32_t idx, const char** name, size_t* name_len, uint32_t* length) {
+    if (!g || idx >= g->names.size()) return OVL_E_ARG;
+    if (name) *name = g->names[idx].data();
+    if (name_len) *name_len = g->names[idx].size();
+    if (length) *length = g->lengths[idx];
+    return OVL_OK;
+}
+
+int ovl_gfa_edges(const ovl_gfa* g, const ovl_gfa_edge** edges, uint64_t* n_edges) {
+    if (!g || !edges || !n_edges) return OVL_E_ARG;
+    *edges = g->edges.empty() ? nullptr : g->edges.data();
+    *n_edges = g->edges.size();
+    return OVL_OK;
+}
+
+}  // extern "C"
