@@ -127,6 +127,27 @@ public:
         return nb;
     }
 
+    // optional device post-pass: the layout stage's alignment filters over the rows of the last call
+    // (ovl_filter_rows; phasm/cli/assembler.py:76-86, phasm/filter.py:36-122)
+    py::array_t<uint32_t> filter_rows(bool contained_reads, unsigned min_read_length, unsigned min_overlap_length,
+                                      py::object max_overhang_abs, double max_overhang_rel, bool collapse_pairs) {
+        ovl_filter_opts o;
+        std::memset(&o, 0, sizeof o);
+        o.contained_reads = contained_reads ? 1 : 0;
+        o.min_read_length = min_read_length;
+        o.min_overlap_length = min_overlap_length;
+        o.max_overhang = max_overhang_abs.is_none() ? 0 : 1;
+        o.max_overhang_abs = max_overhang_abs.is_none() ? 0 : max_overhang_abs.cast<int64_t>();
+        o.max_overhang_rel = max_overhang_rel;
+        o.collapse_pairs = collapse_pairs ? 1 : 0;
+        const ovl_row* rows = nullptr;
+        uint64_t n = 0;
+        check(ovl_filter_rows(ctx_, &o, &rows, &n, nullptr));
+        py::array_t<uint32_t> a({(py::ssize_t)n, (py::ssize_t)5});
+        if (n) std::memcpy(a.mutable_data(), rows, n * sizeof(ovl_row));
+        return a;
+    }
+
     uint64_t run_only(unsigned min_length) {
         const ovl_row* rows = nullptr;
         uint64_t n = 0;
@@ -178,6 +199,10 @@ PYBIND11_MODULE(overlapper, m) {
         .def("run", &Overlapper::run_only)
         .def("write_gfa", &Overlapper::write_gfa, py::arg("fd"), py::arg("header") = true,
              py::arg("segments") = true, py::arg("edges") = true)
+        .def("filter_rows", &Overlapper::filter_rows, py::arg("contained_reads") = true,
+             py::arg("min_read_length") = 0, py::arg("min_overlap_length") = 0,
+             py::arg("max_overhang_abs") = py::int_(1000), py::arg("max_overhang_rel") = 0.8,
+             py::arg("collapse_pairs") = false)
         .def("stats", &Overlapper::stats)
         .def("__len__", &Overlapper::size);
 }

@@ -79,7 +79,7 @@ def test_extension_module_surface(ext):
     # positional-only names arg0/arg1 like the reference binding (src/phasm.cpp:14-15)
     assert "arg0: str, arg1: str" in cls.add_sequence.__doc__
     assert "overlaps(self: phasm.overlapper.ExactOverlapper, arg0: " in cls.overlaps.__doc__
-    for extra in ("add_read", "add_fasta", "overlaps_arrays", "write_gfa", "stats"):
+    for extra in ("add_read", "add_fasta", "overlaps_arrays", "write_gfa", "stats", "filter_rows"):
         assert hasattr(cls, extra)
 
 
@@ -178,3 +178,25 @@ def test_cli_stdout_default(ext, tmp_path):
     head, edges = split_gfa(r.stdout)
     want_head, want_edges = expected_gfa(toy)
     assert head == want_head and edges == want_edges
+
+
+@pytest.mark.gpu
+def test_extension_filter_rows_matches_restatement(ext):
+    """The additive filter_rows of the drop-in module (ovl_filter_rows) against the CPU restatement
+    of the reference's layout filters (oracle/filters.py, pinned on the reference's own classes)."""
+    import numpy as np
+    from oracle import filters as F
+    from phasm_b200 import synth
+    reads = synth.edge_mix(9, 200)
+    ov = ext.ExactOverlapper()
+    lens = []
+    for name, seq in reads:
+        ov.add_read(name, seq)
+        lens += [len(seq), len(seq)]
+    rows = ov.overlaps_arrays(200)
+    assert len(rows) > 0
+    for opt in (dict(), dict(contained_reads=True, collapse_pairs=True, max_overhang_abs=None),
+                dict(contained_reads=False, min_overlap_length=400)):
+        kept, _ = F.filter_rows(rows.tolist(), lens, **opt)
+        got = ov.filter_rows(**opt)
+        assert np.array_equal(got, rows[np.asarray(kept, dtype=np.int64)].reshape(-1, 5)), opt
