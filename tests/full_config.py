@@ -2,7 +2,7 @@
 """Full-size BASELINE config on 1..8 GPUs, checked through the restriction property.
 
     python -m torch.distributed.run --nnodes=1 --nproc-per-node N --master-addr 127.0.0.1 \
-        --master-port 29533 tools/full_config.py --cfg 3 [--window-bases 60e6] [--out file.json]
+        --master-port 29533 tests/full_config.py --cfg 3 [--window-bases 60e6] [--out file.json]
 
 Every rank generates and stages only its read range of the FULL config (BASELINE.json configs,
 phasm_b200/synth.py), the sharded job runs twice (idempotence), and rank 0 checks

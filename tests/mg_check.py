@@ -2,7 +2,7 @@
 """Multi-GPU equivalence check (run under torchrun, one rank per GPU):
 
     python -m torch.distributed.run --nnodes=1 --nproc-per-node N --master-addr 127.0.0.1 \
-        --master-port 29511 tools/mg_check.py [--cfg 2 --scale 0.05] [--mirror 1]
+        --master-port 29511 tests/mg_check.py [--cfg 2 --scale 0.05] [--mirror 1]
 
 Every rank stages only its read range; rank 0 compares the gathered rows with the CPU oracle
 (oracle/overlap_oracle.c) run on the whole read set.  TEST code: may import oracle/.

@@ -1,5 +1,5 @@
 """Multi-GPU path: host plumbing on CPU (gloo, world_size 2) and, on a box with >= 2 GPUs, the
-whole sharded job against the oracle (tools/mg_check.py under torchrun)."""
+whole sharded job against the oracle (tests/mg_check.py under torchrun)."""
 import os
 import subprocess
 import sys
@@ -106,7 +106,7 @@ def test_sharded_job_matches_oracle(extra):
     world = 4 if n >= 4 and "--edge" not in extra else 2
     cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node", str(world),
            "--master-addr", "127.0.0.1", "--master-port", "29519",
-           os.path.join(ROOT, "tools", "mg_check.py")] + extra
+           os.path.join(ROOT, "tests", "mg_check.py")] + extra
     r = subprocess.run(cmd, capture_output=True, text=True, timeout=900, cwd=ROOT)
     assert r.returncode == 0, r.stdout[-3000:] + r.stderr[-3000:]
     assert " OK" in r.stdout
