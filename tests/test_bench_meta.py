@@ -1,0 +1,39 @@
+"""Host-side checks of the measurement plumbing (no GPU): the committed ncu capture that
+bench.py's `roofline.traffic` comes from, and the reference arm's contract keys."""
+import json
+import os
+import subprocess
+import sys
+
+import helpers
+
+ROOT = helpers.ROOT
+
+
+def test_committed_traffic_capture_covers_the_hot_kernels():
+    sys.path.insert(0, ROOT)
+    import bench
+    traffic, src = bench.ncu_traffic()
+    assert traffic and src.endswith("_traffic.json")
+    for prefix in ("k1_pack", "k3_probe", "k4a_head", "k4b_tail"):
+        got = [v for n, v in traffic.items() if n.startswith(prefix)]
+        assert got and all(v > 1e6 for v in got), prefix   # bytes per launch of the bench workload
+    # the launch list and the full summary of the same round are committed beside it
+    tag = src.split("_traffic.json")[0]
+    for suffix in ("_launches.csv", "_launches_summary.txt", "_ncu_full_summary.csv", "_bench.json"):
+        assert os.path.exists(os.path.join(ROOT, "profiles", tag + suffix)), suffix
+    with open(os.path.join(ROOT, "profiles", tag + "_bench.json")) as f:
+        line = json.loads(f.read().strip().splitlines()[-1])
+    for key in ("metric", "value", "unit", "n_gpus", "steps", "warmup", "ms_per_step", "higher_is_better",
+                "scaling", "vs_baseline", "dtype", "data", "config", "e2e", "gpu_launches", "roofline",
+                "cpu_baseline", "clocks"):
+        assert key in line, key
+    assert line["roofline"]["traffic"] and 0 < line["roofline"]["dram_frac"] < 1
+    assert line["gpu_launches"] > 0 and line["e2e"]["h2d_bytes_per_step"] > 0
+
+
+def test_reference_arm_nonzero_rank_exits_quietly():
+    env = dict(os.environ, RANK="1", WORLD_SIZE="2", LOCAL_RANK="1")
+    r = subprocess.run([sys.executable, os.path.join(ROOT, "bench.py"), "--impl", "reference", "--gpus", "2",
+                        "--steps", "1", "--warmup", "0"], capture_output=True, text=True, env=env, timeout=120)
+    assert r.returncode == 0 and r.stdout.strip() == ""
