@@ -29,6 +29,24 @@ def test_matches_reference_parser_on_golden_cases(tmp_path):
         assert got == c["edges"], k
 
 
+def test_python_edge_parser_matches_reference_on_golden_cases():
+    from phasm.io import gfa
+    with open(GOLD) as f:
+        cases = json.load(f)
+    n = 0
+    for c in cases:
+        want = iter(c["edges"])
+        for line in c["text"].splitlines(keepends=True):
+            if line.startswith("E"):
+                sid1, sid2, ar, br, _aln, _tags = gfa.gfa2_parse_edge(line)
+                assert [sid1, sid2, list(ar), list(br)] == next(want)
+                n += 1
+    assert n > 300
+    assert gfa.gfa2_parse_edge("E\tid\ta+\tb-\t1\t2$\t3\t4\t4M\tXX:i:1\n") == ("a+", "b-", (1, 2), (3, 4), "4M", ["XX:i:1"])
+    with pytest.raises(ValueError):
+        gfa.gfa2_parse_edge("S\ta\t5\t*\n")
+
+
 def test_errors(tmp_path):
     with pytest.raises(ValueError, match="unknown segment"):
         parse(tmp_path, "S\ta\t5\t*\nE\t*\ta+\tb-\t0\t5\t0\t5\t*\n")          # the reference: KeyError
