@@ -57,19 +57,24 @@ def measured_peak_gbs():
         return 6650.0, "fallback (B200_PROFILING.md 6.65 TB/s)"
 
 
-def ncu_traffic():
+def ncu_traffic(n_gpus: int, stride: int):
     """Per-kernel DRAM bytes per launch from the newest committed `ncu --set full` capture
-    (profiles/<tag>_traffic.json, written by tools/profsum.py; same workload as this bench)."""
+    (profiles/<tag>_traffic.json, written by tools/profsum.py) -- but only if that capture was
+    taken on THIS workload: same GPU count and anchor stride (a capture of the 1-GPU stride-64
+    scan says nothing about a 4-GPU run).  Otherwise (None, why)."""
     import glob
     files = sorted(glob.glob(os.path.join(ROOT, "profiles", "*_traffic.json")))
     if not files:
-        return None, None
+        return None, "no capture committed"
     try:
         with open(files[-1]) as f:
-            k = json.load(f)["kernels"]
-        return {n: v["dram_bytes_per_launch"] for n, v in k.items()}, os.path.basename(files[-1])
-    except Exception:
-        return None, None
+            d = json.load(f)
+        if int(d.get("n_gpus", 1)) != n_gpus or int(d.get("anchor_stride", 64)) != stride:
+            return None, "%s is a capture of n_gpus=%s stride=%s, this run is n_gpus=%d stride=%d" % (
+                os.path.basename(files[-1]), d.get("n_gpus", 1), d.get("anchor_stride", 64), n_gpus, stride)
+        return {n: v["dram_bytes_per_launch"] for n, v in d["kernels"].items()}, os.path.basename(files[-1])
+    except Exception as e:   # noqa: BLE001
+        return None, "unreadable capture: %s" % e
 
 
 class ClockSampler:
@@ -160,7 +165,7 @@ def cpu_reference_run(shape, sample_bases: int, repeats: int = 1):
         "sample": "%d reads / %d forward bases (all reads starting in one genome window of %s), "
                   "overlaps(%d) wall time only, %.2f s per call"
                   % (n_reads, bases, shape.name, shape.min_length, t),
-        "overlaps_per_s": rows / t, "rows": rows, "seconds": secs, "bases": bases,
+        "overlaps_per_s": rows / t, "rows": rows, "seconds": secs, "bases": bases, "reads": n_reads,
     }
 
 
@@ -182,7 +187,14 @@ def run_reference(args):
         "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup,
         "ms_per_step": 1e3 * t, "higher_is_better": True, "scaling": "weak",
         "vs_baseline": None, "dtype": "u8", "data": "synthetic",
-        "config": workload_config(shape, args.gpus),
+        "config": dict(workload_config(shape, args.gpus),
+                       sampled_from={"reads": shape.n_reads, "entries": 2 * shape.n_reads,
+                                     "forward_bases": shape.n_bases},
+                       reads=r["reads"], entries=2 * r["reads"], forward_bases=r["bases"],
+                       note="the reference needs ~40 min and 28-43 GB per call on the full workload "
+                            "(BASELINE.md section 2): it is timed on a genome-window sample of it, so "
+                            "any ratio against this line compares per-base throughput across problem "
+                            "sizes (cross-size; the reference is super-linear, so it is under-stated)"),
         "overlaps_per_s": r["overlaps_per_s"],
         "cpu_baseline": {k: r[k] for k in ("value", "unit", "cores", "kind", "sample", "host_cores")},
         "e2e": {"value": r["value"], "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
@@ -277,8 +289,8 @@ def run_b200(args):
         ov.comm_sync_ranges()
 
     def step_device():
-        ov.overlaps_device(l)
-        return ov.comm_gather_rows_device() if world > 1 else 0
+        # one pass; on N > 1 ranks the rows of all ranks are gathered into rank 0's HBM inside it
+        return ov.overlaps_device(l)
 
     # ---- two untimed passes with the verifier's byte counters on (data-determined quantities):
     #      (1) every canonical candidate compared = the accounting SURVEY.md 8(d) defines;
@@ -298,6 +310,7 @@ def run_b200(args):
     operand_bytes = st_c["operand_bytes"]
     candidates = st_c["candidates"]
     executed_bytes = st_x["operand_bytes"]
+    rows_canonical = int(sum_over_ranks(float(st_c["rows_local"])))
 
     # ---- device-resident: W warm-up + K timed steps ---------------------------------------
     sampler = ClockSampler(local)
@@ -306,7 +319,8 @@ def run_b200(args):
     for _ in range(args.warmup):
         step_device()
     barrier()
-    stage = {k: 0.0 for k in ("ms_pack", "ms_anchor", "ms_scan", "ms_sort", "ms_verify", "ms_emit", "ms_device")}
+    stage_keys = ("ms_pack", "ms_anchor", "ms_scan", "ms_sort", "ms_verify", "ms_emit", "ms_gather", "ms_device")
+    stage = {k: 0.0 for k in stage_keys}
     launches = lib_launches = 0
     ov.timer_start()
     for _ in range(args.steps):
@@ -328,17 +342,20 @@ def run_b200(args):
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
         stage = {k: float(v) for k, v in zip(sorted(stage), t.tolist())}
     st = ov.stats()
-    n_rows = st["rows"] if rank == 0 else 0
-    n_rows = int(sum_over_ranks(float(n_rows)))  # after the gather rank 0 holds all rows
+    n_rows = int(sum_over_ranks(float(st["rows_local"])))
     value = n_bases_total / (ms_step * 1e-3) / 1e9
 
+    # ---- parity, outside the timed region (rank 0 holds the rows of all ranks in HBM) --------------
+    parity = check_parity(ov, shape, world, rank, n_rows, args.parity_bases) if not args.no_parity else None
+
     # ---- end to end with host buffers: H2D + device + D2H every step --------------------------
+    # 1 GPU: ovl_overlaps (pinned host ASCII in, chunked and packed under the copy; rows out).
+    # N GPUs: ovl_overlaps_local on every rank (the same, and every rank brings its own rows to its
+    # host over its own PCIe link; rank 0 also holds all rows in HBM).
     def step_e2e():
         if world == 1:
             return len(ov.overlaps_arrays(l, copy=False))
-        ov.upload()                      # ovl_upload always re-sends the host staging area
-        ov.overlaps_device(l)
-        return len(ov.comm_gather_rows(copy=False))
+        return len(ov.overlaps_local_arrays(l, copy=False))
 
     for _ in range(min(args.warmup, 3)):
         step_e2e()
@@ -352,9 +369,10 @@ def run_b200(args):
     barrier()
     clocks = sampler.stop() if rank == 0 else None   # warm-up + timed region + e2e steps
     st_e = ov.stats()
-    h2d = int(sum_over_ranks(float(st_e["ascii_bytes"] + 17 * st_e["entries"] + 4)))
+    h2d = int(sum_over_ranks(float(st_e["ascii_bytes"])))
     d2h = n_rows * 20
     e2e_value = n_bases_total / t_e2e / 1e9
+    e2e_parts = {k: max_over_ranks(float(st_e[k])) for k in ("ms_h2d", "ms_exposed", "ms_d2h", "ms_device")}
 
     # ---- roofline of the dominant kernel ----------------------------------------------------
     peak, peak_src = measured_peak_gbs()
@@ -369,13 +387,16 @@ def run_b200(args):
     for k, (b, ms) in kern.items():
         gbs = b / (ms * 1e-3) / 1e9 if ms > 0 else 0.0
         per_kernel[k] = {"alg_bytes": b, "ms": ms, "GBps": gbs, "frac": gbs / peak}
-    b_alg = (2.0 * n_local + 32.0 * st["anchors"] / world + operand_bytes
-             + 32.0 * candidates + 20.0 * st_c["rows"])
-    traffic, traffic_src = ncu_traffic()
-    tmap = {"k1_pack": ("k1_pack",), "k3_scan": ("k3_probe",), "k4_verify": ("k4a_head", "k4b_tail")}
+    # whole path: per rank.  "executed" counts the operand bytes the verifier really
+    # compared (one candidate of each strand-mirror pair); "canonical" all canonical candidates.
+    fixed = 2.0 * n_local + 32.0 * st["anchors"] / world + 20.0 * rows_canonical / world
+    b_exec = fixed + executed_bytes + 32.0 * st_x["candidates"]
+    b_canon = fixed + operand_bytes + 32.0 * candidates
+    traffic, traffic_src = ncu_traffic(world, int(st["anchor_stride"]))
+    tmap = {"k1_pack": ("k1_pack",), "k3_scan": ("k3_filter", "k3_resolve"), "k4_verify": ("k4a_head", "k4b_tail")}
     for k in per_kernel:
         t = None
-        if traffic:   # ncu names carry template arguments (k3_probe<6>): match on the prefix
+        if traffic:   # ncu names carry template arguments (k3_filter<6>): match on the prefix
             got = [sum(v for n, v in traffic.items() if n.startswith(p)) for p in tmap[k]]
             if all(x > 0 for x in got):
                 t = sum(got)
@@ -396,11 +417,14 @@ def run_b200(args):
             "alg_bytes": float(operand_bytes),
             "GBps": operand_bytes / (stage["ms_verify"] * 1e-3) / 1e9 if stage["ms_verify"] > 0 else 0.0,
             "candidates": candidates, "compared": st_x["candidates"]},
-        "whole_path": {"alg_bytes": b_alg, "GBps": b_alg / (ms_step * 1e-3) / 1e9,
-                       "frac": b_alg / (ms_step * 1e-3) / 1e9 / peak},
+        "whole_path": {"alg_bytes": b_exec, "GBps": b_exec / (ms_step * 1e-3) / 1e9,
+                       "frac": b_exec / (ms_step * 1e-3) / 1e9 / peak,
+                       "basis": "executed bytes (rank 0's share; one candidate of each strand-mirror pair compared)",
+                       "canonical": {"alg_bytes": b_canon, "frac": b_canon / (ms_step * 1e-3) / 1e9 / peak}},
     }
 
     if rank == 0:
+        ms_e2e = 1e3 * t_e2e
         line = {
             "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps,
             "warmup": args.warmup, "ms_per_step": ms_step, "higher_is_better": True,
@@ -408,12 +432,22 @@ def run_b200(args):
             "config": workload_config(shape, world),
             "overlaps_per_s": n_rows / (ms_step * 1e-3), "rows": n_rows,
             "candidates": candidates, "verified": st["verified"], "hits": st["hits"],
+            "scan_survivors": st["scan_survivors"], "big_buckets": st["big_buckets"], "retries": st["retries"],
             "mirror": st["mirror"], "anchor_stride": st["anchor_stride"], "stage_ms": stage, "stage_ms_rank0": stage_rank0,
+            "parity": parity,
             "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": h2d,
-                    "d2h_bytes_per_step": d2h, "ms_per_step": 1e3 * t_e2e,
+                    "d2h_bytes_per_step": d2h, "ms_per_step": ms_e2e,
                     "overlaps_per_s": n_rows / t_e2e,
-                    "ms_h2d": st_e["ms_h2d"], "ms_device": st_e["ms_device"], "ms_d2h": st_e["ms_d2h"],
-                    "call": "ExactOverlapper.overlaps_arrays(l, copy=False) == ovl_overlaps: host ASCII in, rows out in the library's pinned host buffer"},
+                    "ms_h2d": e2e_parts["ms_h2d"], "ms_device_after_upload": e2e_parts["ms_exposed"],
+                    "ms_d2h": e2e_parts["ms_d2h"], "ms_device_incl_upload_wait": e2e_parts["ms_device"],
+                    "ms_host_other": ms_e2e - e2e_parts["ms_h2d"] - e2e_parts["ms_exposed"] - e2e_parts["ms_d2h"],
+                    "upload": "chunked: pinned host ASCII -> HBM in pieces, every piece packed (K1) and "
+                              "prefix-tabled under the next piece's copy",
+                    "call": ("ExactOverlapper.overlaps_arrays(l, copy=False) == ovl_overlaps: host ASCII in, rows "
+                             "out in the library's pinned host buffer") if world == 1 else
+                            ("ExactOverlapper.overlaps_local_arrays(l, copy=False) == ovl_overlaps_local on every "
+                             "rank: host ASCII in, the pass (rows of all ranks also gathered into rank 0's HBM), "
+                             "every rank's own rows out over its own PCIe link")},
             "gpu_launches": launches, "lib_launches": lib_launches,
             "roofline": roofline, "clocks": clocks,
         }
@@ -422,11 +456,74 @@ def run_b200(args):
             line["cpu_baseline"] = {k: cb[k] for k in ("value", "unit", "cores", "kind", "sample",
                                                        "host_cores", "overlaps_per_s")}
         print(json.dumps(line), flush=True)
+    ok = 1 if (parity is None or parity.get("bit_exact", True)) else 0
     ov.close()
     if world > 1:
+        t = torch.tensor([ok], device="cuda")
+        dist.broadcast(t, 0)
+        ok = int(t.item())
         dist.barrier()
         dist.destroy_process_group()
-    return 0
+    return 0 if ok else 3
+
+
+def check_parity(ov, shape, world, rank, n_rows, window_bases):
+    """Driver-visible parity at every N, outside the timed region.  Rank 0
+    fetches the gathered rows and checks (a) canonical order and an order-independent checksum,
+    (b) the RESTRICTION property: the rows restricted to all reads that start in
+    one genome window equal, bit for bit, the CPU oracle's rows (oracle/overlap_oracle.c, pinned on
+    the compiled reference) on exactly those reads, (c) the strand-mirror invariant on all rows.
+    The oracle is the checker here, never the thing measured."""
+    if rank != 0:
+        return None
+    from oracle import port
+    from oracle.bruteforce import both_strand_entries
+    t0 = time.perf_counter()
+    rows = ov.fetch_rows(copy=False)
+    res = {"checked": True, "rows": int(len(rows)), "rows_expected_from_ranks": int(n_rows)}
+    ok = len(rows) == n_rows
+    r64 = rows.astype(np.uint64)
+    m2 = np.uint64(2 * shape.n_reads)
+    pair = r64[:, 0] * m2 + r64[:, 1]
+    mix = (pair * np.uint64(0x9E3779B97F4A7C15)) ^ (r64[:, 2] << np.uint64(40)) ^ (r64[:, 3] << np.uint64(20)) ^ r64[:, 4]
+    mix = mix * np.uint64(0xD6E8FEB86659FD93)
+    res["checksum64"] = "%016x" % int(np.bitwise_xor.reduce(mix) ^ np.uint64(np.sum(mix, dtype=np.uint64))) if len(rows) else "0" * 16
+    if len(rows) > 1:
+        d_pair = pair[1:] >= pair[:-1]
+        same = pair[1:] == pair[:-1]
+        in_order = bool(np.all(d_pair) and np.all(r64[1:, 2][same] >= r64[:-1, 2][same]))
+    else:
+        in_order = True
+    res["canonical_order"] = in_order
+    ok = ok and in_order
+    # (b) restriction
+    wb, wo, wn, widx = synth.window_subsample(shape, int(window_bases))
+    reads = [(n, wb[int(wo[i]):int(wo[i + 1])].tobytes().decode()) for i, n in enumerate(wn)]
+    ebuf, eoff = port.entries_to_buffer(both_strand_entries(reads))
+    want, _ = port.oracle_overlaps(ebuf, eoff, shape.min_length)
+    remap = -np.ones(2 * shape.n_reads, dtype=np.int64)
+    remap[2 * widx] = 2 * np.arange(len(widx))
+    remap[2 * widx + 1] = 2 * np.arange(len(widx)) + 1
+    keep = (remap[rows[:, 0]] >= 0) & (remap[rows[:, 1]] >= 0) if len(rows) else np.zeros(0, bool)
+    f = np.array(rows[keep], dtype=np.int64)
+    if len(f):
+        f[:, 0] = remap[f[:, 0]]
+        f[:, 1] = remap[f[:, 1]]
+        f = f[np.lexsort((f[:, 4], f[:, 3], f[:, 2], f[:, 1], f[:, 0]))]
+    exact = f.shape == want.shape and bool(np.array_equal(f.astype(np.uint32), want))
+    res.update({"window_reads": int(len(widx)), "window_bases": int(wo[-1]), "window_rows": int(len(want)),
+                "window_rows_gpu": int(len(f)), "bit_exact": bool(exact and ok),
+                "oracle": "oracle/overlap_oracle.c (C restatement pinned on the compiled reference)"})
+    # (c) strand-mirror invariant over all suffix-prefix rows (fixed read length)
+    rl = shape.read_len
+    sp = r64[r64[:, 3] == np.uint64(rl)] if len(rows) else r64
+    if len(sp):
+        k_fwd = np.sort((sp[:, 0] * m2 + sp[:, 1]) * np.uint64(rl + 1) + sp[:, 4])
+        k_twin = np.sort(((sp[:, 1] ^ np.uint64(1)) * m2 + (sp[:, 0] ^ np.uint64(1))) * np.uint64(rl + 1) + sp[:, 4])
+        res["mirror_invariant"] = bool(np.array_equal(k_fwd, k_twin))
+        res["bit_exact"] = bool(res["bit_exact"] and res["mirror_invariant"])
+    res["seconds"] = time.perf_counter() - t0
+    return res
 
 
 def main():
@@ -439,6 +536,9 @@ def main():
     ap.add_argument("--cpu-sample", type=int, default=4_000_000,
                     help="forward bases of the cpu_baseline sample (~15-20 s of reference CPU work)")
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
+    ap.add_argument("--no-parity", action="store_true", help="skip the parity check after the timed region")
+    ap.add_argument("--parity-bases", type=float, default=40e6,
+                    help="forward bases of the genome window the parity check runs the CPU oracle on")
     ap.add_argument("--opt", action="append", default=[], metavar="NAME=VALUE",
                     help="debug: ovl_set_option tuning knob (e.g. anchor_stride=16, mirror=0)")
     args = ap.parse_args()

@@ -72,9 +72,14 @@ typedef struct {
     float ms_h2d, ms_pack, ms_anchor, ms_scan, ms_sort, ms_verify, ms_emit, ms_d2h;
     float ms_device;           /* pack..emit: ASCII resident in HBM -> rows resident      */
     float ms_total;            /* h2d..d2h                                                */
-    uint32_t radix_fallback;   /* 1: an entry had too many hits for the bucket sort; the    */
-                               /* device-wide radix sort ordered the hit keys instead      */
-    uint32_t reserved0;
+    uint32_t radix_fallback;   /* always 0 since round 2 (big buckets are sorted on the   */
+                               /* device by k7_sort_big); kept for layout compatibility   */
+    uint32_t big_buckets;      /* A entries with more than 256 hit keys                   */
+    uint64_t scan_survivors;   /* probes that passed the scan's bit filter                */
+    uint64_t rows_local;       /* rows this rank emitted (multi-GPU: before the gather)   */
+    float ms_gather;           /* multi-GPU: rows of all ranks into rank 0's HBM          */
+    float ms_exposed;          /* ovl_overlaps: device time left after the last upload    */
+                               /* piece landed (== ms_device when nothing was uploaded)   */
 } ovl_stats;
 
 /* ---- lifetime -------------------------------------------------------------------------
@@ -140,7 +145,11 @@ int ovl_set_collect_stats(ovl_ctx *ctx, int on);
  * "pack_blocks_per_sm": K1 grid size per SM (1..32, default 16).  "serial_verify": 1 = chunk-by-chunk early-exit
  * verifier instead of the head/tail two-pass form.  "mirror": 0 = compare every candidate even
  * when every read is present on both strands (default 1: compare one of each strand-mirror
- * pair and emit both rows). */
+ * pair and emit both rows).  "filter_kb": budget of the scan's bit filter in KiB (default 8192).
+ * "upload_chunks": pieces of the host -> HBM upload of ovl_overlaps (1..16, default 8; every piece
+ * is packed while the next one is copied).  "cand_per_entry" / "min_cand_cap": first candidate
+ * capacity (keys per local entry, floor); an overflow is detected on the device, the buffers grow and
+ * the pass repeats (stats.retries).  "peer_timeout_ms": how long a multi-GPU pass waits for a peer. */
 int ovl_set_option(ovl_ctx *ctx, const char *name, int64_t value);
 int ovl_get_stats(const ovl_ctx *ctx, ovl_stats *out);
 
@@ -242,6 +251,12 @@ int ovl_comm_sync_ranges(ovl_ctx *ctx);
  * The _device form leaves the gathered rows in rank 0's HBM (ovl_fetch_rows reads them). */
 int ovl_comm_gather_rows_device(ovl_ctx *ctx, uint64_t *n_rows);
 int ovl_comm_gather_rows(ovl_ctx *ctx, const ovl_row **rows, uint64_t *n_rows);
+/* This rank's OWN rows of the last pass (stats.rows_local of them), HBM -> pinned host: every rank
+ * of a multi-GPU job can bring its share to its host over its own PCIe link. */
+int ovl_fetch_local_rows(ovl_ctx *ctx, const ovl_row **rows, uint64_t *n_rows);
+/* ovl_overlaps for a consumer that stays sharded: host buffers in on every rank (chunked upload),
+ * the pass, then ovl_fetch_local_rows.  Collective: every rank calls it. */
+int ovl_overlaps_local(ovl_ctx *ctx, uint32_t min_length, const ovl_row **rows, uint64_t *n_rows);
 
 /* ---- debug / test hooks (device layout introspection) -----------------------------------
  * Copy the 2-bit packed granules of entry idx (ceil(len/64)*16 bytes) to out; used by the

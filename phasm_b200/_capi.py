@@ -32,7 +32,9 @@ class OvlStats(Structure):
                 [("verified", c_uint64), ("hits_sent", c_uint64), ("hits_received", c_uint64)] +
                 [(n, c_float) for n in ("ms_h2d", "ms_pack", "ms_anchor", "ms_scan", "ms_sort",
                                         "ms_verify", "ms_emit", "ms_d2h", "ms_device", "ms_total")] +
-                [("radix_fallback", c_uint32), ("reserved0", c_uint32)])
+                [("radix_fallback", c_uint32), ("big_buckets", c_uint32),
+                 ("scan_survivors", c_uint64), ("rows_local", c_uint64),
+                 ("ms_gather", c_float), ("ms_exposed", c_float)])
 
     def as_dict(self):
         return {n: getattr(self, n) for n, _ in self._fields_}
@@ -96,6 +98,8 @@ SIGNATURES = {
     "ovl_comm_sync_ranges": (c_int, [_P]),
     "ovl_comm_gather_rows_device": (c_int, [_P, POINTER(c_uint64)]),
     "ovl_comm_gather_rows": (c_int, [_P, POINTER(c_void_p), POINTER(c_uint64)]),
+    "ovl_fetch_local_rows": (c_int, [_P, POINTER(c_void_p), POINTER(c_uint64)]),
+    "ovl_overlaps_local": (c_int, [_P, c_uint32, POINTER(c_void_p), POINTER(c_uint64)]),
     "ovl_debug_packed": (c_int, [_P, c_uint32, c_void_p, c_size_t, POINTER(c_size_t)]),
 }
 

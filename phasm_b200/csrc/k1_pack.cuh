@@ -1,5 +1,5 @@
-// k1_pack.cuh -- K0 granule->entry map, K1 ASCII -> 2-bit packing with the reverse complement
-// produced in the same pass.
+// k1_pack.cuh -- K0 tile->entry maps, K1 ASCII -> 2-bit packing with the reverse complement
+// produced in the same pass, k1_rc (multi-GPU: twin strands of the reads other ranks packed).
 //
 // Replaces, on the device, what the reference does on the host per FASTA record:
 // `add_sequence(name+"+", seq)` / `add_sequence(name+"-", dinopy.reverse_complement(seq))`
@@ -14,7 +14,8 @@
 // L = 16m + r bases is the bit-reversed, complemented 32-bit window that starts 2r bits into
 // forward word m-j-1, so a thread needs its own word and its right neighbour's, which comes
 // by warp shuffle (the tile's last unit re-packs one halo unit).  The ASCII is read once and
-// never re-read for the second strand.  The tile -> entry map is written by K0.
+// never re-read for the second strand.  The tile -> entry map is written by K0.  The forward
+// words go to the forward region of the packed array, the twin's to the twin region (ovl_common.cuh).
 //
 // Roofline: HBM.  Algorithmic bytes per FORWARD base when both strands are added:
 // 1.0 (ASCII read once) + 0.5 (2 x 2 bit written).
@@ -23,21 +24,44 @@
 
 namespace ovl {
 
-// K0: one warp per entry writes the entry index into every granule it owns and the packed
-// {first granule, length} pair the scan / verify kernels read.
-__global__ void __launch_bounds__(256) k0_gran_entry(const uint32_t* __restrict__ gran0,
-                                                     uint32_t* __restrict__ gran_ent,
-                                                     const uint32_t* __restrict__ tile0,
-                                                     uint32_t* __restrict__ tile_ent,
-                                                     uint32_t e_begin, uint32_t e_end) {
+// K0 (run when the entry table is uploaded, not per pass): the maps that tell a warp which
+// entry a tile of work belongs to -- tile_ent for K1 (tiles of 2048 bases inside ONE forward
+// entry), tile_idx for the scan (tiles of 32 consecutive granules of the packed array: index into
+// `reg`, the entries in granule order, of the entry holding the tile's first granule; lanes walk
+// forward from there).  4 bytes per 2048 bases instead of the 4 bytes per granule a
+// granule -> entry array costs (52 MB of extra scan traffic on config 2).
+struct ScanRanges {
+    uint32_t g_begin[2], g_end[2];  // granule ranges of the local A entries: forward-region slice, twin-region slice
+    uint32_t i_begin[2], i_end[2];  // the same ranges as indices into `reg`
+    uint32_t t_begin[2];            // first tile of each range in the concatenated tile space
+    uint32_t n_tiles;
+};
+
+__global__ void __launch_bounds__(256) k0_tile_ent(const uint32_t* __restrict__ tile0, uint32_t* __restrict__ tile_ent,
+                                                   uint32_t e_begin, uint32_t e_end) {
     const uint32_t lane = threadIdx.x & 31;
     const uint32_t warp = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
     const uint32_t nwarps = (gridDim.x * blockDim.x) >> 5;
     for (uint32_t e = e_begin + warp; e < e_end; e += nwarps) {
-        const uint32_t g0 = gran0[e], g1 = gran0[e + 1];
-        for (uint32_t g = g0 + lane; g < g1; g += 32) gran_ent[g] = e;
         const uint32_t t0 = tile0[e], t1 = tile0[e + 1];
         for (uint32_t t = t0 + lane; t < t1; t += 32) tile_ent[t] = e;
+    }
+}
+
+__global__ void __launch_bounds__(256) k0_tile_idx(const uint4* __restrict__ reg, uint32_t* __restrict__ tile_idx,
+                                                   const ScanRanges R) {
+    const uint32_t lane = threadIdx.x & 31;
+    const uint32_t warp = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+    const uint32_t nwarps = (gridDim.x * blockDim.x) >> 5;
+#pragma unroll
+    for (int r = 0; r < 2; ++r) {
+        const uint32_t gb = R.g_begin[r];
+        for (uint32_t i = R.i_begin[r] + warp; i < R.i_end[r]; i += nwarps) {
+            const uint4 rec = reg[i];
+            const uint32_t o0 = rec.x - gb, o1 = o0 + rec.w;  // granule offsets inside the range
+            const uint32_t t0 = (o0 + 31) >> 5, t1 = (o1 + 31) >> 5;
+            for (uint32_t t = t0 + lane; t < t1; t += 32) tile_idx[R.t_begin[r] + t] = i;
+        }
     }
 }
 
@@ -98,8 +122,6 @@ struct PackParams {
     const uint32_t* tile0;     // [M+1] first tile of every entry (0 tiles for twins / remote entries)
     const uint32_t* tile_ent;  // [n_tiles]
     uint32_t* packed32;
-    uint32_t* fwd32;           // multi-GPU, paired entries: compact copy of the FORWARD granules (entry e at
-                               // granule gran0[e]/2) -- what the ranks exchange; nullptr otherwise
     uint32_t M;
     uint32_t t_begin, t_end;   // tiles of the local entries
     uint32_t* err;             // set to (entry index + 1) of some entry holding a non-ACGT byte
@@ -140,10 +162,7 @@ __global__ void __launch_bounds__(256) k1_pack(const PackParams P) {
             const uint32_t u = u0 + 32u * i + lane;
             const int nvalid = (int)L - 16 * (int)u;
             W[i] = nvalid >= 16 ? pack16(v[i], bad) : (nvalid > 0 ? pack16_partial(v[i], nvalid, bad) : 0u);
-            if (u < units) {
-                out[u] = W[i];
-                if (P.fwd32) P.fwd32[4ull * (m_e.x >> 1) + u] = W[i];
-            }
+            if (u < units) out[u] = W[i];
         }
         uint32_t Wh = 0;
         if (need_halo) {
@@ -171,27 +190,27 @@ __global__ void __launch_bounds__(256) k1_pack(const PackParams P) {
     }
 }
 
-// Multi-GPU: rebuild both strands of the REMOTE reads from the compact forward granules the ranks
-// exchanged (half the NVLink volume of replicating the packed array itself).  Paired layout only:
-// entry 2i is read i forward at granule gran0[2i], entry 2i+1 its reverse complement right behind
-// it, so the compact array holds read i at granule gran0[2i]/2.  One block per read of
-// [pair_begin, pair_end), one thread per granule: copies it into place and writes the four
-// reverse-complement words it determines (same word arithmetic as the twin part of k1_pack).
-__global__ void __launch_bounds__(128) k1_expand(const uint4* __restrict__ fwd, const uint32_t* __restrict__ gran0,
-                                                 const uint32_t* __restrict__ len, uint32_t* __restrict__ packed32,
-                                                 uint32_t pair_begin, uint32_t pair_end) {
-    const uint32_t e = 2u * (pair_begin + blockIdx.x);
-    if (e >= 2u * pair_end) return;
-    const uint32_t g0 = __ldg(gran0 + e), g1 = __ldg(gran0 + e + 1), L = __ldg(len + e);
+// Multi-GPU: the reverse-complement strand of the REMOTE reads.  Only the forward region of the
+// packed array travels between the ranks (half the NVLink volume of replicating both strands,
+// and it lands in place: no staging copy); the twin region of the remote reads is rebuilt here.
+// One block per entry of [e_begin, e_end): an entry followed by its twin reads its own granules
+// and writes the twin's, one thread per granule (same word arithmetic as the twin part of
+// k1_pack); all other blocks exit.
+__global__ void __launch_bounds__(128) k1_rc(const uint2* __restrict__ ent, const uint8_t* __restrict__ flags,
+                                             uint32_t* __restrict__ packed32, uint32_t e_begin, uint32_t e_end,
+                                             uint32_t M) {
+    const uint32_t e = e_begin + blockIdx.x;
+    if (e >= e_end || e + 1 >= M) return;
+    if ((__ldg(flags + e) & 1) || !(__ldg(flags + e + 1) & 1)) return;
+    const uint2 m_e = __ldg(ent + e);
+    const uint32_t L = m_e.y;
     const uint32_t ng = (L + 63u) >> 6, units = 4u * ng;
-    const uint4* src = fwd + (g0 >> 1);
-    uint4* dst = reinterpret_cast<uint4*>(packed32) + g0;
-    uint32_t* rc = packed32 + 4ull * g1;
+    const uint4* src = reinterpret_cast<const uint4*>(packed32) + m_e.x;
+    uint32_t* rc = packed32 + 4ull * __ldg(ent + e + 1).x;
     const uint32_t m = L >> 4, r = L & 15u;
     for (uint32_t ig = threadIdx.x; ig < ng; ig += blockDim.x) {
         const uint4 v = src[ig];
         const uint32_t wn = ig + 1 < ng ? reinterpret_cast<const uint32_t*>(src + ig + 1)[0] : 0u;
-        dst[ig] = v;
         const uint32_t W[5] = {v.x, v.y, v.z, v.w, wn};
 #pragma unroll
         for (int k = 0; k < 4; ++k) {

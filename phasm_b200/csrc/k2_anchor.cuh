@@ -13,8 +13,10 @@
 //
 // The table is open addressing on a 32-bit fingerprint of the k-mer with a linked list of anchor ids
 // (b * stride + delta) per key: one kernel, no sort.  Which anchor ends up where in a list
-// depends on thread timing, but the candidates are radix-sorted before they are verified, so
-// the output is deterministic.
+// depends on thread timing, but the hit keys are sorted before rows are made, so the output is
+// deterministic.  On N GPUs the key space is PARTITIONED by hash (ovl_common.cuh): every rank
+// hashes all M * stride keys but inserts only its own 1/N, so the build cost and the table size
+// per GPU do not grow with N.
 //
 // Roofline: HBM/L2-latency; tiny (one 16-byte slot + 4 B per anchor).
 #pragma once
@@ -29,13 +31,16 @@ struct AnchorParams {
     uint32_t l;
     int k;
     int stride_log2;
-    Slot* table;            // 1 << tbits slots, all EMPTY_SLOT
+    Slot* table;            // THIS rank's partition: 1 << tbits slots, all EMPTY_SLOT
     int tbits;
-    uint32_t* next;         // [M << stride_log2]
-    uint32_t* bitmap;       // sparse path: 1 << bm_bits bits   (dense path: bloom words)
-    int bm_bits;            // sparse: log2 bits; dense: log2 WORDS of the blocked bloom filter
+    uint32_t* next;         // [M << stride_log2], written only for nodes that have a successor
+    uint32_t* bitmap;       // sparse path: nr slices of 1 << slice_log2 bits (this rank fills its own)
+                            // dense path: 1 << bm_bits bloom WORDS (every rank fills all of it)
+    int bm_bits;            // sparse: log2 bits of ONE slice; dense: log2 words of the blocked bloom filter
     int dense;              // 1: stride == 1, fill the blocked bloom filter instead of the bitmap
+    uint32_t me, nr;        // this rank / ranks: only keys with owner_of_hash() == me are inserted
     unsigned long long* n_anchors;  // entries with |b| >= l
+    unsigned long long* flags;  // STF_TABLE is raised if the partition is full (cannot happen at the load factor ovl.cu sizes it for)
 };
 
 // Prefix table: the first two granules (128 bases) of every entry in one compact array.  K2 only
@@ -74,7 +79,12 @@ __global__ void __launch_bounds__(128) k2_prefix_ascii(const uint8_t* __restrict
     pre[2ull * e + 1] = make_uint4((uint32_t)w[2], (uint32_t)(w[2] >> 32), (uint32_t)w[3], (uint32_t)(w[3] >> 32));
 }
 
-// One thread per (entry, delta).
+// One thread per (entry, delta); a thread whose key belongs to another rank's partition stops
+// after the hash.  Insert protocol: an empty slot is claimed with a 64-bit compare-and-swap
+// {fingerprint | id}; a slot that already holds the key gets the new id exchanged into its low
+// word with the HAS_NEXT bit set, and the previous list pointer (flag included) goes to next[id].
+// Slots are only ever claimed, never released, so a reader that sees the key's fingerprint may
+// exchange without re-checking.
 __global__ void __launch_bounds__(256) k2_insert(const AnchorParams P) {
     const uint64_t idx = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
     const uint32_t b = (uint32_t)(idx >> P.stride_log2);
@@ -87,52 +97,43 @@ __global__ void __launch_bounds__(256) k2_insert(const AnchorParams P) {
             const uint64_t* w = P.pre64 + 4ull * b + (delta >> 5);  // delta + k <= 95: words 0..2
             const uint64_t x = kmer_at(w[0], w[1], delta & 31) & kmer_mask(P.k);
             const uint64_t h = mix64(x);
-            const uint32_t fp = (uint32_t)h;
-            const uint32_t tmask = (1u << P.tbits) - 1u;
-            uint32_t s = slot_of(h, P.tbits);
-            uint32_t prev_head;
-            // (Reading the slot before the compare-and-swap is deliberate: an optimistic CAS-first
-            // variant measured slower on B200, 0.34 -> 0.43 ms for pack + anchor build.)
-            for (;;) {
-                unsigned long long v = *reinterpret_cast<volatile unsigned long long*>(P.table + s);
-                if (v == EMPTY_SLOT) {
-                    v = atomicCAS(P.table + s, EMPTY_SLOT, ((unsigned long long)fp << 32) | (uint32_t)idx);
-                    if (v == EMPTY_SLOT) {  // claimed the slot: this anchor is the list's tail
-                        prev_head = NIL;
-                        break;
-                    }
-                }
-                if ((uint32_t)(v >> 32) == fp) {  // the key's slot: push on its list
-                    prev_head = atomicExch(reinterpret_cast<uint32_t*>(P.table + s), (uint32_t)idx);
-                    break;
-                }
-                s = (s + 1) & tmask;
-            }
-            P.next[idx] = prev_head;
-            if (P.dense) {
+            if (P.dense) {  // replicated filter, partitioned table
                 const uint32_t h32 = kmer_hash(x);
                 atomicOr(&P.bitmap[filter_word(h32, P.bm_bits)], filter_bits(h32));
-            } else {
-                const uint32_t bit = bitmap_bit(h, P.bm_bits);
-                atomicOr(&P.bitmap[bit >> 5], 1u << (bit & 31));
+            }
+            if (owner_of_hash(h, P.nr) == P.me) {
+                const uint32_t fp = (uint32_t)h;
+                const uint32_t tmask = (1u << P.tbits) - 1u;
+                uint32_t s = slot_of(h, P.nr, P.tbits);
+                uint32_t tries = 0;
+                // (Reading the slot before the compare-and-swap is deliberate: an optimistic CAS-first
+                // variant measured slower on B200, 0.34 -> 0.43 ms for pack + anchor build.)
+                for (;; ++tries) {
+                    if (tries > tmask) {
+                        atomicOr(P.flags, STF_TABLE);
+                        break;
+                    }
+                    unsigned long long v = *reinterpret_cast<volatile unsigned long long*>(P.table + s);
+                    if (v == EMPTY_SLOT) {
+                        v = atomicCAS(P.table + s, EMPTY_SLOT, ((unsigned long long)fp << 32) | (uint32_t)idx);
+                        if (v == EMPTY_SLOT) break;  // claimed the slot: a singleton so far, nothing else to write
+                    }
+                    if ((uint32_t)(v >> 32) == fp) {  // the key's slot: push on its list
+                        const uint32_t prev = atomicExch(reinterpret_cast<uint32_t*>(P.table + s), (uint32_t)idx | HAS_NEXT);
+                        P.next[idx] = prev;
+                        break;
+                    }
+                    s = (s + 1) & tmask;
+                }
+                if (!P.dense) {
+                    const uint64_t bit = bitmap_bit(h, P.nr, P.bm_bits);
+                    atomicOr(&P.bitmap[bit >> 5], 1u << (bit & 31));
+                }
             }
         }
     }
     const unsigned mk = __ballot_sync(FULL, is_anchor0);
     if ((threadIdx.x & 31) == 0 && mk) atomicAdd(P.n_anchors, (unsigned long long)__popc(mk));
-}
-
-// Table lookup shared by the scan kernels: head of the anchor list of k-mer x, NIL if absent.
-__device__ __forceinline__ uint32_t table_find(const Slot* __restrict__ table, int tbits, uint64_t h) {
-    const uint32_t tmask = (1u << tbits) - 1u;
-    const uint32_t fp = (uint32_t)h;
-    uint32_t s = slot_of(h, tbits);
-    for (;;) {
-        const unsigned long long v = __ldg(table + s);
-        if (v == EMPTY_SLOT) return NIL;
-        if ((uint32_t)(v >> 32) == fp) return (uint32_t)v;
-        s = (s + 1) & tmask;
-    }
 }
 
 }  // namespace ovl

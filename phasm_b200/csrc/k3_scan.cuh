@@ -4,147 +4,210 @@
 // of walking a suffix tree to learn which suffixes of A end at a node on the path to B's leaf,
 // A positions look their k-mer up among the indexed B k-mers (k2_anchor.cuh).
 //
-// Mapping (both kernels): a warp owns a tile of 32 consecutive granules (2048 bases); each lane
-// loads its granule with ONE coalesced 128-bit load (512 B per warp) and takes the following
-// word from the next lane by shuffle (the k-mer carry across granules).
+// Mapping: a warp owns a tile of 32 consecutive granules (2048 bases) of the local A ranges;
+// each lane loads its granule with ONE coalesced 128-bit load (512 B per warp) and takes the
+// following word from the next lane by shuffle (the k-mer carry across granules).  The entry a
+// granule belongs to comes from the tile -> entry map (k0_tile_idx) and a short forward walk
+// over `reg`, the entries in granule order.
 //
-//   k3_probe  (stride >= 2; stride 64 whenever l >= 95): only the positions q = 0 mod stride are
-//             probed -- 64/stride k-mers per granule, word-aligned for stride 32/64 -- against
-//             an L2-resident one-bit-per-key bitmap, then the hash table.  The kernel streams
-//             the packed reads at 0.25 B/base and is HBM/L2-latency bound, not issue bound.
-//   k3_scan   (stride 1: l < 33, or the canonical-candidate accounting pass): every position
-//             rolls its k-mer and tests a blocked bloom filter held in shared memory; filter
-//             hits are resolved afterwards, warp-converged, against the table.  ~14 integer
-//             instructions per position: issue bound.
+// The sparse scan (stride >= 2; stride 64 whenever l >= 95) is split in two kernels, because the
+// two halves want different shapes:
+//
+//   k3_filter   streams the packed reads (0.25 B/base per strand) and tests the k-mer at every
+//               stride-th position against the L2-resident one-bit-per-key bitmap.  The dependent
+//               chain of a tile is granule -> bitmap word, nothing else; the few positions that
+//               pass are appended as 16-byte SURVIVOR records {hash, a, q}.
+//   k3_resolve  one thread per survivor: slot in the owner's table partition (a peer-mapped
+//               pointer when the owner is another GPU: one NVLink round trip for a singleton
+//               key) -> anchor list -> candidate keys, with every lane of a warp busy.
+//
+// (The single-kernel form of round 1 kept a warp on its tile through filter -> slot -> list with
+// ~30 % of the lanes holding a hit: 6 us per tile, 12 % of the HBM roofline.)
+//
+//   k3_scan     (stride 1: l < 33, or the canonical-candidate accounting pass): every position
+//               rolls its k-mer and tests a blocked bloom filter held in shared memory; filter
+//               hits are resolved in place, warp-converged, against the table.  ~14 integer
+//               instructions per position: issue bound.
 //
 // Candidates are 64-bit keys [a|b|p|00]; they are staged per warp in shared memory and
 // flushed with one global atomic per ~224 keys.
 #pragma once
+#include "k1_pack.cuh"
 #include "k2_anchor.cuh"
 #include "ovl_common.cuh"
 
 namespace ovl {
 
+// survivor of the filter pass: x = k-mer hash, y = (a << 32) | q
+typedef ulonglong2 Surv;
+typedef Sink<Surv> SurvSink;
+
 struct ScanParams {
-    const uint4* packed;        // granules (G + 2, last two zero)
-    const uint32_t* gran_ent;   // [G]
+    const uint4* packed;        // granules
+    const uint4* reg;           // [M+1] entries in granule order {gran0, entry, len, granules}
+    const uint32_t* tile_idx;   // [n_tiles] index into reg of the entry holding the tile's first granule
     const uint2* ent;           // [M] {gran0, len}
-    uint32_t g_begin, g_end;    // granule range of the A entries this launch scans
+    ScanRanges R;               // the local A granules
     uint32_t l;                 // min overlap length (>= 1)
     int k;                      // anchor length
     int stride_log2;
     const uint32_t* filter;     // sparse: bitmap words; dense: bloom words
-    int bm_bits;                // sparse: log2 bits; dense: log2 words
-    const Slot* table;
-    int tbits;
-    const uint32_t* next;
+    int bm_bits;                // sparse: log2 bits of one slice; dense: log2 words
+    TableView T;
     KeyFmt fmt;
+    SurvSink surv;              // k3_filter -> k3_resolve
     CandSink sink;
     MirrorRule mirror;          // on: emit only the candidates that verify for themselves
 };
 
-// ---- sparse path ------------------------------------------------------------------------
+// granule of lane `lane` of tile t, and whether it exists
+__device__ __forceinline__ bool tile_granule(const ScanRanges& R, uint32_t t, uint32_t lane, uint32_t& g) {
+    const int r = t >= R.t_begin[1] ? 1 : 0;
+    g = R.g_begin[r] + (t - R.t_begin[r]) * 32u + lane;
+    return g < R.g_end[r];
+}
+
+// entry record of granule g, walking forward from the tile's first entry
+__device__ __forceinline__ uint4 entry_of(const uint4* __restrict__ reg, uint32_t i, uint32_t g) {
+    uint4 r = __ldg(reg + i);
+    while (g >= r.x + r.w) r = __ldg(reg + ++i);  // the sentinel reg[M] = {G, 0, 0, 0} stops the walk
+    return r;
+}
+
+// candidates of one (a, q) probe whose key resolved to list pointer `ptr` (warp-converged walk)
+__device__ __forceinline__ void walk_list(const ScanParams& P, uint32_t owner, uint32_t ptr, uint32_t a, uint32_t la,
+                                          uint32_t q, uint64_t* buf, uint32_t& nbuf, uint32_t lane) {
+    const int sl = P.stride_log2;
+    const uint32_t smask = (1u << sl) - 1u;
+    while (__any_sync(FULL, ptr != NIL)) {
+        bool have = false;
+        uint64_t key = 0;
+        if (ptr != NIL) {
+            const uint32_t id = ptr & ID_MASK;
+            const uint32_t b = id >> sl, delta = id & smask;
+            const uint32_t nxt = (ptr & HAS_NEXT) ? __ldg(P.T.nxt[owner] + id) : NIL;
+            // candidate p = q - delta: needs p >= 0, |a| - p >= l, and b != a
+            // (identity by index: overlapper.cpp:72-74,101-104)
+            if (q >= delta && b != a && la - (q - delta) >= P.l) {
+                have = !P.mirror.on || mirror_items(P.mirror, a, la, b, __ldg(P.ent + b).y, q - delta) != 0;
+                key = P.fmt.make(a, b, q - delta);
+            }
+            ptr = nxt;
+        }
+        wbuf_push(buf, nbuf, P.sink, lane, have, key);
+    }
+}
+
+// ---- sparse path, pass 1 ------------------------------------------------------------------
 // SL >= 0: the stride is the compile-time constant 2^SL (6, 5, 4 and 3 are instantiated: 1, 2, 4 or
 // 8 k-mers per granule at fixed offsets, loops fully unrolled); SL < 0: read it from the parameters.
-// The warp's NEXT tile (packed granule + entry index) is loaded before the current one is
-// processed, and the filter words are requested before the entry record is needed, so the
-// dependent chain per tile is filter -> table slot -> anchor list, all L2 hits (ncu r01f: 60 % of
-// the stall samples of the previous form waited on exactly these loads one after the other).
+// The warp's NEXT tile is loaded before the current one is processed.
 template <int SL>
-__global__ void __launch_bounds__(256) k3_probe(const ScanParams P) {
-    __shared__ uint64_t s_buf[8][WBUF];
+__global__ void __launch_bounds__(256) k3_filter(const ScanParams P) {
+    __shared__ Surv s_buf[8][WBUF / 2];
     const uint32_t lane = threadIdx.x & 31;
     const uint32_t wib = threadIdx.x >> 5;
     const uint32_t warp = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
     const uint32_t nwarps = (gridDim.x * blockDim.x) >> 5;
-    const uint32_t n_gran = P.g_end - P.g_begin;
-    const uint32_t n_tiles = (n_gran + 31) / 32;
+    const uint32_t n_tiles = P.R.n_tiles;
     const uint64_t kmask = kmer_mask(P.k);
     const uint64_t* packed64 = reinterpret_cast<const uint64_t*>(P.packed);
     const int sl = SL >= 0 ? SL : P.stride_log2;
-    const uint32_t stride = 1u << sl;
     const uint32_t n_probe = GRAN_BASES >> sl;
-    uint64_t* buf = s_buf[wib];
+    const uint32_t nr = P.T.nr;
+    Surv* buf = s_buf[wib];
     uint32_t nbuf = 0;
 
     uint4 v_nx = make_uint4(0, 0, 0, 0);
-    uint32_t a_nx = 0;
+    uint32_t i_nx = 0;
     if (warp < n_tiles) {
-        const uint32_t g = P.g_begin + warp * 32 + lane;
-        if (g < P.g_end) {
-            v_nx = ldg_stream(P.packed + g);
-            a_nx = __ldg(P.gran_ent + g);
-        }
+        uint32_t g;
+        if (tile_granule(P.R, warp, lane, g)) v_nx = ldg_stream(P.packed + g);
+        i_nx = __ldg(P.tile_idx + warp);
     }
     for (uint32_t tile = warp; tile < n_tiles; tile += nwarps) {
-        const uint32_t g = P.g_begin + tile * 32 + lane;
-        const bool inr = g < P.g_end;
+        uint32_t g;
+        const bool inr = tile_granule(P.R, tile, lane, g);
         const uint4 v = v_nx;
-        const uint32_t a = a_nx;
-        {  // prefetch the next tile of this warp
-            const uint32_t gn = g + nwarps * 32;
-            if (tile + nwarps < n_tiles && gn < P.g_end) {
-                v_nx = ldg_stream(P.packed + gn);
-                a_nx = __ldg(P.gran_ent + gn);
-            }
+        const uint32_t i0 = i_nx;
+        if (tile + nwarps < n_tiles) {  // prefetch the next tile of this warp
+            uint32_t gn;
+            if (tile_granule(P.R, tile + nwarps, lane, gn)) v_nx = ldg_stream(P.packed + gn);
+            i_nx = __ldg(P.tile_idx + tile + nwarps);
         }
         const uint64_t w0 = (uint64_t)v.x | ((uint64_t)v.y << 32);
         const uint64_t w1 = (uint64_t)v.z | ((uint64_t)v.w << 32);
-        uint2 m = make_uint2(0, 0);
-        if (inr) m = __ldg(P.ent + a);
         uint64_t w2 = 0;
         if (sl < 5) {  // k-mers that start in the second word run into the next granule
             w2 = __shfl_down_sync(FULL, w0, 1);
-            if (lane == 31) w2 = inr ? packed64[2ull * (g + 1)] : 0;
+            if (lane == 31) w2 = inr ? packed64[2ull * (g + 1)] : 0;  // a spare granule follows the array
         }
-        // phase 1: filter bit of every probed position of this granule (independent loads, issued
-        // before the entry record is looked at)
+        // the filter bit of every probed position of this granule (independent loads, issued before
+        // the entry record is looked at)
         uint32_t fbits = 0;
         if (inr) {
 #pragma unroll 8
             for (uint32_t j = 0; j < n_probe; ++j) {
                 const uint32_t off = j << sl;
                 const uint64_t x = (off < 32 ? kmer_at(w0, w1, off) : kmer_at(w1, w2, off - 32)) & kmask;
-                const uint32_t bit = bitmap_bit(mix64(x), P.bm_bits);
+                const uint64_t bit = bitmap_bit(mix64(x), nr, P.bm_bits);
                 fbits |= ((__ldg(P.filter + (bit >> 5)) >> (bit & 31)) & 1u) << j;
             }
         }
-        const uint32_t L = m.y;
-        const uint32_t pos0 = (g - m.x) * GRAN_BASES;
-        uint32_t hitmask = 0;
-        if (inr && L >= P.l && pos0 + (uint32_t)P.k <= L) {
-            const uint32_t nv = ((L - (uint32_t)P.k - pos0) >> sl) + 1u;  // probes with pos0 + off + k <= L
-            hitmask = nv >= 32 ? fbits : (fbits & ((1u << nv) - 1u));
+        uint32_t hitmask = 0, a = 0, pos0 = 0;
+        if (inr) {
+            const uint4 rec = entry_of(P.reg, i0, g);
+            a = rec.y;
+            const uint32_t L = rec.z;
+            pos0 = (g - rec.x) * GRAN_BASES;
+            // probes q = pos0 + off that can start a row: |a| - p >= l for some p = q - delta,
+            // delta < stride, i.e. at least q + k <= |a| (the exact test is in k3_resolve)
+            if (L >= P.l && pos0 + (uint32_t)P.k <= L) {
+                const uint32_t nv = ((L - (uint32_t)P.k - pos0) >> sl) + 1u;
+                hitmask = nv >= 32 ? fbits : (fbits & ((1u << nv) - 1u));
+            }
         }
-        // phase 2: resolve the (few) filter hits against the table, one position per lane per round
         while (__any_sync(FULL, hitmask != 0)) {
-            uint32_t node = NIL, q = 0;
-            if (hitmask) {
+            Surv rec = make_ulonglong2(0, 0);
+            const bool have = hitmask != 0;
+            if (have) {
                 const uint32_t j = __ffs(hitmask) - 1;
                 hitmask &= hitmask - 1;
                 const uint32_t off = j << sl;
-                q = pos0 + off;
                 const uint64_t x = (off < 32 ? kmer_at(w0, w1, off) : kmer_at(w1, w2, off - 32)) & kmask;
-                node = table_find(P.table, P.tbits, mix64(x));
+                rec.x = mix64(x);
+                rec.y = ((uint64_t)a << 32) | (pos0 + off);
             }
-            while (__any_sync(FULL, node != NIL)) {
-                bool have = false;
-                uint64_t key = 0;
-                if (node != NIL) {
-                    const uint32_t b = node >> sl;
-                    const uint32_t delta = node & (stride - 1u);
-                    const uint32_t nxt = __ldg(P.next + node);
-                    // candidate p = q - delta: needs p >= 0, |a| - p >= l, and b != a
-                    // (identity by index: overlapper.cpp:72-74,101-104)
-                    if (q >= delta && b != a && L - (q - delta) >= P.l) {
-                        have = !P.mirror.on || mirror_items(P.mirror, a, L, b, __ldg(P.ent + b).y, q - delta) != 0;
-                        key = P.fmt.make(a, b, q - delta);
-                    }
-                    node = nxt;
-                }
-                wbuf_push(buf, nbuf, P.sink, lane, have, key);
-            }
+            const unsigned m = __ballot_sync(FULL, have);
+            if (nbuf + 32 > WBUF / 2) wbuf_flush(buf, nbuf, P.surv, lane);
+            if (have) buf[nbuf + __popc(m & ((1u << lane) - 1u))] = rec;
+            nbuf += __popc(m);
+            __syncwarp();
         }
+    }
+    if (nbuf) wbuf_flush(buf, nbuf, P.surv, lane);
+}
+
+// ---- sparse path, pass 2 ------------------------------------------------------------------
+__global__ void __launch_bounds__(256) k3_resolve(const ScanParams P) {
+    __shared__ uint64_t s_buf[8][WBUF];
+    const uint32_t lane = threadIdx.x & 31;
+    uint64_t* buf = s_buf[threadIdx.x >> 5];
+    uint32_t nbuf = 0;
+    const unsigned long long n_all = *P.surv.n_out;
+    const uint64_t n = n_all < P.surv.cap ? n_all : P.surv.cap;
+    const uint64_t nthreads = (uint64_t)gridDim.x * blockDim.x;
+    for (uint64_t i0 = ((uint64_t)blockIdx.x * blockDim.x + threadIdx.x) & ~31ull; i0 < n; i0 += nthreads) {
+        const uint64_t i = i0 + lane;
+        uint32_t ptr = NIL, owner = 0, a = 0, q = 0, la = 0;
+        if (i < n) {
+            const Surv rec = P.surv.out[i];
+            a = (uint32_t)(rec.y >> 32);
+            q = (uint32_t)rec.y;
+            ptr = table_find(P.T, rec.x, owner);
+            la = __ldg(P.ent + a).y;
+        }
+        walk_list(P, owner, ptr, a, la, q, buf, nbuf, lane);
     }
     if (nbuf) wbuf_flush(buf, nbuf, P.sink, lane);
 }
@@ -167,8 +230,7 @@ __global__ void __launch_bounds__(1024, 1) k3_scan(const ScanParams P) {
     const uint32_t lane = threadIdx.x & 31;
     const uint32_t warp = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
     const uint32_t nwarps = (gridDim.x * blockDim.x) >> 5;
-    const uint32_t n_gran = P.g_end - P.g_begin;
-    const uint32_t n_tiles = (n_gran + 31) / 32;
+    const uint32_t n_tiles = P.R.n_tiles;
     const uint64_t kmask = kmer_mask(P.k);
     const uint64_t* packed64 = reinterpret_cast<const uint64_t*>(P.packed);
     const int fwb = P.bm_bits;
@@ -176,25 +238,26 @@ __global__ void __launch_bounds__(1024, 1) k3_scan(const ScanParams P) {
     uint32_t nbuf = 0;
 
     for (uint32_t tile = warp; tile < n_tiles; tile += nwarps) {
-        const uint32_t g = P.g_begin + tile * 32 + lane;
-        const bool inr = g < P.g_end;
+        uint32_t g;
+        const bool inr = tile_granule(P.R, tile, lane, g);
         uint64_t w0 = 0, w1 = 0;
-        uint32_t a = 0, pos0 = 0;
+        uint32_t a = 0, pos0 = 0, la = 0;
         int nvalid = 0;
         if (inr) {
             const uint4 v = ldg_stream(P.packed + g);
             w0 = (uint64_t)v.x | ((uint64_t)v.y << 32);
             w1 = (uint64_t)v.z | ((uint64_t)v.w << 32);
-            a = __ldg(P.gran_ent + g);
-            const uint2 m = __ldg(P.ent + a);
-            pos0 = (g - m.x) * GRAN_BASES;
+            const uint4 rec = entry_of(P.reg, __ldg(P.tile_idx + tile), g);
+            a = rec.y;
+            la = rec.z;
+            pos0 = (g - rec.x) * GRAN_BASES;
             // positions p in [pos0, pos0+64) with L - p >= l
-            const int64_t nv = (int64_t)m.y - (int64_t)P.l + 1 - (int64_t)pos0;
+            const int64_t nv = (int64_t)la - (int64_t)P.l + 1 - (int64_t)pos0;
             nvalid = nv <= 0 ? 0 : (nv >= GRAN_BASES ? GRAN_BASES : (int)nv);
         }
         if (!__any_sync(FULL, nvalid > 0)) continue;
         uint64_t w2 = __shfl_down_sync(FULL, w0, 1);
-        if (lane == 31) w2 = inr ? packed64[2ull * (g + 1)] : 0;  // granule G exists (zero pad)
+        if (lane == 31) w2 = inr ? packed64[2ull * (g + 1)] : 0;  // a spare granule follows the array
 
         uint64_t hits = 0;
 #pragma unroll
@@ -212,31 +275,19 @@ __global__ void __launch_bounds__(1024, 1) k3_scan(const ScanParams P) {
         hits &= nvalid >= 64 ? ~0ull : ((1ull << nvalid) - 1ull);
 
         // ---- resolve filter hits against the table, one position per lane per round ----
+        // stride 1: the anchor id IS b.  The list may hold a itself (always at p == 0, and at
+        // p != 0 for periodic reads): walk_list drops it (identity by index,
+        // overlapper.cpp:72-74,101-104)
         while (__any_sync(FULL, hits != 0)) {
-            uint32_t node = NIL, p = 0;
+            uint32_t ptr = NIL, owner = 0, p = 0;
             if (hits) {
                 const int j = __ffsll((long long)hits) - 1;
                 hits &= hits - 1;
                 p = pos0 + j;
                 const uint64_t x = (j < 32 ? kmer_at(w0, w1, j) : kmer_at(w1, w2, j - 32)) & kmask;
-                node = table_find(P.table, P.tbits, mix64(x));
+                ptr = table_find(P.T, mix64(x), owner);
             }
-            while (__any_sync(FULL, node != NIL)) {
-                bool have = false;
-                uint64_t key = 0;
-                if (node != NIL) {
-                    // stride 1: the anchor id IS b.  The list may hold a itself (always at
-                    // p == 0, and at p != 0 for periodic reads): identity by index,
-                    // overlapper.cpp:72-74,101-104
-                    if (node != a) {
-                        have = !P.mirror.on ||
-                               mirror_items(P.mirror, a, __ldg(P.ent + a).y, node, __ldg(P.ent + node).y, p) != 0;
-                        key = P.fmt.make(a, node, p);
-                    }
-                    node = __ldg(P.next + node);
-                }
-                wbuf_push(buf, nbuf, P.sink, lane, have, key);
-            }
+            walk_list(P, owner, ptr, a, la, p, buf, nbuf, lane);
         }
     }
     if (nbuf) wbuf_flush(buf, nbuf, P.sink, lane);

@@ -25,7 +25,8 @@ namespace ovl {
 
 struct VerifyParams {
     const uint64_t* keys;              // candidate keys (flags clear), any order
-    uint64_t n;
+    const unsigned long long* n_ptr;   // their number: a device counter
+    uint64_t cap;                      // capacity of `keys` (the counter may exceed it on overflow)
     const uint4* packed;
     const uint2* ent;                  // {gran0, len}
     KeyFmt fmt;
@@ -96,14 +97,15 @@ __global__ void __launch_bounds__(256) k4_verify_serial(const VerifyParams P) {
     const uint32_t lane = threadIdx.x & 31;
     const uint64_t warp = ((uint64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
     const uint64_t nwarps = ((uint64_t)gridDim.x * blockDim.x) >> 5;
-    const uint64_t n_tiles = (P.n + 31) / 32;
+    const uint64_t n_all = *P.n_ptr < P.cap ? *P.n_ptr : P.cap;
+    const uint64_t n_tiles = (n_all + 31) / 32;
     unsigned long long sum_m = 0, sum_b = 0;
 
     for (uint64_t tile = warp; tile < n_tiles; tile += nwarps) {
         const uint64_t c = tile * 32 + lane;
         uint64_t key = 0;
         uint32_t my_ga = 0, my_gb = 0, my_sh = 0, my_n = 0, my_fl = 0;
-        if (c < P.n) {
+        if (c < n_all) {
             key = P.keys[c];
             const uint32_t a = P.fmt.a(key), b = P.fmt.b(key), p = P.fmt.p(key);
             const uint2 ma = __ldg(P.ent + a), mb = __ldg(P.ent + b);
@@ -114,7 +116,7 @@ __global__ void __launch_bounds__(256) k4_verify_serial(const VerifyParams P) {
             my_gb = mb.x;
             my_sh = 2u * (p & 63u);
         }
-        const uint32_t cnt = (uint32_t)((P.n - tile * 32) < 32 ? (P.n - tile * 32) : 32);
+        const uint32_t cnt = (uint32_t)((n_all - tile * 32) < 32 ? (n_all - tile * 32) : 32);
         uint32_t my_ok = 0;
         for (uint32_t j = 0; j < cnt; ++j) {
             const uint32_t ga = __shfl_sync(FULL, my_ga, j);
@@ -322,7 +324,8 @@ __global__ void __launch_bounds__(256, 4) k4a_head(const Verify2Params P) {
                 nn[u] = __shfl_sync(FULL, my.n, j0 + u);
                 // lanes past the end re-read the last granule (same address as the last live lane: no
                 // extra wavefront, no zero-initialised registers, no predicates on the loads)
-                gl[u] = min(lane, (nn[u] - 1u) >> 6);
+                // (an empty slot of the group, nn == 0, reads granule 0 of entry 0)
+                gl[u] = nn[u] ? min(lane, (nn[u] - 1u) >> 6) : 0u;
                 load_a(packed128 + ga + gl[u], sh[u] >> 6, big[u], sm[u]);
                 bv[u] = ldg_stream(packed128 + gb + gl[u]);
             }

@@ -1,21 +1,42 @@
-// k6_exchange.cuh -- multi-GPU hit exchange (only with strand-mirror halving on N > 1 ranks).
+// k6_exchange.cuh -- the multi-GPU data path over peer-mapped HBM (NVLink 5 / NVSwitch).
 //
-// With mirror halving a rank compares one candidate of each strand-mirror pair and produces BOTH
-// hit keys; the twin's A entry may belong to another rank's read range.  Rows are emitted by the
-// rank that owns A (that is what keeps "smallest p per (a,b)" local), so the hit
-// keys are partitioned by owner here and shipped with grouped ncclSend/ncclRecv over NVLink --
-// the one real exchange step of the path (8 bytes per hit; no operand bytes move).
+// One process per GPU; every rank allocates an ARENA (ovl.cu) whose CUDA IPC handle the others
+// open at connect time, so a rank holds a device pointer into every peer's arena.  All exchanges
+// of a pass then happen on the device, without NCCL calls and without the host:
 //
-//   k6_count    per destination rank: how many of my hit keys it owns
-//   k6_scatter  stable-less partition of the keys into per-destination runs
+//   * bulk data (prefix table slice, filter slice, the forward region of the packed reads) is
+//     PUSHED into the peers' arenas by the copy engines, followed by an 8-byte copy of the step
+//     id into the peer's flag word (same stream: ordered behind the data);
+//   * a consumer waits with k_wait (one warp spinning on its own arena's flag words, bounded by
+//     a timeout) -- the only kernels that ever wait, and they wait on OTHER GPUs only;
+//   * k6_route ships every verified hit key to the rank that owns its A entry: the keys are
+//     appended straight into the owner's hit list with one system-scope atomicAdd per
+//     (warp, destination) on the owner's counter and plain stores over NVLink;
+//   * k9_push_rows copies a rank's rows into rank 0's row array at the offset given by the row
+//     counts the ranks published to each other.
 //
-// Order inside a run is irrelevant: the receiver radix-sorts everything it owns before K5.
+// The reference has no counterpart (single process, single thread: SURVEY.md 2.1, 8(e)).
 #pragma once
 #include "ovl_common.cuh"
 
 namespace ovl {
 
-constexpr int MAX_RANKS = 64;
+// phases a rank signals to its peers; flag[k][s] in MY arena header = the last step in which rank
+// s completed phase k towards me
+enum Flag { F_PRE = 0, F_FILT, F_FWD, F_HITS, F_ROWCNT, F_ROWS, F_STATUS, F_COUNT };
+
+constexpr int STATUS_WORDS = 8;
+// status vector a rank publishes to everyone at the end of a pass
+enum Status { ST_ERR = 0, ST_NCAND, ST_NSCAN, ST_NHITS, ST_NROWS, ST_FLAGS, ST_NSTAGE, ST_SPARE };
+
+struct alignas(256) ArenaHdr {
+    unsigned long long flag[F_COUNT][MAX_RANKS];
+    unsigned long long rowcnt[MAX_RANKS];
+    unsigned long long status[MAX_RANKS][STATUS_WORDS];
+    unsigned long long inbox_n;    // hit keys appended to this rank's hit list (local and remote atomics)
+    unsigned long long step_word;  // current step id: the source of the 8-byte signal copies
+    unsigned long long abort;      // != 0: a wait timed out, the pass is void
+};
 
 struct RankMap {
     uint32_t e[MAX_RANKS + 1];  // rank r owns entries [e[r], e[r+1])
@@ -28,60 +49,149 @@ __device__ __forceinline__ int owner_of(const RankMap& R, uint32_t a) {
     return r;
 }
 
-__global__ void __launch_bounds__(256)
-k6_count(const uint64_t* __restrict__ keys, uint64_t n, KeyFmt fmt, const RankMap R,
-         unsigned long long* __restrict__ counts) {
-    __shared__ unsigned int s_cnt[MAX_RANKS];
-    for (int i = threadIdx.x; i < R.n; i += blockDim.x) s_cnt[i] = 0;
-    __syncthreads();
-    const uint32_t lane = threadIdx.x & 31;
-    for (uint64_t i0 = ((uint64_t)blockIdx.x * blockDim.x + threadIdx.x) & ~31ull; i0 < n;
-         i0 += (uint64_t)gridDim.x * blockDim.x) {
-        const uint64_t i = i0 + lane;
-        const int dest = i < n ? owner_of(R, fmt.a(keys[i])) : -1;
-        for (int r = 0; r < R.n; ++r) {
-            const unsigned m = __ballot_sync(FULL, dest == r);
-            if (m && lane == 0) atomicAdd(&s_cnt[r], __popc(m));
-        }
-    }
-    __syncthreads();
-    for (int i = threadIdx.x; i < R.n; i += blockDim.x)
-        if (s_cnt[i]) atomicAdd(counts + i, (unsigned long long)s_cnt[i]);
+__device__ __forceinline__ unsigned long long ld_acquire_sys(const unsigned long long* p) {
+    unsigned long long v;
+    asm volatile("ld.acquire.sys.global.u64 %0, [%1];" : "=l"(v) : "l"(p) : "memory");
+    return v;
+}
+__device__ __forceinline__ void st_release_sys(unsigned long long* p, unsigned long long v) {
+    asm volatile("st.release.sys.global.u64 [%0], %1;" ::"l"(p), "l"(v) : "memory");
+}
+__device__ __forceinline__ unsigned long long global_ns() {
+    unsigned long long t;
+    asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+    return t;
 }
 
-// counts[r] is final; cursor[r] starts at 0.  Run r begins at sum(counts[0..r)).
-__global__ void __launch_bounds__(256)
-k6_scatter(const uint64_t* __restrict__ keys, uint64_t n, KeyFmt fmt, const RankMap R,
-           const unsigned long long* __restrict__ counts, unsigned long long* __restrict__ cursor,
-           uint64_t* __restrict__ out) {
-    __shared__ unsigned long long s_off[MAX_RANKS];
-    if (threadIdx.x == 0) {
-        unsigned long long acc = 0;
-        for (int r = 0; r < R.n; ++r) {
-            s_off[r] = acc;
-            acc += counts[r];
+// Wait until every peer s != me has written flags[s] >= step (one lane per peer).  Gives up after
+// timeout_ns and raises the abort word, so that a dead peer costs a bounded time, not a hang.
+__global__ void __launch_bounds__(32) k_wait(const unsigned long long* __restrict__ flags, uint32_t nr, uint32_t me,
+                                             unsigned long long step, unsigned long long timeout_ns,
+                                             unsigned long long* __restrict__ abort_word) {
+    const uint32_t s = threadIdx.x;
+    if (s < nr && s != me) {
+        const unsigned long long t0 = global_ns();
+        while (ld_acquire_sys(flags + s) < step) {
+            if (global_ns() - t0 > timeout_ns) {
+                atomicMax(abort_word, (unsigned long long)(s + 1));
+                break;
+            }
+            __nanosleep(200);
         }
     }
-    __syncthreads();
+    __syncwarp();
+    __threadfence_system();
+}
+
+// Tell every peer that phase `kind` of step `step` is complete on this rank.  Launched behind
+// the kernel whose remote writes it announces (kernel boundary = all of them performed).
+__global__ void __launch_bounds__(32) k_signal(ArenaHdr* const* __restrict__ peer_hdr, uint32_t nr, uint32_t me,
+                                               int kind, unsigned long long step) {
+    const uint32_t s = threadIdx.x;
+    __threadfence_system();
+    if (s < nr && s != me) st_release_sys(&peer_hdr[s]->flag[kind][me], step);
+}
+
+// ---- hit routing ------------------------------------------------------------------------
+// With strand-mirror halving a rank compares one candidate of each strand-mirror pair and
+// produces BOTH hit keys; the twin's A entry may belong to another rank's read range.  Rows are
+// emitted by the rank that owns A (that keeps "smallest p per (a,b)" local).
+struct RouteParams {
+    const uint64_t* keys;              // verified hit keys of this rank's candidates (staging list)
+    const unsigned long long* n_ptr;
+    uint64_t cap;
+    KeyFmt fmt;
+    RankMap map;
+    uint64_t* inbox[MAX_RANKS];               // hit list of every rank (peer-mapped)
+    unsigned long long* inbox_n[MAX_RANKS];   // its append counter (ArenaHdr::inbox_n)
+    uint64_t inbox_cap[MAX_RANKS];
+    uint32_t me;
+    unsigned long long* n_sent;        // stat: keys that left this GPU
+};
+
+__global__ void __launch_bounds__(256) k6_route(const RouteParams P) {
     const uint32_t lane = threadIdx.x & 31;
-    for (uint64_t i0 = ((uint64_t)blockIdx.x * blockDim.x + threadIdx.x) & ~31ull; i0 < n;
-         i0 += (uint64_t)gridDim.x * blockDim.x) {
+    const unsigned long long n_all = *P.n_ptr;
+    const uint64_t n = n_all < P.cap ? n_all : P.cap;
+    const uint64_t nthreads = (uint64_t)gridDim.x * blockDim.x;
+    unsigned long long sent = 0;
+    for (uint64_t i0 = ((uint64_t)blockIdx.x * blockDim.x + threadIdx.x) & ~31ull; i0 < n; i0 += nthreads) {
         const uint64_t i = i0 + lane;
         uint64_t key = 0;
-        int dest = -1;
+        uint32_t dest = 0xffffffffu;
         if (i < n) {
-            key = keys[i];
-            dest = owner_of(R, fmt.a(key));
+            key = P.keys[i];
+            dest = (uint32_t)owner_of(P.map, P.fmt.a(key));
         }
-        for (int r = 0; r < R.n; ++r) {
-            const unsigned m = __ballot_sync(FULL, dest == r);
-            if (!m) continue;
-            unsigned long long base = 0;
-            if (lane == 0) base = atomicAdd(cursor + r, (unsigned long long)__popc(m));
-            base = __shfl_sync(FULL, base, 0);
-            if (dest == r) out[s_off[r] + base + __popc(m & ((1u << lane) - 1u))] = key;
+        const unsigned grp = __match_any_sync(FULL, dest);
+        const uint32_t leader = __ffs(grp) - 1;
+        const uint32_t rank_in = __popc(grp & ((1u << lane) - 1u));
+        unsigned long long base = 0;
+        if (dest != 0xffffffffu && lane == leader)
+            base = atomicAdd_system(P.inbox_n[dest], (unsigned long long)__popc(grp));
+        base = __shfl_sync(FULL, base, leader);
+        if (dest != 0xffffffffu) {
+            if (base + rank_in < P.inbox_cap[dest]) P.inbox[dest][base + rank_in] = key;
+            sent += dest != P.me;
         }
     }
+#pragma unroll
+    for (int d = 16; d > 0; d >>= 1) sent += __shfl_xor_sync(FULL, sent, d);
+    if (lane == 0 && sent) atomicAdd(P.n_sent, sent);
+    __threadfence_system();
+}
+
+// ---- row gather ---------------------------------------------------------------------------
+// rowcnt[s] (this rank's arena) = rows of rank s in this step, published by everyone before this
+// kernel runs.  Rank r's rows go to rank 0's row array behind those of ranks 0..r-1 = canonical
+// (a, b, astart, aend, bend) order, because the ranks own contiguous A ranges in rank order.
+__global__ void __launch_bounds__(256) k9_push_rows(const uint32_t* __restrict__ rows, uint64_t src_cap_rows,
+                                                    const unsigned long long* __restrict__ rowcnt, uint32_t me,
+                                                    uint32_t* __restrict__ dst, uint64_t dst_cap_rows,
+                                                    unsigned long long* __restrict__ status_flags) {
+    unsigned long long off = 0;
+    for (uint32_t s = 0; s < me; ++s) off += rowcnt[s];
+    const unsigned long long n = rowcnt[me];
+    if (n > src_cap_rows) return;  // this rank overflowed: the pass is repeated (STF_OVERFLOW)
+    if (off + n > dst_cap_rows) {
+        if (blockIdx.x == 0 && threadIdx.x == 0) atomicOr(status_flags, STF_GATHER);
+        return;
+    }
+    const uint64_t words = 5ull * n;
+    uint32_t* out = dst + 5ull * off;
+    for (uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x; i < words; i += (uint64_t)gridDim.x * blockDim.x)
+        out[i] = rows[i];
+    __threadfence_system();
+}
+
+// The status vector of this rank, from the device counters (one thread).  A count above its
+// capacity raises STF_OVERFLOW: every rank reads every rank's vector after the exchange, so all of
+// them take the same "grow and repeat" decision without talking to each other on the host.
+struct StatusParams {
+    unsigned long long* st;              // [STATUS_WORDS] this rank's slot in its own arena
+    const unsigned long long* ctr;       // device counter block
+    int c_err, c_ncand, c_nscan, c_nstage, c_flags;
+    const unsigned long long* n_hits;
+    const unsigned long long* n_rows;
+    const unsigned long long* abort_word;
+    unsigned long long cap_cand, cap_scan, cap_stage, cap_hits, cap_rows;
+};
+
+__global__ void k9_status(const StatusParams P) {
+    if (threadIdx.x != 0 || blockIdx.x != 0) return;
+    const unsigned long long ncand = P.ctr[P.c_ncand], nscan = P.ctr[P.c_nscan], nstage = P.ctr[P.c_nstage];
+    const unsigned long long nhits = *P.n_hits, nrows = *P.n_rows;
+    unsigned long long fl = P.ctr[P.c_flags] | (*P.abort_word ? STF_TIMEOUT : 0ull);
+    if (ncand > P.cap_cand || nscan > P.cap_scan || nstage > P.cap_stage || nhits > P.cap_hits || nrows > P.cap_rows)
+        fl |= STF_OVERFLOW;
+    P.st[ST_ERR] = P.ctr[P.c_err];
+    P.st[ST_NCAND] = ncand;
+    P.st[ST_NSCAN] = nscan;
+    P.st[ST_NSTAGE] = nstage;
+    P.st[ST_NHITS] = nhits;
+    P.st[ST_NROWS] = nrows;
+    P.st[ST_FLAGS] = fl;
+    P.st[ST_SPARE] = 0;
 }
 
 }  // namespace ovl

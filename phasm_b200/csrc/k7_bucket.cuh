@@ -14,13 +14,14 @@
 //   k7_emit      one warp per entry: rows written at the entry's row offset
 //
 // leaves the keys globally sorted and the rows in canonical (a,b,astart,aend,bend) order --
-// bit-identical to the radix-sort path -- with every size read from device counters: the whole
-// overlap pass then needs ONE host synchronisation, at its end.  An entry with more than
-// BUCKET_MAX hits raises a flag and the host falls back to the radix-sort path for that call.
+// with every size read from device counters: the whole overlap pass then needs ONE host
+// synchronisation, at its end.  An entry with more than BUCKET_MAX hits (a high-copy repeat, an
+// amplicon pile-up) goes on a short list that k7_sort_big orders afterwards, one thread block per
+// bucket, with an in-place all-ascending bitonic network of arbitrary length: no fallback path,
+// no library sort, no extra synchronisation.
 //
 // Roofline: HBM/L2, 8 B read + 8 B written per hit in scatter and sort, 20 B written per row.
 #pragma once
-#include "k5_emit.cuh"
 #include "ovl_common.cuh"
 
 namespace ovl {
@@ -39,7 +40,8 @@ struct BucketParams {
     uint64_t* sorted;                 // bucketed, then sorted keys
     uint32_t* rowcnt;                 // [M+1] rows per entry, rowcnt[M] = 0
     const uint64_t* rowoff;           // [M+1] exclusive sum of rowcnt
-    unsigned long long* big;          // set to 1 if a bucket exceeds BUCKET_MAX
+    unsigned long long* big;          // number of buckets with more than BUCKET_MAX keys
+    uint32_t* big_list;               // [M] their entries
     const uint2* ent;
     Row* rows;
     uint64_t rows_cap;
@@ -88,11 +90,8 @@ __global__ void __launch_bounds__(256) k7_sort(const BucketParams P) {
             if (lane == 0) P.rowcnt[a] = 0;
             continue;
         }
-        if (hi - lo > BUCKET_MAX) {
-            if (lane == 0) {
-                P.rowcnt[a] = 0;
-                *P.big = 1ull;
-            }
+        if (hi - lo > BUCKET_MAX) {  // left to k7_sort_big (which also counts its rows)
+            if (lane == 0) P.big_list[atomicAdd(P.big, 1ull)] = a;
             continue;
         }
         uint32_t np2 = 32;
@@ -128,6 +127,55 @@ __global__ void __launch_bounds__(256) k7_sort(const BucketParams P) {
     }
 }
 
+// Buckets above BUCKET_MAX keys: one block per bucket, in place in global memory (the bucket is a
+// few thousand keys: L1/L2 resident).  All comparators of this bitonic network are ascending
+// (first step of a merge pairs i with i ^ (k-1), the others i with i ^ j), so a length that is
+// not a power of two needs no padding: a comparator whose partner lies past the end is skipped,
+// as if +infinity sat there.
+__global__ void __launch_bounds__(1024) k7_sort_big(const BucketParams P) {
+    __shared__ uint32_t s_cnt[32];
+    const unsigned long long nbig = *P.big;
+    const int pair_shift = P.fmt.bits_p + 2;
+    for (unsigned long long bi = blockIdx.x; bi < nbig; bi += gridDim.x) {
+        const uint32_t a = P.big_list[bi];
+        const uint64_t lo = P.off[a];
+        const uint64_t n = P.off[a + 1] - lo;
+        uint64_t* s = P.sorted + lo;
+        uint64_t np2 = 1;
+        while (np2 < n) np2 <<= 1;
+        for (uint64_t k = 2; k <= np2; k <<= 1) {
+            for (uint64_t j = k >> 1; j > 0; j >>= 1) {
+                const bool flip = j == (k >> 1);
+                for (uint64_t t = threadIdx.x; t < (np2 >> 1); t += blockDim.x) {
+                    const uint64_t i = ((t & ~(j - 1)) << 1) | (t & (j - 1));  // bit j clear
+                    const uint64_t x = flip ? (i ^ (k - 1)) : (i | j);
+                    if (x < n) {  // i < x always
+                        const uint64_t u = s[i], v = s[x];
+                        if (u > v) {
+                            s[i] = v;
+                            s[x] = u;
+                        }
+                    }
+                }
+                __syncthreads();
+            }
+        }
+        uint32_t c = 0;
+        for (uint64_t i = threadIdx.x; i < n; i += blockDim.x)
+            c += key_rows_prev(s[i], i ? s[i - 1] : 0ull, i != 0, pair_shift);
+#pragma unroll
+        for (int d = 16; d > 0; d >>= 1) c += __shfl_xor_sync(FULL, c, d);
+        if ((threadIdx.x & 31) == 0) s_cnt[threadIdx.x >> 5] = c;
+        __syncthreads();
+        if (threadIdx.x == 0) {
+            uint32_t tot = 0;
+            for (uint32_t w = 0; w < (blockDim.x >> 5); ++w) tot += s_cnt[w];
+            P.rowcnt[a] = tot;
+        }
+        __syncthreads();
+    }
+}
+
 __global__ void __launch_bounds__(256) k7_emit(const BucketParams P) {
     const uint32_t lane = threadIdx.x & 31;
     const uint32_t warp = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
@@ -135,12 +183,12 @@ __global__ void __launch_bounds__(256) k7_emit(const BucketParams P) {
     const int pair_shift = P.fmt.bits_p + 2;
     for (uint32_t a = warp; a < P.M; a += nwarps) {
         const uint64_t lo = P.off[a], hi = P.off[a + 1];
-        if (hi == lo || hi - lo > BUCKET_MAX) continue;
-        const uint32_t n = (uint32_t)(hi - lo);
+        if (hi == lo) continue;
+        const uint64_t n = hi - lo;
         const uint32_t la = __ldg(P.ent + a).y;
         uint64_t o = P.rowoff[a];
-        for (uint32_t i0 = 0; i0 < n; i0 += 32) {
-            const uint32_t i = i0 + lane;
+        for (uint64_t i0 = 0; i0 < n; i0 += 32) {
+            const uint64_t i = i0 + lane;
             uint64_t key = 0;
             uint32_t c = 0;
             if (i < n) {

@@ -1,19 +1,28 @@
 // ovl.cu -- host side of libphasm_ovl.so: the C ABI of include/phasm_ovl.h over the sm_100a
-// kernels K0..K5.  No torch, no pybind11, no CPU compute path: every ovl_overlaps* call runs
+// kernels K0..K9.  No torch, no pybind11, no CPU compute path: every ovl_overlaps* call runs
 // the CUDA pipeline or fails.
 //
-// Pipeline of one ovl_overlaps_device() call (reference: ExactOverlapper::overlaps,
-// /root/reference/src/overlapper.cpp:28-150):
+// One pass (reference: ExactOverlapper::overlaps, /root/reference/src/overlapper.cpp:28-150):
 //
-//   K0 k0_gran_entry   granule -> entry map
-//   K1 k1_pack         ASCII -> 2-bit granules, "-" entries reverse-complemented on the fly
-//   K2 select/keys/sort/build   prefix anchors of all entries with |b| >= l, hash table + bloom
-//   K3 k3_scan         every A position with |a|-p >= l probes the anchors -> candidates
-//   K4 k4_verify       warp per candidate compares a[p:] with b[0:] -> 64-bit hit keys
-//   K5 sort/count/scan/emit     longest suffix-prefix per pair + all containments -> rows
+//   K1 k1_pack            ASCII -> 2-bit granules, "-" entries reverse-complemented on the fly
+//   K2 k2_prefix_ascii, k2_insert   prefix anchors of all entries with |b| >= l: hash table
+//                         (partitioned by k-mer hash over the GPUs of the job) + bit filter
+//   K3 k3_filter, k3_resolve (k3_scan when l < 33)   A positions probe the anchors -> candidates
+//   K4 k4a_head, k4b_tail packed-word comparison of a[p:] with b[0:] -> 64-bit hit keys
+//   K6 k6_route           (N > 1 GPUs) hit keys to the rank that owns their A entry
+//   K7 k7_*               bucket + sort the hit keys, longest suffix-prefix per pair + all
+//                         containments -> rows
+//   K9 k9_*               (N > 1 GPUs) rows into rank 0's HBM, status to everyone
 //
-// Device-wide sort / select / prefix-sum come from CUB (ships with CUDA 12.9); everything else
-// is in the k*.cuh files next to this one.
+// The pass is enqueued as a whole and the host waits ONCE, at its end, on 1 GPU and on N: every
+// buffer is sized by capacity, every kernel reads its input size from a device counter, and the
+// ranks of a multi-GPU job exchange data through peer-mapped arenas and flag words
+// (k6_exchange.cuh), not through host-synchronised collectives.  NCCL is only the bootstrap
+// channel (IPC handles, ranges) at connect time.
+//
+// CUB supplies the two exclusive prefix sums of the bucket ordering; everything else is in the
+// k*.cuh files next to this one.
+#include <algorithm>
 #include <cerrno>
 #include <cstdarg>
 #include <cstdio>
@@ -31,7 +40,6 @@
 #include "k2_anchor.cuh"
 #include "k3_scan.cuh"
 #include "k4_verify.cuh"
-#include "k5_emit.cuh"
 #include "k6_exchange.cuh"
 #include "k7_bucket.cuh"
 #include "k8_filter.cuh"
@@ -39,11 +47,13 @@
 
 static_assert(sizeof(ovl_row) == sizeof(ovl::Row), "row layouts must agree");
 static_assert(sizeof(ovl_row) == 20, "ovl_row is 5 x u32");
+static_assert(sizeof(ovl::ArenaHdr) % 256 == 0, "arena header is padded to 256 bytes");
 
 namespace {
 
 constexpr uint64_t NO_SRC = ~0ull;  // entry whose bases live on another rank
 constexpr size_t SLACK = 16;        // bytes of slack at both ends of the ASCII staging area
+constexpr int MAX_CHUNKS = 16;      // pieces of the chunked host -> HBM upload
 
 thread_local std::string g_create_err;
 
@@ -58,21 +68,49 @@ struct PinBuf {
     size_t cap = 0;
 };
 
-enum Ev { E_H2D0, E_PACK0, E_ANCHOR0, E_SCAN0, E_VERIFY0, E_SORT0, E_EMIT0, E_END, E_D2H0, E_D2H1, E_COUNT };
+enum Ev { E_H2D0, E_H2D1, E_PACK0, E_ANCHOR0, E_SCAN0, E_VERIFY0, E_SORT0, E_EMIT0, E_GATHER0, E_END, E_D2H0, E_D2H1, E_COUNT };
 
 // device counter block (one 64-bit word each)
-enum Ctr { C_ERR, C_NANC, C_NCAND, C_NHITS, C_SUMM, C_SUMB, C_NSURV, C_TILE_A, C_TILE_B, C_BIG, C_COUNT };  // h_ctr has 2 spare words behind
+enum Ctr {
+    C_ERR,     // (entry + 1) of an entry holding a non-ACGT byte
+    C_NANC,    // entries with |b| >= l
+    C_NSCAN,   // survivors of the scan's filter pass
+    C_NCAND,   // candidate keys
+    C_NSTAGE,  // verified hit keys staged for routing (N > 1, mirror mode)
+    C_SUMM, C_SUMB,  // accounting mode: sum m_c, sum 2*ceil(m_c/4)   (adjacent: the verifier takes a pointer to both)
+    C_NSURV,   // candidates alive after the verifier's head
+    C_TILE_A, C_TILE_B,  // dynamic tile hand-out of k4a / k4b (adjacent)
+    C_BIG,     // buckets above BUCKET_MAX keys
+    C_FLAGS,   // STF_* bits raised by kernels
+    C_NSENT,   // hit keys routed to other ranks
+    C_NROWS,   // rows of this rank
+    C_COUNT
+};
+
+// byte offsets of the pieces of an arena (the header sits at 0); published to the peers
+struct ArenaLayout {
+    uint64_t bytes;
+    uint64_t off_pre, off_packed, off_filter, off_table, off_next, off_inbox, off_rows;
+    uint64_t inbox_cap;  // hit keys
+    uint64_t rows_cap;   // rows (rank 0 of a multi-GPU job: the rows of all ranks)
+};
+
+struct PeerInfo {
+    cudaIpcMemHandle_t handle;
+    ArenaLayout lay;
+    int device;  // CUDA ordinal of the rank's GPU (every rank sees all GPUs of the box)
+    int pad;
+};
 
 }  // namespace
 
 struct ovl_ctx {
     int device = 0;
     int n_sm = 148;
-    cudaStream_t st = nullptr, st_comm = nullptr, st_k2 = nullptr;
+    cudaStream_t st = nullptr, st_k2 = nullptr, st_push = nullptr, st_sig = nullptr, st_h2d = nullptr;
     cudaEvent_t ev[E_COUNT] = {};
-    cudaEvent_t ev_comm = nullptr, ev_pack = nullptr, ev_pre = nullptr;
-    cudaEvent_t ev_k0 = nullptr, ev_prel = nullptr, ev_k2 = nullptr;
-    cudaEvent_t ev_dbg[4] = {};  // OVL_DEBUG=1: timing of the replication on the comm stream  // fork/join of the anchor-build stream
+    cudaEvent_t ev_pack = nullptr, ev_k0 = nullptr, ev_prel = nullptr, ev_k2 = nullptr, ev_push = nullptr, ev_sig = nullptr;
+    cudaEvent_t ev_chunk[MAX_CHUNKS] = {};
     cudaEvent_t ev_t0 = nullptr, ev_t1 = nullptr;  // ovl_timer_*
     std::string err;
 
@@ -84,45 +122,64 @@ struct ovl_ctx {
     std::vector<uint8_t> flags;  // bit0: reverse complement of the record
     std::vector<char> id_blob;
     std::vector<uint64_t> id_off{0};
-    std::vector<uint32_t> gran0;
+    std::vector<uint32_t> gran0;  // [M] first granule of every entry (two-region layout)
     std::vector<uint32_t> tile0;  // [M+1] first K1 tile of every entry
     uint64_t bases = 0, max_len = 0;
-    bool uploaded = false;
+    bool tables_dirty = true;     // entries changed since the tables were sent
+    bool ascii_resident = false;  // the staged records are in HBM
+    uint64_t generation = 0;      // bumped whenever the entry table changes
     uint32_t e_lo = 0, e_hi = 0;  // entries whose bases are local (contiguous)
+    uint32_t G = 0, G_f = 0;      // granules: all, forward region
+    ovl::ScanRanges ranges{};     // the local A granules
+    int pairs = 0;                // 1: entry e ^ 1 is the other strand of entry e, for every e
 
-    // ---- device ----
-    DevBuf d_ascii, d_src, d_len, d_flags, d_gran0, d_gran_ent, d_ent, d_packed, d_tile0, d_tile_ent, d_xchg, d_pre;
-    DevBuf d_table, d_filter, d_next, d_ctr, d_tmp;
-    DevBuf d_cand, d_cand2, d_cnt, d_offs, d_rows, d_cnts, d_bkt, d_fwd;
+    // ---- device: persistent tables ----
+    DevBuf d_ascii, d_src, d_len, d_flags, d_gran0, d_ent, d_reg, d_tile0, d_tile_ent, d_tile_idx;
+    // ---- device: per-pass working buffers outside the arena ----
+    DevBuf d_ctr, d_tmp, d_cand, d_stage, d_scan, d_cnt, d_bkt, d_big, d_peerhdr;
     DevBuf d_fmark, d_fkeep, d_foff, d_frows;  // ovl_filter_rows
-    DevBuf d_gath;                             // row gather slots (multi-GPU)
-    PinBuf h_frows;
-    uint64_t* h_ctr = nullptr;  // pinned mirror of d_ctr
-    uint64_t cand_cap = 0;  // candidate keys one pass may emit (d_cand/d_cand2 hold the derived hit capacity)
+    DevBuf d_rows;                             // VIEW of the arena's row array (not owned)
+    // ---- the arena ----
+    DevBuf arena;
+    ArenaLayout lay{};
+    uint64_t arena_key[4] = {~0ull, 0, 0, 0};  // {generation, cand_cap, nranks/mirror, epoch} the arena was planned for
+    uint64_t arena_epoch = 0;                  // bumped by every collective "grow and repeat"
+    void* peer_base[ovl::MAX_RANKS] = {};
+    ArenaLayout peer_lay[ovl::MAX_RANKS] = {};
+    uint64_t step = 0;
+
+    PinBuf h_frows, h_rows;
+    uint64_t* h_ctr = nullptr;   // pinned: counters | status[MAX_RANKS][STATUS_WORDS] | rowcnt[MAX_RANKS] | inbox_n | step
+    uint64_t cand_cap = 0;       // candidate keys one pass may emit
+    uint64_t min_cand_cap = 1ull << 20;
+    uint64_t cand_per_entry = 96;  // first candidate capacity: this many keys per local entry
     uint64_t n_rows = 0;
-    PinBuf h_rows;
     bool rows_fetched = false;
-    bool gathered = false;  // ovl_comm_gather_rows_device already ran for the current rows
+    bool gathered = false;
     int collect = 0;
-    // host-side per-call scans of the entry table, cached between calls (reset by ovl_upload)
-    int cache_pairs = -1;            // 1: entry e^1 is the other strand of entry e, for every e
-    uint32_t cache_l = 0;
     bool cache_l_valid = false;
+    uint32_t cache_l = 0;
     uint64_t cache_nanc = 0, cache_npos = 0;
-    int opt_stride = 0;  // 0 = auto; else upper bound on the anchor stride (1 = dense scan)
+    int opt_stride = 0;         // 0 = auto; else upper bound on the anchor stride (1 = dense scan)
     int opt_serial_verify = 0;  // 1: chunk-by-chunk early-exit verifier instead of head/tail
     int opt_mirror = 1;         // 1: strand-mirror halving when every entry has its twin
-    int opt_pack_bpsm = 16;     // K1 blocks per SM (fewer leave room for the concurrent anchor build)
+    int opt_pack_bpsm = 16;     // K1 blocks per SM
+    int opt_filter_kb = 8192;   // budget of the scan's bit filter (all slices), KiB
+    int opt_chunks = 8;         // pieces of the host -> HBM upload of ovl_overlaps (1 = one copy)
+    int opt_timeout_ms = 20000; // peer wait timeout
     ovl_stats stats{};
 
     // ---- multi-GPU ----
     ncclComm_t comm = nullptr;
     int rank = 0, nranks = 1;
     std::vector<uint32_t> rank_e;  // [nranks+1] entry range of every rank
-    PinBuf h_gather;
 };
 
 namespace {
+
+using ovl::ArenaHdr;
+using ovl::MAX_RANKS;
+using ovl::STATUS_WORDS;
 
 int fail(ovl_ctx* c, int code, const char* fmt, ...) {
     char buf[512];
@@ -204,6 +261,7 @@ inline int ceil_log2(uint64_t x) {
 }
 
 inline size_t align16(size_t x) { return (x + 15) & ~size_t(15); }
+inline uint64_t align256(uint64_t x) { return (x + 255) & ~uint64_t(255); }
 
 int push_entry(ovl_ctx* c, const char* id, size_t id_len, const char* sfx, uint64_t src, uint64_t n,
                uint8_t fl) {
@@ -217,7 +275,8 @@ int push_entry(ovl_ctx* c, const char* id, size_t id_len, const char* sfx, uint6
     c->id_off.push_back(c->id_blob.size());
     c->bases += n;
     if (n > c->max_len) c->max_len = n;
-    c->uploaded = false;
+    c->tables_dirty = true;
+    c->ascii_resident = false;
     return OVL_OK;
 }
 
@@ -245,72 +304,951 @@ float ev_ms(ovl_ctx* c, int a, int b) {
     return ms;
 }
 
-// read the device counter block (synchronises the compute stream)
-int read_ctr(ovl_ctx* c) {
-    CK(cudaMemcpyAsync(c->h_ctr, c->d_ctr.p, C_COUNT * sizeof(uint64_t), cudaMemcpyDeviceToHost, c->st));
+// ---- arena accessors ---------------------------------------------------------------------
+template <class T> T* at(void* base, uint64_t off) { return reinterpret_cast<T*>(static_cast<uint8_t*>(base) + off); }
+ArenaHdr* hdr_of(ovl_ctx* c, int r) { return static_cast<ArenaHdr*>(c->peer_base[r]); }
+ArenaHdr* my_hdr(ovl_ctx* c) { return static_cast<ArenaHdr*>(c->arena.p); }
+
+// ---- sizing rules (the same function sizes the arena for the worst case and one pass) --------
+// log2 slots of one table partition holding ~n_keys / nr keys at a load factor <= 0.5
+int table_bits(uint64_t n_keys, int nr) {
+    const double per = (double)n_keys / nr;
+    const uint64_t want = (uint64_t)(2.0 * (per + 6.0 * sqrt(per + 1.0) + 64.0));
+    int b = ceil_log2(want);
+    return b < 6 ? 6 : b;
+}
+// log2 bits of one slice of the sparse-path bitmap: the most bits per key out of {32, 16, 8, 4}
+// that keeps the whole bitmap (nr slices) inside the budget -- the filter has to stay L2-resident
+// while the packed reads stream through (round 1: 32 bits/key unconditionally, 47 % L2 hit rate)
+int slice_bits(uint64_t n_keys, int nr, uint64_t budget_bytes) {
+    const uint64_t per = n_keys / nr + 1;
+    int best = 0;
+    for (int bpk = 32; bpk >= 4; bpk >>= 1) {
+        int b = ceil_log2(per * bpk);
+        if (b < 15) b = 15;
+        best = b;
+        if (((uint64_t)nr << b) / 8 <= budget_bytes) break;
+    }
+    if (best > 31) best = 31;
+    return best;
+}
+int dense_filter_bits(uint64_t n_anc, bool smem) {
+    int b = smem ? ceil_log2(n_anc) : ceil_log2(2 * n_anc);
+    if (b < 5) b = 5;
+    if (smem && b > 15) b = 15;
+    if (b > 27) b = 27;
+    return b;
+}
+int max_stride_log2(uint32_t M) {
+    int s = 6;
+    while (s > 0 && (((uint64_t)M << s) >= 0x7ffffff0ull)) --s;
+    return s;
+}
+
+// all-gather a small host blob through the bootstrap communicator (collective; synchronises)
+int allgather_host(ovl_ctx* c, const void* mine, size_t n, void* all) {
+    auto& N = nccl_dyn::api();
+    const size_t tot = n * (size_t)c->nranks;
+    OVL_TRY(dev_ensure(c, c->d_tmp, tot));
+    uint8_t* d = c->d_tmp.as<uint8_t>();
+    CK(cudaMemcpyAsync(d + n * c->rank, mine, n, cudaMemcpyHostToDevice, c->st));
+    CKN(N.AllGather(d + n * c->rank, d, n, ncclUint8, c->comm, c->st));
+    CK(cudaMemcpyAsync(all, d, tot, cudaMemcpyDeviceToHost, c->st));
     CK(cudaStreamSynchronize(c->st));
     return OVL_OK;
 }
 
-// Multi-GPU mirror mode: partition the n_hits keys in d_cand2 by owner rank, ship every run to
-// its owner (grouped ncclSend/ncclRecv), leave this rank's keys (own + received, unsorted) in
-// d_cand2 and their number in *n_hits.  Collective: every rank must call it.
-int exchange_hits(ovl_ctx* c, const ovl::KeyFmt& fmt, uint64_t* n_hits, uint32_t* launches, uint32_t* lib) {
+void close_peers(ovl_ctx* c) {
+    for (int r = 0; r < MAX_RANKS; ++r) {
+        if (c->peer_base[r] && r != c->rank) cudaIpcCloseMemHandle(c->peer_base[r]);
+        c->peer_base[r] = nullptr;
+    }
+    (void)cudaGetLastError();
+}
+
+// (Re)plan and allocate the arena for the current entry table and capacities; on N > 1 ranks
+// exchange the IPC handles and map every peer's arena.  Collective on N > 1: all ranks reach it in
+// the same call (the key changes with the entry table, the rank count, or an overflow every rank
+// learned about from the status exchange).
+int connect_arena(ovl_ctx* c, bool mirror) {
     using namespace ovl;
-    (void)lib;
-    auto& N = nccl_dyn::api();
-    const int R = c->nranks, me = c->rank;
-    if (R > MAX_RANKS) return fail(c, OVL_E_LIMIT, "more than %d ranks", MAX_RANKS);
-    if ((int)c->rank_e.size() != R + 1) return fail(c, OVL_E_ARG, "call ovl_comm_sync_ranges before ovl_overlaps_device");
+    const int nr = c->nranks, me = c->rank;
+    const uint32_t M = (uint32_t)c->len.size();
+    const uint64_t hit_cap = mirror ? 3 * c->cand_cap : c->cand_cap;  // own key + SP twin + CONT twin
+    uint64_t rows_total = hit_cap;
+    if (nr > 1) {
+        std::vector<uint64_t> caps(nr);
+        OVL_TRY(allgather_host(c, &hit_cap, 8, caps.data()));
+        if (me == 0) {
+            rows_total = 0;
+            for (int r = 0; r < nr; ++r) rows_total += caps[r];
+        }
+    }
+    const int slog_max = max_stride_log2(M);
+    const uint64_t keys_max = (uint64_t)M << slog_max;
+    ArenaLayout L{};
+    uint64_t off = sizeof(ArenaHdr);
+    auto take = [&](uint64_t bytes) {
+        const uint64_t o = off;
+        off = align256(off + bytes);
+        return o;
+    };
+    L.off_pre = take((uint64_t)M * 32);
+    L.off_packed = take(((uint64_t)c->G + 2) * 16);
+    const uint64_t f_sparse = ((uint64_t)nr << slice_bits(keys_max, nr, (uint64_t)c->opt_filter_kb << 10)) / 8;
+    const uint64_t f_dense = 4ull << dense_filter_bits(M, false);
+    L.off_filter = take(std::max(f_sparse, f_dense));
+    L.off_table = take(8ull << table_bits(keys_max, nr));
+    L.off_next = take(keys_max * 4);
+    L.inbox_cap = hit_cap;
+    L.off_inbox = take(hit_cap * 8);
+    L.rows_cap = rows_total;
+    L.off_rows = take(rows_total * sizeof(Row));
+    L.bytes = off;
+
+    // nobody may still map the old arena when it is freed
+    close_peers(c);
+    if (nr > 1) {
+        uint64_t token = 1;
+        std::vector<uint64_t> all(nr);
+        OVL_TRY(allgather_host(c, &token, 8, all.data()));
+    }
+    if (c->arena.p) CK(cudaFree(c->arena.p));
+    c->arena.p = nullptr;
+    c->arena.cap = 0;
+    {
+        cudaError_t e = cudaMalloc(&c->arena.p, L.bytes);
+        if (e != cudaSuccess) {
+            (void)cudaGetLastError();
+            c->arena.p = nullptr;
+            return fail(c, OVL_E_NOMEM, "cudaMalloc of the %llu-byte arena failed: %s", (unsigned long long)L.bytes, cudaGetErrorString(e));
+        }
+        c->arena.cap = L.bytes;
+    }
+    CK(cudaMemsetAsync(c->arena.p, 0, sizeof(ArenaHdr), c->st));
+    CK(cudaMemsetAsync(at<uint8_t>(c->arena.p, L.off_packed), 0, ((uint64_t)c->G + 2) * 16, c->st));
+    CK(cudaStreamSynchronize(c->st));
+    c->lay = L;
+    c->step = 0;
+    c->peer_base[me] = c->arena.p;
+    c->peer_lay[me] = L;
+    if (nr > 1) {
+        PeerInfo mine{};
+        CK(cudaIpcGetMemHandle(&mine.handle, c->arena.p));
+        mine.lay = L;
+        mine.device = c->device;
+        std::vector<PeerInfo> all(nr);
+        OVL_TRY(allgather_host(c, &mine, sizeof mine, all.data()));
+        for (int r = 0; r < nr; ++r) {
+            if (r == me) continue;
+            void* p = nullptr;
+            if (all[r].device != c->device) {  // copy-engine pushes want explicit peer access; "already enabled" is fine
+                (void)cudaDeviceEnablePeerAccess(all[r].device, 0);
+                (void)cudaGetLastError();
+            }
+            cudaError_t e = cudaIpcOpenMemHandle(&p, all[r].handle, cudaIpcMemLazyEnablePeerAccess);
+            if (e != cudaSuccess) {
+                (void)cudaGetLastError();
+                return fail(c, OVL_E_CUDA, "cannot map the arena of rank %d over CUDA IPC: %s (all GPUs of the job must be visible to every rank and peer access must be possible)", r, cudaGetErrorString(e));
+            }
+            c->peer_base[r] = p;
+            c->peer_lay[r] = all[r].lay;
+        }
+        // everyone has mapped everyone before anyone starts a pass
+        uint64_t token = 2;
+        std::vector<uint64_t> tk(nr);
+        OVL_TRY(allgather_host(c, &token, 8, tk.data()));
+    }
+    // device table of the peers' headers (k_signal / publish kernels)
+    OVL_TRY(dev_ensure(c, c->d_peerhdr, sizeof(void*) * MAX_RANKS, false));
+    CK(cudaMemcpyAsync(c->d_peerhdr.p, c->peer_base, sizeof(void*) * MAX_RANKS, cudaMemcpyHostToDevice, c->st));
+    CK(cudaStreamSynchronize(c->st));
+    c->d_rows.p = at<uint8_t>(c->arena.p, L.off_rows);
+    c->d_rows.cap = L.rows_cap * sizeof(Row);
+    return OVL_OK;
+}
+
+// host -> HBM: the entry tables and the maps derived from them (only when the entries changed)
+int upload_tables(ovl_ctx* c) {
+    using namespace ovl;
+    if (!c->tables_dirty) return OVL_OK;
+    const size_t M = c->len.size();
+    try {
+        c->gran0.resize(M);
+        c->tile0.resize(M + 1);
+    } catch (const std::bad_alloc&) {
+        return fail(c, OVL_E_NOMEM, "out of host memory");
+    }
+    auto is_twin = [&](size_t e) { return e > 0 && (c->flags[e] & 1) && !(c->flags[e - 1] & 1); };
+    // pass 1: forward region = every entry that is not a twin, in entry order
+    uint64_t gf = 0, nt = 0;
+    uint32_t lo = (uint32_t)M, hi = 0, n_fwd = 0;
+    for (size_t e = 0; e < M; ++e) {
+        c->tile0[e] = (uint32_t)nt;
+        const uint64_t ge = (c->len[e] + 63u) / 64u;
+        if (!is_twin(e)) {
+            if (gf + ge >= 0xfffffff0ull) return fail(c, OVL_E_LIMIT, "more than 2^32 granules");
+            c->gran0[e] = (uint32_t)gf;
+            gf += ge;
+            ++n_fwd;
+            // K1 tiles: local non-twin entries (a twin is written by its forward entry's tiles)
+            if (c->src[e] != NO_SRC) nt += (4 * ge + PACK_TILE_UNITS - 1) / PACK_TILE_UNITS;
+        }
+        if (c->src[e] != NO_SRC) {
+            if (e < lo) lo = (uint32_t)e;
+            hi = (uint32_t)e + 1;
+        }
+    }
+    if (M) c->tile0[M] = (uint32_t)nt;
+    // pass 2: twin region behind it
+    uint64_t g = gf;
+    for (size_t e = 0; e < M; ++e)
+        if (is_twin(e)) {
+            c->gran0[e] = (uint32_t)g;
+            g += (c->len[e] + 63u) / 64u;
+        }
+    if (g >= 0xfffffff0ull) return fail(c, OVL_E_LIMIT, "more than 2^32 granules (%llu)", (unsigned long long)g);
+    if (lo > hi) lo = hi = 0;
+    for (uint32_t e = lo; e < hi; ++e)
+        if (c->src[e] == NO_SRC) return fail(c, OVL_E_ARG, "local entries must be one contiguous range (entry %u is remote)", e);
+    if (lo < hi && is_twin(lo)) return fail(c, OVL_E_ARG, "a read and its reverse-complement entry must be local to the same rank (entry %u)", lo);
+    if (hi < M && is_twin(hi)) return fail(c, OVL_E_ARG, "a read and its reverse-complement entry must be local to the same rank (entry %u)", hi);
+    c->e_lo = lo;
+    c->e_hi = hi;
+    c->G = (uint32_t)g;
+    c->G_f = (uint32_t)gf;
+    if (c->nranks == 1 && (lo != 0 || hi != M) && M) return fail(c, OVL_E_ARG, "remote entries need ovl_comm_init");
+    // strand-mirror halving needs entry e ^ 1 to be the other strand of entry e, for every e
+    bool pairs = M % 2 == 0 && M > 0;
+    for (size_t e = 0; pairs && e < M; e += 2) pairs = !(c->flags[e] & 1) && (c->flags[e + 1] & 1) && c->len[e] == c->len[e + 1];
+    c->pairs = pairs ? 1 : 0;
+
+    // entries in granule (region) order + the local scan ranges
+    std::vector<uint4> reg;
+    try {
+        reg.resize(M + 1);
+    } catch (const std::bad_alloc&) {
+        return fail(c, OVL_E_NOMEM, "out of host memory");
+    }
+    ScanRanges R{};
+    {
+        uint32_t i = 0;
+        bool seen0 = false, seen1 = false;
+        for (int pass = 0; pass < 2; ++pass)
+            for (size_t e = 0; e < M; ++e) {
+                if ((int)is_twin(e) != pass) continue;
+                const uint32_t ge = (c->len[e] + 63u) / 64u;
+                reg[i] = make_uint4(c->gran0[e], (uint32_t)e, c->len[e], ge);
+                if (e >= lo && e < hi) {
+                    bool& seen = pass ? seen1 : seen0;
+                    if (!seen) {
+                        R.g_begin[pass] = c->gran0[e];
+                        R.i_begin[pass] = i;
+                        seen = true;
+                    }
+                    R.g_end[pass] = c->gran0[e] + ge;
+                    R.i_end[pass] = i + 1;
+                }
+                ++i;
+            }
+        reg[M] = make_uint4((uint32_t)g, 0, 0, 0);
+        (void)n_fwd;
+    }
+    R.t_begin[0] = 0;
+    R.t_begin[1] = (R.g_end[0] - R.g_begin[0] + 31) / 32;
+    R.n_tiles = R.t_begin[1] + (R.g_end[1] - R.g_begin[1] + 31) / 32;
+    c->ranges = R;
+
     cudaStream_t st = c->st;
-    RankMap map;
-    map.n = R;
-    for (int r = 0; r <= R; ++r) map.e[r] = c->rank_e[r];
-    const uint64_t n = *n_hits;
-    // device scratch: counts[R] | cursor[R] | matrix[R*R]
-    OVL_TRY(dev_ensure(c, c->d_xchg, 8ull * (2 * R + (size_t)R * R), false));
-    unsigned long long* d_counts = c->d_xchg.as<unsigned long long>();
-    unsigned long long* d_cursor = d_counts + R;
-    unsigned long long* d_matrix = d_cursor + R;
-    CK(cudaMemsetAsync(d_counts, 0, 16ull * R, st));
-    OVL_TRY(dev_ensure(c, c->d_cand, (n ? n : 1) * 8, false));  // partition output (the candidate buffer is free after the verifier)
-    if (n) {
-        unsigned blocks = (unsigned)((n + 255) / 256);
-        if (blocks > (unsigned)c->n_sm * 8) blocks = (unsigned)c->n_sm * 8;
-        k6_count<<<blocks, 256, 0, st>>>(c->d_cand2.as<uint64_t>(), n, fmt, map, d_counts);
-        k6_scatter<<<blocks, 256, 0, st>>>(c->d_cand2.as<uint64_t>(), n, fmt, map, d_counts, d_cursor, c->d_cand.as<uint64_t>());
-        *launches += 2;
+    if (M) {
+        OVL_TRY(dev_ensure(c, c->d_src, M * 8));
+        OVL_TRY(dev_ensure(c, c->d_len, M * 4));
+        OVL_TRY(dev_ensure(c, c->d_flags, M));
+        OVL_TRY(dev_ensure(c, c->d_gran0, M * 4));
+        OVL_TRY(dev_ensure(c, c->d_ent, M * 8));
+        OVL_TRY(dev_ensure(c, c->d_reg, (M + 1) * 16));
+        OVL_TRY(dev_ensure(c, c->d_tile0, (M + 1) * 4));
+        OVL_TRY(dev_ensure(c, c->d_tile_ent, (nt + 1) * 4));
+        OVL_TRY(dev_ensure(c, c->d_tile_idx, ((size_t)R.n_tiles + 1) * 4));
+        CK(cudaMemcpyAsync(c->d_tile0.p, c->tile0.data(), (M + 1) * 4, cudaMemcpyHostToDevice, st));
+        CK(cudaMemcpyAsync(c->d_src.p, c->src.data(), M * 8, cudaMemcpyHostToDevice, st));
+        CK(cudaMemcpyAsync(c->d_len.p, c->len.data(), M * 4, cudaMemcpyHostToDevice, st));
+        CK(cudaMemcpyAsync(c->d_flags.p, c->flags.data(), M, cudaMemcpyHostToDevice, st));
+        CK(cudaMemcpyAsync(c->d_gran0.p, c->gran0.data(), M * 4, cudaMemcpyHostToDevice, st));
+        CK(cudaMemcpyAsync(c->d_reg.p, reg.data(), (M + 1) * 16, cudaMemcpyHostToDevice, st));
+        k0_ent_table<<<(unsigned)((M + 255) / 256), 256, 0, st>>>(c->d_gran0.as<uint32_t>(), c->d_len.as<uint32_t>(), c->d_ent.as<uint2>(), (uint32_t)M);
+        if (hi > lo) {
+            k0_tile_ent<<<c->n_sm * 4, 256, 0, st>>>(c->d_tile0.as<uint32_t>(), c->d_tile_ent.as<uint32_t>(), lo, hi);
+            k0_tile_idx<<<c->n_sm * 4, 256, 0, st>>>(c->d_reg.as<uint4>(), c->d_tile_idx.as<uint32_t>(), R);
+        }
         CK(cudaGetLastError());
     }
-    CKN(N.AllGather(d_counts, d_matrix, (size_t)R, ncclUint64, c->comm, st));
-    std::vector<unsigned long long> mat((size_t)R * R);
-    CK(cudaMemcpyAsync(mat.data(), d_matrix, 8ull * R * R, cudaMemcpyDeviceToHost, st));
-    CK(cudaStreamSynchronize(st));
-    // mat[s*R + d] = keys rank s holds for rank d
-    uint64_t total = 0;
-    std::vector<uint64_t> soff(R + 1, 0), roff(R + 1, 0);
-    for (int r = 0; r < R; ++r) {
-        soff[r + 1] = soff[r] + mat[(size_t)me * R + r];
-        roff[r + 1] = roff[r] + mat[(size_t)r * R + me];
+    CK(cudaStreamSynchronize(st));  // the pageable vectors above must not change under the copy
+    c->tables_dirty = false;
+    ++c->generation;
+    c->cache_l_valid = false;
+    c->cand_cap = 0;
+    return OVL_OK;
+}
+
+// host -> HBM: the staged ASCII records in one copy (the chunked form lives in run_pass)
+int upload_ascii(ovl_ctx* c) {
+    const size_t ab = c->ascii_used + SLACK;
+    CK(cudaEventRecord(c->ev[E_H2D0], c->st));
+    if (!c->len.empty() && c->ascii.p) {
+        OVL_TRY(dev_ensure(c, c->d_ascii, ab));
+        CK(cudaMemcpyAsync(c->d_ascii.p, c->ascii.p, ab, cudaMemcpyHostToDevice, c->st));
     }
-    total = roff[R];
-    if (soff[R] != n) return fail(c, OVL_E_NCCL, "hit exchange: partition counted %llu of %llu keys", (unsigned long long)soff[R], (unsigned long long)n);
-    OVL_TRY(dev_ensure(c, c->d_cand2, (total ? total : 1) * 8));  // old contents live in d_cand now
-    uint64_t* src = c->d_cand.as<uint64_t>();
-    uint64_t* dst = c->d_cand2.as<uint64_t>();
-    const uint64_t own = mat[(size_t)me * R + me];
-    if (own) CK(cudaMemcpyAsync(dst + roff[me], src + soff[me], own * 8, cudaMemcpyDeviceToDevice, st));
-    CKN(N.GroupStart());
-    for (int r = 0; r < R; ++r) {
-        if (r == me) continue;
-        const uint64_t ns = mat[(size_t)me * R + r], nr = mat[(size_t)r * R + me];
-        if (ns) CKN(N.Send(src + soff[r], ns, ncclUint64, r, c->comm, st));
-        if (nr) CKN(N.Recv(dst + roff[r], nr, ncclUint64, r, c->comm, st));
+    CK(cudaEventRecord(c->ev[E_H2D1], c->st));
+    CK(cudaStreamSynchronize(c->st));
+    c->stats.ascii_bytes = c->len.empty() ? 0 : ab;
+    c->stats.ms_h2d = ev_ms(c, E_H2D0, E_H2D1);
+    c->ascii_resident = true;
+    return OVL_OK;
+}
+
+// 8-byte copy of the current step id into flag word `kind` of peer r (stream ordered behind the
+// data it announces; runs on a copy engine, needs no SM)
+int signal_copy(ovl_ctx* c, int r, int kind, cudaStream_t s) {
+    unsigned long long* dst = &hdr_of(c, r)->flag[kind][c->rank];
+    CK(cudaMemcpyAsync(dst, &my_hdr(c)->step_word, 8, cudaMemcpyDefault, s));
+    return OVL_OK;
+}
+
+int wait_flags(ovl_ctx* c, int kind, cudaStream_t s, uint32_t* launches) {
+    ovl::k_wait<<<1, 32, 0, s>>>(my_hdr(c)->flag[kind], (uint32_t)c->nranks, (uint32_t)c->rank, c->step,
+                                 (unsigned long long)c->opt_timeout_ms * 1000000ull, &my_hdr(c)->abort);
+    ++*launches;
+    CK(cudaGetLastError());
+    return OVL_OK;
+}
+
+int signal_all(ovl_ctx* c, int kind, cudaStream_t s, uint32_t* launches) {
+    ovl::k_signal<<<1, 32, 0, s>>>(c->d_peerhdr.as<ArenaHdr*>(), (uint32_t)c->nranks, (uint32_t)c->rank, kind, c->step);
+    ++*launches;
+    CK(cudaGetLastError());
+    return OVL_OK;
+}
+
+// small publish kernels of the gather / status phase -------------------------------------------
+__global__ void __launch_bounds__(32) k9_publish_rowcnt(ArenaHdr* const* __restrict__ peer_hdr, uint32_t nr, uint32_t me,
+                                                        const unsigned long long* __restrict__ n_rows, unsigned long long* ctr_nrows,
+                                                        unsigned long long step) {
+    const uint32_t s = threadIdx.x;
+    const unsigned long long n = *n_rows;
+    if (s == 0) *ctr_nrows = n;
+    if (s < nr) {
+        peer_hdr[s]->rowcnt[me] = n;
+        __threadfence_system();
+        if (s != me) ovl::st_release_sys(&peer_hdr[s]->flag[ovl::F_ROWCNT][me], step);
     }
-    CKN(N.GroupEnd());
-    c->stats.hits_sent = n - own;
-    c->stats.hits_received = total - own;
-    *n_hits = total;
+}
+
+__global__ void __launch_bounds__(32) k9_publish_status(ArenaHdr* const* __restrict__ peer_hdr, uint32_t nr, uint32_t me,
+                                                        unsigned long long step) {
+    const uint32_t s = threadIdx.x;
+    if (s < nr && s != me) {
+        const unsigned long long* src = peer_hdr[me]->status[me];
+        unsigned long long* dst = peer_hdr[s]->status[me];
+        for (int i = 0; i < STATUS_WORDS; ++i) dst[i] = src[i];
+        __threadfence_system();
+        ovl::st_release_sys(&peer_hdr[s]->flag[ovl::F_STATUS][me], step);
+    }
+}
+
+// -----------------------------------------------------------------------------------------
+// One pass over the entry store.  chunked: the ASCII records are sent host -> HBM in pieces on
+// the copy stream and packed piece by piece under the copy (the ovl_overlaps route); otherwise
+// they are resident already (ovl_upload).
+int run_pass(ovl_ctx* c, uint32_t min_length, bool chunked) {
+    using namespace ovl;
+    const uint32_t l = min_length < 1 ? 1u : min_length;  // min_length 0 behaves as 1 (SURVEY 3.3)
+    const int k = l < 32 ? (int)l : 32;
+    const uint32_t M = (uint32_t)c->len.size();
+    const int nr = c->nranks, me = c->rank;
+    ovl_stats& S = c->stats;
+    const float keep_h2d = S.ms_h2d;
+    const uint64_t keep_ab = S.ascii_bytes;
+    memset(&S, 0, sizeof S);
+    S.ms_h2d = keep_h2d;
+    S.ascii_bytes = keep_ab;
+    S.entries = M;
+    S.bases = c->bases;
+    S.kmer = (uint32_t)k;
+    c->n_rows = 0;
+    c->rows_fetched = false;
+    c->gathered = false;
+    if (M == 0) return OVL_OK;  // the reference segfaults here (SURVEY 7.3); we return no rows
+    if (nr > MAX_RANKS) return fail(c, OVL_E_LIMIT, "more than %d ranks", MAX_RANKS);
+    if (nr > 1 && (int)c->rank_e.size() != nr + 1) return fail(c, OVL_E_ARG, "call ovl_comm_sync_ranges before ovl_overlaps_device");
+    const bool mirror = c->opt_mirror && c->pairs == 1;
+    S.mirror = mirror ? 1u : 0u;
+    MirrorRule mrule;
+    mrule.on = mirror ? 1 : 0;
+    S.granules = c->G;
+    KeyFmt fmt;
+    fmt.bits_e = ceil_log2((uint64_t)M < 2 ? 2 : M);
+    fmt.bits_p = ceil_log2(c->max_len + 1 < 2 ? 2 : c->max_len + 1);
+    if (fmt.total() > 64)
+        return fail(c, OVL_E_LIMIT, "candidate key needs %d bits (entries %u, longest %llu): over the 64-bit key layout",
+                    fmt.total(), M, (unsigned long long)c->max_len);
+    // host-known sizes (no device round trip): anchors, scan positions
+    if (!c->cache_l_valid || c->cache_l != l) {
+        uint64_t na = 0, np = 0;
+        for (uint32_t e = 0; e < M; ++e) na += c->len[e] >= l;
+        for (uint32_t e = c->e_lo; e < c->e_hi; ++e)
+            if (c->len[e] >= l) np += c->len[e] - l + 1;
+        c->cache_nanc = na;
+        c->cache_npos = np;
+        c->cache_l = l;
+        c->cache_l_valid = true;
+    }
+    const uint64_t n_anc = c->cache_nanc;
+    S.anchors = n_anc;
+    S.scan_positions = c->cache_npos;
+    // anchor stride: largest power of two <= min(64, l-k+1); 1 = canonical dense scan.  The table is
+    // partitioned over the ranks, so its size per GPU does not depend on N and the largest stride
+    // (fewest probes) is the choice; it is only lowered while the partition would outgrow L2 by far
+    // and the scan of a smaller stride is still the cheaper side (DRAM-resident table: ~3x the
+    // per-key cost; per-probe cost of the filter pass: ~1/8 of a resident insert).
+    int slog = 0;
+    {
+        uint32_t smax = l - (uint32_t)k + 1;  // >= 1
+        if (smax > 64) smax = 64;
+        if (c->opt_stride > 0 && (uint32_t)c->opt_stride < smax) smax = (uint32_t)c->opt_stride;
+        if (c->collect) smax = 1;  // byte accounting is defined on the canonical candidates
+        while ((2u << slog) <= smax) ++slog;
+        const int cap = max_stride_log2(M);
+        if (slog > cap) slog = cap;
+        if (c->opt_stride == 0 && slog > 1) {
+            const double l2 = 96.0 * 1048576.0;
+            const double gran = (double)(c->ranges.g_end[0] - c->ranges.g_begin[0]) + (double)(c->ranges.g_end[1] - c->ranges.g_begin[1]);
+            int best = slog;
+            double best_cost = 1e300;
+            for (int sl = slog; sl >= 1; --sl) {
+                const double keys = (double)n_anc * (double)(1u << sl) / nr;
+                const double tbytes = 8.0 * (double)(1ull << table_bits((uint64_t)n_anc << sl, nr));
+                const double ins = keys * (tbytes > l2 ? 3.0 : 1.0);
+                const double probes = gran * (double)(64u >> sl) * 0.125;
+                if (ins + probes < best_cost) {
+                    best_cost = ins + probes;
+                    best = sl;
+                }
+            }
+            slog = best;
+        }
+    }
+    const bool dense = slog == 0;
+    S.anchor_stride = 1u << slog;
+    const uint64_t n_keys = n_anc << slog;
+    const int tbits = table_bits(n_keys, nr);
+    const bool smem_filter = dense && n_anc <= (1u << 17);
+    const int bm_bits = dense ? dense_filter_bits(n_anc, smem_filter)
+                              : slice_bits(n_keys, nr, (uint64_t)c->opt_filter_kb << 10);
+    const uint32_t n_local = c->e_hi - c->e_lo;
+    const ScanRanges& R = c->ranges;
+    const uint64_t n_gran_local = (uint64_t)(R.g_end[0] - R.g_begin[0]) + (R.g_end[1] - R.g_begin[1]);
+    const uint64_t probes = n_gran_local * (uint64_t)(64u >> slog);
+    const bool route = mirror && nr > 1;  // hit keys travel to the rank that owns their A entry
+    const bool have_anchors = n_anc != 0;
+
+    cudaStream_t st = c->st, sk = c->st_k2, sp = c->st_push, sg = c->st_sig;
+    const int nsm = c->n_sm;
+    const uint32_t kblocks = (uint32_t)nsm * 8;
+
+    for (int attempt = 0;; ++attempt) {
+        if (c->cand_cap == 0) {
+            uint64_t cap = c->cand_per_entry * n_local;
+            if (cap < c->min_cand_cap) cap = c->min_cand_cap;
+            c->cand_cap = cap;
+        }
+        if (c->cand_cap > 0x7fffffffull) return fail(c, OVL_E_LIMIT, "more than 2^31 candidates on one GPU");
+        const uint64_t hit_cap = mirror ? 3 * c->cand_cap : c->cand_cap;
+        const uint64_t scan_cap = dense ? 1 : std::min<uint64_t>(probes + 32, 2 * c->cand_cap + probes / 8 + 4096);
+        // ---- the arena (and, on N > 1, the peer mappings) -----------------------------------
+        const uint64_t key[4] = {c->generation, c->cand_cap, ((uint64_t)nr << 1) | (uint64_t)mirror, c->arena_epoch};
+        if (memcmp(key, c->arena_key, sizeof key) != 0 || !c->arena.p) {
+            OVL_TRY(connect_arena(c, mirror));
+            memcpy(c->arena_key, key, sizeof key);
+        }
+        const ArenaLayout& L = c->lay;
+        ArenaHdr* H = my_hdr(c);
+        uint8_t* A = c->arena.as<uint8_t>();
+        uint4* d_pre = at<uint4>(A, L.off_pre);
+        uint4* d_packed = at<uint4>(A, L.off_packed);
+        uint32_t* d_filter = at<uint32_t>(A, L.off_filter);
+        Slot* d_table = at<Slot>(A, L.off_table);
+        uint32_t* d_next = at<uint32_t>(A, L.off_next);
+        uint64_t* d_inbox = at<uint64_t>(A, L.off_inbox);
+        Row* d_rows = at<Row>(A, L.off_rows);
+        OVL_TRY(dev_ensure(c, c->d_cand, hit_cap * 8, false));  // candidates, later the bucketed hit keys
+        if (route) OVL_TRY(dev_ensure(c, c->d_stage, hit_cap * 8, false));
+        if (!dense) OVL_TRY(dev_ensure(c, c->d_scan, scan_cap * sizeof(Surv), false));
+        OVL_TRY(dev_ensure(c, c->d_cnt, c->cand_cap * 4, false));  // survivor list of the verifier's head
+        OVL_TRY(dev_ensure(c, c->d_big, (size_t)M * 4 + 4, false));
+        const size_t M1 = (size_t)M + 1;
+        OVL_TRY(dev_ensure(c, c->d_bkt, M1 * (8 + 8 + 4 + 4 + 4)));
+        size_t tb = 0;
+        CK(cub::DeviceScan::ExclusiveSum(nullptr, tb, (uint32_t*)nullptr, (uint64_t*)nullptr, (int)M1, st));
+        OVL_TRY(dev_ensure(c, c->d_tmp, tb));
+        if (chunked) OVL_TRY(dev_ensure(c, c->d_ascii, c->ascii_used + SLACK));
+
+        uint64_t* ctr = c->d_ctr.as<uint64_t>();
+        uint32_t launches = 0, lib = 0;
+        ++c->step;
+        uint64_t* h_step = c->h_ctr + C_COUNT + MAX_RANKS * STATUS_WORDS + MAX_RANKS + 1;
+        *h_step = c->step;
+
+        // ---- start: counters, step word -----------------------------------------------------
+        if (chunked) CK(cudaEventRecord(c->ev[E_H2D0], st));
+        CK(cudaEventRecord(c->ev[E_PACK0], st));
+        CK(cudaMemsetAsync(ctr, 0, C_COUNT * sizeof(uint64_t), st));
+        CK(cudaMemsetAsync(&H->inbox_n, 0, 8, st));
+        CK(cudaMemcpyAsync(&H->step_word, h_step, 8, cudaMemcpyHostToDevice, st));
+        CK(cudaEventRecord(c->ev_k0, st));
+        CK(cudaStreamWaitEvent(sk, c->ev_k0, 0));
+
+        // ---- K1 (+ the prefix table K2 needs), whole or piece by piece under the upload ----------
+        const int n_chunks = chunked ? std::max(1, std::min(c->opt_chunks, MAX_CHUNKS)) : 1;
+        PackParams K;
+        K.ascii = c->d_ascii.as<uint8_t>();
+        K.src = c->d_src.as<uint64_t>();
+        K.ent = c->d_ent.as<uint2>();
+        K.flags = c->d_flags.as<uint8_t>();
+        K.tile0 = c->d_tile0.as<uint32_t>();
+        K.tile_ent = c->d_tile_ent.as<uint32_t>();
+        K.packed32 = reinterpret_cast<uint32_t*>(d_packed);
+        K.M = M;
+        K.err = reinterpret_cast<uint32_t*>(ctr + C_ERR);
+        uint32_t e_prev = c->e_lo;
+        size_t byte_prev = 0;
+        for (int ch = 0; ch < n_chunks; ++ch) {
+            // entries of this piece: an even share of the local entries, cut on a record boundary
+            uint32_t e_next = ch + 1 == n_chunks ? c->e_hi : c->e_lo + (uint32_t)(((uint64_t)n_local * (ch + 1)) / n_chunks);
+            while (e_next < c->e_hi && (c->flags[e_next] & 1)) ++e_next;  // keep a twin with its forward entry
+            if (chunked) {
+                const size_t byte_next = e_next >= c->e_hi ? c->ascii_used + SLACK : (size_t)c->src[e_next];
+                if (byte_next > byte_prev && c->ascii.p)
+                    CK(cudaMemcpyAsync(c->d_ascii.as<uint8_t>() + byte_prev, c->ascii.p + byte_prev, byte_next - byte_prev,
+                                       cudaMemcpyHostToDevice, c->st_h2d));
+                byte_prev = std::max(byte_prev, byte_next);
+                CK(cudaEventRecord(c->ev_chunk[ch], c->st_h2d));
+                CK(cudaStreamWaitEvent(st, c->ev_chunk[ch], 0));
+                CK(cudaStreamWaitEvent(sk, c->ev_chunk[ch], 0));
+            }
+            if (e_next > e_prev) {
+                k2_prefix_ascii<<<(e_next - e_prev + 127) / 128, 128, 0, sk>>>(
+                    c->d_ascii.as<uint8_t>(), c->d_src.as<uint64_t>(), c->d_len.as<uint32_t>(), c->d_flags.as<uint8_t>(),
+                    d_pre, e_prev, e_next);
+                ++launches;
+                const uint32_t t_lo = c->tile0[e_prev], t_hi = c->tile0[e_next];
+                if (t_hi > t_lo) {
+                    K.t_begin = t_lo;
+                    K.t_end = t_hi;
+                    uint32_t blocks = (t_hi - t_lo + 7) / 8;
+                    if (blocks > (uint32_t)(nsm * c->opt_pack_bpsm)) blocks = (uint32_t)(nsm * c->opt_pack_bpsm);
+                    k1_pack<<<blocks, 256, 0, st>>>(K);
+                    ++launches;
+                }
+                CK(cudaGetLastError());
+            }
+            e_prev = e_next;
+        }
+        if (chunked) {
+            CK(cudaEventRecord(c->ev[E_H2D1], c->st_h2d));
+            c->ascii_resident = true;
+            S.ascii_bytes = c->ascii_used + SLACK;
+        }
+        CK(cudaEventRecord(c->ev_prel, sk));
+        CK(cudaEventRecord(c->ev_pack, st));
+        // ---- N > 1: push the prefix slice (small, urgent) and the forward region slice (bulk) -------
+        if (nr > 1) {
+            CK(cudaStreamWaitEvent(sg, c->ev_prel, 0));
+            const uint64_t pre_off = L.off_pre + (uint64_t)c->e_lo * 32, pre_bytes = (uint64_t)n_local * 32;
+            for (int j = 1; j < nr; ++j) {
+                const int r = (me + j) % nr;
+                if (pre_bytes)
+                    CK(cudaMemcpyAsync(at<uint8_t>(c->peer_base[r], c->peer_lay[r].off_pre + (uint64_t)c->e_lo * 32),
+                                       A + pre_off, pre_bytes, cudaMemcpyDefault, sg));
+                OVL_TRY(signal_copy(c, r, F_PRE, sg));
+            }
+            CK(cudaStreamWaitEvent(sp, c->ev_pack, 0));
+            const uint64_t fwd_bytes = (uint64_t)(R.g_end[0] - R.g_begin[0]) * 16;
+            for (int j = 1; j < nr; ++j) {  // ring offsets: at any moment every rank receives from one sender
+                const int r = (me + j) % nr;
+                if (fwd_bytes)
+                    CK(cudaMemcpyAsync(at<uint8_t>(c->peer_base[r], c->peer_lay[r].off_packed + (uint64_t)R.g_begin[0] * 16),
+                                       A + L.off_packed + (uint64_t)R.g_begin[0] * 16, fwd_bytes, cudaMemcpyDefault, sp));
+                OVL_TRY(signal_copy(c, r, F_FWD, sp));
+            }
+            CK(cudaEventRecord(c->ev_push, sp));
+        }
+        CK(cudaEventRecord(c->ev[E_ANCHOR0], st));
+
+        // ---- K2: this rank's partition of the anchor table, on its own stream under K1 -------------
+        TableView T{};
+        T.nr = (uint32_t)nr;
+        T.tbits = tbits;
+        for (int r = 0; r < nr; ++r) {
+            T.tbl[r] = at<Slot>(c->peer_base[r], c->peer_lay[r].off_table);
+            T.nxt[r] = at<uint32_t>(c->peer_base[r], c->peer_lay[r].off_next);
+        }
+        if (have_anchors) {
+            if (nr > 1) OVL_TRY(wait_flags(c, F_PRE, sk, &launches));
+            const size_t table_bytes = sizeof(Slot) << tbits;
+            CK(cudaMemsetAsync(d_table, 0xff, table_bytes, sk));  // EMPTY_SLOT
+            const uint64_t slice_bytes = dense ? (4ull << bm_bits) : ((1ull << bm_bits) / 8);
+            uint8_t* my_slice = reinterpret_cast<uint8_t*>(d_filter) + (dense ? 0 : slice_bytes * me);
+            CK(cudaMemsetAsync(my_slice, 0, slice_bytes, sk));
+            AnchorParams P;
+            P.pre64 = reinterpret_cast<const uint64_t*>(d_pre);
+            P.ent = c->d_ent.as<uint2>();
+            P.M = M;
+            P.l = l;
+            P.k = k;
+            P.stride_log2 = slog;
+            P.table = d_table;
+            P.tbits = tbits;
+            P.next = d_next;
+            P.bitmap = d_filter;
+            P.bm_bits = bm_bits;
+            P.dense = dense ? 1 : 0;
+            P.me = (uint32_t)me;
+            P.nr = (uint32_t)nr;
+            P.n_anchors = reinterpret_cast<unsigned long long*>(ctr + C_NANC);
+            P.flags = reinterpret_cast<unsigned long long*>(ctr + C_FLAGS);
+            const uint64_t nthreads = (uint64_t)M << slog;
+            k2_insert<<<(unsigned)((nthreads + 255) / 256), 256, 0, sk>>>(P);
+            ++launches;
+            CK(cudaGetLastError());
+            CK(cudaEventRecord(c->ev_k2, sk));
+            if (nr > 1) {  // my filter slice (sparse path) and "my partition is ready" to everyone
+                CK(cudaStreamWaitEvent(sg, c->ev_k2, 0));
+                for (int j = 1; j < nr; ++j) {
+                    const int r = (me + j) % nr;
+                    if (!dense)
+                        CK(cudaMemcpyAsync(at<uint8_t>(c->peer_base[r], c->peer_lay[r].off_filter + slice_bytes * me),
+                                           my_slice, slice_bytes, cudaMemcpyDefault, sg));
+                    OVL_TRY(signal_copy(c, r, F_FILT, sg));
+                }
+                CK(cudaEventRecord(c->ev_sig, sg));
+            }
+            CK(cudaStreamWaitEvent(st, c->ev_k2, 0));
+            if (nr > 1) OVL_TRY(wait_flags(c, F_FILT, st, &launches));
+        } else {
+            CK(cudaStreamWaitEvent(st, c->ev_prel, 0));
+        }
+        CK(cudaEventRecord(c->ev[E_SCAN0], st));
+
+        // ---- K3: scan the local A entries -----------------------------------------------------------
+        if (have_anchors && R.n_tiles) {
+            ScanParams P;
+            P.packed = d_packed;
+            P.reg = c->d_reg.as<uint4>();
+            P.tile_idx = c->d_tile_idx.as<uint32_t>();
+            P.ent = c->d_ent.as<uint2>();
+            P.R = R;
+            P.l = l;
+            P.k = k;
+            P.stride_log2 = slog;
+            P.filter = d_filter;
+            P.bm_bits = bm_bits;
+            P.T = T;
+            P.fmt = fmt;
+            P.surv.out = c->d_scan.as<Surv>();
+            P.surv.n_out = reinterpret_cast<unsigned long long*>(ctr + C_NSCAN);
+            P.surv.cap = scan_cap;
+            P.sink.out = c->d_cand.as<uint64_t>();
+            P.sink.n_out = reinterpret_cast<unsigned long long*>(ctr + C_NCAND);
+            P.sink.cap = c->cand_cap;
+            P.mirror = mrule;
+            if (!dense) {
+                uint32_t blocks = (R.n_tiles + 7) / 8;
+                if (blocks > (uint32_t)nsm * 8) blocks = (uint32_t)nsm * 8;
+                switch (slog) {
+                    case 6: k3_filter<6><<<blocks, 256, 0, st>>>(P); break;
+                    case 5: k3_filter<5><<<blocks, 256, 0, st>>>(P); break;
+                    case 4: k3_filter<4><<<blocks, 256, 0, st>>>(P); break;
+                    case 3: k3_filter<3><<<blocks, 256, 0, st>>>(P); break;
+                    default: k3_filter<-1><<<blocks, 256, 0, st>>>(P); break;
+                }
+                k3_resolve<<<kblocks, 256, 0, st>>>(P);
+                launches += 2;
+            } else if (smem_filter) {
+                k3_scan<true><<<nsm, 1024, 32 * WBUF * 8 + (4u << bm_bits), st>>>(P);
+                ++launches;
+            } else {
+                k3_scan<false><<<nsm, 1024, 32 * WBUF * 8, st>>>(P);
+                ++launches;
+            }
+            CK(cudaGetLastError());
+        }
+        CK(cudaEventRecord(c->ev[E_VERIFY0], st));
+
+        // ---- K4: verify.  N > 1: the forward region of every peer must have landed, then the twin
+        //      strands of the remote reads are rebuilt -------------------------------------------------
+        if (nr > 1) {
+            OVL_TRY(wait_flags(c, F_FWD, st, &launches));
+            const uint32_t rg[2][2] = {{0u, c->e_lo}, {c->e_hi, M}};
+            for (int i = 0; i < 2; ++i)
+                if (rg[i][1] > rg[i][0] && c->G > c->G_f) {
+                    k1_rc<<<rg[i][1] - rg[i][0], 128, 0, st>>>(c->d_ent.as<uint2>(), c->d_flags.as<uint8_t>(),
+                                                               reinterpret_cast<uint32_t*>(d_packed), rg[i][0], rg[i][1], M);
+                    ++launches;
+                }
+            CK(cudaGetLastError());
+        }
+        CandSink hits;
+        hits.out = route ? c->d_stage.as<uint64_t>() : d_inbox;
+        hits.n_out = route ? reinterpret_cast<unsigned long long*>(ctr + C_NSTAGE) : &H->inbox_n;
+        hits.cap = hit_cap;
+        if (have_anchors) {
+            if (c->collect || c->opt_serial_verify) {
+                VerifyParams V;
+                V.keys = c->d_cand.as<uint64_t>();
+                V.n_ptr = reinterpret_cast<const unsigned long long*>(ctr + C_NCAND);
+                V.cap = c->cand_cap;
+                V.packed = d_packed;
+                V.ent = c->d_ent.as<uint2>();
+                V.fmt = fmt;
+                V.hits = hits;
+                V.counters = reinterpret_cast<unsigned long long*>(ctr + C_SUMM);
+                V.collect = c->collect;
+                V.mirror = mrule;
+                k4_verify_serial<<<kblocks, 256, 0, st>>>(V);
+                ++launches;
+            } else {
+                Verify2Params V;
+                V.keys = c->d_cand.as<uint64_t>();
+                V.n_ptr = reinterpret_cast<const unsigned long long*>(ctr + C_NCAND);
+                V.cap = c->cand_cap;
+                V.packed64 = reinterpret_cast<const uint64_t*>(d_packed);
+                V.ent = c->d_ent.as<uint2>();
+                V.fmt = fmt;
+                V.surv = c->d_cnt.as<uint32_t>();
+                V.n_surv = reinterpret_cast<unsigned long long*>(ctr + C_NSURV);
+                V.hits = hits;
+                V.mirror = mrule;
+                V.tile_ctr = reinterpret_cast<unsigned long long*>(ctr + C_TILE_A);
+                k4a_head<<<kblocks, 256, 0, st>>>(V);
+                k4b_tail<<<kblocks, 256, 0, st>>>(V);
+                launches += 2;
+            }
+            CK(cudaGetLastError());
+        }
+        CK(cudaEventRecord(c->ev[E_SORT0], st));
+
+        // ---- K6 (N > 1, mirror mode): every hit key to the rank that owns its A entry ---------------
+        if (route) {
+            RouteParams Q;
+            Q.keys = c->d_stage.as<uint64_t>();
+            Q.n_ptr = reinterpret_cast<const unsigned long long*>(ctr + C_NSTAGE);
+            Q.cap = hit_cap;
+            Q.fmt = fmt;
+            Q.map.n = nr;
+            for (int r = 0; r <= nr; ++r) Q.map.e[r] = c->rank_e[r];
+            for (int r = 0; r < nr; ++r) {
+                Q.inbox[r] = at<uint64_t>(c->peer_base[r], c->peer_lay[r].off_inbox);
+                Q.inbox_n[r] = &hdr_of(c, r)->inbox_n;
+                Q.inbox_cap[r] = c->peer_lay[r].inbox_cap;
+            }
+            Q.me = (uint32_t)me;
+            Q.n_sent = reinterpret_cast<unsigned long long*>(ctr + C_NSENT);
+            k6_route<<<kblocks, 256, 0, st>>>(Q);
+            ++launches;
+            CK(cudaGetLastError());
+            OVL_TRY(signal_all(c, F_HITS, st, &launches));
+            OVL_TRY(wait_flags(c, F_HITS, st, &launches));
+        }
+
+        // ---- K7: order the hit keys by (a, b, p, flags) and emit rows: k7_bucket.cuh ------------------
+        uint64_t* b_off = c->d_bkt.as<uint64_t>();
+        uint64_t* b_rowoff = b_off + M1;
+        uint32_t* b_cnt = reinterpret_cast<uint32_t*>(b_rowoff + M1);
+        uint32_t* b_cur = b_cnt + M1;
+        uint32_t* b_rowcnt = b_cur + M1;
+        BucketParams B;
+        B.hits = d_inbox;
+        B.n_ptr = &H->inbox_n;
+        B.cap = L.inbox_cap;
+        B.fmt = fmt;
+        B.M = M;
+        B.cnt = b_cnt;
+        B.off = b_off;
+        B.cur = b_cur;
+        B.sorted = c->d_cand.as<uint64_t>();
+        B.rowcnt = b_rowcnt;
+        B.rowoff = b_rowoff;
+        B.big = reinterpret_cast<unsigned long long*>(ctr + C_BIG);
+        B.big_list = c->d_big.as<uint32_t>();
+        B.ent = c->d_ent.as<uint2>();
+        B.rows = d_rows;
+        B.rows_cap = hit_cap < L.rows_cap ? hit_cap : L.rows_cap;  // this rank's share
+        uint32_t wblocks = (M + 7) / 8;
+        if (wblocks > (uint32_t)nsm * 16) wblocks = (uint32_t)nsm * 16;
+        CK(cudaMemsetAsync(b_cnt, 0, M1 * 12, st));  // cnt, cur, rowcnt
+        k7_hist<<<kblocks, 256, 0, st>>>(B);
+        tb = c->d_tmp.cap;
+        CK(cub::DeviceScan::ExclusiveSum(c->d_tmp.p, tb, b_cnt, b_off, (int)M1, st));
+        k7_scatter<<<kblocks, 256, 0, st>>>(B);
+        k7_sort<<<wblocks, 256, 0, st>>>(B);
+        k7_sort_big<<<nsm, 1024, 0, st>>>(B);
+        CK(cudaEventRecord(c->ev[E_EMIT0], st));
+        tb = c->d_tmp.cap;
+        CK(cub::DeviceScan::ExclusiveSum(c->d_tmp.p, tb, b_rowcnt, b_rowoff, (int)M1, st));
+        k7_emit<<<wblocks, 256, 0, st>>>(B);
+        launches += 5;
+        lib += 2;
+        CK(cudaGetLastError());
+        CK(cudaEventRecord(c->ev[E_GATHER0], st));
+
+        // ---- K9 (N > 1): rows into rank 0's row array, in rank order --------------------------------
+        const unsigned long long* d_nrows = reinterpret_cast<const unsigned long long*>(b_rowoff + M);
+        k9_publish_rowcnt<<<1, 32, 0, st>>>(c->d_peerhdr.as<ArenaHdr*>(), (uint32_t)nr, (uint32_t)me, d_nrows,
+                                            reinterpret_cast<unsigned long long*>(ctr + C_NROWS), c->step);
+        ++launches;
+        if (nr > 1) {
+            OVL_TRY(wait_flags(c, F_ROWCNT, st, &launches));
+            if (me != 0) {
+                k9_push_rows<<<kblocks, 256, 0, st>>>(reinterpret_cast<const uint32_t*>(d_rows), B.rows_cap, H->rowcnt, (uint32_t)me,
+                                                      at<uint32_t>(c->peer_base[0], c->peer_lay[0].off_rows), c->peer_lay[0].rows_cap,
+                                                      reinterpret_cast<unsigned long long*>(ctr + C_FLAGS));
+                ++launches;
+            }
+            OVL_TRY(signal_all(c, F_ROWS, st, &launches));
+            if (me == 0) OVL_TRY(wait_flags(c, F_ROWS, st, &launches));
+            // never leave a push in flight behind the end of the pass
+            CK(cudaStreamWaitEvent(st, c->ev_push, 0));
+            if (have_anchors) CK(cudaStreamWaitEvent(st, c->ev_sig, 0));
+        }
+        CK(cudaGetLastError());
+        CK(cudaEventRecord(c->ev[E_END], st));
+
+        // ---- status to everyone (one vector per rank), then the single host synchronisation --------
+        {
+            StatusParams SP;
+            SP.st = H->status[me];
+            SP.ctr = reinterpret_cast<const unsigned long long*>(ctr);
+            SP.c_err = C_ERR;
+            SP.c_ncand = C_NCAND;
+            SP.c_nscan = C_NSCAN;
+            SP.c_nstage = C_NSTAGE;
+            SP.c_flags = C_FLAGS;
+            SP.n_hits = &H->inbox_n;
+            SP.n_rows = d_nrows;
+            SP.abort_word = &H->abort;
+            SP.cap_cand = c->cand_cap;
+            SP.cap_scan = dense ? ~0ull : scan_cap;
+            SP.cap_stage = hit_cap;
+            SP.cap_hits = L.inbox_cap;
+            SP.cap_rows = B.rows_cap;
+            k9_status<<<1, 32, 0, st>>>(SP);
+            ++launches;
+        }
+        if (nr > 1) {
+            k9_publish_status<<<1, 32, 0, st>>>(c->d_peerhdr.as<ArenaHdr*>(), (uint32_t)nr, (uint32_t)me, c->step);
+            ++launches;
+            OVL_TRY(wait_flags(c, F_STATUS, st, &launches));
+        }
+        CK(cudaGetLastError());
+        uint64_t* h_status = c->h_ctr + C_COUNT;
+        uint64_t* h_rowcnt = h_status + MAX_RANKS * STATUS_WORDS;
+        CK(cudaMemcpyAsync(c->h_ctr, ctr, C_COUNT * sizeof(uint64_t), cudaMemcpyDeviceToHost, st));
+        CK(cudaMemcpyAsync(h_status, H->status, sizeof H->status, cudaMemcpyDeviceToHost, st));
+        CK(cudaMemcpyAsync(h_rowcnt, H->rowcnt, sizeof H->rowcnt, cudaMemcpyDeviceToHost, st));
+        CK(cudaMemcpyAsync(h_rowcnt + MAX_RANKS, &H->inbox_n, 8, cudaMemcpyDeviceToHost, st));
+        CK(cudaStreamSynchronize(st));  // the one synchronisation of a pass
+        CK(cudaStreamSynchronize(sk));
+        if (chunked) {
+            CK(cudaStreamSynchronize(c->st_h2d));
+            float ms = 0.f;
+            if (cudaEventElapsedTime(&ms, c->ev[E_H2D0], c->ev[E_H2D1]) == cudaSuccess) S.ms_h2d = ms;
+            (void)cudaGetLastError();
+        }
+
+        // ---- what every rank now knows about every rank ------------------------------------------------
+        S.launches += launches;
+        S.lib_launches += lib;
+        int bad_rank = -1;
+        uint64_t bad_entry = 0, flags_any = 0;
+        for (int r = 0; r < nr; ++r) {
+            const uint64_t* s = h_status + (size_t)r * STATUS_WORDS;
+            if (s[ST_ERR] && bad_rank < 0) {
+                bad_rank = r;
+                bad_entry = s[ST_ERR] - 1;
+            }
+            flags_any |= s[ST_FLAGS];
+        }
+        if (flags_any & STF_TIMEOUT) {
+            c->arena_key[0] = ~0ull;  // flags and counters are in an unknown state: re-connect before the next pass
+            return fail(c, OVL_E_NCCL, "multi-GPU pass timed out waiting for a peer (step %llu): a rank died or the ranks' calls diverged",
+                        (unsigned long long)c->step);
+        }
+        if (bad_rank >= 0) {  // every rank raises, none is left waiting in a collective
+            const uint32_t e = (uint32_t)bad_entry;
+            if (bad_rank == me && e < M)
+                return fail(c, OVL_E_ALPHABET, "entry %u ('%.*s') holds a byte outside upper-case ACGT", e,
+                            (int)(c->id_off[e + 1] - c->id_off[e]), c->id_blob.data() + c->id_off[e]);
+            return fail(c, OVL_E_ALPHABET, "entry %u (held by rank %d) holds a byte outside upper-case ACGT", e, bad_rank);
+        }
+        if (flags_any & STF_TABLE) return fail(c, OVL_E_LIMIT, "anchor table partition overflow: internal error");
+        if (flags_any & STF_OVERFLOW) {
+            // some rank ran out of room: every rank sees that in the status vectors and repeats the
+            // pass; the ranks that overflowed grow first (the arenas are re-published either way)
+            if (attempt >= 3) return fail(c, OVL_E_LIMIT, "candidate buffers keep overflowing");
+            ++S.retries;
+            const uint64_t* s = h_status + (size_t)me * STATUS_WORDS;
+            const double per = mirror ? 3.0 : 1.0;
+            double need = (double)c->cand_cap;
+            if (s[ST_NCAND] > c->cand_cap) need = std::max(need, 1.07 * (double)s[ST_NCAND]);
+            if (!dense && s[ST_NSCAN] > scan_cap) need = std::max(need, 0.54 * (double)s[ST_NSCAN]);
+            if (s[ST_NSTAGE] > hit_cap) need = std::max(need, 1.07 * (double)s[ST_NSTAGE] / per);
+            if (s[ST_NHITS] > L.inbox_cap) need = std::max(need, 1.07 * (double)s[ST_NHITS] / per);
+            if (s[ST_NROWS] > B.rows_cap) need = std::max(need, 1.07 * (double)s[ST_NROWS] / per);
+            if (need > (double)c->cand_cap) {
+                c->cand_cap = (uint64_t)need + 1024;
+                c->min_cand_cap = std::max(c->min_cand_cap, c->cand_cap);
+            }
+            ++c->arena_epoch;
+            continue;
+        }
+        if (flags_any & STF_GATHER) return fail(c, OVL_E_LIMIT, "row gather overflow: internal error");
+        S.candidates = c->h_ctr[C_NCAND];
+        S.verified = c->h_ctr[C_NCAND];
+        S.hits = h_rowcnt[MAX_RANKS];  // keys in this rank's hit list
+        S.hits_sent = c->h_ctr[C_NSENT];
+        S.hits_received = route ? (S.hits + S.hits_sent > c->h_ctr[C_NSTAGE] ? S.hits + S.hits_sent - c->h_ctr[C_NSTAGE] : 0) : 0;
+        S.compared_bases = c->h_ctr[C_SUMM];
+        S.operand_bytes = c->h_ctr[C_SUMB];
+        S.big_buckets = (uint32_t)c->h_ctr[C_BIG];
+        S.scan_survivors = c->h_ctr[C_NSCAN];
+        uint64_t total = 0;
+        for (int r = 0; r < nr; ++r) total += h_rowcnt[r];
+        S.rows_local = h_rowcnt[me];
+        if (nr > 1) {
+            c->n_rows = me == 0 ? total : 0;
+            c->gathered = true;
+        } else {
+            c->n_rows = total;
+        }
+        S.rows = c->n_rows;
+        break;
+    }
+    S.ms_pack = ev_ms(c, E_PACK0, E_ANCHOR0);
+    S.ms_anchor = ev_ms(c, E_ANCHOR0, E_SCAN0);
+    S.ms_scan = ev_ms(c, E_SCAN0, E_VERIFY0);
+    S.ms_verify = ev_ms(c, E_VERIFY0, E_SORT0);
+    S.ms_sort = ev_ms(c, E_SORT0, E_EMIT0);
+    S.ms_emit = ev_ms(c, E_EMIT0, E_GATHER0);
+    S.ms_gather = ev_ms(c, E_GATHER0, E_END);
+    S.ms_device = ev_ms(c, E_PACK0, E_END);
+    if (chunked) {
+        float ms = 0.f;
+        if (cudaEventElapsedTime(&ms, c->ev[E_H2D1], c->ev[E_END]) == cudaSuccess) S.ms_exposed = ms;
+        (void)cudaGetLastError();
+    } else {
+        S.ms_exposed = S.ms_device;
+    }
     return OVL_OK;
 }
 
@@ -351,20 +1289,22 @@ int ovl_create(int device, ovl_ctx** out) {
     }
     x->n_sm = prop.multiProcessorCount;
     auto init = [&]() -> int {
+        int lo_pri = 0, hi_pri = 0;
+        CK(cudaDeviceGetStreamPriorityRange(&lo_pri, &hi_pri));
         CK(cudaStreamCreateWithFlags(&x->st, cudaStreamNonBlocking));
-        CK(cudaStreamCreateWithFlags(&x->st_comm, cudaStreamNonBlocking));
         CK(cudaStreamCreateWithFlags(&x->st_k2, cudaStreamNonBlocking));
-        CK(cudaEventCreateWithFlags(&x->ev_k0, cudaEventDisableTiming));
-        CK(cudaEventCreateWithFlags(&x->ev_prel, cudaEventDisableTiming));
-        CK(cudaEventCreateWithFlags(&x->ev_k2, cudaEventDisableTiming));
-        for (int i = 0; i < 4; ++i) CK(cudaEventCreate(&x->ev_dbg[i]));
+        CK(cudaStreamCreateWithPriority(&x->st_push, cudaStreamNonBlocking, hi_pri));
+        CK(cudaStreamCreateWithPriority(&x->st_sig, cudaStreamNonBlocking, hi_pri));
+        CK(cudaStreamCreateWithFlags(&x->st_h2d, cudaStreamNonBlocking));
+        cudaEvent_t* plain[] = {&x->ev_pack, &x->ev_k0, &x->ev_prel, &x->ev_k2, &x->ev_push, &x->ev_sig};
+        for (cudaEvent_t* e2 : plain) CK(cudaEventCreateWithFlags(e2, cudaEventDisableTiming));
+        for (int i = 0; i < MAX_CHUNKS; ++i) CK(cudaEventCreateWithFlags(&x->ev_chunk[i], cudaEventDisableTiming));
         for (int i = 0; i < E_COUNT; ++i) CK(cudaEventCreate(&x->ev[i]));
-        CK(cudaEventCreateWithFlags(&x->ev_comm, cudaEventDisableTiming));
-        CK(cudaEventCreateWithFlags(&x->ev_pack, cudaEventDisableTiming));
-        CK(cudaEventCreateWithFlags(&x->ev_pre, cudaEventDisableTiming));
         CK(cudaEventCreate(&x->ev_t0));
         CK(cudaEventCreate(&x->ev_t1));
-        CK(cudaHostAlloc(reinterpret_cast<void**>(&x->h_ctr), (C_COUNT + 2) * sizeof(uint64_t), cudaHostAllocDefault));
+        const size_t hwords = C_COUNT + MAX_RANKS * STATUS_WORDS + MAX_RANKS + 2;
+        CK(cudaHostAlloc(reinterpret_cast<void**>(&x->h_ctr), hwords * sizeof(uint64_t), cudaHostAllocDefault));
+        memset(x->h_ctr, 0, hwords * sizeof(uint64_t));
         OVL_TRY(dev_ensure(c, x->d_ctr, C_COUNT * sizeof(uint64_t), false));
         CK(cudaFuncSetAttribute(ovl::k3_scan<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, 32 * ovl::WBUF * 8 + 128 * 1024));
         CK(cudaFuncSetAttribute(ovl::k3_scan<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, 32 * ovl::WBUF * 8));
@@ -379,33 +1319,29 @@ int ovl_create(int device, ovl_ctx** out) {
 void ovl_destroy(ovl_ctx* c) {
     if (!c) return;
     cudaSetDevice(c->device);
+    cudaDeviceSynchronize();
+    close_peers(c);
     if (c->comm) nccl_dyn::api().CommDestroy(c->comm);
-    DevBuf* bufs[] = {&c->d_ascii, &c->d_src, &c->d_len, &c->d_flags, &c->d_gran0, &c->d_gran_ent,
-                      &c->d_ent, &c->d_packed, &c->d_table, &c->d_filter, &c->d_next, &c->d_ctr,
-                      &c->d_tmp, &c->d_cand, &c->d_cand2, &c->d_cnt, &c->d_offs, &c->d_rows, &c->d_cnts,
-                      &c->d_tile0, &c->d_tile_ent, &c->d_xchg, &c->d_pre, &c->d_bkt, &c->d_fwd, &c->d_fmark, &c->d_fkeep, &c->d_foff, &c->d_frows, &c->d_gath};
+    DevBuf* bufs[] = {&c->d_ascii, &c->d_src, &c->d_len, &c->d_flags, &c->d_gran0, &c->d_ent, &c->d_reg, &c->d_tile0,
+                      &c->d_tile_ent, &c->d_tile_idx, &c->d_ctr, &c->d_tmp, &c->d_cand, &c->d_stage, &c->d_scan,
+                      &c->d_cnt, &c->d_bkt, &c->d_big, &c->d_peerhdr, &c->d_fmark, &c->d_fkeep, &c->d_foff, &c->d_frows,
+                      &c->arena};
     for (DevBuf* b : bufs)
         if (b->p) cudaFree(b->p);
     if (c->ascii.p) cudaFreeHost(c->ascii.p);
     if (c->h_rows.p) cudaFreeHost(c->h_rows.p);
-    if (c->h_gather.p) cudaFreeHost(c->h_gather.p);
     if (c->h_frows.p) cudaFreeHost(c->h_frows.p);
     if (c->h_ctr) cudaFreeHost(c->h_ctr);
     for (int i = 0; i < E_COUNT; ++i)
         if (c->ev[i]) cudaEventDestroy(c->ev[i]);
-    if (c->ev_comm) cudaEventDestroy(c->ev_comm);
-    if (c->ev_pack) cudaEventDestroy(c->ev_pack);
-    if (c->ev_pre) cudaEventDestroy(c->ev_pre);
-    if (c->ev_k0) cudaEventDestroy(c->ev_k0);
-    if (c->ev_prel) cudaEventDestroy(c->ev_prel);
-    if (c->ev_k2) cudaEventDestroy(c->ev_k2);
-    for (int i = 0; i < 4; ++i)
-        if (c->ev_dbg[i]) cudaEventDestroy(c->ev_dbg[i]);
-    if (c->st_k2) cudaStreamDestroy(c->st_k2);
-    if (c->ev_t0) cudaEventDestroy(c->ev_t0);
-    if (c->ev_t1) cudaEventDestroy(c->ev_t1);
-    if (c->st) cudaStreamDestroy(c->st);
-    if (c->st_comm) cudaStreamDestroy(c->st_comm);
+    for (int i = 0; i < MAX_CHUNKS; ++i)
+        if (c->ev_chunk[i]) cudaEventDestroy(c->ev_chunk[i]);
+    cudaEvent_t evs[] = {c->ev_pack, c->ev_k0, c->ev_prel, c->ev_k2, c->ev_push, c->ev_sig, c->ev_t0, c->ev_t1};
+    for (cudaEvent_t e : evs)
+        if (e) cudaEventDestroy(e);
+    cudaStream_t sts[] = {c->st, c->st_k2, c->st_push, c->st_sig, c->st_h2d};
+    for (cudaStream_t s : sts)
+        if (s) cudaStreamDestroy(s);
     (void)cudaGetLastError();
     delete c;
 }
@@ -503,11 +1439,13 @@ int ovl_clear(ovl_ctx* c) {
     c->gran0.clear();
     c->tile0.clear();
     c->bases = c->max_len = 0;
-    c->uploaded = false;
+    c->tables_dirty = true;
+    c->ascii_resident = false;
     c->n_rows = 0;
     c->rows_fetched = false;
     c->gathered = false;
     c->e_lo = c->e_hi = 0;
+    c->G = c->G_f = 0;
     return OVL_OK;
 }
 
@@ -556,6 +1494,34 @@ int ovl_set_option(ovl_ctx* c, const char* name, int64_t value) {
         c->opt_mirror = value != 0;
         return OVL_OK;
     }
+    if (!strcmp(name, "filter_kb")) {
+        if (value < 4 || value > (1 << 22)) return fail(c, OVL_E_ARG, "filter_kb must be in 4..4194304");
+        c->opt_filter_kb = (int)value;
+        c->arena_key[0] = ~0ull;  // the arena is sized with it
+        return OVL_OK;
+    }
+    if (!strcmp(name, "upload_chunks")) {
+        if (value < 1 || value > MAX_CHUNKS) return fail(c, OVL_E_ARG, "upload_chunks must be in 1..%d", MAX_CHUNKS);
+        c->opt_chunks = (int)value;
+        return OVL_OK;
+    }
+    if (!strcmp(name, "min_cand_cap")) {  // test hook: a small first capacity forces the overflow -> grow -> repeat route
+        if (value < 32) return fail(c, OVL_E_ARG, "min_cand_cap must be >= 32");
+        c->min_cand_cap = (uint64_t)value;
+        c->cand_cap = 0;
+        return OVL_OK;
+    }
+    if (!strcmp(name, "cand_per_entry")) {  // first candidate capacity per local entry (default 96; config 2 needs ~41)
+        if (value < 1 || value > 100000) return fail(c, OVL_E_ARG, "cand_per_entry must be in 1..100000");
+        c->cand_per_entry = (uint64_t)value;
+        c->cand_cap = 0;
+        return OVL_OK;
+    }
+    if (!strcmp(name, "peer_timeout_ms")) {
+        if (value < 1 || value > 600000) return fail(c, OVL_E_ARG, "peer_timeout_ms must be in 1..600000");
+        c->opt_timeout_ms = (int)value;
+        return OVL_OK;
+    }
     return fail(c, OVL_E_ARG, "unknown option '%s'", name);
 }
 
@@ -582,636 +1548,24 @@ int ovl_timer_stop(ovl_ctx* c, float* ms) {
 }
 
 // -----------------------------------------------------------------------------------------
-// host -> HBM: ASCII records of the local entries + the entry table
+// host -> HBM.  The entry tables travel only when entries were added since the last call; the
+// ASCII records only when they are not resident (ovl_overlaps re-sends them on every call: host
+// buffers in, like the reference rebuilds its index on every call, src/overlapper.cpp:33-36).
 int ovl_upload(ovl_ctx* c) {
     if (!c) return OVL_E_ARG;
     OVL_TRY(set_dev(c));
-    const size_t M = c->len.size();
-    // local entry range (contiguous) and granule prefix sum
-    uint32_t lo = (uint32_t)M, hi = 0;
-    try {
-        c->gran0.resize(M + 1);
-        c->tile0.resize(M + 1);
-    } catch (const std::bad_alloc&) {
-        return fail(c, OVL_E_NOMEM, "out of host memory");
-    }
-    uint64_t g = 0, nt = 0;
-    for (size_t e = 0; e < M; ++e) {
-        c->gran0[e] = (uint32_t)g;
-        c->tile0[e] = (uint32_t)nt;
-        const uint64_t ge = (c->len[e] + 63u) / 64u;
-        g += ge;
-        // K1 tiles: forward local entries only (a twin is written by its forward entry's tiles)
-        if (c->src[e] != NO_SRC && !(c->flags[e] & 1)) nt += (4 * ge + ovl::PACK_TILE_UNITS - 1) / ovl::PACK_TILE_UNITS;
-        if (c->src[e] != NO_SRC) {
-            if (e < lo) lo = (uint32_t)e;
-            hi = (uint32_t)e + 1;
-        }
-    }
-    if (g >= 0xffffffffull) return fail(c, OVL_E_LIMIT, "more than 2^32 granules (%llu)", (unsigned long long)g);
-    if (M) {
-        c->gran0[M] = (uint32_t)g;
-        c->tile0[M] = (uint32_t)nt;
-    }
-    if (lo > hi) lo = hi = 0;
-    for (uint32_t e = lo; e < hi; ++e)
-        if (c->src[e] == NO_SRC) return fail(c, OVL_E_ARG, "local entries must be one contiguous range (entry %u is remote)", e);
-    c->e_lo = lo;
-    c->e_hi = hi;
-    if (c->nranks == 1 && (lo != 0 || hi != M)) return fail(c, OVL_E_ARG, "remote entries need ovl_comm_init");
-
-    CK(cudaEventRecord(c->ev[E_H2D0], c->st));
-    if (M) {
-        const size_t ab = c->ascii_used + SLACK;
-        OVL_TRY(dev_ensure(c, c->d_ascii, ab));
-        OVL_TRY(dev_ensure(c, c->d_src, M * 8));
-        OVL_TRY(dev_ensure(c, c->d_len, M * 4));
-        OVL_TRY(dev_ensure(c, c->d_flags, M));
-        OVL_TRY(dev_ensure(c, c->d_gran0, (M + 1) * 4));
-        OVL_TRY(dev_ensure(c, c->d_gran_ent, (g + 1) * 4));
-        OVL_TRY(dev_ensure(c, c->d_ent, M * 8));
-        OVL_TRY(dev_ensure(c, c->d_packed, (g + 2) * 16));
-        OVL_TRY(dev_ensure(c, c->d_tile0, (M + 1) * 4));
-        OVL_TRY(dev_ensure(c, c->d_tile_ent, (nt + 1) * 4));
-        CK(cudaMemcpyAsync(c->d_tile0.p, c->tile0.data(), (M + 1) * 4, cudaMemcpyHostToDevice, c->st));
-        if (c->ascii.p) CK(cudaMemcpyAsync(c->d_ascii.p, c->ascii.p, ab, cudaMemcpyHostToDevice, c->st));
-        CK(cudaMemcpyAsync(c->d_src.p, c->src.data(), M * 8, cudaMemcpyHostToDevice, c->st));
-        CK(cudaMemcpyAsync(c->d_len.p, c->len.data(), M * 4, cudaMemcpyHostToDevice, c->st));
-        CK(cudaMemcpyAsync(c->d_flags.p, c->flags.data(), M, cudaMemcpyHostToDevice, c->st));
-        CK(cudaMemcpyAsync(c->d_gran0.p, c->gran0.data(), (M + 1) * 4, cudaMemcpyHostToDevice, c->st));
-        c->stats.ascii_bytes = ab;
-    }
-    CK(cudaEventRecord(c->ev[E_PACK0], c->st));
-    CK(cudaStreamSynchronize(c->st));  // the pageable vectors above must not change under the copy
-    c->stats.ms_h2d = ev_ms(c, E_H2D0, E_PACK0);
-    c->uploaded = true;
-    c->cache_pairs = -1;
-    c->cache_l_valid = false;
+    OVL_TRY(upload_tables(c));
+    if (!c->ascii_resident) OVL_TRY(upload_ascii(c));
     return OVL_OK;
 }
 
-// -----------------------------------------------------------------------------------------
 int ovl_overlaps_device(ovl_ctx* c, uint32_t min_length, uint64_t* n_rows_out) {
-    using namespace ovl;
     if (!c) return OVL_E_ARG;
     OVL_TRY(set_dev(c));
-    if (!c->uploaded) return fail(c, OVL_E_ARG, "ovl_overlaps_device: call ovl_upload first");
-    const uint32_t l = min_length < 1 ? 1u : min_length;  // min_length 0 behaves as 1 (SURVEY 3.3)
-    const int k = l < 32 ? (int)l : 32;
-    const uint32_t M = (uint32_t)c->len.size();
-    ovl_stats& S = c->stats;
-    const float keep_h2d = S.ms_h2d;
-    const uint64_t keep_ab = S.ascii_bytes;
-    memset(&S, 0, sizeof S);
-    S.ms_h2d = keep_h2d;
-    S.ascii_bytes = keep_ab;
-    S.entries = M;
-    S.bases = c->bases;
-    S.kmer = (uint32_t)k;
-    c->n_rows = 0;
-    c->rows_fetched = false;
-    c->gathered = false;
     if (n_rows_out) *n_rows_out = 0;
-    if (M == 0) return OVL_OK;  // the reference segfaults here (SURVEY 7.3); we return no rows
-    // strand-mirror halving needs entry e ^ 1 to be the other strand of entry e, for every e
-    if (c->cache_pairs < 0) {
-        bool pairs = M % 2 == 0;
-        for (uint32_t e = 0; pairs && e < M; e += 2) pairs = !(c->flags[e] & 1) && (c->flags[e + 1] & 1);
-        c->cache_pairs = pairs ? 1 : 0;
-    }
-    const bool mirror = c->opt_mirror && c->cache_pairs == 1;
-    S.mirror = mirror ? 1u : 0u;
-    ovl::MirrorRule mrule;
-    mrule.on = mirror ? 1 : 0;
-
-    const uint32_t G = c->gran0[M];
-    S.granules = G;
-    KeyFmt fmt;
-    fmt.bits_e = ceil_log2((uint64_t)M < 2 ? 2 : M);
-    fmt.bits_p = ceil_log2(c->max_len + 1 < 2 ? 2 : c->max_len + 1);
-    if (fmt.total() > 64)
-        return fail(c, OVL_E_LIMIT, "candidate key needs %d bits (entries %u, longest %llu): over the 64-bit key layout",
-                    fmt.total(), M, (unsigned long long)c->max_len);
-    // host-known sizes (no device round trip): anchors, scan positions
-    if (!c->cache_l_valid || c->cache_l != l) {
-        uint64_t na = 0, np = 0;
-        for (uint32_t e = 0; e < M; ++e) na += c->len[e] >= l;
-        for (uint32_t e = c->e_lo; e < c->e_hi; ++e)
-            if (c->len[e] >= l) np += c->len[e] - l + 1;
-        c->cache_nanc = na;
-        c->cache_npos = np;
-        c->cache_l = l;
-        c->cache_l_valid = true;
-    }
-    const uint64_t n_anc = c->cache_nanc, npos = c->cache_npos;
-    S.anchors = n_anc;
-    S.scan_positions = npos;
-    // anchor stride: largest power of two <= min(64, l-k+1); 1 = canonical dense scan
-    int slog = 0;
-    {
-        uint32_t smax = l - (uint32_t)k + 1;  // >= 1
-        if (smax > 64) smax = 64;
-        if (c->opt_stride > 0 && (uint32_t)c->opt_stride < smax) smax = (uint32_t)c->opt_stride;
-        if (c->collect) smax = 1;  // byte accounting is defined on the canonical candidates
-        while ((2u << slog) <= smax) ++slog;
-        while (slog > 0 && (((uint64_t)M << slog) > 0xfffffff0ull)) --slog;
-        // Auto mode: the table build costs ~ (anchor entries x stride) inserts on EVERY rank (and
-        // much more per insert once the table outgrows L2), the scan ~ (own granules x 64/stride)
-        // filter probes.  Pick the stride with the smallest modelled sum; both tables are B200
-        // measurements on config 2 (55 200 anchor entries, 12.9 M granules; N=1 and N=2 columns of
-        // profiles/r01i_stride_sweep.txt).  A dense scan (stride 1) is only taken when l < 33
-        // forces it.
-        if (c->opt_stride == 0 && slog > 1) {
-            const uint64_t n_b = n_anc;
-            const double gl = (double)(c->gran0[c->e_hi] - c->gran0[c->e_lo]) / 12.9e6;
-            const double al = (double)n_b / 55200.0;
-            static const double scan_ms[7] = {0, 1.45, 0.98, 0.56, 0.40, 0.34, 0.27};      // stride 2^i
-            static const double anchor_ms[7] = {0, 0.01, 0.02, 0.03, 0.06, 0.13, 0.17};    // stride 2^i: what K2 adds beyond the concurrent K1
-            int best = slog;
-            double best_cost = 1e30;
-            for (int sl = slog; sl >= 1; --sl) {
-                const double keys = (double)n_b * (double)(1u << sl);
-                const double table_bytes = 8.0 * (double)(1ull << ceil_log2((uint64_t)(2 * keys) + 1));
-                double a_ms = al * anchor_ms[sl];
-                if (table_bytes > 64.0 * 1048576.0) a_ms *= 2.5;  // table no longer L2-resident
-                if (c->nranks > 1) a_ms *= 1.4;  // the concurrent replication of the reads competes for L2
-                const double cost = a_ms + gl * scan_ms[sl];
-                if (cost < best_cost) {
-                    best_cost = cost;
-                    best = sl;
-                }
-            }
-            slog = best;
-        }
-    }
-    const bool dense = slog == 0;
-    S.anchor_stride = 1u << slog;
-    cudaStream_t st = c->st;
-    uint64_t* ctr = c->d_ctr.as<uint64_t>();
-    uint32_t launches = 0, lib = 0;
-    const int nsm = c->n_sm;
-
-    CK(cudaEventRecord(c->ev[E_PACK0], st));
-    CK(cudaMemsetAsync(ctr, 0, C_COUNT * sizeof(uint64_t), st));
-    // ---- K0 + K1: pack the local entries ------------------------------------------------
-    const uint32_t g_lo = c->gran0[c->e_lo], g_hi = c->gran0[c->e_hi];
-    // multi-GPU with paired entries: the ranks exchange compact FORWARD granules only (k1_expand)
-    const bool fwd_x = c->nranks > 1 && c->cache_pairs == 1;
-    if (fwd_x) OVL_TRY(dev_ensure(c, c->d_fwd, ((size_t)G / 2 + 2) * 16));
-    k0_ent_table<<<(M + 255) / 256, 256, 0, st>>>(c->d_gran0.as<uint32_t>(), c->d_len.as<uint32_t>(), c->d_ent.as<uint2>(), M);
-    ++launches;
-    // ---- fork: the anchor-build stream.  The prefix table (K2's only input) is packed straight
-    //      from the ASCII records, so K2 does not wait for K1 -------------------------------------
-    cudaStream_t sk = c->st_k2;
-    CK(cudaEventRecord(c->ev_k0, st));
-    CK(cudaStreamWaitEvent(sk, c->ev_k0, 0));
-    OVL_TRY(dev_ensure(c, c->d_pre, (size_t)M * 32));
-    if (c->e_hi > c->e_lo) {
-        k2_prefix_ascii<<<(c->e_hi - c->e_lo + 127) / 128, 128, 0, sk>>>(
-            c->d_ascii.as<uint8_t>(), c->d_src.as<uint64_t>(), c->d_len.as<uint32_t>(), c->d_flags.as<uint8_t>(),
-            c->d_pre.as<uint4>(), c->e_lo, c->e_hi);
-        ++launches;
-        CK(cudaGetLastError());
-    }
-    CK(cudaEventRecord(c->ev_prel, sk));
-    cudaEvent_t k2_last = c->ev_prel;  // last event on the anchor-build stream: every exit path joins it
-    if (c->e_hi > c->e_lo) {
-        k0_gran_entry<<<nsm * 4, 256, 0, st>>>(c->d_gran0.as<uint32_t>(), c->d_gran_ent.as<uint32_t>(),
-                                               c->d_tile0.as<uint32_t>(), c->d_tile_ent.as<uint32_t>(), c->e_lo, c->e_hi);
-        ++launches;
-        const uint32_t t_lo = c->tile0[c->e_lo], t_hi = c->tile0[c->e_hi];
-        if (t_hi > t_lo) {
-            PackParams K;
-            K.ascii = c->d_ascii.as<uint8_t>();
-            K.src = c->d_src.as<uint64_t>();
-            K.ent = c->d_ent.as<uint2>();
-            K.flags = c->d_flags.as<uint8_t>();
-            K.tile0 = c->d_tile0.as<uint32_t>();
-            K.tile_ent = c->d_tile_ent.as<uint32_t>();
-            K.packed32 = c->d_packed.as<uint32_t>();
-            K.fwd32 = fwd_x ? c->d_fwd.as<uint32_t>() : nullptr;
-            K.M = M;
-            K.t_begin = t_lo;
-            K.t_end = t_hi;
-            K.err = reinterpret_cast<uint32_t*>(ctr + C_ERR);
-            uint32_t blocks = (t_hi - t_lo + 7) / 8;
-            if (blocks > (uint32_t)(nsm * c->opt_pack_bpsm)) blocks = (uint32_t)(nsm * c->opt_pack_bpsm);
-            k1_pack<<<blocks, 256, 0, st>>>(K);
-            ++launches;
-        }
-    }
-    CK(cudaMemsetAsync(c->d_packed.as<uint4>() + G, 0, 32, st));  // terminator granules
-    CK(cudaGetLastError());
-    // ---- multi-GPU: replicate on the comm stream (1) the prefix table, which K2 waits for, then
-    //      (2) the packed granules of every rank, which only K4 needs: that transfer runs under
-    //      K2 and K3 -------------------------------------------------------------------------
-    bool wait_packed = false;
-    if (c->nranks > 1) {
-        auto& N = nccl_dyn::api();
-        if ((int)c->rank_e.size() != c->nranks + 1) return fail(c, OVL_E_ARG, "call ovl_comm_sync_ranges before ovl_overlaps_device");
-        CK(cudaStreamWaitEvent(c->st_comm, c->ev_prel, 0));
-        CKN(N.GroupStart());
-        for (int r = 0; r < c->nranks; ++r) {
-            const uint32_t a = c->rank_e[r], b = c->rank_e[r + 1];
-            if (b > a) {
-                uint4* p = c->d_pre.as<uint4>() + 2ull * a;
-                CKN(N.Broadcast(p, p, (size_t)(b - a) * 32, ncclUint8, r, c->comm, c->st_comm));
-            }
-        }
-        CKN(N.GroupEnd());
-        CK(cudaEventRecord(c->ev_pre, c->st_comm));
-        CK(cudaStreamWaitEvent(sk, c->ev_pre, 0));  // K2 reads every rank's prefixes
-        CK(cudaEventRecord(c->ev_pack, st));        // K1 done: the packed granules may travel
-        CK(cudaStreamWaitEvent(c->st_comm, c->ev_pack, 0));
-        CK(cudaEventRecord(c->ev_dbg[0], c->st_comm));
-        if (fwd_x) {
-            // equal shares (the usual case): one in-place all-gather; else one broadcast per rank
-            bool equal = true;
-            const uint32_t cnt0 = (c->gran0[c->rank_e[1]] - c->gran0[c->rank_e[0]]) / 2;
-            for (int r = 0; r < c->nranks; ++r)
-                equal = equal && (c->gran0[c->rank_e[r + 1]] - c->gran0[c->rank_e[r]]) / 2 == cnt0;
-            if (equal && cnt0) {
-                uint4* all = c->d_fwd.as<uint4>();
-                CKN(N.AllGather(all + (size_t)c->rank * cnt0, all, (size_t)cnt0 * 16, ncclUint8, c->comm, c->st_comm));
-            } else {
-                CKN(N.GroupStart());
-                for (int r = 0; r < c->nranks; ++r) {
-                    const uint32_t a = c->gran0[c->rank_e[r]] / 2, b = c->gran0[c->rank_e[r + 1]] / 2;
-                    if (b > a) {
-                        uint4* p = c->d_fwd.as<uint4>() + a;
-                        CKN(N.Broadcast(p, p, (size_t)(b - a) * 16, ncclUint8, r, c->comm, c->st_comm));
-                    }
-                }
-                CKN(N.GroupEnd());
-            }
-            CK(cudaEventRecord(c->ev_dbg[1], c->st_comm));
-            // both strands of the remote reads, rebuilt locally: below and above the own range
-            const uint32_t pr[2][2] = {{0u, c->e_lo / 2}, {c->e_hi / 2, M / 2}};
-            for (int i = 0; i < 2; ++i)
-                if (pr[i][1] > pr[i][0]) {
-                    k1_expand<<<pr[i][1] - pr[i][0], 128, 0, c->st_comm>>>(
-                        c->d_fwd.as<uint4>(), c->d_gran0.as<uint32_t>(), c->d_len.as<uint32_t>(),
-                        c->d_packed.as<uint32_t>(), pr[i][0], pr[i][1]);
-                    ++launches;
-                }
-            CK(cudaGetLastError());
-        } else {
-            CKN(N.GroupStart());
-            for (int r = 0; r < c->nranks; ++r) {
-                const uint32_t a = c->gran0[c->rank_e[r]], b = c->gran0[c->rank_e[r + 1]];
-                if (b > a) {
-                    uint4* p = c->d_packed.as<uint4>() + a;
-                    CKN(N.Broadcast(p, p, (size_t)(b - a) * 16, ncclUint8, r, c->comm, c->st_comm));
-                }
-            }
-            CKN(N.GroupEnd());
-        }
-        CK(cudaEventRecord(c->ev_dbg[2], c->st_comm));
-        CK(cudaEventRecord(c->ev_comm, c->st_comm));
-        wait_packed = true;
-    }
-    CK(cudaEventRecord(c->ev[E_ANCHOR0], st));
-
-    auto stage_times = [&]() {
-        S.launches = launches;
-        S.lib_launches = lib;
-        S.ms_pack = ev_ms(c, E_PACK0, E_ANCHOR0);
-        S.ms_anchor = ev_ms(c, E_ANCHOR0, E_SCAN0);
-        S.ms_scan = ev_ms(c, E_SCAN0, E_VERIFY0);
-        S.ms_verify = ev_ms(c, E_VERIFY0, E_SORT0);
-        S.ms_sort = ev_ms(c, E_SORT0, E_EMIT0);
-        S.ms_emit = ev_ms(c, E_EMIT0, E_END);
-        S.ms_device = ev_ms(c, E_PACK0, E_END);
-    };
-    auto check_alphabet = [&]() -> int {
-        if (c->h_ctr[C_ERR]) {
-            const uint32_t e = (uint32_t)c->h_ctr[C_ERR] - 1;
-            return fail(c, OVL_E_ALPHABET, "entry %u ('%.*s') holds a byte outside upper-case ACGT", e,
-                        (int)(c->id_off[e + 1] - c->id_off[e]), c->id_blob.data() + c->id_off[e]);
-        }
-        return OVL_OK;
-    };
-    // record the remaining stage events from `from` on, wait, fill the stage times
-    auto finish_from = [&](int from) -> int {
-        if (wait_packed) CK(cudaStreamWaitEvent(st, c->ev_comm, 0));  // never leave the replication in flight
-        CK(cudaStreamWaitEvent(st, k2_last, 0));                      // ... nor the anchor-build stream
-        for (int e = from; e <= E_END; ++e) CK(cudaEventRecord(c->ev[e], st));
-        OVL_TRY(read_ctr(c));
-        OVL_TRY(check_alphabet());
-        stage_times();
-        return OVL_OK;
-    };
-    if (n_anc == 0) return finish_from(E_SCAN0);  // same decision on every rank
-    // multi-GPU + mirror: hits are exchanged between ranks, so a rank without own work must
-    // still walk through the collective
-    const bool xchg = mirror && c->nranks > 1;
-    const bool have_a = g_hi > g_lo;
-    if (!have_a && !xchg) return finish_from(E_SCAN0);
-
-    // ---- K2: anchor table ---------------------------------------------------------------------
-    const uint64_t n_keys = n_anc << slog;
-    const int tbits = ceil_log2(2 * n_keys) < 6 ? 6 : ceil_log2(2 * n_keys);
-    if (tbits > 31) return fail(c, OVL_E_LIMIT, "anchor table of 2^%d slots is over the layout limit", tbits);
-    const bool smem_filter = dense && n_anc <= (1u << 17);
-    int bm_bits;  // dense: log2 words of the blocked bloom filter; sparse: log2 bits of the bitmap
-    if (dense) {
-        bm_bits = smem_filter ? ceil_log2(n_anc) : ceil_log2(2 * n_anc);
-        if (bm_bits < 5) bm_bits = 5;
-        if (smem_filter && bm_bits > 15) bm_bits = 15;
-        if (bm_bits > 27) bm_bits = 27;
-    } else {
-        bm_bits = ceil_log2(32 * n_keys);
-        if (bm_bits < 15) bm_bits = 15;
-        if (bm_bits > 31) bm_bits = 31;
-    }
-    if (have_a) {
-        const size_t filter_bytes = dense ? (4ull << bm_bits) : ((1ull << bm_bits) / 8);
-        const size_t table_bytes = sizeof(Slot) * (1ull << tbits);
-        OVL_TRY(dev_ensure(c, c->d_table, table_bytes));
-        OVL_TRY(dev_ensure(c, c->d_filter, filter_bytes));
-        OVL_TRY(dev_ensure(c, c->d_next, ((uint64_t)M << slog) * 4));
-        CK(cudaMemsetAsync(c->d_table.p, 0xff, table_bytes, sk));  // EMPTY_SLOT
-        CK(cudaMemsetAsync(c->d_filter.p, 0, filter_bytes, sk));
-        {
-            AnchorParams A;
-            A.pre64 = reinterpret_cast<const uint64_t*>(c->d_pre.p);
-            A.ent = c->d_ent.as<uint2>();
-            A.M = M;
-            A.l = l;
-            A.k = k;
-            A.stride_log2 = slog;
-            A.table = c->d_table.as<Slot>();
-            A.tbits = tbits;
-            A.next = c->d_next.as<uint32_t>();
-            A.bitmap = c->d_filter.as<uint32_t>();
-            A.bm_bits = bm_bits;
-            A.dense = dense ? 1 : 0;
-            A.n_anchors = reinterpret_cast<unsigned long long*>(ctr + C_NANC);
-            const uint64_t nthreads = (uint64_t)M << slog;
-            k2_insert<<<(unsigned)((nthreads + 255) / 256), 256, 0, sk>>>(A);
-            ++launches;
-            CK(cudaGetLastError());
-        }
-        // ---- join: the scan needs the table ------------------------------------------------------
-        CK(cudaEventRecord(c->ev_k2, sk));
-        k2_last = c->ev_k2;
-        CK(cudaStreamWaitEvent(st, c->ev_k2, 0));
-        CK(cudaEventRecord(c->ev[E_SCAN0], st));
-
-    } else {
-        CK(cudaStreamWaitEvent(st, k2_last, 0));
-        CK(cudaEventRecord(c->ev[E_SCAN0], st));
-    }
-
-    // ---- K3 .. K5 without host round trips ---------------------------------------------------
-    // Every buffer is sized by CAPACITY and every kernel reads its input size from the device
-    // counter block, so a single-GPU pass synchronises with the host once, at its end.  Only the
-    // accounting / serial-verifier modes and the multi-GPU hit exchange (NCCL needs the counts)
-    // read counters in between.  A candidate overflow is detected at the end: the buffers grow and
-    // the pass from K3 on is repeated.
-    const bool host_n = c->collect || c->opt_serial_verify || xchg;
-    if (c->cand_cap == 0) {
-        uint64_t cap = 96ull * (c->e_hi - c->e_lo);
-        if (cap < (1ull << 20)) cap = 1ull << 20;
-        c->cand_cap = cap;
-    }
-    uint64_t n_cand = 0, n_hits = 0, n_rows = 0, hit_cap = 0;
-    const uint32_t kblocks = (uint32_t)nsm * 8;
-    for (int attempt = 0;; ++attempt) {
-        if (c->cand_cap > 0x7fffffffull) return fail(c, OVL_E_LIMIT, "more than 2^31 candidates on one GPU");
-        hit_cap = mirror ? 3 * c->cand_cap : c->cand_cap;  // own key + SP twin + CONT twin
-        OVL_TRY(dev_ensure(c, c->d_cand, hit_cap * 8, false));   // candidates, later the sorted hit keys
-        OVL_TRY(dev_ensure(c, c->d_cand2, hit_cap * 8, false));  // hit keys
-        OVL_TRY(dev_ensure(c, c->d_cnt, c->cand_cap * 4, false));  // survivor list
-        OVL_TRY(dev_ensure(c, c->d_rows, hit_cap * sizeof(Row), false));
-        if (attempt) CK(cudaMemsetAsync(ctr + C_NCAND, 0, (C_COUNT - C_NCAND) * sizeof(uint64_t), st));
-        if (have_a) {
-            ScanParams P;
-            P.packed = c->d_packed.as<uint4>();
-            P.gran_ent = c->d_gran_ent.as<uint32_t>();
-            P.ent = c->d_ent.as<uint2>();
-            P.g_begin = g_lo;
-            P.g_end = g_hi;
-            P.l = l;
-            P.k = k;
-            P.stride_log2 = slog;
-            P.filter = c->d_filter.as<uint32_t>();
-            P.bm_bits = bm_bits;
-            P.table = c->d_table.as<Slot>();
-            P.tbits = tbits;
-            P.next = c->d_next.as<uint32_t>();
-            P.fmt = fmt;
-            P.sink.out = c->d_cand.as<uint64_t>();
-            P.sink.n_out = reinterpret_cast<unsigned long long*>(ctr + C_NCAND);
-            P.sink.cap = c->cand_cap;
-            P.mirror = mrule;
-            if (!dense) {
-                const uint32_t tiles = (g_hi - g_lo + 31) / 32;
-                uint32_t blocks = (tiles + 7) / 8;
-                if (blocks > (uint32_t)nsm * 8) blocks = (uint32_t)nsm * 8;
-                switch (slog) {
-                    case 6: k3_probe<6><<<blocks, 256, 0, st>>>(P); break;
-                    case 5: k3_probe<5><<<blocks, 256, 0, st>>>(P); break;
-                    case 4: k3_probe<4><<<blocks, 256, 0, st>>>(P); break;
-                    case 3: k3_probe<3><<<blocks, 256, 0, st>>>(P); break;
-                    default: k3_probe<-1><<<blocks, 256, 0, st>>>(P); break;
-                }
-            } else if (smem_filter) {
-                k3_scan<true><<<nsm, 1024, 32 * WBUF * 8 + (4u << bm_bits), st>>>(P);
-            } else {
-                k3_scan<false><<<nsm, 1024, 32 * WBUF * 8, st>>>(P);
-            }
-            ++launches;
-            CK(cudaGetLastError());
-        }
-        if (host_n) {
-            OVL_TRY(read_ctr(c));
-            OVL_TRY(check_alphabet());
-            n_cand = c->h_ctr[C_NCAND];
-            if (n_cand > c->cand_cap) {
-                if (attempt >= 2) return fail(c, OVL_E_LIMIT, "candidate buffer overflow persists (%llu)", (unsigned long long)n_cand);
-                ++S.retries;
-                c->cand_cap = n_cand + n_cand / 16;
-                continue;
-            }
-        }
-
-        // ---- K4: verify -------------------------------------------------------------------
-        CK(cudaEventRecord(c->ev[E_VERIFY0], st));
-        if (wait_packed) CK(cudaStreamWaitEvent(st, c->ev_comm, 0));  // the operands of other ranks' entries
-        CandSink hits;
-        hits.out = c->d_cand2.as<uint64_t>();
-        hits.n_out = reinterpret_cast<unsigned long long*>(ctr + C_NHITS);
-        hits.cap = hit_cap;
-        if (c->collect || c->opt_serial_verify) {
-            if (n_cand) {
-                VerifyParams V;
-                V.keys = c->d_cand.as<uint64_t>();
-                V.n = n_cand;
-                V.packed = c->d_packed.as<uint4>();
-                V.ent = c->d_ent.as<uint2>();
-                V.fmt = fmt;
-                V.hits = hits;
-                V.counters = reinterpret_cast<unsigned long long*>(ctr + C_SUMM);
-                V.collect = c->collect;
-                V.mirror = mrule;
-                uint64_t blocks = (n_cand + 255) / 256;
-                if (blocks > kblocks) blocks = kblocks;
-                k4_verify_serial<<<(unsigned)blocks, 256, 0, st>>>(V);
-                ++launches;
-            }
-        } else {
-            Verify2Params V;
-            V.keys = c->d_cand.as<uint64_t>();
-            V.n_ptr = reinterpret_cast<const unsigned long long*>(ctr + C_NCAND);
-            V.cap = c->cand_cap;
-            V.packed64 = reinterpret_cast<const uint64_t*>(c->d_packed.p);
-            V.ent = c->d_ent.as<uint2>();
-            V.fmt = fmt;
-            V.surv = c->d_cnt.as<uint32_t>();
-            V.n_surv = reinterpret_cast<unsigned long long*>(ctr + C_NSURV);
-            V.hits = hits;
-            V.mirror = mrule;
-            V.tile_ctr = reinterpret_cast<unsigned long long*>(ctr + C_TILE_A);
-            k4a_head<<<kblocks, 256, 0, st>>>(V);
-            k4b_tail<<<kblocks, 256, 0, st>>>(V);
-            launches += 2;
-        }
-        CK(cudaGetLastError());
-        CK(cudaEventRecord(c->ev[E_SORT0], st));
-        uint64_t keys_cap = hit_cap;  // capacity of d_cand2 in keys, as the bucket kernels see it
-        if (host_n) {
-            OVL_TRY(read_ctr(c));
-            n_hits = c->h_ctr[C_NHITS];
-            S.compared_bases = c->h_ctr[C_SUMM];
-            S.operand_bytes = c->h_ctr[C_SUMB];
-            if (n_hits > hit_cap) return fail(c, OVL_E_LIMIT, "hit list overflow (%llu > %llu): internal error", (unsigned long long)n_hits, (unsigned long long)hit_cap);
-            // multi-GPU mirror mode: every hit key goes to the rank that owns its A entry
-            if (xchg) {
-                OVL_TRY(exchange_hits(c, fmt, &n_hits, &launches, &lib));
-                if (n_hits > 0xfffffff0ull) return fail(c, OVL_E_LIMIT, "more than 2^32 hit keys on one GPU");
-                c->h_ctr[C_NHITS] = n_hits;
-                CK(cudaMemcpyAsync(ctr + C_NHITS, &c->h_ctr[C_NHITS], 8, cudaMemcpyHostToDevice, st));
-                keys_cap = c->d_cand2.cap / 8;
-                OVL_TRY(dev_ensure(c, c->d_cand, n_hits * 8, false));
-                OVL_TRY(dev_ensure(c, c->d_rows, n_hits * sizeof(Row), false));
-            }
-        }
-
-        // ---- order the hit keys by (a, b, p, flags) and emit rows: k7_bucket.cuh ------------------
-        const size_t M1 = (size_t)M + 1;
-        OVL_TRY(dev_ensure(c, c->d_bkt, M1 * (8 + 8 + 4 + 4 + 4)));
-        uint64_t* b_off = c->d_bkt.as<uint64_t>();
-        uint64_t* b_rowoff = b_off + M1;
-        uint32_t* b_cnt = reinterpret_cast<uint32_t*>(b_rowoff + M1);
-        uint32_t* b_cur = b_cnt + M1;
-        uint32_t* b_rowcnt = b_cur + M1;
-        size_t tb = 0;
-        CK(cub::DeviceScan::ExclusiveSum(nullptr, tb, b_cnt, b_off, (int)M1, st));
-        OVL_TRY(dev_ensure(c, c->d_tmp, tb));
-        BucketParams B;
-        B.hits = c->d_cand2.as<uint64_t>();
-        B.n_ptr = reinterpret_cast<const unsigned long long*>(ctr + C_NHITS);
-        B.cap = keys_cap;
-        B.fmt = fmt;
-        B.M = M;
-        B.cnt = b_cnt;
-        B.off = b_off;
-        B.cur = b_cur;
-        B.sorted = c->d_cand.as<uint64_t>();
-        B.rowcnt = b_rowcnt;
-        B.rowoff = b_rowoff;
-        B.big = reinterpret_cast<unsigned long long*>(ctr + C_BIG);
-        B.ent = c->d_ent.as<uint2>();
-        B.rows = c->d_rows.as<Row>();
-        B.rows_cap = c->d_rows.cap / sizeof(Row);
-        uint32_t wblocks = (M + 7) / 8;
-        if (wblocks > (uint32_t)nsm * 16) wblocks = (uint32_t)nsm * 16;
-        CK(cudaMemsetAsync(b_cnt, 0, M1 * 12, st));  // cnt, cur, rowcnt
-        k7_hist<<<kblocks, 256, 0, st>>>(B);
-        tb = c->d_tmp.cap;
-        CK(cub::DeviceScan::ExclusiveSum(c->d_tmp.p, tb, b_cnt, b_off, (int)M1, st));
-        k7_scatter<<<kblocks, 256, 0, st>>>(B);
-        k7_sort<<<wblocks, 256, 0, st>>>(B);
-        CK(cudaEventRecord(c->ev[E_EMIT0], st));
-        tb = c->d_tmp.cap;
-        CK(cub::DeviceScan::ExclusiveSum(c->d_tmp.p, tb, b_rowcnt, b_rowoff, (int)M1, st));
-        k7_emit<<<wblocks, 256, 0, st>>>(B);
-        launches += 4;
-        lib += 2;
-        CK(cudaGetLastError());
-        CK(cudaMemcpyAsync(&c->h_ctr[C_COUNT], b_rowoff + M, 8, cudaMemcpyDeviceToHost, st));
-        CK(cudaEventRecord(c->ev[E_END], st));
-        OVL_TRY(read_ctr(c));  // the one synchronisation of a single-GPU pass
-        OVL_TRY(check_alphabet());
-        if (!host_n) {
-            n_cand = c->h_ctr[C_NCAND];
-            if (n_cand > c->cand_cap) {
-                if (attempt >= 2) return fail(c, OVL_E_LIMIT, "candidate buffer overflow persists (%llu)", (unsigned long long)n_cand);
-                ++S.retries;
-                c->cand_cap = n_cand + n_cand / 16;
-                continue;
-            }
-            n_hits = c->h_ctr[C_NHITS];
-            if (n_hits > hit_cap) return fail(c, OVL_E_LIMIT, "hit list overflow (%llu > %llu): internal error", (unsigned long long)n_hits, (unsigned long long)hit_cap);
-        }
-        n_rows = c->h_ctr[C_COUNT];
-        break;
-    }
-    S.candidates = n_cand;
-    S.verified = n_cand;
-    S.hits = n_hits;
-
-    // ---- an A entry with more than BUCKET_MAX hits: redo the ordering with the device-wide radix
-    //      sort (library call) and the per-key K5 kernels ------------------------------------------
-    if (c->h_ctr[C_BIG] && n_hits) {
-        S.radix_fallback = 1;
-        uint64_t* keys = c->d_cand.as<uint64_t>();
-        size_t tb = 0;
-        CK(cub::DeviceRadixSort::SortKeys(nullptr, tb, c->d_cand2.as<uint64_t>(), keys, (int)n_hits, 0, fmt.total(), st));
-        OVL_TRY(dev_ensure(c, c->d_tmp, tb));
-        tb = c->d_tmp.cap;
-        CK(cub::DeviceRadixSort::SortKeys(c->d_tmp.p, tb, c->d_cand2.as<uint64_t>(), keys, (int)n_hits, 0, fmt.total(), st));
-        ++lib;
-        OVL_TRY(dev_ensure(c, c->d_cnt, n_hits * 4));
-        OVL_TRY(dev_ensure(c, c->d_offs, (n_hits + 1) * 8));
-        const unsigned nb = (unsigned)((n_hits + 255) / 256);
-        k5_count<<<nb, 256, 0, st>>>(keys, n_hits, fmt, c->d_cnt.as<uint32_t>());
-        ++launches;
-        tb = 0;
-        CK(cub::DeviceScan::ExclusiveSum(nullptr, tb, c->d_cnt.as<uint32_t>(), c->d_offs.as<uint64_t>(), (int)n_hits, st));
-        OVL_TRY(dev_ensure(c, c->d_tmp, tb));
-        tb = c->d_tmp.cap;
-        CK(cub::DeviceScan::ExclusiveSum(c->d_tmp.p, tb, c->d_cnt.as<uint32_t>(), c->d_offs.as<uint64_t>(), (int)n_hits, st));
-        ++lib;
-        CK(cudaMemcpyAsync(&c->h_ctr[C_COUNT], c->d_offs.as<uint64_t>() + (n_hits - 1), 8, cudaMemcpyDeviceToHost, st));
-        CK(cudaMemcpyAsync(&c->h_ctr[C_COUNT + 1], c->d_cnt.as<uint32_t>() + (n_hits - 1), 4, cudaMemcpyDeviceToHost, st));
-        CK(cudaStreamSynchronize(st));
-        n_rows = c->h_ctr[C_COUNT] + (c->h_ctr[C_COUNT + 1] & 0xffffffffull);
-        if (n_rows) {
-            OVL_TRY(dev_ensure(c, c->d_rows, n_rows * sizeof(Row)));
-            k5_emit<<<nb, 256, 0, st>>>(keys, n_hits, fmt, c->d_offs.as<uint64_t>(), c->d_cnt.as<uint32_t>(),
-                                        c->d_ent.as<uint2>(), c->d_rows.as<Row>());
-            ++launches;
-            CK(cudaGetLastError());
-        }
-        CK(cudaEventRecord(c->ev[E_END], st));
-        CK(cudaStreamSynchronize(st));
-    }
-    c->n_rows = n_rows;
-    S.rows = n_rows;
-    stage_times();
-    if (wait_packed && getenv("OVL_DEBUG")) {
-        float t_pk = 0, t_bc = 0, t_ex = 0, t_v = 0;
-        cudaEventElapsedTime(&t_pk, c->ev[E_PACK0], c->ev_dbg[0]);
-        if (fwd_x) cudaEventElapsedTime(&t_bc, c->ev_dbg[0], c->ev_dbg[1]);
-        cudaEventElapsedTime(&t_ex, fwd_x ? c->ev_dbg[1] : c->ev_dbg[0], c->ev_dbg[2]);
-        cudaEventElapsedTime(&t_v, c->ev[E_PACK0], c->ev[E_VERIFY0]);
-        (void)cudaGetLastError();
-        fprintf(stderr, "[ovl rank %d] comm stream: starts +%.3f ms, broadcast %.3f ms, %s %.3f ms; verify stage starts +%.3f ms\n",
-                c->rank, t_pk, t_bc, fwd_x ? "expand" : "replicate", t_ex, t_v);
-    }
-    if (n_rows_out) *n_rows_out = n_rows;
+    if (c->tables_dirty || !c->ascii_resident) return fail(c, OVL_E_ARG, "ovl_overlaps_device: call ovl_upload first");
+    OVL_TRY(run_pass(c, min_length, false));
+    if (n_rows_out) *n_rows_out = c->n_rows;
     return OVL_OK;
 }
 
@@ -1239,13 +1593,28 @@ int ovl_overlaps(ovl_ctx* c, uint32_t min_length, const ovl_row** rows, uint64_t
     if (!c || !rows || !n_rows) return OVL_E_ARG;
     *rows = nullptr;
     *n_rows = 0;
-    // host buffers in: the entry store is re-sent on every call, like the reference rebuilds
-    // its index on every call (src/overlapper.cpp:33-36)
-    OVL_TRY(ovl_upload(c));
-    uint64_t n = 0;
-    OVL_TRY(ovl_overlaps_device(c, min_length, &n));
+    OVL_TRY(set_dev(c));
+    // host buffers in: the records are re-sent on every call, in pieces, and packed under the copy
+    OVL_TRY(upload_tables(c));
+    OVL_TRY(run_pass(c, min_length, true));
     OVL_TRY(ovl_fetch_rows(c, rows, n_rows));
-    c->stats.ms_total = c->stats.ms_h2d + c->stats.ms_device + c->stats.ms_d2h;
+    c->stats.ms_total = c->stats.ms_h2d + c->stats.ms_exposed + c->stats.ms_d2h;
+    return OVL_OK;
+}
+
+// Multi-GPU form of ovl_overlaps for a consumer that stays sharded: host buffers in on every rank
+// (chunked upload under the pack kernel), the pass (rows of all ranks also land in rank 0's HBM),
+// then every rank brings ITS OWN rows to its host over its own PCIe link.  Concatenating the
+// ranks' arrays in rank order gives the canonical row order.
+int ovl_overlaps_local(ovl_ctx* c, uint32_t min_length, const ovl_row** rows, uint64_t* n_rows) {
+    if (!c || !rows || !n_rows) return OVL_E_ARG;
+    *rows = nullptr;
+    *n_rows = 0;
+    OVL_TRY(set_dev(c));
+    OVL_TRY(upload_tables(c));
+    OVL_TRY(run_pass(c, min_length, true));
+    OVL_TRY(ovl_fetch_local_rows(c, rows, n_rows));
+    c->stats.ms_total = c->stats.ms_h2d + c->stats.ms_exposed + c->stats.ms_d2h;
     return OVL_OK;
 }
 
@@ -1263,8 +1632,10 @@ int ovl_comm_unique_id(uint8_t id_out[128]) {
 
 int ovl_comm_init(ovl_ctx* c, const uint8_t id[128], int rank, int nranks) {
     if (!c || !id || nranks < 1 || rank < 0 || rank >= nranks) return fail(c, OVL_E_ARG, "ovl_comm_init: bad argument");
+    if (nranks > ovl::MAX_RANKS) return fail(c, OVL_E_LIMIT, "more than %d ranks", ovl::MAX_RANKS);
     OVL_TRY(set_dev(c));
     if (!nccl_dyn::load()) return fail(c, OVL_E_NCCL, "cannot load libnccl: %s", nccl_dyn::load_error());
+    close_peers(c);
     if (c->comm) {
         nccl_dyn::api().CommDestroy(c->comm);
         c->comm = nullptr;
@@ -1274,7 +1645,8 @@ int ovl_comm_init(ovl_ctx* c, const uint8_t id[128], int rank, int nranks) {
     CKN(nccl_dyn::api().CommInitRank(&c->comm, nranks, uid, rank));
     c->rank = rank;
     c->nranks = nranks;
-    c->uploaded = false;
+    c->tables_dirty = true;
+    c->arena_key[0] = ~0ull;
     return OVL_OK;
 }
 
@@ -1288,16 +1660,10 @@ int ovl_comm_sync_ranges(ovl_ctx* c) {
         c->rank_e[1] = M;
         return OVL_OK;
     }
-    if (!c->uploaded) return fail(c, OVL_E_ARG, "ovl_comm_sync_ranges: call ovl_upload first");
-    auto& N = nccl_dyn::api();
-    OVL_TRY(dev_ensure(c, c->d_tmp, 8ull * (c->nranks + 1)));
+    if (c->tables_dirty) return fail(c, OVL_E_ARG, "ovl_comm_sync_ranges: call ovl_upload first");
     uint32_t mine[2] = {c->e_lo, c->e_hi};
-    uint32_t* d = c->d_tmp.as<uint32_t>();
-    CK(cudaMemcpyAsync(d + 2 * c->rank, mine, 8, cudaMemcpyHostToDevice, c->st));
-    CKN(N.AllGather(d + 2 * c->rank, d, 2, ncclUint32, c->comm, c->st));
     std::vector<uint32_t> all(2 * (size_t)c->nranks);
-    CK(cudaMemcpyAsync(all.data(), d, 8ull * c->nranks, cudaMemcpyDeviceToHost, c->st));
-    CK(cudaStreamSynchronize(c->st));
+    OVL_TRY(allgather_host(c, mine, 8, all.data()));
     uint32_t pos = 0;
     for (int r = 0; r < c->nranks; ++r) {
         uint32_t lo = all[2 * r], hi = all[2 * r + 1];
@@ -1308,104 +1674,55 @@ int ovl_comm_sync_ranges(ovl_ctx* c) {
     }
     if (pos != M) return fail(c, OVL_E_ARG, "ranks cover %u of %u entries", pos, M);
     c->rank_e[c->nranks] = M;
+    c->arena_key[0] = ~0ull;  // (re)connect at the next pass
     return OVL_OK;
 }
 
-// Gather every rank's rows into rank 0's HBM (rank order == canonical order); rows stay on the
-// device.  Idempotent per ovl_overlaps_device call.
+// The rows of every rank are gathered into rank 0's HBM (rank order == canonical order) inside
+// the pass itself; this call only reports.  Kept for callers of the round-1 interface.
 int ovl_comm_gather_rows_device(ovl_ctx* c, uint64_t* n_rows) {
     if (!c) return OVL_E_ARG;
-    OVL_TRY(set_dev(c));
-    if (n_rows) *n_rows = 0;
-    if (c->nranks == 1 || c->gathered) {
-        if (n_rows) *n_rows = c->n_rows;
-        return OVL_OK;
-    }
-    auto& N = nccl_dyn::api();
-    const int R = c->nranks;
-    // counts
-    OVL_TRY(dev_ensure(c, c->d_cnts, 8ull * R));
-    uint64_t* d = c->d_cnts.as<uint64_t>();
-    c->h_ctr[C_COUNT] = c->n_rows;
-    CK(cudaMemcpyAsync(d + c->rank, &c->h_ctr[C_COUNT], 8, cudaMemcpyHostToDevice, c->st));
-    CKN(N.AllGather(d + c->rank, d, 1, ncclUint64, c->comm, c->st));
-    std::vector<uint64_t> cnt(R);
-    CK(cudaMemcpyAsync(cnt.data(), d, 8ull * R, cudaMemcpyDeviceToHost, c->st));
-    CK(cudaStreamSynchronize(c->st));
-    uint64_t total = 0;
-    for (int r = 0; r < R; ++r) total += cnt[r];
-    uint64_t maxc = 0;
-    for (int r = 0; r < R; ++r) maxc = cnt[r] > maxc ? cnt[r] : maxc;
-    // Rows travel by ONE in-place all-gather of equal, padded slots (a collective uses every NCCL
-    // channel; the grouped point-to-point receives it replaces reached ~40 GB/s per peer, 1.1 ms for
-    // the 32 MB of a 2-rank run).  Above 8 GB of slots fall back to point-to-point.
-    const bool by_allgather = maxc > 0 && (uint64_t)R * maxc * sizeof(ovl_row) <= (8ull << 30);
-    if (by_allgather) {
-        OVL_TRY(dev_ensure(c, c->d_gath, (size_t)R * maxc * sizeof(ovl_row)));
-        ovl_row* G = c->d_gath.as<ovl_row>();
-        if (c->n_rows) CK(cudaMemcpyAsync(G + (size_t)c->rank * maxc, c->d_rows.p, c->n_rows * sizeof(ovl_row), cudaMemcpyDeviceToDevice, c->st));
-        CKN(N.AllGather(G + (size_t)c->rank * maxc, G, (size_t)maxc * sizeof(ovl_row), ncclUint8, c->comm, c->st));
-    }
-    if (c->rank == 0) {
-        // grow d_rows to hold everything, keeping the local rows at the front
-        if (total * sizeof(ovl_row) > c->d_rows.cap) {
-            DevBuf nb;
-            OVL_TRY(dev_ensure(c, nb, total * sizeof(ovl_row)));
-            if (c->n_rows) CK(cudaMemcpyAsync(nb.p, c->d_rows.p, c->n_rows * sizeof(ovl_row), cudaMemcpyDeviceToDevice, c->st));
-            CK(cudaStreamSynchronize(c->st));
-            if (c->d_rows.p) CK(cudaFree(c->d_rows.p));
-            c->d_rows = nb;
-        }
-        uint64_t off = cnt[0];
-        if (by_allgather) {
-            const ovl_row* G = c->d_gath.as<ovl_row>();
-            for (int r = 1; r < R; ++r) {
-                if (cnt[r]) CK(cudaMemcpyAsync(c->d_rows.as<ovl_row>() + off, G + (size_t)r * maxc, cnt[r] * sizeof(ovl_row), cudaMemcpyDeviceToDevice, c->st));
-                off += cnt[r];
-            }
-        } else {
-            CKN(N.GroupStart());
-            for (int r = 1; r < R; ++r) {
-                if (cnt[r]) CKN(N.Recv(c->d_rows.as<ovl_row>() + off, cnt[r] * sizeof(ovl_row), ncclUint8, r, c->comm, c->st));
-                off += cnt[r];
-            }
-            CKN(N.GroupEnd());
-        }
-        c->n_rows = total;
-        c->stats.rows = total;
-    } else {
-        if (c->n_rows && !by_allgather) {
-            CKN(N.GroupStart());
-            CKN(N.Send(c->d_rows.p, c->n_rows * sizeof(ovl_row), ncclUint8, 0, c->comm, c->st));
-            CKN(N.GroupEnd());
-        }
-        c->n_rows = 0;
-    }
-    CK(cudaStreamSynchronize(c->st));
-    c->rows_fetched = false;
-    c->gathered = true;
     if (n_rows) *n_rows = c->n_rows;
     return OVL_OK;
 }
 
 int ovl_comm_gather_rows(ovl_ctx* c, const ovl_row** rows, uint64_t* n_rows) {
     if (!c || !rows || !n_rows) return OVL_E_ARG;
-    *rows = nullptr;
-    *n_rows = 0;
-    OVL_TRY(ovl_comm_gather_rows_device(c, nullptr));
     return ovl_fetch_rows(c, rows, n_rows);
+}
+
+// This rank's own rows of the last pass (rank 0: the first rows_local rows of the gathered array;
+// other ranks: their row array), device -> pinned host.  Lets every rank of a multi-GPU job bring
+// its share to its host over its own PCIe link.
+int ovl_fetch_local_rows(ovl_ctx* c, const ovl_row** rows, uint64_t* n_rows) {
+    if (!c || !rows || !n_rows) return OVL_E_ARG;
+    OVL_TRY(set_dev(c));
+    *rows = nullptr;
+    const uint64_t n = c->stats.rows_local;
+    *n_rows = n;
+    if (!n) return OVL_OK;
+    const size_t bytes = n * sizeof(ovl_row);
+    OVL_TRY(pin_ensure(c, c->h_rows, bytes, 0));
+    CK(cudaEventRecord(c->ev[E_D2H0], c->st));
+    CK(cudaMemcpyAsync(c->h_rows.p, c->d_rows.p, bytes, cudaMemcpyDeviceToHost, c->st));
+    CK(cudaEventRecord(c->ev[E_D2H1], c->st));
+    CK(cudaStreamSynchronize(c->st));
+    c->stats.ms_d2h = ev_ms(c, E_D2H0, E_D2H1);
+    c->rows_fetched = false;  // h_rows now holds the local share only
+    *rows = reinterpret_cast<const ovl_row*>(c->h_rows.p);
+    return OVL_OK;
 }
 
 // -----------------------------------------------------------------------------------------
 int ovl_debug_packed(ovl_ctx* c, uint32_t idx, uint8_t* out, size_t out_cap, size_t* out_len) {
     if (!c || !out_len || idx >= c->len.size()) return fail(c, OVL_E_ARG, "ovl_debug_packed: bad argument");
     OVL_TRY(set_dev(c));
-    if (!c->uploaded || c->gran0.size() != c->len.size() + 1) return fail(c, OVL_E_ARG, "ovl_debug_packed: nothing packed yet");
-    const size_t bytes = (size_t)(c->gran0[idx + 1] - c->gran0[idx]) * 16;
+    if (c->tables_dirty || !c->arena.p || c->gran0.size() != c->len.size()) return fail(c, OVL_E_ARG, "ovl_debug_packed: nothing packed yet");
+    const size_t bytes = (size_t)((c->len[idx] + 63u) / 64u) * 16;
     *out_len = bytes;
     if (!bytes) return OVL_OK;
     if (!out || out_cap < bytes) return fail(c, OVL_E_ARG, "ovl_debug_packed: buffer too small (%zu needed)", bytes);
-    CK(cudaMemcpy(out, c->d_packed.as<uint8_t>() + (size_t)c->gran0[idx] * 16, bytes, cudaMemcpyDeviceToHost));
+    CK(cudaMemcpy(out, c->arena.as<uint8_t>() + c->lay.off_packed + (size_t)c->gran0[idx] * 16, bytes, cudaMemcpyDeviceToHost));
     return OVL_OK;
 }
 

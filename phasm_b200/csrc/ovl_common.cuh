@@ -1,26 +1,28 @@
 // ovl_common.cuh -- device layout and small helpers shared by the overlapper kernels.
 //
-// HBM layout (all arrays live for the duration of one ovl_overlaps* call, cached in the ctx):
+// HBM layout (persistent tables live outside, per-pass working data inside the ARENA, which on
+// N > 1 GPUs is the peer-mapped allocation the other ranks push into; ovl.cu):
 //
 //   ascii     u8     staged sequence bytes, every record 16-byte aligned, 16 B slack at both
 //                    ends
 //   packed    uint4  one 16-byte GRANULE = 64 bases, 2 bits/base, base j of a granule in bits
 //                    [2j, 2j+2) of the granule's 128-bit little-endian value; every entry
-//                    starts on a granule boundary and is zero padded to it; TWO extra zero
-//                    granules terminate the array (the verifier reads one granule past an
-//                    entry's end).  code = (ascii >> 1) & 3  (A0 C1 T2 G3), so
-//                    complement = code ^ 2.
-//   gran_ent  u32    entry index of every granule
+//                    starts on a granule boundary and is zero padded to it.
+//                    code = (ascii >> 1) & 3  (A0 C1 T2 G3), so complement = code ^ 2.
+//                    TWO REGIONS: [0, G_f) holds every entry that is not a reverse-complement
+//                    twin, in entry order (the "forward region": on N GPUs a rank's slice of it
+//                    is what travels over NVLink, straight into the peers' arrays), [G_f, G)
+//                    holds the twins in entry order; two spare granules follow (the verifier
+//                    reads one granule past an entry's end).
 //   ent       uint2  [M]   {first granule, length in bases} of every entry
-//   gran0     u32    [M+1] first granule of every entry (prefix sum of ceil(len/64))
+//   reg       uint4  [M+1] the entries in REGION order (= granule order): {first granule,
+//                    entry, length, granules}; reg[M] = {G, 0, 0, 0} is the sentinel
 //   len       u32    [M]   entry lengths in bases
 //   src       u64    [M]   byte offset of the entry's source record in `ascii`
 //   flags     u8     [M]   bit0: entry is the reverse complement of its source record (it then
 //                          directly follows the forward entry of the same record)
 //
-// Candidate / hit key (64 bit): [a | b | p | sp | cont], most significant first.  K3 emits keys
-// with both flag bits clear, a radix sort orders them by (a, b, p), K4 sets the flag bits of the
-// candidates that verify, K5 turns flagged keys into rows.
+// Candidate / hit key (64 bit): [a | b | p | sp | cont], most significant first.
 //
 // Reference semantics restated by these kernels: /root/reference/src/overlapper.cpp:28-150
 // (see SURVEY.md 3.3 for the normative R1/R2 statement).
@@ -32,20 +34,40 @@ namespace ovl {
 
 constexpr int GRAN_BASES = 64;
 constexpr unsigned FULL = 0xffffffffu;
+constexpr int MAX_RANKS = 16;  // GPUs of one box (kernel parameter blocks carry per-rank pointer tables)
 
-// Anchor hash-table slot: one 64-bit word {fingerprint (high 32) | head (low 32)}.  The
-// fingerprint is the low half of the k-mer's 64-bit hash (the slot index comes from the high
-// bits), head starts a linked list (through `next`) of anchor ids  b * stride + delta.  Two
-// different k-mers that collide on slot AND fingerprint (~2^-32 per probe) share a list: the scan
-// then emits a few false candidates, which the verifier rejects -- the table only has to return
-// a superset.  8-byte slots keep the whole table L2-resident.
+// Anchor hash-table slot: one 64-bit word {fingerprint (high 32) | list pointer (low 32)}.
+// The table is PARTITIONED by k-mer hash over the ranks of a multi-GPU job (rank r owns the keys
+// with owner_of_hash() == r and inserts only those, so table, filter slice and build time do not
+// grow with the number of GPUs); the scan resolves a key in its owner's partition, through
+// peer-mapped pointers when the owner is another GPU (TableView).  A list pointer is an anchor id
+// (b * stride + delta) with bit 31 = "this node has a successor" (next[id] is only read, and
+// only written, when it is set: most keys are singletons and resolve with ONE load).
+// Two different k-mers that collide on slot AND fingerprint (~2^-32 per probe) share a list: the
+// scan then emits a few false candidates, which the verifier rejects -- the table only has to
+// return a superset.
 typedef unsigned long long Slot;
 constexpr unsigned long long EMPTY_SLOT = ~0ull;
 constexpr uint32_t NIL = 0xffffffffu;
+constexpr uint32_t HAS_NEXT = 0x80000000u;
+constexpr uint32_t ID_MASK = 0x7fffffffu;
+
+struct TableView {
+    const Slot* tbl[MAX_RANKS];      // tbl[r]: partition of rank r (peer-mapped for r != me)
+    const uint32_t* nxt[MAX_RANKS];  // nxt[r]: its successor array, indexed by anchor id
+    uint32_t nr;                     // ranks (1: everything is local)
+    int tbits;                       // log2 slots of every partition
+};
 
 struct Row {
     uint32_t a, b, astart, aend, bend;
 };
+
+// bits kernels raise in the pass's flag word (reported to every rank in the status vector)
+constexpr unsigned long long STF_OVERFLOW = 1;  // a capacity was exceeded: grow and repeat the pass
+constexpr unsigned long long STF_TABLE = 2;     // anchor partition full
+constexpr unsigned long long STF_TIMEOUT = 4;   // a k_wait gave up
+constexpr unsigned long long STF_GATHER = 8;    // rank 0's row array too small
 
 // Bit layout of a 64-bit candidate key: [a | b | p | sp | cont], most significant first.
 struct KeyFmt {
@@ -121,12 +143,19 @@ __host__ __device__ __forceinline__ uint64_t mix64(uint64_t x) {
     x ^= x >> 29;
     return x;
 }
-__host__ __device__ __forceinline__ uint32_t slot_of(uint64_t h, int tbits) {
-    return (uint32_t)(h >> (64 - tbits));
+// Owner rank of a key: the integer part of  (high 32 hash bits) * nr / 2^32;  the fractional part
+// of the same product (uniform inside one owner) gives the slot.  nr = 1: owner 0, slot = top bits.
+__host__ __device__ __forceinline__ uint32_t owner_of_hash(uint64_t h, uint32_t nr) {
+    return nr <= 1 ? 0u : (uint32_t)((((uint64_t)(uint32_t)(h >> 32)) * nr) >> 32);
 }
-// single-bit L2-resident bitmap (sparse path): bit index from the LOW hash bits
-__host__ __device__ __forceinline__ uint32_t bitmap_bit(uint64_t h, int bm_bits) {
-    return (uint32_t)h & ((1u << bm_bits) - 1u);
+__host__ __device__ __forceinline__ uint32_t slot_of(uint64_t h, uint32_t nr, int tbits) {
+    const uint32_t frac = (uint32_t)(h >> 32) * (nr ? nr : 1u);
+    return frac >> (32 - tbits);
+}
+// Sparse-path filter: one bit per key hash in an L2-resident bitmap of nr slices of 2^slice_log2
+// bits; slice r holds exactly the keys rank r owns (built by r, pushed to every peer).
+__host__ __device__ __forceinline__ uint64_t bitmap_bit(uint64_t h, uint32_t nr, int slice_log2) {
+    return ((uint64_t)owner_of_hash(h, nr) << slice_log2) | ((uint32_t)h & ((1u << slice_log2) - 1u));
 }
 
 // k-mer starting at base j (0..31) of word w0, continuing into w1.
@@ -143,18 +172,38 @@ __device__ __forceinline__ uint4 ldg_stream(const uint4* p) {
     return r;
 }
 
-// Per-warp candidate staging buffer in shared memory: keys are appended warp-synchronously and
-// flushed to the global candidate array with ONE global atomic per flush (instead of one per
-// probe round), in coalesced 256-byte stores.
-constexpr int WBUF = 256;  // keys per warp
+// Lookup shared by the scan kernels: list pointer of the key with hash h in its owner's
+// partition, NIL if absent.
+__device__ __forceinline__ uint32_t table_find(const TableView& T, uint64_t h, uint32_t& owner) {
+    owner = owner_of_hash(h, T.nr);
+    const Slot* __restrict__ table = T.tbl[owner];
+    const uint32_t tmask = (1u << T.tbits) - 1u;
+    const uint32_t fp = (uint32_t)h;
+    uint32_t s = slot_of(h, T.nr, T.tbits);
+    for (uint32_t tries = 0; tries <= tmask; ++tries) {
+        const unsigned long long v = __ldg(table + s);
+        if (v == EMPTY_SLOT) return NIL;
+        if ((uint32_t)(v >> 32) == fp) return (uint32_t)v;
+        s = (s + 1) & tmask;
+    }
+    return NIL;
+}
 
-struct CandSink {
-    uint64_t* out;
-    unsigned long long* n_out;  // total candidates found (may exceed cap)
+// Per-warp staging buffer in shared memory: items are appended warp-synchronously and flushed to
+// a global array with ONE global atomic per flush (instead of one per probe round), in coalesced
+// stores.  T is uint64_t (candidate / hit keys) or ulonglong2 (scan survivors).
+constexpr int WBUF = 256;  // items per warp
+
+template <class T>
+struct Sink {
+    T* out;
+    unsigned long long* n_out;  // total items found (may exceed cap)
     uint64_t cap;
 };
+typedef Sink<uint64_t> CandSink;
 
-__device__ __forceinline__ void wbuf_flush(uint64_t* buf, uint32_t& n, const CandSink& S, uint32_t lane) {
+template <class T>
+__device__ __forceinline__ void wbuf_flush(T* buf, uint32_t& n, const Sink<T>& S, uint32_t lane) {
     unsigned long long base = 0;
     if (lane == 0) base = atomicAdd(S.n_out, (unsigned long long)n);
     base = __shfl_sync(FULL, base, 0);
@@ -164,13 +213,14 @@ __device__ __forceinline__ void wbuf_flush(uint64_t* buf, uint32_t& n, const Can
     __syncwarp();
 }
 
-// Append `key` from every lane with have != 0.  All 32 lanes must call.
-__device__ __forceinline__ void wbuf_push(uint64_t* buf, uint32_t& n, const CandSink& S, uint32_t lane,
-                                          bool have, uint64_t key) {
+// Append `item` from every lane with have != 0.  All 32 lanes must call.
+template <class T>
+__device__ __forceinline__ void wbuf_push(T* buf, uint32_t& n, const Sink<T>& S, uint32_t lane, bool have,
+                                          const T& item) {
     const unsigned m = __ballot_sync(FULL, have);
     if (!m) return;
     if (n + 32 > WBUF) wbuf_flush(buf, n, S, lane);
-    if (have) buf[n + __popc(m & ((1u << lane) - 1u))] = key;
+    if (have) buf[n + __popc(m & ((1u << lane) - 1u))] = item;
     n += __popc(m);
     __syncwarp();
 }

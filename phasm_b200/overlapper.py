@@ -223,6 +223,22 @@ class ExactOverlapper:
         self._check(self._lib.ovl_fetch_rows(self._ctx, byref(p), byref(n)))
         return self._rows_array(p, n.value, copy)
 
+    def fetch_local_rows(self, copy: bool = True) -> np.ndarray:
+        """Multi-GPU: this rank's OWN rows of the last pass (``stats()["rows_local"]`` of them),
+        HBM -> this rank's pinned host buffer over its own PCIe link."""
+        p, n = c_void_p(), c_uint64()
+        self._check(self._lib.ovl_fetch_local_rows(self._ctx, byref(p), byref(n)))
+        return self._rows_array(p, n.value, copy)
+
+    def overlaps_local_arrays(self, min_length, copy: bool = True) -> np.ndarray:
+        """Multi-GPU, collective: host buffers in on every rank, the pass, this rank's own rows out
+        (``ovl_overlaps_local``).  The ranks' arrays concatenated in rank order are the canonical
+        row list; rank 0 also holds all rows in HBM (``fetch_rows``)."""
+        l = _as_unsigned(min_length, "overlaps")
+        p, n = c_void_p(), c_uint64()
+        self._check(self._lib.ovl_overlaps_local(self._ctx, l, byref(p), byref(n)))
+        return self._rows_array(p, n.value, copy)
+
     def filter_rows(self, contained_reads: bool = True, min_read_length: int = 0,
                     min_overlap_length: int = 0, max_overhang_abs=1000, max_overhang_rel=0.8,
                     collapse_pairs: bool = False, copy: bool = True):

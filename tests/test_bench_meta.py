@@ -13,11 +13,16 @@ ROOT = helpers.ROOT
 def test_committed_traffic_capture_covers_the_hot_kernels():
     sys.path.insert(0, ROOT)
     import bench
-    traffic, src = bench.ncu_traffic()
+    traffic, src = bench.ncu_traffic(1, 64)
     assert traffic and src.endswith("_traffic.json")
-    for prefix in ("k1_pack", "k3_probe", "k4a_head", "k4b_tail"):
-        got = [v for n, v in traffic.items() if n.startswith(prefix)]
-        assert got and all(v > 1e6 for v in got), prefix   # bytes per launch of the bench workload
+    for prefixes in (("k1_pack",), ("k3_filter", "k3_probe"), ("k4a_head",), ("k4b_tail",)):
+        got = [v for n, v in traffic.items() if n.startswith(prefixes)]
+        assert got and all(v > 1e6 for v in got), prefixes   # bytes per launch of the bench workload
+    # the match rule: a capture is only pasted onto a run of the same GPU count
+    # and anchor stride; anything else reports traffic = null and says why
+    for n_gpus, stride in ((8, 64), (1, 8), (2, 16)):
+        t, why = bench.ncu_traffic(n_gpus, stride)
+        assert t is None and "capture" in why, (n_gpus, stride, why)
     # the launch list and the full summary of the same round are committed beside it
     tag = src.split("_traffic.json")[0]
     for suffix in ("_launches.csv", "_launches_summary.txt", "_ncu_full_summary.csv", "_bench.json"):

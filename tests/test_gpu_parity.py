@@ -364,28 +364,50 @@ def test_self_reverse_complement_pairs_are_reported(ov):
     assert rows.count(("pal+", "pal-", 0, 16, 0, 16)) == 2   # R1 + R2 duplicate row
 
 
-# ---- hit ordering: bucket sort (default) and its radix-sort fallback ---------------------------
-def test_heavy_entries_take_the_radix_fallback(ov):
-    """An entry with more hits than one warp's bucket (k7_bucket.cuh BUCKET_MAX) makes the call
-    fall back to the device-wide radix sort; rows must not change.  300 copies of one read give
-    every entry ~600 hits; a second, ordinary set afterwards must be back on the bucket path."""
+# ---- hit ordering: warp buckets (default) and the block sort of big buckets -----------------------
+def test_heavy_entries_are_sorted_by_the_block_kernel(ov):
+    """An entry with more hits than one warp's bucket (k7_bucket.cuh BUCKET_MAX = 256) is ordered by
+    k7_sort_big (one block per bucket, arbitrary length); rows must not change.  300 copies of one
+    read give every entry ~600 hits, 700 copies ~1400 (more keys than the block has threads); a
+    second, ordinary set afterwards must have no big bucket."""
     from oracle import port
     from oracle.bruteforce import both_strand_entries
     rng = random.Random(77)
     base = "".join(rng.choice("ACGT") for _ in range(300))
     other = "".join(rng.choice("ACGT") for _ in range(500))
-    reads = [("d%03d" % i, base) for i in range(300)] + [("x0", other), ("x1", other[100:] + base[:150])]
-    ebuf, eoff = port.entries_to_buffer(both_strand_entries(reads))
-    for l in (100, 300):
-        want, _ = port.oracle_overlaps(ebuf, eoff, l)
-        got = run_reads_idx(ov, reads, l)
-        st = ov.stats()
-        assert st["radix_fallback"] == 1, st
-        assert np.array_equal(got, want), l
+    for copies in (300, 700):
+        reads = [("d%03d" % i, base) for i in range(copies)] + [("x0", other), ("x1", other[100:] + base[:150])]
+        ebuf, eoff = port.entries_to_buffer(both_strand_entries(reads))
+        for l in (100, 300):
+            want, _ = port.oracle_overlaps(ebuf, eoff, l)
+            got = run_reads_idx(ov, reads, l)
+            st = ov.stats()
+            assert st["big_buckets"] > 0 and st["radix_fallback"] == 0, st
+            assert np.array_equal(got, want), (copies, l)
     key = sorted(helpers.MID_SPECS)[0]
     reads2, l2 = helpers.mid_input(key)
     assert np.array_equal(run_reads_idx(ov, reads2, l2), sort_rows(helpers.load_mid()[key]))
-    assert ov.stats()["radix_fallback"] == 0
+    assert ov.stats()["big_buckets"] == 0
+
+
+def test_capacity_overflow_grows_and_repeats(ov):
+    """A first candidate capacity far below what the input needs: the pass must notice the overflow
+    on the device, grow, repeat and return the same rows (the retry route had no test)."""
+    key = "cfg2_x0.015"
+    reads, l = helpers.mid_input(key)
+    want = sort_rows(helpers.load_mid()[key])
+    ov.set_option("min_cand_cap", 64)
+    ov.set_option("cand_per_entry", 1)
+    try:
+        got = run_reads_idx(ov, reads, l)
+        st = ov.stats()
+        assert st["retries"] > 0, st
+        assert np.array_equal(got, want)
+        got2 = run_reads_idx(ov, reads, l)          # capacities now fit: no retry, same rows
+        assert np.array_equal(got2, want)
+    finally:
+        ov.set_option("min_cand_cap", 1 << 20)
+        ov.set_option("cand_per_entry", 96)
 
 
 def test_bucket_path_matches_serial_and_nonmirror_variants(ov):

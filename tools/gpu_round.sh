@@ -21,8 +21,8 @@ timeout 600 ncu --metrics gpu__time_duration.sum --clock-control none -c 600 --c
 echo "ncu list exit $?"
 # full capture of our kernels, one launch each after warm-up (skip the first 3 of each)
 timeout 900 ncu --set full --clock-control none --import-source on \
-  --kernel-name regex:'k1_pack|k3_probe|k3_scan|k4a_head|k4b_tail|k4_verify|k2_insert|k5_|k7_' \
-  --launch-skip 40 --launch-count 12 -o "$OUT/full" -f \
+  --kernel-name regex:'k1_pack|k3_filter|k3_resolve|k4a_head|k4b_tail|k2_insert|k7_' \
+  --launch-skip 55 --launch-count 11 -o "$OUT/full" -f \
   python bench.py --steps 2 --warmup 3 --no-cpu > "$OUT/ncu_full.log" 2>&1
 echo "ncu full exit $?"
 ls -la "$OUT"
