@@ -165,6 +165,12 @@ int ovl_timer_stop(ovl_ctx *ctx, float *ms);
  * reverse complement made on the device) or one entry.  Record name = header line after '>',
  * right-stripped; multi-line records and blank lines are accepted (tests/data/test.fasta). */
 int ovl_add_fasta(ovl_ctx *ctx, const char *path, int both_strands, uint32_t *n_records);
+/* Multi-GPU form: every rank reads the same file; the records are split into nranks contiguous,
+ * base-balanced ranges in rank order, only the records [*rec_lo, *rec_hi) of `rank` are staged and
+ * the others are declared by name and length, so that every rank holds the same entry table (and
+ * rank 0 every id for the GFA2 writer). */
+int ovl_add_fasta_shard(ovl_ctx *ctx, const char *path, int both_strands, int rank, int nranks,
+                        uint32_t *n_records, uint32_t *rec_lo, uint32_t *rec_hi);
 
 /* ovl_write_gfa replaces the GFA2 writing loop of phasm/cli/assembler.py:30,38,46-48 over
  * gfa_header/gfa_line (phasm/io/gfa.py:230-240), byte for byte: `what` bit0 = header line

@@ -29,6 +29,8 @@ logger = logging.getLogger()
 
 def overlap(args):
     out = args.output
+    if getattr(args, "gpus", 1) > 1:
+        return _overlap_multi(args)
     overlapper = ExactOverlapper()
 
     if getattr(args, "python_io", False) or not _has_fd(out):
@@ -55,7 +57,38 @@ def overlap(args):
         out.flush()
         overlapper.write_gfa(out.fileno(), True, True, True)
 
+    _write_stats(args, overlapper.stats())
     logger.info("Done.")
+
+
+def _overlap_multi(args):
+    """``--gpus N``: one process per GPU, reads sharded by record range, rows gathered to this
+    process (rank 0), which writes the same bytes as the single-GPU route (E lines in the same
+    canonical order).  No counterpart in the reference (single process)."""
+    from phasm_b200 import multi, worker
+    if not _has_fd(args.output):
+        raise SystemExit("phasm overlap --gpus N needs an output with a file descriptor")
+    logger.info("Building suffix tree and searching for pairwise overlaps...")
+    port = multi.free_port()
+    procs = multi.spawn_workers(args.gpus, args.fasta_input, args.min_length, port)
+    try:
+        logger.info("Writing to GFA2...")
+        st = worker.run_rank(0, args.gpus, port, args.fasta_input, args.min_length, out=args.output)
+    finally:
+        codes = [p.wait() for p in procs]
+    if any(codes):
+        raise SystemExit("phasm overlap: a GPU worker failed (exit codes %s)" % codes)
+    _write_stats(args, st)
+    logger.info("Done.")
+
+
+def _write_stats(args, st):
+    """``--stats json``: counters and device stage times of the run, one JSON object on stderr
+    (for roofline accounting; off by default like every flag the reference
+    does not have)."""
+    if getattr(args, "stats", None) == "json":
+        import json
+        sys.stderr.write(json.dumps({"phasm_overlap_stats": dict(st)}) + "\n")
 
 
 def _has_fd(f) -> bool:
@@ -103,6 +136,14 @@ def main(argv=None):
         '--python-io', action='store_true',
         help="Read the FASTA and write the GFA2 lines in Python, row by row, as the "
              "reference does (default: native reader/writer, same bytes)."
+    )
+    overlap_parser.add_argument(
+        '--gpus', type=int, required=False, default=1,
+        help="Number of GPUs of this machine to shard the reads over (default: 1)."
+    )
+    overlap_parser.add_argument(
+        '--stats', choices=['json'], required=False, default=None,
+        help="Write counters and stage times of the run as one JSON line to stderr."
     )
     overlap_parser.add_argument(
         'fasta_input', help="The fasta file with reads.")

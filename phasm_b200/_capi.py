@@ -85,6 +85,8 @@ SIGNATURES = {
     "ovl_timer_start": (c_int, [_P]),
     "ovl_timer_stop": (c_int, [_P, POINTER(c_float)]),
     "ovl_add_fasta": (c_int, [_P, c_char_p, c_int, POINTER(c_uint32)]),
+    "ovl_add_fasta_shard": (c_int, [_P, c_char_p, c_int, c_int, c_int, POINTER(c_uint32), POINTER(c_uint32),
+                                    POINTER(c_uint32)]),
     "ovl_write_gfa": (c_int, [_P, c_int, c_int, POINTER(c_uint64)]),
     "ovl_filter_rows": (c_int, [_P, POINTER(OvlFilterOpts), POINTER(c_void_p), POINTER(c_uint64),
                                 POINTER(OvlFilterStats)]),

@@ -915,7 +915,6 @@ int run_pass(ovl_ctx* c, uint32_t min_length, bool chunked) {
             P.dense = dense ? 1 : 0;
             P.me = (uint32_t)me;
             P.nr = (uint32_t)nr;
-            P.n_anchors = reinterpret_cast<unsigned long long*>(ctr + C_NANC);
             P.flags = reinterpret_cast<unsigned long long*>(ctr + C_FLAGS);
             const uint64_t nthreads = (uint64_t)M << slog;
             k2_insert<<<(unsigned)((nthreads + 255) / 256), 256, 0, sk>>>(P);

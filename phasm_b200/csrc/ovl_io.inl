@@ -6,6 +6,7 @@
 //                   over gfa_header/gfa_line (/root/reference/phasm/io/gfa.py:230-240).
 // Pure byte shuffling on the host; no overlap computation happens here.
 #include <algorithm>
+#include <cmath>
 #include <fcntl.h>
 #include <sys/mman.h>
 #include <sys/stat.h>
@@ -53,19 +54,38 @@ int write_all(ovl_ctx* c, int fd, const char* p, size_t n) {
     return OVL_OK;
 }
 
-}  // namespace
-
-extern "C" {
+// One pass over the lines of a FASTA image.  on_header(name, len) opens a record, on_seq(p, n) adds a
+// sequence line to it; returns false if sequence data precedes the first header.
+template <class H, class Q>
+bool fasta_lines(const char* base, const char* end, H on_header, Q on_seq) {
+    const char* p = base;
+    bool open_rec = false;
+    while (p < end) {
+        const char* nl = static_cast<const char*>(memchr(p, '\n', (size_t)(end - p)));
+        const char* le = nl ? nl : end;
+        const size_t n = rstrip(p, (size_t)(le - p));
+        if (n && p[0] == '>') {
+            if (!on_header(p + 1, n - 1)) return true;  // the callback asked to stop
+            open_rec = true;
+        } else if (n) {
+            if (!open_rec) return false;
+            if (!on_seq(p, n)) return true;
+        }
+        p = nl ? nl + 1 : end;
+    }
+    return true;
+}
 
 // FASTA rules (documented; dinopy's own are unverifiable here): a record starts
 // at a line beginning with '>'; its name is the rest of that line, right-stripped; its sequence
 // is the concatenation of the following lines (right-stripped, blank lines skipped) up to the
 // next '>' line or EOF.  Bytes are taken as they are: anything outside upper-case ACGT is
 // rejected later by the pack kernel (OVL_E_ALPHABET).
-int ovl_add_fasta(ovl_ctx* c, const char* path, int both_strands, uint32_t* n_records) {
-    if (!c || !path) return fail(c, OVL_E_ARG, "ovl_add_fasta: NULL argument");
-    if (n_records) *n_records = 0;
-    OVL_TRY(set_dev(c));
+// nranks > 1: records are split into contiguous, base-balanced ranges in rank order; only the
+// records of `rank` are staged, the others are declared by name and length (ovl_add_remote with
+// names), so that every rank builds the same entry table and rank 0 can write every id.
+int add_fasta_impl(ovl_ctx* c, const char* path, int both_strands, int rank, int nranks, uint32_t* n_records,
+                   uint32_t* rec_lo, uint32_t* rec_hi) {
     const int fd = open(path, O_RDONLY);
     if (fd < 0) return fail(c, OVL_E_ARG, "ovl_add_fasta: cannot open '%s': %s", path, strerror(errno));
     struct stat sb;
@@ -85,43 +105,62 @@ int ovl_add_fasta(ovl_ctx* c, const char* path, int both_strands, uint32_t* n_re
     const char* const base = static_cast<const char*>(mp);
     const char* const end = base + fsz;
     int rc = OVL_OK;
-    uint32_t nrec = 0;
+    uint32_t nrec = 0, lo = 0, hi = 0xffffffffu;
     try {
-        rc = pin_ensure(c, c->ascii, c->ascii_used + fsz + SLACK, c->ascii_used);
-        const char* p = base;
-        bool open_rec = false;
+        if (nranks > 1) {  // pass 1: record lengths -> this rank's record range
+            std::vector<uint64_t> csum{0};
+            const bool ok = fasta_lines(base, end,
+                [&](const char*, size_t) { csum.push_back(csum.back()); return true; },
+                [&](const char*, size_t n) { csum.back() += n; return true; });
+            if (!ok) rc = fail(c, OVL_E_ARG, "ovl_add_fasta: '%s' has sequence data before the first '>' line", path);
+            const size_t R = csum.size() - 1;
+            auto cut = [&](int k) -> uint32_t {  // boundary whose prefix sum is closest to k/nranks of the bases
+                if (k <= 0) return 0;
+                if (k >= nranks) return (uint32_t)R;
+                const double target = (double)csum[R] * k / nranks;
+                size_t i = (size_t)(std::lower_bound(csum.begin(), csum.end(), (uint64_t)target) - csum.begin());
+                if (i > R) i = R;
+                if (i > 0 && fabs((double)csum[i - 1] - target) <= fabs((double)csum[i] - target)) --i;
+                return (uint32_t)i;
+            };
+            lo = cut(rank);
+            hi = cut(rank + 1);
+            if (hi < lo) hi = lo;
+        }
+        if (rc == OVL_OK) rc = pin_ensure(c, c->ascii, c->ascii_used + (nranks > 1 ? 0 : fsz) + SLACK, c->ascii_used);
+        bool open_rec = false, local = true;
         const char* name = nullptr;
         size_t name_len = 0, rec_off = 0, rec_len = 0;
         auto close_rec = [&]() -> int {
             if (!open_rec) return OVL_OK;
             open_rec = false;
-            c->ascii_used = rec_off + align16(rec_len);
+            const uint64_t src = local ? rec_off : NO_SRC;
+            if (local) c->ascii_used = rec_off + align16(rec_len);
             ++nrec;
             if (both_strands) {
-                OVL_TRY(push_entry(c, name, name_len, "+", rec_off, rec_len, 0));
-                return push_entry(c, name, name_len, "-", rec_off, rec_len, 1);
+                OVL_TRY(push_entry(c, name, name_len, "+", src, rec_len, 0));
+                return push_entry(c, name, name_len, "-", src, rec_len, 1);
             }
-            return push_entry(c, name, name_len, nullptr, rec_off, rec_len, 0);
+            return push_entry(c, name, name_len, nullptr, src, rec_len, 0);
         };
-        while (rc == OVL_OK && p < end) {
-            const char* nl = static_cast<const char*>(memchr(p, '\n', (size_t)(end - p)));
-            const char* le = nl ? nl : end;
-            size_t n = rstrip(p, (size_t)(le - p));
-            if (n && p[0] == '>') {
-                rc = close_rec();
-                name = p + 1;
-                name_len = n - 1;
-                rec_off = c->ascii_used;
-                rec_len = 0;
-                open_rec = true;
-            } else if (n) {
-                if (!open_rec) {
-                    rc = fail(c, OVL_E_ARG, "ovl_add_fasta: '%s' has sequence data before the first '>' line", path);
-                    break;
-                }
-                rc = stage_append(c, rec_off, rec_len, p, n);
-            }
-            p = nl ? nl + 1 : end;
+        if (rc == OVL_OK) {
+            const bool ok = fasta_lines(base, end,
+                [&](const char* nm, size_t nl) {
+                    rc = close_rec();
+                    name = nm;
+                    name_len = nl;
+                    rec_off = c->ascii_used;
+                    rec_len = 0;
+                    open_rec = true;
+                    local = nrec >= lo && nrec < hi;
+                    return rc == OVL_OK;
+                },
+                [&](const char* p, size_t n) {
+                    if (local) rc = stage_append(c, rec_off, rec_len, p, n);
+                    else rec_len += n;
+                    return rc == OVL_OK;
+                });
+            if (!ok) rc = fail(c, OVL_E_ARG, "ovl_add_fasta: '%s' has sequence data before the first '>' line", path);
         }
         if (rc == OVL_OK) rc = close_rec();
     } catch (const std::bad_alloc&) {
@@ -129,7 +168,28 @@ int ovl_add_fasta(ovl_ctx* c, const char* path, int both_strands, uint32_t* n_re
     }
     munmap(mp, fsz);
     if (n_records) *n_records = nrec;
+    if (rec_lo) *rec_lo = lo;
+    if (rec_hi) *rec_hi = hi == 0xffffffffu ? nrec : hi;
     return rc;
+}
+
+}  // namespace
+
+extern "C" {
+
+int ovl_add_fasta(ovl_ctx* c, const char* path, int both_strands, uint32_t* n_records) {
+    if (!c || !path) return fail(c, OVL_E_ARG, "ovl_add_fasta: NULL argument");
+    if (n_records) *n_records = 0;
+    OVL_TRY(set_dev(c));
+    return add_fasta_impl(c, path, both_strands, 0, 1, n_records, nullptr, nullptr);
+}
+
+int ovl_add_fasta_shard(ovl_ctx* c, const char* path, int both_strands, int rank, int nranks, uint32_t* n_records,
+                        uint32_t* rec_lo, uint32_t* rec_hi) {
+    if (!c || !path || nranks < 1 || rank < 0 || rank >= nranks) return fail(c, OVL_E_ARG, "ovl_add_fasta_shard: bad argument");
+    if (n_records) *n_records = 0;
+    OVL_TRY(set_dev(c));
+    return add_fasta_impl(c, path, both_strands, rank, nranks, n_records, rec_lo, rec_hi);
 }
 
 // what: bit0 header line, bit1 segment lines, bit2 edge lines (of the last ovl_overlaps* call).

@@ -171,6 +171,21 @@ public:
         d["ms_device"] = s.ms_device;
         d["ms_d2h"] = s.ms_d2h;
         d["ms_total"] = s.ms_total;
+        d["ms_pack"] = s.ms_pack;
+        d["ms_anchor"] = s.ms_anchor;
+        d["ms_scan"] = s.ms_scan;
+        d["ms_verify"] = s.ms_verify;
+        d["ms_sort"] = s.ms_sort;
+        d["ms_emit"] = s.ms_emit;
+        d["ms_exposed"] = s.ms_exposed;
+        d["granules"] = s.granules;
+        d["anchors"] = s.anchors;
+        d["scan_survivors"] = s.scan_survivors;
+        d["ascii_bytes"] = s.ascii_bytes;
+        d["operand_bytes"] = s.operand_bytes;
+        d["mirror"] = s.mirror;
+        d["retries"] = s.retries;
+        d["big_buckets"] = s.big_buckets;
         return d;
     }
 

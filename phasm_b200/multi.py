@@ -2,19 +2,31 @@
 
 SURVEY.md 8(e): the entry table is partitioned into contiguous A ranges balanced on bases; rank
 r stages only its own reads, learns the lengths of all the others (so that every rank sees the
-same entry table), packs its range, and the packed granules / hit keys are exchanged inside the
-library over NCCL (``ovl_comm_*``).  This module is the host-side plumbing around that:
+same entry table) and packs its range.  Everything that moves between the GPUs during a pass
+(prefix table, filter slices, packed reads, hit keys, rows) moves inside the library over
+peer-mapped HBM (``phasm_b200/csrc/k6_exchange.cuh``); this module is only the host-side
+plumbing around it:
 
-* ``plan_ranges``      contiguous, base-balanced read ranges
-* ``ShardedOverlapper`` builds the identical entry table on every rank from rank-local reads,
-  using a ``torch.distributed`` process group only for the small host-side exchanges (read
-  lengths, the 128-byte NCCL id).  Works with the ``gloo`` backend too, which is what the CPU
-  tests use (with a stand-in for the device object).
+* ``plan_ranges``        contiguous, base-balanced read ranges
+* ``TcpRendezvous``      a byte all-gather between the ranks over localhost TCP (standard library
+                         only): the channel for the read lengths and the 128-byte NCCL id
+* ``ShardedOverlapper``  builds the identical entry table on every rank from rank-local reads
+* ``spawn_workers``      what ``phasm overlap --gpus N`` uses: N-1 child processes + this one
+
+No torch here: any object with ``rank``, ``world`` and ``allgather_bytes(bytes) -> [bytes]`` works
+as the channel (``bench.py`` and the tests pass an adapter over ``torch.distributed``, NCCL or
+gloo, because torchrun has already set one up for them).
 
 The reference has no counterpart (single process, single thread: SURVEY.md 2.1).
 """
 from __future__ import annotations
 
+import os
+import socket
+import struct
+import subprocess
+import sys
+import time
 from typing import List, Optional, Sequence, Tuple
 
 import numpy as np
@@ -43,32 +55,112 @@ def plan_ranges(lengths: Sequence[int], world: int) -> List[Tuple[int, int]]:
     return [(cuts[k], cuts[k + 1]) for k in range(world)]
 
 
-def _all_gather_lengths(local: np.ndarray, dist, device) -> List[np.ndarray]:
-    """All-gather variable-length uint32 arrays through a process group."""
-    import torch
-    world = dist.get_world_size()
-    n = torch.tensor([len(local)], dtype=torch.int64, device=device)
-    ns = [torch.zeros(1, dtype=torch.int64, device=device) for _ in range(world)]
-    dist.all_gather(ns, n)
-    counts = [int(x.item()) for x in ns]
-    cap = max(max(counts), 1)
-    buf = torch.zeros(cap, dtype=torch.int64, device=device)
-    if len(local):
-        buf[:len(local)] = torch.from_numpy(local.astype(np.int64)).to(device)
-    outs = [torch.zeros(cap, dtype=torch.int64, device=device) for _ in range(world)]
-    dist.all_gather(outs, buf)
-    return [o[:c].cpu().numpy().astype(np.uint32) for o, c in zip(outs, counts)]
+# ---- byte channel between the ranks ---------------------------------------------------------------
+def _send_blob(sock: socket.socket, blob: bytes) -> None:
+    sock.sendall(struct.pack("<Q", len(blob)) + blob)
+
+
+def _recv_exact(sock: socket.socket, n: int) -> bytes:
+    parts = []
+    while n:
+        chunk = sock.recv(min(n, 1 << 20))
+        if not chunk:
+            raise ConnectionError("rendezvous peer closed the connection")
+        parts.append(chunk)
+        n -= len(chunk)
+    return b"".join(parts)
+
+
+def _recv_blob(sock: socket.socket) -> bytes:
+    (n,) = struct.unpack("<Q", _recv_exact(sock, 8))
+    return _recv_exact(sock, n)
+
+
+class TcpRendezvous:
+    """All-gather of byte strings between ``world`` processes of one host: rank 0 listens on
+    ``addr:port``, the others connect and stay connected.  Only small control data travels here."""
+
+    def __init__(self, rank: int, world: int, addr: str = "127.0.0.1", port: int = 29571,
+                 timeout: float = 120.0):
+        self.rank, self.world = rank, world
+        self._peers: List[Optional[socket.socket]] = [None] * world
+        self._sock: Optional[socket.socket] = None
+        if world == 1:
+            return
+        if rank == 0:
+            srv = socket.socket(socket.AF_INET, socket.SOCK_STREAM)
+            srv.setsockopt(socket.SOL_SOCKET, socket.SO_REUSEADDR, 1)
+            srv.bind((addr, port))
+            srv.listen(world)
+            srv.settimeout(timeout)
+            try:
+                for _ in range(world - 1):
+                    conn, _ = srv.accept()
+                    conn.settimeout(timeout)
+                    (r,) = struct.unpack("<I", _recv_exact(conn, 4))
+                    if not 0 < r < world or self._peers[r] is not None:
+                        raise ConnectionError("rendezvous: unexpected rank %d" % r)
+                    self._peers[r] = conn
+            finally:
+                srv.close()
+        else:
+            deadline = time.time() + timeout
+            while True:
+                s = socket.socket(socket.AF_INET, socket.SOCK_STREAM)
+                try:
+                    s.connect((addr, port))
+                    break
+                except OSError:
+                    s.close()
+                    if time.time() > deadline:
+                        raise
+                    time.sleep(0.05)
+            s.settimeout(timeout)
+            s.sendall(struct.pack("<I", rank))
+            self._sock = s
+
+    def allgather_bytes(self, blob: bytes) -> List[bytes]:
+        if self.world == 1:
+            return [blob]
+        if self.rank == 0:
+            got = [blob] + [_recv_blob(self._peers[r]) for r in range(1, self.world)]
+            packed = b"".join(struct.pack("<Q", len(b)) + b for b in got)
+            for r in range(1, self.world):
+                _send_blob(self._peers[r], packed)
+            return got
+        _send_blob(self._sock, blob)
+        packed = _recv_blob(self._sock)
+        out, pos = [], 0
+        for _ in range(self.world):
+            (n,) = struct.unpack_from("<Q", packed, pos)
+            out.append(packed[pos + 8:pos + 8 + n])
+            pos += 8 + n
+        return out
+
+    def barrier(self) -> None:
+        self.allgather_bytes(b"")
+
+    def close(self) -> None:
+        for s in self._peers + [self._sock]:
+            if s is not None:
+                try:
+                    s.close()
+                except OSError:
+                    pass
+        self._peers = [None] * self.world
+        self._sock = None
 
 
 class ShardedOverlapper:
     """One rank's view of an N-GPU overlap job.
 
     ``make_overlapper`` builds the per-rank device object (``ExactOverlapper(local_rank)`` in
-    production; a stand-in with the same methods in the CPU tests).
+    production; a stand-in with the same methods in the CPU tests).  ``chan`` is the byte channel
+    between the ranks (``TcpRendezvous`` or anything with the same three members).
     """
 
-    def __init__(self, make_overlapper, rank: int, world: int, dist=None, device="cpu"):
-        self.rank, self.world, self.dist, self.device = rank, world, dist, device
+    def __init__(self, make_overlapper, chan):
+        self.rank, self.world, self.chan = chan.rank, chan.world, chan
         self.ov = make_overlapper()
         self.ranges: Optional[List[Tuple[int, int]]] = None
 
@@ -77,10 +169,7 @@ class ShardedOverlapper:
         everywhere: remote reads are declared by length only."""
         offsets = np.asarray(offsets, dtype=np.uint64)
         local_len = np.diff(offsets).astype(np.uint32)
-        if self.world > 1:
-            all_len = _all_gather_lengths(local_len, self.dist, self.device)
-        else:
-            all_len = [local_len]
+        all_len = [np.frombuffer(b, dtype=np.uint32) for b in self.chan.allgather_bytes(local_len.tobytes())]
         lo = 0
         self.ranges = []
         for r, ln in enumerate(all_len):
@@ -93,26 +182,41 @@ class ShardedOverlapper:
         return self.ranges
 
     def connect(self):
-        """NCCL communicator of the library (id made on rank 0, broadcast through ``dist``),
-        upload, range check."""
+        """NCCL bootstrap communicator of the library (id made on rank 0, shipped through the
+        channel), upload, range check.  The peer-memory arenas are mapped by the first pass."""
         if self.world > 1:
-            import torch
-            uid = torch.zeros(128, dtype=torch.uint8, device=self.device)
-            if self.rank == 0:
-                raw = type(self.ov).comm_unique_id()
-                uid.copy_(torch.frombuffer(bytearray(raw), dtype=torch.uint8))
-            self.dist.broadcast(uid, 0)
-            self.ov.comm_init(bytes(uid.cpu().numpy().tobytes()), self.rank, self.world)
+            raw = type(self.ov).comm_unique_id() if self.rank == 0 else b""
+            uid = self.chan.allgather_bytes(raw)[0]
+            self.ov.comm_init(uid, self.rank, self.world)
         self.ov.upload()
         if self.world > 1:
             self.ov.comm_sync_ranges()
 
     def overlaps_device(self, min_length: int) -> int:
-        """Device pass on every rank + gather of the rows into rank 0's HBM."""
-        n = self.ov.overlaps_device(min_length)
-        return self.ov.comm_gather_rows_device() if self.world > 1 else n
+        """Device pass on every rank; the rows of all ranks land in rank 0's HBM inside it."""
+        return self.ov.overlaps_device(min_length)
 
     def overlaps_arrays(self, min_length: int) -> np.ndarray:
         """Rows on rank 0 (canonical order), an empty array elsewhere."""
         self.ov.overlaps_device(min_length)
-        return self.ov.comm_gather_rows() if self.world > 1 else self.ov.fetch_rows()
+        return self.ov.fetch_rows()
+
+
+# ---- process fan-out for the CLI -----------------------------------------------------------------
+def free_port() -> int:
+    with socket.socket(socket.AF_INET, socket.SOCK_STREAM) as s:
+        s.bind(("127.0.0.1", 0))
+        return s.getsockname()[1]
+
+
+def spawn_workers(world: int, fasta: str, min_length: int, port: int) -> List[subprocess.Popen]:
+    """Start ranks 1..world-1 as child processes (``python -m phasm_b200.worker``), the rank handed
+    over in the environment.  The children never touch the output file."""
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    procs = []
+    for r in range(1, world):
+        env = dict(os.environ, PHASM_OVL_RANK=str(r), PHASM_OVL_WORLD=str(world), PHASM_OVL_PORT=str(port))
+        env["PYTHONPATH"] = root + os.pathsep + env.get("PYTHONPATH", "")
+        procs.append(subprocess.Popen([sys.executable, "-m", "phasm_b200.worker", fasta, str(int(min_length))],
+                                      env=env, stdout=subprocess.DEVNULL))
+    return procs

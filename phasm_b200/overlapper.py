@@ -141,6 +141,15 @@ class ExactOverlapper:
         self._check(self._lib.ovl_add_fasta(self._ctx, os.fsencode(path), int(both_strands), byref(n)))
         return n.value
 
+    def add_fasta_shard(self, path, rank: int, world: int, both_strands: bool = True):
+        """Multi-GPU ingest (``ovl_add_fasta_shard``): stage this rank's record range of the file,
+        declare the other records by name and length.  Returns ``(n_records, lo, hi)``."""
+        import os
+        n, lo, hi = c_uint32(), c_uint32(), c_uint32()
+        self._check(self._lib.ovl_add_fasta_shard(self._ctx, os.fsencode(path), int(both_strands), int(rank),
+                                                  int(world), byref(n), byref(lo), byref(hi)))
+        return n.value, lo.value, hi.value
+
     def write_gfa(self, out, header: bool = True, segments: bool = True, edges: bool = True) -> int:
         """Native GFA2 writer (``ovl_write_gfa``): header / S-lines / E-lines of the last
         ``overlaps*`` call, byte-identical to phasm/cli/assembler.py:30,38,46-48.  ``out`` is a

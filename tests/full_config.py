@@ -24,11 +24,13 @@ import time
 
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 sys.path.insert(0, ROOT)
+sys.path.insert(0, os.path.join(ROOT, "tests"))
 
 import numpy as np  # noqa: E402
 import torch  # noqa: E402
 import torch.distributed as dist  # noqa: E402
 
+import helpers  # noqa: E402
 from phasm_b200 import multi, synth  # noqa: E402
 from phasm_b200.overlapper import ExactOverlapper  # noqa: E402
 
@@ -54,7 +56,7 @@ def main():
     buf, off, names = synth.generate(sh, ranges[rank])
     t_gen = time.perf_counter() - t0
 
-    so = multi.ShardedOverlapper(lambda: ExactOverlapper(local), rank, world, dist, torch.device("cuda", local))
+    so = multi.ShardedOverlapper(lambda: ExactOverlapper(local), helpers.TorchChan(dist))
     so.add_local_reads(buf, off, names)
     so.connect()
     n1 = so.overlaps_device(l)            # first pass sizes the buffers

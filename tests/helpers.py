@@ -82,3 +82,21 @@ def has_gpu() -> bool:
         return False
     n = ctypes.c_int(0)
     return lib.cudaGetDeviceCount(ctypes.byref(n)) == 0 and n.value > 0
+
+
+class TorchChan:
+    """Byte channel for phasm_b200.multi.ShardedOverlapper over an initialised torch.distributed
+    process group (gloo on CPU, nccl under torchrun on a GPU box): the tests' stand-in for
+    phasm_b200.multi.TcpRendezvous."""
+
+    def __init__(self, dist):
+        self.dist = dist
+        self.rank, self.world = dist.get_rank(), dist.get_world_size()
+
+    def allgather_bytes(self, blob: bytes):
+        out = [None] * self.world
+        self.dist.all_gather_object(out, bytes(blob))
+        return out
+
+    def barrier(self):
+        self.dist.barrier()

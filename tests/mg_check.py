@@ -13,11 +13,13 @@ import sys
 
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 sys.path.insert(0, ROOT)
+sys.path.insert(0, os.path.join(ROOT, "tests"))
 
 import numpy as np  # noqa: E402
 import torch  # noqa: E402
 import torch.distributed as dist  # noqa: E402
 
+import helpers  # noqa: E402
 from phasm_b200 import multi, synth  # noqa: E402
 from phasm_b200.overlapper import ExactOverlapper  # noqa: E402
 
@@ -28,6 +30,9 @@ def main():
     ap.add_argument("--scale", type=float, default=0.05)
     ap.add_argument("--mirror", type=int, default=1)
     ap.add_argument("--edge", type=int, default=0, help="use synth.edge_mix(seed, l) instead of a config")
+    ap.add_argument("--lmin", type=int, default=200, help="min_length of the --edge set")
+    ap.add_argument("--small-caps", type=int, default=0, help="1: tiny first capacities -> the collective grow-and-repeat route")
+    ap.add_argument("--bad-base", type=int, default=0, help="1: one non-ACGT byte on the LAST rank: every rank must raise")
     args = ap.parse_args()
     rank, world = int(os.environ["RANK"]), int(os.environ["WORLD_SIZE"])
     local = int(os.environ.get("LOCAL_RANK", rank))
@@ -35,8 +40,8 @@ def main():
     dist.init_process_group("nccl", device_id=torch.device("cuda", local))
 
     if args.edge:
-        reads = synth.edge_mix(args.edge, 200)
-        l = 200
+        reads = synth.edge_mix(args.edge, args.lmin)
+        l = args.lmin
         lens = [len(s) for _, s in reads]
         ranges = multi.plan_ranges(lens, world)
         lo, hi = ranges[rank]
@@ -53,11 +58,34 @@ def main():
         ranges = multi.plan_ranges([sh.read_len] * sh.n_reads, world)
         buf, off, names = synth.generate(sh, ranges[rank])
 
-    so = multi.ShardedOverlapper(lambda: ExactOverlapper(local), rank, world, dist, torch.device("cuda", local))
+    so = multi.ShardedOverlapper(lambda: ExactOverlapper(local), helpers.TorchChan(dist))
     so.ov.set_option("mirror", args.mirror)
+    so.ov.set_option("peer_timeout_ms", 8000)
+    if args.small_caps:
+        so.ov.set_option("min_cand_cap", 64)
+        so.ov.set_option("cand_per_entry", 1)
+    if args.bad_base and rank == world - 1 and len(buf):
+        buf = buf.copy()
+        buf[len(buf) // 2] = ord("N")
     got_ranges = so.add_local_reads(buf, off, names)
     assert got_ranges == ranges, (got_ranges, ranges)
     so.connect()
+    if args.bad_base:
+        # a bad byte on one shard must raise on EVERY rank (status exchange), not hang the others
+        try:
+            so.overlaps_arrays(l)
+            raised = False
+        except ValueError as e:
+            raised = "ACGT" in str(e)
+        t = torch.tensor([int(raised)], device="cuda")
+        dist.all_reduce(t, op=dist.ReduceOp.MIN)
+        ok = int(t.item())
+        if rank == 0:
+            print("mg_check world=%d bad-base: %s" % (world, "every rank raised OK" if ok else "MISMATCH"), flush=True)
+        so.ov.close()
+        dist.barrier()
+        dist.destroy_process_group()
+        return 0 if ok else 1
     rows = so.overlaps_arrays(l)
     rows2 = so.overlaps_arrays(l)          # repeatable
     st = so.ov.stats()
@@ -74,6 +102,8 @@ def main():
         want, _ = port.oracle_overlaps(ebuf, eoff, l)
         same = rows.shape == want.shape and np.array_equal(rows, want)   # already canonical order
         ok = int(same and np.array_equal(rows, rows2))
+        if args.small_caps:
+            ok = int(ok and st["retries"] == 0)    # second call: capacities fit
         print("mg_check world=%d mirror=%d rows=%d want=%d %s" % (world, st["mirror"], len(rows), len(want),
                                                                    "OK" if ok else "MISMATCH"), flush=True)
     print("rank %d: candidates %d hits %d sent %d received %d device %.3f ms" % (

@@ -33,8 +33,9 @@ def test_plan_ranges_tiles_and_balances():
 # ---- CPU: gloo world_size 2, stand-in device object ---------------------------------------------
 _WORKER = r'''
 import os, sys
-sys.path.insert(0, sys.argv[1])
+sys.path.insert(0, sys.argv[1]); sys.path.insert(0, os.path.join(sys.argv[1], "tests"))
 import numpy as np, torch, torch.distributed as dist
+import helpers
 from phasm_b200 import multi
 
 class FakeOverlapper:
@@ -61,7 +62,7 @@ lo, hi = ranges[rank]
 mine = all_lens[lo:hi]
 off = np.concatenate(([0], np.cumsum(mine))).astype(np.uint64)
 buf = np.full(int(off[-1]), 65, dtype=np.uint8)
-so = multi.ShardedOverlapper(FakeOverlapper, rank, world, dist, "cpu")
+so = multi.ShardedOverlapper(FakeOverlapper, helpers.TorchChan(dist))
 got = so.add_local_reads(buf, off, ["r%d" % i for i in range(lo, hi)])
 assert got == ranges, (got, ranges)
 assert so.ov.lengths == all_lens, so.ov.lengths          # same entry table on every rank
@@ -87,6 +88,45 @@ def test_sharded_plumbing_gloo_world2(tmp_path):
     assert "worker 0 ok" in r.stdout and "worker 1 ok" in r.stdout
 
 
+# ---- CPU: the torch-free byte channel the CLI uses ---------------------------------------------------
+_RDV = r'''
+import sys
+sys.path.insert(0, sys.argv[1])
+from phasm_b200.multi import TcpRendezvous
+rank, world, port = int(sys.argv[2]), int(sys.argv[3]), int(sys.argv[4])
+ch = TcpRendezvous(rank, world, port=port, timeout=60)
+got = ch.allgather_bytes(bytes([rank]) * (rank * 1000 + 1))
+assert [len(b) for b in got] == [r * 1000 + 1 for r in range(world)], [len(b) for b in got]
+assert all(set(b) == {r} for r, b in enumerate(got))
+uid = ch.allgather_bytes(b"U" * 128 if rank == 0 else b"")[0]      # how the NCCL id travels
+assert uid == b"U" * 128
+ch.barrier(); ch.close()
+print("rdv %d ok" % rank)
+'''
+
+
+def test_tcp_rendezvous_allgather_world3(tmp_path):
+    from phasm_b200.multi import free_port
+    script = tmp_path / "rdv.py"
+    script.write_text(_RDV)
+    port = free_port()
+    procs = [subprocess.Popen([sys.executable, str(script), ROOT, str(r), "3", str(port)],
+                              stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True) for r in range(3)]
+    outs = [p.communicate(timeout=120)[0] for p in procs]
+    assert all(p.returncode == 0 for p in procs), outs
+    assert all("rdv %d ok" % r in outs[r] for r in range(3)), outs
+
+
+def test_product_packages_do_not_import_torch():
+    import re
+    for pkg in ("phasm_b200", "phasm"):
+        for dirpath, _, files in os.walk(os.path.join(ROOT, pkg)):
+            for f in files:
+                if f.endswith(".py"):
+                    src = open(os.path.join(dirpath, f)).read()
+                    assert not re.search(r"^\s*(import|from)\s+torch\b", src, re.M), os.path.join(dirpath, f)
+
+
 # ---- GPU: N ranks vs the oracle -------------------------------------------------------------------
 def _n_gpus():
     try:
@@ -98,15 +138,75 @@ def _n_gpus():
 
 @pytest.mark.gpu
 @pytest.mark.parametrize("extra", [["--cfg", "2", "--scale", "0.03"], ["--cfg", "4", "--scale", "0.01"],
-                                   ["--edge", "3"], ["--cfg", "1", "--scale", "0.02", "--mirror", "0"]])
+                                   ["--edge", "3"], ["--cfg", "1", "--scale", "0.02", "--mirror", "0"],
+                                   ["--cfg", "2", "--scale", "0.02", "--small-caps", "1"],
+                                   ["--cfg", "2", "--scale", "0.01", "--bad-base", "1"],
+                                   ["--edge", "4", "--lmin", "33"], ["--edge", "5", "--lmin", "20"]])
 def test_sharded_job_matches_oracle(extra):
     n = _n_gpus()
     if n < 2:
         pytest.skip("needs >= 2 GPUs")
-    world = 4 if n >= 4 and "--edge" not in extra else 2
+    world = (8 if n >= 8 else 4 if n >= 4 else 2) if "--edge" not in extra else 2
     cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node", str(world),
            "--master-addr", "127.0.0.1", "--master-port", "29519",
            os.path.join(ROOT, "tests", "mg_check.py")] + extra
     r = subprocess.run(cmd, capture_output=True, text=True, timeout=900, cwd=ROOT)
     assert r.returncode == 0, r.stdout[-3000:] + r.stderr[-3000:]
     assert " OK" in r.stdout
+
+
+@pytest.mark.gpu
+def test_cli_overlap_gpus2_writes_the_same_bytes(tmp_path):
+    """`phasm overlap --gpus 2` (one process per GPU over the TCP rendezvous, no torch) against
+    `--gpus 1`: header and S lines byte-identical in order, E lines identical as lines in order too
+    (both routes emit canonical order)."""
+    if _n_gpus() < 2:
+        pytest.skip("needs >= 2 GPUs")
+    from phasm_b200 import synth
+    sh = synth.CONFIGS[2].scaled(0.01)
+    buf, off, names = synth.generate(sh)
+    fa = tmp_path / "reads.fasta"
+    with open(fa, "w") as f:
+        for i, n in enumerate(names):
+            f.write(">%s\n%s\n" % (n, buf[int(off[i]):int(off[i + 1])].tobytes().decode()))
+    outs = []
+    for g in (1, 2):
+        out = tmp_path / ("out%d.gfa" % g)
+        r = subprocess.run([sys.executable, "-m", "phasm", "overlap", "-l", str(sh.min_length), "--gpus", str(g),
+                            "--stats", "json", "-o", str(out), str(fa)], capture_output=True, text=True, timeout=600, cwd=ROOT)
+        assert r.returncode == 0, r.stdout[-2000:] + r.stderr[-2000:]
+        assert "phasm_overlap_stats" in r.stderr
+        outs.append(open(out, "rb").read())
+    assert outs[0] == outs[1] and outs[0].count(b"\nE\t") > 1000
+
+
+@pytest.mark.gpu
+def test_fasta_shard_ingest_builds_the_same_entry_table_on_every_rank(tmp_path):
+    """ovl_add_fasta_shard: what every rank of `phasm overlap --gpus N` does with the same file.  No
+    communicator is needed to check the ingest, so three 'ranks' are three objects on one GPU."""
+    from phasm_b200.overlapper import ExactOverlapper
+    rng = np.random.default_rng(5)
+    lens = [int(x) for x in rng.integers(1, 4000, size=61)] + [0, 7]
+    fa = tmp_path / "r.fasta"
+    with open(fa, "w") as f:
+        for i, n in enumerate(lens):
+            seq = "".join("ACGT"[int(c)] for c in rng.integers(0, 4, size=n))
+            f.write(">read%d some description\n" % i)
+            for k in range(0, n, 70):
+                f.write(seq[k:k + 70] + "\n")
+    world = 3
+    ref = ExactOverlapper()
+    assert ref.add_fasta(str(fa)) == len(lens)
+    ids, lengths = ref.ids(), ref.lengths().tolist()
+    ref.close()
+    covered = 0
+    for r in range(world):
+        ov = ExactOverlapper()
+        n, lo, hi = ov.add_fasta_shard(str(fa), r, world)
+        assert n == len(lens) and lo == covered and lo <= hi
+        covered = hi
+        assert ov.ids() == ids and ov.lengths().tolist() == lengths       # same table everywhere
+        if hi > lo:   # the rank's share is about 1/world of the bases
+            assert abs(sum(lens[lo:hi]) - sum(lens) / world) <= max(lens)
+        ov.close()
+    assert covered == len(lens)
