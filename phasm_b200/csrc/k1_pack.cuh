@@ -25,16 +25,15 @@
 namespace ovl {
 
 // K0 (run when the entry table is uploaded, not per pass): the maps that tell a warp which
-// entry a tile of work belongs to -- tile_ent for K1 (tiles of 2048 bases inside ONE forward
-// entry), tile_idx for the scan (tiles of 32 consecutive granules of the packed array: index into
-// `reg`, the entries in granule order, of the entry holding the tile's first granule; lanes walk
-// forward from there).  4 bytes per 2048 bases instead of the 4 bytes per granule a
-// granule -> entry array costs (52 MB of extra scan traffic on config 2).
+// entry a tile of work belongs to -- tile_ent for K1 (tiles of 2048 bases = 128 sixteen-base units
+// inside ONE forward entry) and scan_tiles for the scan (tiles of 32 granules inside ONE entry of
+// either strand: one 16-byte record {first granule, entry, length, first granule's index in the
+// entry} per tile, so that a warp learns everything about its tile from a single uniform load).
+// 16 bytes per 2048 bases instead of the 4 bytes per granule a granule -> entry array costs
+// (52 MB of extra scan traffic on config 2 in round 1).
 struct ScanRanges {
-    uint32_t g_begin[2], g_end[2];  // granule ranges of the local A entries: forward-region slice, twin-region slice
-    uint32_t i_begin[2], i_end[2];  // the same ranges as indices into `reg`
-    uint32_t t_begin[2];            // first tile of each range in the concatenated tile space
-    uint32_t n_tiles;
+    uint32_t g_begin[2], g_end[2];  // granule ranges of the local entries: forward-region slice, twin-region slice
+    uint32_t n_tiles;               // scan tiles of the local entries
 };
 
 __global__ void __launch_bounds__(256) k0_tile_ent(const uint32_t* __restrict__ tile0, uint32_t* __restrict__ tile_ent,
@@ -48,20 +47,17 @@ __global__ void __launch_bounds__(256) k0_tile_ent(const uint32_t* __restrict__ 
     }
 }
 
-__global__ void __launch_bounds__(256) k0_tile_idx(const uint4* __restrict__ reg, uint32_t* __restrict__ tile_idx,
-                                                   const ScanRanges R) {
+// stile0[e - e_begin] = first scan tile of local entry e (prefix sum of ceil(granules / 32))
+__global__ void __launch_bounds__(256) k0_scan_tiles(const uint32_t* __restrict__ stile0, const uint32_t* __restrict__ gran0,
+                                                     const uint32_t* __restrict__ len, uint4* __restrict__ scan_tiles,
+                                                     uint32_t e_begin, uint32_t e_end) {
     const uint32_t lane = threadIdx.x & 31;
     const uint32_t warp = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
     const uint32_t nwarps = (gridDim.x * blockDim.x) >> 5;
-#pragma unroll
-    for (int r = 0; r < 2; ++r) {
-        const uint32_t gb = R.g_begin[r];
-        for (uint32_t i = R.i_begin[r] + warp; i < R.i_end[r]; i += nwarps) {
-            const uint4 rec = reg[i];
-            const uint32_t o0 = rec.x - gb, o1 = o0 + rec.w;  // granule offsets inside the range
-            const uint32_t t0 = (o0 + 31) >> 5, t1 = (o1 + 31) >> 5;
-            for (uint32_t t = t0 + lane; t < t1; t += 32) tile_idx[R.t_begin[r] + t] = i;
-        }
+    for (uint32_t e = e_begin + warp; e < e_end; e += nwarps) {
+        const uint32_t t0 = stile0[e - e_begin], t1 = stile0[e - e_begin + 1];
+        const uint32_t g0 = gran0[e], L = len[e];
+        for (uint32_t t = t0 + lane; t < t1; t += 32) scan_tiles[t] = make_uint4(g0 + 32u * (t - t0), e, L, 32u * (t - t0));
     }
 }
 

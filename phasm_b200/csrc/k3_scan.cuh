@@ -4,11 +4,10 @@
 // of walking a suffix tree to learn which suffixes of A end at a node on the path to B's leaf,
 // A positions look their k-mer up among the indexed B k-mers (k2_anchor.cuh).
 //
-// Mapping: a warp owns a tile of 32 consecutive granules (2048 bases) of the local A ranges;
-// each lane loads its granule with ONE coalesced 128-bit load (512 B per warp) and takes the
-// following word from the next lane by shuffle (the k-mer carry across granules).  The entry a
-// granule belongs to comes from the tile -> entry map (k0_tile_idx) and a short forward walk
-// over `reg`, the entries in granule order.
+// Mapping: a warp owns a tile of 32 consecutive granules (2048 bases) of ONE local entry (one
+// 16-byte tile record from k0_scan_tiles tells it which); each lane loads its granule with ONE
+// coalesced 128-bit load (512 B per warp) and takes the following word from the next lane by
+// shuffle (the k-mer carry across granules).  Everything about the entry is warp-uniform.
 //
 // The sparse scan (stride >= 2; stride 64 whenever l >= 95) is split in two kernels, because the
 // two halves want different shapes:
@@ -34,6 +33,7 @@
 #pragma once
 #include "k1_pack.cuh"
 #include "k2_anchor.cuh"
+#include "k6_exchange.cuh"
 #include "ovl_common.cuh"
 
 namespace ovl {
@@ -44,10 +44,9 @@ typedef Sink<Surv> SurvSink;
 
 struct ScanParams {
     const uint4* packed;        // granules
-    const uint4* reg;           // [M+1] entries in granule order {gran0, entry, len, granules}
-    const uint32_t* tile_idx;   // [n_tiles] index into reg of the entry holding the tile's first granule
+    const uint4* tiles;         // [n_tiles] {first granule, entry, length, index of the first granule in the entry}
+    uint32_t n_tiles;
     const uint2* ent;           // [M] {gran0, len}
-    ScanRanges R;               // the local A granules
     uint32_t l;                 // min overlap length (>= 1)
     int k;                      // anchor length
     int stride_log2;
@@ -59,20 +58,6 @@ struct ScanParams {
     CandSink sink;
     MirrorRule mirror;          // on: emit only the candidates that verify for themselves
 };
-
-// granule of lane `lane` of tile t, and whether it exists
-__device__ __forceinline__ bool tile_granule(const ScanRanges& R, uint32_t t, uint32_t lane, uint32_t& g) {
-    const int r = t >= R.t_begin[1] ? 1 : 0;
-    g = R.g_begin[r] + (t - R.t_begin[r]) * 32u + lane;
-    return g < R.g_end[r];
-}
-
-// entry record of granule g, walking forward from the tile's first entry
-__device__ __forceinline__ uint4 entry_of(const uint4* __restrict__ reg, uint32_t i, uint32_t g) {
-    uint4 r = __ldg(reg + i);
-    while (g >= r.x + r.w) r = __ldg(reg + ++i);  // the sentinel reg[M] = {G, 0, 0, 0} stops the walk
-    return r;
-}
 
 // candidates of one (a, q) probe whose key resolved to list pointer `ptr` (warp-converged walk)
 __device__ __forceinline__ void walk_list(const ScanParams& P, uint32_t owner, uint32_t ptr, uint32_t a, uint32_t la,
@@ -101,15 +86,19 @@ __device__ __forceinline__ void walk_list(const ScanParams& P, uint32_t owner, u
 // ---- sparse path, pass 1 ------------------------------------------------------------------
 // SL >= 0: the stride is the compile-time constant 2^SL (6, 5, 4 and 3 are instantiated: 1, 2, 4 or
 // 8 k-mers per granule at fixed offsets, loops fully unrolled); SL < 0: read it from the parameters.
-// The warp's NEXT tile is loaded before the current one is processed.
+// Two tiles are in flight per warp: the tile record of tile i+2 and the granule of tile i+1 are
+// requested before tile i is hashed, so the only exposed dependent load of a tile is its bitmap
+// word.  Stride 64 / 32 (one or two probes per lane) keep the hashes in registers and place the
+// survivors with one warp prefix sum; smaller strides use a ballot round per probe.
 template <int SL>
 __global__ void __launch_bounds__(256) k3_filter(const ScanParams P) {
     __shared__ Surv s_buf[8][WBUF / 2];
+    constexpr uint32_t SCAP = WBUF / 2;
     const uint32_t lane = threadIdx.x & 31;
     const uint32_t wib = threadIdx.x >> 5;
     const uint32_t warp = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
     const uint32_t nwarps = (gridDim.x * blockDim.x) >> 5;
-    const uint32_t n_tiles = P.R.n_tiles;
+    const uint32_t n_tiles = P.n_tiles;
     const uint64_t kmask = kmer_mask(P.k);
     const uint64_t* packed64 = reinterpret_cast<const uint64_t*>(P.packed);
     const int sl = SL >= 0 ? SL : P.stride_log2;
@@ -118,74 +107,142 @@ __global__ void __launch_bounds__(256) k3_filter(const ScanParams P) {
     Surv* buf = s_buf[wib];
     uint32_t nbuf = 0;
 
-    uint4 v_nx = make_uint4(0, 0, 0, 0);
-    uint32_t i_nx = 0;
+    // pipeline: rec_cur / v_cur = this tile; rec_nx = the next tile's record (its granule is
+    // requested at the top of the iteration); the record after that is requested there too
+    uint4 rec_cur = make_uint4(0, 0, 0, 0), rec_nx = rec_cur, v_cur = rec_cur;
     if (warp < n_tiles) {
-        uint32_t g;
-        if (tile_granule(P.R, warp, lane, g)) v_nx = ldg_stream(P.packed + g);
-        i_nx = __ldg(P.tile_idx + warp);
+        rec_cur = __ldg(P.tiles + warp);
+        if (warp + nwarps < n_tiles) rec_nx = __ldg(P.tiles + warp + nwarps);
+        if (rec_cur.w + lane < ((rec_cur.z + 63u) >> 6)) v_cur = ldg_stream(P.packed + rec_cur.x + lane);
     }
     for (uint32_t tile = warp; tile < n_tiles; tile += nwarps) {
-        uint32_t g;
-        const bool inr = tile_granule(P.R, tile, lane, g);
-        const uint4 v = v_nx;
-        const uint32_t i0 = i_nx;
-        if (tile + nwarps < n_tiles) {  // prefetch the next tile of this warp
-            uint32_t gn;
-            if (tile_granule(P.R, tile + nwarps, lane, gn)) v_nx = ldg_stream(P.packed + gn);
-            i_nx = __ldg(P.tile_idx + tile + nwarps);
-        }
+        const uint4 rec = rec_cur;
+        const uint4 v = v_cur;
+        uint4 rec_n2 = make_uint4(0, 0, 0, 0);
+        if (tile + 2 * nwarps < n_tiles) rec_n2 = __ldg(P.tiles + tile + 2 * nwarps);
+        v_cur = make_uint4(0, 0, 0, 0);
+        if (tile + nwarps < n_tiles && rec_nx.w + lane < ((rec_nx.z + 63u) >> 6))
+            v_cur = ldg_stream(P.packed + rec_nx.x + lane);
+        rec_cur = rec_nx;
+        rec_nx = rec_n2;
+
+        const uint32_t a = rec.y, L = rec.z;
+        const uint32_t u = rec.w + lane;  // granule of this lane inside the entry
+        const bool inr = u < ((L + 63u) >> 6);
+        const uint32_t pos0 = u * GRAN_BASES;
         const uint64_t w0 = (uint64_t)v.x | ((uint64_t)v.y << 32);
         const uint64_t w1 = (uint64_t)v.z | ((uint64_t)v.w << 32);
         uint64_t w2 = 0;
         if (sl < 5) {  // k-mers that start in the second word run into the next granule
             w2 = __shfl_down_sync(FULL, w0, 1);
-            if (lane == 31) w2 = inr ? packed64[2ull * (g + 1)] : 0;  // a spare granule follows the array
+            if (lane == 31) w2 = inr ? packed64[2ull * (rec.x + lane + 1)] : 0;  // a spare granule follows the array
         }
-        // the filter bit of every probed position of this granule (independent loads, issued before
-        // the entry record is looked at)
-        uint32_t fbits = 0;
-        if (inr) {
+        // probes q = pos0 + off that can start a row: |a| - p >= l for some p = q - delta,
+        // delta < stride, i.e. at least q + k <= |a| (the exact test is in k3_resolve)
+        uint32_t nv = 0;
+        if (inr && L >= P.l && pos0 + (uint32_t)P.k <= L) nv = ((L - (uint32_t)P.k - pos0) >> sl) + 1u;
+        if (nv > n_probe) nv = n_probe;
+
+        if (SL >= 5) {
+            // ---- one or two probes per lane: hashes stay in registers ----
+            constexpr int NP = SL == 6 ? 1 : 2;
+            uint64_t h[NP];
+            uint32_t pass = 0;
+#pragma unroll
+            for (int j = 0; j < NP; ++j) {
+                const uint64_t x = (j == 0 ? w0 : w1) & kmask;
+                h[j] = mix64(x);
+                if ((uint32_t)j < nv) {
+                    const uint64_t bit = bitmap_bit(h[j], nr, P.bm_bits);
+                    pass |= ((__ldg(P.filter + (bit >> 5)) >> (bit & 31)) & 1u) << j;
+                }
+            }
+            const uint32_t cnt = __popc(pass);
+            uint32_t incl = cnt;
+#pragma unroll
+            for (int d = 1; d < 32; d <<= 1) {
+                const uint32_t t = __shfl_up_sync(FULL, incl, d);
+                if (lane >= (uint32_t)d) incl += t;
+            }
+            const uint32_t total = __shfl_sync(FULL, incl, 31);
+            if (total) {  // warp-uniform
+                if (nbuf + total > SCAP) wbuf_flush(buf, nbuf, P.surv, lane);
+                uint32_t o = nbuf + incl - cnt;
+#pragma unroll
+                for (int j = 0; j < NP; ++j)
+                    if ((pass >> j) & 1u) buf[o++] = make_ulonglong2(h[j], ((uint64_t)a << 32) | (pos0 + 32u * j));
+                nbuf += total;
+                __syncwarp();
+            }
+        } else {
+            // ---- 4 or more probes per lane: one ballot round per probe ----
+            uint32_t hitmask = 0;
+            if (nv) {
 #pragma unroll 8
-            for (uint32_t j = 0; j < n_probe; ++j) {
-                const uint32_t off = j << sl;
-                const uint64_t x = (off < 32 ? kmer_at(w0, w1, off) : kmer_at(w1, w2, off - 32)) & kmask;
-                const uint64_t bit = bitmap_bit(mix64(x), nr, P.bm_bits);
-                fbits |= ((__ldg(P.filter + (bit >> 5)) >> (bit & 31)) & 1u) << j;
+                for (uint32_t j = 0; j < n_probe; ++j) {
+                    const uint32_t off = j << sl;
+                    const uint64_t x = (off < 32 ? kmer_at(w0, w1, off) : kmer_at(w1, w2, off - 32)) & kmask;
+                    const uint64_t bit = bitmap_bit(mix64(x), nr, P.bm_bits);
+                    hitmask |= ((__ldg(P.filter + (bit >> 5)) >> (bit & 31)) & 1u) << j;
+                }
+                hitmask = nv >= 32 ? hitmask : (hitmask & ((1u << nv) - 1u));
             }
-        }
-        uint32_t hitmask = 0, a = 0, pos0 = 0;
-        if (inr) {
-            const uint4 rec = entry_of(P.reg, i0, g);
-            a = rec.y;
-            const uint32_t L = rec.z;
-            pos0 = (g - rec.x) * GRAN_BASES;
-            // probes q = pos0 + off that can start a row: |a| - p >= l for some p = q - delta,
-            // delta < stride, i.e. at least q + k <= |a| (the exact test is in k3_resolve)
-            if (L >= P.l && pos0 + (uint32_t)P.k <= L) {
-                const uint32_t nv = ((L - (uint32_t)P.k - pos0) >> sl) + 1u;
-                hitmask = nv >= 32 ? fbits : (fbits & ((1u << nv) - 1u));
+            while (__any_sync(FULL, hitmask != 0)) {
+                Surv r = make_ulonglong2(0, 0);
+                const bool have = hitmask != 0;
+                if (have) {
+                    const uint32_t j = __ffs(hitmask) - 1;
+                    hitmask &= hitmask - 1;
+                    const uint32_t off = j << sl;
+                    const uint64_t x = (off < 32 ? kmer_at(w0, w1, off) : kmer_at(w1, w2, off - 32)) & kmask;
+                    r.x = mix64(x);
+                    r.y = ((uint64_t)a << 32) | (pos0 + off);
+                }
+                const unsigned m = __ballot_sync(FULL, have);
+                if (nbuf + 32 > SCAP) wbuf_flush(buf, nbuf, P.surv, lane);
+                if (have) buf[nbuf + __popc(m & ((1u << lane) - 1u))] = r;
+                nbuf += __popc(m);
+                __syncwarp();
             }
-        }
-        while (__any_sync(FULL, hitmask != 0)) {
-            Surv rec = make_ulonglong2(0, 0);
-            const bool have = hitmask != 0;
-            if (have) {
-                const uint32_t j = __ffs(hitmask) - 1;
-                hitmask &= hitmask - 1;
-                const uint32_t off = j << sl;
-                const uint64_t x = (off < 32 ? kmer_at(w0, w1, off) : kmer_at(w1, w2, off - 32)) & kmask;
-                rec.x = mix64(x);
-                rec.y = ((uint64_t)a << 32) | (pos0 + off);
-            }
-            const unsigned m = __ballot_sync(FULL, have);
-            if (nbuf + 32 > WBUF / 2) wbuf_flush(buf, nbuf, P.surv, lane);
-            if (have) buf[nbuf + __popc(m & ((1u << lane) - 1u))] = rec;
-            nbuf += __popc(m);
-            __syncwarp();
         }
     }
     if (nbuf) wbuf_flush(buf, nbuf, P.surv, lane);
+}
+
+// ---- sparse path, N > 1 GPUs: survivors to the rank that owns their k-mer -----------------------
+struct ProbeRouteParams {
+    const Surv* items;                // survivors of this rank's filter pass
+    const unsigned long long* n_ptr;
+    uint64_t cap;
+    uint32_t nr, me;
+    Surv* inbox[MAX_RANKS];                  // probe list of every rank (peer-mapped)
+    unsigned long long* inbox_n[MAX_RANKS];  // its append counter (ArenaHdr::scan_n)
+    uint64_t inbox_cap[MAX_RANKS];
+};
+
+__global__ void __launch_bounds__(256) k3_route(const ProbeRouteParams P) {
+    const uint32_t lane = threadIdx.x & 31;
+    const unsigned long long n_all = *P.n_ptr;
+    const uint64_t n = n_all < P.cap ? n_all : P.cap;
+    const uint64_t nthreads = (uint64_t)gridDim.x * blockDim.x;
+    for (uint64_t i0 = ((uint64_t)blockIdx.x * blockDim.x + threadIdx.x) & ~31ull; i0 < n; i0 += nthreads) {
+        const uint64_t i = i0 + lane;
+        Surv rec = make_ulonglong2(0, 0);
+        uint32_t dest = 0xffffffffu;
+        if (i < n) {
+            rec = P.items[i];
+            dest = owner_of_hash(rec.x, P.nr);
+        }
+        const unsigned grp = __match_any_sync(FULL, dest);
+        const uint32_t leader = __ffs(grp) - 1;
+        const uint32_t rank_in = __popc(grp & ((1u << lane) - 1u));
+        unsigned long long base = 0;
+        if (dest != 0xffffffffu && lane == leader)
+            base = atomicAdd_system(P.inbox_n[dest], (unsigned long long)__popc(grp));
+        base = __shfl_sync(FULL, base, leader);
+        if (dest != 0xffffffffu && base + rank_in < P.inbox_cap[dest]) P.inbox[dest][base + rank_in] = rec;
+    }
+    __threadfence_system();
 }
 
 // ---- sparse path, pass 2 ------------------------------------------------------------------
@@ -230,7 +287,7 @@ __global__ void __launch_bounds__(1024, 1) k3_scan(const ScanParams P) {
     const uint32_t lane = threadIdx.x & 31;
     const uint32_t warp = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
     const uint32_t nwarps = (gridDim.x * blockDim.x) >> 5;
-    const uint32_t n_tiles = P.R.n_tiles;
+    const uint32_t n_tiles = P.n_tiles;
     const uint64_t kmask = kmer_mask(P.k);
     const uint64_t* packed64 = reinterpret_cast<const uint64_t*>(P.packed);
     const int fwb = P.bm_bits;
@@ -238,19 +295,17 @@ __global__ void __launch_bounds__(1024, 1) k3_scan(const ScanParams P) {
     uint32_t nbuf = 0;
 
     for (uint32_t tile = warp; tile < n_tiles; tile += nwarps) {
-        uint32_t g;
-        const bool inr = tile_granule(P.R, tile, lane, g);
+        const uint4 rec = __ldg(P.tiles + tile);
+        const uint32_t a = rec.y, la = rec.z;
+        const uint32_t g = rec.x + lane;
+        const bool inr = rec.w + lane < ((la + 63u) >> 6);
+        const uint32_t pos0 = (rec.w + lane) * GRAN_BASES;
         uint64_t w0 = 0, w1 = 0;
-        uint32_t a = 0, pos0 = 0, la = 0;
         int nvalid = 0;
         if (inr) {
             const uint4 v = ldg_stream(P.packed + g);
             w0 = (uint64_t)v.x | ((uint64_t)v.y << 32);
             w1 = (uint64_t)v.z | ((uint64_t)v.w << 32);
-            const uint4 rec = entry_of(P.reg, __ldg(P.tile_idx + tile), g);
-            a = rec.y;
-            la = rec.z;
-            pos0 = (g - rec.x) * GRAN_BASES;
             // positions p in [pos0, pos0+64) with L - p >= l
             const int64_t nv = (int64_t)la - (int64_t)P.l + 1 - (int64_t)pos0;
             nvalid = nv <= 0 ? 0 : (nv >= GRAN_BASES ? GRAN_BASES : (int)nv);

@@ -9,9 +9,13 @@
 //     id into the peer's flag word (same stream: ordered behind the data);
 //   * a consumer waits with k_wait (one warp spinning on its own arena's flag words, bounded by
 //     a timeout) -- the only kernels that ever wait, and they wait on OTHER GPUs only;
-//   * k6_route ships every verified hit key to the rank that owns its A entry: the keys are
-//     appended straight into the owner's hit list with one system-scope atomicAdd per
-//     (warp, destination) on the owner's counter and plain stores over NVLink;
+//   * k3_route ships every scan survivor (16 bytes: k-mer hash, A entry, position) to the rank
+//     that owns the k-mer's slice of the anchor table, k6_route every verified hit key to the rank
+//     that owns its A entry: the items are appended straight into the owner's list with one
+//     system-scope atomicAdd per (warp, destination) on the owner's counter and plain stores over
+//     NVLink (lanes with the same destination write consecutive slots).  Looking the table up
+//     remotely instead (one 8-byte peer load per probe) was measured first: every such load moves
+//     a 32-byte sector plus packet headers, and the scan of 2 GPUs took 2.2x the time of one;
 //   * k9_push_rows copies a rank's rows into rank 0's row array at the offset given by the row
 //     counts the ranks published to each other.
 //
@@ -23,7 +27,7 @@ namespace ovl {
 
 // phases a rank signals to its peers; flag[k][s] in MY arena header = the last step in which rank
 // s completed phase k towards me
-enum Flag { F_PRE = 0, F_FILT, F_FWD, F_HITS, F_ROWCNT, F_ROWS, F_STATUS, F_COUNT };
+enum Flag { F_PRE = 0, F_FILT, F_SCAN, F_FWD, F_HITS, F_ROWCNT, F_ROWS, F_STATUS, F_COUNT };
 
 constexpr int STATUS_WORDS = 8;
 // status vector a rank publishes to everyone at the end of a pass
@@ -34,6 +38,7 @@ struct alignas(256) ArenaHdr {
     unsigned long long rowcnt[MAX_RANKS];
     unsigned long long status[MAX_RANKS][STATUS_WORDS];
     unsigned long long inbox_n;    // hit keys appended to this rank's hit list (local and remote atomics)
+    unsigned long long scan_n;     // scan survivors appended to this rank's probe list (idem)
     unsigned long long step_word;  // current step id: the source of the 8-byte signal copies
     unsigned long long abort;      // != 0: a wait timed out, the pass is void
 };
@@ -171,6 +176,7 @@ struct StatusParams {
     unsigned long long* st;              // [STATUS_WORDS] this rank's slot in its own arena
     const unsigned long long* ctr;       // device counter block
     int c_err, c_ncand, c_nscan, c_nstage, c_flags;
+    const unsigned long long* n_probes;  // this rank's probe list (scan survivors routed to it)
     const unsigned long long* n_hits;
     const unsigned long long* n_rows;
     const unsigned long long* abort_word;
@@ -179,7 +185,8 @@ struct StatusParams {
 
 __global__ void k9_status(const StatusParams P) {
     if (threadIdx.x != 0 || blockIdx.x != 0) return;
-    const unsigned long long ncand = P.ctr[P.c_ncand], nscan = P.ctr[P.c_nscan], nstage = P.ctr[P.c_nstage];
+    const unsigned long long ncand = P.ctr[P.c_ncand], nstage = P.ctr[P.c_nstage];
+    const unsigned long long nscan = P.ctr[P.c_nscan] > *P.n_probes ? P.ctr[P.c_nscan] : *P.n_probes;
     const unsigned long long nhits = *P.n_hits, nrows = *P.n_rows;
     unsigned long long fl = P.ctr[P.c_flags] | (*P.abort_word ? STF_TIMEOUT : 0ull);
     if (ncand > P.cap_cand || nscan > P.cap_scan || nstage > P.cap_stage || nhits > P.cap_hits || nrows > P.cap_rows)

@@ -90,7 +90,8 @@ enum Ctr {
 // byte offsets of the pieces of an arena (the header sits at 0); published to the peers
 struct ArenaLayout {
     uint64_t bytes;
-    uint64_t off_pre, off_packed, off_filter, off_table, off_next, off_inbox, off_rows;
+    uint64_t off_pre, off_packed, off_filter, off_table, off_next, off_scan, off_inbox, off_rows;
+    uint64_t scan_cap;   // scan survivors (probe list)
     uint64_t inbox_cap;  // hit keys
     uint64_t rows_cap;   // rows (rank 0 of a multi-GPU job: the rows of all ranks)
 };
@@ -112,6 +113,8 @@ struct ovl_ctx {
     cudaEvent_t ev_pack = nullptr, ev_k0 = nullptr, ev_prel = nullptr, ev_k2 = nullptr, ev_push = nullptr, ev_sig = nullptr;
     cudaEvent_t ev_chunk[MAX_CHUNKS] = {};
     cudaEvent_t ev_t0 = nullptr, ev_t1 = nullptr;  // ovl_timer_*
+    cudaEvent_t ev_dbg[8] = {};                    // OVL_DEBUG=1: time line of the side streams
+    int debug = 0;
     std::string err;
 
     // ---- host entry store ----
@@ -134,7 +137,7 @@ struct ovl_ctx {
     int pairs = 0;                // 1: entry e ^ 1 is the other strand of entry e, for every e
 
     // ---- device: persistent tables ----
-    DevBuf d_ascii, d_src, d_len, d_flags, d_gran0, d_ent, d_reg, d_tile0, d_tile_ent, d_tile_idx;
+    DevBuf d_ascii, d_src, d_len, d_flags, d_gran0, d_ent, d_tile0, d_tile_ent, d_stile0, d_scan_tiles;
     // ---- device: per-pass working buffers outside the arena ----
     DevBuf d_ctr, d_tmp, d_cand, d_stage, d_scan, d_cnt, d_bkt, d_big, d_peerhdr;
     DevBuf d_fmark, d_fkeep, d_foff, d_frows;  // ovl_filter_rows
@@ -142,7 +145,7 @@ struct ovl_ctx {
     // ---- the arena ----
     DevBuf arena;
     ArenaLayout lay{};
-    uint64_t arena_key[4] = {~0ull, 0, 0, 0};  // {generation, cand_cap, nranks/mirror, epoch} the arena was planned for
+    uint64_t arena_key[4] = {~0ull, 0, 0, 0};  // {generation, cand_cap, nranks/stride/mirror, epoch} the arena was planned for
     uint64_t arena_epoch = 0;                  // bumped by every collective "grow and repeat"
     void* peer_base[ovl::MAX_RANKS] = {};
     ArenaLayout peer_lay[ovl::MAX_RANKS] = {};
@@ -370,7 +373,7 @@ void close_peers(ovl_ctx* c) {
 // exchange the IPC handles and map every peer's arena.  Collective on N > 1: all ranks reach it in
 // the same call (the key changes with the entry table, the rank count, or an overflow every rank
 // learned about from the status exchange).
-int connect_arena(ovl_ctx* c, bool mirror) {
+int connect_arena(ovl_ctx* c, bool mirror, uint64_t scan_cap) {
     using namespace ovl;
     const int nr = c->nranks, me = c->rank;
     const uint32_t M = (uint32_t)c->len.size();
@@ -400,6 +403,8 @@ int connect_arena(ovl_ctx* c, bool mirror) {
     L.off_filter = take(std::max(f_sparse, f_dense));
     L.off_table = take(8ull << table_bits(keys_max, nr));
     L.off_next = take(keys_max * 4);
+    L.scan_cap = scan_cap;
+    L.off_scan = take(scan_cap * 16);
     L.inbox_cap = hit_cap;
     L.off_inbox = take(hit_cap * 8);
     L.rows_cap = rows_total;
@@ -482,7 +487,7 @@ int upload_tables(ovl_ctx* c) {
     auto is_twin = [&](size_t e) { return e > 0 && (c->flags[e] & 1) && !(c->flags[e - 1] & 1); };
     // pass 1: forward region = every entry that is not a twin, in entry order
     uint64_t gf = 0, nt = 0;
-    uint32_t lo = (uint32_t)M, hi = 0, n_fwd = 0;
+    uint32_t lo = (uint32_t)M, hi = 0;
     for (size_t e = 0; e < M; ++e) {
         c->tile0[e] = (uint32_t)nt;
         const uint64_t ge = (c->len[e] + 63u) / 64u;
@@ -490,7 +495,6 @@ int upload_tables(ovl_ctx* c) {
             if (gf + ge >= 0xfffffff0ull) return fail(c, OVL_E_LIMIT, "more than 2^32 granules");
             c->gran0[e] = (uint32_t)gf;
             gf += ge;
-            ++n_fwd;
             // K1 tiles: local non-twin entries (a twin is written by its forward entry's tiles)
             if (c->src[e] != NO_SRC) nt += (4 * ge + PACK_TILE_UNITS - 1) / PACK_TILE_UNITS;
         }
@@ -523,40 +527,32 @@ int upload_tables(ovl_ctx* c) {
     for (size_t e = 0; pairs && e < M; e += 2) pairs = !(c->flags[e] & 1) && (c->flags[e + 1] & 1) && c->len[e] == c->len[e + 1];
     c->pairs = pairs ? 1 : 0;
 
-    // entries in granule (region) order + the local scan ranges
-    std::vector<uint4> reg;
+    // the local granule ranges (what travels / what is scanned) and the scan tiles of the local entries
+    ScanRanges R{};
+    std::vector<uint32_t> stile0;
     try {
-        reg.resize(M + 1);
+        stile0.resize((size_t)(hi - lo) + 1);
     } catch (const std::bad_alloc&) {
         return fail(c, OVL_E_NOMEM, "out of host memory");
     }
-    ScanRanges R{};
     {
-        uint32_t i = 0;
-        bool seen0 = false, seen1 = false;
-        for (int pass = 0; pass < 2; ++pass)
-            for (size_t e = 0; e < M; ++e) {
-                if ((int)is_twin(e) != pass) continue;
-                const uint32_t ge = (c->len[e] + 63u) / 64u;
-                reg[i] = make_uint4(c->gran0[e], (uint32_t)e, c->len[e], ge);
-                if (e >= lo && e < hi) {
-                    bool& seen = pass ? seen1 : seen0;
-                    if (!seen) {
-                        R.g_begin[pass] = c->gran0[e];
-                        R.i_begin[pass] = i;
-                        seen = true;
-                    }
-                    R.g_end[pass] = c->gran0[e] + ge;
-                    R.i_end[pass] = i + 1;
-                }
-                ++i;
+        bool seen[2] = {false, false};
+        uint64_t ntile = 0;
+        for (uint32_t e = lo; e < hi; ++e) {
+            const int r = is_twin(e) ? 1 : 0;
+            const uint32_t ge = (c->len[e] + 63u) / 64u;
+            if (!seen[r]) {
+                R.g_begin[r] = c->gran0[e];
+                seen[r] = true;
             }
-        reg[M] = make_uint4((uint32_t)g, 0, 0, 0);
-        (void)n_fwd;
+            R.g_end[r] = c->gran0[e] + ge;
+            stile0[e - lo] = (uint32_t)ntile;
+            ntile += (ge + 31) / 32;
+        }
+        if (ntile >= 0xfffffff0ull) return fail(c, OVL_E_LIMIT, "too many scan tiles");
+        stile0[hi - lo] = (uint32_t)ntile;
+        R.n_tiles = (uint32_t)ntile;
     }
-    R.t_begin[0] = 0;
-    R.t_begin[1] = (R.g_end[0] - R.g_begin[0] + 31) / 32;
-    R.n_tiles = R.t_begin[1] + (R.g_end[1] - R.g_begin[1] + 31) / 32;
     c->ranges = R;
 
     cudaStream_t st = c->st;
@@ -566,20 +562,21 @@ int upload_tables(ovl_ctx* c) {
         OVL_TRY(dev_ensure(c, c->d_flags, M));
         OVL_TRY(dev_ensure(c, c->d_gran0, M * 4));
         OVL_TRY(dev_ensure(c, c->d_ent, M * 8));
-        OVL_TRY(dev_ensure(c, c->d_reg, (M + 1) * 16));
         OVL_TRY(dev_ensure(c, c->d_tile0, (M + 1) * 4));
         OVL_TRY(dev_ensure(c, c->d_tile_ent, (nt + 1) * 4));
-        OVL_TRY(dev_ensure(c, c->d_tile_idx, ((size_t)R.n_tiles + 1) * 4));
+        OVL_TRY(dev_ensure(c, c->d_stile0, stile0.size() * 4));
+        OVL_TRY(dev_ensure(c, c->d_scan_tiles, ((size_t)R.n_tiles + 1) * 16));
         CK(cudaMemcpyAsync(c->d_tile0.p, c->tile0.data(), (M + 1) * 4, cudaMemcpyHostToDevice, st));
         CK(cudaMemcpyAsync(c->d_src.p, c->src.data(), M * 8, cudaMemcpyHostToDevice, st));
         CK(cudaMemcpyAsync(c->d_len.p, c->len.data(), M * 4, cudaMemcpyHostToDevice, st));
         CK(cudaMemcpyAsync(c->d_flags.p, c->flags.data(), M, cudaMemcpyHostToDevice, st));
         CK(cudaMemcpyAsync(c->d_gran0.p, c->gran0.data(), M * 4, cudaMemcpyHostToDevice, st));
-        CK(cudaMemcpyAsync(c->d_reg.p, reg.data(), (M + 1) * 16, cudaMemcpyHostToDevice, st));
+        CK(cudaMemcpyAsync(c->d_stile0.p, stile0.data(), stile0.size() * 4, cudaMemcpyHostToDevice, st));
         k0_ent_table<<<(unsigned)((M + 255) / 256), 256, 0, st>>>(c->d_gran0.as<uint32_t>(), c->d_len.as<uint32_t>(), c->d_ent.as<uint2>(), (uint32_t)M);
         if (hi > lo) {
             k0_tile_ent<<<c->n_sm * 4, 256, 0, st>>>(c->d_tile0.as<uint32_t>(), c->d_tile_ent.as<uint32_t>(), lo, hi);
-            k0_tile_idx<<<c->n_sm * 4, 256, 0, st>>>(c->d_reg.as<uint4>(), c->d_tile_idx.as<uint32_t>(), R);
+            k0_scan_tiles<<<c->n_sm * 4, 256, 0, st>>>(c->d_stile0.as<uint32_t>(), c->d_gran0.as<uint32_t>(), c->d_len.as<uint32_t>(),
+                                                       c->d_scan_tiles.as<uint4>(), lo, hi);
         }
         CK(cudaGetLastError());
     }
@@ -766,9 +763,9 @@ int run_pass(ovl_ctx* c, uint32_t min_length, bool chunked) {
         const uint64_t hit_cap = mirror ? 3 * c->cand_cap : c->cand_cap;
         const uint64_t scan_cap = dense ? 1 : std::min<uint64_t>(probes + 32, 2 * c->cand_cap + probes / 8 + 4096);
         // ---- the arena (and, on N > 1, the peer mappings) -----------------------------------
-        const uint64_t key[4] = {c->generation, c->cand_cap, ((uint64_t)nr << 1) | (uint64_t)mirror, c->arena_epoch};
+        const uint64_t key[4] = {c->generation, c->cand_cap, ((uint64_t)nr << 8) | ((uint64_t)slog << 1) | (uint64_t)mirror, c->arena_epoch};
         if (memcmp(key, c->arena_key, sizeof key) != 0 || !c->arena.p) {
-            OVL_TRY(connect_arena(c, mirror));
+            OVL_TRY(connect_arena(c, mirror, scan_cap));
             memcpy(c->arena_key, key, sizeof key);
         }
         const ArenaLayout& L = c->lay;
@@ -779,11 +776,13 @@ int run_pass(ovl_ctx* c, uint32_t min_length, bool chunked) {
         uint32_t* d_filter = at<uint32_t>(A, L.off_filter);
         Slot* d_table = at<Slot>(A, L.off_table);
         uint32_t* d_next = at<uint32_t>(A, L.off_next);
+        Surv* d_probes = at<Surv>(A, L.off_scan);
         uint64_t* d_inbox = at<uint64_t>(A, L.off_inbox);
         Row* d_rows = at<Row>(A, L.off_rows);
         OVL_TRY(dev_ensure(c, c->d_cand, hit_cap * 8, false));  // candidates, later the bucketed hit keys
         if (route) OVL_TRY(dev_ensure(c, c->d_stage, hit_cap * 8, false));
-        if (!dense) OVL_TRY(dev_ensure(c, c->d_scan, scan_cap * sizeof(Surv), false));
+        const bool route_probes = !dense && nr > 1;  // scan survivors travel to the rank that owns their k-mer
+        if (route_probes) OVL_TRY(dev_ensure(c, c->d_scan, scan_cap * sizeof(Surv), false));
         OVL_TRY(dev_ensure(c, c->d_cnt, c->cand_cap * 4, false));  // survivor list of the verifier's head
         OVL_TRY(dev_ensure(c, c->d_big, (size_t)M * 4 + 4, false));
         const size_t M1 = (size_t)M + 1;
@@ -803,7 +802,7 @@ int run_pass(ovl_ctx* c, uint32_t min_length, bool chunked) {
         if (chunked) CK(cudaEventRecord(c->ev[E_H2D0], st));
         CK(cudaEventRecord(c->ev[E_PACK0], st));
         CK(cudaMemsetAsync(ctr, 0, C_COUNT * sizeof(uint64_t), st));
-        CK(cudaMemsetAsync(&H->inbox_n, 0, 8, st));
+        CK(cudaMemsetAsync(&H->inbox_n, 0, 16, st));  // inbox_n, scan_n
         CK(cudaMemcpyAsync(&H->step_word, h_step, 8, cudaMemcpyHostToDevice, st));
         CK(cudaEventRecord(c->ev_k0, st));
         CK(cudaStreamWaitEvent(sk, c->ev_k0, 0));
@@ -872,6 +871,7 @@ int run_pass(ovl_ctx* c, uint32_t min_length, bool chunked) {
                                        A + pre_off, pre_bytes, cudaMemcpyDefault, sg));
                 OVL_TRY(signal_copy(c, r, F_PRE, sg));
             }
+            if (c->debug) CK(cudaEventRecord(c->ev_dbg[2], sg));
             CK(cudaStreamWaitEvent(sp, c->ev_pack, 0));
             const uint64_t fwd_bytes = (uint64_t)(R.g_end[0] - R.g_begin[0]) * 16;
             for (int j = 1; j < nr; ++j) {  // ring offsets: at any moment every rank receives from one sender
@@ -882,6 +882,7 @@ int run_pass(ovl_ctx* c, uint32_t min_length, bool chunked) {
                 OVL_TRY(signal_copy(c, r, F_FWD, sp));
             }
             CK(cudaEventRecord(c->ev_push, sp));
+            if (c->debug) CK(cudaEventRecord(c->ev_dbg[4], sp));
         }
         CK(cudaEventRecord(c->ev[E_ANCHOR0], st));
 
@@ -895,6 +896,7 @@ int run_pass(ovl_ctx* c, uint32_t min_length, bool chunked) {
         }
         if (have_anchors) {
             if (nr > 1) OVL_TRY(wait_flags(c, F_PRE, sk, &launches));
+            if (c->debug) CK(cudaEventRecord(c->ev_dbg[0], sk));
             const size_t table_bytes = sizeof(Slot) << tbits;
             CK(cudaMemsetAsync(d_table, 0xff, table_bytes, sk));  // EMPTY_SLOT
             const uint64_t slice_bytes = dense ? (4ull << bm_bits) : ((1ull << bm_bits) / 8);
@@ -921,6 +923,7 @@ int run_pass(ovl_ctx* c, uint32_t min_length, bool chunked) {
             ++launches;
             CK(cudaGetLastError());
             CK(cudaEventRecord(c->ev_k2, sk));
+            if (c->debug) CK(cudaEventRecord(c->ev_dbg[1], sk));
             if (nr > 1) {  // my filter slice (sparse path) and "my partition is ready" to everyone
                 CK(cudaStreamWaitEvent(sg, c->ev_k2, 0));
                 for (int j = 1; j < nr; ++j) {
@@ -931,6 +934,7 @@ int run_pass(ovl_ctx* c, uint32_t min_length, bool chunked) {
                     OVL_TRY(signal_copy(c, r, F_FILT, sg));
                 }
                 CK(cudaEventRecord(c->ev_sig, sg));
+                if (c->debug) CK(cudaEventRecord(c->ev_dbg[3], sg));
             }
             CK(cudaStreamWaitEvent(st, c->ev_k2, 0));
             if (nr > 1) OVL_TRY(wait_flags(c, F_FILT, st, &launches));
@@ -943,10 +947,9 @@ int run_pass(ovl_ctx* c, uint32_t min_length, bool chunked) {
         if (have_anchors && R.n_tiles) {
             ScanParams P;
             P.packed = d_packed;
-            P.reg = c->d_reg.as<uint4>();
-            P.tile_idx = c->d_tile_idx.as<uint32_t>();
+            P.tiles = c->d_scan_tiles.as<uint4>();
+            P.n_tiles = R.n_tiles;
             P.ent = c->d_ent.as<uint2>();
-            P.R = R;
             P.l = l;
             P.k = k;
             P.stride_log2 = slog;
@@ -954,8 +957,9 @@ int run_pass(ovl_ctx* c, uint32_t min_length, bool chunked) {
             P.bm_bits = bm_bits;
             P.T = T;
             P.fmt = fmt;
-            P.surv.out = c->d_scan.as<Surv>();
-            P.surv.n_out = reinterpret_cast<unsigned long long*>(ctr + C_NSCAN);
+            // 1 GPU: the filter pass appends straight to the probe list the resolve pass reads
+            P.surv.out = route_probes ? c->d_scan.as<Surv>() : d_probes;
+            P.surv.n_out = route_probes ? reinterpret_cast<unsigned long long*>(ctr + C_NSCAN) : &H->scan_n;
             P.surv.cap = scan_cap;
             P.sink.out = c->d_cand.as<uint64_t>();
             P.sink.n_out = reinterpret_cast<unsigned long long*>(ctr + C_NCAND);
@@ -971,8 +975,30 @@ int run_pass(ovl_ctx* c, uint32_t min_length, bool chunked) {
                     case 3: k3_filter<3><<<blocks, 256, 0, st>>>(P); break;
                     default: k3_filter<-1><<<blocks, 256, 0, st>>>(P); break;
                 }
+                ++launches;
+                if (route_probes) {
+                    ProbeRouteParams Q;
+                    Q.items = c->d_scan.as<Surv>();
+                    Q.n_ptr = reinterpret_cast<const unsigned long long*>(ctr + C_NSCAN);
+                    Q.cap = scan_cap;
+                    Q.nr = (uint32_t)nr;
+                    Q.me = (uint32_t)me;
+                    for (int r = 0; r < nr; ++r) {
+                        Q.inbox[r] = at<Surv>(c->peer_base[r], c->peer_lay[r].off_scan);
+                        Q.inbox_n[r] = &hdr_of(c, r)->scan_n;
+                        Q.inbox_cap[r] = c->peer_lay[r].scan_cap;
+                    }
+                    k3_route<<<kblocks, 256, 0, st>>>(Q);
+                    ++launches;
+                    CK(cudaGetLastError());
+                    OVL_TRY(signal_all(c, F_SCAN, st, &launches));
+                    OVL_TRY(wait_flags(c, F_SCAN, st, &launches));
+                    P.surv.out = d_probes;
+                    P.surv.n_out = &H->scan_n;
+                    P.surv.cap = L.scan_cap;
+                }
                 k3_resolve<<<kblocks, 256, 0, st>>>(P);
-                launches += 2;
+                ++launches;
             } else if (smem_filter) {
                 k3_scan<true><<<nsm, 1024, 32 * WBUF * 8 + (4u << bm_bits), st>>>(P);
                 ++launches;
@@ -1133,6 +1159,7 @@ int run_pass(ovl_ctx* c, uint32_t min_length, bool chunked) {
             SP.c_nscan = C_NSCAN;
             SP.c_nstage = C_NSTAGE;
             SP.c_flags = C_FLAGS;
+            SP.n_probes = &H->scan_n;
             SP.n_hits = &H->inbox_n;
             SP.n_rows = d_nrows;
             SP.abort_word = &H->abort;
@@ -1220,7 +1247,7 @@ int run_pass(ovl_ctx* c, uint32_t min_length, bool chunked) {
         S.compared_bases = c->h_ctr[C_SUMM];
         S.operand_bytes = c->h_ctr[C_SUMB];
         S.big_buckets = (uint32_t)c->h_ctr[C_BIG];
-        S.scan_survivors = c->h_ctr[C_NSCAN];
+        S.scan_survivors = h_status[(size_t)me * STATUS_WORDS + ST_NSCAN];
         uint64_t total = 0;
         for (int r = 0; r < nr; ++r) total += h_rowcnt[r];
         S.rows_local = h_rowcnt[me];
@@ -1232,6 +1259,22 @@ int run_pass(ovl_ctx* c, uint32_t min_length, bool chunked) {
         }
         S.rows = c->n_rows;
         break;
+    }
+    if (c->debug) {
+        auto rel = [&](cudaEvent_t e) {
+            float ms = -1.f;
+            if (cudaEventElapsedTime(&ms, c->ev[E_PACK0], e) != cudaSuccess) {
+                (void)cudaGetLastError();
+                ms = -1.f;
+            }
+            return ms;
+        };
+        fprintf(stderr, "[ovl rank %d step %llu] +ms: pack_end %.3f | sk: pre_wait_end %.3f insert_end %.3f | sg: pre_pushed %.3f filt_pushed %.3f | "
+                        "sp: fwd_pushed %.3f | st: scan0 %.3f verify0 %.3f sort0 %.3f emit0 %.3f gather0 %.3f end %.3f\n",
+                c->rank, (unsigned long long)c->step, rel(c->ev[E_ANCHOR0]), rel(c->ev_dbg[0]), rel(c->ev_dbg[1]),
+                c->nranks > 1 ? rel(c->ev_dbg[2]) : -1.f, c->nranks > 1 ? rel(c->ev_dbg[3]) : -1.f,
+                c->nranks > 1 ? rel(c->ev_dbg[4]) : -1.f, rel(c->ev[E_SCAN0]), rel(c->ev[E_VERIFY0]), rel(c->ev[E_SORT0]),
+                rel(c->ev[E_EMIT0]), rel(c->ev[E_GATHER0]), rel(c->ev[E_END]));
     }
     S.ms_pack = ev_ms(c, E_PACK0, E_ANCHOR0);
     S.ms_anchor = ev_ms(c, E_ANCHOR0, E_SCAN0);
@@ -1301,6 +1344,8 @@ int ovl_create(int device, ovl_ctx** out) {
         for (int i = 0; i < E_COUNT; ++i) CK(cudaEventCreate(&x->ev[i]));
         CK(cudaEventCreate(&x->ev_t0));
         CK(cudaEventCreate(&x->ev_t1));
+        for (int i = 0; i < 8; ++i) CK(cudaEventCreate(&x->ev_dbg[i]));
+        x->debug = getenv("OVL_DEBUG") ? atoi(getenv("OVL_DEBUG")) : 0;
         const size_t hwords = C_COUNT + MAX_RANKS * STATUS_WORDS + MAX_RANKS + 2;
         CK(cudaHostAlloc(reinterpret_cast<void**>(&x->h_ctr), hwords * sizeof(uint64_t), cudaHostAllocDefault));
         memset(x->h_ctr, 0, hwords * sizeof(uint64_t));
@@ -1321,8 +1366,8 @@ void ovl_destroy(ovl_ctx* c) {
     cudaDeviceSynchronize();
     close_peers(c);
     if (c->comm) nccl_dyn::api().CommDestroy(c->comm);
-    DevBuf* bufs[] = {&c->d_ascii, &c->d_src, &c->d_len, &c->d_flags, &c->d_gran0, &c->d_ent, &c->d_reg, &c->d_tile0,
-                      &c->d_tile_ent, &c->d_tile_idx, &c->d_ctr, &c->d_tmp, &c->d_cand, &c->d_stage, &c->d_scan,
+    DevBuf* bufs[] = {&c->d_ascii, &c->d_src, &c->d_len, &c->d_flags, &c->d_gran0, &c->d_ent, &c->d_tile0,
+                      &c->d_tile_ent, &c->d_stile0, &c->d_scan_tiles, &c->d_ctr, &c->d_tmp, &c->d_cand, &c->d_stage, &c->d_scan,
                       &c->d_cnt, &c->d_bkt, &c->d_big, &c->d_peerhdr, &c->d_fmark, &c->d_fkeep, &c->d_foff, &c->d_frows,
                       &c->arena};
     for (DevBuf* b : bufs)
@@ -1335,7 +1380,8 @@ void ovl_destroy(ovl_ctx* c) {
         if (c->ev[i]) cudaEventDestroy(c->ev[i]);
     for (int i = 0; i < MAX_CHUNKS; ++i)
         if (c->ev_chunk[i]) cudaEventDestroy(c->ev_chunk[i]);
-    cudaEvent_t evs[] = {c->ev_pack, c->ev_k0, c->ev_prel, c->ev_k2, c->ev_push, c->ev_sig, c->ev_t0, c->ev_t1};
+    cudaEvent_t evs[] = {c->ev_pack, c->ev_k0, c->ev_prel, c->ev_k2, c->ev_push, c->ev_sig, c->ev_t0, c->ev_t1,
+                         c->ev_dbg[0], c->ev_dbg[1], c->ev_dbg[2], c->ev_dbg[3], c->ev_dbg[4], c->ev_dbg[5], c->ev_dbg[6], c->ev_dbg[7]};
     for (cudaEvent_t e : evs)
         if (e) cudaEventDestroy(e);
     cudaStream_t sts[] = {c->st, c->st_k2, c->st_push, c->st_sig, c->st_h2d};
