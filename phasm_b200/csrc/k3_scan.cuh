@@ -214,35 +214,14 @@ struct ProbeRouteParams {
     const Surv* items;                // survivors of this rank's filter pass
     const unsigned long long* n_ptr;
     uint64_t cap;
-    uint32_t nr, me;
-    Surv* inbox[MAX_RANKS];                  // probe list of every rank (peer-mapped)
-    unsigned long long* inbox_n[MAX_RANKS];  // its append counter (ArenaHdr::scan_n)
-    uint64_t inbox_cap[MAX_RANKS];
+    RouteLists<Surv> lists;           // probe list of every rank (counter: ArenaHdr::scan_n)
 };
 
 __global__ void __launch_bounds__(256) k3_route(const ProbeRouteParams P) {
-    const uint32_t lane = threadIdx.x & 31;
     const unsigned long long n_all = *P.n_ptr;
     const uint64_t n = n_all < P.cap ? n_all : P.cap;
-    const uint64_t nthreads = (uint64_t)gridDim.x * blockDim.x;
-    for (uint64_t i0 = ((uint64_t)blockIdx.x * blockDim.x + threadIdx.x) & ~31ull; i0 < n; i0 += nthreads) {
-        const uint64_t i = i0 + lane;
-        Surv rec = make_ulonglong2(0, 0);
-        uint32_t dest = 0xffffffffu;
-        if (i < n) {
-            rec = P.items[i];
-            dest = owner_of_hash(rec.x, P.nr);
-        }
-        const unsigned grp = __match_any_sync(FULL, dest);
-        const uint32_t leader = __ffs(grp) - 1;
-        const uint32_t rank_in = __popc(grp & ((1u << lane) - 1u));
-        unsigned long long base = 0;
-        if (dest != 0xffffffffu && lane == leader)
-            base = atomicAdd_system(P.inbox_n[dest], (unsigned long long)__popc(grp));
-        base = __shfl_sync(FULL, base, leader);
-        if (dest != 0xffffffffu && base + rank_in < P.inbox_cap[dest]) P.inbox[dest][base + rank_in] = rec;
-    }
-    __threadfence_system();
+    const uint32_t nr = P.lists.nr;
+    route_items<Surv>(P.items, n, P.lists, [nr](const Surv& r) { return owner_of_hash(r.x, nr); }, nullptr);
 }
 
 // ---- sparse path, pass 2 ------------------------------------------------------------------

@@ -97,53 +97,112 @@ __global__ void __launch_bounds__(32) k_signal(ArenaHdr* const* __restrict__ pee
     if (s < nr && s != me) st_release_sys(&peer_hdr[s]->flag[kind][me], step);
 }
 
-// ---- hit routing ------------------------------------------------------------------------
+// Small, urgent pushes (prefix slice, filter slice): plain 16-byte stores into every peer's arena
+// from a few blocks.  (A copy-engine copy of the same bytes queued behind the bulk copy of the
+// packed reads to the same peer and arrived 0.14 ms late at 2 GPUs.)  blockIdx.y picks the peer.
+struct PushTargets {
+    uint4* dst[MAX_RANKS];  // where this rank's slice lives in every peer's arena
+    uint32_t nr, me;
+};
+
+__global__ void __launch_bounds__(256) k_push(const uint4* __restrict__ src, const PushTargets T, uint64_t n16) {
+    const uint32_t r = (T.me + 1u + blockIdx.y) % T.nr;
+    uint4* __restrict__ dst = T.dst[r];
+    for (uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n16; i += (uint64_t)gridDim.x * blockDim.x)
+        dst[i] = src[i];
+    __threadfence_system();
+}
+
+// ---- item routing -----------------------------------------------------------------------
+// Append every item to the list of the rank dest_of(item) says (scan survivors -> owner of the
+// k-mer's table slice; hit keys -> owner of the A entry).  A block takes a tile of 256 * ITEMS
+// items, ranks them per destination in shared memory (warp-aggregated), reserves the space with ONE
+// system-scope atomicAdd per destination on the owner's counter and then stores the items -- lanes
+// with the same destination write consecutive slots.  (The first form reserved per warp: ~150 000
+// atomics on one remote address per pass, ~0.4 ms of serialised NVLink round trips at 2 GPUs.)
+constexpr int ROUTE_ITEMS = 4;
+
+template <class T>
+struct RouteLists {
+    T* inbox[MAX_RANKS];                     // list of every rank (peer-mapped)
+    unsigned long long* inbox_n[MAX_RANKS];  // its append counter (in the owner's ArenaHdr)
+    uint64_t inbox_cap[MAX_RANKS];
+    uint32_t nr, me;
+};
+
+template <class T, class DestFn>
+__device__ __forceinline__ void route_items(const T* __restrict__ items, uint64_t n, const RouteLists<T>& R, DestFn dest_of,
+                                            unsigned long long* n_sent) {
+    __shared__ unsigned int s_cnt[MAX_RANKS];
+    __shared__ unsigned long long s_base[MAX_RANKS];
+    const uint32_t lane = threadIdx.x & 31;
+    const uint64_t tile_items = (uint64_t)blockDim.x * ROUTE_ITEMS;
+    const uint64_t n_tiles = (n + tile_items - 1) / tile_items;
+    if (threadIdx.x < MAX_RANKS) s_cnt[threadIdx.x] = 0;
+    __syncthreads();
+    unsigned long long sent = 0;
+    for (uint64_t tile = blockIdx.x; tile < n_tiles; tile += gridDim.x) {
+        T it[ROUTE_ITEMS];
+        uint32_t dest[ROUTE_ITEMS], off[ROUTE_ITEMS];
+#pragma unroll
+        for (int j = 0; j < ROUTE_ITEMS; ++j) {
+            const uint64_t i = tile * tile_items + (uint64_t)j * blockDim.x + threadIdx.x;
+            dest[j] = 0xffffffffu;
+            if (i < n) {
+                it[j] = items[i];
+                dest[j] = dest_of(it[j]);
+            }
+        }
+#pragma unroll
+        for (int j = 0; j < ROUTE_ITEMS; ++j) {
+            const unsigned grp = __match_any_sync(FULL, dest[j]);
+            const uint32_t leader = __ffs(grp) - 1;
+            uint32_t base = 0;
+            if (lane == leader && dest[j] != 0xffffffffu) base = atomicAdd(&s_cnt[dest[j]], (unsigned)__popc(grp));
+            base = __shfl_sync(FULL, base, leader);
+            off[j] = base + __popc(grp & ((1u << lane) - 1u));
+        }
+        __syncthreads();
+        if (threadIdx.x < R.nr && s_cnt[threadIdx.x])
+            s_base[threadIdx.x] = atomicAdd_system(R.inbox_n[threadIdx.x], (unsigned long long)s_cnt[threadIdx.x]);
+        __syncthreads();
+#pragma unroll
+        for (int j = 0; j < ROUTE_ITEMS; ++j)
+            if (dest[j] != 0xffffffffu) {
+                const unsigned long long pos = s_base[dest[j]] + off[j];
+                if (pos < R.inbox_cap[dest[j]]) R.inbox[dest[j]][pos] = it[j];
+                sent += dest[j] != R.me;
+            }
+        __syncthreads();
+        if (threadIdx.x < MAX_RANKS) s_cnt[threadIdx.x] = 0;
+        __syncthreads();
+    }
+    if (n_sent) {
+#pragma unroll
+        for (int d = 16; d > 0; d >>= 1) sent += __shfl_xor_sync(FULL, sent, d);
+        if (lane == 0 && sent) atomicAdd(n_sent, sent);
+    }
+    __threadfence_system();
+}
+
 // With strand-mirror halving a rank compares one candidate of each strand-mirror pair and
-// produces BOTH hit keys; the twin's A entry may belong to another rank's read range.  Rows are
-// emitted by the rank that owns A (that keeps "smallest p per (a,b)" local).
+// produces BOTH hit keys, and on N > 1 GPUs a candidate is verified by the rank that owns its
+// k-mer, not its A entry.  Rows are emitted by the rank that owns A (that keeps "smallest p per
+// (a,b)" local).
 struct RouteParams {
     const uint64_t* keys;              // verified hit keys of this rank's candidates (staging list)
     const unsigned long long* n_ptr;
     uint64_t cap;
     KeyFmt fmt;
     RankMap map;
-    uint64_t* inbox[MAX_RANKS];               // hit list of every rank (peer-mapped)
-    unsigned long long* inbox_n[MAX_RANKS];   // its append counter (ArenaHdr::inbox_n)
-    uint64_t inbox_cap[MAX_RANKS];
-    uint32_t me;
+    RouteLists<uint64_t> lists;        // hit list of every rank
     unsigned long long* n_sent;        // stat: keys that left this GPU
 };
 
 __global__ void __launch_bounds__(256) k6_route(const RouteParams P) {
-    const uint32_t lane = threadIdx.x & 31;
     const unsigned long long n_all = *P.n_ptr;
     const uint64_t n = n_all < P.cap ? n_all : P.cap;
-    const uint64_t nthreads = (uint64_t)gridDim.x * blockDim.x;
-    unsigned long long sent = 0;
-    for (uint64_t i0 = ((uint64_t)blockIdx.x * blockDim.x + threadIdx.x) & ~31ull; i0 < n; i0 += nthreads) {
-        const uint64_t i = i0 + lane;
-        uint64_t key = 0;
-        uint32_t dest = 0xffffffffu;
-        if (i < n) {
-            key = P.keys[i];
-            dest = (uint32_t)owner_of(P.map, P.fmt.a(key));
-        }
-        const unsigned grp = __match_any_sync(FULL, dest);
-        const uint32_t leader = __ffs(grp) - 1;
-        const uint32_t rank_in = __popc(grp & ((1u << lane) - 1u));
-        unsigned long long base = 0;
-        if (dest != 0xffffffffu && lane == leader)
-            base = atomicAdd_system(P.inbox_n[dest], (unsigned long long)__popc(grp));
-        base = __shfl_sync(FULL, base, leader);
-        if (dest != 0xffffffffu) {
-            if (base + rank_in < P.inbox_cap[dest]) P.inbox[dest][base + rank_in] = key;
-            sent += dest != P.me;
-        }
-    }
-#pragma unroll
-    for (int d = 16; d > 0; d >>= 1) sent += __shfl_xor_sync(FULL, sent, d);
-    if (lane == 0 && sent) atomicAdd(P.n_sent, sent);
-    __threadfence_system();
+    route_items<uint64_t>(P.keys, n, P.lists, [&](uint64_t key) { return (uint32_t)owner_of(P.map, P.fmt.a(key)); }, P.n_sent);
 }
 
 // ---- row gather ---------------------------------------------------------------------------

@@ -746,7 +746,9 @@ int run_pass(ovl_ctx* c, uint32_t min_length, bool chunked) {
     const ScanRanges& R = c->ranges;
     const uint64_t n_gran_local = (uint64_t)(R.g_end[0] - R.g_begin[0]) + (R.g_end[1] - R.g_begin[1]);
     const uint64_t probes = n_gran_local * (uint64_t)(64u >> slog);
-    const bool route = mirror && nr > 1;  // hit keys travel to the rank that owns their A entry
+    // N > 1: a candidate is verified by the rank that owns its k-mer (and, with mirror halving, yields
+    // its twin's key too): every hit key travels to the rank that owns its A entry
+    const bool route = nr > 1;
     const bool have_anchors = n_anc != 0;
 
     cudaStream_t st = c->st, sk = c->st_k2, sp = c->st_push, sg = c->st_sig;
@@ -863,14 +865,17 @@ int run_pass(ovl_ctx* c, uint32_t min_length, bool chunked) {
         // ---- N > 1: push the prefix slice (small, urgent) and the forward region slice (bulk) -------
         if (nr > 1) {
             CK(cudaStreamWaitEvent(sg, c->ev_prel, 0));
-            const uint64_t pre_off = L.off_pre + (uint64_t)c->e_lo * 32, pre_bytes = (uint64_t)n_local * 32;
-            for (int j = 1; j < nr; ++j) {
-                const int r = (me + j) % nr;
-                if (pre_bytes)
-                    CK(cudaMemcpyAsync(at<uint8_t>(c->peer_base[r], c->peer_lay[r].off_pre + (uint64_t)c->e_lo * 32),
-                                       A + pre_off, pre_bytes, cudaMemcpyDefault, sg));
-                OVL_TRY(signal_copy(c, r, F_PRE, sg));
+            const uint64_t pre_bytes = (uint64_t)n_local * 32;
+            if (pre_bytes) {
+                PushTargets PT{};
+                PT.nr = (uint32_t)nr;
+                PT.me = (uint32_t)me;
+                for (int r = 0; r < nr; ++r) PT.dst[r] = at<uint4>(c->peer_base[r], c->peer_lay[r].off_pre + (uint64_t)c->e_lo * 32);
+                k_push<<<dim3(16, nr - 1), 256, 0, sg>>>(d_pre + 2ull * c->e_lo, PT, pre_bytes / 16);
+                ++launches;
+                CK(cudaGetLastError());
             }
+            OVL_TRY(signal_all(c, F_PRE, sg, &launches));
             if (c->debug) CK(cudaEventRecord(c->ev_dbg[2], sg));
             CK(cudaStreamWaitEvent(sp, c->ev_pack, 0));
             const uint64_t fwd_bytes = (uint64_t)(R.g_end[0] - R.g_begin[0]) * 16;
@@ -926,13 +931,16 @@ int run_pass(ovl_ctx* c, uint32_t min_length, bool chunked) {
             if (c->debug) CK(cudaEventRecord(c->ev_dbg[1], sk));
             if (nr > 1) {  // my filter slice (sparse path) and "my partition is ready" to everyone
                 CK(cudaStreamWaitEvent(sg, c->ev_k2, 0));
-                for (int j = 1; j < nr; ++j) {
-                    const int r = (me + j) % nr;
-                    if (!dense)
-                        CK(cudaMemcpyAsync(at<uint8_t>(c->peer_base[r], c->peer_lay[r].off_filter + slice_bytes * me),
-                                           my_slice, slice_bytes, cudaMemcpyDefault, sg));
-                    OVL_TRY(signal_copy(c, r, F_FILT, sg));
+                if (!dense) {
+                    PushTargets PT{};
+                    PT.nr = (uint32_t)nr;
+                    PT.me = (uint32_t)me;
+                    for (int r = 0; r < nr; ++r) PT.dst[r] = at<uint4>(c->peer_base[r], c->peer_lay[r].off_filter + slice_bytes * me);
+                    k_push<<<dim3(32, nr - 1), 256, 0, sg>>>(reinterpret_cast<const uint4*>(my_slice), PT, slice_bytes / 16);
+                    ++launches;
+                    CK(cudaGetLastError());
                 }
+                OVL_TRY(signal_all(c, F_FILT, sg, &launches));
                 CK(cudaEventRecord(c->ev_sig, sg));
                 if (c->debug) CK(cudaEventRecord(c->ev_dbg[3], sg));
             }
@@ -981,12 +989,12 @@ int run_pass(ovl_ctx* c, uint32_t min_length, bool chunked) {
                     Q.items = c->d_scan.as<Surv>();
                     Q.n_ptr = reinterpret_cast<const unsigned long long*>(ctr + C_NSCAN);
                     Q.cap = scan_cap;
-                    Q.nr = (uint32_t)nr;
-                    Q.me = (uint32_t)me;
+                    Q.lists.nr = (uint32_t)nr;
+                    Q.lists.me = (uint32_t)me;
                     for (int r = 0; r < nr; ++r) {
-                        Q.inbox[r] = at<Surv>(c->peer_base[r], c->peer_lay[r].off_scan);
-                        Q.inbox_n[r] = &hdr_of(c, r)->scan_n;
-                        Q.inbox_cap[r] = c->peer_lay[r].scan_cap;
+                        Q.lists.inbox[r] = at<Surv>(c->peer_base[r], c->peer_lay[r].off_scan);
+                        Q.lists.inbox_n[r] = &hdr_of(c, r)->scan_n;
+                        Q.lists.inbox_cap[r] = c->peer_lay[r].scan_cap;
                     }
                     k3_route<<<kblocks, 256, 0, st>>>(Q);
                     ++launches;
@@ -1073,11 +1081,12 @@ int run_pass(ovl_ctx* c, uint32_t min_length, bool chunked) {
             Q.map.n = nr;
             for (int r = 0; r <= nr; ++r) Q.map.e[r] = c->rank_e[r];
             for (int r = 0; r < nr; ++r) {
-                Q.inbox[r] = at<uint64_t>(c->peer_base[r], c->peer_lay[r].off_inbox);
-                Q.inbox_n[r] = &hdr_of(c, r)->inbox_n;
-                Q.inbox_cap[r] = c->peer_lay[r].inbox_cap;
+                Q.lists.inbox[r] = at<uint64_t>(c->peer_base[r], c->peer_lay[r].off_inbox);
+                Q.lists.inbox_n[r] = &hdr_of(c, r)->inbox_n;
+                Q.lists.inbox_cap[r] = c->peer_lay[r].inbox_cap;
             }
-            Q.me = (uint32_t)me;
+            Q.lists.nr = (uint32_t)nr;
+            Q.lists.me = (uint32_t)me;
             Q.n_sent = reinterpret_cast<unsigned long long*>(ctr + C_NSENT);
             k6_route<<<kblocks, 256, 0, st>>>(Q);
             ++launches;
