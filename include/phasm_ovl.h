@@ -243,18 +243,25 @@ int ovl_gfa_segment(const ovl_gfa *g, uint32_t idx, const char **name, size_t *n
 int ovl_gfa_edges(const ovl_gfa *g, const ovl_gfa_edge **edges, uint64_t *n_edges);
 
 /* ---- multi-GPU (one process per GPU) ---------------------------------------------------
- * All ranks add the SAME entry table in the same order; rank r scans only the A entries of
- * its contiguous, base-balanced range and returns only those rows.  The rank's packed reads
- * and prefix anchors are exchanged with ncclAllGather over NVLink (libnccl is dlopen'ed on
- * first use).  ovl_comm_unique_id fills a 128-byte NCCL id on rank 0, the caller ships it to
- * the other ranks (torch.distributed, a file, ...) and every rank calls ovl_comm_init. */
+ * All ranks declare the SAME entry table in the same order (the reads of the other ranks by length
+ * only: ovl_add_remote); rank r holds the bases of one contiguous range.  NCCL is used once, as the
+ * bootstrap channel (libnccl is dlopen'ed on first use): ovl_comm_unique_id fills a 128-byte id on
+ * rank 0, the caller ships it to the other ranks (a socket, torch.distributed, a file, ...) and
+ * every rank calls ovl_comm_init.  The first pass then maps every rank's working arena into every
+ * other rank (CUDA IPC); from there on all exchanges of a pass are device-side pushes over NVLink
+ * into peer memory (phasm_b200/csrc/k6_exchange.cuh) -- no NCCL call and no host round trip inside
+ * a pass.  Every rank calls ovl_overlaps_device / ovl_overlaps_local in step; an error or a
+ * capacity overflow on any rank is seen by all of them in the same pass (all raise / all repeat). */
 int ovl_comm_unique_id(uint8_t id_out[128]);
 int ovl_comm_init(ovl_ctx *ctx, const uint8_t id[128], int rank, int nranks);
 /* After ovl_upload on every rank: exchange the local entry ranges and check that they tile the
  * entry table in rank order. */
 int ovl_comm_sync_ranges(ovl_ctx *ctx);
-/* Gather every rank's rows to rank 0 (rank order == canonical order); other ranks get 0.
- * The _device form leaves the gathered rows in rank 0's HBM (ovl_fetch_rows reads them). */
+/* After a pass the rows live where they were emitted: rank r holds the rows of its A range in its
+ * HBM (rank order == canonical order), like the reads.  On rank 0, ovl_overlaps_device reports the
+ * row count of the whole job, and ovl_fetch_rows / ovl_comm_gather_rows[_device] PULL the other
+ * ranks' rows over NVLink behind rank 0's own (the other ranks do not take part; valid until any
+ * rank starts its next pass or changes its entries).  Other ranks get 0 rows from these calls. */
 int ovl_comm_gather_rows_device(ovl_ctx *ctx, uint64_t *n_rows);
 int ovl_comm_gather_rows(ovl_ctx *ctx, const ovl_row **rows, uint64_t *n_rows);
 /* This rank's OWN rows of the last pass (stats.rows_local of them), HBM -> pinned host: every rank
@@ -268,6 +275,13 @@ int ovl_overlaps_local(ovl_ctx *ctx, uint32_t min_length, const ovl_row **rows, 
  * Copy the 2-bit packed granules of entry idx (ceil(len/64)*16 bytes) to out; used by the
  * pack / reverse-complement parity tests. */
 int ovl_debug_packed(ovl_ctx *ctx, uint32_t idx, uint8_t *out, size_t out_cap, size_t *out_len);
+/* The multi-GPU placement rule, evaluated on the host (no device needed): for candidate (a, p, b)
+ * with entry lengths la, lb on a job of n_ranks ranks owning the entry ranges rank_e[0..n_ranks],
+ * *items = the OVL_HIT-style item bits (2 = suffix-prefix, 1 = containment) the candidate has to
+ * compare itself under strand-mirror halving (0: its twins cover it), *verifier = the rank that
+ * compares it.  Used by the tests of the "exactly one of every twin pair" property. */
+int ovl_debug_mirror_items(int n_ranks, const uint32_t *rank_e, uint32_t a, uint32_t la, uint32_t b,
+                           uint32_t lb, uint32_t p, uint32_t *items, int *verifier);
 
 #ifdef __cplusplus
 }

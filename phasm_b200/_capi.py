@@ -103,6 +103,8 @@ SIGNATURES = {
     "ovl_fetch_local_rows": (c_int, [_P, POINTER(c_void_p), POINTER(c_uint64)]),
     "ovl_overlaps_local": (c_int, [_P, c_uint32, POINTER(c_void_p), POINTER(c_uint64)]),
     "ovl_debug_packed": (c_int, [_P, c_uint32, c_void_p, c_size_t, POINTER(c_size_t)]),
+    "ovl_debug_mirror_items": (c_int, [c_int, c_void_p, c_uint32, c_uint32, c_uint32, c_uint32, c_uint32,
+                                       POINTER(c_uint32), POINTER(c_int)]),
 }
 
 _lib = None

@@ -84,12 +84,111 @@ __device__ __forceinline__ void walk_list(const ScanParams& P, uint32_t owner, u
 }
 
 // ---- sparse path, pass 1 ------------------------------------------------------------------
-// SL >= 0: the stride is the compile-time constant 2^SL (6, 5, 4 and 3 are instantiated: 1, 2, 4 or
-// 8 k-mers per granule at fixed offsets, loops fully unrolled); SL < 0: read it from the parameters.
-// Two tiles are in flight per warp: the tile record of tile i+2 and the granule of tile i+1 are
-// requested before tile i is hashed, so the only exposed dependent load of a tile is its bitmap
-// word.  Stride 64 / 32 (one or two probes per lane) keep the hashes in registers and place the
-// survivors with one warp prefix sum; smaller strides use a ballot round per probe.
+// Stride 64 / 32 (one or two probes per lane, the k-mers sit at fixed word offsets): a three-stage
+// software pipeline per warp.  In iteration i the warp
+//   (1) requests the tile record of tile i+3 and the granule of tile i+2,
+//   (2) hashes the k-mers of tile i+1 (its granule was requested one iteration ago) and requests
+//       their bitmap words -- all of them before any is looked at,
+//   (3) tests the bitmap words of tile i (requested one iteration ago) and places the survivors with
+//       one ballot per probe.
+// No load is consumed in the iteration that issued it (ncu r02e, previous two-stage form: 38 % of
+// the stall samples sat on the two bitmap words, which were also loaded one after the other).
+__device__ __forceinline__ uint32_t bitmap_word(uint64_t h, uint32_t nr, int slice_log2) {
+    return (owner_of_hash(h, nr) << (slice_log2 - 5)) | (((uint32_t)h & ((1u << slice_log2) - 1u)) >> 5);
+}
+
+template <int SL>
+__global__ void __launch_bounds__(256, 4) k3_filter_wide(const ScanParams P) {
+    static_assert(SL == 5 || SL == 6, "one or two probes per granule");
+    constexpr int NP = SL == 6 ? 1 : 2;
+    constexpr uint32_t SCAP = WBUF / 2;
+    __shared__ Surv s_buf[8][SCAP];
+    const uint32_t lane = threadIdx.x & 31;
+    const uint32_t ltmask = (1u << lane) - 1u;
+    const uint32_t warp = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+    const uint32_t nwarps = (gridDim.x * blockDim.x) >> 5;
+    const uint32_t n_tiles = P.n_tiles;
+    const uint64_t kmask = kmer_mask(P.k);
+    const uint32_t nr = P.T.nr;
+    const uint32_t kk = (uint32_t)P.k, ll = P.l;
+    const int bmb = P.bm_bits;
+    Surv* buf = s_buf[threadIdx.x >> 5];
+    uint32_t nbuf = 0;
+
+    const uint4 zero4 = make_uint4(0, 0, 0, 0);
+    auto load_rec = [&](uint32_t t) -> uint4 { return t < n_tiles ? __ldg(P.tiles + t) : zero4; };
+    auto load_gran = [&](const uint4& rec) -> uint4 {  // a record of length 0 (no tile) loads nothing
+        return rec.w + lane < ((rec.z + 63u) >> 6) ? ldg_stream(P.packed + rec.x + lane) : zero4;
+    };
+    // stage (2): hashes and bitmap words of one tile
+    uint64_t h_cur[NP], h_nx[NP];
+    uint32_t bw_cur[NP], bw_nx[NP];
+    uint32_t a_cur = 0, q_cur = 0, nv_cur = 0, a_nx, q_nx, nv_nx;
+    auto hash_tile = [&](const uint4& rec, const uint4& v, uint64_t (&h)[NP], uint32_t (&bw)[NP], uint32_t& a, uint32_t& q,
+                         uint32_t& nv) {
+        const uint32_t L = rec.z;
+        const uint32_t u = rec.w + lane;  // granule of this lane inside the entry
+        a = rec.y;
+        q = u * GRAN_BASES;
+        // probes q + 32 j that can start a row: at least q + k <= |a| (the exact test is in k3_resolve)
+        nv = 0;
+        if (u < ((L + 63u) >> 6) && L >= ll && q + kk <= L) nv = ((L - kk - q) >> SL) + 1u;
+        h[0] = mix64(((uint64_t)v.x | ((uint64_t)v.y << 32)) & kmask);
+        if (NP == 2) h[NP - 1] = mix64(((uint64_t)v.z | ((uint64_t)v.w << 32)) & kmask);
+#pragma unroll
+        for (int j = 0; j < NP; ++j)  // lanes without a probe read word 0 (one broadcast line)
+            bw[j] = __ldg(P.filter + ((uint32_t)j < nv ? bitmap_word(h[j], nr, bmb) : 0u));
+    };
+
+    uint4 rec1 = load_rec(warp + nwarps), rec2 = load_rec(warp + 2 * nwarps);
+    uint4 v1 = load_gran(rec1);
+    {
+        const uint4 rec0 = load_rec(warp);
+        const uint4 v0 = load_gran(rec0);
+        hash_tile(rec0, v0, h_cur, bw_cur, a_cur, q_cur, nv_cur);
+    }
+    for (uint32_t tile = warp; tile < n_tiles; tile += nwarps) {
+        const uint4 rec3 = load_rec(tile + 3 * nwarps);
+        const uint4 v2 = load_gran(rec2);
+        hash_tile(rec1, v1, h_nx, bw_nx, a_nx, q_nx, nv_nx);
+
+        // stage (3): this tile's survivors
+        uint32_t m[NP], total = 0;
+#pragma unroll
+        for (int j = 0; j < NP; ++j) {
+            const bool pass = (uint32_t)j < nv_cur && ((bw_cur[j] >> ((uint32_t)h_cur[j] & 31u)) & 1u);
+            m[j] = __ballot_sync(FULL, pass);
+            total += __popc(m[j]);
+        }
+        if (total) {  // warp-uniform
+            if (nbuf + total > SCAP) wbuf_flush(buf, nbuf, P.surv, lane);
+            uint32_t o = nbuf;
+#pragma unroll
+            for (int j = 0; j < NP; ++j) {
+                if ((m[j] >> lane) & 1u)
+                    buf[o + __popc(m[j] & ltmask)] = make_ulonglong2(h_cur[j], ((uint64_t)a_cur << 32) | (q_cur + 32u * j));
+                o += __popc(m[j]);
+            }
+            nbuf += total;
+            __syncwarp();
+        }
+#pragma unroll
+        for (int j = 0; j < NP; ++j) {
+            h_cur[j] = h_nx[j];
+            bw_cur[j] = bw_nx[j];
+        }
+        a_cur = a_nx;
+        q_cur = q_nx;
+        nv_cur = nv_nx;
+        rec1 = rec2;
+        v1 = v2;
+        rec2 = rec3;
+    }
+    if (nbuf) wbuf_flush(buf, nbuf, P.surv, lane);
+}
+
+// Smaller strides (SL = 4, 3: 4 or 8 probes per lane at fixed offsets, loops unrolled; SL < 0: the
+// stride is read from the parameters): two tiles in flight per warp, one ballot round per probe.
 template <int SL>
 __global__ void __launch_bounds__(256) k3_filter(const ScanParams P) {
     __shared__ Surv s_buf[8][WBUF / 2];
@@ -143,67 +242,34 @@ __global__ void __launch_bounds__(256) k3_filter(const ScanParams P) {
         if (inr && L >= P.l && pos0 + (uint32_t)P.k <= L) nv = ((L - (uint32_t)P.k - pos0) >> sl) + 1u;
         if (nv > n_probe) nv = n_probe;
 
-        if (SL >= 5) {
-            // ---- one or two probes per lane: hashes stay in registers ----
-            constexpr int NP = SL == 6 ? 1 : 2;
-            uint64_t h[NP];
-            uint32_t pass = 0;
-#pragma unroll
-            for (int j = 0; j < NP; ++j) {
-                const uint64_t x = (j == 0 ? w0 : w1) & kmask;
-                h[j] = mix64(x);
-                if ((uint32_t)j < nv) {
-                    const uint64_t bit = bitmap_bit(h[j], nr, P.bm_bits);
-                    pass |= ((__ldg(P.filter + (bit >> 5)) >> (bit & 31)) & 1u) << j;
-                }
-            }
-            const uint32_t cnt = __popc(pass);
-            uint32_t incl = cnt;
-#pragma unroll
-            for (int d = 1; d < 32; d <<= 1) {
-                const uint32_t t = __shfl_up_sync(FULL, incl, d);
-                if (lane >= (uint32_t)d) incl += t;
-            }
-            const uint32_t total = __shfl_sync(FULL, incl, 31);
-            if (total) {  // warp-uniform
-                if (nbuf + total > SCAP) wbuf_flush(buf, nbuf, P.surv, lane);
-                uint32_t o = nbuf + incl - cnt;
-#pragma unroll
-                for (int j = 0; j < NP; ++j)
-                    if ((pass >> j) & 1u) buf[o++] = make_ulonglong2(h[j], ((uint64_t)a << 32) | (pos0 + 32u * j));
-                nbuf += total;
-                __syncwarp();
-            }
-        } else {
-            // ---- 4 or more probes per lane: one ballot round per probe ----
-            uint32_t hitmask = 0;
-            if (nv) {
+        // ---- 4 or more probes per lane: one ballot round per probe ----
+        uint32_t hitmask = 0;
+        if (nv) {
 #pragma unroll 8
-                for (uint32_t j = 0; j < n_probe; ++j) {
-                    const uint32_t off = j << sl;
-                    const uint64_t x = (off < 32 ? kmer_at(w0, w1, off) : kmer_at(w1, w2, off - 32)) & kmask;
-                    const uint64_t bit = bitmap_bit(mix64(x), nr, P.bm_bits);
-                    hitmask |= ((__ldg(P.filter + (bit >> 5)) >> (bit & 31)) & 1u) << j;
-                }
-                hitmask = nv >= 32 ? hitmask : (hitmask & ((1u << nv) - 1u));
+            for (uint32_t j = 0; j < n_probe; ++j) {
+                const uint32_t off = j << sl;
+                const uint64_t x = (off < 32 ? kmer_at(w0, w1, off) : kmer_at(w1, w2, off - 32)) & kmask;
+                const uint64_t bit = bitmap_bit(mix64(x), nr, P.bm_bits);
+                hitmask |= ((__ldg(P.filter + (bit >> 5)) >> (bit & 31)) & 1u) << j;
             }
-            while (__any_sync(FULL, hitmask != 0)) {
-                Surv r = make_ulonglong2(0, 0);
-                const bool have = hitmask != 0;
-                if (have) {
-                    const uint32_t j = __ffs(hitmask) - 1;
-                    hitmask &= hitmask - 1;
-                    const uint32_t off = j << sl;
-                    const uint64_t x = (off < 32 ? kmer_at(w0, w1, off) : kmer_at(w1, w2, off - 32)) & kmask;
-                    r.x = mix64(x);
-                    r.y = ((uint64_t)a << 32) | (pos0 + off);
-                }
-                const unsigned m = __ballot_sync(FULL, have);
-                if (nbuf + 32 > SCAP) wbuf_flush(buf, nbuf, P.surv, lane);
-                if (have) buf[nbuf + __popc(m & ((1u << lane) - 1u))] = r;
-                nbuf += __popc(m);
-                __syncwarp();
+            hitmask = nv >= 32 ? hitmask : (hitmask & ((1u << nv) - 1u));
+        }
+        while (__any_sync(FULL, hitmask != 0)) {
+            Surv r = make_ulonglong2(0, 0);
+            const bool have = hitmask != 0;
+            if (have) {
+                const uint32_t j = __ffs(hitmask) - 1;
+                hitmask &= hitmask - 1;
+                const uint32_t off = j << sl;
+                const uint64_t x = (off < 32 ? kmer_at(w0, w1, off) : kmer_at(w1, w2, off - 32)) & kmask;
+                r.x = mix64(x);
+                r.y = ((uint64_t)a << 32) | (pos0 + off);
             }
+            const unsigned m = __ballot_sync(FULL, have);
+            if (nbuf + 32 > SCAP) wbuf_flush(buf, nbuf, P.surv, lane);
+            if (have) buf[nbuf + __popc(m & ((1u << lane) - 1u))] = r;
+            nbuf += __popc(m);
+            __syncwarp();
         }
     }
     if (nbuf) wbuf_flush(buf, nbuf, P.surv, lane);

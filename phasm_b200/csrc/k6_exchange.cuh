@@ -4,20 +4,27 @@
 // open at connect time, so a rank holds a device pointer into every peer's arena.  All exchanges
 // of a pass then happen on the device, without NCCL calls and without the host:
 //
-//   * bulk data (prefix table slice, filter slice, the forward region of the packed reads) is
-//     PUSHED into the peers' arenas by the copy engines, followed by an 8-byte copy of the step
-//     id into the peer's flag word (same stream: ordered behind the data);
+//   * the forward strands of the packed reads (the bulk: 0.25 B/base) are PUSHED into the arenas
+//     of the peers that compare against them by the copy engines, in pieces over several streams,
+//     each followed by an 8-byte copy of the step id into the peer's flag word (same stream:
+//     ordered behind the data).  Which peers: verifier_rank() (ovl_common.cuh) places a candidate
+//     on one of the two ranks that hold its reads so that rank r only needs the reads of ranks
+//     r+1 .. r+floor(N/2) -- half of an all-gather -- and never a remote reverse complement;
+//   * the small, urgent slices (prefix table, filter bitmap) are pushed by a few blocks of plain
+//     stores (k_push): a copy-engine copy of them queued behind the bulk copy to the same peer;
 //   * a consumer waits with k_wait (one warp spinning on its own arena's flag words, bounded by
 //     a timeout) -- the only kernels that ever wait, and they wait on OTHER GPUs only;
-//   * k3_route ships every scan survivor (16 bytes: k-mer hash, A entry, position) to the rank
-//     that owns the k-mer's slice of the anchor table, k6_route every verified hit key to the rank
-//     that owns its A entry: the items are appended straight into the owner's list with one
-//     system-scope atomicAdd per (warp, destination) on the owner's counter and plain stores over
-//     NVLink (lanes with the same destination write consecutive slots).  Looking the table up
-//     remotely instead (one 8-byte peer load per probe) was measured first: every such load moves
-//     a 32-byte sector plus packet headers, and the scan of 2 GPUs took 2.2x the time of one;
-//   * k9_push_rows copies a rank's rows into rank 0's row array at the offset given by the row
-//     counts the ranks published to each other.
+//   * three item exchanges route 8/16-byte records to the rank that needs them next: k3_route the
+//     scan survivors (k-mer hash, A entry, position) to the rank that owns the k-mer's slice of
+//     the anchor table, k6_route_cand the candidate keys to the rank that compares them,
+//     k6_route the verified hit keys to the rank that owns their A entry.  A block ranks 1024
+//     items per destination in shared memory, reserves room with ONE system-scope atomicAdd per
+//     destination on the owner's counter and stores the items over NVLink (lanes with the same
+//     destination write consecutive slots).  Looking the table up remotely instead (one 8-byte peer
+//     load per probe) was measured first: every such load moves a 32-byte sector plus packet
+//     headers, and the scan of 2 GPUs took 2.2x the time of one;
+//   * the rows stay on the rank that emitted them (sharded by A range like the reads); rank 0
+//     pulls them with copy-engine copies only when a consumer asks for all of them in one place.
 //
 // The reference has no counterpart (single process, single thread: SURVEY.md 2.1, 8(e)).
 #pragma once
@@ -27,7 +34,7 @@ namespace ovl {
 
 // phases a rank signals to its peers; flag[k][s] in MY arena header = the last step in which rank
 // s completed phase k towards me
-enum Flag { F_PRE = 0, F_FILT, F_SCAN, F_FWD, F_HITS, F_ROWCNT, F_ROWS, F_STATUS, F_COUNT };
+enum Flag { F_PRE = 0, F_FILT, F_SCAN, F_CAND, F_FWD, F_HITS, F_STATUS, F_COUNT };
 
 constexpr int STATUS_WORDS = 8;
 // status vector a rank publishes to everyone at the end of a pass
@@ -35,24 +42,13 @@ enum Status { ST_ERR = 0, ST_NCAND, ST_NSCAN, ST_NHITS, ST_NROWS, ST_FLAGS, ST_N
 
 struct alignas(256) ArenaHdr {
     unsigned long long flag[F_COUNT][MAX_RANKS];
-    unsigned long long rowcnt[MAX_RANKS];
     unsigned long long status[MAX_RANKS][STATUS_WORDS];
     unsigned long long inbox_n;    // hit keys appended to this rank's hit list (local and remote atomics)
     unsigned long long scan_n;     // scan survivors appended to this rank's probe list (idem)
+    unsigned long long cand_n;     // candidate keys appended to this rank's verify list (idem)
     unsigned long long step_word;  // current step id: the source of the 8-byte signal copies
     unsigned long long abort;      // != 0: a wait timed out, the pass is void
 };
-
-struct RankMap {
-    uint32_t e[MAX_RANKS + 1];  // rank r owns entries [e[r], e[r+1])
-    int n;
-};
-
-__device__ __forceinline__ int owner_of(const RankMap& R, uint32_t a) {
-    int r = 0;
-    while (r + 1 < R.n && a >= R.e[r + 1]) ++r;
-    return r;
-}
 
 __device__ __forceinline__ unsigned long long ld_acquire_sys(const unsigned long long* p) {
     unsigned long long v;
@@ -68,13 +64,14 @@ __device__ __forceinline__ unsigned long long global_ns() {
     return t;
 }
 
-// Wait until every peer s != me has written flags[s] >= step (one lane per peer).  Gives up after
-// timeout_ns and raises the abort word, so that a dead peer costs a bounded time, not a hang.
+// Wait until every peer s in `mask` (s != me) has written flags[s] >= step (one lane per peer).
+// Gives up after timeout_ns and raises the abort word, so that a dead peer costs a bounded time,
+// not a hang.
 __global__ void __launch_bounds__(32) k_wait(const unsigned long long* __restrict__ flags, uint32_t nr, uint32_t me,
-                                             unsigned long long step, unsigned long long timeout_ns,
+                                             uint32_t mask, unsigned long long step, unsigned long long timeout_ns,
                                              unsigned long long* __restrict__ abort_word) {
     const uint32_t s = threadIdx.x;
-    if (s < nr && s != me) {
+    if (s < nr && s != me && ((mask >> s) & 1u)) {
         const unsigned long long t0 = global_ns();
         while (ld_acquire_sys(flags + s) < step) {
             if (global_ns() - t0 > timeout_ns) {
@@ -205,27 +202,16 @@ __global__ void __launch_bounds__(256) k6_route(const RouteParams P) {
     route_items<uint64_t>(P.keys, n, P.lists, [&](uint64_t key) { return (uint32_t)owner_of(P.map, P.fmt.a(key)); }, P.n_sent);
 }
 
-// ---- row gather ---------------------------------------------------------------------------
-// rowcnt[s] (this rank's arena) = rows of rank s in this step, published by everyone before this
-// kernel runs.  Rank r's rows go to rank 0's row array behind those of ranks 0..r-1 = canonical
-// (a, b, astart, aend, bend) order, because the ranks own contiguous A ranges in rank order.
-__global__ void __launch_bounds__(256) k9_push_rows(const uint32_t* __restrict__ rows, uint64_t src_cap_rows,
-                                                    const unsigned long long* __restrict__ rowcnt, uint32_t me,
-                                                    uint32_t* __restrict__ dst, uint64_t dst_cap_rows,
-                                                    unsigned long long* __restrict__ status_flags) {
-    unsigned long long off = 0;
-    for (uint32_t s = 0; s < me; ++s) off += rowcnt[s];
-    const unsigned long long n = rowcnt[me];
-    if (n > src_cap_rows) return;  // this rank overflowed: the pass is repeated (STF_OVERFLOW)
-    if (off + n > dst_cap_rows) {
-        if (blockIdx.x == 0 && threadIdx.x == 0) atomicOr(status_flags, STF_GATHER);
-        return;
-    }
-    const uint64_t words = 5ull * n;
-    uint32_t* out = dst + 5ull * off;
-    for (uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x; i < words; i += (uint64_t)gridDim.x * blockDim.x)
-        out[i] = rows[i];
-    __threadfence_system();
+// Candidate keys (flags clear) to the rank that compares them: verifier_rank() of the two entries'
+// owners -- one of the two, so that one operand of every comparison is local, and chosen so that a
+// rank needs the forward strands of only half of its peers (ovl_common.cuh).
+__global__ void __launch_bounds__(256) k6_route_cand(const RouteParams P) {
+    const unsigned long long n_all = *P.n_ptr;
+    const uint64_t n = n_all < P.cap ? n_all : P.cap;
+    route_items<uint64_t>(P.keys, n, P.lists, [&](uint64_t key) {
+        const uint32_t a = P.fmt.a(key), b = P.fmt.b(key);
+        return (uint32_t)verifier_rank(P.map.n, owner_of(P.map, a), owner_of(P.map, b), a, b);
+    }, P.n_sent);
 }
 
 // The status vector of this rank, from the device counters (one thread).  A count above its
@@ -236,19 +222,21 @@ struct StatusParams {
     const unsigned long long* ctr;       // device counter block
     int c_err, c_ncand, c_nscan, c_nstage, c_flags;
     const unsigned long long* n_probes;  // this rank's probe list (scan survivors routed to it)
+    const unsigned long long* n_candin;  // this rank's verify list (candidate keys routed to it)
     const unsigned long long* n_hits;
     const unsigned long long* n_rows;
     const unsigned long long* abort_word;
-    unsigned long long cap_cand, cap_scan, cap_stage, cap_hits, cap_rows;
+    unsigned long long cap_cand, cap_candin, cap_scan, cap_stage, cap_hits, cap_rows;
 };
 
 __global__ void k9_status(const StatusParams P) {
     if (threadIdx.x != 0 || blockIdx.x != 0) return;
-    const unsigned long long ncand = P.ctr[P.c_ncand], nstage = P.ctr[P.c_nstage];
+    const unsigned long long nfound = P.ctr[P.c_ncand], ncandin = *P.n_candin, nstage = P.ctr[P.c_nstage];
+    const unsigned long long ncand = nfound > ncandin ? nfound : ncandin;
     const unsigned long long nscan = P.ctr[P.c_nscan] > *P.n_probes ? P.ctr[P.c_nscan] : *P.n_probes;
     const unsigned long long nhits = *P.n_hits, nrows = *P.n_rows;
     unsigned long long fl = P.ctr[P.c_flags] | (*P.abort_word ? STF_TIMEOUT : 0ull);
-    if (ncand > P.cap_cand || nscan > P.cap_scan || nstage > P.cap_stage || nhits > P.cap_hits || nrows > P.cap_rows)
+    if (nfound > P.cap_cand || ncandin > P.cap_candin || nscan > P.cap_scan || nstage > P.cap_stage || nhits > P.cap_hits || nrows > P.cap_rows)
         fl |= STF_OVERFLOW;
     P.st[ST_ERR] = P.ctr[P.c_err];
     P.st[ST_NCAND] = ncand;

@@ -88,10 +88,13 @@ enum Ctr {
 };
 
 // byte offsets of the pieces of an arena (the header sits at 0); published to the peers
+constexpr int PUSH_STREAMS = 4;
+
 struct ArenaLayout {
     uint64_t bytes;
-    uint64_t off_pre, off_packed, off_filter, off_table, off_next, off_scan, off_inbox, off_rows;
+    uint64_t off_pre, off_packed, off_filter, off_table, off_next, off_scan, off_cand, off_inbox, off_rows;
     uint64_t scan_cap;   // scan survivors (probe list)
+    uint64_t cand_cap;   // candidate keys routed to this rank for comparison (N > 1)
     uint64_t inbox_cap;  // hit keys
     uint64_t rows_cap;   // rows (rank 0 of a multi-GPU job: the rows of all ranks)
 };
@@ -109,13 +112,19 @@ struct ovl_ctx {
     int device = 0;
     int n_sm = 148;
     cudaStream_t st = nullptr, st_k2 = nullptr, st_push = nullptr, st_sig = nullptr, st_h2d = nullptr;
+    cudaStream_t st_pushv[PUSH_STREAMS] = {};  // [0] == st_push: the bulk pushes of a pass run on several copy engines
+    cudaEvent_t ev_piece[PUSH_STREAMS] = {};
     cudaEvent_t ev[E_COUNT] = {};
     cudaEvent_t ev_pack = nullptr, ev_k0 = nullptr, ev_prel = nullptr, ev_k2 = nullptr, ev_push = nullptr, ev_sig = nullptr;
     cudaEvent_t ev_chunk[MAX_CHUNKS] = {};
     cudaEvent_t ev_t0 = nullptr, ev_t1 = nullptr;  // ovl_timer_*
-    cudaEvent_t ev_dbg[8] = {};                    // OVL_DEBUG=1: time line of the side streams
+    cudaEvent_t ev_dbg[12] = {};                    // OVL_DEBUG=1: time line of the side streams
     int debug = 0;
     std::string err;
+    // resident blocks per SM of the persistent (grid-stride) kernels, from the occupancy calculator
+    struct {
+        int filter6 = 1, filter5 = 1, filter4 = 1, filter3 = 1, filterx = 1, resolve = 1, route = 1, head = 1, tail = 1, pack = 1;
+    } occ;
 
     // ---- host entry store ----
     PinBuf ascii;            // [SLACK][record, 16-byte aligned]...[SLACK]
@@ -158,7 +167,8 @@ struct ovl_ctx {
     uint64_t cand_per_entry = 96;  // first candidate capacity: this many keys per local entry
     uint64_t n_rows = 0;
     bool rows_fetched = false;
-    bool gathered = false;
+    bool gathered = false;       // N > 1, rank 0: the peers' rows of the last pass have been pulled into this rank's row array
+    uint64_t rowcnt_all[ovl::MAX_RANKS] = {};  // rows of every rank in the last pass
     int collect = 0;
     bool cache_l_valid = false;
     uint32_t cache_l = 0;
@@ -405,6 +415,8 @@ int connect_arena(ovl_ctx* c, bool mirror, uint64_t scan_cap) {
     L.off_next = take(keys_max * 4);
     L.scan_cap = scan_cap;
     L.off_scan = take(scan_cap * 16);
+    L.cand_cap = nr > 1 ? c->cand_cap : 0;
+    L.off_cand = take(L.cand_cap * 8);
     L.inbox_cap = hit_cap;
     L.off_inbox = take(hit_cap * 8);
     L.rows_cap = rows_total;
@@ -612,8 +624,8 @@ int signal_copy(ovl_ctx* c, int r, int kind, cudaStream_t s) {
     return OVL_OK;
 }
 
-int wait_flags(ovl_ctx* c, int kind, cudaStream_t s, uint32_t* launches) {
-    ovl::k_wait<<<1, 32, 0, s>>>(my_hdr(c)->flag[kind], (uint32_t)c->nranks, (uint32_t)c->rank, c->step,
+int wait_flags(ovl_ctx* c, int kind, cudaStream_t s, uint32_t* launches, uint32_t mask = 0xffffffffu) {
+    ovl::k_wait<<<1, 32, 0, s>>>(my_hdr(c)->flag[kind], (uint32_t)c->nranks, (uint32_t)c->rank, mask, c->step,
                                  (unsigned long long)c->opt_timeout_ms * 1000000ull, &my_hdr(c)->abort);
     ++*launches;
     CK(cudaGetLastError());
@@ -628,19 +640,6 @@ int signal_all(ovl_ctx* c, int kind, cudaStream_t s, uint32_t* launches) {
 }
 
 // small publish kernels of the gather / status phase -------------------------------------------
-__global__ void __launch_bounds__(32) k9_publish_rowcnt(ArenaHdr* const* __restrict__ peer_hdr, uint32_t nr, uint32_t me,
-                                                        const unsigned long long* __restrict__ n_rows, unsigned long long* ctr_nrows,
-                                                        unsigned long long step) {
-    const uint32_t s = threadIdx.x;
-    const unsigned long long n = *n_rows;
-    if (s == 0) *ctr_nrows = n;
-    if (s < nr) {
-        peer_hdr[s]->rowcnt[me] = n;
-        __threadfence_system();
-        if (s != me) ovl::st_release_sys(&peer_hdr[s]->flag[ovl::F_ROWCNT][me], step);
-    }
-}
-
 __global__ void __launch_bounds__(32) k9_publish_status(ArenaHdr* const* __restrict__ peer_hdr, uint32_t nr, uint32_t me,
                                                         unsigned long long step) {
     const uint32_t s = threadIdx.x;
@@ -680,8 +679,15 @@ int run_pass(ovl_ctx* c, uint32_t min_length, bool chunked) {
     if (nr > 1 && (int)c->rank_e.size() != nr + 1) return fail(c, OVL_E_ARG, "call ovl_comm_sync_ranges before ovl_overlaps_device");
     const bool mirror = c->opt_mirror && c->pairs == 1;
     S.mirror = mirror ? 1u : 0u;
-    MirrorRule mrule;
+    MirrorRule mrule{};
     mrule.on = mirror ? 1 : 0;
+    mrule.map.n = nr;
+    if (nr > 1)
+        for (int r = 0; r <= nr; ++r) mrule.map.e[r] = c->rank_e[r];
+    // the peers whose forward strands this rank compares against (verifier_rank, ovl_common.cuh)
+    uint32_t need_mask = 0;
+    for (int s = 0; s < nr; ++s)
+        if (ovl::needs_reads_of(nr, me, s)) need_mask |= 1u << s;
     S.granules = c->G;
     KeyFmt fmt;
     fmt.bits_e = ceil_log2((uint64_t)M < 2 ? 2 : M);
@@ -746,8 +752,9 @@ int run_pass(ovl_ctx* c, uint32_t min_length, bool chunked) {
     const ScanRanges& R = c->ranges;
     const uint64_t n_gran_local = (uint64_t)(R.g_end[0] - R.g_begin[0]) + (R.g_end[1] - R.g_begin[1]);
     const uint64_t probes = n_gran_local * (uint64_t)(64u >> slog);
-    // N > 1: a candidate is verified by the rank that owns its k-mer (and, with mirror halving, yields
-    // its twin's key too): every hit key travels to the rank that owns its A entry
+    // N > 1: a candidate is found by the rank that owns its k-mer, compared by verifier_rank() of its
+    // two entries (and, with mirror halving, yields its twins' keys too) and emitted by the rank that
+    // owns its A entry: candidate keys and hit keys are routed between the ranks
     const bool route = nr > 1;
     const bool have_anchors = n_anc != 0;
 
@@ -797,14 +804,14 @@ int run_pass(ovl_ctx* c, uint32_t min_length, bool chunked) {
         uint64_t* ctr = c->d_ctr.as<uint64_t>();
         uint32_t launches = 0, lib = 0;
         ++c->step;
-        uint64_t* h_step = c->h_ctr + C_COUNT + MAX_RANKS * STATUS_WORDS + MAX_RANKS + 1;
+        uint64_t* h_step = c->h_ctr + C_COUNT + MAX_RANKS * STATUS_WORDS + MAX_RANKS + 3;
         *h_step = c->step;
 
         // ---- start: counters, step word -----------------------------------------------------
         if (chunked) CK(cudaEventRecord(c->ev[E_H2D0], st));
         CK(cudaEventRecord(c->ev[E_PACK0], st));
         CK(cudaMemsetAsync(ctr, 0, C_COUNT * sizeof(uint64_t), st));
-        CK(cudaMemsetAsync(&H->inbox_n, 0, 16, st));  // inbox_n, scan_n
+        CK(cudaMemsetAsync(&H->inbox_n, 0, 24, st));  // inbox_n, scan_n, cand_n
         CK(cudaMemcpyAsync(&H->step_word, h_step, 8, cudaMemcpyHostToDevice, st));
         CK(cudaEventRecord(c->ev_k0, st));
         CK(cudaStreamWaitEvent(sk, c->ev_k0, 0));
@@ -877,14 +884,39 @@ int run_pass(ovl_ctx* c, uint32_t min_length, bool chunked) {
             }
             OVL_TRY(signal_all(c, F_PRE, sg, &launches));
             if (c->debug) CK(cudaEventRecord(c->ev_dbg[2], sg));
-            CK(cudaStreamWaitEvent(sp, c->ev_pack, 0));
+            // bulk: my slice of the forward region to the ranks that compare against my reads (half
+            // of the peers), in ring order (at any moment a rank receives from one sender per stream)
+            // and in pieces over several streams so that more than one copy engine drives NVLink
             const uint64_t fwd_bytes = (uint64_t)(R.g_end[0] - R.g_begin[0]) * 16;
-            for (int j = 1; j < nr; ++j) {  // ring offsets: at any moment every rank receives from one sender
-                const int r = (me + j) % nr;
-                if (fwd_bytes)
-                    CK(cudaMemcpyAsync(at<uint8_t>(c->peer_base[r], c->peer_lay[r].off_packed + (uint64_t)R.g_begin[0] * 16),
-                                       A + L.off_packed + (uint64_t)R.g_begin[0] * 16, fwd_bytes, cudaMemcpyDefault, sp));
-                OVL_TRY(signal_copy(c, r, F_FWD, sp));
+            int dst[MAX_RANKS], nd = 0;
+            for (int j = 1; j < nr; ++j) {
+                const int r = (me - j + nr) % nr;
+                if (needs_reads_of(nr, r, me)) dst[nd++] = r;
+            }
+            const int pieces = nd ? std::max(1, PUSH_STREAMS / nd) : 1;
+            for (int i = 0; i < PUSH_STREAMS; ++i) CK(cudaStreamWaitEvent(c->st_pushv[i], c->ev_pack, 0));
+            for (int i = 0; i < nd; ++i) {
+                const int r = dst[i];
+                const uint64_t gran = fwd_bytes / 16;
+                cudaStream_t last = nullptr;
+                for (int q = 0; q < pieces; ++q) {
+                    const uint64_t g0 = gran * q / pieces, g1 = gran * (q + 1) / pieces;
+                    cudaStream_t sq = c->st_pushv[(i * pieces + q) % PUSH_STREAMS];
+                    if (g1 > g0)
+                        CK(cudaMemcpyAsync(at<uint8_t>(c->peer_base[r], c->peer_lay[r].off_packed + ((uint64_t)R.g_begin[0] + g0) * 16),
+                                           A + L.off_packed + ((uint64_t)R.g_begin[0] + g0) * 16, (g1 - g0) * 16, cudaMemcpyDefault, sq));
+                    if (q + 1 < pieces) {
+                        CK(cudaEventRecord(c->ev_piece[q], sq));
+                    } else {
+                        last = sq;
+                    }
+                }
+                for (int q = 0; q + 1 < pieces; ++q) CK(cudaStreamWaitEvent(last, c->ev_piece[q], 0));
+                OVL_TRY(signal_copy(c, r, F_FWD, last));
+            }
+            for (int i = 1; i < PUSH_STREAMS; ++i) {  // ev_push = every push stream drained
+                CK(cudaEventRecord(c->ev_piece[i], c->st_pushv[i]));
+                CK(cudaStreamWaitEvent(sp, c->ev_piece[i], 0));
             }
             CK(cudaEventRecord(c->ev_push, sp));
             if (c->debug) CK(cudaEventRecord(c->ev_dbg[4], sp));
@@ -952,7 +984,9 @@ int run_pass(ovl_ctx* c, uint32_t min_length, bool chunked) {
         CK(cudaEventRecord(c->ev[E_SCAN0], st));
 
         // ---- K3: scan the local A entries -----------------------------------------------------------
-        if (have_anchors && R.n_tiles) {
+        // (a rank without local reads still takes part in every exchange and resolves the probes of
+        // the others against its partition of the table)
+        if (have_anchors) {
             ScanParams P;
             P.packed = d_packed;
             P.tiles = c->d_scan_tiles.as<uint4>();
@@ -974,16 +1008,20 @@ int run_pass(ovl_ctx* c, uint32_t min_length, bool chunked) {
             P.sink.cap = c->cand_cap;
             P.mirror = mrule;
             if (!dense) {
-                uint32_t blocks = (R.n_tiles + 7) / 8;
-                if (blocks > (uint32_t)nsm * 8) blocks = (uint32_t)nsm * 8;
-                switch (slog) {
-                    case 6: k3_filter<6><<<blocks, 256, 0, st>>>(P); break;
-                    case 5: k3_filter<5><<<blocks, 256, 0, st>>>(P); break;
-                    case 4: k3_filter<4><<<blocks, 256, 0, st>>>(P); break;
-                    case 3: k3_filter<3><<<blocks, 256, 0, st>>>(P); break;
-                    default: k3_filter<-1><<<blocks, 256, 0, st>>>(P); break;
+                if (R.n_tiles) {
+                    // persistent grids: exactly the blocks that are resident at once (a static tile split
+                    // over 8 blocks per SM with 5 resident ran 1.6 waves: ncu r02e)
+                    const uint32_t want = (R.n_tiles + 7) / 8;
+                    auto grid = [&](int resident) { return std::min<uint32_t>(want, (uint32_t)(nsm * resident)); };
+                    switch (slog) {
+                        case 6: k3_filter_wide<6><<<grid(c->occ.filter6), 256, 0, st>>>(P); break;
+                        case 5: k3_filter_wide<5><<<grid(c->occ.filter5), 256, 0, st>>>(P); break;
+                        case 4: k3_filter<4><<<grid(c->occ.filter4), 256, 0, st>>>(P); break;
+                        case 3: k3_filter<3><<<grid(c->occ.filter3), 256, 0, st>>>(P); break;
+                        default: k3_filter<-1><<<grid(c->occ.filterx), 256, 0, st>>>(P); break;
+                    }
+                    ++launches;
                 }
-                ++launches;
                 if (route_probes) {
                     ProbeRouteParams Q;
                     Q.items = c->d_scan.as<Surv>();
@@ -996,37 +1034,71 @@ int run_pass(ovl_ctx* c, uint32_t min_length, bool chunked) {
                         Q.lists.inbox_n[r] = &hdr_of(c, r)->scan_n;
                         Q.lists.inbox_cap[r] = c->peer_lay[r].scan_cap;
                     }
-                    k3_route<<<kblocks, 256, 0, st>>>(Q);
+                    k3_route<<<(uint32_t)(nsm * c->occ.route), 256, 0, st>>>(Q);
                     ++launches;
                     CK(cudaGetLastError());
                     OVL_TRY(signal_all(c, F_SCAN, st, &launches));
                     OVL_TRY(wait_flags(c, F_SCAN, st, &launches));
+                    if (c->debug) CK(cudaEventRecord(c->ev_dbg[5], st));
                     P.surv.out = d_probes;
                     P.surv.n_out = &H->scan_n;
                     P.surv.cap = L.scan_cap;
                 }
-                k3_resolve<<<kblocks, 256, 0, st>>>(P);
+                k3_resolve<<<(uint32_t)(nsm * c->occ.resolve), 256, 0, st>>>(P);
                 ++launches;
-            } else if (smem_filter) {
-                k3_scan<true><<<nsm, 1024, 32 * WBUF * 8 + (4u << bm_bits), st>>>(P);
-                ++launches;
-            } else {
-                k3_scan<false><<<nsm, 1024, 32 * WBUF * 8, st>>>(P);
+                if (c->debug) CK(cudaEventRecord(c->ev_dbg[8], st));
+            } else if (R.n_tiles) {
+                if (smem_filter)
+                    k3_scan<true><<<nsm, 1024, 32 * WBUF * 8 + (4u << bm_bits), st>>>(P);
+                else
+                    k3_scan<false><<<nsm, 1024, 32 * WBUF * 8, st>>>(P);
                 ++launches;
             }
             CK(cudaGetLastError());
         }
+        // ---- N > 1: every candidate key to the rank that compares it ----------------------------------
+        const uint64_t* d_vkeys = c->d_cand.as<uint64_t>();
+        const unsigned long long* d_vn = reinterpret_cast<const unsigned long long*>(ctr + C_NCAND);
+        uint64_t vcap = c->cand_cap;
+        if (route && have_anchors) {
+            RouteParams Q;
+            Q.keys = c->d_cand.as<uint64_t>();
+            Q.n_ptr = reinterpret_cast<const unsigned long long*>(ctr + C_NCAND);
+            Q.cap = c->cand_cap;
+            Q.fmt = fmt;
+            Q.map = mrule.map;
+            for (int r = 0; r < nr; ++r) {
+                Q.lists.inbox[r] = at<uint64_t>(c->peer_base[r], c->peer_lay[r].off_cand);
+                Q.lists.inbox_n[r] = &hdr_of(c, r)->cand_n;
+                Q.lists.inbox_cap[r] = c->peer_lay[r].cand_cap;
+            }
+            Q.lists.nr = (uint32_t)nr;
+            Q.lists.me = (uint32_t)me;
+            Q.n_sent = nullptr;
+            k6_route_cand<<<kblocks, 256, 0, st>>>(Q);
+            ++launches;
+            CK(cudaGetLastError());
+            OVL_TRY(signal_all(c, F_CAND, st, &launches));
+            OVL_TRY(wait_flags(c, F_CAND, st, &launches));
+            d_vkeys = at<uint64_t>(A, L.off_cand);
+            d_vn = &H->cand_n;
+            vcap = L.cand_cap;
+        }
         CK(cudaEventRecord(c->ev[E_VERIFY0], st));
 
-        // ---- K4: verify.  N > 1: the forward region of every peer must have landed, then the twin
-        //      strands of the remote reads are rebuilt -------------------------------------------------
+        // ---- K4: verify.  N > 1: the forward strands of the peers this rank compares against must
+        //      have landed.  With strand-mirror halving the compared candidate of a twin pair is the
+        //      one whose remote entry is a forward strand, so nothing else is needed; without it the
+        //      reverse-complement entries of those peers are rebuilt here -------------------------------
         if (nr > 1) {
-            OVL_TRY(wait_flags(c, F_FWD, st, &launches));
-            const uint32_t rg[2][2] = {{0u, c->e_lo}, {c->e_hi, M}};
-            for (int i = 0; i < 2; ++i)
-                if (rg[i][1] > rg[i][0] && c->G > c->G_f) {
-                    k1_rc<<<rg[i][1] - rg[i][0], 128, 0, st>>>(c->d_ent.as<uint2>(), c->d_flags.as<uint8_t>(),
-                                                               reinterpret_cast<uint32_t*>(d_packed), rg[i][0], rg[i][1], M);
+            OVL_TRY(wait_flags(c, F_FWD, st, &launches, need_mask));
+            if (c->debug) CK(cudaEventRecord(c->ev_dbg[9], st));
+            if (!mirror && c->G > c->G_f)
+                for (int s = 0; s < nr; ++s) {
+                    const uint32_t e0 = c->rank_e[s], e1 = c->rank_e[s + 1];
+                    if (!((need_mask >> s) & 1u) || e1 <= e0) continue;
+                    k1_rc<<<e1 - e0, 128, 0, st>>>(c->d_ent.as<uint2>(), c->d_flags.as<uint8_t>(),
+                                                   reinterpret_cast<uint32_t*>(d_packed), e0, e1, M);
                     ++launches;
                 }
             CK(cudaGetLastError());
@@ -1038,9 +1110,9 @@ int run_pass(ovl_ctx* c, uint32_t min_length, bool chunked) {
         if (have_anchors) {
             if (c->collect || c->opt_serial_verify) {
                 VerifyParams V;
-                V.keys = c->d_cand.as<uint64_t>();
-                V.n_ptr = reinterpret_cast<const unsigned long long*>(ctr + C_NCAND);
-                V.cap = c->cand_cap;
+                V.keys = d_vkeys;
+                V.n_ptr = d_vn;
+                V.cap = vcap;
                 V.packed = d_packed;
                 V.ent = c->d_ent.as<uint2>();
                 V.fmt = fmt;
@@ -1052,9 +1124,9 @@ int run_pass(ovl_ctx* c, uint32_t min_length, bool chunked) {
                 ++launches;
             } else {
                 Verify2Params V;
-                V.keys = c->d_cand.as<uint64_t>();
-                V.n_ptr = reinterpret_cast<const unsigned long long*>(ctr + C_NCAND);
-                V.cap = c->cand_cap;
+                V.keys = d_vkeys;
+                V.n_ptr = d_vn;
+                V.cap = vcap;
                 V.packed64 = reinterpret_cast<const uint64_t*>(d_packed);
                 V.ent = c->d_ent.as<uint2>();
                 V.fmt = fmt;
@@ -1078,8 +1150,7 @@ int run_pass(ovl_ctx* c, uint32_t min_length, bool chunked) {
             Q.n_ptr = reinterpret_cast<const unsigned long long*>(ctr + C_NSTAGE);
             Q.cap = hit_cap;
             Q.fmt = fmt;
-            Q.map.n = nr;
-            for (int r = 0; r <= nr; ++r) Q.map.e[r] = c->rank_e[r];
+            Q.map = mrule.map;
             for (int r = 0; r < nr; ++r) {
                 Q.lists.inbox[r] = at<uint64_t>(c->peer_base[r], c->peer_lay[r].off_inbox);
                 Q.lists.inbox_n[r] = &hdr_of(c, r)->inbox_n;
@@ -1093,6 +1164,7 @@ int run_pass(ovl_ctx* c, uint32_t min_length, bool chunked) {
             CK(cudaGetLastError());
             OVL_TRY(signal_all(c, F_HITS, st, &launches));
             OVL_TRY(wait_flags(c, F_HITS, st, &launches));
+            if (c->debug) CK(cudaEventRecord(c->ev_dbg[10], st));
         }
 
         // ---- K7: order the hit keys by (a, b, p, flags) and emit rows: k7_bucket.cuh ------------------
@@ -1136,21 +1208,12 @@ int run_pass(ovl_ctx* c, uint32_t min_length, bool chunked) {
         CK(cudaGetLastError());
         CK(cudaEventRecord(c->ev[E_GATHER0], st));
 
-        // ---- K9 (N > 1): rows into rank 0's row array, in rank order --------------------------------
+        // ---- end of the data path.  The rows stay where they were emitted: sharded by A range over
+        //      the ranks' HBM like the reads (rank order = canonical order).  A consumer that wants
+        //      them in one place pulls them afterwards (ovl_fetch_rows / ovl_comm_gather_rows_device
+        //      on rank 0); the row counts travel in the status vectors below ------------------------
         const unsigned long long* d_nrows = reinterpret_cast<const unsigned long long*>(b_rowoff + M);
-        k9_publish_rowcnt<<<1, 32, 0, st>>>(c->d_peerhdr.as<ArenaHdr*>(), (uint32_t)nr, (uint32_t)me, d_nrows,
-                                            reinterpret_cast<unsigned long long*>(ctr + C_NROWS), c->step);
-        ++launches;
         if (nr > 1) {
-            OVL_TRY(wait_flags(c, F_ROWCNT, st, &launches));
-            if (me != 0) {
-                k9_push_rows<<<kblocks, 256, 0, st>>>(reinterpret_cast<const uint32_t*>(d_rows), B.rows_cap, H->rowcnt, (uint32_t)me,
-                                                      at<uint32_t>(c->peer_base[0], c->peer_lay[0].off_rows), c->peer_lay[0].rows_cap,
-                                                      reinterpret_cast<unsigned long long*>(ctr + C_FLAGS));
-                ++launches;
-            }
-            OVL_TRY(signal_all(c, F_ROWS, st, &launches));
-            if (me == 0) OVL_TRY(wait_flags(c, F_ROWS, st, &launches));
             // never leave a push in flight behind the end of the pass
             CK(cudaStreamWaitEvent(st, c->ev_push, 0));
             if (have_anchors) CK(cudaStreamWaitEvent(st, c->ev_sig, 0));
@@ -1169,6 +1232,8 @@ int run_pass(ovl_ctx* c, uint32_t min_length, bool chunked) {
             SP.c_nstage = C_NSTAGE;
             SP.c_flags = C_FLAGS;
             SP.n_probes = &H->scan_n;
+            SP.n_candin = &H->cand_n;
+            SP.cap_candin = route ? L.cand_cap : ~0ull;
             SP.n_hits = &H->inbox_n;
             SP.n_rows = d_nrows;
             SP.abort_word = &H->abort;
@@ -1190,8 +1255,7 @@ int run_pass(ovl_ctx* c, uint32_t min_length, bool chunked) {
         uint64_t* h_rowcnt = h_status + MAX_RANKS * STATUS_WORDS;
         CK(cudaMemcpyAsync(c->h_ctr, ctr, C_COUNT * sizeof(uint64_t), cudaMemcpyDeviceToHost, st));
         CK(cudaMemcpyAsync(h_status, H->status, sizeof H->status, cudaMemcpyDeviceToHost, st));
-        CK(cudaMemcpyAsync(h_rowcnt, H->rowcnt, sizeof H->rowcnt, cudaMemcpyDeviceToHost, st));
-        CK(cudaMemcpyAsync(h_rowcnt + MAX_RANKS, &H->inbox_n, 8, cudaMemcpyDeviceToHost, st));
+        CK(cudaMemcpyAsync(h_rowcnt + MAX_RANKS, &H->inbox_n, 24, cudaMemcpyDeviceToHost, st));  // inbox_n, scan_n, cand_n
         CK(cudaStreamSynchronize(st));  // the one synchronisation of a pass
         CK(cudaStreamSynchronize(sk));
         if (chunked) {
@@ -1249,7 +1313,7 @@ int run_pass(ovl_ctx* c, uint32_t min_length, bool chunked) {
         }
         if (flags_any & STF_GATHER) return fail(c, OVL_E_LIMIT, "row gather overflow: internal error");
         S.candidates = c->h_ctr[C_NCAND];
-        S.verified = c->h_ctr[C_NCAND];
+        S.verified = route ? h_rowcnt[MAX_RANKS + 2] : c->h_ctr[C_NCAND];  // N > 1: the candidates routed to this rank
         S.hits = h_rowcnt[MAX_RANKS];  // keys in this rank's hit list
         S.hits_sent = c->h_ctr[C_NSENT];
         S.hits_received = route ? (S.hits + S.hits_sent > c->h_ctr[C_NSTAGE] ? S.hits + S.hits_sent - c->h_ctr[C_NSTAGE] : 0) : 0;
@@ -1258,14 +1322,16 @@ int run_pass(ovl_ctx* c, uint32_t min_length, bool chunked) {
         S.big_buckets = (uint32_t)c->h_ctr[C_BIG];
         S.scan_survivors = h_status[(size_t)me * STATUS_WORDS + ST_NSCAN];
         uint64_t total = 0;
-        for (int r = 0; r < nr; ++r) total += h_rowcnt[r];
-        S.rows_local = h_rowcnt[me];
-        if (nr > 1) {
-            c->n_rows = me == 0 ? total : 0;
-            c->gathered = true;
-        } else {
-            c->n_rows = total;
+        for (int r = 0; r < nr; ++r) {
+            h_rowcnt[r] = h_status[(size_t)r * STATUS_WORDS + ST_NROWS];
+            c->rowcnt_all[r] = h_rowcnt[r];
+            total += h_rowcnt[r];
         }
+        S.rows_local = h_rowcnt[me];
+        // N > 1: rank 0 reports the job's row count; the rows of the other ranks are still in their
+        // HBM (gather_rows_pull brings them over when somebody asks for them)
+        c->n_rows = nr > 1 ? (me == 0 ? total : 0) : total;
+        c->gathered = nr == 1;
         S.rows = c->n_rows;
         break;
     }
@@ -1278,12 +1344,14 @@ int run_pass(ovl_ctx* c, uint32_t min_length, bool chunked) {
             }
             return ms;
         };
+        const bool mg = c->nranks > 1;
         fprintf(stderr, "[ovl rank %d step %llu] +ms: pack_end %.3f | sk: pre_wait_end %.3f insert_end %.3f | sg: pre_pushed %.3f filt_pushed %.3f | "
-                        "sp: fwd_pushed %.3f | st: scan0 %.3f verify0 %.3f sort0 %.3f emit0 %.3f gather0 %.3f end %.3f\n",
+                        "sp: fwd_pushed %.3f | st: scan0 %.3f probes_in %.3f resolve_end %.3f cands_in(verify0) %.3f fwd_in %.3f sort0 %.3f "
+                        "hits_in %.3f emit0 %.3f end %.3f\n",
                 c->rank, (unsigned long long)c->step, rel(c->ev[E_ANCHOR0]), rel(c->ev_dbg[0]), rel(c->ev_dbg[1]),
-                c->nranks > 1 ? rel(c->ev_dbg[2]) : -1.f, c->nranks > 1 ? rel(c->ev_dbg[3]) : -1.f,
-                c->nranks > 1 ? rel(c->ev_dbg[4]) : -1.f, rel(c->ev[E_SCAN0]), rel(c->ev[E_VERIFY0]), rel(c->ev[E_SORT0]),
-                rel(c->ev[E_EMIT0]), rel(c->ev[E_GATHER0]), rel(c->ev[E_END]));
+                mg ? rel(c->ev_dbg[2]) : -1.f, mg ? rel(c->ev_dbg[3]) : -1.f, mg ? rel(c->ev_dbg[4]) : -1.f, rel(c->ev[E_SCAN0]),
+                mg ? rel(c->ev_dbg[5]) : -1.f, rel(c->ev_dbg[8]), rel(c->ev[E_VERIFY0]), mg ? rel(c->ev_dbg[9]) : -1.f,
+                rel(c->ev[E_SORT0]), mg ? rel(c->ev_dbg[10]) : -1.f, rel(c->ev[E_EMIT0]), rel(c->ev[E_END]));
     }
     S.ms_pack = ev_ms(c, E_PACK0, E_ANCHOR0);
     S.ms_anchor = ev_ms(c, E_ANCHOR0, E_SCAN0);
@@ -1291,7 +1359,7 @@ int run_pass(ovl_ctx* c, uint32_t min_length, bool chunked) {
     S.ms_verify = ev_ms(c, E_VERIFY0, E_SORT0);
     S.ms_sort = ev_ms(c, E_SORT0, E_EMIT0);
     S.ms_emit = ev_ms(c, E_EMIT0, E_GATHER0);
-    S.ms_gather = ev_ms(c, E_GATHER0, E_END);
+    S.ms_gather = 0.f;  // set by gather_rows_pull when somebody asks for all rows on rank 0
     S.ms_device = ev_ms(c, E_PACK0, E_END);
     if (chunked) {
         float ms = 0.f;
@@ -1300,6 +1368,42 @@ int run_pass(ovl_ctx* c, uint32_t min_length, bool chunked) {
     } else {
         S.ms_exposed = S.ms_device;
     }
+    return OVL_OK;
+}
+
+// Rank 0 of a multi-GPU job: pull the rows of the other ranks (still in their HBM, at the start of
+// their row arrays) behind this rank's own rows, over NVLink with the copy engines.  Rank order =
+// canonical row order.  Valid until any rank starts its next pass or changes its entry store; the
+// other ranks do not take part.
+int gather_rows_pull(ovl_ctx* c) {
+    if (c->nranks == 1 || c->gathered) return OVL_OK;
+    c->gathered = true;
+    if (c->rank != 0) return OVL_OK;
+    uint64_t off = c->rowcnt_all[0];
+    CK(cudaEventRecord(c->ev_dbg[6], c->st));
+    CK(cudaEventRecord(c->ev_pack, c->st));
+    int used = 0;
+    for (int r = 1; r < c->nranks; ++r) {
+        const uint64_t n = c->rowcnt_all[r];
+        if (n) {
+            if (off + n > c->lay.rows_cap) return fail(c, OVL_E_LIMIT, "row gather overflow: internal error");
+            cudaStream_t s = c->st_pushv[used % PUSH_STREAMS];
+            if (used < PUSH_STREAMS) CK(cudaStreamWaitEvent(s, c->ev_pack, 0));
+            CK(cudaMemcpyAsync(c->d_rows.as<uint8_t>() + off * sizeof(ovl::Row),
+                               at<uint8_t>(c->peer_base[r], c->peer_lay[r].off_rows), n * sizeof(ovl::Row), cudaMemcpyDefault, s));
+            ++used;
+        }
+        off += n;
+    }
+    for (int i = 0; i < std::min(used, PUSH_STREAMS); ++i) {
+        CK(cudaEventRecord(c->ev_piece[i], c->st_pushv[i]));
+        CK(cudaStreamWaitEvent(c->st, c->ev_piece[i], 0));
+    }
+    CK(cudaEventRecord(c->ev_dbg[7], c->st));
+    CK(cudaStreamSynchronize(c->st));
+    float ms = 0.f;
+    CK(cudaEventElapsedTime(&ms, c->ev_dbg[6], c->ev_dbg[7]));
+    c->stats.ms_gather = ms;
     return OVL_OK;
 }
 
@@ -1344,7 +1448,11 @@ int ovl_create(int device, ovl_ctx** out) {
         CK(cudaDeviceGetStreamPriorityRange(&lo_pri, &hi_pri));
         CK(cudaStreamCreateWithFlags(&x->st, cudaStreamNonBlocking));
         CK(cudaStreamCreateWithFlags(&x->st_k2, cudaStreamNonBlocking));
-        CK(cudaStreamCreateWithPriority(&x->st_push, cudaStreamNonBlocking, hi_pri));
+        for (int i = 0; i < PUSH_STREAMS; ++i) {
+            CK(cudaStreamCreateWithPriority(&x->st_pushv[i], cudaStreamNonBlocking, hi_pri));
+            CK(cudaEventCreateWithFlags(&x->ev_piece[i], cudaEventDisableTiming));
+        }
+        x->st_push = x->st_pushv[0];
         CK(cudaStreamCreateWithPriority(&x->st_sig, cudaStreamNonBlocking, hi_pri));
         CK(cudaStreamCreateWithFlags(&x->st_h2d, cudaStreamNonBlocking));
         cudaEvent_t* plain[] = {&x->ev_pack, &x->ev_k0, &x->ev_prel, &x->ev_k2, &x->ev_push, &x->ev_sig};
@@ -1353,14 +1461,30 @@ int ovl_create(int device, ovl_ctx** out) {
         for (int i = 0; i < E_COUNT; ++i) CK(cudaEventCreate(&x->ev[i]));
         CK(cudaEventCreate(&x->ev_t0));
         CK(cudaEventCreate(&x->ev_t1));
-        for (int i = 0; i < 8; ++i) CK(cudaEventCreate(&x->ev_dbg[i]));
+        for (int i = 0; i < 12; ++i) CK(cudaEventCreate(&x->ev_dbg[i]));
         x->debug = getenv("OVL_DEBUG") ? atoi(getenv("OVL_DEBUG")) : 0;
-        const size_t hwords = C_COUNT + MAX_RANKS * STATUS_WORDS + MAX_RANKS + 2;
+        const size_t hwords = C_COUNT + MAX_RANKS * STATUS_WORDS + MAX_RANKS + 4;
         CK(cudaHostAlloc(reinterpret_cast<void**>(&x->h_ctr), hwords * sizeof(uint64_t), cudaHostAllocDefault));
         memset(x->h_ctr, 0, hwords * sizeof(uint64_t));
         OVL_TRY(dev_ensure(c, x->d_ctr, C_COUNT * sizeof(uint64_t), false));
         CK(cudaFuncSetAttribute(ovl::k3_scan<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, 32 * ovl::WBUF * 8 + 128 * 1024));
         CK(cudaFuncSetAttribute(ovl::k3_scan<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, 32 * ovl::WBUF * 8));
+        auto resident = [&](auto kernel, int& out_n) -> int {
+            int nb = 0;
+            CK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&nb, kernel, 256, 0));
+            out_n = nb < 1 ? 1 : nb;
+            return OVL_OK;
+        };
+        OVL_TRY(resident(ovl::k3_filter_wide<6>, x->occ.filter6));
+        OVL_TRY(resident(ovl::k3_filter_wide<5>, x->occ.filter5));
+        OVL_TRY(resident(ovl::k3_filter<4>, x->occ.filter4));
+        OVL_TRY(resident(ovl::k3_filter<3>, x->occ.filter3));
+        OVL_TRY(resident(ovl::k3_filter<-1>, x->occ.filterx));
+        OVL_TRY(resident(ovl::k3_resolve, x->occ.resolve));
+        OVL_TRY(resident(ovl::k3_route, x->occ.route));
+        OVL_TRY(resident(ovl::k4a_head, x->occ.head));
+        OVL_TRY(resident(ovl::k4b_tail, x->occ.tail));
+        OVL_TRY(resident(ovl::k1_pack, x->occ.pack));
         return OVL_OK;
     };
     int rc = init();
@@ -1390,12 +1514,17 @@ void ovl_destroy(ovl_ctx* c) {
     for (int i = 0; i < MAX_CHUNKS; ++i)
         if (c->ev_chunk[i]) cudaEventDestroy(c->ev_chunk[i]);
     cudaEvent_t evs[] = {c->ev_pack, c->ev_k0, c->ev_prel, c->ev_k2, c->ev_push, c->ev_sig, c->ev_t0, c->ev_t1,
-                         c->ev_dbg[0], c->ev_dbg[1], c->ev_dbg[2], c->ev_dbg[3], c->ev_dbg[4], c->ev_dbg[5], c->ev_dbg[6], c->ev_dbg[7]};
+                         c->ev_dbg[0], c->ev_dbg[1], c->ev_dbg[2], c->ev_dbg[3], c->ev_dbg[4], c->ev_dbg[5], c->ev_dbg[6], c->ev_dbg[7],
+                         c->ev_dbg[8], c->ev_dbg[9], c->ev_dbg[10], c->ev_dbg[11]};
     for (cudaEvent_t e : evs)
         if (e) cudaEventDestroy(e);
-    cudaStream_t sts[] = {c->st, c->st_k2, c->st_push, c->st_sig, c->st_h2d};
+    cudaStream_t sts[] = {c->st, c->st_k2, c->st_sig, c->st_h2d};
     for (cudaStream_t s : sts)
         if (s) cudaStreamDestroy(s);
+    for (int i = 0; i < PUSH_STREAMS; ++i) {
+        if (c->st_pushv[i]) cudaStreamDestroy(c->st_pushv[i]);
+        if (c->ev_piece[i]) cudaEventDestroy(c->ev_piece[i]);
+    }
     (void)cudaGetLastError();
     delete c;
 }
@@ -1630,6 +1759,7 @@ int ovl_fetch_rows(ovl_ctx* c, const ovl_row** rows, uint64_t* n_rows) {
     *n_rows = c->n_rows;
     if (!c->n_rows) return OVL_OK;
     if (!c->rows_fetched) {
+        OVL_TRY(gather_rows_pull(c));
         const size_t bytes = c->n_rows * sizeof(ovl_row);
         OVL_TRY(pin_ensure(c, c->h_rows, bytes, 0));
         CK(cudaEventRecord(c->ev[E_D2H0], c->st));
@@ -1732,10 +1862,12 @@ int ovl_comm_sync_ranges(ovl_ctx* c) {
     return OVL_OK;
 }
 
-// The rows of every rank are gathered into rank 0's HBM (rank order == canonical order) inside
-// the pass itself; this call only reports.  Kept for callers of the round-1 interface.
+// Rank 0: pull the rows of the other ranks of the last pass into this rank's HBM (rank order ==
+// canonical order) and report the job's row count; other ranks: no-op.  Not collective.
 int ovl_comm_gather_rows_device(ovl_ctx* c, uint64_t* n_rows) {
     if (!c) return OVL_E_ARG;
+    OVL_TRY(set_dev(c));
+    OVL_TRY(gather_rows_pull(c));
     if (n_rows) *n_rows = c->n_rows;
     return OVL_OK;
 }
@@ -1777,6 +1909,18 @@ int ovl_debug_packed(ovl_ctx* c, uint32_t idx, uint8_t* out, size_t out_cap, siz
     if (!bytes) return OVL_OK;
     if (!out || out_cap < bytes) return fail(c, OVL_E_ARG, "ovl_debug_packed: buffer too small (%zu needed)", bytes);
     CK(cudaMemcpy(out, c->arena.as<uint8_t>() + c->lay.off_packed + (size_t)c->gran0[idx] * 16, bytes, cudaMemcpyDeviceToHost));
+    return OVL_OK;
+}
+
+int ovl_debug_mirror_items(int n_ranks, const uint32_t* rank_e, uint32_t a, uint32_t la, uint32_t b, uint32_t lb,
+                           uint32_t p, uint32_t* items, int* verifier) {
+    if (n_ranks < 1 || n_ranks > ovl::MAX_RANKS || !rank_e || !items || !verifier || p >= la) return OVL_E_ARG;
+    ovl::MirrorRule R{};
+    R.on = 1;
+    R.map.n = n_ranks;
+    for (int r = 0; r <= n_ranks; ++r) R.map.e[r] = rank_e[r];
+    *items = ovl::mirror_items(R, a, la, b, lb, p);
+    *verifier = ovl::verifier_rank(n_ranks, ovl::owner_of(R.map, a), ovl::owner_of(R.map, b), a, b);
     return OVL_OK;
 }
 

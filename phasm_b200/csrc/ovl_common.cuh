@@ -92,12 +92,45 @@ struct KeyFmt {
 constexpr uint64_t HIT_CONT = 1;  // rem >= |b|: b wholly inside a (R2 row)
 constexpr uint64_t HIT_SP = 2;    // rem <= |b|: suffix-prefix (R1 candidate)
 
+// Entry ranges of the ranks of a multi-GPU job (rank r holds the reads of entries [e[r], e[r+1])).
+struct RankMap {
+    uint32_t e[MAX_RANKS + 1];
+    int n;  // ranks; <= 1: single GPU
+};
+__host__ __device__ __forceinline__ int owner_of(const RankMap& R, uint32_t a) {
+    int r = 0;
+    while (r + 1 < R.n && a >= R.e[r + 1]) ++r;
+    return r;
+}
+// The rank that compares a candidate whose entries live on ranks ra and rb.  It is one of the two
+// (so one operand is always local), it is the same for a candidate and its strand-mirror twins
+// (symmetric in the two READS), and it is chosen along the ring so that rank r only ever needs the
+// reads of ranks r+1 .. r+floor(n/2): half of the all-gather a "verify where the candidate was
+// found" rule needs.  d == n/2 (n even) is the tie: split by the parity of the two read numbers.
+__host__ __device__ __forceinline__ int verifier_rank(int n, int ra, int rb, uint32_t a, uint32_t b) {
+    if (ra == rb) return ra;
+    int d = rb - ra;
+    if (d < 0) d += n;
+    if (2 * d < n) return ra;
+    if (2 * d > n) return rb;
+    const bool hi = (((a >> 1) + (b >> 1)) & 1u) != 0;
+    return hi ? (ra > rb ? ra : rb) : (ra < rb ? ra : rb);
+}
+// does rank r compare candidates that involve reads of rank s (does s have to send them to r)?
+__host__ __device__ __forceinline__ bool needs_reads_of(int n, int r, int s) {
+    if (r == s) return false;
+    int d = s - r;
+    if (d < 0) d += n;
+    return 2 * d <= n;
+}
+
 // Strand-mirror halving (k4_verify.cuh explains why it is exact).  When every read is present
 // on both strands (entry e ^ 1 is the other strand of entry e) only one candidate of each
 // strand-mirror pair is compared.  mirror_items() returns the HIT_* items candidate (a,p,b)
 // has to verify and emit itself; 0 means its twins cover it.
 struct MirrorRule {
     int on;
+    RankMap map;
 };
 // SP twins (a,.,b) <-> (b^1,.,a^1): which of the two compares is decided by a rule that is
 // symmetric under the swap and splits every rank's candidates about evenly (a plain "smaller a
@@ -107,11 +140,22 @@ __host__ __device__ __forceinline__ bool sp_self(uint32_t a, uint32_t bt) {
     const bool lt = a < bt;
     return (((a ^ bt) >> 1) & 1u) ? !lt : lt;
 }
-__device__ __forceinline__ uint32_t mirror_items(const MirrorRule& R, uint32_t a, uint32_t la, uint32_t b,
+// Candidates across two ranks: the twin maps (SP and CONT alike) turn the entry of the REMOTE read
+// (the one the comparing rank does not hold) into its other strand, so "compare the one whose remote
+// entry is the forward strand" picks exactly one of every twin pair -- and the reverse-complement
+// strands of remote reads are never needed: only forward strands travel, none is rebuilt.
+__host__ __device__ __forceinline__ uint32_t mirror_items(const MirrorRule& R, uint32_t a, uint32_t la, uint32_t b,
                                                  uint32_t lb, uint32_t p) {
     const uint32_t rem = la - p;
     uint32_t fl = (rem <= lb ? (uint32_t)HIT_SP : 0u) | (rem >= lb ? (uint32_t)HIT_CONT : 0u);
     if (R.on) {
+        if (R.map.n > 1) {
+            const int ra = owner_of(R.map, a), rb = owner_of(R.map, b);
+            if (ra != rb) {
+                const uint32_t remote = verifier_rank(R.map.n, ra, rb, a, b) == ra ? b : a;
+                return (remote & 1u) ? 0u : fl;
+            }
+        }
         if ((fl & HIT_SP) && !sp_self(a, b ^ 1u)) fl &= ~(uint32_t)HIT_SP;
         if (a & 1u) fl &= ~(uint32_t)HIT_CONT;
     }

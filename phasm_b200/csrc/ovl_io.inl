@@ -305,6 +305,7 @@ extern "C" int ovl_filter_rows(ovl_ctx* c, const ovl_filter_opts* o, const ovl_r
     if (fs) fs->rows_in = n;
     if (n == 0) return OVL_OK;
     if (n >= 0xffffffffull) return fail(c, OVL_E_LIMIT, "ovl_filter_rows: more than 2^32 rows");
+    OVL_TRY(gather_rows_pull(c));  // multi-GPU, rank 0: the other ranks' rows are still in their HBM
     cudaStream_t st = c->st;
     const size_t fm_bytes = ((size_t)M * 4 + 7) & ~(size_t)7;
     OVL_TRY(dev_ensure(c, c->d_fmark, fm_bytes + 16));  // firstmark[M] | counters[2]

@@ -193,13 +193,18 @@ class ShardedOverlapper:
             self.ov.comm_sync_ranges()
 
     def overlaps_device(self, min_length: int) -> int:
-        """Device pass on every rank; the rows of all ranks land in rank 0's HBM inside it."""
+        """Device pass on every rank; every rank keeps the rows of its A range in its HBM."""
         return self.ov.overlaps_device(min_length)
 
     def overlaps_arrays(self, min_length: int) -> np.ndarray:
-        """Rows on rank 0 (canonical order), an empty array elsewhere."""
+        """All rows on rank 0 (canonical order; pulled from the other ranks' HBM), an empty array
+        elsewhere.  The ranks meet again before returning: nobody starts another pass or tears its
+        arena down while rank 0 is still pulling."""
         self.ov.overlaps_device(min_length)
-        return self.ov.fetch_rows()
+        rows = self.ov.fetch_rows()
+        if self.world > 1:
+            self.chan.allgather_bytes(b"")
+        return rows
 
 
 # ---- process fan-out for the CLI -----------------------------------------------------------------

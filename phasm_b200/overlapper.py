@@ -222,6 +222,9 @@ class ExactOverlapper:
         self._check(self._lib.ovl_upload(self._ctx))
 
     def overlaps_device(self, min_length) -> int:
+        """One pass over HBM-resident inputs; the rows stay in HBM.  Multi-GPU: collective; every
+        rank ends with the rows of its A range in its own HBM, rank 0 returns the job's row count
+        (the others 0) and ``fetch_rows`` on rank 0 pulls all of them over NVLink."""
         n = c_uint64()
         self._check(self._lib.ovl_overlaps_device(self._ctx, _as_unsigned(min_length, "overlaps"),
                                                   byref(n)))

@@ -105,6 +105,61 @@ print("rdv %d ok" % rank)
 '''
 
 
+def test_placement_rule_keeps_exactly_one_of_every_twin_pair():
+    """The multi-GPU placement rule (ovl_common.cuh: verifier_rank / mirror_items), evaluated on the
+    host through the library: for every candidate item (suffix-prefix or containment) exactly one
+    of {the item, its strand-mirror twin} is compared, both on the same rank, that rank holds one of
+    the two reads, the read it does not hold enters as a forward strand, and rank r only ever needs
+    the reads of ranks r+1 .. r+floor(N/2)."""
+    import ctypes
+    from phasm_b200 import _capi
+    lib = _capi.load_library()
+    rng = np.random.default_rng(7)
+    for n_ranks in (1, 2, 3, 4, 5, 8):
+        reads = 6 * n_ranks
+        cuts = np.linspace(0, reads, n_ranks + 1).astype(np.uint32) * 2      # entry ranges, cut between reads
+        rank_e = (ctypes.c_uint32 * (n_ranks + 1))(*[int(x) for x in cuts])
+        lens = rng.integers(50, 200, size=reads)
+        owner = lambda e: int(np.searchsorted(cuts, e, side="right") - 1)
+
+        def rule(a, b, p):
+            items, ver = ctypes.c_uint32(), ctypes.c_int()
+            la, lb = int(lens[a >> 1]), int(lens[b >> 1])
+            assert lib.ovl_debug_mirror_items(n_ranks, rank_e, a, la, b, lb, p, ctypes.byref(items), ctypes.byref(ver)) == 0
+            return items.value, ver.value
+
+        work = np.zeros(n_ranks)
+        for _ in range(4000):
+            a, b = (int(x) for x in rng.integers(0, 2 * reads, size=2))
+            if a == b:
+                continue
+            la, lb = int(lens[a >> 1]), int(lens[b >> 1])
+            p = int(rng.integers(0, la))
+            rem = la - p
+            mine, ver = rule(a, b, p)
+            ra, rb = owner(a), owner(b)
+            assert ver in (ra, rb)
+            if ra != rb:
+                d = (rb - ra) % n_ranks if ver == ra else (ra - rb) % n_ranks   # ver needs the rank d ahead of it
+                assert 1 <= d <= n_ranks // 2
+                if mine:
+                    assert ((b if ver == ra else a) & 1) == 0      # the remote entry is a forward strand
+            work[ver] += bin(mine).count("1")
+            if rem <= lb:        # SP item: twin (b^1, lb-rem, a^1)
+                t, tver = rule(b ^ 1, a ^ 1, lb - rem)
+                assert tver == ver
+                if (a, p, b) == (b ^ 1, lb - rem, a ^ 1):
+                    assert mine & 2                                # its own twin: compares itself
+                else:
+                    assert bool(mine & 2) != bool(t & 2)
+            if rem >= lb:        # CONT item: twin (a^1, la-p-lb, b^1)
+                t, tver = rule(a ^ 1, b ^ 1, la - p - lb)
+                assert tver == ver
+                assert bool(mine & 1) != bool(t & 1)
+        if n_ranks > 1:
+            assert work.min() > 0.6 * work.mean(), work           # the compares spread over the ranks
+
+
 def test_tcp_rendezvous_allgather_world3(tmp_path):
     from phasm_b200.multi import free_port
     script = tmp_path / "rdv.py"

@@ -12,7 +12,7 @@ echo "pytest exit $T" >> "$OUT/pytest_gpu.log"; tail -15 "$OUT/pytest_gpu.log"
 timeout 600 python bench.py --steps 20 --warmup 3 > "$OUT/bench.json" 2> "$OUT/bench.err"; B=$?
 echo "bench exit $B"; python tools/benchsum.py < "$OUT/bench.json"; tail -5 "$OUT/bench.err"
 if [ "${2:-}" = "sweep" ]; then
-  for o in filter_kb=2048 filter_kb=4096 filter_kb=16384 pack_blocks_per_sm=8 anchor_stride=32; do
+  for o in anchor_stride=64 anchor_stride=16 filter_kb=4096 filter_kb=32768; do
     echo "== $o"
     timeout 300 python bench.py --steps 10 --warmup 3 --no-cpu --no-parity --opt $o 2>&1 | tee -a "$OUT/sweep.jsonl" | python tools/benchsum.py
   done
