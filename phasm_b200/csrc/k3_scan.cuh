@@ -54,14 +54,20 @@ struct ScanParams {
     int bm_bits;                // sparse: log2 bits of one slice; dense: log2 words
     TableView T;
     KeyFmt fmt;
-    SurvSink surv;              // k3_filter -> k3_resolve
-    CandSink sink;
+    SurvSink surv;              // k3_filter: survivors to the rank that owns their k-mer
+    SegList<Surv> probes;       // k3_resolve: the survivors routed to this rank
+    CandSink sink;              // candidate keys to the rank that compares them
     MirrorRule mirror;          // on: emit only the candidates that verify for themselves
 };
 
 // candidates of one (a, q) probe whose key resolved to list pointer `ptr` (warp-converged walk)
+__device__ __forceinline__ uint32_t cand_dest(const ScanParams& P, uint64_t key) {
+    const uint32_t a = P.fmt.a(key), b = P.fmt.b(key);
+    return (uint32_t)verifier_rank(P.mirror.map.n, owner_of(P.mirror.map, a), owner_of(P.mirror.map, b), a, b);
+}
+
 __device__ __forceinline__ void walk_list(const ScanParams& P, uint32_t owner, uint32_t ptr, uint32_t a, uint32_t la,
-                                          uint32_t q, uint64_t* buf, uint32_t& nbuf, uint32_t lane) {
+                                          uint32_t q, uint64_t* buf, uint32_t& nbuf, uint32_t lane, RouteScratch* rs) {
     const int sl = P.stride_log2;
     const uint32_t smask = (1u << sl) - 1u;
     while (__any_sync(FULL, ptr != NIL)) {
@@ -79,7 +85,7 @@ __device__ __forceinline__ void walk_list(const ScanParams& P, uint32_t owner, u
             }
             ptr = nxt;
         }
-        wbuf_push(buf, nbuf, P.sink, lane, have, key);
+        wbuf_push(buf, nbuf, P.sink, lane, have, key, rs, [&](uint64_t k2) { return cand_dest(P, k2); });
     }
 }
 
@@ -103,6 +109,8 @@ __global__ void __launch_bounds__(256, 4) k3_filter_wide(const ScanParams P) {
     constexpr int NP = SL == 6 ? 1 : 2;
     constexpr uint32_t SCAP = WBUF / 2;
     __shared__ Surv s_buf[8][SCAP];
+    __shared__ RouteScratch s_rs[8];
+    RouteScratch* rs = &s_rs[threadIdx.x >> 5];
     const uint32_t lane = threadIdx.x & 31;
     const uint32_t ltmask = (1u << lane) - 1u;
     const uint32_t warp = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
@@ -110,6 +118,7 @@ __global__ void __launch_bounds__(256, 4) k3_filter_wide(const ScanParams P) {
     const uint32_t n_tiles = P.n_tiles;
     const uint64_t kmask = kmer_mask(P.k);
     const uint32_t nr = P.T.nr;
+    auto surv_dest = [nr](const Surv& r) { return owner_of_hash(r.x, nr); };
     const uint32_t kk = (uint32_t)P.k, ll = P.l;
     const int bmb = P.bm_bits;
     Surv* buf = s_buf[threadIdx.x >> 5];
@@ -161,7 +170,7 @@ __global__ void __launch_bounds__(256, 4) k3_filter_wide(const ScanParams P) {
             total += __popc(m[j]);
         }
         if (total) {  // warp-uniform
-            if (nbuf + total > SCAP) wbuf_flush(buf, nbuf, P.surv, lane);
+            if (nbuf + total > SCAP) wbuf_flush(buf, nbuf, P.surv, lane, rs, surv_dest);
             uint32_t o = nbuf;
 #pragma unroll
             for (int j = 0; j < NP; ++j) {
@@ -184,7 +193,7 @@ __global__ void __launch_bounds__(256, 4) k3_filter_wide(const ScanParams P) {
         v1 = v2;
         rec2 = rec3;
     }
-    if (nbuf) wbuf_flush(buf, nbuf, P.surv, lane);
+    if (nbuf) wbuf_flush(buf, nbuf, P.surv, lane, rs, surv_dest);
 }
 
 // Smaller strides (SL = 4, 3: 4 or 8 probes per lane at fixed offsets, loops unrolled; SL < 0: the
@@ -192,9 +201,11 @@ __global__ void __launch_bounds__(256, 4) k3_filter_wide(const ScanParams P) {
 template <int SL>
 __global__ void __launch_bounds__(256) k3_filter(const ScanParams P) {
     __shared__ Surv s_buf[8][WBUF / 2];
+    __shared__ RouteScratch s_rs[8];
     constexpr uint32_t SCAP = WBUF / 2;
     const uint32_t lane = threadIdx.x & 31;
     const uint32_t wib = threadIdx.x >> 5;
+    RouteScratch* rs = &s_rs[wib];
     const uint32_t warp = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
     const uint32_t nwarps = (gridDim.x * blockDim.x) >> 5;
     const uint32_t n_tiles = P.n_tiles;
@@ -203,6 +214,7 @@ __global__ void __launch_bounds__(256) k3_filter(const ScanParams P) {
     const int sl = SL >= 0 ? SL : P.stride_log2;
     const uint32_t n_probe = GRAN_BASES >> sl;
     const uint32_t nr = P.T.nr;
+    auto surv_dest = [nr](const Surv& r) { return owner_of_hash(r.x, nr); };
     Surv* buf = s_buf[wib];
     uint32_t nbuf = 0;
 
@@ -266,58 +278,50 @@ __global__ void __launch_bounds__(256) k3_filter(const ScanParams P) {
                 r.y = ((uint64_t)a << 32) | (pos0 + off);
             }
             const unsigned m = __ballot_sync(FULL, have);
-            if (nbuf + 32 > SCAP) wbuf_flush(buf, nbuf, P.surv, lane);
+            if (nbuf + 32 > SCAP) wbuf_flush(buf, nbuf, P.surv, lane, rs, surv_dest);
             if (have) buf[nbuf + __popc(m & ((1u << lane) - 1u))] = r;
             nbuf += __popc(m);
             __syncwarp();
         }
     }
-    if (nbuf) wbuf_flush(buf, nbuf, P.surv, lane);
-}
-
-// ---- sparse path, N > 1 GPUs: survivors to the rank that owns their k-mer -----------------------
-struct ProbeRouteParams {
-    const Surv* items;                // survivors of this rank's filter pass
-    const unsigned long long* n_ptr;
-    uint64_t cap;
-    RouteLists<Surv> lists;           // probe list of every rank (counter: ArenaHdr::scan_n)
-};
-
-__global__ void __launch_bounds__(256) k3_route(const ProbeRouteParams P) {
-    const unsigned long long n_all = *P.n_ptr;
-    const uint64_t n = n_all < P.cap ? n_all : P.cap;
-    const uint32_t nr = P.lists.nr;
-    route_items<Surv>(P.items, n, P.lists, [nr](const Surv& r) { return owner_of_hash(r.x, nr); }, nullptr);
+    if (nbuf) wbuf_flush(buf, nbuf, P.surv, lane, rs, surv_dest);
 }
 
 // ---- sparse path, pass 2 ------------------------------------------------------------------
 __global__ void __launch_bounds__(256) k3_resolve(const ScanParams P) {
     __shared__ uint64_t s_buf[8][WBUF];
+    __shared__ RouteScratch s_rs[8];
     const uint32_t lane = threadIdx.x & 31;
     uint64_t* buf = s_buf[threadIdx.x >> 5];
+    RouteScratch* rs = &s_rs[threadIdx.x >> 5];
     uint32_t nbuf = 0;
-    const unsigned long long n_all = *P.surv.n_out;
-    const uint64_t n = n_all < P.surv.cap ? n_all : P.surv.cap;
     const uint64_t nthreads = (uint64_t)gridDim.x * blockDim.x;
-    for (uint64_t i0 = ((uint64_t)blockIdx.x * blockDim.x + threadIdx.x) & ~31ull; i0 < n; i0 += nthreads) {
-        const uint64_t i = i0 + lane;
-        uint32_t ptr = NIL, owner = 0, a = 0, q = 0, la = 0;
-        if (i < n) {
-            const Surv rec = P.surv.out[i];
-            a = (uint32_t)(rec.y >> 32);
-            q = (uint32_t)rec.y;
-            ptr = table_find(P.T, rec.x, owner);
-            la = __ldg(P.ent + a).y;
+    for (uint32_t seg = 0; seg < P.probes.nr; ++seg) {  // the survivors every source rank sent here
+        const unsigned long long n_all = P.probes.n[seg];
+        const uint64_t n = n_all < P.probes.seg_cap ? n_all : P.probes.seg_cap;
+        const Surv* __restrict__ list = P.probes.base + (uint64_t)seg * P.probes.seg_cap;
+        for (uint64_t i0 = ((uint64_t)blockIdx.x * blockDim.x + threadIdx.x) & ~31ull; i0 < n; i0 += nthreads) {
+            const uint64_t i = i0 + lane;
+            uint32_t ptr = NIL, owner = 0, a = 0, q = 0, la = 0;
+            if (i < n) {
+                const Surv rec = list[i];
+                a = (uint32_t)(rec.y >> 32);
+                q = (uint32_t)rec.y;
+                ptr = table_find(P.T, rec.x, owner);
+                la = __ldg(P.ent + a).y;
+            }
+            walk_list(P, owner, ptr, a, la, q, buf, nbuf, lane, rs);
         }
-        walk_list(P, owner, ptr, a, la, q, buf, nbuf, lane);
     }
-    if (nbuf) wbuf_flush(buf, nbuf, P.sink, lane);
+    if (nbuf) wbuf_flush(buf, nbuf, P.sink, lane, rs, [&](uint64_t k2) { return cand_dest(P, k2); });
 }
 
 // ---- dense path (stride 1) -----------------------------------------------------------------
 template <bool SMEM_FILTER>
 __global__ void __launch_bounds__(1024, 1) k3_scan(const ScanParams P) {
     extern __shared__ __align__(16) unsigned char s_raw[];
+    __shared__ RouteScratch s_rs[32];
+    RouteScratch* rs = &s_rs[threadIdx.x >> 5];
     uint64_t* s_bufs = reinterpret_cast<uint64_t*>(s_raw);               // [32][WBUF]
     uint32_t* s_filter = reinterpret_cast<uint32_t*>(s_raw + 32 * WBUF * 8);
     const uint32_t* filt;
@@ -387,10 +391,10 @@ __global__ void __launch_bounds__(1024, 1) k3_scan(const ScanParams P) {
                 const uint64_t x = (j < 32 ? kmer_at(w0, w1, j) : kmer_at(w1, w2, j - 32)) & kmask;
                 ptr = table_find(P.T, mix64(x), owner);
             }
-            walk_list(P, owner, ptr, a, la, p, buf, nbuf, lane);
+            walk_list(P, owner, ptr, a, la, p, buf, nbuf, lane, rs);
         }
     }
-    if (nbuf) wbuf_flush(buf, nbuf, P.sink, lane);
+    if (nbuf) wbuf_flush(buf, nbuf, P.sink, lane, rs, [&](uint64_t k2) { return cand_dest(P, k2); });
 }
 
 }  // namespace ovl

@@ -24,9 +24,7 @@
 namespace ovl {
 
 struct VerifyParams {
-    const uint64_t* keys;              // candidate keys (flags clear), any order
-    const unsigned long long* n_ptr;   // their number: a device counter
-    uint64_t cap;                      // capacity of `keys` (the counter may exceed it on overflow)
+    SegList<uint64_t> keys;            // candidate keys (flags clear), any order: the verify list of this rank
     const uint4* packed;
     const uint2* ent;                  // {gran0, len}
     KeyFmt fmt;
@@ -90,15 +88,26 @@ __device__ __forceinline__ void hit_keys(const KeyFmt& fmt, const uint2* __restr
     if (fl & HIT_CONT) out[2] = fmt.make(at, bt, la - p - lb) | HIT_CONT;
 }
 
+// a hit key goes to the rank that owns its A entry (rows are emitted per A entry)
+template <class Params>
+__device__ __forceinline__ uint32_t hit_dest(const Params& P, uint64_t key) {
+    return (uint32_t)owner_of(P.mirror.map, P.fmt.a(key));
+}
+
 __global__ void __launch_bounds__(256) k4_verify_serial(const VerifyParams P) {
     __shared__ uint64_t s_buf[8][WBUF];
+    __shared__ RouteScratch s_rs[8];
+    __shared__ unsigned long long s_pre[MAX_RANKS + 1];
     uint64_t* buf = s_buf[threadIdx.x >> 5];
+    RouteScratch* rs = &s_rs[threadIdx.x >> 5];
     uint32_t nbuf = 0;
     const uint32_t lane = threadIdx.x & 31;
     const uint64_t warp = ((uint64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
     const uint64_t nwarps = ((uint64_t)gridDim.x * blockDim.x) >> 5;
-    const uint64_t n_all = *P.n_ptr < P.cap ? *P.n_ptr : P.cap;
+    seg_prefix(P.keys, s_pre);
+    const uint64_t n_all = s_pre[P.keys.nr];
     const uint64_t n_tiles = (n_all + 31) / 32;
+    auto dest = [&](uint64_t k2) { return hit_dest(P, k2); };
     unsigned long long sum_m = 0, sum_b = 0;
 
     for (uint64_t tile = warp; tile < n_tiles; tile += nwarps) {
@@ -106,7 +115,7 @@ __global__ void __launch_bounds__(256) k4_verify_serial(const VerifyParams P) {
         uint64_t key = 0;
         uint32_t my_ga = 0, my_gb = 0, my_sh = 0, my_n = 0, my_fl = 0;
         if (c < n_all) {
-            key = P.keys[c];
+            key = P.keys.base[seg_phys(P.keys, s_pre, c)];
             const uint32_t a = P.fmt.a(key), b = P.fmt.b(key), p = P.fmt.p(key);
             const uint2 ma = __ldg(P.ent + a), mb = __ldg(P.ent + b);
             const uint32_t rem = ma.y - p;
@@ -163,9 +172,9 @@ __global__ void __launch_bounds__(256) k4_verify_serial(const VerifyParams P) {
         uint64_t hk[3] = {0, 0, 0};
         if (my_ok) hit_keys(P.fmt, P.ent, P.mirror, key, my_fl, hk);
 #pragma unroll
-        for (int i = 0; i < 3; ++i) wbuf_push(buf, nbuf, P.hits, lane, hk[i] != 0, hk[i]);
+        for (int i = 0; i < 3; ++i) wbuf_push(buf, nbuf, P.hits, lane, hk[i] != 0, hk[i], rs, dest);
     }
-    if (nbuf) wbuf_flush(buf, nbuf, P.hits, lane);
+    if (nbuf) wbuf_flush(buf, nbuf, P.hits, lane, rs, dest);
     if (lane == 0) {
         if (P.collect && sum_m) {
             atomicAdd(P.counters + 0, sum_m);
@@ -211,13 +220,12 @@ constexpr int HEAD_UNROLL = 4;
 // Multi-GPU: the twin's key may belong to another rank's A range; k6_exchange.cuh ships every
 // hit key to the rank that owns its A entry before the sort.
 struct Verify2Params {
-    const uint64_t* keys;              // candidate keys (flags clear), any order
-    const unsigned long long* n_ptr;   // their number: a device counter (no host round trip after the scan)
-    uint64_t cap;                      // capacity of `keys` (the counter may exceed it on overflow)
+    SegList<uint64_t> keys;            // candidate keys (flags clear), any order: the verify list of this rank
+                                       // (sizes are device counters: no host round trip after the scan)
     const uint64_t* packed64;
     const uint2* ent;                  // {gran0, len}
     KeyFmt fmt;
-    uint32_t* surv;                    // k4a -> k4b: indices of candidates alive after the head
+    uint32_t* surv;                    // k4a -> k4b: physical indices (into keys.base) of the candidates alive after the head
     unsigned long long* n_surv;
     CandSink hits;                     // verified keys with their flag bits set
     MirrorRule mirror;                 // on: the scan kept only the self-verifying candidates
@@ -295,19 +303,25 @@ __device__ __forceinline__ uint4 align_a_dyn(const uint4 b, const uint2 s, uint3
 
 __global__ void __launch_bounds__(256, 4) k4a_head(const Verify2Params P) {
     __shared__ uint64_t s_buf[8][WBUF];
+    __shared__ RouteScratch s_rs[8];
+    __shared__ unsigned long long s_pre[MAX_RANKS + 1];
     const uint32_t lane = threadIdx.x & 31;
-    const uint64_t n_all = *P.n_ptr < P.cap ? *P.n_ptr : P.cap;
+    seg_prefix(P.keys, s_pre);
+    const uint64_t n_all = s_pre[P.keys.nr];
     const uint64_t n_tiles = (n_all + 31) / 32;
     uint64_t* buf = s_buf[threadIdx.x >> 5];
+    RouteScratch* rs = &s_rs[threadIdx.x >> 5];
+    auto dest = [&](uint64_t k2) { return hit_dest(P, k2); };
     uint32_t nbuf = 0;
     const uint4* packed128 = reinterpret_cast<const uint4*>(P.packed64);
 
     for (uint64_t tile = next_tile(P.tile_ctr, lane); tile < n_tiles; tile = next_tile(P.tile_ctr, lane)) {
         const uint64_t c = tile * 32 + lane;
-        uint64_t key = 0;
+        uint64_t key = 0, phys = 0;
         CandMeta my = {0, 0, 0, 0, 0};  // n == 0 marks "no candidate" (a real one has n >= l >= 1)
         if (c < n_all) {
-            key = P.keys[c];
+            phys = seg_phys(P.keys, s_pre, c);
+            key = P.keys.base[phys];
             my = cand_meta(P, key);
         }
         uint32_t ok_mask = 0;  // bit j: candidate j matched over its head
@@ -348,16 +362,16 @@ __global__ void __launch_bounds__(256, 4) k4a_head(const Verify2Params P) {
         uint64_t hk[3] = {0, 0, 0};
         if (done) hit_keys(P.fmt, P.ent, P.mirror, key, my.fl, hk);
 #pragma unroll
-        for (int i = 0; i < 3; ++i) wbuf_push(buf, nbuf, P.hits, lane, hk[i] != 0, hk[i]);
+        for (int i = 0; i < 3; ++i) wbuf_push(buf, nbuf, P.hits, lane, hk[i] != 0, hk[i], rs, dest);
         const unsigned am = __ballot_sync(FULL, alive);
         if (am) {
             unsigned long long base = 0;
             if (lane == 0) base = atomicAdd(P.n_surv, (unsigned long long)__popc(am));
             base = __shfl_sync(FULL, base, 0);
-            if (alive) P.surv[base + __popc(am & ((1u << lane) - 1u))] = (uint32_t)c;
+            if (alive) P.surv[base + __popc(am & ((1u << lane) - 1u))] = (uint32_t)phys;
         }
     }
-    if (nbuf) wbuf_flush(buf, nbuf, P.hits, lane);
+    if (nbuf) wbuf_flush(buf, nbuf, P.hits, lane, rs, dest);
 }
 
 // OR of the differences of compare-granules [FIRST_GRAN, ceil(n/64)) for one lane (stride 32,
@@ -419,6 +433,9 @@ __device__ __forceinline__ uint4 tail_diff(const uint4* __restrict__ pa, const u
 
 __global__ void __launch_bounds__(256, 4) k4b_tail(const Verify2Params P) {
     __shared__ uint64_t s_buf[8][WBUF];
+    __shared__ RouteScratch s_rs[8];
+    RouteScratch* rs = &s_rs[threadIdx.x >> 5];
+    auto dest = [&](uint64_t k2) { return hit_dest(P, k2); };
     const uint32_t lane = threadIdx.x & 31;
     const uint64_t ns = *P.n_surv;
     const uint64_t n_tiles = (ns + 31) / 32;
@@ -433,7 +450,7 @@ __global__ void __launch_bounds__(256, 4) k4b_tail(const Verify2Params P) {
         uint64_t key = 0;
         CandMeta my = {0, 0, 0, 0, 0};
         if (s < ns) {
-            key = P.keys[P.surv[s]];
+            key = P.keys.base[P.surv[s]];
             my = cand_meta(P, key);
         }
         const uint32_t cnt = (uint32_t)((ns - tile * 32) < 32 ? (ns - tile * 32) : 32);
@@ -460,9 +477,9 @@ __global__ void __launch_bounds__(256, 4) k4b_tail(const Verify2Params P) {
         uint64_t hk[3] = {0, 0, 0};
         if ((ok_mask >> lane) & 1u) hit_keys(P.fmt, P.ent, P.mirror, key, my.fl, hk);
 #pragma unroll
-        for (int i = 0; i < 3; ++i) wbuf_push(buf, nbuf, P.hits, lane, hk[i] != 0, hk[i]);
+        for (int i = 0; i < 3; ++i) wbuf_push(buf, nbuf, P.hits, lane, hk[i] != 0, hk[i], rs, dest);
     }
-    if (nbuf) wbuf_flush(buf, nbuf, P.hits, lane);
+    if (nbuf) wbuf_flush(buf, nbuf, P.hits, lane, rs, dest);
 }
 
 }  // namespace ovl

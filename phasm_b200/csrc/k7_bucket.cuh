@@ -29,9 +29,7 @@ namespace ovl {
 constexpr uint32_t BUCKET_MAX = 256;  // keys one warp sorts in shared memory
 
 struct BucketParams {
-    const uint64_t* hits;             // unsorted hit keys
-    const unsigned long long* n_ptr;  // their number (device counter)
-    uint64_t cap;                     // capacity of `hits` (the counter may exceed it on overflow)
+    SegList<uint64_t> hits;           // unsorted hit keys: the hit list of this rank (sizes are device counters)
     KeyFmt fmt;
     uint32_t M;
     uint32_t* cnt;                    // [M+1] hits per entry (zeroed by the host), cnt[M] stays 0
@@ -47,26 +45,28 @@ struct BucketParams {
     uint64_t rows_cap;
 };
 
-__device__ __forceinline__ uint64_t hit_count(const BucketParams& P) {
-    const unsigned long long n = *P.n_ptr;
-    return n < P.cap ? n : P.cap;
+// f(key) for every key of the hit list (segment by segment, grid-stride inside)
+template <class F>
+__device__ __forceinline__ void for_each_hit(const BucketParams& P, F f) {
+    for (uint32_t seg = 0; seg < P.hits.nr; ++seg) {
+        const unsigned long long n_all = P.hits.n[seg];
+        const uint64_t n = n_all < P.hits.seg_cap ? n_all : P.hits.seg_cap;
+        const uint64_t* __restrict__ list = P.hits.base + (uint64_t)seg * P.hits.seg_cap;
+        for (uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (uint64_t)gridDim.x * blockDim.x) f(list[i]);
+    }
 }
 
 __global__ void __launch_bounds__(256) k7_hist(const BucketParams P) {
-    const uint64_t n = hit_count(P);
     const int sa = 2 + P.fmt.bits_p + P.fmt.bits_e;
-    for (uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (uint64_t)gridDim.x * blockDim.x)
-        atomicAdd(P.cnt + (uint32_t)(P.hits[i] >> sa), 1u);
+    for_each_hit(P, [&](uint64_t key) { atomicAdd(P.cnt + (uint32_t)(key >> sa), 1u); });
 }
 
 __global__ void __launch_bounds__(256) k7_scatter(const BucketParams P) {
-    const uint64_t n = hit_count(P);
     const int sa = 2 + P.fmt.bits_p + P.fmt.bits_e;
-    for (uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (uint64_t)gridDim.x * blockDim.x) {
-        const uint64_t key = P.hits[i];
+    for_each_hit(P, [&](uint64_t key) {
         const uint32_t a = (uint32_t)(key >> sa);
         P.sorted[P.off[a] + atomicAdd(P.cur + a, 1u)] = key;
-    }
+    });
 }
 
 // rows of key i of a sorted run whose predecessor is `prev` (have_prev = false at a run start)

@@ -74,18 +74,21 @@ enum Ev { E_H2D0, E_H2D1, E_PACK0, E_ANCHOR0, E_SCAN0, E_VERIFY0, E_SORT0, E_EMI
 enum Ctr {
     C_ERR,     // (entry + 1) of an entry holding a non-ACGT byte
     C_NANC,    // entries with |b| >= l
-    C_NSCAN,   // survivors of the scan's filter pass
-    C_NCAND,   // candidate keys
-    C_NSTAGE,  // verified hit keys staged for routing (N > 1, mirror mode)
     C_SUMM, C_SUMB,  // accounting mode: sum m_c, sum 2*ceil(m_c/4)   (adjacent: the verifier takes a pointer to both)
     C_NSURV,   // candidates alive after the verifier's head
     C_TILE_A, C_TILE_B,  // dynamic tile hand-out of k4a / k4b (adjacent)
     C_BIG,     // buckets above BUCKET_MAX keys
     C_FLAGS,   // STF_* bits raised by kernels
-    C_NSENT,   // hit keys routed to other ranks
     C_NROWS,   // rows of this rank
-    C_COUNT
+    C_SEND,    // [L_COUNT][MAX_RANKS] items this rank appended to its segment of every rank's lists (N > 1)
+    C_COUNT = C_SEND + ovl::L_COUNT * ovl::MAX_RANKS
 };
+
+// pinned host mirror read after the one synchronisation of a pass (64-bit words)
+constexpr int H_STATUS = C_COUNT;                                             // [MAX_RANKS][STATUS_WORDS]
+constexpr int H_SEGN = H_STATUS + ovl::MAX_RANKS * ovl::STATUS_WORDS;          // [L_COUNT][MAX_RANKS]
+constexpr int H_STEP = H_SEGN + ovl::L_COUNT * ovl::MAX_RANKS;                 // the step id (source of a H2D copy)
+constexpr int H_WORDS = H_STEP + 1;
 
 // byte offsets of the pieces of an arena (the header sits at 0); published to the peers
 constexpr int PUSH_STREAMS = 4;
@@ -93,10 +96,8 @@ constexpr int PUSH_STREAMS = 4;
 struct ArenaLayout {
     uint64_t bytes;
     uint64_t off_pre, off_packed, off_filter, off_table, off_next, off_scan, off_cand, off_inbox, off_rows;
-    uint64_t scan_cap;   // scan survivors (probe list)
-    uint64_t cand_cap;   // candidate keys routed to this rank for comparison (N > 1)
-    uint64_t inbox_cap;  // hit keys
-    uint64_t rows_cap;   // rows (rank 0 of a multi-GPU job: the rows of all ranks)
+    uint64_t seg_cap[ovl::L_COUNT];  // items per SEGMENT (one segment per source rank) of the probe / verify / hit list
+    uint64_t rows_cap;               // rows (rank 0 of a multi-GPU job: room for the rows of all ranks, for the pull)
 };
 
 struct PeerInfo {
@@ -123,7 +124,7 @@ struct ovl_ctx {
     std::string err;
     // resident blocks per SM of the persistent (grid-stride) kernels, from the occupancy calculator
     struct {
-        int filter6 = 1, filter5 = 1, filter4 = 1, filter3 = 1, filterx = 1, resolve = 1, route = 1, head = 1, tail = 1, pack = 1;
+        int filter6 = 1, filter5 = 1, filter4 = 1, filter3 = 1, filterx = 1, resolve = 1, head = 1, tail = 1, pack = 1;
     } occ;
 
     // ---- host entry store ----
@@ -148,7 +149,7 @@ struct ovl_ctx {
     // ---- device: persistent tables ----
     DevBuf d_ascii, d_src, d_len, d_flags, d_gran0, d_ent, d_tile0, d_tile_ent, d_stile0, d_scan_tiles;
     // ---- device: per-pass working buffers outside the arena ----
-    DevBuf d_ctr, d_tmp, d_cand, d_stage, d_scan, d_cnt, d_bkt, d_big, d_peerhdr;
+    DevBuf d_ctr, d_tmp, d_cand, d_cnt, d_bkt, d_big, d_peerhdr;
     DevBuf d_fmark, d_fkeep, d_foff, d_frows;  // ovl_filter_rows
     DevBuf d_rows;                             // VIEW of the arena's row array (not owned)
     // ---- the arena ----
@@ -161,7 +162,7 @@ struct ovl_ctx {
     uint64_t step = 0;
 
     PinBuf h_frows, h_rows;
-    uint64_t* h_ctr = nullptr;   // pinned: counters | status[MAX_RANKS][STATUS_WORDS] | rowcnt[MAX_RANKS] | inbox_n | step
+    uint64_t* h_ctr = nullptr;   // pinned, H_WORDS words: counters | status of every rank | segment counts | step
     uint64_t cand_cap = 0;       // candidate keys one pass may emit
     uint64_t min_cand_cap = 1ull << 20;
     uint64_t cand_per_entry = 96;  // first candidate capacity: this many keys per local entry
@@ -388,10 +389,15 @@ int connect_arena(ovl_ctx* c, bool mirror, uint64_t scan_cap) {
     const int nr = c->nranks, me = c->rank;
     const uint32_t M = (uint32_t)c->len.size();
     const uint64_t hit_cap = mirror ? 3 * c->cand_cap : c->cand_cap;  // own key + SP twin + CONT twin
-    uint64_t rows_total = hit_cap;
+    // the three item lists: one segment per source rank.  Items spread about evenly over the
+    // destinations (k-mer hash, placement rule, base-balanced A ranges): a segment gets twice its
+    // even share, the receiver checks the counts and the pass is repeated larger if one overflows
+    auto seg = [&](uint64_t total) { return nr > 1 ? 2 * total / nr + 64 : total; };
+    const uint64_t own_rows = (uint64_t)nr * seg(hit_cap);  // a rank emits at most one row per hit key in its list
+    uint64_t rows_total = own_rows;
     if (nr > 1) {
         std::vector<uint64_t> caps(nr);
-        OVL_TRY(allgather_host(c, &hit_cap, 8, caps.data()));
+        OVL_TRY(allgather_host(c, &own_rows, 8, caps.data()));
         if (me == 0) {
             rows_total = 0;
             for (int r = 0; r < nr; ++r) rows_total += caps[r];
@@ -413,12 +419,13 @@ int connect_arena(ovl_ctx* c, bool mirror, uint64_t scan_cap) {
     L.off_filter = take(std::max(f_sparse, f_dense));
     L.off_table = take(8ull << table_bits(keys_max, nr));
     L.off_next = take(keys_max * 4);
-    L.scan_cap = scan_cap;
-    L.off_scan = take(scan_cap * 16);
-    L.cand_cap = nr > 1 ? c->cand_cap : 0;
-    L.off_cand = take(L.cand_cap * 8);
-    L.inbox_cap = hit_cap;
-    L.off_inbox = take(hit_cap * 8);
+    L.seg_cap[L_SCAN] = seg(scan_cap);
+    L.seg_cap[L_CAND] = seg(c->cand_cap);
+    L.seg_cap[L_HITS] = seg(hit_cap);
+    if ((uint64_t)nr * L.seg_cap[L_CAND] > 0xfffffff0ull) return fail(c, OVL_E_LIMIT, "more than 2^32 candidate slots on one GPU");
+    L.off_scan = take((uint64_t)nr * L.seg_cap[L_SCAN] * 16);
+    L.off_cand = take((uint64_t)nr * L.seg_cap[L_CAND] * 8);
+    L.off_inbox = take((uint64_t)nr * L.seg_cap[L_HITS] * 8);
     L.rows_cap = rows_total;
     L.off_rows = take(rows_total * sizeof(Row));
     L.bytes = off;
@@ -754,8 +761,8 @@ int run_pass(ovl_ctx* c, uint32_t min_length, bool chunked) {
     const uint64_t probes = n_gran_local * (uint64_t)(64u >> slog);
     // N > 1: a candidate is found by the rank that owns its k-mer, compared by verifier_rank() of its
     // two entries (and, with mirror halving, yields its twins' keys too) and emitted by the rank that
-    // owns its A entry: candidate keys and hit keys are routed between the ranks
-    const bool route = nr > 1;
+    // owns its A entry: survivors, candidate keys and hit keys go straight from the producing kernel
+    // into the consumer rank's list (ovl_common.cuh: Sink / SegList)
     const bool have_anchors = n_anc != 0;
 
     cudaStream_t st = c->st, sk = c->st_k2, sp = c->st_push, sg = c->st_sig;
@@ -769,7 +776,6 @@ int run_pass(ovl_ctx* c, uint32_t min_length, bool chunked) {
             c->cand_cap = cap;
         }
         if (c->cand_cap > 0x7fffffffull) return fail(c, OVL_E_LIMIT, "more than 2^31 candidates on one GPU");
-        const uint64_t hit_cap = mirror ? 3 * c->cand_cap : c->cand_cap;
         const uint64_t scan_cap = dense ? 1 : std::min<uint64_t>(probes + 32, 2 * c->cand_cap + probes / 8 + 4096);
         // ---- the arena (and, on N > 1, the peer mappings) -----------------------------------
         const uint64_t key[4] = {c->generation, c->cand_cap, ((uint64_t)nr << 8) | ((uint64_t)slog << 1) | (uint64_t)mirror, c->arena_epoch};
@@ -785,14 +791,11 @@ int run_pass(ovl_ctx* c, uint32_t min_length, bool chunked) {
         uint32_t* d_filter = at<uint32_t>(A, L.off_filter);
         Slot* d_table = at<Slot>(A, L.off_table);
         uint32_t* d_next = at<uint32_t>(A, L.off_next);
-        Surv* d_probes = at<Surv>(A, L.off_scan);
-        uint64_t* d_inbox = at<uint64_t>(A, L.off_inbox);
         Row* d_rows = at<Row>(A, L.off_rows);
-        OVL_TRY(dev_ensure(c, c->d_cand, hit_cap * 8, false));  // candidates, later the bucketed hit keys
-        if (route) OVL_TRY(dev_ensure(c, c->d_stage, hit_cap * 8, false));
-        const bool route_probes = !dense && nr > 1;  // scan survivors travel to the rank that owns their k-mer
-        if (route_probes) OVL_TRY(dev_ensure(c, c->d_scan, scan_cap * sizeof(Surv), false));
-        OVL_TRY(dev_ensure(c, c->d_cnt, c->cand_cap * 4, false));  // survivor list of the verifier's head
+        const uint64_t hits_room = (uint64_t)nr * L.seg_cap[L_HITS];  // hit keys this rank's list can hold = rows it can emit
+        const uint64_t cand_room = (uint64_t)nr * L.seg_cap[L_CAND];
+        OVL_TRY(dev_ensure(c, c->d_cand, hits_room * 8, false));  // the bucketed, then sorted hit keys
+        OVL_TRY(dev_ensure(c, c->d_cnt, cand_room * 4, false));   // survivor list of the verifier's head
         OVL_TRY(dev_ensure(c, c->d_big, (size_t)M * 4 + 4, false));
         const size_t M1 = (size_t)M + 1;
         OVL_TRY(dev_ensure(c, c->d_bkt, M1 * (8 + 8 + 4 + 4 + 4)));
@@ -804,14 +807,14 @@ int run_pass(ovl_ctx* c, uint32_t min_length, bool chunked) {
         uint64_t* ctr = c->d_ctr.as<uint64_t>();
         uint32_t launches = 0, lib = 0;
         ++c->step;
-        uint64_t* h_step = c->h_ctr + C_COUNT + MAX_RANKS * STATUS_WORDS + MAX_RANKS + 3;
+        uint64_t* h_step = c->h_ctr + H_STEP;
         *h_step = c->step;
 
         // ---- start: counters, step word -----------------------------------------------------
         if (chunked) CK(cudaEventRecord(c->ev[E_H2D0], st));
         CK(cudaEventRecord(c->ev[E_PACK0], st));
         CK(cudaMemsetAsync(ctr, 0, C_COUNT * sizeof(uint64_t), st));
-        CK(cudaMemsetAsync(&H->inbox_n, 0, 24, st));  // inbox_n, scan_n, cand_n
+        CK(cudaMemsetAsync(H->seg_n, 0, sizeof H->seg_n, st));
         CK(cudaMemcpyAsync(&H->step_word, h_step, 8, cudaMemcpyHostToDevice, st));
         CK(cudaEventRecord(c->ev_k0, st));
         CK(cudaStreamWaitEvent(sk, c->ev_k0, 0));
@@ -983,6 +986,40 @@ int run_pass(ovl_ctx* c, uint32_t min_length, bool chunked) {
         }
         CK(cudaEventRecord(c->ev[E_SCAN0], st));
 
+        // ---- the three item lists of this pass: where this rank appends (its segment in every
+        //      rank's list), and its own list as the consumers see it ---------------------------------
+        const uint64_t off_list[L_COUNT] = {L.off_scan, L.off_cand, L.off_inbox};
+        const size_t item_size[L_COUNT] = {sizeof(Surv), 8, 8};
+        auto fill_sink = [&](auto& sink, int kind) {
+            using T = std::remove_pointer_t<std::remove_reference_t<decltype(sink.seg[0])>>;
+            sink.nr = (uint32_t)nr;
+            for (int r = 0; r < nr; ++r) {
+                const ArenaLayout& PL = c->peer_lay[r];
+                const uint64_t o = kind == L_SCAN ? PL.off_scan : kind == L_CAND ? PL.off_cand : PL.off_inbox;
+                sink.seg[r] = at<T>(c->peer_base[r], o + (uint64_t)me * PL.seg_cap[kind] * item_size[kind]);
+                sink.cap[r] = PL.seg_cap[kind];
+            }
+            // 1 GPU: the only segment's counter is the list's own; N GPUs: counters in this rank's
+            // memory, published with the phase signal
+            sink.cnt = nr > 1 ? reinterpret_cast<unsigned long long*>(ctr + C_SEND + kind * MAX_RANKS) : &H->seg_n[kind][0];
+        };
+        auto fill_list = [&](auto& list, int kind) {
+            using T = std::remove_const_t<std::remove_pointer_t<std::remove_reference_t<decltype(list.base)>>>;
+            list.base = at<T>(A, off_list[kind]);
+            list.n = H->seg_n[kind];
+            list.seg_cap = L.seg_cap[kind];
+            list.nr = (uint32_t)nr;
+        };
+        // phase done: my counts of list `kind` to every rank, then wait for everybody's
+        auto exchange = [&](int flag, int kind) -> int {
+            if (nr == 1) return OVL_OK;
+            k_signal_counts<<<1, 32, 0, st>>>(c->d_peerhdr.as<ArenaHdr*>(), (uint32_t)nr, (uint32_t)me, flag, kind,
+                                              reinterpret_cast<const unsigned long long*>(ctr + C_SEND + kind * MAX_RANKS), c->step);
+            ++launches;
+            CK(cudaGetLastError());
+            return wait_flags(c, flag, st, &launches);
+        };
+
         // ---- K3: scan the local A entries -----------------------------------------------------------
         // (a rank without local reads still takes part in every exchange and resolves the probes of
         // the others against its partition of the table)
@@ -999,13 +1036,9 @@ int run_pass(ovl_ctx* c, uint32_t min_length, bool chunked) {
             P.bm_bits = bm_bits;
             P.T = T;
             P.fmt = fmt;
-            // 1 GPU: the filter pass appends straight to the probe list the resolve pass reads
-            P.surv.out = route_probes ? c->d_scan.as<Surv>() : d_probes;
-            P.surv.n_out = route_probes ? reinterpret_cast<unsigned long long*>(ctr + C_NSCAN) : &H->scan_n;
-            P.surv.cap = scan_cap;
-            P.sink.out = c->d_cand.as<uint64_t>();
-            P.sink.n_out = reinterpret_cast<unsigned long long*>(ctr + C_NCAND);
-            P.sink.cap = c->cand_cap;
+            fill_sink(P.surv, L_SCAN);
+            fill_list(P.probes, L_SCAN);
+            fill_sink(P.sink, L_CAND);
             P.mirror = mrule;
             if (!dense) {
                 if (R.n_tiles) {
@@ -1021,29 +1054,10 @@ int run_pass(ovl_ctx* c, uint32_t min_length, bool chunked) {
                         default: k3_filter<-1><<<grid(c->occ.filterx), 256, 0, st>>>(P); break;
                     }
                     ++launches;
-                }
-                if (route_probes) {
-                    ProbeRouteParams Q;
-                    Q.items = c->d_scan.as<Surv>();
-                    Q.n_ptr = reinterpret_cast<const unsigned long long*>(ctr + C_NSCAN);
-                    Q.cap = scan_cap;
-                    Q.lists.nr = (uint32_t)nr;
-                    Q.lists.me = (uint32_t)me;
-                    for (int r = 0; r < nr; ++r) {
-                        Q.lists.inbox[r] = at<Surv>(c->peer_base[r], c->peer_lay[r].off_scan);
-                        Q.lists.inbox_n[r] = &hdr_of(c, r)->scan_n;
-                        Q.lists.inbox_cap[r] = c->peer_lay[r].scan_cap;
-                    }
-                    k3_route<<<(uint32_t)(nsm * c->occ.route), 256, 0, st>>>(Q);
-                    ++launches;
                     CK(cudaGetLastError());
-                    OVL_TRY(signal_all(c, F_SCAN, st, &launches));
-                    OVL_TRY(wait_flags(c, F_SCAN, st, &launches));
-                    if (c->debug) CK(cudaEventRecord(c->ev_dbg[5], st));
-                    P.surv.out = d_probes;
-                    P.surv.n_out = &H->scan_n;
-                    P.surv.cap = L.scan_cap;
                 }
+                OVL_TRY(exchange(F_SCAN, L_SCAN));  // the survivors went straight into their owners' probe lists
+                if (c->debug) CK(cudaEventRecord(c->ev_dbg[5], st));
                 k3_resolve<<<(uint32_t)(nsm * c->occ.resolve), 256, 0, st>>>(P);
                 ++launches;
                 if (c->debug) CK(cudaEventRecord(c->ev_dbg[8], st));
@@ -1055,34 +1069,7 @@ int run_pass(ovl_ctx* c, uint32_t min_length, bool chunked) {
                 ++launches;
             }
             CK(cudaGetLastError());
-        }
-        // ---- N > 1: every candidate key to the rank that compares it ----------------------------------
-        const uint64_t* d_vkeys = c->d_cand.as<uint64_t>();
-        const unsigned long long* d_vn = reinterpret_cast<const unsigned long long*>(ctr + C_NCAND);
-        uint64_t vcap = c->cand_cap;
-        if (route && have_anchors) {
-            RouteParams Q;
-            Q.keys = c->d_cand.as<uint64_t>();
-            Q.n_ptr = reinterpret_cast<const unsigned long long*>(ctr + C_NCAND);
-            Q.cap = c->cand_cap;
-            Q.fmt = fmt;
-            Q.map = mrule.map;
-            for (int r = 0; r < nr; ++r) {
-                Q.lists.inbox[r] = at<uint64_t>(c->peer_base[r], c->peer_lay[r].off_cand);
-                Q.lists.inbox_n[r] = &hdr_of(c, r)->cand_n;
-                Q.lists.inbox_cap[r] = c->peer_lay[r].cand_cap;
-            }
-            Q.lists.nr = (uint32_t)nr;
-            Q.lists.me = (uint32_t)me;
-            Q.n_sent = nullptr;
-            k6_route_cand<<<kblocks, 256, 0, st>>>(Q);
-            ++launches;
-            CK(cudaGetLastError());
-            OVL_TRY(signal_all(c, F_CAND, st, &launches));
-            OVL_TRY(wait_flags(c, F_CAND, st, &launches));
-            d_vkeys = at<uint64_t>(A, L.off_cand);
-            d_vn = &H->cand_n;
-            vcap = L.cand_cap;
+            OVL_TRY(exchange(F_CAND, L_CAND));  // the candidate keys went straight into their verifiers' lists
         }
         CK(cudaEventRecord(c->ev[E_VERIFY0], st));
 
@@ -1103,20 +1090,14 @@ int run_pass(ovl_ctx* c, uint32_t min_length, bool chunked) {
                 }
             CK(cudaGetLastError());
         }
-        CandSink hits;
-        hits.out = route ? c->d_stage.as<uint64_t>() : d_inbox;
-        hits.n_out = route ? reinterpret_cast<unsigned long long*>(ctr + C_NSTAGE) : &H->inbox_n;
-        hits.cap = hit_cap;
         if (have_anchors) {
             if (c->collect || c->opt_serial_verify) {
                 VerifyParams V;
-                V.keys = d_vkeys;
-                V.n_ptr = d_vn;
-                V.cap = vcap;
+                fill_list(V.keys, L_CAND);
                 V.packed = d_packed;
                 V.ent = c->d_ent.as<uint2>();
                 V.fmt = fmt;
-                V.hits = hits;
+                fill_sink(V.hits, L_HITS);
                 V.counters = reinterpret_cast<unsigned long long*>(ctr + C_SUMM);
                 V.collect = c->collect;
                 V.mirror = mrule;
@@ -1124,15 +1105,13 @@ int run_pass(ovl_ctx* c, uint32_t min_length, bool chunked) {
                 ++launches;
             } else {
                 Verify2Params V;
-                V.keys = d_vkeys;
-                V.n_ptr = d_vn;
-                V.cap = vcap;
+                fill_list(V.keys, L_CAND);
                 V.packed64 = reinterpret_cast<const uint64_t*>(d_packed);
                 V.ent = c->d_ent.as<uint2>();
                 V.fmt = fmt;
                 V.surv = c->d_cnt.as<uint32_t>();
                 V.n_surv = reinterpret_cast<unsigned long long*>(ctr + C_NSURV);
-                V.hits = hits;
+                fill_sink(V.hits, L_HITS);
                 V.mirror = mrule;
                 V.tile_ctr = reinterpret_cast<unsigned long long*>(ctr + C_TILE_A);
                 k4a_head<<<kblocks, 256, 0, st>>>(V);
@@ -1142,30 +1121,10 @@ int run_pass(ovl_ctx* c, uint32_t min_length, bool chunked) {
             CK(cudaGetLastError());
         }
         CK(cudaEventRecord(c->ev[E_SORT0], st));
-
-        // ---- K6 (N > 1, mirror mode): every hit key to the rank that owns its A entry ---------------
-        if (route) {
-            RouteParams Q;
-            Q.keys = c->d_stage.as<uint64_t>();
-            Q.n_ptr = reinterpret_cast<const unsigned long long*>(ctr + C_NSTAGE);
-            Q.cap = hit_cap;
-            Q.fmt = fmt;
-            Q.map = mrule.map;
-            for (int r = 0; r < nr; ++r) {
-                Q.lists.inbox[r] = at<uint64_t>(c->peer_base[r], c->peer_lay[r].off_inbox);
-                Q.lists.inbox_n[r] = &hdr_of(c, r)->inbox_n;
-                Q.lists.inbox_cap[r] = c->peer_lay[r].inbox_cap;
-            }
-            Q.lists.nr = (uint32_t)nr;
-            Q.lists.me = (uint32_t)me;
-            Q.n_sent = reinterpret_cast<unsigned long long*>(ctr + C_NSENT);
-            k6_route<<<kblocks, 256, 0, st>>>(Q);
-            ++launches;
-            CK(cudaGetLastError());
-            OVL_TRY(signal_all(c, F_HITS, st, &launches));
-            OVL_TRY(wait_flags(c, F_HITS, st, &launches));
-            if (c->debug) CK(cudaEventRecord(c->ev_dbg[10], st));
-        }
+        // the hit keys (a matching candidate's own and its twins') went straight into the hit list of
+        // the rank that owns their A entry
+        if (have_anchors) OVL_TRY(exchange(F_HITS, L_HITS));
+        if (c->debug && nr > 1) CK(cudaEventRecord(c->ev_dbg[10], st));
 
         // ---- K7: order the hit keys by (a, b, p, flags) and emit rows: k7_bucket.cuh ------------------
         uint64_t* b_off = c->d_bkt.as<uint64_t>();
@@ -1174,9 +1133,7 @@ int run_pass(ovl_ctx* c, uint32_t min_length, bool chunked) {
         uint32_t* b_cur = b_cnt + M1;
         uint32_t* b_rowcnt = b_cur + M1;
         BucketParams B;
-        B.hits = d_inbox;
-        B.n_ptr = &H->inbox_n;
-        B.cap = L.inbox_cap;
+        fill_list(B.hits, L_HITS);
         B.fmt = fmt;
         B.M = M;
         B.cnt = b_cnt;
@@ -1189,7 +1146,7 @@ int run_pass(ovl_ctx* c, uint32_t min_length, bool chunked) {
         B.big_list = c->d_big.as<uint32_t>();
         B.ent = c->d_ent.as<uint2>();
         B.rows = d_rows;
-        B.rows_cap = hit_cap < L.rows_cap ? hit_cap : L.rows_cap;  // this rank's share
+        B.rows_cap = hits_room < L.rows_cap ? hits_room : L.rows_cap;  // this rank's share
         uint32_t wblocks = (M + 7) / 8;
         if (wblocks > (uint32_t)nsm * 16) wblocks = (uint32_t)nsm * 16;
         CK(cudaMemsetAsync(b_cnt, 0, M1 * 12, st));  // cnt, cur, rowcnt
@@ -1225,22 +1182,15 @@ int run_pass(ovl_ctx* c, uint32_t min_length, bool chunked) {
         {
             StatusParams SP;
             SP.st = H->status[me];
-            SP.ctr = reinterpret_cast<const unsigned long long*>(ctr);
-            SP.c_err = C_ERR;
-            SP.c_ncand = C_NCAND;
-            SP.c_nscan = C_NSCAN;
-            SP.c_nstage = C_NSTAGE;
-            SP.c_flags = C_FLAGS;
-            SP.n_probes = &H->scan_n;
-            SP.n_candin = &H->cand_n;
-            SP.cap_candin = route ? L.cand_cap : ~0ull;
-            SP.n_hits = &H->inbox_n;
-            SP.n_rows = d_nrows;
+            SP.err = reinterpret_cast<const unsigned long long*>(ctr + C_ERR);
+            SP.flags = reinterpret_cast<const unsigned long long*>(ctr + C_FLAGS);
             SP.abort_word = &H->abort;
-            SP.cap_cand = c->cand_cap;
-            SP.cap_scan = dense ? ~0ull : scan_cap;
-            SP.cap_stage = hit_cap;
-            SP.cap_hits = L.inbox_cap;
+            SP.seg_n = &H->seg_n[0][0];
+            for (int kk = 0; kk < L_COUNT; ++kk) SP.seg_cap[kk] = L.seg_cap[kk];
+            SP.nr = (uint32_t)nr;
+            SP.n_surv = reinterpret_cast<const unsigned long long*>(ctr + C_NSURV);
+            SP.cap_surv = cand_room;
+            SP.n_rows = d_nrows;
             SP.cap_rows = B.rows_cap;
             k9_status<<<1, 32, 0, st>>>(SP);
             ++launches;
@@ -1251,11 +1201,11 @@ int run_pass(ovl_ctx* c, uint32_t min_length, bool chunked) {
             OVL_TRY(wait_flags(c, F_STATUS, st, &launches));
         }
         CK(cudaGetLastError());
-        uint64_t* h_status = c->h_ctr + C_COUNT;
-        uint64_t* h_rowcnt = h_status + MAX_RANKS * STATUS_WORDS;
+        uint64_t* h_status = c->h_ctr + H_STATUS;
+        uint64_t* h_segn = c->h_ctr + H_SEGN;
         CK(cudaMemcpyAsync(c->h_ctr, ctr, C_COUNT * sizeof(uint64_t), cudaMemcpyDeviceToHost, st));
         CK(cudaMemcpyAsync(h_status, H->status, sizeof H->status, cudaMemcpyDeviceToHost, st));
-        CK(cudaMemcpyAsync(h_rowcnt + MAX_RANKS, &H->inbox_n, 24, cudaMemcpyDeviceToHost, st));  // inbox_n, scan_n, cand_n
+        CK(cudaMemcpyAsync(h_segn, H->seg_n, sizeof H->seg_n, cudaMemcpyDeviceToHost, st));
         CK(cudaStreamSynchronize(st));  // the one synchronisation of a pass
         CK(cudaStreamSynchronize(sk));
         if (chunked) {
@@ -1296,38 +1246,44 @@ int run_pass(ovl_ctx* c, uint32_t min_length, bool chunked) {
             // pass; the ranks that overflowed grow first (the arenas are re-published either way)
             if (attempt >= 3) return fail(c, OVL_E_LIMIT, "candidate buffers keep overflowing");
             ++S.retries;
-            const uint64_t* s = h_status + (size_t)me * STATUS_WORDS;
-            const double per = mirror ? 3.0 : 1.0;
-            double need = (double)c->cand_cap;
-            if (s[ST_NCAND] > c->cand_cap) need = std::max(need, 1.07 * (double)s[ST_NCAND]);
-            if (!dense && s[ST_NSCAN] > scan_cap) need = std::max(need, 0.54 * (double)s[ST_NSCAN]);
-            if (s[ST_NSTAGE] > hit_cap) need = std::max(need, 1.07 * (double)s[ST_NSTAGE] / per);
-            if (s[ST_NHITS] > L.inbox_cap) need = std::max(need, 1.07 * (double)s[ST_NHITS] / per);
-            if (s[ST_NROWS] > B.rows_cap) need = std::max(need, 1.07 * (double)s[ST_NROWS] / per);
-            if (need > (double)c->cand_cap) {
-                c->cand_cap = (uint64_t)need + 1024;
+            // this rank's fullest buffer, in 1/1024 of its capacity: every capacity scales with cand_cap
+            const uint64_t fill = h_status[(size_t)me * STATUS_WORDS + ST_FILL];
+            if (fill > 1024) {
+                c->cand_cap = (uint64_t)(1.07 * (double)c->cand_cap * (double)fill / 1024.0) + 1024;
                 c->min_cand_cap = std::max(c->min_cand_cap, c->cand_cap);
             }
             ++c->arena_epoch;
             continue;
         }
-        if (flags_any & STF_GATHER) return fail(c, OVL_E_LIMIT, "row gather overflow: internal error");
-        S.candidates = c->h_ctr[C_NCAND];
-        S.verified = route ? h_rowcnt[MAX_RANKS + 2] : c->h_ctr[C_NCAND];  // N > 1: the candidates routed to this rank
-        S.hits = h_rowcnt[MAX_RANKS];  // keys in this rank's hit list
-        S.hits_sent = c->h_ctr[C_NSENT];
-        S.hits_received = route ? (S.hits + S.hits_sent > c->h_ctr[C_NSTAGE] ? S.hits + S.hits_sent - c->h_ctr[C_NSTAGE] : 0) : 0;
+        // items this rank produced (sent) and holds (received), per list
+        auto sent = [&](int kind, bool remote_only) {
+            uint64_t t = 0;
+            if (nr == 1) return remote_only ? 0ull : (unsigned long long)h_segn[kind * MAX_RANKS];
+            for (int d = 0; d < nr; ++d)
+                if (!remote_only || d != me) t += c->h_ctr[C_SEND + kind * MAX_RANKS + d];
+            return (unsigned long long)t;
+        };
+        auto held = [&](int kind, bool remote_only) {
+            uint64_t t = 0;
+            for (int r = 0; r < nr; ++r)
+                if (!remote_only || r != me) t += h_segn[kind * MAX_RANKS + r];
+            return (unsigned long long)t;
+        };
+        S.scan_survivors = sent(L_SCAN, false);
+        S.candidates = sent(L_CAND, false);   // found by this rank
+        S.verified = held(L_CAND, false);     // compared by this rank
+        S.hits = held(L_HITS, false);         // keys in this rank's hit list
+        S.hits_sent = sent(L_HITS, true);
+        S.hits_received = held(L_HITS, true);
         S.compared_bases = c->h_ctr[C_SUMM];
         S.operand_bytes = c->h_ctr[C_SUMB];
         S.big_buckets = (uint32_t)c->h_ctr[C_BIG];
-        S.scan_survivors = h_status[(size_t)me * STATUS_WORDS + ST_NSCAN];
         uint64_t total = 0;
         for (int r = 0; r < nr; ++r) {
-            h_rowcnt[r] = h_status[(size_t)r * STATUS_WORDS + ST_NROWS];
-            c->rowcnt_all[r] = h_rowcnt[r];
-            total += h_rowcnt[r];
+            c->rowcnt_all[r] = h_status[(size_t)r * STATUS_WORDS + ST_NROWS];
+            total += c->rowcnt_all[r];
         }
-        S.rows_local = h_rowcnt[me];
+        S.rows_local = c->rowcnt_all[me];
         // N > 1: rank 0 reports the job's row count; the rows of the other ranks are still in their
         // HBM (gather_rows_pull brings them over when somebody asks for them)
         c->n_rows = nr > 1 ? (me == 0 ? total : 0) : total;
@@ -1416,6 +1372,10 @@ int ovl_create(int device, ovl_ctx** out) {
     ovl_ctx* c = nullptr;
     if (!out) return fail(c, OVL_E_ARG, "ovl_create: out is NULL");
     *out = nullptr;
+    // A pass keeps 9 streams busy (main, K2, signals, 4 push streams, H2D); with the default of 8
+    // hardware queues two of them may share one and serialise.  Only effective when this is the
+    // first CUDA call of the process; callers that initialise CUDA earlier set it themselves.
+    setenv("CUDA_DEVICE_MAX_CONNECTIONS", "32", 0);
     int n = 0;
     cudaError_t e = cudaGetDeviceCount(&n);
     if (e != cudaSuccess || n <= 0) {
@@ -1447,7 +1407,9 @@ int ovl_create(int device, ovl_ctx** out) {
         int lo_pri = 0, hi_pri = 0;
         CK(cudaDeviceGetStreamPriorityRange(&lo_pri, &hi_pri));
         CK(cudaStreamCreateWithFlags(&x->st, cudaStreamNonBlocking));
-        CK(cudaStreamCreateWithFlags(&x->st_k2, cudaStreamNonBlocking));
+        // K2 is latency bound and small; at high priority its blocks take the SM slots K1's retiring
+        // blocks free, so it really runs UNDER K1 (at equal priority it ran behind it: r02f time line)
+        CK(cudaStreamCreateWithPriority(&x->st_k2, cudaStreamNonBlocking, hi_pri));
         for (int i = 0; i < PUSH_STREAMS; ++i) {
             CK(cudaStreamCreateWithPriority(&x->st_pushv[i], cudaStreamNonBlocking, hi_pri));
             CK(cudaEventCreateWithFlags(&x->ev_piece[i], cudaEventDisableTiming));
@@ -1463,7 +1425,7 @@ int ovl_create(int device, ovl_ctx** out) {
         CK(cudaEventCreate(&x->ev_t1));
         for (int i = 0; i < 12; ++i) CK(cudaEventCreate(&x->ev_dbg[i]));
         x->debug = getenv("OVL_DEBUG") ? atoi(getenv("OVL_DEBUG")) : 0;
-        const size_t hwords = C_COUNT + MAX_RANKS * STATUS_WORDS + MAX_RANKS + 4;
+        const size_t hwords = H_WORDS;
         CK(cudaHostAlloc(reinterpret_cast<void**>(&x->h_ctr), hwords * sizeof(uint64_t), cudaHostAllocDefault));
         memset(x->h_ctr, 0, hwords * sizeof(uint64_t));
         OVL_TRY(dev_ensure(c, x->d_ctr, C_COUNT * sizeof(uint64_t), false));
@@ -1481,7 +1443,6 @@ int ovl_create(int device, ovl_ctx** out) {
         OVL_TRY(resident(ovl::k3_filter<3>, x->occ.filter3));
         OVL_TRY(resident(ovl::k3_filter<-1>, x->occ.filterx));
         OVL_TRY(resident(ovl::k3_resolve, x->occ.resolve));
-        OVL_TRY(resident(ovl::k3_route, x->occ.route));
         OVL_TRY(resident(ovl::k4a_head, x->occ.head));
         OVL_TRY(resident(ovl::k4b_tail, x->occ.tail));
         OVL_TRY(resident(ovl::k1_pack, x->occ.pack));
@@ -1500,7 +1461,7 @@ void ovl_destroy(ovl_ctx* c) {
     close_peers(c);
     if (c->comm) nccl_dyn::api().CommDestroy(c->comm);
     DevBuf* bufs[] = {&c->d_ascii, &c->d_src, &c->d_len, &c->d_flags, &c->d_gran0, &c->d_ent, &c->d_tile0,
-                      &c->d_tile_ent, &c->d_stile0, &c->d_scan_tiles, &c->d_ctr, &c->d_tmp, &c->d_cand, &c->d_stage, &c->d_scan,
+                      &c->d_tile_ent, &c->d_stile0, &c->d_scan_tiles, &c->d_ctr, &c->d_tmp, &c->d_cand,
                       &c->d_cnt, &c->d_bkt, &c->d_big, &c->d_peerhdr, &c->d_fmark, &c->d_fkeep, &c->d_foff, &c->d_frows,
                       &c->arena};
     for (DevBuf* b : bufs)

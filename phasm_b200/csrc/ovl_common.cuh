@@ -233,40 +233,127 @@ __device__ __forceinline__ uint32_t table_find(const TableView& T, uint64_t h, u
     return NIL;
 }
 
-// Per-warp staging buffer in shared memory: items are appended warp-synchronously and flushed to
-// a global array with ONE global atomic per flush (instead of one per probe round), in coalesced
-// stores.  T is uint64_t (candidate / hit keys) or ulonglong2 (scan survivors).
+// ---- item lists between the stages (and, on N > 1 GPUs, between the ranks) ----------------------
+// Three kinds of items flow through a pass: scan survivors (to the rank that owns their k-mer),
+// candidate keys (to the rank that compares them), hit keys (to the rank that owns their A entry).
+// The list of a rank has one SEGMENT per source rank: source s appends to its own segment of
+// every destination's list, reserving room with atomics on counters in ITS OWN memory, and
+// publishes the counts with its "phase done" signal (k6_exchange.cuh).  No remote atomic, no
+// separate routing pass: the producing kernel stores straight into peer memory over NVLink while
+// it computes.  N = 1: one segment, one counter.
+//
+// Producer side.  Items are staged per warp in shared memory (WBUF items, appended
+// warp-synchronously) and flushed with one atomic per (flush, destination), in runs of
+// consecutive slots per destination.
 constexpr int WBUF = 256;  // items per warp
 
 template <class T>
 struct Sink {
-    T* out;
-    unsigned long long* n_out;  // total items found (may exceed cap)
-    uint64_t cap;
+    T* seg[MAX_RANKS];          // my segment in the list of every rank (peer-mapped for r != me)
+    uint64_t cap[MAX_RANKS];    // its capacity
+    unsigned long long* cnt;    // [nr] items appended per destination (may exceed cap: overflow is detected by the receiver)
+    uint32_t nr;
 };
 typedef Sink<uint64_t> CandSink;
 
-template <class T>
-__device__ __forceinline__ void wbuf_flush(T* buf, uint32_t& n, const Sink<T>& S, uint32_t lane) {
-    unsigned long long base = 0;
-    if (lane == 0) base = atomicAdd(S.n_out, (unsigned long long)n);
-    base = __shfl_sync(FULL, base, 0);
-    for (uint32_t i = lane; i < n; i += 32)
-        if (base + i < S.cap) S.out[base + i] = buf[i];
+// per-warp scratch of a routed flush
+struct RouteScratch {
+    unsigned long long base[MAX_RANKS];
+    uint32_t cnt[MAX_RANKS];
+    uint8_t dest[WBUF];
+};
+
+template <class T, class DestFn>
+__device__ __forceinline__ void wbuf_flush(T* buf, uint32_t& n, const Sink<T>& S, uint32_t lane, RouteScratch* rs,
+                                           DestFn dest_of) {
+    if (S.nr <= 1) {
+        unsigned long long base = 0;
+        if (lane == 0) base = atomicAdd(S.cnt, (unsigned long long)n);
+        base = __shfl_sync(FULL, base, 0);
+        for (uint32_t i = lane; i < n; i += 32)
+            if (base + i < S.cap[0]) S.seg[0][base + i] = buf[i];
+    } else {
+        // pass 1: destination of every item, items per destination
+        if (lane < MAX_RANKS) rs->cnt[lane] = 0;
+        __syncwarp();
+        for (uint32_t i0 = 0; i0 < n; i0 += 32) {
+            const uint32_t i = i0 + lane;
+            uint32_t d = 0xffu;
+            if (i < n) {
+                d = dest_of(buf[i]);
+                rs->dest[i] = (uint8_t)d;
+            }
+            const unsigned grp = __match_any_sync(FULL, d);
+            if (d != 0xffu && lane == (uint32_t)(__ffs(grp) - 1)) rs->cnt[d] += __popc(grp);
+            __syncwarp();
+        }
+        // one reservation per destination, on this rank's own counters
+        if (lane < S.nr) {
+            const uint32_t c = rs->cnt[lane];
+            rs->base[lane] = c ? atomicAdd(S.cnt + lane, (unsigned long long)c) : 0ull;
+            rs->cnt[lane] = 0;
+        }
+        __syncwarp();
+        // pass 2: every item to its slot; the items of one destination fill consecutive slots
+        for (uint32_t i0 = 0; i0 < n; i0 += 32) {
+            const uint32_t i = i0 + lane;
+            const uint32_t d = i < n ? rs->dest[i] : 0xffu;
+            const unsigned grp = __match_any_sync(FULL, d);
+            uint32_t off = 0;
+            if (d != 0xffu) off = rs->cnt[d];
+            __syncwarp();
+            if (d != 0xffu) {
+                if (lane == (uint32_t)(__ffs(grp) - 1)) rs->cnt[d] = off + __popc(grp);
+                const unsigned long long pos = rs->base[d] + off + __popc(grp & ((1u << lane) - 1u));
+                if (pos < S.cap[d]) S.seg[d][pos] = buf[i];
+            }
+            __syncwarp();
+        }
+    }
     n = 0;
     __syncwarp();
 }
 
 // Append `item` from every lane with have != 0.  All 32 lanes must call.
-template <class T>
-__device__ __forceinline__ void wbuf_push(T* buf, uint32_t& n, const Sink<T>& S, uint32_t lane, bool have,
-                                          const T& item) {
+template <class T, class DestFn>
+__device__ __forceinline__ void wbuf_push(T* buf, uint32_t& n, const Sink<T>& S, uint32_t lane, bool have, const T& item,
+                                          RouteScratch* rs, DestFn dest_of) {
     const unsigned m = __ballot_sync(FULL, have);
     if (!m) return;
-    if (n + 32 > WBUF) wbuf_flush(buf, n, S, lane);
+    if (n + 32 > WBUF) wbuf_flush(buf, n, S, lane, rs, dest_of);
     if (have) buf[n + __popc(m & ((1u << lane) - 1u))] = item;
     n += __popc(m);
     __syncwarp();
+}
+
+// Consumer side: the list as the concatenation of its segments.
+template <class T>
+struct SegList {
+    const T* base;                 // nr segments of seg_cap items each
+    const unsigned long long* n;   // [nr] items in every segment (counters; may exceed seg_cap on overflow)
+    uint64_t seg_cap;
+    uint32_t nr;
+};
+// pre[s] = logical index of the first item of segment s, pre[nr] = total (block-shared table)
+template <class T>
+__device__ __forceinline__ void seg_prefix(const SegList<T>& L, unsigned long long* s_pre) {
+    if (threadIdx.x == 0) {
+        unsigned long long acc = 0;
+        for (uint32_t s = 0; s < L.nr; ++s) {
+            s_pre[s] = acc;
+            const unsigned long long c = L.n[s];
+            acc += c < L.seg_cap ? c : L.seg_cap;
+        }
+        s_pre[L.nr] = acc;
+    }
+    __syncthreads();
+}
+// physical index (into base) of logical item i < pre[nr]
+template <class T>
+__device__ __forceinline__ uint64_t seg_phys(const SegList<T>& L, const unsigned long long* s_pre, uint64_t i) {
+    uint32_t s = 0;
+    while (s + 1 < L.nr && i >= s_pre[s + 1]) ++s;
+    return (uint64_t)s * L.seg_cap + (i - s_pre[s]);
 }
 
 }  // namespace ovl

@@ -13,6 +13,8 @@ from __future__ import annotations
 import os
 import sys
 
+os.environ.setdefault("CUDA_DEVICE_MAX_CONNECTIONS", "32")   # 9 busy streams per pass (ovl_create)
+
 from .multi import TcpRendezvous
 from .overlapper import ExactOverlapper
 

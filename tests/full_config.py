@@ -19,6 +19,7 @@ TEST code: may import oracle/.
 import argparse
 import json
 import os
+os.environ.setdefault("CUDA_DEVICE_MAX_CONNECTIONS", "32")
 import sys
 import time
 

@@ -9,6 +9,7 @@ Every rank stages only its read range; rank 0 compares the gathered rows with th
 """
 import argparse
 import os
+os.environ.setdefault("CUDA_DEVICE_MAX_CONNECTIONS", "32")
 import sys
 
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
