@@ -219,6 +219,39 @@ typedef struct {
 int ovl_filter_rows(ovl_ctx *ctx, const ovl_filter_opts *opts, const ovl_row **rows, uint64_t *n_rows,
                     ovl_filter_stats *stats);
 
+/* ---- assembly-graph edge list on the device (graph part; OPTIONAL) ------
+ * ovl_build_graph replaces build_assembly_graph (phasm/assembly_graph.py:136-179) as the reference's
+ * `layout` stage feeds it (phasm/cli/assembler.py:93-100): the rows of the last ovl_overlaps* call
+ * (use_filtered == 0) or the rows kept by the last ovl_filter_rows call (use_filtered != 0), taken in
+ * order as LocalAlignments with brange = (0, bend).  Every row LocalAlignment.classify
+ * (phasm/alignments.py:248-258) calls OVERLAP_AB adds the two directed edges
+ *     a -> b        weight = astart,                           overlap_len = max(aend - astart, bend)
+ *     b^1 -> a^1    weight = (|b| - bend) - (|a| - aend),      same overlap_len
+ * (x^1 = OrientedRead.reverse() = the other strand's entry; needs a strand-paired entry table,
+ * else OVL_E_ARG); contained rows add nothing; OVERLAP_BA cannot occur with bstart == 0 but is
+ * implemented.  networkx.DiGraph semantics: the LAST row of an ordered node pair decides the
+ * attributes, the FIRST its place in the adjacency order, a node exists iff it ends an edge.
+ * The edges come back sorted by (u, v) (a CSR adjacency) in a pinned buffer owned by the ctx, valid
+ * until the next ovl_build_graph / ovl_overlaps* call.  Nodes are entry indices. */
+typedef struct {
+    uint32_t u, v;
+    int32_t edge_len;       /* the reference's edge attribute `weight` (edge_len)              */
+    uint32_t overlap_len;
+    uint64_t first_seq;     /* 2 * (row that first added the edge) + (0 | 1: which of its two add_edge calls) */
+} ovl_edge;
+
+typedef struct {
+    uint64_t rows_in;
+    uint64_t rows_overlap;  /* rows of an OVERLAP type (two add_edge calls each)               */
+    uint64_t n_edges;       /* networkx.number_of_edges(g)                                     */
+    uint64_t n_nodes;       /* networkx.number_of_nodes(g)                                     */
+    float ms_device;
+    uint32_t reserved0;
+} ovl_graph_stats;
+
+int ovl_build_graph(ovl_ctx *ctx, int use_filtered, const ovl_edge **edges, uint64_t *n_edges,
+                    ovl_graph_stats *stats);
+
 /* ---- GFA2 ingest for the consumer of the overlaps (parsing part; host only,
  * needs no GPU and no ctx) ----------------------------------------------------------------
  * ovl_gfa_read replaces the two Python passes of the reference's `layout` stage over the GFA2 file

@@ -60,6 +60,19 @@ class OvlFilterStats(Structure):
         return {n: getattr(self, n) for n, _ in self._fields_ if n != "reserved0"}
 
 
+class OvlEdge(Structure):
+    _fields_ = [("u", c_uint32), ("v", c_uint32), ("edge_len", ctypes.c_int32), ("overlap_len", c_uint32),
+                ("first_seq", c_uint64)]
+
+
+class OvlGraphStats(Structure):
+    _fields_ = [("rows_in", c_uint64), ("rows_overlap", c_uint64), ("n_edges", c_uint64),
+                ("n_nodes", c_uint64), ("ms_device", c_float), ("reserved0", c_uint32)]
+
+    def as_dict(self):
+        return {n: getattr(self, n) for n, _ in self._fields_ if n != "reserved0"}
+
+
 # every symbol include/phasm_ovl.h declares: name -> (restype, argtypes)
 _P = c_void_p
 SIGNATURES = {
@@ -90,6 +103,7 @@ SIGNATURES = {
     "ovl_write_gfa": (c_int, [_P, c_int, c_int, POINTER(c_uint64)]),
     "ovl_filter_rows": (c_int, [_P, POINTER(OvlFilterOpts), POINTER(c_void_p), POINTER(c_uint64),
                                 POINTER(OvlFilterStats)]),
+    "ovl_build_graph": (c_int, [_P, c_int, POINTER(c_void_p), POINTER(c_uint64), POINTER(OvlGraphStats)]),
     "ovl_gfa_read": (c_int, [c_char_p, POINTER(_P)]),
     "ovl_gfa_free": (None, [_P]),
     "ovl_gfa_counts": (c_int, [_P, POINTER(c_uint32), POINTER(c_uint64)]),

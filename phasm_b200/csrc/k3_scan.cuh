@@ -119,7 +119,7 @@ __global__ void __launch_bounds__(256, 4) k3_filter_wide(const ScanParams P) {
     const uint64_t kmask = kmer_mask(P.k);
     const uint32_t nr = P.T.nr;
     auto surv_dest = [nr](const Surv& r) { return owner_of_hash(r.x, nr); };
-    const uint32_t kk = (uint32_t)P.k, ll = P.l;
+    const uint32_t ll = P.l;
     const int bmb = P.bm_bits;
     Surv* buf = s_buf[threadIdx.x >> 5];
     uint32_t nbuf = 0;
@@ -139,9 +139,12 @@ __global__ void __launch_bounds__(256, 4) k3_filter_wide(const ScanParams P) {
         const uint32_t u = rec.w + lane;  // granule of this lane inside the entry
         a = rec.y;
         q = u * GRAN_BASES;
-        // probes q + 32 j that can start a row: at least q + k <= |a| (the exact test is in k3_resolve)
+        // probes q + 32 j that can start a row: p = q - delta, delta < stride, needs |a| - p >= l, i.e.
+        // q <= |a| - l + stride - 1 (stride <= l - k + 1, so the k-mer lies inside the read; the exact
+        // test per candidate is in k3_resolve)
         nv = 0;
-        if (u < ((L + 63u) >> 6) && L >= ll && q + kk <= L) nv = ((L - kk - q) >> SL) + 1u;
+        const uint32_t qmax = L - ll + ((1u << SL) - 1u);  // only used when L >= ll
+        if (u < ((L + 63u) >> 6) && L >= ll && q <= qmax) nv = ((qmax - q) >> SL) + 1u;
         h[0] = mix64(((uint64_t)v.x | ((uint64_t)v.y << 32)) & kmask);
         if (NP == 2) h[NP - 1] = mix64(((uint64_t)v.z | ((uint64_t)v.w << 32)) & kmask);
 #pragma unroll
@@ -192,6 +195,180 @@ __global__ void __launch_bounds__(256, 4) k3_filter_wide(const ScanParams P) {
         rec1 = rec2;
         v1 = v2;
         rec2 = rec3;
+    }
+    if (nbuf) wbuf_flush(buf, nbuf, P.surv, lane, rs, surv_dest);
+}
+
+// ---- the same pass with bulk-async tile staging (stride 64 / 32; the default) -------------------
+// A warp owns a CONTIGUOUS range of tiles (so its granule stream and its tile records are contiguous
+// in HBM) and keeps a ring of BULK_STAGES tiles of 512 B in shared memory: one lane issues a
+// `cp.async.bulk` global -> shared copy per tile (SASS UBLKCP) whose completion is counted on the
+// stage's mbarrier (expect_tx), BULK_STAGES tiles ahead of the tile being hashed; the lanes read their
+// granule with one LDS.128.  The granule loads cost no registers and no per-lane address arithmetic,
+// and 3 KB per warp are in flight whatever the compiler does with the loop (ncu r02f, register
+// pipeline: 5.3 long-scoreboard stall cycles per issued instruction, 55 % of the issue slots used).
+// The tile records come 32 at a time, one coalesced load per lane; the bitmap words of tile i are
+// requested while tile i-1's are tested, as in k3_filter_wide.
+constexpr int BULK_STAGES = 6;
+
+__device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
+__device__ __forceinline__ void mbar_init(uint32_t bar, uint32_t count) {
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(bar), "r"(count) : "memory");
+}
+__device__ __forceinline__ void mbar_expect_tx(uint32_t bar, uint32_t bytes) {
+    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void bulk_g2s(uint32_t dst, const void* src, uint32_t bytes, uint32_t bar) {
+    asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(dst),
+                 "l"(src), "r"(bytes), "r"(bar)
+                 : "memory");
+}
+__device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity) {
+    uint32_t done;
+    do {
+        asm volatile(
+            "{\n\t.reg .pred p;\n\t"
+            "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\t"
+            "selp.u32 %0, 1, 0, p;\n\t}"
+            : "=r"(done)
+            : "r"(bar), "r"(parity)
+            : "memory");
+    } while (!done);
+}
+
+template <int SL>
+__global__ void __launch_bounds__(256, 4) k3_filter_bulk(const ScanParams P) {
+    static_assert(SL == 5 || SL == 6, "one or two probes per granule");
+    constexpr int NP = SL == 6 ? 1 : 2;
+    constexpr int S = BULK_STAGES;
+    constexpr uint32_t SCAP = WBUF / 2;
+    __shared__ __align__(128) uint4 s_ring[8][S][32];
+    __shared__ __align__(8) unsigned long long s_bar[8][S];
+    __shared__ Surv s_buf[8][SCAP];
+    __shared__ RouteScratch s_rs[8];
+    const uint32_t wib = threadIdx.x >> 5;
+    RouteScratch* rs = &s_rs[wib];
+    const uint32_t lane = threadIdx.x & 31;
+    const uint32_t ltmask = (1u << lane) - 1u;
+    const uint32_t warp = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+    const uint32_t nwarps = (gridDim.x * blockDim.x) >> 5;
+    const uint32_t per = (P.n_tiles + nwarps - 1) / nwarps;
+    const uint32_t t_begin = min(P.n_tiles, warp * per), t_end = min(P.n_tiles, t_begin + per);
+    const uint32_t n = t_end - t_begin;  // tiles of this warp
+    const uint64_t kmask = kmer_mask(P.k);
+    const uint32_t nr = P.T.nr;
+    auto surv_dest = [nr](const Surv& r) { return owner_of_hash(r.x, nr); };
+    const uint32_t ll = P.l;
+    const int bmb = P.bm_bits;
+    Surv* buf = s_buf[wib];
+    uint32_t nbuf = 0;
+    const uint32_t ring0 = smem_u32(&s_ring[wib][0][0]), bar0 = smem_u32(&s_bar[wib][0]);
+
+    if (lane == 0) {
+#pragma unroll
+        for (int s = 0; s < S; ++s) mbar_init(bar0 + 8u * s, 1);
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    }
+    __syncwarp();
+
+    // tile records, 32 at a time: lane j holds the record of tile t_begin + 32 * blk + j
+    const uint4 zero4 = make_uint4(0, 0, 0, 0);
+    auto load_recs = [&](uint32_t blk) -> uint4 {
+        const uint32_t i = 32u * blk + lane;
+        return i < n ? __ldg(P.tiles + t_begin + i) : zero4;
+    };
+    uint4 rec_cur = load_recs(0), rec_nxt = load_recs(1);
+    uint32_t blk = 0;
+    // issue the copy of this warp's tile i (i < n) into its stage
+    auto issue = [&](uint32_t i) {
+        const bool in_cur = (i >> 5) == blk;  // else it belongs to the next block of records (S <= 32)
+        const uint32_t src_lane = i & 31u;
+        const uint32_t x = __shfl_sync(FULL, in_cur ? rec_cur.x : rec_nxt.x, src_lane);
+        const uint32_t z = __shfl_sync(FULL, in_cur ? rec_cur.z : rec_nxt.z, src_lane);
+        const uint32_t w = __shfl_sync(FULL, in_cur ? rec_cur.w : rec_nxt.w, src_lane);
+        if (lane == 0) {
+            const uint32_t ng = ((z + 63u) >> 6) - w;  // granules of the entry from this tile on (>= 1)
+            const uint32_t bytes = 16u * (ng < 32u ? ng : 32u);
+            const uint32_t st = i % S;
+            mbar_expect_tx(bar0 + 8u * st, bytes);
+            bulk_g2s(ring0 + 512u * st, P.packed + x, bytes, bar0 + 8u * st);
+        }
+    };
+    for (uint32_t i = 0; i < (uint32_t)S && i < n; ++i) issue(i);
+
+    uint64_t h_prev[NP];
+    uint32_t bw_prev[NP];
+    uint32_t a_prev = 0, q_prev = 0, nv_prev = 0;
+#pragma unroll
+    for (int j = 0; j < NP; ++j) {
+        h_prev[j] = 0;
+        bw_prev[j] = 0;
+    }
+    for (uint32_t i = 0; i <= n; ++i) {
+        uint64_t h[NP];
+        uint32_t bw[NP];
+        uint32_t a = 0, q = 0, nv = 0;
+#pragma unroll
+        for (int j = 0; j < NP; ++j) {
+            h[j] = 0;
+            bw[j] = 0;
+        }
+        if (i < n) {  // warp-uniform
+            if ((i >> 5) != blk) {  // entering the next block of records
+                ++blk;
+                rec_cur = rec_nxt;
+                rec_nxt = load_recs(blk + 1);
+            }
+            const uint32_t src_lane = i & 31u;
+            a = __shfl_sync(FULL, rec_cur.y, src_lane);
+            const uint32_t L = __shfl_sync(FULL, rec_cur.z, src_lane);
+            const uint32_t u = __shfl_sync(FULL, rec_cur.w, src_lane) + lane;  // granule of this lane inside the entry
+            const uint32_t st = i % S;
+            mbar_wait(bar0 + 8u * st, (i / S) & 1u);
+            uint4 v = zero4;
+            const bool inr = u < ((L + 63u) >> 6);
+            if (inr) v = s_ring[wib][st][lane];
+            q = u * GRAN_BASES;
+            // probes q + 32 j that can start a row: p = q - delta, delta < stride, needs |a| - p >= l, i.e.
+            // q <= |a| - l + stride - 1 (the exact test per candidate is in k3_resolve)
+            const uint32_t qmax = L - ll + ((1u << SL) - 1u);  // only used when L >= ll
+            if (inr && L >= ll && q <= qmax) nv = ((qmax - q) >> SL) + 1u;
+            h[0] = mix64(((uint64_t)v.x | ((uint64_t)v.y << 32)) & kmask);
+            if (NP == 2) h[NP - 1] = mix64(((uint64_t)v.z | ((uint64_t)v.w << 32)) & kmask);
+#pragma unroll
+            for (int j = 0; j < NP; ++j)  // lanes without a probe read word 0 (one broadcast line)
+                bw[j] = __ldg(P.filter + ((uint32_t)j < nv ? bitmap_word(h[j], nr, bmb) : 0u));
+            __syncwarp();  // every lane has its granule: the stage can be refilled
+            if (i + S < n) issue(i + S);
+        }
+        // the previous tile's survivors (its bitmap words were requested one iteration ago)
+        uint32_t m[NP], total = 0;
+#pragma unroll
+        for (int j = 0; j < NP; ++j) {
+            const bool pass = (uint32_t)j < nv_prev && ((bw_prev[j] >> ((uint32_t)h_prev[j] & 31u)) & 1u);
+            m[j] = __ballot_sync(FULL, pass);
+            total += __popc(m[j]);
+        }
+        if (total) {  // warp-uniform
+            if (nbuf + total > SCAP) wbuf_flush(buf, nbuf, P.surv, lane, rs, surv_dest);
+            uint32_t o = nbuf;
+#pragma unroll
+            for (int j = 0; j < NP; ++j) {
+                if ((m[j] >> lane) & 1u)
+                    buf[o + __popc(m[j] & ltmask)] = make_ulonglong2(h_prev[j], ((uint64_t)a_prev << 32) | (q_prev + 32u * j));
+                o += __popc(m[j]);
+            }
+            nbuf += total;
+            __syncwarp();
+        }
+#pragma unroll
+        for (int j = 0; j < NP; ++j) {
+            h_prev[j] = h[j];
+            bw_prev[j] = bw[j];
+        }
+        a_prev = a;
+        q_prev = q;
+        nv_prev = nv;
     }
     if (nbuf) wbuf_flush(buf, nbuf, P.surv, lane, rs, surv_dest);
 }
@@ -249,9 +426,10 @@ __global__ void __launch_bounds__(256) k3_filter(const ScanParams P) {
             if (lane == 31) w2 = inr ? packed64[2ull * (rec.x + lane + 1)] : 0;  // a spare granule follows the array
         }
         // probes q = pos0 + off that can start a row: |a| - p >= l for some p = q - delta,
-        // delta < stride, i.e. at least q + k <= |a| (the exact test is in k3_resolve)
+        // delta < stride, i.e. q <= |a| - l + stride - 1 (the exact test is in k3_resolve)
         uint32_t nv = 0;
-        if (inr && L >= P.l && pos0 + (uint32_t)P.k <= L) nv = ((L - (uint32_t)P.k - pos0) >> sl) + 1u;
+        const uint32_t qmax = L - P.l + ((1u << sl) - 1u);  // only used when L >= l
+        if (inr && L >= P.l && pos0 <= qmax) nv = ((qmax - pos0) >> sl) + 1u;
         if (nv > n_probe) nv = n_probe;
 
         // ---- 4 or more probes per lane: one ballot round per probe ----

@@ -107,9 +107,9 @@ __global__ void __launch_bounds__(256) k8_compact(const Row* __restrict__ rows, 
 }
 
 __global__ void __launch_bounds__(256) k8_count_marked(const uint32_t* __restrict__ firstmark, uint32_t M,
-                                                       unsigned long long* __restrict__ out) {
+                                                       unsigned long long* __restrict__ out, uint32_t unmarked) {
     unsigned long long c = 0;
-    for (uint32_t e = blockIdx.x * blockDim.x + threadIdx.x; e < M; e += gridDim.x * blockDim.x) c += firstmark[e] != 0xffffffffu;
+    for (uint32_t e = blockIdx.x * blockDim.x + threadIdx.x; e < M; e += gridDim.x * blockDim.x) c += firstmark[e] != unmarked;
 #pragma unroll
     for (int d = 16; d > 0; d >>= 1) c += __shfl_xor_sync(FULL, c, d);
     if ((threadIdx.x & 31) == 0 && c) atomicAdd(out, c);

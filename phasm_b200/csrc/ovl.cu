@@ -43,6 +43,7 @@
 #include "k6_exchange.cuh"
 #include "k7_bucket.cuh"
 #include "k8_filter.cuh"
+#include "k10_graph.cuh"
 #include "nccl_dyn.h"
 
 static_assert(sizeof(ovl_row) == sizeof(ovl::Row), "row layouts must agree");
@@ -124,7 +125,7 @@ struct ovl_ctx {
     std::string err;
     // resident blocks per SM of the persistent (grid-stride) kernels, from the occupancy calculator
     struct {
-        int filter6 = 1, filter5 = 1, filter4 = 1, filter3 = 1, filterx = 1, resolve = 1, head = 1, tail = 1, pack = 1;
+        int bulk6 = 1, bulk5 = 1, filter6 = 1, filter5 = 1, filter4 = 1, filter3 = 1, filterx = 1, resolve = 1, head = 1, tail = 1, pack = 1;
     } occ;
 
     // ---- host entry store ----
@@ -151,6 +152,9 @@ struct ovl_ctx {
     // ---- device: per-pass working buffers outside the arena ----
     DevBuf d_ctr, d_tmp, d_cand, d_cnt, d_bkt, d_big, d_peerhdr;
     DevBuf d_fmark, d_fkeep, d_foff, d_frows;  // ovl_filter_rows
+    DevBuf d_gkeys, d_gseqs, d_gflag, d_goff, d_gedges, d_gmark;  // ovl_build_graph
+    uint64_t n_frows = 0;      // rows kept by the last ovl_filter_rows
+    bool frows_valid = false;  // ... and they belong to the rows of the last pass
     DevBuf d_rows;                             // VIEW of the arena's row array (not owned)
     // ---- the arena ----
     DevBuf arena;
@@ -161,7 +165,7 @@ struct ovl_ctx {
     ArenaLayout peer_lay[ovl::MAX_RANKS] = {};
     uint64_t step = 0;
 
-    PinBuf h_frows, h_rows;
+    PinBuf h_frows, h_rows, h_gedges;
     uint64_t* h_ctr = nullptr;   // pinned, H_WORDS words: counters | status of every rank | segment counts | step
     uint64_t cand_cap = 0;       // candidate keys one pass may emit
     uint64_t min_cand_cap = 1ull << 20;
@@ -179,6 +183,7 @@ struct ovl_ctx {
     int opt_mirror = 1;         // 1: strand-mirror halving when every entry has its twin
     int opt_pack_bpsm = 16;     // K1 blocks per SM
     int opt_filter_kb = 8192;   // budget of the scan's bit filter (all slices), KiB
+    int opt_scan_bulk = 0;      // 1: k3_filter_bulk (cp.async.bulk tile ring), 0: k3_filter_wide (register pipeline)
     int opt_chunks = 8;         // pieces of the host -> HBM upload of ovl_overlaps (1 = one copy)
     int opt_timeout_ms = 20000; // peer wait timeout
     ovl_stats stats{};
@@ -679,6 +684,7 @@ int run_pass(ovl_ctx* c, uint32_t min_length, bool chunked) {
     S.bases = c->bases;
     S.kmer = (uint32_t)k;
     c->n_rows = 0;
+    c->frows_valid = false;
     c->rows_fetched = false;
     c->gathered = false;
     if (M == 0) return OVL_OK;  // the reference segfaults here; we return no rows
@@ -1047,8 +1053,14 @@ int run_pass(ovl_ctx* c, uint32_t min_length, bool chunked) {
                     const uint32_t want = (R.n_tiles + 7) / 8;
                     auto grid = [&](int resident) { return std::min<uint32_t>(want, (uint32_t)(nsm * resident)); };
                     switch (slog) {
-                        case 6: k3_filter_wide<6><<<grid(c->occ.filter6), 256, 0, st>>>(P); break;
-                        case 5: k3_filter_wide<5><<<grid(c->occ.filter5), 256, 0, st>>>(P); break;
+                        case 6:
+                            if (c->opt_scan_bulk) k3_filter_bulk<6><<<grid(c->occ.bulk6), 256, 0, st>>>(P);
+                            else k3_filter_wide<6><<<grid(c->occ.filter6), 256, 0, st>>>(P);
+                            break;
+                        case 5:
+                            if (c->opt_scan_bulk) k3_filter_bulk<5><<<grid(c->occ.bulk5), 256, 0, st>>>(P);
+                            else k3_filter_wide<5><<<grid(c->occ.filter5), 256, 0, st>>>(P);
+                            break;
                         case 4: k3_filter<4><<<grid(c->occ.filter4), 256, 0, st>>>(P); break;
                         case 3: k3_filter<3><<<grid(c->occ.filter3), 256, 0, st>>>(P); break;
                         default: k3_filter<-1><<<grid(c->occ.filterx), 256, 0, st>>>(P); break;
@@ -1425,6 +1437,7 @@ int ovl_create(int device, ovl_ctx** out) {
         CK(cudaEventCreate(&x->ev_t1));
         for (int i = 0; i < 12; ++i) CK(cudaEventCreate(&x->ev_dbg[i]));
         x->debug = getenv("OVL_DEBUG") ? atoi(getenv("OVL_DEBUG")) : 0;
+        if (getenv("OVL_SCAN_BULK")) x->opt_scan_bulk = atoi(getenv("OVL_SCAN_BULK")) != 0;  // A/B switch for whole test runs
         const size_t hwords = H_WORDS;
         CK(cudaHostAlloc(reinterpret_cast<void**>(&x->h_ctr), hwords * sizeof(uint64_t), cudaHostAllocDefault));
         memset(x->h_ctr, 0, hwords * sizeof(uint64_t));
@@ -1437,6 +1450,8 @@ int ovl_create(int device, ovl_ctx** out) {
             out_n = nb < 1 ? 1 : nb;
             return OVL_OK;
         };
+        OVL_TRY(resident(ovl::k3_filter_bulk<6>, x->occ.bulk6));
+        OVL_TRY(resident(ovl::k3_filter_bulk<5>, x->occ.bulk5));
         OVL_TRY(resident(ovl::k3_filter_wide<6>, x->occ.filter6));
         OVL_TRY(resident(ovl::k3_filter_wide<5>, x->occ.filter5));
         OVL_TRY(resident(ovl::k3_filter<4>, x->occ.filter4));
@@ -1463,12 +1478,13 @@ void ovl_destroy(ovl_ctx* c) {
     DevBuf* bufs[] = {&c->d_ascii, &c->d_src, &c->d_len, &c->d_flags, &c->d_gran0, &c->d_ent, &c->d_tile0,
                       &c->d_tile_ent, &c->d_stile0, &c->d_scan_tiles, &c->d_ctr, &c->d_tmp, &c->d_cand,
                       &c->d_cnt, &c->d_bkt, &c->d_big, &c->d_peerhdr, &c->d_fmark, &c->d_fkeep, &c->d_foff, &c->d_frows,
-                      &c->arena};
+                      &c->d_gkeys, &c->d_gseqs, &c->d_gflag, &c->d_goff, &c->d_gedges, &c->d_gmark, &c->arena};
     for (DevBuf* b : bufs)
         if (b->p) cudaFree(b->p);
     if (c->ascii.p) cudaFreeHost(c->ascii.p);
     if (c->h_rows.p) cudaFreeHost(c->h_rows.p);
     if (c->h_frows.p) cudaFreeHost(c->h_frows.p);
+    if (c->h_gedges.p) cudaFreeHost(c->h_gedges.p);
     if (c->h_ctr) cudaFreeHost(c->h_ctr);
     for (int i = 0; i < E_COUNT; ++i)
         if (c->ev[i]) cudaEventDestroy(c->ev[i]);
@@ -1586,6 +1602,7 @@ int ovl_clear(ovl_ctx* c) {
     c->tables_dirty = true;
     c->ascii_resident = false;
     c->n_rows = 0;
+    c->frows_valid = false;
     c->rows_fetched = false;
     c->gathered = false;
     c->e_lo = c->e_hi = 0;
@@ -1642,6 +1659,10 @@ int ovl_set_option(ovl_ctx* c, const char* name, int64_t value) {
         if (value < 4 || value > (1 << 22)) return fail(c, OVL_E_ARG, "filter_kb must be in 4..4194304");
         c->opt_filter_kb = (int)value;
         c->arena_key[0] = ~0ull;  // the arena is sized with it
+        return OVL_OK;
+    }
+    if (!strcmp(name, "scan_bulk")) {  // 1: bulk-async tile ring in the stride-32/64 filter pass, 0: register pipeline
+        c->opt_scan_bulk = value != 0;
         return OVL_OK;
     }
     if (!strcmp(name, "upload_chunks")) {

@@ -337,7 +337,7 @@ extern "C" int ovl_filter_rows(ovl_ctx* c, const ovl_filter_opts* o, const ovl_r
     if (blocks > (unsigned)c->n_sm * 16) blocks = (unsigned)c->n_sm * 16;
     if (o->contained_reads) {
         k8_mark<<<blocks, 256, 0, st>>>(P);
-        k8_count_marked<<<(M + 255) / 256 < 1024 ? (M + 255) / 256 : 1024, 256, 0, st>>>(fmark, M, fctr + 1);
+        k8_count_marked<<<(M + 255) / 256 < 1024 ? (M + 255) / 256 : 1024, 256, 0, st>>>(fmark, M, fctr + 1, 0xffffffffu);
     }
     k8_keep<<<blocks, 256, 0, st>>>(P);
     const uint32_t* kfinal = keep;
@@ -367,11 +367,123 @@ extern "C" int ovl_filter_rows(ovl_ctx* c, const ovl_filter_opts* o, const ovl_r
         *rows = reinterpret_cast<const ovl_row*>(c->h_frows.p);
     }
     *n_rows = kept;
+    c->n_frows = kept;
+    c->frows_valid = true;
     if (fs) {
         fs->rows_kept = kept;
         fs->rows_contained = h[2];
         fs->entries_removed = h[3];
         fs->ms_device = ev_ms(c, E_D2H0, E_D2H1);
+    }
+    return OVL_OK;
+}
+
+// =========================================================================================
+// Assembly-graph edge list (k10_graph.cuh; include/phasm_ovl.h has the contract).
+extern "C" int ovl_build_graph(ovl_ctx* c, int use_filtered, const ovl_edge** edges, uint64_t* n_edges, ovl_graph_stats* gs) {
+    using namespace ovl;
+    static_assert(sizeof(ovl_edge) == sizeof(Edge) && sizeof(ovl_edge) == 24, "edge record layout");
+    if (!c || !edges || !n_edges) return fail(c, OVL_E_ARG, "ovl_build_graph: NULL argument");
+    OVL_TRY(set_dev(c));
+    *edges = nullptr;
+    *n_edges = 0;
+    if (gs) memset(gs, 0, sizeof *gs);
+    if (use_filtered && !c->frows_valid) return fail(c, OVL_E_ARG, "ovl_build_graph: no ovl_filter_rows result for the rows of the last pass");
+    const uint64_t n = use_filtered ? c->n_frows : c->n_rows;
+    const uint32_t M = (uint32_t)c->len.size();
+    if (gs) gs->rows_in = n;
+    if (n == 0) return OVL_OK;
+    if (!c->pairs) return fail(c, OVL_E_ARG, "ovl_build_graph: the entry table is not strand-paired (node reversal is entry ^ 1)");
+    if (n >= 0x3fffffffull) return fail(c, OVL_E_LIMIT, "ovl_build_graph: more than 2^30 rows");
+    if (!use_filtered) OVL_TRY(gather_rows_pull(c));  // multi-GPU, rank 0: the other ranks' rows are still in their HBM
+    cudaStream_t st = c->st;
+    OVL_TRY(dev_ensure(c, c->d_gflag, n * 4));
+    OVL_TRY(dev_ensure(c, c->d_goff, (n + 1) * 8));
+    OVL_TRY(dev_ensure(c, c->d_gmark, (size_t)M * 4 + 16));  // node_mark[M] | counter
+    GraphParams P{};
+    P.rows = use_filtered ? c->d_frows.as<Row>() : c->d_rows.as<Row>();
+    P.n = n;
+    P.ent = c->d_ent.as<uint2>();
+    P.flag = c->d_gflag.as<uint32_t>();
+    P.off = c->d_goff.as<uint64_t>();
+    P.node_mark = c->d_gmark.as<uint32_t>();
+    unsigned long long* nctr = reinterpret_cast<unsigned long long*>(c->d_gmark.as<uint8_t>() + (((size_t)M * 4 + 7) & ~(size_t)7));
+    unsigned blocks = (unsigned)((n + 255) / 256);
+    if (blocks > (unsigned)c->n_sm * 16) blocks = (unsigned)c->n_sm * 16;
+    CK(cudaEventRecord(c->ev[E_D2H0], st));
+    CK(cudaMemsetAsync(P.node_mark, 0, (size_t)M * 4 + 16, st));
+    k10_flag<<<blocks, 256, 0, st>>>(P);
+    CK(cudaGetLastError());
+    size_t tb = 0;
+    CK(cub::DeviceScan::ExclusiveSum(nullptr, tb, P.flag, c->d_goff.as<uint64_t>(), (int)n, st));
+    OVL_TRY(dev_ensure(c, c->d_tmp, tb));
+    tb = c->d_tmp.cap;
+    CK(cub::DeviceScan::ExclusiveSum(c->d_tmp.p, tb, P.flag, c->d_goff.as<uint64_t>(), (int)n, st));
+    uint64_t h[2] = {0, 0};
+    CK(cudaMemcpyAsync(&h[0], c->d_goff.as<uint64_t>() + (n - 1), 8, cudaMemcpyDeviceToHost, st));
+    CK(cudaMemcpyAsync(&h[1], P.flag + (n - 1), 4, cudaMemcpyDeviceToHost, st));
+    CK(cudaStreamSynchronize(st));
+    const uint64_t n_ovl = h[0] + (h[1] & 0xffffffffull), n_items = 2 * n_ovl;
+    uint64_t n_e = 0, n_nodes = 0;
+    if (n_items) {
+        // keys | keys' and seqs | seqs' (radix sort ping-pong), last[] reuses the flag array's owner
+        OVL_TRY(dev_ensure(c, c->d_gkeys, 2 * n_items * 8));
+        OVL_TRY(dev_ensure(c, c->d_gseqs, 3 * n_items * 4));
+        OVL_TRY(dev_ensure(c, c->d_gedges, n_items * sizeof(Edge) + (n_items + 1) * 8));
+        uint64_t* k0 = c->d_gkeys.as<uint64_t>();
+        uint32_t* s0 = c->d_gseqs.as<uint32_t>();
+        P.keys = k0;
+        P.seqs = s0;
+        P.n_items = n_items;
+        k10_items<<<blocks, 256, 0, st>>>(P);
+        CK(cudaGetLastError());
+        cub::DoubleBuffer<uint64_t> dk(k0, k0 + n_items);
+        cub::DoubleBuffer<uint32_t> dv(s0, s0 + n_items);
+        const int end_bit = 32 + ceil_log2((uint64_t)M + 1);
+        tb = 0;
+        CK(cub::DeviceRadixSort::SortPairs(nullptr, tb, dk, dv, (int)n_items, 0, end_bit, st));
+        OVL_TRY(dev_ensure(c, c->d_tmp, tb));
+        tb = c->d_tmp.cap;
+        CK(cub::DeviceRadixSort::SortPairs(c->d_tmp.p, tb, dk, dv, (int)n_items, 0, end_bit, st));
+        P.keys = dk.Current();
+        P.seqs = dv.Current();
+        P.last = s0 + 2 * n_items;
+        uint64_t* eoff = reinterpret_cast<uint64_t*>(c->d_gedges.as<uint8_t>() + n_items * sizeof(Edge));
+        P.eoff = eoff;
+        P.edges = c->d_gedges.as<Edge>();
+        unsigned b2 = (unsigned)((n_items + 255) / 256);
+        if (b2 > (unsigned)c->n_sm * 16) b2 = (unsigned)c->n_sm * 16;
+        k10_runs<<<b2, 256, 0, st>>>(P);
+        CK(cudaGetLastError());
+        tb = 0;
+        CK(cub::DeviceScan::ExclusiveSum(nullptr, tb, P.last, eoff, (int)n_items, st));
+        OVL_TRY(dev_ensure(c, c->d_tmp, tb));
+        tb = c->d_tmp.cap;
+        CK(cub::DeviceScan::ExclusiveSum(c->d_tmp.p, tb, P.last, eoff, (int)n_items, st));
+        k10_edges<<<b2, 256, 0, st>>>(P);
+        k8_count_marked<<<(M + 255) / 256 < 1024 ? (M + 255) / 256 : 1024, 256, 0, st>>>(P.node_mark, M, nctr, 0u);
+        CK(cudaGetLastError());
+        uint64_t g[2] = {0, 0};
+        CK(cudaMemcpyAsync(&g[0], eoff + (n_items - 1), 8, cudaMemcpyDeviceToHost, st));
+        CK(cudaMemcpyAsync(&g[1], nctr, 8, cudaMemcpyDeviceToHost, st));
+        CK(cudaEventRecord(c->ev[E_D2H1], st));
+        CK(cudaStreamSynchronize(st));
+        n_e = g[0] + 1;  // the last item always closes a run
+        n_nodes = g[1];
+        OVL_TRY(pin_ensure(c, c->h_gedges, n_e * sizeof(ovl_edge), 0));
+        CK(cudaMemcpyAsync(c->h_gedges.p, c->d_gedges.p, n_e * sizeof(ovl_edge), cudaMemcpyDeviceToHost, st));
+        CK(cudaStreamSynchronize(st));
+        *edges = reinterpret_cast<const ovl_edge*>(c->h_gedges.p);
+    } else {
+        CK(cudaEventRecord(c->ev[E_D2H1], st));
+        CK(cudaStreamSynchronize(st));
+    }
+    *n_edges = n_e;
+    if (gs) {
+        gs->rows_overlap = n_ovl;
+        gs->n_edges = n_e;
+        gs->n_nodes = n_nodes;
+        gs->ms_device = ev_ms(c, E_D2H0, E_D2H1);
     }
     return OVL_OK;
 }

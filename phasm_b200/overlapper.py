@@ -30,6 +30,10 @@ __doc__module__ = "Optimised C++ all-vs-all exact overlap finder for PHASM"  # p
 
 Row = Tuple[str, str, int, int, int, int]
 
+# one edge of the assembly graph (ovl_edge in include/phasm_ovl.h)
+EDGE_DTYPE = np.dtype([("u", "<u4"), ("v", "<u4"), ("edge_len", "<i4"), ("overlap_len", "<u4"), ("first_seq", "<u8")])
+assert EDGE_DTYPE.itemsize == ctypes.sizeof(_capi.OvlEdge)
+
 
 def _as_bytes(x, what: str) -> bytes:
     if isinstance(x, str):
@@ -273,6 +277,24 @@ class ExactOverlapper:
         p, n = c_void_p(), c_uint64()
         self._check(self._lib.ovl_filter_rows(self._ctx, byref(o), byref(p), byref(n), byref(st)))
         return self._rows_array(p, n.value, copy), st.as_dict()
+
+    def build_graph(self, filtered: bool = True):
+        """Optional device post-pass: the edge list of the assembly graph the reference's ``layout``
+        stage builds from the alignments (``build_assembly_graph``, ``phasm/assembly_graph.py:136-179``)
+        -- over the rows kept by the last ``filter_rows`` call (``filtered=True``, what
+        ``assembler.py:93-100`` feeds it) or over all rows of the last ``overlaps*`` call.
+        Returns ``(edges, stats)``: a structured array (``EDGE_DTYPE``: u, v, edge_len, overlap_len,
+        first_seq) sorted by (u, v) on entry indices, and a dict with networkx's node / edge counts."""
+        from ._capi import OvlGraphStats
+        st = OvlGraphStats()
+        p, n = c_void_p(), c_uint64()
+        self._check(self._lib.ovl_build_graph(self._ctx, int(bool(filtered)), byref(p), byref(n), byref(st)))
+        if n.value:
+            buf = ctypes.string_at(p.value, n.value * EDGE_DTYPE.itemsize)
+            edges = np.frombuffer(buf, dtype=EDGE_DTYPE).copy()
+        else:
+            edges = np.zeros(0, dtype=EDGE_DTYPE)
+        return edges, st.as_dict()
 
     def set_collect_stats(self, on: bool) -> None:
         self._check(self._lib.ovl_set_collect_stats(self._ctx, int(bool(on))))

@@ -37,6 +37,27 @@ def sort_rows(arr: np.ndarray) -> np.ndarray:
     return arr[order]
 
 
+def edges_digest(edges) -> str:
+    """sha256 of an edge table [(u, v, edge_len, overlap_len, rank)] sorted by (u, v), as int64."""
+    import hashlib
+    arr = np.asarray(sorted(tuple(int(x) for x in e) for e in edges), dtype=np.int64).reshape(-1, 5)
+    return hashlib.sha256(np.ascontiguousarray(arr).tobytes()).hexdigest()
+
+
+def first_seq_to_rank(edges):
+    """Edges (u, v, w, ol, first_seq) sorted by (u, v) -> the same with first_seq replaced by the rank
+    of the edge in networkx's g.edges() order: nodes in order of first appearance (as u or v of an
+    add_edge call), each node's out-edges in order of first insertion."""
+    by_seq = sorted(edges, key=lambda e: e[4])
+    node_order = {}
+    for u, v, _, _, _ in by_seq:
+        node_order.setdefault(u, len(node_order))
+        node_order.setdefault(v, len(node_order))
+    ranked = sorted(edges, key=lambda e: (node_order[e[0]], e[4]))
+    rank = {(e[0], e[1]): r for r, e in enumerate(ranked)}
+    return [(u, v, w, ol, rank[(u, v)]) for u, v, w, ol, _ in edges]
+
+
 def reads_of(buf, off, names):
     return [(n, buf[int(off[i]):int(off[i + 1])].tobytes().decode()) for i, n in enumerate(names)]
 

@@ -1,0 +1,162 @@
+"""f4 assembly-graph build: the CPU restatement against golden vectors made with the
+reference's own build_assembly_graph, and the device post-pass (ovl_build_graph) against both."""
+import json
+import os
+
+import numpy as np
+import pytest
+
+import helpers
+from helpers import edges_digest, first_seq_to_rank, sort_rows
+from oracle import filters as F
+from oracle import graph as G
+
+GOLD = os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden", "graph.json")
+
+
+@pytest.fixture(scope="module")
+def gold():
+    with open(GOLD) as f:
+        return json.load(f)
+
+
+def filter_kwargs(opt):
+    return dict(contained_reads=True, **opt)
+
+
+def chain_input(c):
+    if c["case"] == "tiny":
+        return [tuple(r) for r in c["rows"]], c["lens"], None
+    reads, l = helpers.mid_input(c["case"])
+    lens = []
+    for _, s in reads:
+        lens += [len(s), len(s)]
+    rows = [tuple(int(x) for x in r) for r in sort_rows(helpers.load_mid()[c["case"]])]
+    return rows, lens, (reads, l)
+
+
+def check_graph(edges, n_nodes, want, what):
+    """edges: (u, v, w, ol, first_seq) sorted by (u, v)."""
+    assert n_nodes == want["n_nodes"], what
+    assert len(edges) == want["n_edges"], what
+    ranked = first_seq_to_rank(edges)
+    if "edges" in want:
+        assert [list(e) for e in ranked] == want["edges"], what
+    else:
+        assert edges_digest(ranked) == want["sha256"], what
+
+
+def test_restatement_matches_reference_on_general_alignments(gold):
+    n_ba = 0
+    for c in gold["aln"]:
+        edges, n_nodes = G.build_graph(c["alns"], c["lens"])
+        check_graph(edges, n_nodes, c["graph"], "aln")
+        n_ba += sum(F.classify(s, e, bs, be, c["lens"][a], c["lens"][b]) == F.OVERLAP_BA for a, b, s, e, bs, be in c["alns"])
+    assert n_ba > 20  # the OVERLAP_BA branch (assembly_graph.py:163-172) is exercised
+
+
+def test_restatement_matches_reference_layout_chain(gold):
+    n = 0
+    for c in gold["chain"]:
+        rows, lens, _ = chain_input(c)
+        if c["opt"] is not None:
+            kept, _ = F.filter_rows(rows, lens, **filter_kwargs(c["opt"]))
+            rows = [rows[i] for i in kept]
+        edges, n_nodes = G.build_graph([(a, b, s, e, 0, be) for a, b, s, e, be in rows], lens)
+        check_graph(edges, n_nodes, c["graph"], (c["case"], c["opt"]))
+        n += 1
+    assert n == len(gold["chain"]) and n >= 30
+
+
+def test_last_alignment_of_a_pair_decides_the_attributes():
+    lens = [100, 100, 100, 100]
+    alns = [(0, 2, 40, 100, 0, 60), (0, 2, 50, 100, 0, 50)]
+    edges, n_nodes = G.build_graph(alns, lens)
+    assert edges == [(0, 2, 50, 50, 0), (3, 1, 50, 50, 1)] and n_nodes == 4
+
+
+# ---- device ------------------------------------------------------------------------------------
+@pytest.fixture(scope="module")
+def ov():
+    from phasm_b200.overlapper import ExactOverlapper
+    o = ExactOverlapper()
+    yield o
+    o.close()
+
+
+def device_edges(arr):
+    return [(int(e["u"]), int(e["v"]), int(e["edge_len"]), int(e["overlap_len"]), int(e["first_seq"])) for e in arr]
+
+
+@pytest.mark.gpu
+def test_device_graph_matches_reference_on_mid_cases(ov, gold):
+    done = 0
+    for key in sorted(helpers.MID_SPECS):
+        cs = [c for c in gold["chain"] if c["case"] == key]
+        if not cs:
+            continue
+        reads, l = helpers.mid_input(key)
+        ov.clear()
+        lens = []
+        for name, seq in reads:
+            ov.add_read(name, seq)
+            lens += [len(seq), len(seq)]
+        rows = ov.overlaps_arrays(l)
+        for c in cs:
+            if c["opt"] is None:
+                arr, st = ov.build_graph(filtered=False)
+                n_in = len(rows)
+            else:
+                kept, _ = ov.filter_rows(**filter_kwargs(c["opt"]))
+                arr, st = ov.build_graph(filtered=True)
+                n_in = len(kept)
+            edges = device_edges(arr)
+            assert edges == sorted(edges)
+            check_graph(edges, st["n_nodes"], c["graph"], (key, c["opt"]))
+            assert st["rows_in"] == n_in and st["n_edges"] == len(edges)
+            done += 1
+    assert done >= 15
+
+
+@pytest.mark.gpu
+def test_device_graph_against_restatement_on_edge_mix(ov):
+    from phasm_b200 import synth
+    reads = synth.edge_mix(7, 150)
+    ov.clear()
+    lens = []
+    for name, seq in reads:
+        ov.add_read(name, seq)
+        lens += [len(seq), len(seq)]
+    rows = ov.overlaps_arrays(150)
+    assert len(rows) > 0
+    for opt in (None, dict(contained_reads=True), dict(contained_reads=False, max_overhang_abs=None),
+                dict(contained_reads=True, collapse_pairs=True)):
+        if opt is None:
+            use = rows.tolist()
+            arr, st = ov.build_graph(filtered=False)
+        else:
+            kept, _ = F.filter_rows(rows.tolist(), lens, **opt)
+            use = [rows[i].tolist() for i in kept]
+            ov.filter_rows(**opt)
+            arr, st = ov.build_graph(filtered=True)
+        want, n_nodes = G.build_graph([(a, b, s, e, 0, be) for a, b, s, e, be in use], lens)
+        assert device_edges(arr) == want, opt
+        assert st["n_nodes"] == n_nodes and st["rows_in"] == len(use)
+
+
+@pytest.mark.gpu
+def test_device_graph_needs_a_filter_result_and_pairs(ov):
+    ov.clear()
+    ov.add_read("r0", "ACGTACGTACGTACGTACGTAAAA")
+    ov.add_read("r1", "ACGTACGTACGTAAAACCCCGGGG")
+    ov.overlaps_arrays(8)
+    with pytest.raises(ValueError):
+        ov.build_graph(filtered=True)          # no filter_rows call for this pass
+    arr, st = ov.build_graph(filtered=False)
+    assert st["rows_in"] > 0
+    ov.clear()
+    ov.add_sequence("x", "ACGTACGTACGTACGTACGTAAAA")   # not strand-paired
+    ov.add_sequence("y", "ACGTACGTACGTAAAACCCCGGGG")
+    if len(ov.overlaps_arrays(8)):
+        with pytest.raises(ValueError):
+            ov.build_graph(filtered=False)
