@@ -538,6 +538,20 @@ def check_parity(ov, shape, world, rank, n_rows, window_bases):
         k_twin = np.sort(((sp[:, 1] ^ np.uint64(1)) * m2 + (sp[:, 0] ^ np.uint64(1))) * np.uint64(rl + 1) + sp[:, 4])
         res["mirror_invariant"] = bool(np.array_equal(k_fwd, k_twin))
         res["bit_exact"] = bool(res["bit_exact"] and res["mirror_invariant"])
+    # (d) the whole row set against the UNMODIFIED reference at full size, when its digest is committed
+    # for exactly this workload (tests/golden/config<k>_full.json: the compiled reference run once on
+    # the build host, tests/golden/make_config1_full.py) -- N = 1 only: at N GPUs the genome is N times as long
+    gold_path = os.path.join(ROOT, "tests", "golden", "config%d_full.json" % CONFIG_ID)
+    if world == 1 and os.path.exists(gold_path):
+        import hashlib
+        with open(gold_path) as f:
+            gold = json.load(f)
+        if gold.get("shape") == shape.name and gold.get("forward_bases") == shape.n_bases and "t0" in gold:
+            digest = hashlib.sha256(np.ascontiguousarray(rows, dtype=np.uint32).tobytes()).hexdigest() if in_order else None
+            res["reference_full"] = {"rows": gold["t0"]["rows"], "sha256_equal": digest == gold["t0"]["sha256"],
+                                     "reference_seconds": gold.get("t0_overlaps_seconds"),
+                                     "source": "tests/golden/config%d_full.json (oracle/_ref on the full workload)" % CONFIG_ID}
+            res["bit_exact"] = bool(res["bit_exact"] and res["reference_full"]["sha256_equal"])
     res["seconds"] = time.perf_counter() - t0
     return res
 

@@ -304,7 +304,7 @@ extern "C" int ovl_filter_rows(ovl_ctx* c, const ovl_filter_opts* o, const ovl_r
     const uint32_t M = (uint32_t)c->len.size();
     if (fs) fs->rows_in = n;
     if (n == 0) return OVL_OK;
-    if (n >= 0xffffffffull) return fail(c, OVL_E_LIMIT, "ovl_filter_rows: more than 2^32 rows");
+    if (n > 0x7fffffffull) return fail(c, OVL_E_LIMIT, "ovl_filter_rows: more than 2^31 rows (CUB item counts are int)");
     OVL_TRY(gather_rows_pull(c));  // multi-GPU, rank 0: the other ranks' rows are still in their HBM
     cudaStream_t st = c->st;
     const size_t fm_bytes = ((size_t)M * 4 + 7) & ~(size_t)7;

@@ -15,7 +15,6 @@ Follows the reference's caller ``phasm/cli/assembler.py:31-42``: ``add_sequence(
 from __future__ import annotations
 
 import argparse
-import hashlib
 import json
 import os
 import resource
@@ -26,19 +25,13 @@ import numpy as np
 
 ROOT = os.path.dirname(os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 sys.path.insert(0, ROOT)
+sys.path.insert(0, os.path.join(ROOT, "tests"))
 
 from oracle import port, ref  # noqa: E402
 from oracle.bruteforce import both_strand_entries  # noqa: E402
 from phasm_b200 import synth  # noqa: E402
+from helpers import rows_digest  # noqa: E402
 
-
-def rows_digest(rows: np.ndarray) -> dict:
-    """Digest of canonically sorted (a,b,astart,aend,bend) uint32 rows (entry indices)."""
-    rows = np.ascontiguousarray(rows, dtype=np.uint32)
-    if len(rows):
-        order = np.lexsort((rows[:, 4], rows[:, 3], rows[:, 2], rows[:, 1], rows[:, 0]))
-        rows = np.ascontiguousarray(rows[order])
-    return {"rows": int(len(rows)), "sha256": hashlib.sha256(rows.tobytes()).hexdigest()}
 
 
 def main():

@@ -37,6 +37,13 @@ def sort_rows(arr: np.ndarray) -> np.ndarray:
     return arr[order]
 
 
+def rows_digest(rows) -> dict:
+    """Row count + sha256 of the canonically sorted (a, b, astart, aend, bend) uint32 rows."""
+    import hashlib
+    rows = sort_rows(rows)
+    return {"rows": int(len(rows)), "sha256": hashlib.sha256(np.ascontiguousarray(rows).tobytes()).hexdigest()}
+
+
 def edges_digest(edges) -> str:
     """sha256 of an edge table [(u, v, edge_len, overlap_len, rank)] sorted by (u, v), as int64."""
     import hashlib

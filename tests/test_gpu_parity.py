@@ -430,3 +430,24 @@ def test_bucket_path_matches_serial_and_nonmirror_variants(ov):
         ov.set_collect_stats(False)
         ov.set_option("serial_verify", 0)
         ov.set_option("mirror", 1)
+
+
+def test_config1_full_equals_the_reference_digest(ov):
+    """BASELINE config 1 IN FULL (200 Mbases, 40 000 entries, -l 1000) against the UNMODIFIED reference:
+    tests/golden/config1_full.json holds the row count and the sha256 of the sorted rows of the compiled
+    reference's run on exactly this input (18 min, 14.5 GB on one host core;
+    tests/golden/make_config1_full.py)."""
+    import json
+    import os
+    from phasm_b200 import synth
+    with open(os.path.join(helpers.GOLDEN, "config1_full.json")) as f:
+        gold = json.load(f)
+    sh = synth.CONFIGS[1]
+    assert sh.name == gold["shape"] and sh.seed == gold["seed"]
+    buf, off, names = synth.generate(sh)
+    assert int(off[-1]) == gold["forward_bases"] and len(names) == gold["reads"]
+    ov.clear()
+    ov.add_reads_bulk(buf, off, names)
+    got = ov.overlaps_arrays(sh.min_length, copy=False)
+    assert helpers.rows_digest(got) == gold["t0"]
+    ov.clear()
