@@ -85,9 +85,11 @@ __global__ void __launch_bounds__(128) k2_prefix_ascii(const uint8_t* __restrict
 // Slots are only ever claimed, never released, so a reader that sees the key's fingerprint may
 // exchange without re-checking.
 __global__ void __launch_bounds__(256) k2_insert(const AnchorParams P) {
-    const uint64_t idx = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
-    const uint32_t b = (uint32_t)(idx >> P.stride_log2);
-    if (b < P.M) {
+    // grid-stride: the host may launch fewer blocks than keys / 256 so that the kernel trickles along
+    // beside K1 instead of taking its SM slots (k2_blocks_per_sm)
+    const uint64_t n_idx = (uint64_t)P.M << P.stride_log2;
+    for (uint64_t idx = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x; idx < n_idx; idx += (uint64_t)gridDim.x * blockDim.x) {
+        const uint32_t b = (uint32_t)(idx >> P.stride_log2);
         const uint2 m = __ldg(P.ent + b);
         if (m.y >= P.l) {
             const uint32_t delta = (uint32_t)idx & ((1u << P.stride_log2) - 1u);

@@ -103,7 +103,7 @@ __device__ __forceinline__ uint32_t bitmap_word(uint64_t h, uint32_t nr, int sli
     return (owner_of_hash(h, nr) << (slice_log2 - 5)) | (((uint32_t)h & ((1u << slice_log2) - 1u)) >> 5);
 }
 
-template <int SL>
+template <int SL, bool MULTI>
 __global__ void __launch_bounds__(256, 4) k3_filter_wide(const ScanParams P) {
     static_assert(SL == 5 || SL == 6, "one or two probes per granule");
     constexpr int NP = SL == 6 ? 1 : 2;
@@ -117,7 +117,7 @@ __global__ void __launch_bounds__(256, 4) k3_filter_wide(const ScanParams P) {
     const uint32_t nwarps = (gridDim.x * blockDim.x) >> 5;
     const uint32_t n_tiles = P.n_tiles;
     const uint64_t kmask = kmer_mask(P.k);
-    const uint32_t nr = P.T.nr;
+    const uint32_t nr = MULTI ? P.T.nr : 1u;  // one GPU: the owner arithmetic folds away
     auto surv_dest = [nr](const Surv& r) { return owner_of_hash(r.x, nr); };
     const uint32_t ll = P.l;
     const int bmb = P.bm_bits;

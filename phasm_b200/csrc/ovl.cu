@@ -183,6 +183,7 @@ struct ovl_ctx {
     int opt_mirror = 1;         // 1: strand-mirror halving when every entry has its twin
     int opt_pack_bpsm = 16;     // K1 blocks per SM
     int opt_filter_kb = 8192;   // budget of the scan's bit filter (all slices), KiB
+    int opt_k2_bpsm = 0;        // K2 blocks per SM (0 = one thread per key): fewer let it trickle beside K1
     int opt_scan_bulk = 0;      // 1: k3_filter_bulk (cp.async.bulk tile ring), 0: k3_filter_wide (register pipeline)
     int opt_chunks = 8;         // pieces of the host -> HBM upload of ovl_overlaps (1 = one copy)
     int opt_timeout_ms = 20000; // peer wait timeout
@@ -965,7 +966,9 @@ int run_pass(ovl_ctx* c, uint32_t min_length, bool chunked) {
             P.nr = (uint32_t)nr;
             P.flags = reinterpret_cast<unsigned long long*>(ctr + C_FLAGS);
             const uint64_t nthreads = (uint64_t)M << slog;
-            k2_insert<<<(unsigned)((nthreads + 255) / 256), 256, 0, sk>>>(P);
+            unsigned k2_blocks = (unsigned)((nthreads + 255) / 256);
+            if (c->opt_k2_bpsm > 0 && k2_blocks > (unsigned)(nsm * c->opt_k2_bpsm)) k2_blocks = (unsigned)(nsm * c->opt_k2_bpsm);
+            k2_insert<<<k2_blocks, 256, 0, sk>>>(P);
             ++launches;
             CK(cudaGetLastError());
             CK(cudaEventRecord(c->ev_k2, sk));
@@ -1055,11 +1058,13 @@ int run_pass(ovl_ctx* c, uint32_t min_length, bool chunked) {
                     switch (slog) {
                         case 6:
                             if (c->opt_scan_bulk) k3_filter_bulk<6><<<grid(c->occ.bulk6), 256, 0, st>>>(P);
-                            else k3_filter_wide<6><<<grid(c->occ.filter6), 256, 0, st>>>(P);
+                            else if (nr > 1) k3_filter_wide<6, true><<<grid(c->occ.filter6), 256, 0, st>>>(P);
+                            else k3_filter_wide<6, false><<<grid(c->occ.filter6), 256, 0, st>>>(P);
                             break;
                         case 5:
                             if (c->opt_scan_bulk) k3_filter_bulk<5><<<grid(c->occ.bulk5), 256, 0, st>>>(P);
-                            else k3_filter_wide<5><<<grid(c->occ.filter5), 256, 0, st>>>(P);
+                            else if (nr > 1) k3_filter_wide<5, true><<<grid(c->occ.filter5), 256, 0, st>>>(P);
+                            else k3_filter_wide<5, false><<<grid(c->occ.filter5), 256, 0, st>>>(P);
                             break;
                         case 4: k3_filter<4><<<grid(c->occ.filter4), 256, 0, st>>>(P); break;
                         case 3: k3_filter<3><<<grid(c->occ.filter3), 256, 0, st>>>(P); break;
@@ -1452,8 +1457,8 @@ int ovl_create(int device, ovl_ctx** out) {
         };
         OVL_TRY(resident(ovl::k3_filter_bulk<6>, x->occ.bulk6));
         OVL_TRY(resident(ovl::k3_filter_bulk<5>, x->occ.bulk5));
-        OVL_TRY(resident(ovl::k3_filter_wide<6>, x->occ.filter6));
-        OVL_TRY(resident(ovl::k3_filter_wide<5>, x->occ.filter5));
+        OVL_TRY(resident(ovl::k3_filter_wide<6, true>, x->occ.filter6));
+        OVL_TRY(resident(ovl::k3_filter_wide<5, true>, x->occ.filter5));
         OVL_TRY(resident(ovl::k3_filter<4>, x->occ.filter4));
         OVL_TRY(resident(ovl::k3_filter<3>, x->occ.filter3));
         OVL_TRY(resident(ovl::k3_filter<-1>, x->occ.filterx));
@@ -1659,6 +1664,11 @@ int ovl_set_option(ovl_ctx* c, const char* name, int64_t value) {
         if (value < 4 || value > (1 << 22)) return fail(c, OVL_E_ARG, "filter_kb must be in 4..4194304");
         c->opt_filter_kb = (int)value;
         c->arena_key[0] = ~0ull;  // the arena is sized with it
+        return OVL_OK;
+    }
+    if (!strcmp(name, "k2_blocks_per_sm")) {
+        if (value < 0 || value > 64) return fail(c, OVL_E_ARG, "k2_blocks_per_sm must be in 0..64");
+        c->opt_k2_bpsm = (int)value;
         return OVL_OK;
     }
     if (!strcmp(name, "scan_bulk")) {  // 1: bulk-async tile ring in the stride-32/64 filter pass, 0: register pipeline
