@@ -31,7 +31,8 @@ constexpr uint32_t BUCKET_MAX = 256;  // keys one warp sorts in shared memory
 struct BucketParams {
     SegList<uint64_t> hits;           // unsorted hit keys: the hit list of this rank (sizes are device counters)
     KeyFmt fmt;
-    uint32_t M;
+    uint32_t a0;                      // first entry of this rank's A range: every hit key routed here has a in [a0, a0 + M)
+    uint32_t M;                       // entries of the A range (the arrays below are indexed by a - a0: K7 does not grow with the ranks)
     uint32_t* cnt;                    // [M+1] hits per entry (zeroed by the host), cnt[M] stays 0
     const uint64_t* off;              // [M+1] exclusive sum of cnt
     uint32_t* cur;                    // [M] scatter cursors (zeroed by the host)
@@ -69,9 +70,10 @@ __global__ void __launch_bounds__(256) k7_hist(const BucketParams P) {
     const int sa = 2 + P.fmt.bits_p + P.fmt.bits_e;
     const uint32_t lane = threadIdx.x & 31;
     for_each_hit(P, [&](uint64_t key, bool valid) {
-        const uint32_t a = valid ? (uint32_t)(key >> sa) : 0xffffffffu;
+        uint32_t a = valid ? (uint32_t)(key >> sa) - P.a0 : 0xffffffffu;
+        if (a >= P.M) a = 0xffffffffu;  // cannot happen (keys are routed by owner); never index out of range
         const unsigned grp = __match_any_sync(FULL, a);
-        if (valid && lane == (uint32_t)(__ffs(grp) - 1)) atomicAdd(P.cnt + a, (uint32_t)__popc(grp));
+        if (a != 0xffffffffu && lane == (uint32_t)(__ffs(grp) - 1)) atomicAdd(P.cnt + a, (uint32_t)__popc(grp));
     });
 }
 
@@ -79,13 +81,15 @@ __global__ void __launch_bounds__(256) k7_scatter(const BucketParams P) {
     const int sa = 2 + P.fmt.bits_p + P.fmt.bits_e;
     const uint32_t lane = threadIdx.x & 31;
     for_each_hit(P, [&](uint64_t key, bool valid) {
-        const uint32_t a = valid ? (uint32_t)(key >> sa) : 0xffffffffu;
+        uint32_t a = valid ? (uint32_t)(key >> sa) - P.a0 : 0xffffffffu;
+        if (a >= P.M) a = 0xffffffffu;
+        const bool live = a != 0xffffffffu;
         const unsigned grp = __match_any_sync(FULL, a);
         const int leader = __ffs(grp) - 1;
         uint32_t base = 0;
-        if (valid && lane == (uint32_t)leader) base = atomicAdd(P.cur + a, (uint32_t)__popc(grp));
+        if (live && lane == (uint32_t)leader) base = atomicAdd(P.cur + a, (uint32_t)__popc(grp));
         base = __shfl_sync(FULL, base, leader);
-        if (valid) P.sorted[P.off[a] + base + __popc(grp & ((1u << lane) - 1u))] = key;
+        if (live) P.sorted[P.off[a] + base + __popc(grp & ((1u << lane) - 1u))] = key;
     });
 }
 
@@ -205,7 +209,8 @@ __global__ void __launch_bounds__(256) k7_emit(const BucketParams P) {
         const uint64_t lo = P.off[a], hi = P.off[a + 1];
         if (hi == lo) continue;
         const uint64_t n = hi - lo;
-        const uint32_t la = __ldg(P.ent + a).y;
+        const uint32_t ea = P.a0 + a;  // the entry
+        const uint32_t la = __ldg(P.ent + ea).y;
         uint64_t o = P.rowoff[a];
         for (uint64_t i0 = 0; i0 < n; i0 += 32) {
             const uint64_t i = i0 + lane;
@@ -226,10 +231,10 @@ __global__ void __launch_bounds__(256) k7_emit(const BucketParams P) {
                 const uint32_t p = P.fmt.p(key), b = P.fmt.b(key);
                 if ((key & HIT_CONT) && w < P.rows_cap) {
                     const uint32_t lb = __ldg(P.ent + b).y;
-                    P.rows[w] = Row{a, b, p, p + lb, lb};  // R2
+                    P.rows[w] = Row{ea, b, p, p + lb, lb};  // R2
                     ++w;
                 }
-                if (w < o + inc && w < P.rows_cap) P.rows[w] = Row{a, b, p, la, la - p};  // R1 (longest)
+                if (w < o + inc && w < P.rows_cap) P.rows[w] = Row{ea, b, p, la, la - p};  // R1 (longest)
             }
             o += __shfl_sync(FULL, inc, 31);
         }

@@ -1152,7 +1152,11 @@ int run_pass(ovl_ctx* c, uint32_t min_length, bool chunked) {
         BucketParams B;
         fill_list(B.hits, L_HITS);
         B.fmt = fmt;
-        B.M = M;
+        // bucket arrays over THIS rank's A range only (every hit key routed here has its a in it)
+        const uint32_t Mb = n_local;
+        const size_t Mb1 = (size_t)Mb + 1;
+        B.a0 = c->e_lo;
+        B.M = Mb;
         B.cnt = b_cnt;
         B.off = b_off;
         B.cur = b_cur;
@@ -1164,18 +1168,19 @@ int run_pass(ovl_ctx* c, uint32_t min_length, bool chunked) {
         B.ent = c->d_ent.as<uint2>();
         B.rows = d_rows;
         B.rows_cap = hits_room < L.rows_cap ? hits_room : L.rows_cap;  // this rank's share
-        uint32_t wblocks = (M + 7) / 8;
+        uint32_t wblocks = (Mb + 7) / 8;
+        if (wblocks < 1) wblocks = 1;
         if (wblocks > (uint32_t)nsm * 16) wblocks = (uint32_t)nsm * 16;
         CK(cudaMemsetAsync(b_cnt, 0, M1 * 12, st));  // cnt, cur, rowcnt
         k7_hist<<<kblocks, 256, 0, st>>>(B);
         tb = c->d_tmp.cap;
-        CK(cub::DeviceScan::ExclusiveSum(c->d_tmp.p, tb, b_cnt, b_off, (int)M1, st));
+        CK(cub::DeviceScan::ExclusiveSum(c->d_tmp.p, tb, b_cnt, b_off, (int)Mb1, st));
         k7_scatter<<<kblocks, 256, 0, st>>>(B);
         k7_sort<<<wblocks, 256, 0, st>>>(B);
         k7_sort_big<<<nsm, 1024, 0, st>>>(B);
         CK(cudaEventRecord(c->ev[E_EMIT0], st));
         tb = c->d_tmp.cap;
-        CK(cub::DeviceScan::ExclusiveSum(c->d_tmp.p, tb, b_rowcnt, b_rowoff, (int)M1, st));
+        CK(cub::DeviceScan::ExclusiveSum(c->d_tmp.p, tb, b_rowcnt, b_rowoff, (int)Mb1, st));
         k7_emit<<<wblocks, 256, 0, st>>>(B);
         launches += 5;
         lib += 2;
@@ -1186,7 +1191,7 @@ int run_pass(ovl_ctx* c, uint32_t min_length, bool chunked) {
         //      the ranks' HBM like the reads (rank order = canonical order).  A consumer that wants
         //      them in one place pulls them afterwards (ovl_fetch_rows / ovl_comm_gather_rows_device
         //      on rank 0); the row counts travel in the status vectors below ------------------------
-        const unsigned long long* d_nrows = reinterpret_cast<const unsigned long long*>(b_rowoff + M);
+        const unsigned long long* d_nrows = reinterpret_cast<const unsigned long long*>(b_rowoff + Mb);
         if (nr > 1) {
             // never leave a push in flight behind the end of the pass
             CK(cudaStreamWaitEvent(st, c->ev_push, 0));

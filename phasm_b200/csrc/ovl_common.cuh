@@ -217,41 +217,20 @@ __device__ __forceinline__ uint4 ldg_stream(const uint4* p) {
 }
 
 // Lookup shared by the scan kernels: list pointer of the key with hash h in its owner's
-// partition, NIL if absent.  K2 inserts with plain linear probing (slot s, s+1, ...); the lookup
-// walks the same sequence but fetches a whole 32-byte sector = 4 aligned slots per step (two
-// 128-bit loads issued together) and examines the slots from s on in order, so a probe sequence of
-// up to 4 slots costs ONE L2 round trip instead of up to 4 dependent ones (ncu r02f, k3_resolve: the
-// slot-by-slot loop ran 4.7 dependent loads per warp step -- the slowest lane's chain -- at load
-// factor 0.42).
+// partition, NIL if absent.  (Measured and not kept, r02i: fetching a whole 32-byte sector = 4 slots
+// per probe step -- 4.7 dependent loads per warp step became ~2, but k3_resolve stayed at 87 us:
+// it is bound by its ~360 instructions per 32 survivors at 44 resident warps, not by this chain.)
 __device__ __forceinline__ uint32_t table_find(const TableView& T, uint64_t h, uint32_t& owner) {
     owner = owner_of_hash(h, T.nr);
     const Slot* __restrict__ table = T.tbl[owner];
     const uint32_t tmask = (1u << T.tbits) - 1u;
     const uint32_t fp = (uint32_t)h;
     uint32_t s = slot_of(h, T.nr, T.tbits);
-    if (T.tbits < 2) {  // degenerate tables: slot by slot
-        for (uint32_t tries = 0; tries <= tmask; ++tries) {
-            const unsigned long long v = __ldg(table + s);
-            if (v == EMPTY_SLOT) return NIL;
-            if ((uint32_t)(v >> 32) == fp) return (uint32_t)v;
-            s = (s + 1) & tmask;
-        }
-        return NIL;
-    }
-    uint32_t first = s & 3u;  // slots of the first sector before s are not part of the probe sequence
-    s &= ~3u;
-    for (uint32_t tries = 0; tries <= tmask; tries += 4) {
-        const ulonglong2 v01 = __ldg(reinterpret_cast<const ulonglong2*>(table + s));
-        const ulonglong2 v23 = __ldg(reinterpret_cast<const ulonglong2*>(table + s + 2));
-        const unsigned long long v[4] = {v01.x, v01.y, v23.x, v23.y};
-#pragma unroll
-        for (uint32_t j = 0; j < 4; ++j) {
-            if (j < first) continue;
-            if (v[j] == EMPTY_SLOT) return NIL;
-            if ((uint32_t)(v[j] >> 32) == fp) return (uint32_t)v[j];
-        }
-        first = 0;
-        s = (s + 4) & tmask;
+    for (uint32_t tries = 0; tries <= tmask; ++tries) {
+        const unsigned long long v = __ldg(table + s);
+        if (v == EMPTY_SLOT) return NIL;
+        if ((uint32_t)(v >> 32) == fp) return (uint32_t)v;
+        s = (s + 1) & tmask;
     }
     return NIL;
 }

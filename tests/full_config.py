@@ -82,6 +82,8 @@ def main():
                "gbases_per_s_device": sh.n_bases / (float(ms.item()) * 1e-3) / 1e9,
                "s_call_with_gather_and_d2h": t_call, "s_generate_rank0": t_gen,
                "anchor_stride": st["anchor_stride"], "mirror": st["mirror"],
+               "big_buckets_rank0": st["big_buckets"], "retries_rank0": st["retries"],
+               "scan_survivors_rank0": st["scan_survivors"],
                "stage_ms_rank0": {k: st[k] for k in ("ms_pack", "ms_anchor", "ms_scan", "ms_verify", "ms_sort", "ms_emit")}}
         # ---- restriction vs the CPU oracle on one genome window --------------------------------
         wb, wo, wn, widx = synth.window_subsample(sh, int(args.window_bases))
