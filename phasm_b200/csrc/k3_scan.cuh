@@ -474,15 +474,19 @@ __global__ void __launch_bounds__(256) k3_resolve(const ScanParams P) {
     RouteScratch* rs = &s_rs[threadIdx.x >> 5];
     uint32_t nbuf = 0;
     const uint64_t nthreads = (uint64_t)gridDim.x * blockDim.x;
-    for (uint32_t seg = 0; seg < P.probes.nr; ++seg) {  // the survivors every source rank sent here
-        const unsigned long long n_all = P.probes.n[seg];
-        const uint64_t n = n_all < P.probes.seg_cap ? n_all : P.probes.seg_cap;
-        const Surv* __restrict__ list = P.probes.base + (uint64_t)seg * P.probes.seg_cap;
-        for (uint64_t i0 = ((uint64_t)blockIdx.x * blockDim.x + threadIdx.x) & ~31ull; i0 < n; i0 += nthreads) {
+    for (uint32_t seg = 0; seg < P.probes.nr; ++seg) {  // the survivors of every source rank for this rank's k-mers
+        const uint64_t n = seg_count(P.probes, seg);
+        const Surv* __restrict__ list = P.probes.seg[seg];  // in the source's arena: streamed over NVLink
+        const uint64_t first = ((uint64_t)blockIdx.x * blockDim.x + threadIdx.x) & ~31ull;
+        // one record ahead: the (possibly remote) load of the next item is in flight while this one is resolved
+        Surv nxt = make_ulonglong2(0, 0);
+        if (first + lane < n) nxt = list[first + lane];
+        for (uint64_t i0 = first; i0 < n; i0 += nthreads) {
             const uint64_t i = i0 + lane;
+            const Surv rec = nxt;
+            if (i + nthreads < n) nxt = list[i + nthreads];
             uint32_t ptr = NIL, owner = 0, a = 0, q = 0, la = 0;
             if (i < n) {
-                const Surv rec = list[i];
                 a = (uint32_t)(rec.y >> 32);
                 q = (uint32_t)rec.y;
                 ptr = table_find(P.T, rec.x, owner);

@@ -115,7 +115,7 @@ __global__ void __launch_bounds__(256) k4_verify_serial(const VerifyParams P) {
         uint64_t key = 0;
         uint32_t my_ga = 0, my_gb = 0, my_sh = 0, my_n = 0, my_fl = 0;
         if (c < n_all) {
-            key = P.keys.base[seg_phys(P.keys, s_pre, c)];
+            key = seg_item(P.keys, s_pre, c);
             const uint32_t a = P.fmt.a(key), b = P.fmt.b(key), p = P.fmt.p(key);
             const uint2 ma = __ldg(P.ent + a), mb = __ldg(P.ent + b);
             const uint32_t rem = ma.y - p;
@@ -225,7 +225,7 @@ struct Verify2Params {
     const uint64_t* packed64;
     const uint2* ent;                  // {gran0, len}
     KeyFmt fmt;
-    uint32_t* surv;                    // k4a -> k4b: physical indices (into keys.base) of the candidates alive after the head
+    uint32_t* surv;                    // k4a -> k4b: logical indices (into the key list) of the candidates alive after the head
     unsigned long long* n_surv;
     CandSink hits;                     // verified keys with their flag bits set
     MirrorRule mirror;                 // on: the scan kept only the self-verifying candidates
@@ -317,11 +317,10 @@ __global__ void __launch_bounds__(256, 4) k4a_head(const Verify2Params P) {
 
     for (uint64_t tile = next_tile(P.tile_ctr, lane); tile < n_tiles; tile = next_tile(P.tile_ctr, lane)) {
         const uint64_t c = tile * 32 + lane;
-        uint64_t key = 0, phys = 0;
+        uint64_t key = 0;
         CandMeta my = {0, 0, 0, 0, 0};  // n == 0 marks "no candidate" (a real one has n >= l >= 1)
         if (c < n_all) {
-            phys = seg_phys(P.keys, s_pre, c);
-            key = P.keys.base[phys];
+            key = seg_item(P.keys, s_pre, c);
             my = cand_meta(P, key);
         }
         uint32_t ok_mask = 0;  // bit j: candidate j matched over its head
@@ -368,7 +367,7 @@ __global__ void __launch_bounds__(256, 4) k4a_head(const Verify2Params P) {
             unsigned long long base = 0;
             if (lane == 0) base = atomicAdd(P.n_surv, (unsigned long long)__popc(am));
             base = __shfl_sync(FULL, base, 0);
-            if (alive) P.surv[base + __popc(am & ((1u << lane) - 1u))] = (uint32_t)phys;
+            if (alive) P.surv[base + __popc(am & ((1u << lane) - 1u))] = (uint32_t)c;
         }
     }
     if (nbuf) wbuf_flush(buf, nbuf, P.hits, lane, rs, dest);
@@ -434,9 +433,11 @@ __device__ __forceinline__ uint4 tail_diff(const uint4* __restrict__ pa, const u
 __global__ void __launch_bounds__(256, 4) k4b_tail(const Verify2Params P) {
     __shared__ uint64_t s_buf[8][WBUF];
     __shared__ RouteScratch s_rs[8];
+    __shared__ unsigned long long s_pre[MAX_RANKS + 1];
     RouteScratch* rs = &s_rs[threadIdx.x >> 5];
     auto dest = [&](uint64_t k2) { return hit_dest(P, k2); };
     const uint32_t lane = threadIdx.x & 31;
+    seg_prefix(P.keys, s_pre);
     const uint64_t ns = *P.n_surv;
     const uint64_t n_tiles = (ns + 31) / 32;
     uint64_t* buf = s_buf[threadIdx.x >> 5];
@@ -450,7 +451,7 @@ __global__ void __launch_bounds__(256, 4) k4b_tail(const Verify2Params P) {
         uint64_t key = 0;
         CandMeta my = {0, 0, 0, 0, 0};
         if (s < ns) {
-            key = P.keys.base[P.surv[s]];
+            key = seg_item(P.keys, s_pre, P.surv[s]);
             my = cand_meta(P, key);
         }
         const uint32_t cnt = (uint32_t)((ns - tile * 32) < 32 ? (ns - tile * 32) : 32);

@@ -17,18 +17,21 @@
 //   * three item exchanges carry 8/16-byte records to the rank that needs them next: scan
 //     survivors (k-mer hash, A entry, position) to the rank that owns the k-mer's slice of the
 //     anchor table, candidate keys to the rank that compares them, verified hit keys to the rank
-//     that owns their A entry.  They are FUSED into the producing kernels (k3_filter, k3_resolve,
-//     k4a/k4b): a rank's list has one segment per source rank; when a warp's shared-memory staging
-//     buffer is full it sorts the 128-256 items by destination, reserves room with one atomic per
-//     destination on a counter in the SOURCE's own memory and stores the runs straight into its
-//     segment of every destination's list over NVLink, while the kernel goes on computing.  The
-//     per-destination counts travel with the "phase done" signal (k_signal_counts).  History:
+//     that owns their A entry.  They are a PULL: the producing kernel (k3_filter, k3_resolve,
+//     k4a/k4b) sorts the 128-256 items of a warp's shared-memory staging buffer by destination,
+//     reserves room with one atomic per destination on a counter in its OWN memory and stores the
+//     runs into per-destination segments in its OWN arena; the per-destination counts travel with
+//     the "phase done" signal (k_signal_counts), and the consuming kernel of the destination
+//     (k3_resolve, the candidate grouping, k7_hist / k7_scatter) streams the segment out of the
+//     producer's arena through the peer mapping, a whole grid of coalesced loads.  History:
 //     (1) resolving survivors through peer-mapped table pointers (one 8-byte peer load per probe;
 //     every such load moves a 32-byte sector plus packet headers): the scan of 2 GPUs took 2.2x the
 //     time of one; (2) a routing kernel per exchange with one remote atomic per warp: ~150 000
 //     atomics on one remote address, ~0.4 ms of serialised NVLink round trips; (3) the same with
-//     one remote atomic per 1024 items: 0.10 / 0.06 / 0.04 ms per exchange at 2 GPUs
-//     (profiles/r02f_*), now gone with the staging lists they read;
+//     one remote atomic per 1024 items: 0.10 / 0.06 / 0.04 ms per exchange at 2 GPUs; (4) PUSHED from
+//     inside the producing kernels (remote stores in runs of 512 / N bytes): the producers slowed
+//     down with the share of remote items -- filter pass 0.13 / 0.22 / 0.38 ms at 1 / 2 / 4 GPUs,
+//     the stores competing with the bulk copies on the same links (profiles/r02l_*);
 //   * the rows stay on the rank that emitted them (sharded by A range like the reads); rank 0
 //     pulls them with copy-engine copies only when a consumer asks for all of them in one place.
 //
@@ -141,7 +144,7 @@ struct StatusParams {
     const unsigned long long* flags;      // STF_* bits raised by kernels
     const unsigned long long* abort_word;
     const unsigned long long* seg_n;      // [L_COUNT][MAX_RANKS] of this rank's header
-    unsigned long long seg_cap[L_COUNT];  // capacity of one segment of every list
+    unsigned long long seg_cap[L_COUNT][MAX_RANKS];  // capacity of the segment of every source in every list
     uint32_t nr;
     const unsigned long long* n_surv;     // verifier: candidates alive after the head
     unsigned long long cap_surv;
@@ -157,7 +160,7 @@ __global__ void k9_status(const StatusParams P) {
         if (f > fill) fill = f;
     };
     for (int k = 0; k < L_COUNT; ++k)
-        for (uint32_t s = 0; s < P.nr; ++s) see(P.seg_n[k * MAX_RANKS + s], P.seg_cap[k]);
+        for (uint32_t s = 0; s < P.nr; ++s) see(P.seg_n[k * MAX_RANKS + s], P.seg_cap[k][s]);
     see(*P.n_surv, P.cap_surv);
     see(*P.n_rows, P.cap_rows);
     unsigned long long fl = *P.flags | (*P.abort_word ? STF_TIMEOUT : 0ull);

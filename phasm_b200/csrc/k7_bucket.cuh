@@ -52,9 +52,8 @@ template <class F>
 __device__ __forceinline__ void for_each_hit(const BucketParams& P, F f) {
     const uint32_t lane = threadIdx.x & 31;
     for (uint32_t seg = 0; seg < P.hits.nr; ++seg) {
-        const unsigned long long n_all = P.hits.n[seg];
-        const uint64_t n = n_all < P.hits.seg_cap ? n_all : P.hits.seg_cap;
-        const uint64_t* __restrict__ list = P.hits.base + (uint64_t)seg * P.hits.seg_cap;
+        const uint64_t n = seg_count(P.hits, seg);
+        const uint64_t* __restrict__ list = P.hits.seg[seg];  // in the source's arena: streamed over NVLink
         for (uint64_t i0 = ((uint64_t)blockIdx.x * blockDim.x + threadIdx.x) & ~31ull; i0 < n; i0 += (uint64_t)gridDim.x * blockDim.x) {
             const uint64_t i = i0 + lane;
             f(i < n ? list[i] : 0ull, i < n);

@@ -183,6 +183,7 @@ struct ovl_ctx {
     int opt_mirror = 1;         // 1: strand-mirror halving when every entry has its twin
     int opt_pack_bpsm = 16;     // K1 blocks per SM
     int opt_filter_kb = 8192;   // budget of the scan's bit filter (all slices), KiB
+    int opt_group_cands = -1;   // group the candidate keys by A entry before K4: -1 = when N > 1, 0 / 1 = never / always
     int opt_k2_bpsm = 0;        // K2 blocks per SM (0 = one thread per key): fewer let it trickle beside K1
     int opt_scan_bulk = 0;      // 1: k3_filter_bulk (cp.async.bulk tile ring), 0: k3_filter_wide (register pipeline)
     int opt_chunks = 8;         // pieces of the host -> HBM upload of ovl_overlaps (1 = one copy)
@@ -799,9 +800,12 @@ int run_pass(ovl_ctx* c, uint32_t min_length, bool chunked) {
         Slot* d_table = at<Slot>(A, L.off_table);
         uint32_t* d_next = at<uint32_t>(A, L.off_next);
         Row* d_rows = at<Row>(A, L.off_rows);
-        const uint64_t hits_room = (uint64_t)nr * L.seg_cap[L_HITS];  // hit keys this rank's list can hold = rows it can emit
-        const uint64_t cand_room = (uint64_t)nr * L.seg_cap[L_CAND];
-        OVL_TRY(dev_ensure(c, c->d_cand, hits_room * 8, false));  // the bucketed, then sorted hit keys
+        uint64_t hits_room = 0, cand_room = 0;  // hit keys / candidate keys this rank can receive (= rows it can emit / keys it verifies)
+        for (int s2 = 0; s2 < nr; ++s2) {
+            hits_room += c->peer_lay[s2].seg_cap[L_HITS];
+            cand_room += c->peer_lay[s2].seg_cap[L_CAND];
+        }
+        OVL_TRY(dev_ensure(c, c->d_cand, std::max(hits_room, cand_room) * 8, false));  // the candidate keys grouped by A entry (N > 1), then the bucketed / sorted hit keys
         OVL_TRY(dev_ensure(c, c->d_cnt, cand_room * 4, false));   // survivor list of the verifier's head
         OVL_TRY(dev_ensure(c, c->d_big, (size_t)M * 4 + 4, false));
         const size_t M1 = (size_t)M + 1;
@@ -855,10 +859,17 @@ int run_pass(ovl_ctx* c, uint32_t min_length, bool chunked) {
                 CK(cudaStreamWaitEvent(sk, c->ev_chunk[ch], 0));
             }
             if (e_next > e_prev) {
-                k2_prefix_ascii<<<(e_next - e_prev + 127) / 128, 128, 0, sk>>>(
+                // chunked: on K2's stream, beside this piece's K1.  Resident reads: on the main stream AHEAD of
+                // K1 -- the prefix table is what K2 (and, on N GPUs, every peer's K2) waits for, 13 us of work
+                // that took until +0.08..0.14 ms when it had to find SM slots beside the persistent K1 grid
+                k2_prefix_ascii<<<(e_next - e_prev + 127) / 128, 128, 0, chunked ? sk : st>>>(
                     c->d_ascii.as<uint8_t>(), c->d_src.as<uint64_t>(), c->d_len.as<uint32_t>(), c->d_flags.as<uint8_t>(),
                     d_pre, e_prev, e_next);
                 ++launches;
+                if (!chunked) {
+                    CK(cudaEventRecord(c->ev_prel, st));
+                    CK(cudaStreamWaitEvent(sk, c->ev_prel, 0));
+                }
                 const uint32_t t_lo = c->tile0[e_prev], t_hi = c->tile0[e_next];
                 if (t_hi > t_lo) {
                     K.t_begin = t_lo;
@@ -877,7 +888,7 @@ int run_pass(ovl_ctx* c, uint32_t min_length, bool chunked) {
             c->ascii_resident = true;
             S.ascii_bytes = c->ascii_used + SLACK;
         }
-        CK(cudaEventRecord(c->ev_prel, sk));
+        if (chunked || n_local == 0) CK(cudaEventRecord(c->ev_prel, sk));
         CK(cudaEventRecord(c->ev_pack, st));
         // ---- N > 1: push the prefix slice (small, urgent) and the forward region slice (bulk) -------
         if (nr > 1) {
@@ -999,24 +1010,28 @@ int run_pass(ovl_ctx* c, uint32_t min_length, bool chunked) {
         //      rank's list), and its own list as the consumers see it ---------------------------------
         const uint64_t off_list[L_COUNT] = {L.off_scan, L.off_cand, L.off_inbox};
         const size_t item_size[L_COUNT] = {sizeof(Surv), 8, 8};
+        // producer side: the segment for destination r is in MY arena (slot r of my list region)
         auto fill_sink = [&](auto& sink, int kind) {
             using T = std::remove_pointer_t<std::remove_reference_t<decltype(sink.seg[0])>>;
             sink.nr = (uint32_t)nr;
             for (int r = 0; r < nr; ++r) {
-                const ArenaLayout& PL = c->peer_lay[r];
-                const uint64_t o = kind == L_SCAN ? PL.off_scan : kind == L_CAND ? PL.off_cand : PL.off_inbox;
-                sink.seg[r] = at<T>(c->peer_base[r], o + (uint64_t)me * PL.seg_cap[kind] * item_size[kind]);
-                sink.cap[r] = PL.seg_cap[kind];
+                sink.seg[r] = at<T>(A, off_list[kind] + (uint64_t)r * L.seg_cap[kind] * item_size[kind]);
+                sink.cap[r] = L.seg_cap[kind];
             }
             // 1 GPU: the only segment's counter is the list's own; N GPUs: counters in this rank's
             // memory, published with the phase signal
             sink.cnt = nr > 1 ? reinterpret_cast<unsigned long long*>(ctr + C_SEND + kind * MAX_RANKS) : &H->seg_n[kind][0];
         };
+        // consumer side: segment s = slot `me` of rank s's list region, read in place (peer mapping)
         auto fill_list = [&](auto& list, int kind) {
-            using T = std::remove_const_t<std::remove_pointer_t<std::remove_reference_t<decltype(list.base)>>>;
-            list.base = at<T>(A, off_list[kind]);
+            using T = std::remove_const_t<std::remove_pointer_t<std::remove_reference_t<decltype(list.seg[0])>>>;
+            for (int s2 = 0; s2 < nr; ++s2) {
+                const ArenaLayout& PL = c->peer_lay[s2];
+                const uint64_t o = kind == L_SCAN ? PL.off_scan : kind == L_CAND ? PL.off_cand : PL.off_inbox;
+                list.seg[s2] = at<T>(c->peer_base[s2], o + (uint64_t)me * PL.seg_cap[kind] * item_size[kind]);
+                list.cap[s2] = PL.seg_cap[kind];
+            }
             list.n = H->seg_n[kind];
-            list.seg_cap = L.seg_cap[kind];
             list.nr = (uint32_t)nr;
         };
         // phase done: my counts of list `kind` to every rank, then wait for everybody's
@@ -1073,6 +1088,7 @@ int run_pass(ovl_ctx* c, uint32_t min_length, bool chunked) {
                     ++launches;
                     CK(cudaGetLastError());
                 }
+                if (c->debug) CK(cudaEventRecord(c->ev_dbg[6], st));
                 OVL_TRY(exchange(F_SCAN, L_SCAN));  // the survivors went straight into their owners' probe lists
                 if (c->debug) CK(cudaEventRecord(c->ev_dbg[5], st));
                 k3_resolve<<<(uint32_t)(nsm * c->occ.resolve), 256, 0, st>>>(P);
@@ -1123,6 +1139,37 @@ int run_pass(ovl_ctx* c, uint32_t min_length, bool chunked) {
             } else {
                 Verify2Params V;
                 fill_list(V.keys, L_CAND);
+                const bool group = c->opt_group_cands < 0 ? nr > 1 : c->opt_group_cands != 0;
+                if (group) {
+                    // N > 1: the candidates reach their verifier in short runs (a source warp's survivors
+                    // are split over the k-mer owners, and their candidates again over the verifiers), so
+                    // the A operand of consecutive candidates is no longer the same entry and stops
+                    // coming from L1 (N = 2: verify 0.545 -> 0.65 ms).  Group the keys by A entry first:
+                    // the K7 histogram / scatter pair over the candidate list.
+                    uint64_t* g_off = c->d_bkt.as<uint64_t>();
+                    uint32_t* g_cnt = reinterpret_cast<uint32_t*>(g_off + 2 * M1);
+                    BucketParams G{};
+                    fill_list(G.hits, L_CAND);
+                    G.fmt = fmt;
+                    G.a0 = 0;
+                    G.M = M;
+                    G.cnt = g_cnt;
+                    G.off = g_off;
+                    G.cur = g_cnt + M1;
+                    G.sorted = c->d_cand.as<uint64_t>();
+                    CK(cudaMemsetAsync(g_cnt, 0, M1 * 8, st));  // cnt, cur
+                    k7_hist<<<kblocks, 256, 0, st>>>(G);
+                    size_t tbg = c->d_tmp.cap;
+                    CK(cub::DeviceScan::ExclusiveSum(c->d_tmp.p, tbg, g_cnt, g_off, (int)M1, st));
+                    k7_scatter<<<kblocks, 256, 0, st>>>(G);
+                    launches += 2;
+                    lib += 1;
+                    CK(cudaGetLastError());
+                    V.keys.seg[0] = c->d_cand.as<uint64_t>();
+                    V.keys.n = reinterpret_cast<const unsigned long long*>(g_off + M);  // total = last element of the exclusive sum
+                    V.keys.cap[0] = cand_room;
+                    V.keys.nr = 1;
+                }
                 V.packed64 = reinterpret_cast<const uint64_t*>(d_packed);
                 V.ent = c->d_ent.as<uint2>();
                 V.fmt = fmt;
@@ -1208,7 +1255,8 @@ int run_pass(ovl_ctx* c, uint32_t min_length, bool chunked) {
             SP.flags = reinterpret_cast<const unsigned long long*>(ctr + C_FLAGS);
             SP.abort_word = &H->abort;
             SP.seg_n = &H->seg_n[0][0];
-            for (int kk = 0; kk < L_COUNT; ++kk) SP.seg_cap[kk] = L.seg_cap[kk];
+            for (int kk = 0; kk < L_COUNT; ++kk)
+                for (int s2 = 0; s2 < nr; ++s2) SP.seg_cap[kk][s2] = c->peer_lay[s2].seg_cap[kk];
             SP.nr = (uint32_t)nr;
             SP.n_surv = reinterpret_cast<const unsigned long long*>(ctr + C_NSURV);
             SP.cap_surv = cand_room;
@@ -1324,11 +1372,11 @@ int run_pass(ovl_ctx* c, uint32_t min_length, bool chunked) {
         };
         const bool mg = c->nranks > 1;
         fprintf(stderr, "[ovl rank %d step %llu] +ms: pack_end %.3f | sk: pre_wait_end %.3f insert_end %.3f | sg: pre_pushed %.3f filt_pushed %.3f | "
-                        "sp: fwd_pushed %.3f | st: scan0 %.3f probes_in %.3f resolve_end %.3f cands_in(verify0) %.3f fwd_in %.3f sort0 %.3f "
+                        "sp: fwd_pushed %.3f | st: scan0 %.3f filter_end %.3f probes_in %.3f resolve_end %.3f cands_in(verify0) %.3f fwd_in %.3f sort0 %.3f "
                         "hits_in %.3f emit0 %.3f end %.3f\n",
                 c->rank, (unsigned long long)c->step, rel(c->ev[E_ANCHOR0]), rel(c->ev_dbg[0]), rel(c->ev_dbg[1]),
                 mg ? rel(c->ev_dbg[2]) : -1.f, mg ? rel(c->ev_dbg[3]) : -1.f, mg ? rel(c->ev_dbg[4]) : -1.f, rel(c->ev[E_SCAN0]),
-                mg ? rel(c->ev_dbg[5]) : -1.f, rel(c->ev_dbg[8]), rel(c->ev[E_VERIFY0]), mg ? rel(c->ev_dbg[9]) : -1.f,
+                rel(c->ev_dbg[6]), mg ? rel(c->ev_dbg[5]) : -1.f, rel(c->ev_dbg[8]), rel(c->ev[E_VERIFY0]), mg ? rel(c->ev_dbg[9]) : -1.f,
                 rel(c->ev[E_SORT0]), mg ? rel(c->ev_dbg[10]) : -1.f, rel(c->ev[E_EMIT0]), rel(c->ev[E_END]));
     }
     S.ms_pack = ev_ms(c, E_PACK0, E_ANCHOR0);
@@ -1669,6 +1717,10 @@ int ovl_set_option(ovl_ctx* c, const char* name, int64_t value) {
         if (value < 4 || value > (1 << 22)) return fail(c, OVL_E_ARG, "filter_kb must be in 4..4194304");
         c->opt_filter_kb = (int)value;
         c->arena_key[0] = ~0ull;  // the arena is sized with it
+        return OVL_OK;
+    }
+    if (!strcmp(name, "group_cands")) {
+        c->opt_group_cands = value < 0 ? -1 : (value != 0);
         return OVL_OK;
     }
     if (!strcmp(name, "k2_blocks_per_sm")) {

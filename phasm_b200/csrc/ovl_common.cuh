@@ -238,11 +238,11 @@ __device__ __forceinline__ uint32_t table_find(const TableView& T, uint64_t h, u
 // ---- item lists between the stages (and, on N > 1 GPUs, between the ranks) ----------------------
 // Three kinds of items flow through a pass: scan survivors (to the rank that owns their k-mer),
 // candidate keys (to the rank that compares them), hit keys (to the rank that owns their A entry).
-// The list of a rank has one SEGMENT per source rank: source s appends to its own segment of
-// every destination's list, reserving room with atomics on counters in ITS OWN memory, and
-// publishes the counts with its "phase done" signal (k6_exchange.cuh).  No remote atomic, no
-// separate routing pass: the producing kernel stores straight into peer memory over NVLink while
-// it computes.  N = 1: one segment, one counter.
+// The list of a rank has one SEGMENT per source rank.  A source keeps the segments it produces -- one
+// per destination -- in ITS OWN arena (its outbox), reserves room with atomics on counters in its own
+// memory and publishes the counts with its "phase done" signal (k6_exchange.cuh); the destination
+// reads the segment in place over NVLink (SegList below).  No remote atomic, no remote store, no
+// separate routing pass.  N = 1: one segment, one counter.
 //
 // Producer side.  Items are staged per warp in shared memory (WBUF items, appended
 // warp-synchronously) and flushed with one atomic per (flush, destination), in runs of
@@ -251,7 +251,7 @@ constexpr int WBUF = 256;  // items per warp
 
 template <class T>
 struct Sink {
-    T* seg[MAX_RANKS];          // my segment in the list of every rank (peer-mapped for r != me)
+    T* seg[MAX_RANKS];          // the segment (in this rank's arena) of the items for rank r
     uint64_t cap[MAX_RANKS];    // its capacity
     unsigned long long* cnt;    // [nr] items appended per destination (may exceed cap: overflow is detected by the receiver)
     uint32_t nr;
@@ -328,14 +328,25 @@ __device__ __forceinline__ void wbuf_push(T* buf, uint32_t& n, const Sink<T>& S,
     __syncwarp();
 }
 
-// Consumer side: the list as the concatenation of its segments.
+// Consumer side: the list as the concatenation of its segments.  Segment s holds the items source
+// rank s produced for THIS rank and lives in s's arena (its outbox): the consumer reads it in place,
+// through the peer mapping when s is another GPU -- a PULL.  (Round 2 first pushed the items from
+// the producing kernels into the consumer's memory: with 3/4 of the items remote at 4 GPUs the filter
+// pass took 0.38 ms instead of 0.13, its short per-destination runs of 16-byte stores competing with
+// the bulk copies of the packed reads on the same links; streaming reads by a whole grid do not
+// have that problem, and the producers run at their single-GPU speed.)
 template <class T>
 struct SegList {
-    const T* base;                 // nr segments of seg_cap items each
-    const unsigned long long* n;   // [nr] items in every segment (counters; may exceed seg_cap on overflow)
-    uint64_t seg_cap;
+    const T* seg[MAX_RANKS];       // segment s (peer-mapped for s != me)
+    uint64_t cap[MAX_RANKS];       // its capacity (the source's)
+    const unsigned long long* n;   // [nr] items in every segment (counters; may exceed the capacity on overflow)
     uint32_t nr;
 };
+template <class T>
+__device__ __forceinline__ uint64_t seg_count(const SegList<T>& L, uint32_t s) {
+    const unsigned long long c = L.n[s];
+    return c < L.cap[s] ? c : L.cap[s];
+}
 // pre[s] = logical index of the first item of segment s, pre[nr] = total (block-shared table)
 template <class T>
 __device__ __forceinline__ void seg_prefix(const SegList<T>& L, unsigned long long* s_pre) {
@@ -343,19 +354,18 @@ __device__ __forceinline__ void seg_prefix(const SegList<T>& L, unsigned long lo
         unsigned long long acc = 0;
         for (uint32_t s = 0; s < L.nr; ++s) {
             s_pre[s] = acc;
-            const unsigned long long c = L.n[s];
-            acc += c < L.seg_cap ? c : L.seg_cap;
+            acc += seg_count(L, s);
         }
         s_pre[L.nr] = acc;
     }
     __syncthreads();
 }
-// physical index (into base) of logical item i < pre[nr]
+// logical item i < pre[nr]
 template <class T>
-__device__ __forceinline__ uint64_t seg_phys(const SegList<T>& L, const unsigned long long* s_pre, uint64_t i) {
+__device__ __forceinline__ T seg_item(const SegList<T>& L, const unsigned long long* s_pre, uint64_t i) {
     uint32_t s = 0;
     while (s + 1 < L.nr && i >= s_pre[s + 1]) ++s;
-    return (uint64_t)s * L.seg_cap + (i - s_pre[s]);
+    return L.seg[s][i - s_pre[s]];
 }
 
 }  // namespace ovl

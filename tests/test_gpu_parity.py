@@ -432,6 +432,31 @@ def test_bucket_path_matches_serial_and_nonmirror_variants(ov):
         ov.set_option("mirror", 1)
 
 
+def test_tuning_options_do_not_change_rows(ov):
+    """Kernel variants behind ovl_set_option: bulk-async filter ring, candidate grouping before the
+    verifier (the multi-GPU default), K2 / K1 grid sizes."""
+    from phasm_b200 import synth
+    sh = synth.CONFIGS[2].scaled(0.02)
+    buf, off, names = synth.generate(sh)
+    reads = helpers.reads_of(buf, off, names)
+    base = run_reads_idx(ov, reads, sh.min_length)
+    assert len(base) > 1000
+    for opt, val, back in (("scan_bulk", 1, 0), ("group_cands", 1, -1), ("k2_blocks_per_sm", 2, 0),
+                           ("pack_blocks_per_sm", 5, 16)):
+        ov.set_option(opt, val)
+        try:
+            assert np.array_equal(run_reads_idx(ov, reads, sh.min_length), base), opt
+        finally:
+            ov.set_option(opt, back)
+    ov.set_option("anchor_stride", 64)
+    ov.set_option("scan_bulk", 1)
+    try:
+        assert np.array_equal(run_reads_idx(ov, reads, sh.min_length), base), "bulk stride 64"
+    finally:
+        ov.set_option("anchor_stride", 0)
+        ov.set_option("scan_bulk", 0)
+
+
 def test_config1_full_equals_the_reference_digest(ov):
     """BASELINE config 1 IN FULL (200 Mbases, 40 000 entries, -l 1000) against the UNMODIFIED reference:
     tests/golden/config1_full.json holds the row count and the sha256 of the sorted rows of the compiled
