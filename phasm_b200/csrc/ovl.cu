@@ -92,7 +92,7 @@ constexpr int H_STEP = H_SEGN + ovl::L_COUNT * ovl::MAX_RANKS;                 /
 constexpr int H_WORDS = H_STEP + 1;
 
 // byte offsets of the pieces of an arena (the header sits at 0); published to the peers
-constexpr int PUSH_STREAMS = 4;
+constexpr int PUSH_STREAMS = 8;
 
 struct ArenaLayout {
     uint64_t bytes;
@@ -119,6 +119,7 @@ struct ovl_ctx {
     cudaEvent_t ev[E_COUNT] = {};
     cudaEvent_t ev_pack = nullptr, ev_k0 = nullptr, ev_prel = nullptr, ev_k2 = nullptr, ev_push = nullptr, ev_sig = nullptr;
     cudaEvent_t ev_chunk[MAX_CHUNKS] = {};
+    cudaEvent_t ev_kp[MAX_CHUNKS] = {};  // K1 piece i has been packed (N > 1: its forward granules may travel)
     cudaEvent_t ev_t0 = nullptr, ev_t1 = nullptr;  // ovl_timer_*
     cudaEvent_t ev_dbg[12] = {};                    // OVL_DEBUG=1: time line of the side streams
     int debug = 0;
@@ -831,7 +832,22 @@ int run_pass(ovl_ctx* c, uint32_t min_length, bool chunked) {
         CK(cudaStreamWaitEvent(sk, c->ev_k0, 0));
 
         // ---- K1 (+ the prefix table K2 needs), whole or piece by piece under the upload ----------
-        const int n_chunks = chunked ? std::max(1, std::min(c->opt_chunks, MAX_CHUNKS)) : 1;
+        // resident reads on N > 1 GPUs: K1 in 4 pieces, so that the forward granules of a piece start
+        // travelling to the peers while the next piece is packed
+        const int n_chunks = chunked ? std::max(1, std::min(c->opt_chunks, MAX_CHUNKS)) : (nr > 1 ? 4 : 1);
+        uint32_t piece_e[MAX_CHUNKS + 1];  // entry boundaries of the pieces
+        piece_e[0] = c->e_lo;
+        if (!chunked && n_local) {
+            // the prefix table of ALL local entries on the main stream AHEAD of K1 -- it is what K2 (and, on
+            // N GPUs, every peer's K2) waits for: 13 us of work that took until +0.08..0.14 ms when it had to
+            // find SM slots beside the persistent K1 grid
+            k2_prefix_ascii<<<(n_local + 127) / 128, 128, 0, st>>>(
+                c->d_ascii.as<uint8_t>(), c->d_src.as<uint64_t>(), c->d_len.as<uint32_t>(), c->d_flags.as<uint8_t>(),
+                d_pre, c->e_lo, c->e_hi);
+            ++launches;
+            CK(cudaEventRecord(c->ev_prel, st));
+            CK(cudaStreamWaitEvent(sk, c->ev_prel, 0));
+        }
         PackParams K;
         K.ascii = c->d_ascii.as<uint8_t>();
         K.src = c->d_src.as<uint64_t>();
@@ -859,16 +875,11 @@ int run_pass(ovl_ctx* c, uint32_t min_length, bool chunked) {
                 CK(cudaStreamWaitEvent(sk, c->ev_chunk[ch], 0));
             }
             if (e_next > e_prev) {
-                // chunked: on K2's stream, beside this piece's K1.  Resident reads: on the main stream AHEAD of
-                // K1 -- the prefix table is what K2 (and, on N GPUs, every peer's K2) waits for, 13 us of work
-                // that took until +0.08..0.14 ms when it had to find SM slots beside the persistent K1 grid
-                k2_prefix_ascii<<<(e_next - e_prev + 127) / 128, 128, 0, chunked ? sk : st>>>(
-                    c->d_ascii.as<uint8_t>(), c->d_src.as<uint64_t>(), c->d_len.as<uint32_t>(), c->d_flags.as<uint8_t>(),
-                    d_pre, e_prev, e_next);
-                ++launches;
-                if (!chunked) {
-                    CK(cudaEventRecord(c->ev_prel, st));
-                    CK(cudaStreamWaitEvent(sk, c->ev_prel, 0));
+                if (chunked) {  // on K2's stream, beside this piece's K1
+                    k2_prefix_ascii<<<(e_next - e_prev + 127) / 128, 128, 0, sk>>>(
+                        c->d_ascii.as<uint8_t>(), c->d_src.as<uint64_t>(), c->d_len.as<uint32_t>(), c->d_flags.as<uint8_t>(),
+                        d_pre, e_prev, e_next);
+                    ++launches;
                 }
                 const uint32_t t_lo = c->tile0[e_prev], t_hi = c->tile0[e_next];
                 if (t_hi > t_lo) {
@@ -882,6 +893,8 @@ int run_pass(ovl_ctx* c, uint32_t min_length, bool chunked) {
                 CK(cudaGetLastError());
             }
             e_prev = e_next;
+            piece_e[ch + 1] = e_next;
+            if (nr > 1) CK(cudaEventRecord(c->ev_kp[ch], st));
         }
         if (chunked) {
             CK(cudaEventRecord(c->ev[E_H2D1], c->st_h2d));
@@ -908,32 +921,37 @@ int run_pass(ovl_ctx* c, uint32_t min_length, bool chunked) {
             // bulk: my slice of the forward region to the ranks that compare against my reads (half
             // of the peers), in ring order (at any moment a rank receives from one sender per stream)
             // and in pieces over several streams so that more than one copy engine drives NVLink
-            const uint64_t fwd_bytes = (uint64_t)(R.g_end[0] - R.g_begin[0]) * 16;
             int dst[MAX_RANKS], nd = 0;
             for (int j = 1; j < nr; ++j) {
                 const int r = (me - j + nr) % nr;
                 if (needs_reads_of(nr, r, me)) dst[nd++] = r;
             }
-            const int pieces = nd ? std::max(1, PUSH_STREAMS / nd) : 1;
-            for (int i = 0; i < PUSH_STREAMS; ++i) CK(cudaStreamWaitEvent(c->st_pushv[i], c->ev_pack, 0));
+            // piece q = the forward granules of K1 piece q (twins stay with their forward entry, so a piece
+            // is a contiguous granule range of the forward region); it leaves as soon as it is packed
+            auto fwd_gran = [&](uint32_t e) -> uint64_t { return e < c->e_hi ? (uint64_t)c->gran0[e] : (uint64_t)R.g_end[0]; };
+            // every destination has its own group of streams (so its copies never queue behind another
+            // destination's), every piece is split over the streams of the group (several copy engines
+            // per destination), and the group's first stream signals when all of them have drained
+            const int spd = nd ? std::max(1, PUSH_STREAMS / nd) : 1;
             for (int i = 0; i < nd; ++i) {
                 const int r = dst[i];
-                const uint64_t gran = fwd_bytes / 16;
-                cudaStream_t last = nullptr;
-                for (int q = 0; q < pieces; ++q) {
-                    const uint64_t g0 = gran * q / pieces, g1 = gran * (q + 1) / pieces;
-                    cudaStream_t sq = c->st_pushv[(i * pieces + q) % PUSH_STREAMS];
-                    if (g1 > g0)
-                        CK(cudaMemcpyAsync(at<uint8_t>(c->peer_base[r], c->peer_lay[r].off_packed + ((uint64_t)R.g_begin[0] + g0) * 16),
-                                           A + L.off_packed + ((uint64_t)R.g_begin[0] + g0) * 16, (g1 - g0) * 16, cudaMemcpyDefault, sq));
-                    if (q + 1 < pieces) {
-                        CK(cudaEventRecord(c->ev_piece[q], sq));
-                    } else {
-                        last = sq;
+                for (int q = 0; q < n_chunks; ++q) {
+                    const uint64_t g0 = fwd_gran(piece_e[q]), g1 = fwd_gran(piece_e[q + 1]);
+                    for (int t = 0; t < spd; ++t) {
+                        cudaStream_t sq = c->st_pushv[(i * spd + t) % PUSH_STREAMS];
+                        CK(cudaStreamWaitEvent(sq, c->ev_kp[q], 0));
+                        const uint64_t h0 = g0 + (g1 - g0) * t / spd, h1 = g0 + (g1 - g0) * (t + 1) / spd;
+                        if (h1 > h0)
+                            CK(cudaMemcpyAsync(at<uint8_t>(c->peer_base[r], c->peer_lay[r].off_packed + h0 * 16),
+                                               A + L.off_packed + h0 * 16, (h1 - h0) * 16, cudaMemcpyDefault, sq));
                     }
                 }
-                for (int q = 0; q + 1 < pieces; ++q) CK(cudaStreamWaitEvent(last, c->ev_piece[q], 0));
-                OVL_TRY(signal_copy(c, r, F_FWD, last));
+                cudaStream_t first = c->st_pushv[(i * spd) % PUSH_STREAMS];
+                for (int t = 1; t < spd; ++t) {
+                    CK(cudaEventRecord(c->ev_piece[t], c->st_pushv[(i * spd + t) % PUSH_STREAMS]));
+                    CK(cudaStreamWaitEvent(first, c->ev_piece[t], 0));
+                }
+                OVL_TRY(signal_copy(c, r, F_FWD, first));
             }
             for (int i = 1; i < PUSH_STREAMS; ++i) {  // ev_push = every push stream drained
                 CK(cudaEventRecord(c->ev_piece[i], c->st_pushv[i]));
@@ -1165,6 +1183,7 @@ int run_pass(ovl_ctx* c, uint32_t min_length, bool chunked) {
                     launches += 2;
                     lib += 1;
                     CK(cudaGetLastError());
+                    if (c->debug) CK(cudaEventRecord(c->ev_dbg[7], st));
                     V.keys.seg[0] = c->d_cand.as<uint64_t>();
                     V.keys.n = reinterpret_cast<const unsigned long long*>(g_off + M);  // total = last element of the exclusive sum
                     V.keys.cap[0] = cand_room;
@@ -1372,11 +1391,11 @@ int run_pass(ovl_ctx* c, uint32_t min_length, bool chunked) {
         };
         const bool mg = c->nranks > 1;
         fprintf(stderr, "[ovl rank %d step %llu] +ms: pack_end %.3f | sk: pre_wait_end %.3f insert_end %.3f | sg: pre_pushed %.3f filt_pushed %.3f | "
-                        "sp: fwd_pushed %.3f | st: scan0 %.3f filter_end %.3f probes_in %.3f resolve_end %.3f cands_in(verify0) %.3f fwd_in %.3f sort0 %.3f "
+                        "sp: fwd_pushed %.3f | st: scan0 %.3f filter_end %.3f probes_in %.3f resolve_end %.3f cands_in(verify0) %.3f fwd_in %.3f grouped %.3f sort0 %.3f "
                         "hits_in %.3f emit0 %.3f end %.3f\n",
                 c->rank, (unsigned long long)c->step, rel(c->ev[E_ANCHOR0]), rel(c->ev_dbg[0]), rel(c->ev_dbg[1]),
                 mg ? rel(c->ev_dbg[2]) : -1.f, mg ? rel(c->ev_dbg[3]) : -1.f, mg ? rel(c->ev_dbg[4]) : -1.f, rel(c->ev[E_SCAN0]),
-                rel(c->ev_dbg[6]), mg ? rel(c->ev_dbg[5]) : -1.f, rel(c->ev_dbg[8]), rel(c->ev[E_VERIFY0]), mg ? rel(c->ev_dbg[9]) : -1.f,
+                rel(c->ev_dbg[6]), mg ? rel(c->ev_dbg[5]) : -1.f, rel(c->ev_dbg[8]), rel(c->ev[E_VERIFY0]), mg ? rel(c->ev_dbg[9]) : -1.f, mg ? rel(c->ev_dbg[7]) : -1.f,
                 rel(c->ev[E_SORT0]), mg ? rel(c->ev_dbg[10]) : -1.f, rel(c->ev[E_EMIT0]), rel(c->ev[E_END]));
     }
     S.ms_pack = ev_ms(c, E_PACK0, E_ANCHOR0);
@@ -1490,6 +1509,7 @@ int ovl_create(int device, ovl_ctx** out) {
         cudaEvent_t* plain[] = {&x->ev_pack, &x->ev_k0, &x->ev_prel, &x->ev_k2, &x->ev_push, &x->ev_sig};
         for (cudaEvent_t* e2 : plain) CK(cudaEventCreateWithFlags(e2, cudaEventDisableTiming));
         for (int i = 0; i < MAX_CHUNKS; ++i) CK(cudaEventCreateWithFlags(&x->ev_chunk[i], cudaEventDisableTiming));
+        for (int i = 0; i < MAX_CHUNKS; ++i) CK(cudaEventCreateWithFlags(&x->ev_kp[i], cudaEventDisableTiming));
         for (int i = 0; i < E_COUNT; ++i) CK(cudaEventCreate(&x->ev[i]));
         CK(cudaEventCreate(&x->ev_t0));
         CK(cudaEventCreate(&x->ev_t1));
@@ -1546,8 +1566,10 @@ void ovl_destroy(ovl_ctx* c) {
     if (c->h_ctr) cudaFreeHost(c->h_ctr);
     for (int i = 0; i < E_COUNT; ++i)
         if (c->ev[i]) cudaEventDestroy(c->ev[i]);
-    for (int i = 0; i < MAX_CHUNKS; ++i)
+    for (int i = 0; i < MAX_CHUNKS; ++i) {
         if (c->ev_chunk[i]) cudaEventDestroy(c->ev_chunk[i]);
+        if (c->ev_kp[i]) cudaEventDestroy(c->ev_kp[i]);
+    }
     cudaEvent_t evs[] = {c->ev_pack, c->ev_k0, c->ev_prel, c->ev_k2, c->ev_push, c->ev_sig, c->ev_t0, c->ev_t1,
                          c->ev_dbg[0], c->ev_dbg[1], c->ev_dbg[2], c->ev_dbg[3], c->ev_dbg[4], c->ev_dbg[5], c->ev_dbg[6], c->ev_dbg[7],
                          c->ev_dbg[8], c->ev_dbg[9], c->ev_dbg[10], c->ev_dbg[11]};
