@@ -174,6 +174,22 @@ def cpu_reference_run(shape, sample_bases: int, repeats: int = 1):
     }
 
 
+def recorded_full_reference():
+    """The compiled reference's one recorded run on the FULL bench workload (build host, one core):
+    tests/golden/config<k>_full.json, written by tests/golden/make_config1_full.py.  Not a live
+    measurement of this run -- reported beside the live sample so that an equal-work figure exists."""
+    p = os.path.join(ROOT, "tests", "golden", "config%d_full.json" % CONFIG_ID)
+    try:
+        with open(p) as f:
+            g = json.load(f)
+        return {"seconds": g["t0_overlaps_seconds"], "gbases_per_s": g["t0_gbases_per_s"],
+                "overlaps_per_s": g["t0_overlaps_per_s"], "rows": g["t0"]["rows"], "peak_rss_gb": g["t0_peak_rss_gb"],
+                "forward_bases": g["forward_bases"], "host_cores": g["host"]["cores"], "cores_used": 1,
+                "measured_on": "build host (not this box), recorded once", "source": os.path.relpath(p, ROOT)}
+    except Exception:   # noqa: BLE001
+        return None
+
+
 def run_reference(args):
     rank = int(os.environ.get("RANK", "0"))
     if rank != 0:
@@ -204,6 +220,7 @@ def run_reference(args):
         "cpu_baseline": {k: r[k] for k in ("value", "unit", "cores", "kind", "sample", "host_cores")},
         "e2e": {"value": r["value"], "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "gpu_launches": 0,
+        "reference_full_workload_recorded": recorded_full_reference() if args.gpus == 1 else None,
     }
     print(json.dumps(line), flush=True)
     return 0
@@ -471,6 +488,8 @@ def run_b200(args):
             cb = cpu_reference_run(shape, args.cpu_sample, 1)
             line["cpu_baseline"] = {k: cb[k] for k in ("value", "unit", "cores", "kind", "sample",
                                                        "host_cores", "overlaps_per_s")}
+            # beside the live sample: the reference's one recorded run on this very workload in full
+            line["cpu_baseline"]["full_workload_recorded"] = recorded_full_reference()
         print(json.dumps(line), flush=True)
     ok = 1 if (parity is None or parity.get("bit_exact", True)) else 0
     ov.close()

@@ -133,6 +133,44 @@ __global__ void __launch_bounds__(256) k_push(const uint4* __restrict__ src, con
     __threadfence_system();
 }
 
+// The item exchange proper: stream the segments the other ranks produced for this rank out of
+// their arenas into this rank's inbox, with the whole grid and four independent 16-byte loads per
+// thread in flight (measured on this box, tools/p2p_bw.cu, profiles/r02o_p2p_bandwidth.txt: a grid
+// of >= 592 blocks pulls 740 GB/s over NVLink, a copy engine 760 GB/s -- but a copy engine needs
+// the size on the host, and the counts only exist on the device).  The consumers then read local
+// memory: a consumer that streamed the peer segments itself, one record ahead and with its own work
+// between the loads, moved them at 150 GB/s (k3_resolve at 4 GPUs: 0.48 ms instead of 0.09).
+struct PullParams {
+    const uint4* src[MAX_RANKS];     // segment of source s for this rank, in s's arena
+    uint4* dst[MAX_RANKS];           // slot s of this rank's inbox
+    uint64_t cap[MAX_RANKS];         // items that fit (min of the two capacities)
+    const unsigned long long* n;     // [nr] item counts (delivered with the phase signal)
+    uint32_t item_bytes;             // 8 or 16
+    uint32_t nr, me;
+};
+
+__global__ void __launch_bounds__(256) k_pull(const PullParams P) {
+    const uint64_t tid = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x, nth = (uint64_t)gridDim.x * blockDim.x;
+    for (uint32_t j = 1; j < P.nr; ++j) {
+        const uint32_t s = (P.me + j) % P.nr;  // ring order: at any moment the ranks read from different peers
+        const unsigned long long n_all = P.n[s];
+        const uint64_t n = n_all < P.cap[s] ? n_all : P.cap[s];
+        const uint64_t n16 = (n * P.item_bytes + 15) / 16;
+        const uint4* __restrict__ src = P.src[s];
+        uint4* __restrict__ dst = P.dst[s];
+        uint64_t i = tid;
+        for (; i + 3 * nth < n16; i += 4 * nth) {
+            const uint4 v0 = ldg_stream(src + i), v1 = ldg_stream(src + i + nth), v2 = ldg_stream(src + i + 2 * nth),
+                        v3 = ldg_stream(src + i + 3 * nth);
+            dst[i] = v0;
+            dst[i + nth] = v1;
+            dst[i + 2 * nth] = v2;
+            dst[i + 3 * nth] = v3;
+        }
+        for (; i < n16; i += nth) dst[i] = ldg_stream(src + i);
+    }
+}
+
 // The status vector of this rank, from the device counters (one thread).  Every buffer that
 // somebody appends to without a size check on the host is compared with its capacity HERE, on the
 // receiving side: a fill above 1024/1024 raises STF_OVERFLOW.  Every rank reads every rank's vector

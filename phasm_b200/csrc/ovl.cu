@@ -97,6 +97,7 @@ constexpr int PUSH_STREAMS = 8;
 struct ArenaLayout {
     uint64_t bytes;
     uint64_t off_pre, off_packed, off_filter, off_table, off_next, off_scan, off_cand, off_inbox, off_rows;
+    uint64_t off_in[ovl::L_COUNT];   // N > 1: where this rank pulls the other ranks' segments to (one slot per source)
     uint64_t seg_cap[ovl::L_COUNT];  // items per SEGMENT (one segment per source rank) of the probe / verify / hit list
     uint64_t rows_cap;               // rows (rank 0 of a multi-GPU job: room for the rows of all ranks, for the pull)
 };
@@ -400,7 +401,8 @@ int connect_arena(ovl_ctx* c, bool mirror, uint64_t scan_cap) {
     // the three item lists: one segment per source rank.  Items spread about evenly over the
     // destinations (k-mer hash, placement rule, base-balanced A ranges): a segment gets twice its
     // even share, the receiver checks the counts and the pass is repeated larger if one overflows
-    auto seg = [&](uint64_t total) { return nr > 1 ? 2 * total / nr + 64 : total; };
+    // (even: k_pull moves the 8-byte keys in 16-byte units)
+    auto seg = [&](uint64_t total) { return nr > 1 ? ((2 * total / nr + 64 + 1) & ~1ull) : total; };
     const uint64_t own_rows = (uint64_t)nr * seg(hit_cap);  // a rank emits at most one row per hit key in its list
     uint64_t rows_total = own_rows;
     if (nr > 1) {
@@ -434,6 +436,11 @@ int connect_arena(ovl_ctx* c, bool mirror, uint64_t scan_cap) {
     L.off_scan = take((uint64_t)nr * L.seg_cap[L_SCAN] * 16);
     L.off_cand = take((uint64_t)nr * L.seg_cap[L_CAND] * 8);
     L.off_inbox = take((uint64_t)nr * L.seg_cap[L_HITS] * 8);
+    if (nr > 1) {
+        L.off_in[L_SCAN] = take((uint64_t)nr * L.seg_cap[L_SCAN] * 16);
+        L.off_in[L_CAND] = take((uint64_t)nr * L.seg_cap[L_CAND] * 8);
+        L.off_in[L_HITS] = take((uint64_t)nr * L.seg_cap[L_HITS] * 8);
+    }
     L.rows_cap = rows_total;
     L.off_rows = take(rows_total * sizeof(Row));
     L.bytes = off;
@@ -803,8 +810,8 @@ int run_pass(ovl_ctx* c, uint32_t min_length, bool chunked) {
         Row* d_rows = at<Row>(A, L.off_rows);
         uint64_t hits_room = 0, cand_room = 0;  // hit keys / candidate keys this rank can receive (= rows it can emit / keys it verifies)
         for (int s2 = 0; s2 < nr; ++s2) {
-            hits_room += c->peer_lay[s2].seg_cap[L_HITS];
-            cand_room += c->peer_lay[s2].seg_cap[L_CAND];
+            hits_room += std::min(L.seg_cap[L_HITS], c->peer_lay[s2].seg_cap[L_HITS]);
+            cand_room += std::min(L.seg_cap[L_CAND], c->peer_lay[s2].seg_cap[L_CAND]);
         }
         OVL_TRY(dev_ensure(c, c->d_cand, std::max(hits_room, cand_room) * 8, false));  // the candidate keys grouped by A entry (N > 1), then the bucketed / sorted hit keys
         OVL_TRY(dev_ensure(c, c->d_cnt, cand_room * 4, false));   // survivor list of the verifier's head
@@ -932,7 +939,10 @@ int run_pass(ovl_ctx* c, uint32_t min_length, bool chunked) {
             // every destination has its own group of streams (so its copies never queue behind another
             // destination's), every piece is split over the streams of the group (several copy engines
             // per destination), and the group's first stream signals when all of them have drained
-            const int spd = nd ? std::max(1, PUSH_STREAMS / nd) : 1;
+            // (measured on this box, profiles/r02o_p2p_bandwidth.txt: ONE stream drives a copy engine at
+            // 760 GB/s in each direction at once; splitting over 8 streams gives 650 GB/s, and the 32 small
+            // copies of the first form of this loop ran at ~260 GB/s)
+            const int spd = 1;
             for (int i = 0; i < nd; ++i) {
                 const int r = dst[i];
                 for (int q = 0; q < n_chunks; ++q) {
@@ -1044,10 +1054,13 @@ int run_pass(ovl_ctx* c, uint32_t min_length, bool chunked) {
         auto fill_list = [&](auto& list, int kind) {
             using T = std::remove_const_t<std::remove_pointer_t<std::remove_reference_t<decltype(list.seg[0])>>>;
             for (int s2 = 0; s2 < nr; ++s2) {
-                const ArenaLayout& PL = c->peer_lay[s2];
-                const uint64_t o = kind == L_SCAN ? PL.off_scan : kind == L_CAND ? PL.off_cand : PL.off_inbox;
-                list.seg[s2] = at<T>(c->peer_base[s2], o + (uint64_t)me * PL.seg_cap[kind] * item_size[kind]);
-                list.cap[s2] = PL.seg_cap[kind];
+                if (s2 == me) {  // my own segment for myself: in place
+                    list.seg[s2] = at<T>(A, off_list[kind] + (uint64_t)me * L.seg_cap[kind] * item_size[kind]);
+                    list.cap[s2] = L.seg_cap[kind];
+                } else {         // slot s2 of my inbox, filled by k_pull
+                    list.seg[s2] = at<T>(A, L.off_in[kind] + (uint64_t)s2 * L.seg_cap[kind] * item_size[kind]);
+                    list.cap[s2] = std::min(L.seg_cap[kind], c->peer_lay[s2].seg_cap[kind]);
+                }
             }
             list.n = H->seg_n[kind];
             list.nr = (uint32_t)nr;
@@ -1059,7 +1072,24 @@ int run_pass(ovl_ctx* c, uint32_t min_length, bool chunked) {
                                               reinterpret_cast<const unsigned long long*>(ctr + C_SEND + kind * MAX_RANKS), c->step);
             ++launches;
             CK(cudaGetLastError());
-            return wait_flags(c, flag, st, &launches);
+            OVL_TRY(wait_flags(c, flag, st, &launches));
+            // pull the segments the others produced for me into my inbox
+            PullParams PP{};
+            PP.nr = (uint32_t)nr;
+            PP.me = (uint32_t)me;
+            PP.item_bytes = (uint32_t)item_size[kind];
+            PP.n = H->seg_n[kind];
+            for (int s2 = 0; s2 < nr; ++s2) {
+                const ArenaLayout& PL = c->peer_lay[s2];
+                const uint64_t o = kind == L_SCAN ? PL.off_scan : kind == L_CAND ? PL.off_cand : PL.off_inbox;
+                PP.src[s2] = at<uint4>(c->peer_base[s2], o + (uint64_t)me * PL.seg_cap[kind] * item_size[kind]);
+                PP.dst[s2] = at<uint4>(A, L.off_in[kind] + (uint64_t)s2 * L.seg_cap[kind] * item_size[kind]);
+                PP.cap[s2] = std::min(L.seg_cap[kind], PL.seg_cap[kind]);
+            }
+            k_pull<<<(unsigned)(nsm * 6), 256, 0, st>>>(PP);
+            ++launches;
+            CK(cudaGetLastError());
+            return OVL_OK;
         };
 
         // ---- K3: scan the local A entries -----------------------------------------------------------
@@ -1275,7 +1305,7 @@ int run_pass(ovl_ctx* c, uint32_t min_length, bool chunked) {
             SP.abort_word = &H->abort;
             SP.seg_n = &H->seg_n[0][0];
             for (int kk = 0; kk < L_COUNT; ++kk)
-                for (int s2 = 0; s2 < nr; ++s2) SP.seg_cap[kk][s2] = c->peer_lay[s2].seg_cap[kk];
+                for (int s2 = 0; s2 < nr; ++s2) SP.seg_cap[kk][s2] = std::min(L.seg_cap[kk], c->peer_lay[s2].seg_cap[kk]);
             SP.nr = (uint32_t)nr;
             SP.n_surv = reinterpret_cast<const unsigned long long*>(ctr + C_NSURV);
             SP.cap_surv = cand_room;
