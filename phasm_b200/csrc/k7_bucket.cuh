@@ -1,7 +1,7 @@
 // k7_bucket.cuh -- ordering of the verified hit keys and row emission without a host round trip.
 //
 // The hit keys [a | b | p | flags] have to be ordered by (a, b, p, flags) before the
-// select-longest rule of k5_emit.cuh can run (R1/R2, /root/reference/src/overlapper.cpp:64-115).
+// select-longest rule (key_rows_prev below) can run (R1/R2, /root/reference/src/overlapper.cpp:64-115).
 // A device-wide radix sort does that in 6 passes of a library kernel and needs the hit count on
 // the host first.  The keys are far from random, though: an entry `a` owns a few dozen hits, so
 //
