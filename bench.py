@@ -502,6 +502,16 @@ def run_b200(args):
     return 0 if ok else 3
 
 
+def full_rows_digest(rows) -> str:
+    """sha256 of the rows sorted by (a, b, astart, aend, bend), as little-endian uint32 -- the digest
+    tests/golden/make_config1_full.py records for the compiled reference (tests/helpers.py rows_digest)."""
+    import hashlib
+    arr = np.ascontiguousarray(rows, dtype=np.uint32).reshape(-1, 5)
+    if len(arr):
+        arr = np.ascontiguousarray(arr[np.lexsort((arr[:, 4], arr[:, 3], arr[:, 2], arr[:, 1], arr[:, 0]))])
+    return hashlib.sha256(arr.tobytes()).hexdigest()
+
+
 def check_parity(ov, shape, world, rank, n_rows, window_bases):
     """Driver-visible parity at every N, outside the timed region.  Rank 0
     fetches the gathered rows and checks (a) canonical order and an order-independent checksum,
@@ -562,11 +572,10 @@ def check_parity(ov, shape, world, rank, n_rows, window_bases):
     # the build host, tests/golden/make_config1_full.py) -- N = 1 only: at N GPUs the genome is N times as long
     gold_path = os.path.join(ROOT, "tests", "golden", "config%d_full.json" % CONFIG_ID)
     if world == 1 and os.path.exists(gold_path):
-        import hashlib
         with open(gold_path) as f:
             gold = json.load(f)
         if gold.get("shape") == shape.name and gold.get("forward_bases") == shape.n_bases and "t0" in gold:
-            digest = hashlib.sha256(np.ascontiguousarray(rows, dtype=np.uint32).tobytes()).hexdigest() if in_order else None
+            digest = full_rows_digest(rows)
             res["reference_full"] = {"rows": gold["t0"]["rows"], "sha256_equal": digest == gold["t0"]["sha256"],
                                      "reference_seconds": gold.get("t0_overlaps_seconds"),
                                      "source": "tests/golden/config%d_full.json (oracle/_ref on the full workload)" % CONFIG_ID}

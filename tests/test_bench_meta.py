@@ -47,3 +47,24 @@ def test_reference_arm_nonzero_rank_exits_quietly():
     r = subprocess.run([sys.executable, os.path.join(ROOT, "bench.py"), "--impl", "reference", "--gpus", "2",
                         "--steps", "1", "--warmup", "0"], capture_output=True, text=True, env=env, timeout=120)
     assert r.returncode == 0 and r.stdout.strip() == ""
+
+
+def test_full_reference_digest_is_order_independent_and_matches_the_golden_helper():
+    """bench.py's whole-row-set check against the recorded full-size run of the compiled reference
+    (tests/golden/config<k>_full.json) uses the digest of tests/helpers.py::rows_digest."""
+    import numpy as np
+    sys.path.insert(0, ROOT)
+    import bench
+    rng = np.random.default_rng(3)
+    rows = rng.integers(0, 50, size=(5000, 5), dtype=np.uint32)
+    rows[100] = rows[7]                      # duplicate rows are part of the multiset
+    want = helpers.rows_digest(rows)["sha256"]
+    assert bench.full_rows_digest(rows) == want
+    assert bench.full_rows_digest(rows[rng.permutation(len(rows))]) == want
+    assert bench.full_rows_digest(rows[:0]) == helpers.rows_digest(rows[:0])["sha256"]
+    for k in (1, 2):
+        with open(os.path.join(ROOT, "tests", "golden", "config%d_full.json" % k)) as f:
+            g = json.load(f)
+        assert g["t2_equals_t0"] and g["t0"]["rows"] > 0 and len(g["t0"]["sha256"]) == 64
+    rec = bench.recorded_full_reference()
+    assert rec and rec["forward_bases"] == 414000000 and rec["cores_used"] == 1
