@@ -75,6 +75,27 @@ def test_last_alignment_of_a_pair_decides_the_attributes():
     assert edges == [(0, 2, 50, 50, 0), (3, 1, 50, 50, 1)] and n_nodes == 4
 
 
+def test_host_graph_object_reproduces_networkx_insertion_order(gold):
+    """phasm.assembly_graph.edges_to_digraph on the restatement's edge list: same nodes, edges,
+    attributes and g.edges() order as the reference's graph (the golden `rank` column)."""
+    networkx = pytest.importorskip("networkx")
+    from phasm.assembly_graph import edges_to_digraph
+    from phasm_b200.overlapper import EDGE_DTYPE
+    n = 0
+    for c in gold["aln"]:
+        edges, n_nodes = G.build_graph(c["alns"], c["lens"])
+        arr = np.array(edges, dtype=EDGE_DTYPE) if edges else np.zeros(0, dtype=EDGE_DTYPE)
+        ids = ["r%d%s" % (i // 2, "+-"[i % 2]) for i in range(len(c["lens"]))]
+        g = edges_to_digraph(arr, ids)
+        assert networkx.number_of_nodes(g) == c["graph"]["n_nodes"] and networkx.number_of_edges(g) == c["graph"]["n_edges"]
+        index = {name: i for i, name in enumerate(ids)}
+        got = sorted([index[u], index[v], d["weight"], d["overlap_len"], rank]
+                     for rank, (u, v, d) in enumerate(g.edges(data=True)))
+        assert got == c["graph"]["edges"]
+        n += 1
+    assert n == len(gold["aln"])
+
+
 # ---- device ------------------------------------------------------------------------------------
 @pytest.fixture(scope="module")
 def ov():
