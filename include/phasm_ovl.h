@@ -281,9 +281,9 @@ int ovl_gfa_edges(const ovl_gfa *g, const ovl_gfa_edge **edges, uint64_t *n_edge
  * bootstrap channel (libnccl is dlopen'ed on first use): ovl_comm_unique_id fills a 128-byte id on
  * rank 0, the caller ships it to the other ranks (a socket, torch.distributed, a file, ...) and
  * every rank calls ovl_comm_init.  The first pass then maps every rank's working arena into every
- * other rank (CUDA IPC); from there on all exchanges of a pass are device-side pushes over NVLink
- * into peer memory (phasm_b200/csrc/k6_exchange.cuh) -- no NCCL call and no host round trip inside
- * a pass.  Every rank calls ovl_overlaps_device / ovl_overlaps_local in step; an error or a
+ * other rank (CUDA IPC); from there on all exchanges of a pass happen on the device over NVLink
+ * (copy-engine pushes of the packed reads, grid-wide pulls of the item lists:
+ * phasm_b200/csrc/k6_exchange.cuh) -- no NCCL call and no host round trip inside a pass.  Every rank calls ovl_overlaps_device / ovl_overlaps_local in step; an error or a
  * capacity overflow on any rank is seen by all of them in the same pass (all raise / all repeat). */
 int ovl_comm_unique_id(uint8_t id_out[128]);
 int ovl_comm_init(ovl_ctx *ctx, const uint8_t id[128], int rank, int nranks);
