@@ -75,6 +75,69 @@ def test_last_alignment_of_a_pair_decides_the_attributes():
     assert edges == [(0, 2, 50, 50, 0), (3, 1, 50, 50, 1)] and n_nodes == 4
 
 
+@pytest.mark.skipif(not os.path.isdir("/root/reference/phasm"), reason="reference checkout not mounted")
+def test_restatement_against_the_live_reference_function():
+    """oracle/graph.py against build_assembly_graph itself (imported from /root/reference in a
+    subprocess, because its package is also called `phasm`), on fresh random alignments."""
+    import subprocess
+    import sys
+    import tempfile
+    rng = np.random.default_rng(20261105)
+    cases = []
+    for _ in range(60):
+        n_reads = int(rng.integers(2, 7))
+        lens = []
+        for _ in range(n_reads):
+            l = int(rng.integers(4, 40))
+            lens += [l, l]
+        alns = []
+        for _ in range(int(rng.integers(1, 30))):
+            a, b = (int(x) for x in rng.integers(0, 2 * n_reads, size=2))
+            if a >> 1 == b >> 1:
+                continue
+            a0 = int(rng.integers(0, lens[a])); a1 = int(rng.integers(a0 + 1, lens[a] + 1))
+            b0 = int(rng.integers(0, lens[b])); b1 = int(rng.integers(b0 + 1, lens[b] + 1))
+            alns.append([a, b, a0, a1, b0, b1])
+        cases.append({"lens": lens, "alns": alns})
+    script = r'''
+import json, sys
+sys.path.insert(0, "/root/reference")
+import networkx
+from phasm.alignments import LocalAlignment, OrientedRead, Read
+from phasm.assembly_graph import AssemblyGraph, build_assembly_graph
+def _add_edge(self, u, v, attr_dict=None, **attr):      # networkx 1.x call on networkx >= 2
+    d = dict(attr_dict or {}); d.update(attr)
+    return networkx.DiGraph.add_edge(self, u, v, **d)
+AssemblyGraph.add_edge = _add_edge
+out = []
+for c in json.load(open(sys.argv[1])):
+    ids = ["r%d%s" % (i // 2, "+-"[i % 2]) for i in range(len(c["lens"]))]
+    reads = [OrientedRead(Read(i[:-1], int(l)), i[-1]) for i, l in zip(ids, c["lens"])]
+    index = {i: k for k, i in enumerate(ids)}
+    g = build_assembly_graph(LocalAlignment(reads[a], reads[b], (s, e), (bs, be)) for a, b, s, e, bs, be in c["alns"])
+    out.append({"n_nodes": g.number_of_nodes(),
+                "edges": sorted([index[str(u)], index[str(v)], int(d["weight"]), int(d["overlap_len"]), r]
+                                for r, (u, v, d) in enumerate(g.edges(data=True)))})
+json.dump(out, open(sys.argv[2], "w"))
+'''
+    with tempfile.TemporaryDirectory() as td:
+        fin, fout, fs = os.path.join(td, "in.json"), os.path.join(td, "out.json"), os.path.join(td, "run.py")
+        with open(fin, "w") as f:
+            json.dump(cases, f)
+        with open(fs, "w") as f:
+            f.write(script)
+        r = subprocess.run([sys.executable, "-W", "ignore", fs, fin, fout], capture_output=True, text=True, timeout=300, cwd=td)
+        if r.returncode != 0 and "No module named" in r.stderr:
+            pytest.skip("reference dependencies missing: " + r.stderr.strip().splitlines()[-1])
+        assert r.returncode == 0, r.stderr[-2000:]
+        with open(fout) as f:
+            want = json.load(f)
+    for c, w in zip(cases, want):
+        edges, n_nodes = G.build_graph(c["alns"], c["lens"])
+        assert n_nodes == w["n_nodes"]
+        assert [list(e) for e in first_seq_to_rank(edges)] == w["edges"]
+
+
 def test_host_graph_object_reproduces_networkx_insertion_order(gold):
     """phasm.assembly_graph.edges_to_digraph on the restatement's edge list: same nodes, edges,
     attributes and g.edges() order as the reference's graph (the golden `rank` column)."""
