@@ -183,7 +183,7 @@ struct ovl_ctx {
     int opt_stride = 0;         // 0 = auto; else upper bound on the anchor stride (1 = dense scan)
     int opt_serial_verify = 0;  // 1: chunk-by-chunk early-exit verifier instead of head/tail
     int opt_mirror = 1;         // 1: strand-mirror halving when every entry has its twin
-    int opt_pack_bpsm = 16;     // K1 blocks per SM
+    int opt_pack_bpsm = 0;      // K1 blocks per SM; 0 = default: 8 on one GPU (pass 1.078 vs 1.101 ms with 16: profiles/r02i_sweep.jsonl), 16 on N > 1
     int opt_filter_kb = 8192;   // budget of the scan's bit filter (all slices), KiB
     int opt_group_cands = -1;   // group the candidate keys by A entry before K4: -1 = when N > 1, 0 / 1 = never / always
     int opt_k2_bpsm = 0;        // K2 blocks per SM (0 = one thread per key): fewer let it trickle beside K1
@@ -893,7 +893,8 @@ int run_pass(ovl_ctx* c, uint32_t min_length, bool chunked) {
                     K.t_begin = t_lo;
                     K.t_end = t_hi;
                     uint32_t blocks = (t_hi - t_lo + 7) / 8;
-                    if (blocks > (uint32_t)(nsm * c->opt_pack_bpsm)) blocks = (uint32_t)(nsm * c->opt_pack_bpsm);
+                    const int bpsm = c->opt_pack_bpsm > 0 ? c->opt_pack_bpsm : (nr == 1 ? 8 : 16);
+                    if (blocks > (uint32_t)(nsm * bpsm)) blocks = (uint32_t)(nsm * bpsm);
                     k1_pack<<<blocks, 256, 0, st>>>(K);
                     ++launches;
                 }
@@ -1757,7 +1758,7 @@ int ovl_set_option(ovl_ctx* c, const char* name, int64_t value) {
         return OVL_OK;
     }
     if (!strcmp(name, "pack_blocks_per_sm")) {
-        if (value < 1 || value > 32) return fail(c, OVL_E_ARG, "pack_blocks_per_sm must be in 1..32");
+        if (value < 0 || value > 32) return fail(c, OVL_E_ARG, "pack_blocks_per_sm must be in 0..32 (0 = default)");
         c->opt_pack_bpsm = (int)value;
         return OVL_OK;
     }
