@@ -473,7 +473,9 @@ def run_b200(args):
                     "overlaps_per_s": n_rows / t_e2e,
                     "ms_h2d": e2e_parts["ms_h2d"], "ms_device_after_upload": e2e_parts["ms_exposed"],
                     "ms_d2h": e2e_parts["ms_d2h"], "ms_device_incl_upload_wait": e2e_parts["ms_device"],
-                    "ms_host_other": ms_e2e - e2e_parts["ms_h2d"] - e2e_parts["ms_exposed"] - e2e_parts["ms_d2h"],
+                    # (parts: last step, each the max over the ranks -- on N > 1 they come from different
+                    #  ranks and need not add up to the wall time per step)
+                    "ms_host_other": max(0.0, ms_e2e - e2e_parts["ms_h2d"] - e2e_parts["ms_exposed"] - e2e_parts["ms_d2h"]),
                     "upload": "chunked: pinned host ASCII -> HBM in pieces, every piece packed (K1) and "
                               "prefix-tabled under the next piece's copy",
                     "call": ("ExactOverlapper.overlaps_arrays(l, copy=False) == ovl_overlaps: host ASCII in, rows "
