@@ -39,15 +39,22 @@ def main():
     ap.add_argument("--config", type=int, default=1)
     ap.add_argument("--scale", type=float, default=1.0)
     ap.add_argument("--out", default=os.path.join(ROOT, "tests", "golden", "config1_full.json"))
+    ap.add_argument("--window-bases", type=float, default=0.0,
+                    help="configs the reference cannot hold in memory: all reads of the FULL config that start in one "
+                         "genome window of about this many forward bases (synth.window_subsample, the restriction "
+                         "property of SURVEY.md 3.3) instead of the whole config")
     args = ap.parse_args()
     shape = synth.CONFIGS[args.config]
     if args.scale != 1.0:
         shape = shape.scaled(args.scale)
-    buf, off, names = synth.generate(shape)
+    if args.window_bases > 0:
+        buf, off, names, _ = synth.window_subsample(shape, int(args.window_bases))
+    else:
+        buf, off, names = synth.generate(shape)
     reads = [(n, buf[int(off[i]):int(off[i + 1])].tobytes().decode()) for i, n in enumerate(names)]
     ents = both_strand_entries(reads)
     index = {eid: i for i, (eid, _) in enumerate(ents)}
-    rec = {"shape": shape.name, "seed": shape.seed, "reads": len(reads), "entries": len(ents),
+    rec = {"shape": shape.name, "window_bases": int(args.window_bases), "seed": shape.seed, "reads": len(reads), "entries": len(ents),
            "forward_bases": int(off[-1]), "min_length": shape.min_length,
            "host": {"cores": os.cpu_count(), "threads_used": 1,
                     "tmpdir": os.environ.get("TMPDIR", "/tmp")},

@@ -108,3 +108,31 @@ def test_port_matches_compiled_reference_mid():
     want = ref.ref_overlaps(ents, sh.min_length)
     assert port_rows(ents, sh.min_length)[0] == want
     assert len(want) > 100
+
+
+@pytest.mark.parametrize("cfg", [3, 4, 5])
+def test_c_restatement_equals_the_reference_on_full_size_windows(cfg):
+    """T2 against the compiled reference's recorded rows on a ~100 Mbase genome window of the FULL
+    configs the reference cannot hold in memory (tests/golden/config<k>_window.json, made by
+    tests/golden/make_config1_full.py --window-bases 100e6: 10 min and ~8 GB of the reference each).
+    The restriction property makes this window the full-size parity statement for
+    configs 3-5; configs 1 and 2 are pinned in full (config{1,2}_full.json)."""
+    import json
+    import os
+    from phasm_b200 import synth
+    from oracle import port
+    from oracle.bruteforce import both_strand_entries
+    path = os.path.join(helpers.GOLDEN, "config%d_window.json" % cfg)
+    if not os.path.exists(path):
+        pytest.skip("no recorded reference run for config %d" % cfg)
+    with open(path) as f:
+        gold = json.load(f)
+    assert gold["t2_equals_t0"]
+    sh = synth.CONFIGS[cfg]
+    assert sh.name == gold["shape"]
+    buf, off, names, _ = synth.window_subsample(sh, int(gold["window_bases"]))
+    assert int(off[-1]) == gold["forward_bases"] and len(names) == gold["reads"]
+    reads = helpers.reads_of(buf, off, names)
+    ebuf, eoff = port.entries_to_buffer(both_strand_entries(reads))
+    want, _ = port.oracle_overlaps(ebuf, eoff, sh.min_length)
+    assert helpers.rows_digest(want) == gold["t0"]
