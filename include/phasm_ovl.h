@@ -219,6 +219,46 @@ typedef struct {
 int ovl_filter_rows(ovl_ctx *ctx, const ovl_filter_opts *opts, const ovl_row **rows, uint64_t *n_rows,
                     ovl_filter_stats *stats);
 
+/* ---- the same filter for callers that cannot allocate ------------------------------------------
+ * ovl_filter_rows_static has NO counterpart in the reference (its filters are Python objects over
+ * Python lists); it exists for hosts of this library that must not trigger a cudaMalloc at call
+ * time -- a pipeline whose memory pool owns the whole GPU, a latency-bound loop that cannot afford
+ * the device-wide synchronisation cudaMalloc / cudaFree imply, a process whose memory budget is
+ * fixed at load time.  ovl_filter_rows grows ctx-owned buffers on demand; this variant allocates
+ * nothing, ever: no cudaMalloc / cudaFree / host allocation, no ctx, no library primitive that needs
+ * temporary storage.  Its working memory is a fixed array inside the library image
+ * (OVL_STATIC_SCRATCH_BYTES of HBM on every GPU that loads the library, held until the process
+ * exits), which is why the job size is capped:
+ *     n_rows <= OVL_STATIC_MAX_ROWS and n_entries <= OVL_STATIC_MAX_ENTRIES, else OVL_E_LIMIT.
+ * The caller owns every buffer, all in DEVICE memory of `device`:
+ *     d_rows[n_rows]         in   rows in canonical order (as ovl_overlaps* returns them)
+ *     d_entry_len[n_entries] in   length of every entry (ovl_entry_length)
+ *     d_rows_out[n_rows]     out  kept rows, same order, the first d_counts->rows_kept are valid
+ *     d_counts               out  one ovl_static_counts
+ * `stream` is a cudaStream_t (NULL = the default stream).  The call only enqueues work and returns;
+ * results are ready when the stream reaches that point (synchronise or order a copy behind it).
+ * `opts` means what it means for ovl_filter_rows and the kept rows / counters are identical to that
+ * call's on the same rows.  A row naming an entry >= n_entries is dropped and counted in rows_bad.
+ * `err` (may be NULL) receives the message of a failing call; ovl_last_error is not involved.
+ * First call per GPU: looks up the device address of the scratch array (and loads the kernels), so
+ * make that call during set-up, before any stream capture.  Sharing: ONE scratch array per GPU for
+ * all threads and streams; every call clears what it needs, so calls ordered on one stream are safe
+ * back to back, but two calls that may overlap on the same GPU race and must be serialised by the caller. */
+#define OVL_STATIC_MAX_ROWS      (1u << 21)   /* 2 097 152 rows    */
+#define OVL_STATIC_MAX_ENTRIES   (1u << 19)   /*   524 288 entries */
+#define OVL_STATIC_SCRATCH_BYTES 6295808u     /* 6.0 MiB per GPU   */
+
+typedef struct {
+    uint64_t rows_kept;
+    uint64_t rows_contained;   /* as ovl_filter_stats (0 unless opts->contained_reads)        */
+    uint64_t entries_removed;  /* as ovl_filter_stats (0 unless opts->contained_reads)        */
+    uint64_t rows_bad;         /* rows dropped because a or b >= n_entries                    */
+} ovl_static_counts;
+
+int ovl_filter_rows_static(int device, void *stream, const ovl_row *d_rows, uint64_t n_rows,
+                           const uint32_t *d_entry_len, uint32_t n_entries, const ovl_filter_opts *opts,
+                           ovl_row *d_rows_out, ovl_static_counts *d_counts, char *err, size_t err_cap);
+
 /* ---- assembly-graph edge list on the device (graph part; OPTIONAL) ------
  * ovl_build_graph replaces build_assembly_graph (phasm/assembly_graph.py:136-179) as the reference's
  * `layout` stage feeds it (phasm/cli/assembler.py:93-100): the rows of the last ovl_overlaps* call

@@ -60,6 +60,14 @@ class OvlFilterStats(Structure):
         return {n: getattr(self, n) for n, _ in self._fields_ if n != "reserved0"}
 
 
+class OvlStaticCounts(Structure):
+    _fields_ = [(n, c_uint64) for n in ("rows_kept", "rows_contained", "entries_removed", "rows_bad")]
+
+
+OVL_STATIC_MAX_ROWS = 1 << 21
+OVL_STATIC_MAX_ENTRIES = 1 << 19
+
+
 class OvlEdge(Structure):
     _fields_ = [("u", c_uint32), ("v", c_uint32), ("edge_len", ctypes.c_int32), ("overlap_len", c_uint32),
                 ("first_seq", c_uint64)]
@@ -103,6 +111,8 @@ SIGNATURES = {
     "ovl_write_gfa": (c_int, [_P, c_int, c_int, POINTER(c_uint64)]),
     "ovl_filter_rows": (c_int, [_P, POINTER(OvlFilterOpts), POINTER(c_void_p), POINTER(c_uint64),
                                 POINTER(OvlFilterStats)]),
+    "ovl_filter_rows_static": (c_int, [c_int, c_void_p, c_void_p, c_uint64, c_void_p, c_uint32,
+                                       POINTER(OvlFilterOpts), c_void_p, c_void_p, c_char_p, c_size_t]),
     "ovl_build_graph": (c_int, [_P, c_int, POINTER(c_void_p), POINTER(c_uint64), POINTER(OvlGraphStats)]),
     "ovl_gfa_read": (c_int, [c_char_p, POINTER(_P)]),
     "ovl_gfa_free": (None, [_P]),
