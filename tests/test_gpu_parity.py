@@ -476,3 +476,27 @@ def test_config1_full_equals_the_reference_digest(ov):
     got = ov.overlaps_arrays(sh.min_length, copy=False)
     assert helpers.rows_digest(got) == gold["t0"]
     ov.clear()
+
+
+@pytest.mark.parametrize("cfg", [3, 4, 5])
+def test_config_window_equals_the_reference_digest(ov, cfg):
+    """A ~100 Mbase genome window of the FULL configs 3, 4 and 5 against the UNMODIFIED reference:
+    tests/golden/config<k>_window.json holds the row count and the sha256 of the sorted rows of the
+    compiled reference's run on exactly this input (about 10 min and 7-8 GB of one host core each;
+    tests/golden/make_config1_full.py --window-bases 100e6).  Config 4 is the repeat-rich one
+    (segmental duplications, -l 500: the candidate explosion case)."""
+    import json
+    import os
+    from phasm_b200 import synth
+    with open(os.path.join(helpers.GOLDEN, "config%d_window.json" % cfg)) as f:
+        gold = json.load(f)
+    sh = synth.CONFIGS[cfg]
+    assert sh.name == gold["shape"] and sh.seed == gold["seed"]
+    buf, off, names, _ = synth.window_subsample(sh, int(gold["window_bases"]))
+    assert int(off[-1]) == gold["forward_bases"] and len(names) == gold["reads"]
+    ov.clear()
+    ov.add_reads_bulk(buf, off, names)
+    got = ov.overlaps_arrays(sh.min_length, copy=False)
+    assert len(got) == gold["t0"]["rows"]
+    assert helpers.rows_digest(got) == gold["t0"]
+    ov.clear()
