@@ -303,7 +303,11 @@ extern "C" int ovl_filter_rows(ovl_ctx* c, const ovl_filter_opts* o, const ovl_r
     const uint64_t n = c->n_rows;
     const uint32_t M = (uint32_t)c->len.size();
     if (fs) fs->rows_in = n;
-    if (n == 0) return OVL_OK;
+    if (n == 0) {  // an empty pass has an empty, valid filter result (ovl_build_graph(use_filtered) -> empty graph)
+        c->n_frows = 0;
+        c->frows_valid = true;
+        return OVL_OK;
+    }
     if (n > 0x7fffffffull) return fail(c, OVL_E_LIMIT, "ovl_filter_rows: more than 2^31 rows (CUB item counts are int)");
     OVL_TRY(gather_rows_pull(c));  // multi-GPU, rank 0: the other ranks' rows are still in their HBM
     cudaStream_t st = c->st;

@@ -244,3 +244,17 @@ def test_device_graph_needs_a_filter_result_and_pairs(ov):
     if len(ov.overlaps_arrays(8)):
         with pytest.raises(ValueError):
             ov.build_graph(filtered=False)
+
+
+@pytest.mark.gpu
+def test_device_graph_of_a_pass_without_rows_is_empty(ov):
+    """No overlaps -> the reference's build_assembly_graph returns an empty graph
+    (phasm/assembly_graph.py:136-179 adds nothing); filter_rows + build_graph(filtered=True) must
+    not raise on that input."""
+    ov.clear()
+    ov.add_read("r0", "ACGTACGTACGTACGTACGT")
+    assert len(ov.overlaps_arrays(1000)) == 0
+    got, fst = ov.filter_rows()
+    assert got.shape == (0, 5) and fst["rows_kept"] == 0
+    edges, st = ov.build_graph(filtered=True)
+    assert len(edges) == 0 and st["rows_in"] == 0 and st["n_edges"] == 0 and st["n_nodes"] == 0
