@@ -182,6 +182,7 @@ struct StatusParams {
     const unsigned long long* flags;      // STF_* bits raised by kernels
     const unsigned long long* abort_word;
     const unsigned long long* seg_n;      // [L_COUNT][MAX_RANKS] of this rank's header
+    unsigned long long* seg_snap;         // [L_COUNT][MAX_RANKS] copy of seg_n for the host (taken before F_STATUS goes out)
     unsigned long long seg_cap[L_COUNT][MAX_RANKS];  // capacity of the segment of every source in every list
     uint32_t nr;
     const unsigned long long* n_surv;     // verifier: candidates alive after the head
@@ -198,7 +199,11 @@ __global__ void k9_status(const StatusParams P) {
         if (f > fill) fill = f;
     };
     for (int k = 0; k < L_COUNT; ++k)
-        for (uint32_t s = 0; s < P.nr; ++s) see(P.seg_n[k * MAX_RANKS + s], P.seg_cap[k][s]);
+        for (uint32_t s = 0; s < P.nr; ++s) {
+            const unsigned long long n = P.seg_n[k * MAX_RANKS + s];
+            P.seg_snap[k * MAX_RANKS + s] = n;
+            see(n, P.seg_cap[k][s]);
+        }
     see(*P.n_surv, P.cap_surv);
     see(*P.n_rows, P.cap_rows);
     unsigned long long fl = *P.flags | (*P.abort_word ? STF_TIMEOUT : 0ull);

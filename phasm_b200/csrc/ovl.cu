@@ -82,13 +82,16 @@ enum Ctr {
     C_FLAGS,   // STF_* bits raised by kernels
     C_NROWS,   // rows of this rank
     C_SEND,    // [L_COUNT][MAX_RANKS] items this rank appended to its segment of every rank's lists (N > 1)
-    C_COUNT = C_SEND + ovl::L_COUNT * ovl::MAX_RANKS
+    // [L_COUNT][MAX_RANKS] the inbound segment counts of THIS step, copied out of the arena header by
+    // k9_status before the status flag is published (a peer that has seen every flag may already be
+    // writing its next step's counts into the header: ADVICE r2)
+    C_SEGN = C_SEND + ovl::L_COUNT * ovl::MAX_RANKS,
+    C_COUNT = C_SEGN + ovl::L_COUNT * ovl::MAX_RANKS
 };
 
 // pinned host mirror read after the one synchronisation of a pass (64-bit words)
 constexpr int H_STATUS = C_COUNT;                                             // [MAX_RANKS][STATUS_WORDS]
-constexpr int H_SEGN = H_STATUS + ovl::MAX_RANKS * ovl::STATUS_WORDS;          // [L_COUNT][MAX_RANKS]
-constexpr int H_STEP = H_SEGN + ovl::L_COUNT * ovl::MAX_RANKS;                 // the step id (source of a H2D copy)
+constexpr int H_STEP = H_STATUS + ovl::MAX_RANKS * ovl::STATUS_WORDS;          // the step id (source of a H2D copy)
 constexpr int H_WORDS = H_STEP + 1;
 
 // byte offsets of the pieces of an arena (the header sits at 0); published to the peers
@@ -168,7 +171,7 @@ struct ovl_ctx {
     uint64_t step = 0;
 
     PinBuf h_frows, h_rows, h_gedges;
-    uint64_t* h_ctr = nullptr;   // pinned, H_WORDS words: counters | status of every rank | segment counts | step
+    uint64_t* h_ctr = nullptr;   // pinned, H_WORDS words: counters (incl. segment counts) | status of every rank | step
     uint64_t cand_cap = 0;       // candidate keys one pass may emit
     uint64_t min_cand_cap = 1ull << 20;
     uint64_t cand_per_entry = 96;  // first candidate capacity: this many keys per local entry
@@ -1305,6 +1308,7 @@ int run_pass(ovl_ctx* c, uint32_t min_length, bool chunked) {
             SP.flags = reinterpret_cast<const unsigned long long*>(ctr + C_FLAGS);
             SP.abort_word = &H->abort;
             SP.seg_n = &H->seg_n[0][0];
+            SP.seg_snap = reinterpret_cast<unsigned long long*>(ctr + C_SEGN);
             for (int kk = 0; kk < L_COUNT; ++kk)
                 for (int s2 = 0; s2 < nr; ++s2) SP.seg_cap[kk][s2] = std::min(L.seg_cap[kk], c->peer_lay[s2].seg_cap[kk]);
             SP.nr = (uint32_t)nr;
@@ -1322,10 +1326,9 @@ int run_pass(ovl_ctx* c, uint32_t min_length, bool chunked) {
         }
         CK(cudaGetLastError());
         uint64_t* h_status = c->h_ctr + H_STATUS;
-        uint64_t* h_segn = c->h_ctr + H_SEGN;
+        uint64_t* h_segn = c->h_ctr + C_SEGN;  // k9_status's snapshot, part of the counter block
         CK(cudaMemcpyAsync(c->h_ctr, ctr, C_COUNT * sizeof(uint64_t), cudaMemcpyDeviceToHost, st));
         CK(cudaMemcpyAsync(h_status, H->status, sizeof H->status, cudaMemcpyDeviceToHost, st));
-        CK(cudaMemcpyAsync(h_segn, H->seg_n, sizeof H->seg_n, cudaMemcpyDeviceToHost, st));
         CK(cudaStreamSynchronize(st));  // the one synchronisation of a pass
         CK(cudaStreamSynchronize(sk));
         if (chunked) {
@@ -1366,8 +1369,12 @@ int run_pass(ovl_ctx* c, uint32_t min_length, bool chunked) {
             // pass; the ranks that overflowed grow first (the arenas are re-published either way)
             if (attempt >= 3) return fail(c, OVL_E_LIMIT, "candidate buffers keep overflowing");
             ++S.retries;
-            // this rank's fullest buffer, in 1/1024 of its capacity: every capacity scales with cand_cap
-            const uint64_t fill = h_status[(size_t)me * STATUS_WORDS + ST_FILL];
+            // the fullest buffer of ANY rank, in 1/1024 of its capacity: every capacity scales with cand_cap,
+            // and a cross-rank segment is clipped at min(source's, receiver's) capacity while only the
+            // receiver sees it overflow -- so the source has to grow by the receiver's factor as well
+            // (a skewed overflow never converged when every rank grew by its own fill only)
+            uint64_t fill = 0;
+            for (int r = 0; r < nr; ++r) fill = std::max<uint64_t>(fill, h_status[(size_t)r * STATUS_WORDS + ST_FILL]);
             if (fill > 1024) {
                 c->cand_cap = (uint64_t)(1.07 * (double)c->cand_cap * (double)fill / 1024.0) + 1024;
                 c->min_cand_cap = std::max(c->min_cand_cap, c->cand_cap);
