@@ -34,10 +34,15 @@ def run_rank(rank: int, world: int, port: int, fasta: str, min_length: int, out=
         ov.comm_sync_ranges()
         ov.overlaps_device(min_length)
         st = ov.stats()
+        if rank == 0 and world > 1:
+            ov.comm_gather_rows_device()    # the peers' rows into rank 0's HBM: the last time a peer is touched
+        # nobody tears its arena down while a peer may still touch it.  The barrier sits BEFORE the
+        # file is written: formatting a large GFA2 file can outlast the rendezvous' socket timeout,
+        # and the workers have nothing left to contribute once their rows are on rank 0.
+        chan.barrier()
         if rank == 0 and out is not None:
             out.flush()
             ov.write_gfa(out.fileno(), True, True, True)
-        chan.barrier()      # nobody tears its arena down while a peer may still touch it
         return st
     finally:
         ov.close()
