@@ -25,6 +25,25 @@ from phasm_b200 import multi, synth  # noqa: E402
 from phasm_b200.overlapper import ExactOverlapper  # noqa: E402
 
 
+def skewed_reads(seed: int):
+    """A read set whose candidates pile up on the FIRST read range: its reads are made of copies of
+    one 300-base repeat R, and every other read starts with R, so every occurrence of R in the first
+    range is a candidate against every other read while the other ranges attract next to nothing
+    (the grow-and-repeat route when only one rank's inbound lists overflow).  A tiling of
+    a random genome at the end provides real overlaps."""
+    rng = np.random.default_rng(seed)
+    acgt = np.frombuffer(b"ACGT", dtype=np.uint8)
+
+    def rnd(n):
+        return acgt[rng.integers(0, 4, n)].tobytes().decode()
+    rep = rnd(300)
+    reads = [("rep%d" % i, "".join(rep + rnd(75) for _ in range(4))) for i in range(30)]
+    reads += [("pre%d" % i, rep + rnd(1200)) for i in range(60)]
+    genome = rnd(24000)
+    reads += [("til%d" % i, genome[600 * i:600 * i + 1500]) for i in range(38)]
+    return reads
+
+
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--cfg", type=int, default=2)
@@ -32,6 +51,7 @@ def main():
     ap.add_argument("--mirror", type=int, default=1)
     ap.add_argument("--edge", type=int, default=0, help="use synth.edge_mix(seed, l) instead of a config")
     ap.add_argument("--lmin", type=int, default=200, help="min_length of the --edge set")
+    ap.add_argument("--skew", type=int, default=0, help="seed of a read set whose candidates concentrate on rank 0's reads")
     ap.add_argument("--small-caps", type=int, default=0, help="1: tiny first capacities -> the collective grow-and-repeat route")
     ap.add_argument("--bad-base", type=int, default=0, help="1: one non-ACGT byte on the LAST rank: every rank must raise")
     args = ap.parse_args()
@@ -40,8 +60,8 @@ def main():
     torch.cuda.set_device(local)
     dist.init_process_group("nccl", device_id=torch.device("cuda", local))
 
-    if args.edge:
-        reads = synth.edge_mix(args.edge, args.lmin)
+    if args.edge or args.skew:
+        reads = skewed_reads(args.skew) if args.skew else synth.edge_mix(args.edge, args.lmin)
         l = args.lmin
         lens = [len(s) for _, s in reads]
         ranges = multi.plan_ranges(lens, world)
@@ -94,7 +114,7 @@ def main():
     if rank == 0:
         from oracle import port
         from oracle.bruteforce import both_strand_entries
-        if args.edge:
+        if args.edge or args.skew:
             full = reads
         else:
             fb, fo, fn = synth.generate(sh)

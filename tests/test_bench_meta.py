@@ -18,15 +18,19 @@ def test_committed_traffic_capture_covers_the_hot_kernels():
     with open(newest) as f:
         cap = json.load(f)
     n_cap, stride_cap = int(cap["n_gpus"]), int(cap["anchor_stride"])
-    traffic, src = bench.ncu_traffic(n_cap, stride_cap)
+    opts_cap = list(cap.get("options", []))
+    traffic, src = bench.ncu_traffic(n_cap, stride_cap, opts_cap)
     assert traffic and src == os.path.basename(newest)
+    # ... and of the same option set (a capture of another K1 grid is not this run's)
+    t, why = bench.ncu_traffic(n_cap, stride_cap, opts_cap + ["pack_blocks_per_sm=3"])
+    assert t is None and "options" in why
     for prefixes in (("k1_pack",), ("k3_filter", "k3_probe"), ("k4a_head",), ("k4b_tail",)):
         got = [v for n, v in traffic.items() if n.startswith(prefixes)]
         assert got and all(v > 1e6 for v in got), prefixes   # bytes per launch of the bench workload
     # the match rule: a capture is only pasted onto a run of the same GPU count
     # and anchor stride; anything else reports traffic = null and says why
     for n_gpus, stride in ((n_cap + 7, stride_cap), (n_cap, stride_cap * 2), (n_cap + 1, 16)):
-        t, why = bench.ncu_traffic(n_gpus, stride)
+        t, why = bench.ncu_traffic(n_gpus, stride, opts_cap)
         assert t is None and "capture" in why, (n_gpus, stride, why)
     # the launch list and the full summary of the same round are committed beside it
     tag = src.split("_traffic.json")[0]

@@ -196,7 +196,8 @@ def _n_gpus():
                                    ["--edge", "3"], ["--cfg", "1", "--scale", "0.02", "--mirror", "0"],
                                    ["--cfg", "2", "--scale", "0.02", "--small-caps", "1"],
                                    ["--cfg", "2", "--scale", "0.01", "--bad-base", "1"],
-                                   ["--edge", "4", "--lmin", "33"], ["--edge", "5", "--lmin", "20"]])
+                                   ["--edge", "4", "--lmin", "33"], ["--edge", "5", "--lmin", "20"],
+                                   ["--skew", "7", "--lmin", "200", "--small-caps", "1"]])
 def test_sharded_job_matches_oracle(extra):
     n = _n_gpus()
     if n < 2:

@@ -86,16 +86,17 @@ def full_summary(rep: str, dst_csv: str, dst_json: str) -> None:
             a["us"] += val("gpu__time_duration.sum")
     res = {k: {"launches": a["launches"], "dram_bytes_per_launch": a["dram_bytes"] / a["launches"],
                "us_per_launch_under_ncu": a["us"] / a["launches"]} for k, a in per.items()}
-    meta = {"n_gpus": 1, "anchor_stride": 64}
+    meta = {"n_gpus": 1, "anchor_stride": 64, "options": []}
     bj = os.path.join(os.path.dirname(rep), "bench.json")
     try:   # the bench line of the same visit says which workload the capture saw
         with open(bj) as f:
             line = json.loads([l for l in f if l.startswith("{")][-1])
-        meta = {"n_gpus": int(line["n_gpus"]), "anchor_stride": int(line["anchor_stride"])}
+        meta = {"n_gpus": int(line["n_gpus"]), "anchor_stride": int(line["anchor_stride"]),
+                "options": list(line.get("options", []))}
     except Exception:
         pass
     with open(dst_json, "w") as f:
-        json.dump({"n_gpus": meta["n_gpus"], "anchor_stride": meta["anchor_stride"], "source": "ncu --set full --clock-control none, python bench.py --steps 2 --warmup 3 --no-cpu "
+        json.dump({"n_gpus": meta["n_gpus"], "anchor_stride": meta["anchor_stride"], "options": meta.get("options", []), "source": "ncu --set full --clock-control none, python bench.py --steps 2 --warmup 3 --no-cpu "
                              "(BASELINE configs[1]); dram__bytes_read.sum + dram__bytes_write.sum per launch",
                    "kernels": res}, f, indent=1)
         f.write("\n")
