@@ -148,6 +148,56 @@ public:
         return a;
     }
 
+    // optional device post-pass: the edge list of build_assembly_graph (phasm/assembly_graph.py:136-179) over
+    // the rows of the last call / the rows kept by the last filter_rows call (ovl_build_graph).  Returns
+    // (edges, stats) like phasm_b200.overlapper.ExactOverlapper.build_graph: a structured numpy array
+    // (u, v, edge_len, overlap_len, first_seq) sorted by (u, v), and networkx's node / edge counts.
+    py::tuple build_graph(bool filtered) {
+        const ovl_edge* edges = nullptr;
+        uint64_t n = 0;
+        ovl_graph_stats gs;
+        check(ovl_build_graph(ctx_, filtered ? 1 : 0, &edges, &n, &gs));
+        py::module_ np = py::module_::import("numpy");
+        py::list fields;
+        fields.append(py::make_tuple("u", "<u4"));
+        fields.append(py::make_tuple("v", "<u4"));
+        fields.append(py::make_tuple("edge_len", "<i4"));
+        fields.append(py::make_tuple("overlap_len", "<u4"));
+        fields.append(py::make_tuple("first_seq", "<u8"));
+        py::object dtype = np.attr("dtype")(fields);
+        py::bytes raw(n ? reinterpret_cast<const char*>(edges) : "", (size_t)n * sizeof(ovl_edge));
+        py::object arr = np.attr("frombuffer")(raw, dtype).attr("copy")();
+        py::dict d;
+        d["rows_in"] = gs.rows_in;
+        d["rows_overlap"] = gs.rows_overlap;
+        d["n_edges"] = gs.n_edges;
+        d["n_nodes"] = gs.n_nodes;
+        d["ms_device"] = gs.ms_device;
+        return py::make_tuple(arr, d);
+    }
+
+    // entry ids ("name+" / "name-" for reads) and lengths, in entry order: the node names and read
+    // lengths the graph builder needs (phasm/assembly_graph.py of this repo)
+    py::list ids() const {
+        py::list out;
+        const uint32_t m = (uint32_t)size();
+        for (uint32_t i = 0; i < m; ++i) {
+            const char* p = nullptr;
+            size_t n = 0;
+            check(ovl_entry_id(ctx_, i, &p, &n));
+            out.append(py::str(p ? p : "", n));
+        }
+        return out;
+    }
+
+    py::array_t<uint32_t> lengths() const {
+        const uint32_t m = (uint32_t)size();
+        py::array_t<uint32_t> a((py::ssize_t)m);
+        uint32_t* d = a.mutable_data();
+        for (uint32_t i = 0; i < m; ++i) check(ovl_entry_length(ctx_, i, d + i));
+        return a;
+    }
+
     uint64_t run_only(unsigned min_length) {
         const ovl_row* rows = nullptr;
         uint64_t n = 0;
@@ -218,6 +268,9 @@ PYBIND11_MODULE(overlapper, m) {
              py::arg("min_read_length") = 0, py::arg("min_overlap_length") = 0,
              py::arg("max_overhang_abs") = py::int_(1000), py::arg("max_overhang_rel") = 0.8,
              py::arg("collapse_pairs") = false)
+        .def("build_graph", &Overlapper::build_graph, py::arg("filtered") = true)
+        .def("ids", &Overlapper::ids)
+        .def("lengths", &Overlapper::lengths)
         .def("stats", &Overlapper::stats)
         .def("__len__", &Overlapper::size);
 }

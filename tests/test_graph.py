@@ -258,3 +258,45 @@ def test_device_graph_of_a_pass_without_rows_is_empty(ov):
     assert got.shape == (0, 5) and fst["rows_kept"] == 0
     edges, st = ov.build_graph(filtered=True)
     assert len(edges) == 0 and st["rows_in"] == 0 and st["n_edges"] == 0 and st["n_nodes"] == 0
+
+
+@pytest.mark.gpu
+def test_drop_in_module_drives_overlap_filter_and_graph(gold):
+    """f3 -> f4 through the drop-in extension module itself (`phasm.overlapper.ExactOverlapper`, the object
+    the reference's `overlap` stage creates: src/phasm.cpp:8-18): overlaps, the layout filters, then
+    `phasm.assembly_graph.build_assembly_graph` (reference: phasm/assembly_graph.py:136-179) -- against the
+    golden graphs made with the reference's own function (tests/golden/graph.json)."""
+    import __graft_entry__ as g
+    g.build_library()
+    g.build_pybind()
+    import phasm.overlapper as mod
+    from phasm import assembly_graph as AG
+    done = 0
+    for key in sorted(helpers.MID_SPECS)[:3]:
+        cs = [c for c in gold["chain"] if c["case"] == key and c["opt"] is not None]
+        if not cs:
+            continue
+        reads, l = helpers.mid_input(key)
+        ext = mod.ExactOverlapper()
+        for name, seq in reads:
+            ext.add_read(name, seq)
+        rows = ext.overlaps_arrays(l)
+        assert len(rows) == len(helpers.load_mid()[key])
+        assert len(ext) == 2 * len(reads) and ext.ids()[:2] == [reads[0][0] + "+", reads[0][0] + "-"]
+        assert ext.lengths().tolist() == [len(s) for _, s in reads for _ in (0, 1)]
+        for c in cs:
+            kept = ext.filter_rows(**filter_kwargs(c["opt"]))
+            arr, st = ext.build_graph(filtered=True)
+            edges = device_edges(arr)
+            assert edges == sorted(edges) and st["rows_in"] == len(kept)
+            check_graph(edges, st["n_nodes"], c["graph"], (key, c["opt"]))
+            dg = AG.build_assembly_graph(ext, filtered=True)
+            assert dg.number_of_nodes() == c["graph"]["n_nodes"] and dg.number_of_edges() == c["graph"]["n_edges"]
+            ids = ext.ids()
+            first = min(edges, key=lambda e: e[4]) if edges else None
+            if first:
+                u, v = next(iter(dg.edges()))
+                assert (u, v) == (ids[first[0]], ids[first[1]])      # networkx insertion order
+                assert dg[u][v] == {"weight": first[2], "overlap_len": first[3]}
+            done += 1
+    assert done >= 3
