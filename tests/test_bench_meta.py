@@ -72,3 +72,24 @@ def test_full_reference_digest_is_order_independent_and_matches_the_golden_helpe
         assert g["t2_equals_t0"] and g["t0"]["rows"] > 0 and len(g["t0"]["sha256"]) == 64
     rec = bench.recorded_full_reference()
     assert rec and rec["forward_bases"] == 414000000 and rec["cores_used"] == 1
+
+
+def test_reference_arm_times_the_cpu_baseline_sample_whatever_the_step_count():
+    """VERDICT r2 "next" 6c: `--impl reference` and the GPU arm's `cpu_baseline` leg time the SAME fixed
+    genome-window sample (--cpu-sample, 4 Mbases), independent of --steps / --warmup, so one record never
+    carries two different CPU numbers (and the GPU arm's `equal_work` key compares like with like)."""
+    sys.path.insert(0, ROOT)
+    import bench
+    from phasm_b200 import synth
+    shape = bench.workload_shape(1)
+    _, off, names, _ = synth.window_subsample(shape, 4_000_000)
+    r = subprocess.run([sys.executable, os.path.join(ROOT, "bench.py"), "--impl", "reference", "--steps", "1",
+                        "--warmup", "0"], capture_output=True, text=True, timeout=600)
+    assert r.returncode == 0, r.stderr[-2000:]
+    line = json.loads(r.stdout.strip().splitlines()[-1])
+    assert line["impl"] == "reference" and line["config"]["reads"] == len(names)
+    assert line["config"]["forward_bases"] == int(off[-1])
+    assert line["cpu_baseline"]["sample"].startswith("%d reads / %d forward bases" % (len(names), int(off[-1])))
+    assert line["e2e"]["value"] == line["value"] and line["e2e"]["h2d_bytes_per_step"] == 0
+    src = open(os.path.join(ROOT, "bench.py")).read()
+    assert '"equal_work"' in src and "args.steps + args.warmup" not in src
