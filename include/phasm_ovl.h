@@ -72,9 +72,9 @@ typedef struct {
     float ms_h2d, ms_pack, ms_anchor, ms_scan, ms_sort, ms_verify, ms_emit, ms_d2h;
     float ms_device;           /* pack..emit: ASCII resident in HBM -> rows resident      */
     float ms_total;            /* h2d..d2h                                                */
-    uint32_t radix_fallback;   /* always 0 since round 2 (big buckets are sorted on the   */
-                               /* device by k7_sort_big); kept for layout compatibility   */
-    uint32_t big_buckets;      /* A entries with more than 256 hit keys                   */
+    uint32_t big_buckets;      /* A entries with more than 256 hit keys (sorted on the    */
+                               /* device by k7_sort_big; there is no fallback path)       */
+    uint32_t reserved0;        /* 0 (keeps the 64-bit fields below aligned)               */
     uint64_t scan_survivors;   /* probes that passed the scan's bit filter                */
     uint64_t rows_local;       /* rows this rank emitted (multi-GPU: before the gather)   */
     float ms_gather;           /* multi-GPU: rows of all ranks into rank 0's HBM          */

@@ -32,7 +32,7 @@ class OvlStats(Structure):
                 [("verified", c_uint64), ("hits_sent", c_uint64), ("hits_received", c_uint64)] +
                 [(n, c_float) for n in ("ms_h2d", "ms_pack", "ms_anchor", "ms_scan", "ms_sort",
                                         "ms_verify", "ms_emit", "ms_d2h", "ms_device", "ms_total")] +
-                [("radix_fallback", c_uint32), ("big_buckets", c_uint32),
+                [("big_buckets", c_uint32), ("reserved0", c_uint32),
                  ("scan_survivors", c_uint64), ("rows_local", c_uint64),
                  ("ms_gather", c_float), ("ms_exposed", c_float)])
 
